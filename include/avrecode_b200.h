@@ -1,0 +1,167 @@
+/* avrecode_b200.h -- C ABI of the B200-native avrecode hot path (libavrecode_b200.so).
+ *
+ * Drop-in boundary for ddkang/avrecode's per-bin loop.  In the reference that loop lives behind
+ * struct AVCodecHooks (ffmpeg/libavcodec/coding_hooks.h:27-57): libavcodec calls back into
+ * recode.cpp once PER BIN (get / get_bypass / get_terminate, coding_hooks.h:39-48) and once per
+ * residual block (begin_sub_mb / begin_coding_type / end_coding_type, :27-37).  A device cannot be
+ * called per bin, so this ABI moves the boundary up one level: the host hands over whole CABAC
+ * slice payloads plus the few slice-header facts the syntax walk needs, and the library runs
+ *   CABAC decode -> H.264 slice_data state machine -> avrecode model -> range coder   (compress)
+ * and its exact inverse (decompress) in sm_100a kernels.  Each entry point cites what it replaces.
+ *
+ * Conventions: plain pointers and sizes, no C++/torch types; every function returns 0 or a
+ * negative AVR_ERR_* code and never throws; per-slice problems are reported in
+ * avr_slice_result.status (the host then emits skip_coded + literal, exactly like
+ * recode.cpp:1289-1296); a context is bound to one CUDA device and is single-caller, different
+ * contexts may be used concurrently from different threads.  There is NO CPU fallback: without a
+ * usable CUDA device avr_create fails with AVR_ERR_NO_DEVICE.
+ */
+#ifndef AVRECODE_B200_H
+#define AVRECODE_B200_H
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define AVR_ABI_VERSION 1
+
+/* slice_type % 5 (H.264 7.4.3); SP/SI are reported unsupported */
+#define AVR_SLICE_P 0
+#define AVR_SLICE_B 1
+#define AVR_SLICE_I 2
+
+/* avr_slice_desc.flags */
+#define AVR_SLICE_TRANSFORM_8X8        0x01 /* pps.transform_8x8_mode          (h264_cabac.c:1930) */
+#define AVR_SLICE_DIRECT_8X8_INFERENCE 0x02 /* sps.direct_8x8_inference_flag   (h264.h:1165-1177)  */
+#define AVR_SLICE_NEW_PICTURE          0x04 /* frame_spec hook fires before this slice (h264_slice.c:568-573) */
+#define AVR_SLICE_MBAFF                0x08 /* unsupported on device -> status AVR_SLICE_UNSUPPORTED */
+#define AVR_SLICE_FIELD                0x10 /* unsupported on device */
+#define AVR_SLICE_NEW_MODEL            0x20 /* chunk boundary: a fresh h264_model (recode.cpp:618-1059)
+                                               -- estimators {1,1}, both FrameBuffers empty -- starts here.
+                                               Reference-parity ("file") mode sets it on the first slice of a
+                                               file only; chunk mode sets it on every slice. */
+
+/* One CABAC slice payload.  Replaces the arguments of CABACCodingHooks.init_decoder
+ * (coding_hooks.h:41: buf,size) plus the H264SliceContext/H264Context fields the reference's
+ * walker reads through container_of (h264_slice.c:2357-2368, h264_cabac.c:1267-1286). */
+typedef struct avr_slice_desc {
+  uint64_t in_off;        /* compress: offset of the slice_data payload in `in`; decompress: offset of Block.cabac */
+  uint32_t in_size;       /* bytes at in_off */
+  uint32_t payload_size;  /* Recoded.Block.size == `size` of init_decoder (bytes of slice_data) */
+  uint32_t first_mb;      /* first_mb_in_slice */
+  uint16_t mb_width;      /* h->mb_width  */
+  uint16_t mb_height;     /* h->mb_height */
+  int32_t  frame_num;     /* h->frame_num, key of the FrameBuffer flip (recode.cpp:824-843) */
+  uint8_t  slice_type;    /* AVR_SLICE_P/B/I (sl->slice_type_nos) */
+  uint8_t  cabac_init_idc;
+  int8_t   slice_qp;      /* sl->qscale at slice start */
+  uint8_t  num_ref_idx_l0;/* sl->ref_count[0] */
+  uint8_t  num_ref_idx_l1;/* sl->ref_count[1] */
+  uint8_t  chroma_format_idc; /* 1 = 4:2:0 (the only format the kernels walk) */
+  uint8_t  flags;         /* AVR_SLICE_* */
+  uint8_t  reserved;
+} avr_slice_desc;
+
+/* avr_slice_result.status */
+#define AVR_SLICE_OK           0
+#define AVR_SLICE_UNSUPPORTED  1 /* MBAFF/field/I_PCM/4:2:2/4:4:4/SP/SI: leave the slice as a literal */
+#define AVR_SLICE_CORRUPT      2 /* syntax walk failed (overrun, illegal value) */
+#define AVR_SLICE_OVERFLOW     3 /* output did not fit its slot */
+
+typedef struct avr_slice_result {
+  uint64_t out_off;   /* offset of this slice's output in the buffer returned by the call */
+  uint32_t out_size;  /* compress: bytes of Block.cabac; decompress: bytes of rebuilt slice_data */
+  int32_t  status;    /* AVR_SLICE_* */
+  uint32_t n_mbs;     /* macroblocks walked */
+  uint32_t reserved;
+  uint64_t n_bins;    /* CABAC bins decoded (compress) / rebuilt (decompress) */
+} avr_slice_result;
+
+typedef struct avr_config {
+  int32_t abi_version;     /* AVR_ABI_VERSION */
+  int32_t device;          /* CUDA device ordinal */
+  int32_t warps_per_block; /* 0 = default */
+  int32_t reserved;
+} avr_config;
+
+typedef struct avr_ctx avr_ctx;
+
+#define AVR_OK                 0
+#define AVR_ERR_NO_DEVICE     -1 /* no CUDA device / driver: there is no CPU fallback */
+#define AVR_ERR_CUDA          -2
+#define AVR_ERR_ARG           -3
+#define AVR_ERR_NOMEM         -4
+#define AVR_ERR_FORMAT        -5 /* container / bitstream cannot be parsed */
+#define AVR_ERR_STATE         -6 /* staged call sequence violated */
+
+const char* avr_strerror(int code);
+int  avr_abi_version(void);
+
+/* Lifetime.  Replaces av_decoder<Driver> owning the AVCodecHooks table (recode.cpp:212-229). */
+int  avr_create(const avr_config* cfg, avr_ctx** out);
+void avr_destroy(avr_ctx* ctx);
+
+/* One-shot calls with HOST buffers (H2D, kernel, D2H inside).
+ * avr_compress replaces compressor::cabac_decoder (recode.cpp:1134-1268): for each slice the
+ * payload's bins are decoded and re-coded with the model; result i is Block.cabac of slice i.
+ * avr_decompress replaces decompressor::cabac_decoder (recode.cpp:1411-1520): for each slice
+ * Block.cabac is decoded with the model and the original slice_data bytes are rebuilt by the
+ * device CABAC encoder (cabac_code.h:16-86), trailing lone 0x80 already dropped (:1501-1505).
+ * `*out` points into context-owned pinned memory valid until the next call on `ctx`. */
+int  avr_compress(avr_ctx* ctx, const avr_slice_desc* descs, int n_slices,
+                  const uint8_t* in, uint64_t in_bytes,
+                  avr_slice_result* results, const uint8_t** out, uint64_t* out_bytes);
+int  avr_decompress(avr_ctx* ctx, const avr_slice_desc* descs, int n_slices,
+                    const uint8_t* in, uint64_t in_bytes,
+                    avr_slice_result* results, const uint8_t** out, uint64_t* out_bytes);
+
+/* Staged form of the same work, for pipelines that keep inputs resident in HBM:
+ *   avr_stage   copies descs + input bytes to the device (H2D) and sizes the output slots;
+ *   avr_launch  enqueues the kernels on the context's stream (direction 0 = compress, 1 = decompress);
+ *               may be called repeatedly on the same staged input;
+ *   avr_sync    waits for the stream;
+ *   avr_collect copies results + output bytes back (D2H) and compacts them.
+ * avr_last_kernel_ms returns the CUDA-event duration of the most recent avr_launch's hot kernel
+ * measured on the context's own stream (valid after avr_sync). */
+int  avr_stage(avr_ctx* ctx, const avr_slice_desc* descs, int n_slices, const uint8_t* in, uint64_t in_bytes);
+int  avr_launch(avr_ctx* ctx, int direction);
+int  avr_sync(avr_ctx* ctx);
+int  avr_collect(avr_ctx* ctx, avr_slice_result* results, const uint8_t** out, uint64_t* out_bytes);
+int  avr_last_kernel_ms(avr_ctx* ctx, float* ms);
+int  avr_launch_count(avr_ctx* ctx, uint64_t* n_launches); /* kernels launched by this context so far */
+int  avr_flush_l2(avr_ctx* ctx);                           /* bench hygiene: write > L2-size scratch */
+
+/* ---- host side: slice index + recode.proto container (no GPU needed) --------------------------
+ * avr_index_h264 replaces what the reference gets from running libavcodec over the file
+ * (recode.cpp:114-134 + find_next_coded_block_and_emit_literal :1275-1297): it scans an Annex-B
+ * H.264 byte stream, parses SPS/PPS/slice headers and returns one entry per CABAC slice payload in
+ * file order.  recodable == 0 marks payloads the reference would emit as skip_coded (NAL-escaped
+ * payload, size < 8, CAVLC never listed). */
+typedef struct avr_index_entry {
+  avr_slice_desc desc;     /* in_off = payload offset in the file, in_size = payload_size */
+  int32_t  recodable;
+  int32_t  nal_type;
+} avr_index_entry;
+
+int  avr_index_h264(const uint8_t* file, uint64_t file_bytes, avr_index_entry** entries, int* n_entries);
+
+/* chunking mode of the container produced by avr_file_compress */
+#define AVR_MODE_FILE   0  /* reference parity: one model for the whole file -- output is byte-identical
+                              to `recode compress` of the reference (recode.cpp:1115-1125) */
+#define AVR_MODE_SLICE  1  /* B200 format: model reset per slice (every slice is a chunk); recorded in
+                              Recoded.Metadata.version = "avr-b200/slice" */
+
+/* recode compress / decompress (recode.cpp:1102-1309, 1312-1591) on in-memory files.
+ * Output buffers are malloc'ed by the library; release with avr_free. */
+int  avr_file_compress(avr_ctx* ctx, const uint8_t* file, uint64_t file_bytes, int mode,
+                       uint8_t** rec, uint64_t* rec_bytes);
+int  avr_file_decompress(avr_ctx* ctx, const uint8_t* rec, uint64_t rec_bytes,
+                         uint8_t** file, uint64_t* file_bytes);
+void avr_free(void* p);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* AVRECODE_B200_H */
