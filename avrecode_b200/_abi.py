@@ -1,0 +1,69 @@
+"""ctypes mirror of include/avrecode_b200.h (struct layouts + constants).
+
+Shared by the product binding (avrecode_b200/api.py) and by the test-side oracle binding
+(tests/oracle_binding.py); contains no algorithm."""
+import ctypes as C
+
+AVR_SLICE_P, AVR_SLICE_B, AVR_SLICE_I = 0, 1, 2
+AVR_SLICE_TRANSFORM_8X8 = 0x01
+AVR_SLICE_DIRECT_8X8_INFERENCE = 0x02
+AVR_SLICE_NEW_PICTURE = 0x04
+AVR_SLICE_MBAFF = 0x08
+AVR_SLICE_FIELD = 0x10
+AVR_SLICE_NEW_MODEL = 0x20
+
+AVR_SLICE_OK, AVR_SLICE_UNSUPPORTED, AVR_SLICE_CORRUPT, AVR_SLICE_OVERFLOW = 0, 1, 2, 3
+AVR_MODE_FILE, AVR_MODE_SLICE = 0, 1
+
+AVR_OK = 0
+AVR_ERR_NO_DEVICE, AVR_ERR_CUDA, AVR_ERR_ARG, AVR_ERR_NOMEM, AVR_ERR_FORMAT, AVR_ERR_STATE = -1, -2, -3, -4, -5, -6
+
+
+class SliceDesc(C.Structure):
+    _fields_ = [
+        ("in_off", C.c_uint64),
+        ("in_size", C.c_uint32),
+        ("payload_size", C.c_uint32),
+        ("first_mb", C.c_uint32),
+        ("mb_width", C.c_uint16),
+        ("mb_height", C.c_uint16),
+        ("frame_num", C.c_int32),
+        ("slice_type", C.c_uint8),
+        ("cabac_init_idc", C.c_uint8),
+        ("slice_qp", C.c_int8),
+        ("num_ref_idx_l0", C.c_uint8),
+        ("num_ref_idx_l1", C.c_uint8),
+        ("chroma_format_idc", C.c_uint8),
+        ("flags", C.c_uint8),
+        ("reserved", C.c_uint8),
+    ]
+
+
+class SliceResult(C.Structure):
+    _fields_ = [
+        ("out_off", C.c_uint64),
+        ("out_size", C.c_uint32),
+        ("status", C.c_int32),
+        ("n_mbs", C.c_uint32),
+        ("reserved", C.c_uint32),
+        ("n_bins", C.c_uint64),
+    ]
+
+
+class Config(C.Structure):
+    _fields_ = [("abi_version", C.c_int32), ("device", C.c_int32), ("warps_per_block", C.c_int32), ("reserved", C.c_int32)]
+
+
+class IndexEntry(C.Structure):
+    _fields_ = [("desc", SliceDesc), ("recodable", C.c_int32), ("nal_type", C.c_int32)]
+
+
+assert C.sizeof(SliceDesc) == 40, C.sizeof(SliceDesc)
+assert C.sizeof(SliceResult) == 32
+assert C.sizeof(IndexEntry) == 48
+
+
+def copy_desc(d):
+    out = SliceDesc()
+    C.memmove(C.byref(out), C.byref(d), C.sizeof(SliceDesc))
+    return out
