@@ -1,0 +1,72 @@
+// avr_emu.cpp -- HOST EMULATION of the device code, for debugging in the GPU-less dev container.
+// TEST INFRASTRUCTURE ONLY: compiles avrecode_b200/csrc/avr_core.cuh + avr_job.cuh as plain C++
+// (one emulated lane) behind the same call shape as the oracle's C entry points, so that the exact
+// device logic can be diffed against the oracle and the reference on the CPU.  It is never linked
+// into libavrecode_b200.so and is not a fallback: the product fails loudly without a CUDA device.
+#define AVR_HOST_EMULATION 1
+#include <stdlib.h>
+#include <string.h>
+#include <vector>
+#include "../../avrecode_b200/csrc/avr_job.cuh"
+
+using namespace avr;
+
+template <class Dir>
+static int run(const avr_slice_desc* descs, int n, const uint8_t* in, uint64_t in_bytes, avr_slice_result* res,
+               uint8_t** out, uint64_t* out_bytes) {
+  std::vector<SliceIO> ios(n);
+  uint64_t out_total = 0;
+  int max_mbw = 1; uint32_t max_frame = 0;
+  for (int i = 0; i < n; i++) {
+    ios[i].in_off = descs[i].in_off; ios[i].in_size = descs[i].in_size;
+    ios[i].out_off = out_total;
+    ios[i].out_cap = Dir::kDecompress ? descs[i].payload_size + 64 : descs[i].in_size + descs[i].in_size / 8 + 256;
+    out_total += ios[i].out_cap;
+    if (descs[i].mb_width > max_mbw) max_mbw = descs[i].mb_width;
+    uint32_t fb = uint32_t(descs[i].mb_width) * descs[i].mb_height * NNZ_STRIDE;
+    if (fb > max_frame) max_frame = fb;
+    if (descs[i].in_off + descs[i].in_size > in_bytes) return AVR_ERR_ARG;
+  }
+  std::vector<uint8_t> arena(out_total + 16);
+  std::vector<uint8_t> workspace(size_t(MODEL_COUNTERS) * 2 + 2 * size_t(max_frame) + 64);
+  SharedTables tab;
+  fill_shared_tables(&tab, 0, 1);
+  WarpState* ws = new WarpState();
+  std::vector<MbCtx> row(max_mbw);
+  JobArgs a{descs, ios.data(), in, arena.data(), res, workspace.data()};
+  int i = 0;
+  while (i < n) {
+    int j = i + 1;
+    while (j < n && !(descs[j].flags & AVR_SLICE_NEW_MODEL)) j++;
+    JobDesc job;
+    job.first_slice = uint32_t(i); job.n_slices = uint32_t(j - i);
+    job.model_off = 0; job.nnz_off = uint64_t(MODEL_COUNTERS) * 2; job.nnz_frame_bytes = max_frame; job.reserved = 0;
+    run_job<Dir>(a, job, &tab, ws, row.data(), 0);
+    i = j;
+  }
+  delete ws;
+  // compact
+  std::vector<uint8_t> all;
+  for (int k = 0; k < n; k++) {
+    uint64_t off = res[k].out_off;
+    res[k].out_off = all.size();
+    if (res[k].status == AVR_SLICE_OK) all.insert(all.end(), arena.begin() + off, arena.begin() + off + res[k].out_size);
+    else res[k].out_size = 0;
+  }
+  *out_bytes = all.size();
+  *out = static_cast<uint8_t*>(malloc(all.size() ? all.size() : 1));
+  if (!all.empty()) memcpy(*out, all.data(), all.size());
+  return AVR_OK;
+}
+
+extern "C" {
+int avr_emu_compress(const avr_slice_desc* descs, int n, const uint8_t* in, uint64_t in_bytes, avr_slice_result* res,
+                     uint8_t** out, uint64_t* out_bytes) {
+  return run<Compress>(descs, n, in, in_bytes, res, out, out_bytes);
+}
+int avr_emu_decompress(const avr_slice_desc* descs, int n, const uint8_t* in, uint64_t in_bytes, avr_slice_result* res,
+                       uint8_t** out, uint64_t* out_bytes) {
+  return run<Decompress>(descs, n, in, in_bytes, res, out, out_bytes);
+}
+void avr_emu_free(void* p) { free(p); }
+}
