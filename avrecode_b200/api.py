@@ -1,0 +1,208 @@
+"""ctypes binding of include/avrecode_b200.h.
+
+Mirrors the reference's driver surface for this path: Context.file_compress / file_decompress are
+`recode compress` / `recode decompress` (recode.cpp:1102-1309, 1312-1591) on in-memory files;
+Context.compress / decompress are the slice-batch calls that replace the per-slice
+compressor::cabac_decoder / decompressor::cabac_decoder objects (recode.cpp:1134-1268, 1411-1520)."""
+import ctypes as C
+import os
+
+from . import _abi
+from ._abi import SliceDesc, SliceResult, Config, IndexEntry
+
+MODE_FILE, MODE_SLICE = _abi.AVR_MODE_FILE, _abi.AVR_MODE_SLICE
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_lib = None
+
+
+class AvrError(RuntimeError):
+    def __init__(self, code, what):
+        self.code = code
+        super().__init__("%s: %s" % (what, _strerror(code)))
+
+
+class NoDeviceError(AvrError):
+    pass
+
+
+def lib_path():
+    return os.path.join(_HERE, "libavrecode_b200.so")
+
+
+def load_library():
+    """Loads libavrecode_b200.so (built in-tree by avrecode_b200.build / __graft_entry__.build)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    path = lib_path()
+    if not os.path.exists(path):
+        raise FileNotFoundError("%s is missing: run `python -m avrecode_b200.build` (there is no fallback path)" % path)
+    lib = C.CDLL(path)
+    u8p = C.POINTER(C.c_uint8)
+    lib.avr_strerror.restype = C.c_char_p
+    lib.avr_strerror.argtypes = [C.c_int]
+    lib.avr_abi_version.restype = C.c_int
+    lib.avr_create.argtypes = [C.POINTER(Config), C.POINTER(C.c_void_p)]
+    lib.avr_destroy.argtypes = [C.c_void_p]
+    lib.avr_destroy.restype = None
+    batch = [C.c_void_p, C.POINTER(SliceDesc), C.c_int, C.c_void_p, C.c_uint64, C.POINTER(SliceResult),
+             C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]
+    lib.avr_compress.argtypes = batch
+    lib.avr_decompress.argtypes = batch
+    lib.avr_stage.argtypes = [C.c_void_p, C.POINTER(SliceDesc), C.c_int, C.c_void_p, C.c_uint64]
+    lib.avr_launch.argtypes = [C.c_void_p, C.c_int]
+    lib.avr_sync.argtypes = [C.c_void_p]
+    lib.avr_collect.argtypes = [C.c_void_p, C.POINTER(SliceResult), C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]
+    lib.avr_last_kernel_ms.argtypes = [C.c_void_p, C.POINTER(C.c_float)]
+    lib.avr_launch_count.argtypes = [C.c_void_p, C.POINTER(C.c_uint64)]
+    lib.avr_flush_l2.argtypes = [C.c_void_p]
+    lib.avr_index_h264.argtypes = [C.c_void_p, C.c_uint64, C.POINTER(C.POINTER(IndexEntry)), C.POINTER(C.c_int)]
+    lib.avr_file_compress.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]
+    lib.avr_file_decompress.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]
+    lib.avr_free.argtypes = [C.c_void_p]
+    lib.avr_free.restype = None
+    _lib = lib
+    return lib
+
+
+def _strerror(code):
+    try:
+        return load_library().avr_strerror(code).decode()
+    except Exception:  # pragma: no cover
+        return "error %d" % code
+
+
+def _check(rc, what):
+    if rc == _abi.AVR_ERR_NO_DEVICE:
+        raise NoDeviceError(rc, what)
+    if rc != 0:
+        raise AvrError(rc, what)
+
+
+def _buf(data):
+    """-> (address, length, keepalive) for bytes / bytearray / numpy / torch (CPU) buffers."""
+    if isinstance(data, (bytes, bytearray)):
+        arr = (C.c_uint8 * len(data)).from_buffer_copy(data) if isinstance(data, bytes) else (C.c_uint8 * len(data)).from_buffer(data)
+        return C.addressof(arr), len(data), arr
+    if hasattr(data, "data_ptr"):  # torch tensor (pinned host memory for the e2e path)
+        return data.data_ptr(), data.numel() * data.element_size(), data
+    if hasattr(data, "ctypes"):  # numpy
+        return data.ctypes.data, data.nbytes, data
+    raise TypeError("unsupported buffer type %r" % type(data))
+
+
+def index_h264(data):
+    """Slice index of an Annex-B H.264 stream (host only, no GPU): list of IndexEntry."""
+    lib = load_library()
+    addr, n, keep = _buf(data)
+    ents = C.POINTER(IndexEntry)()
+    cnt = C.c_int()
+    _check(lib.avr_index_h264(addr, n, C.byref(ents), C.byref(cnt)), "avr_index_h264")
+    out = []
+    for i in range(cnt.value):
+        e = IndexEntry()
+        C.memmove(C.byref(e), C.byref(ents[i]), C.sizeof(IndexEntry))
+        out.append(e)
+    if cnt.value:
+        lib.avr_free(C.cast(ents, C.c_void_p))
+    return out
+
+
+class Context:
+    """One CUDA device.  Raises NoDeviceError when there is none: no CPU fallback exists."""
+
+    def __init__(self, device=0, warps_per_sm=0):
+        self._lib = load_library()
+        cfg = Config(_abi.AVR_OK + 1, device, warps_per_sm, 0)
+        cfg.abi_version = self._lib.avr_abi_version()
+        h = C.c_void_p()
+        _check(self._lib.avr_create(C.byref(cfg), C.byref(h)), "avr_create")
+        self._h = h
+        self._keep = None
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._lib.avr_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    # ---- slice batches -------------------------------------------------------------------------
+    def _batch(self, fn, what, descs, data):
+        n = len(descs)
+        arr = (SliceDesc * n)(*descs)
+        res = (SliceResult * n)()
+        addr, nbytes, keep = _buf(data)
+        out = C.c_void_p()
+        nout = C.c_uint64()
+        _check(fn(self._h, arr, n, addr, nbytes, res, C.byref(out), C.byref(nout)), what)
+        blob = C.string_at(out, nout.value) if nout.value else b""
+        return list(res), blob
+
+    def compress(self, descs, data):
+        """-> (results, blob); Block.cabac of slice i = blob[r.out_off : r.out_off + r.out_size]."""
+        return self._batch(self._lib.avr_compress, "avr_compress", descs, data)
+
+    def decompress(self, descs, data):
+        return self._batch(self._lib.avr_decompress, "avr_decompress", descs, data)
+
+    # ---- staged pipeline (inputs resident in HBM) ----------------------------------------------
+    def stage(self, descs, data):
+        n = len(descs)
+        arr = (SliceDesc * n)(*descs)
+        addr, nbytes, keep = _buf(data)
+        self._keep = (arr, keep)
+        self._n = n
+        _check(self._lib.avr_stage(self._h, arr, n, addr, nbytes), "avr_stage")
+
+    def launch(self, direction):
+        _check(self._lib.avr_launch(self._h, direction), "avr_launch")
+
+    def sync(self):
+        _check(self._lib.avr_sync(self._h), "avr_sync")
+
+    def collect(self, copy=True):
+        res = (SliceResult * self._n)()
+        out = C.c_void_p()
+        nout = C.c_uint64()
+        _check(self._lib.avr_collect(self._h, res, C.byref(out), C.byref(nout)), "avr_collect")
+        blob = C.string_at(out, nout.value) if (copy and nout.value) else b""
+        return list(res), blob
+
+    def last_kernel_ms(self):
+        ms = C.c_float()
+        _check(self._lib.avr_last_kernel_ms(self._h, C.byref(ms)), "avr_last_kernel_ms")
+        return ms.value
+
+    def launch_count(self):
+        n = C.c_uint64()
+        _check(self._lib.avr_launch_count(self._h, C.byref(n)), "avr_launch_count")
+        return n.value
+
+    def flush_l2(self):
+        _check(self._lib.avr_flush_l2(self._h), "avr_flush_l2")
+
+    # ---- whole files (recode compress / decompress) ---------------------------------------------
+    def file_compress(self, data, mode=MODE_SLICE):
+        addr, n, keep = _buf(data)
+        out = C.c_void_p()
+        nout = C.c_uint64()
+        _check(self._lib.avr_file_compress(self._h, addr, n, mode, C.byref(out), C.byref(nout)), "avr_file_compress")
+        blob = C.string_at(out, nout.value)
+        self._lib.avr_free(out)
+        return blob
+
+    def file_decompress(self, rec):
+        addr, n, keep = _buf(rec)
+        out = C.c_void_p()
+        nout = C.c_uint64()
+        _check(self._lib.avr_file_decompress(self._h, addr, n, C.byref(out), C.byref(nout)), "avr_file_decompress")
+        blob = C.string_at(out, nout.value)
+        self._lib.avr_free(out)
+        return blob

@@ -1,0 +1,66 @@
+"""Builds every native artefact in-tree (no JIT caches):
+
+  avrecode_b200/libavrecode_b200.so   CUDA kernels (sm_100a) + C ABI + host indexer/container
+  avrecode_b200/recode                drop-in CLI linked against the .so
+  oracle/_build/libavr_oracle.so      CPU restatement (test infrastructure)
+  build/libavr_emu.so                 host emulation of the device code (test infrastructure)
+  build/h264gen                       synthetic stream generator (test infrastructure)
+  oracle/_ref/*                       the unmodified reference, only where /root/reference exists
+
+Usage: python -m avrecode_b200.build [--force]
+"""
+import os
+import subprocess
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+CSRC = os.path.join(ROOT, "avrecode_b200", "csrc")
+NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
+
+
+def _newer(target, sources):
+    if not os.path.exists(target):
+        return True
+    t = os.path.getmtime(target)
+    return any(os.path.getmtime(s) > t for s in sources)
+
+
+def _run(cmd):
+    print("+", " ".join(cmd), flush=True)
+    subprocess.check_call(cmd, cwd=ROOT)
+
+
+def build(force=False, with_ref=True):
+    os.makedirs(os.path.join(ROOT, "build"), exist_ok=True)
+    os.makedirs(os.path.join(ROOT, "oracle", "_build"), exist_ok=True)
+    hdrs = [os.path.join(ROOT, "include", "avrecode_b200.h")] + [
+        os.path.join(CSRC, f) for f in ("avr_core.cuh", "avr_job.cuh", "avr_tables.h")]
+    lib = os.path.join(ROOT, "avrecode_b200", "libavrecode_b200.so")
+    lib_src = [os.path.join(CSRC, f) for f in ("avr_lib.cu", "avr_file.cpp", "h264_index.cpp")]
+    if force or _newer(lib, lib_src + hdrs):
+        _run([NVCC, "-std=c++17", *ARCH, "-lineinfo", "-O3", "-Xcompiler", "-fPIC", "-shared", "-cudart", "static",
+              "-o", lib, *lib_src])
+    cli = os.path.join(ROOT, "avrecode_b200", "recode")
+    cli_src = [os.path.join(CSRC, "recode_main.cpp")]
+    if force or _newer(cli, cli_src + [lib]):
+        _run(["g++", "-std=c++17", "-O2", "-o", cli, *cli_src, "-L" + os.path.join(ROOT, "avrecode_b200"),
+              "-lavrecode_b200", "-Wl,-rpath,$ORIGIN"])
+    ora = os.path.join(ROOT, "oracle", "_build", "libavr_oracle.so")
+    ora_src = [os.path.join(ROOT, "oracle", f) for f in ("avr_oracle_lib.cpp", "avr_oracle.hpp")]
+    if force or _newer(ora, ora_src + hdrs):
+        _run(["g++", "-std=c++14", "-O2", "-shared", "-fPIC", "-o", ora, ora_src[0]])
+    emu = os.path.join(ROOT, "build", "libavr_emu.so")
+    emu_src = [os.path.join(ROOT, "tests", "emu", "avr_emu.cpp")]
+    if force or _newer(emu, emu_src + hdrs):
+        _run(["g++", "-std=c++17", "-O2", "-shared", "-fPIC", "-o", emu, emu_src[0]])
+    gen = os.path.join(ROOT, "build", "h264gen")
+    gen_src = [os.path.join(ROOT, "tools", "h264gen.cpp"), ora_src[1]]
+    if force or _newer(gen, gen_src + hdrs):
+        _run(["g++", "-std=c++14", "-O2", "-o", gen, gen_src[0]])
+    if with_ref and os.path.isdir("/root/reference/ffmpeg/libavcodec"):
+        _run(["bash", os.path.join(ROOT, "oracle", "build_ref.sh")])
+
+
+if __name__ == "__main__":
+    build(force="--force" in sys.argv)

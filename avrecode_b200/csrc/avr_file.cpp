@@ -1,0 +1,276 @@
+// avr_file.cpp -- host side of `recode compress | decompress`: recode.proto container codec and the
+// drivers that turn a file into slice batches for the device and back.
+//
+// Mirrors, on the host, compressor::run / find_next_coded_block_and_emit_literal
+// (recode.cpp:1115-1125, 1275-1297) and decompressor::run / read_packet / recognize_coded_block
+// (recode.cpp:1338-1409, 1546-1573).  The container is the reference's Recoded message
+// (recode.proto:1-20) written in field-number order like libprotobuf does, so AVR_MODE_FILE output
+// is byte-identical to the reference's.  libprotobuf is not used (it is not on the box).
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+#include <string>
+#include <vector>
+#include "../../include/avrecode_b200.h"
+
+namespace {
+
+const char kSliceModeTag[] = "avr-b200/slice";
+
+void put_varint(std::string& o, uint64_t v) {
+  while (v >= 0x80) { o.push_back(char((v & 0x7F) | 0x80)); v >>= 7; }
+  o.push_back(char(v));
+}
+void put_len(std::string& o, int field, const uint8_t* p, size_t n) {
+  put_varint(o, (uint64_t(field) << 3) | 2);
+  put_varint(o, n);
+  o.append(reinterpret_cast<const char*>(p), n);
+}
+void put_var(std::string& o, int field, uint64_t v) { put_varint(o, (uint64_t(field) << 3) | 0); put_varint(o, v); }
+
+bool get_varint(const uint8_t*& p, const uint8_t* e, uint64_t* v) {
+  uint64_t r = 0;
+  for (int sh = 0; p < e && sh < 64; sh += 7) {
+    uint8_t b = *p++;
+    r |= uint64_t(b & 0x7F) << sh;
+    if (!(b & 0x80)) { *v = r; return true; }
+  }
+  return false;
+}
+
+struct Block {   // Recoded.Block (recode.proto:9-18)
+  bool has_size = false, has_literal = false, has_skip = false, has_cabac = false, has_parity = false, has_last = false;
+  int64_t size = 0;
+  bool skip = false, parity = false;
+  const uint8_t* literal = nullptr; size_t literal_n = 0;
+  const uint8_t* cabac = nullptr; size_t cabac_n = 0;
+  const uint8_t* last = nullptr; size_t last_n = 0;
+};
+
+bool parse_block(const uint8_t* p, const uint8_t* e, Block* b) {
+  while (p < e) {
+    uint64_t key;
+    if (!get_varint(p, e, &key)) return false;
+    int field = int(key >> 3), wt = int(key & 7);
+    if (wt == 0) {
+      uint64_t v;
+      if (!get_varint(p, e, &v)) return false;
+      if (field == 1) { b->size = int64_t(v); b->has_size = true; }
+      else if (field == 3) { b->skip = v != 0; b->has_skip = true; }
+      else if (field == 5) { b->parity = v != 0; b->has_parity = true; }
+    } else if (wt == 2) {
+      uint64_t n;
+      if (!get_varint(p, e, &n) || n > uint64_t(e - p)) return false;
+      if (field == 2) { b->literal = p; b->literal_n = size_t(n); b->has_literal = true; }
+      else if (field == 4) { b->cabac = p; b->cabac_n = size_t(n); b->has_cabac = true; }
+      else if (field == 6) { b->last = p; b->last_n = size_t(n); b->has_last = true; }
+      p += n;
+    } else if (wt == 1) { if (e - p < 8) return false; p += 8; }
+    else if (wt == 5) { if (e - p < 4) return false; p += 4; }
+    else return false;
+  }
+  return true;
+}
+
+bool parse_container(const uint8_t* p, size_t n, std::vector<Block>* blocks, std::string* version) {
+  const uint8_t* e = p + n;
+  while (p < e) {
+    uint64_t key;
+    if (!get_varint(p, e, &key)) return false;
+    int field = int(key >> 3), wt = int(key & 7);
+    if (wt == 2) {
+      uint64_t len;
+      if (!get_varint(p, e, &len) || len > uint64_t(e - p)) return false;
+      if (field == 2) { Block b; if (!parse_block(p, p + len, &b)) return false; blocks->push_back(b); }
+      else if (field == 1) {   // Metadata: version = field 1
+        const uint8_t* q = p; const uint8_t* qe = p + len;
+        while (q < qe) {
+          uint64_t k2;
+          if (!get_varint(q, qe, &k2)) return false;
+          if ((k2 & 7) == 2) {
+            uint64_t l2;
+            if (!get_varint(q, qe, &l2) || l2 > uint64_t(qe - q)) return false;
+            if ((k2 >> 3) == 1) version->assign(reinterpret_cast<const char*>(q), size_t(l2));
+            q += l2;
+          } else if ((k2 & 7) == 0) { uint64_t v; if (!get_varint(q, qe, &v)) return false; }
+          else return false;
+        }
+      }
+      p += len;
+    } else if (wt == 0) { uint64_t v; if (!get_varint(p, e, &v)) return false; }
+    else if (wt == 1) { if (e - p < 8) return false; p += 8; }
+    else if (wt == 5) { if (e - p < 4) return false; p += 4; }
+    else return false;
+  }
+  return true;
+}
+
+void emit_block(std::string& out, const std::string& body) {
+  put_varint(out, (2u << 3) | 2);
+  put_varint(out, body.size());
+  out.append(body);
+}
+
+int to_malloc(const std::string& s, uint8_t** p, uint64_t* n) {
+  *p = static_cast<uint8_t*>(malloc(s.size() ? s.size() : 1));
+  if (!*p) return AVR_ERR_NOMEM;
+  memcpy(*p, s.data(), s.size());
+  *n = s.size();
+  return AVR_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+void avr_free(void* p) { free(p); }
+
+int avr_file_compress(avr_ctx* ctx, const uint8_t* file, uint64_t file_bytes, int mode, uint8_t** rec, uint64_t* rec_bytes) {
+  if (!ctx || !file || !rec || !rec_bytes || (mode != AVR_MODE_FILE && mode != AVR_MODE_SLICE)) return AVR_ERR_ARG;
+  avr_index_entry* ents = nullptr;
+  int n_ents = 0;
+  int rc = avr_index_h264(file, file_bytes, &ents, &n_ents);
+  if (rc) return rc;
+  std::vector<char> coded(size_t(n_ents), 0);   // 1 = goes to the device
+  for (int i = 0; i < n_ents; i++) coded[i] = ents[i].recodable ? 1 : 0;
+  std::vector<avr_slice_result> res;
+  std::vector<int> map;
+  const uint8_t* out = nullptr;
+  uint64_t out_bytes = 0;
+  // In file mode the slices share one model, so a slice the device rejects poisons everything after
+  // it; drop it (it becomes skip_coded + literal, recode.cpp:1289-1296) and run again.
+  for (int attempt = 0; attempt < 64; attempt++) {
+    std::vector<avr_slice_desc> descs;
+    map.clear();
+    for (int i = 0; i < n_ents; i++) {
+      if (!coded[i]) continue;
+      avr_slice_desc d = ents[i].desc;
+      if (map.empty() || mode == AVR_MODE_SLICE) d.flags |= AVR_SLICE_NEW_MODEL;
+      descs.push_back(d);
+      map.push_back(i);
+    }
+    res.assign(descs.size(), avr_slice_result());
+    rc = avr_compress(ctx, descs.data(), int(descs.size()), file, file_bytes, res.data(), &out, &out_bytes);
+    if (rc) { free(ents); return rc; }
+    bool retry = false;
+    for (size_t k = 0; k < descs.size(); k++) {
+      if (res[k].status != AVR_SLICE_OK) {
+        coded[map[k]] = 0;
+        if (mode == AVR_MODE_FILE) { retry = true; break; }
+      }
+    }
+    if (!retry) break;
+  }
+  std::string o;
+  if (mode == AVR_MODE_SLICE) {
+    std::string meta;
+    put_len(meta, 1, reinterpret_cast<const uint8_t*>(kSliceModeTag), sizeof(kSliceModeTag) - 1);
+    put_len(o, 1, reinterpret_cast<const uint8_t*>(meta.data()), meta.size());
+  }
+  uint64_t prev = 0;
+  size_t k = 0;
+  for (int i = 0; i < n_ents; i++) {
+    const avr_slice_desc& d = ents[i].desc;
+    bool on_device = k < map.size() && map[k] == i;
+    bool ok = on_device && res[k].status == AVR_SLICE_OK;
+    std::string body;
+    if (ok) {
+      std::string lit;
+      put_len(lit, 2, file + prev, size_t(d.in_off - prev));
+      emit_block(o, lit);
+      put_var(body, 1, d.payload_size);
+      put_len(body, 4, out + res[k].out_off, res[k].out_size);
+      put_var(body, 5, d.payload_size & 1);
+      if (d.payload_size > 1) put_len(body, 6, file + d.in_off + d.payload_size - 1, 1);
+      prev = d.in_off + d.payload_size;
+    } else {
+      put_var(body, 1, d.payload_size);
+      put_var(body, 3, 1);
+    }
+    // field-number order inside the block: size(1) literal(2) skip_coded(3) cabac(4) parity(5) last(6)
+    if (!ok) {   // {size, skip_coded}
+      std::string b2;
+      put_var(b2, 1, d.payload_size);
+      put_var(b2, 3, 1);
+      body = b2;
+    }
+    emit_block(o, body);
+    if (on_device) k++;
+  }
+  std::string lit;
+  put_len(lit, 2, file + prev, size_t(file_bytes - prev));
+  emit_block(o, lit);
+  free(ents);
+  return to_malloc(o, rec, rec_bytes);
+}
+
+int avr_file_decompress(avr_ctx* ctx, const uint8_t* rec, uint64_t rec_bytes, uint8_t** file, uint64_t* file_bytes) {
+  if (!ctx || !rec || !file || !file_bytes) return AVR_ERR_ARG;
+  std::vector<Block> blocks;
+  std::string version;
+  if (!parse_container(rec, size_t(rec_bytes), &blocks, &version)) return AVR_ERR_FORMAT;
+  const bool slice_mode = version == kSliceModeTag;
+  if (!version.empty() && !slice_mode) return AVR_ERR_FORMAT;
+  // 1. rebuild the stream with surrogate payloads (recode.cpp:1359-1409, 1537-1544) so the slice
+  //    headers can be indexed exactly as on the compress side
+  std::string stream;
+  struct CodedRef { size_t block; uint64_t off; bool is_cabac; };
+  std::vector<CodedRef> coded;
+  for (size_t i = 0; i < blocks.size(); i++) {
+    const Block& b = blocks[i];
+    if (int(b.has_literal) + int(b.has_cabac) + int(b.has_skip) != 1) return AVR_ERR_FORMAT;   // recode.cpp:1364-1366
+    if (b.has_literal) stream.append(reinterpret_cast<const char*>(b.literal), b.literal_n);
+    else if (b.has_cabac) {
+      if (!b.has_size || b.size < 8 || b.size > (int64_t(1) << 31)) return AVR_ERR_FORMAT;   // :1377-1379, 1538-1540
+      coded.push_back(CodedRef{i, stream.size(), true});
+      stream.append(size_t(b.size), 'X');
+    } else {
+      if (!b.has_size) return AVR_ERR_FORMAT;
+      coded.push_back(CodedRef{i, 0, false});
+    }
+  }
+  avr_index_entry* ents = nullptr;
+  int n_ents = 0;
+  int rc = avr_index_h264(reinterpret_cast<const uint8_t*>(stream.data()), stream.size(), &ents, &n_ents);
+  if (rc) return rc;
+  // 2. pair index entries with coded blocks in order (recognize_coded_block, recode.cpp:1546-1573)
+  if (size_t(n_ents) != coded.size()) { free(ents); return AVR_ERR_FORMAT; }
+  std::vector<avr_slice_desc> descs;
+  std::vector<size_t> which;
+  std::string in;   // all Block.cabac bytes back to back
+  for (int i = 0; i < n_ents; i++) {
+    const Block& b = blocks[coded[i].block];
+    if (uint64_t(b.size) != ents[i].desc.payload_size) { free(ents); return AVR_ERR_FORMAT; }   // "Invalid surrogate block size"
+    if (!coded[i].is_cabac) continue;
+    if (ents[i].desc.in_off != coded[i].off) { free(ents); return AVR_ERR_FORMAT; }
+    avr_slice_desc d = ents[i].desc;
+    d.in_off = in.size();
+    d.in_size = uint32_t(b.cabac_n);
+    if (descs.empty() || slice_mode) d.flags |= AVR_SLICE_NEW_MODEL;
+    in.append(reinterpret_cast<const char*>(b.cabac), b.cabac_n);
+    descs.push_back(d);
+    which.push_back(size_t(i));
+  }
+  free(ents);
+  std::vector<avr_slice_result> res(descs.size());
+  const uint8_t* out = nullptr;
+  uint64_t out_bytes = 0;
+  if (in.empty()) in.push_back(0);
+  rc = avr_decompress(ctx, descs.data(), int(descs.size()), reinterpret_cast<const uint8_t*>(in.data()), in.size(), res.data(), &out, &out_bytes);
+  if (rc) return rc;
+  // 3. splice the rebuilt payloads in, with the x264 padding fix-up of recode.cpp:1345-1354
+  for (size_t k = 0; k < descs.size(); k++) {
+    if (res[k].status != AVR_SLICE_OK) return AVR_ERR_FORMAT;   // "Not all blocks were decoded."
+    const Block& b = blocks[coded[which[k]].block];
+    std::string bytes(reinterpret_cast<const char*>(out + res[k].out_off), res[k].out_size);
+    if (b.has_parity && b.has_last && b.last_n > 0) {
+      if (int(b.parity) != int(bytes.size() & 1)) bytes.push_back(char(b.last[0]));
+      else if (!bytes.empty()) bytes[bytes.size() - 1] = char(b.last[0]);
+    }
+    if (bytes.size() != size_t(b.size)) return AVR_ERR_FORMAT;
+    memcpy(&stream[coded[which[k]].off], bytes.data(), bytes.size());
+  }
+  return to_malloc(stream, file, file_bytes);
+}
+
+}  // extern "C"

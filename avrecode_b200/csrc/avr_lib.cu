@@ -1,0 +1,370 @@
+// avr_lib.cu -- sm_100a kernels + the C ABI of include/avrecode_b200.h (device side).
+//
+// One persistent warp per job slot; jobs are handed out through an atomic counter in descending
+// size order.  All algorithmic code is in avr_core.cuh / avr_job.cuh.  There is no CPU path in
+// this library: without a CUDA device every entry point that needs one fails with
+// AVR_ERR_NO_DEVICE.
+#include <cuda_runtime.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <algorithm>
+#include <new>
+#include <vector>
+#include "avr_job.cuh"
+
+using namespace avr;
+
+namespace {
+
+struct KernelArgs {
+  JobArgs a;
+  const JobDesc* jobs;
+  uint32_t n_jobs;
+  uint32_t* counter;        // next job to hand out
+  uint64_t work_stride;     // bytes of workspace per resident warp
+  uint32_t nnz_frame_bytes; // bytes of one model frame buffer inside a workspace slot
+  uint32_t max_mbw;         // row buffer entries per warp
+};
+
+// Block = one warp.  Shared memory: SharedTables | WarpState | MbCtx row[max_mbw].
+template <class Dir>
+__global__ void __launch_bounds__(32, 8) avr_job_kernel(KernelArgs k) {
+  extern __shared__ __align__(16) uint8_t smem[];
+  SharedTables* tab = reinterpret_cast<SharedTables*>(smem);
+  WarpState* ws = reinterpret_cast<WarpState*>(smem + sizeof(SharedTables));
+  MbCtx* row = reinterpret_cast<MbCtx*>(smem + sizeof(SharedTables) + sizeof(WarpState));
+  const int lane = threadIdx.x & 31;
+  fill_shared_tables(tab, lane, 32);
+  __syncwarp();
+  const uint64_t slot = uint64_t(blockIdx.x) * k.work_stride;
+  for (;;) {
+    uint32_t j = 0;
+    if (lane == 0) j = atomicAdd(k.counter, 1u);
+    j = __shfl_sync(0xFFFFFFFFu, j, 0);
+    if (j >= k.n_jobs) break;
+    JobDesc job = k.jobs[j];
+    job.model_off = slot;
+    job.nnz_off = slot + uint64_t(MODEL_COUNTERS) * 2;
+    job.nnz_frame_bytes = k.nnz_frame_bytes;
+    run_job<Dir>(k.a, job, tab, ws, row, lane);
+  }
+}
+
+__global__ void avr_fill_kernel(uint4* p, size_t n, uint32_t v) {
+  size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x;
+  size_t stride = size_t(gridDim.x) * blockDim.x;
+  uint4 x = make_uint4(v, v, v, v);
+  for (; i < n; i += stride) p[i] = x;
+}
+
+}  // namespace
+
+struct avr_ctx {
+  int device = 0;
+  int sm_count = 0;
+  int max_smem_optin = 0;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  // device buffers, grown on demand
+  uint8_t* d_in = nullptr; size_t d_in_cap = 0;
+  uint8_t* d_out = nullptr; size_t d_out_cap = 0;
+  uint8_t* d_work = nullptr; size_t d_work_cap = 0;
+  uint8_t* d_meta = nullptr; size_t d_meta_cap = 0;   // descs | ios | jobs | results | counter
+  uint8_t* d_flush = nullptr; size_t flush_bytes = 0;
+  // pinned host buffers
+  uint8_t* h_out = nullptr; size_t h_out_cap = 0;
+  uint8_t* h_meta = nullptr; size_t h_meta_cap = 0;
+  // staged batch
+  int n_slices = 0, n_jobs = 0;
+  bool staged = false, launched = false;
+  int direction = 0;
+  std::vector<avr_slice_desc> descs;
+  std::vector<SliceIO> ios[2];       // per direction
+  std::vector<JobDesc> jobs;
+  uint64_t out_total[2] = {0, 0};
+  size_t in_bytes = 0;
+  uint32_t max_mbw = 1, max_frame_bytes = 0;
+  int grid = 0;
+  // meta offsets
+  size_t off_descs = 0, off_ios = 0, off_jobs = 0, off_res = 0, off_counter = 0;
+  float last_ms = 0.f;
+  uint64_t launches = 0;
+  int cfg_warps = 0;
+};
+
+namespace {
+
+bool ck(cudaError_t e, const char* what) {
+  if (e == cudaSuccess) return true;
+  fprintf(stderr, "avrecode_b200: CUDA error in %s: %s\n", what, cudaGetErrorString(e));
+  return false;
+}
+#define CK(x) do { if (!ck((x), #x)) return AVR_ERR_CUDA; } while (0)
+
+int grow_dev(uint8_t** p, size_t* cap, size_t need) {
+  if (need <= *cap) return AVR_OK;
+  if (*p) cudaFree(*p);
+  *p = nullptr; *cap = 0;
+  size_t want = need + need / 4 + 4096;
+  if (!ck(cudaMalloc(reinterpret_cast<void**>(p), want), "cudaMalloc")) return AVR_ERR_NOMEM;
+  *cap = want;
+  return AVR_OK;
+}
+int grow_pinned(uint8_t** p, size_t* cap, size_t need) {
+  if (need <= *cap) return AVR_OK;
+  if (*p) cudaFreeHost(*p);
+  *p = nullptr; *cap = 0;
+  size_t want = need + need / 4 + 4096;
+  if (!ck(cudaMallocHost(reinterpret_cast<void**>(p), want), "cudaMallocHost")) return AVR_ERR_NOMEM;
+  *cap = want;
+  return AVR_OK;
+}
+size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+}  // namespace
+
+extern "C" {
+
+const char* avr_strerror(int code) {
+  switch (code) {
+    case AVR_OK: return "ok";
+    case AVR_ERR_NO_DEVICE: return "no usable CUDA device (this library has no CPU fallback)";
+    case AVR_ERR_CUDA: return "CUDA runtime error";
+    case AVR_ERR_ARG: return "invalid argument";
+    case AVR_ERR_NOMEM: return "out of memory";
+    case AVR_ERR_FORMAT: return "malformed container or bitstream";
+    case AVR_ERR_STATE: return "call sequence violated (stage -> launch -> sync -> collect)";
+    default: return "unknown error";
+  }
+}
+
+int avr_abi_version(void) { return AVR_ABI_VERSION; }
+
+int avr_create(const avr_config* cfg, avr_ctx** out) {
+  if (!out) return AVR_ERR_ARG;
+  *out = nullptr;
+  if (cfg && cfg->abi_version != AVR_ABI_VERSION) return AVR_ERR_ARG;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0) { cudaGetLastError(); return AVR_ERR_NO_DEVICE; }
+  int dev = cfg ? cfg->device : 0;
+  if (dev < 0 || dev >= ndev) return AVR_ERR_ARG;
+  avr_ctx* c = new (std::nothrow) avr_ctx();
+  if (!c) return AVR_ERR_NOMEM;
+  c->device = dev;
+  c->cfg_warps = cfg ? cfg->warps_per_block : 0;
+  if (!ck(cudaSetDevice(dev), "cudaSetDevice")) { delete c; return AVR_ERR_NO_DEVICE; }
+  cudaDeviceProp prop;
+  if (!ck(cudaGetDeviceProperties(&prop, dev), "cudaGetDeviceProperties")) { delete c; return AVR_ERR_CUDA; }
+  c->sm_count = prop.multiProcessorCount;
+  c->max_smem_optin = int(prop.sharedMemPerBlockOptin);
+  if (!ck(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking), "cudaStreamCreate") ||
+      !ck(cudaEventCreate(&c->ev0), "cudaEventCreate") || !ck(cudaEventCreate(&c->ev1), "cudaEventCreate")) {
+    avr_destroy(c);
+    return AVR_ERR_CUDA;
+  }
+  *out = c;
+  return AVR_OK;
+}
+
+void avr_destroy(avr_ctx* c) {
+  if (!c) return;
+  cudaSetDevice(c->device);
+  if (c->stream) cudaStreamSynchronize(c->stream);
+  if (c->d_in) cudaFree(c->d_in);
+  if (c->d_out) cudaFree(c->d_out);
+  if (c->d_work) cudaFree(c->d_work);
+  if (c->d_meta) cudaFree(c->d_meta);
+  if (c->d_flush) cudaFree(c->d_flush);
+  if (c->h_out) cudaFreeHost(c->h_out);
+  if (c->h_meta) cudaFreeHost(c->h_meta);
+  if (c->ev0) cudaEventDestroy(c->ev0);
+  if (c->ev1) cudaEventDestroy(c->ev1);
+  if (c->stream) cudaStreamDestroy(c->stream);
+  delete c;
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------------------------------------------------
+// Staged pipeline: stage (H2D) -> launch (kernels) -> sync -> collect (D2H).
+// ------------------------------------------------------------------------------------------------
+extern "C" {
+
+int avr_stage(avr_ctx* c, const avr_slice_desc* descs, int n, const uint8_t* in, uint64_t in_bytes) {
+  if (!c || n < 0 || (n > 0 && (!descs || !in))) return AVR_ERR_ARG;
+  CK(cudaSetDevice(c->device));
+  CK(cudaStreamSynchronize(c->stream));   // previous batch may still be reading the pinned metadata
+  c->staged = false; c->launched = false;
+  c->n_slices = n; c->in_bytes = size_t(in_bytes);
+  c->descs.assign(descs, descs + n);
+  c->jobs.clear();
+  c->max_mbw = 1; c->max_frame_bytes = 0;
+  for (int dir = 0; dir < 2; dir++) { c->ios[dir].resize(n); c->out_total[dir] = 0; }
+  for (int i = 0; i < n; i++) {
+    const avr_slice_desc& d = descs[i];
+    if (d.in_off + d.in_size > in_bytes) return AVR_ERR_ARG;
+    for (int dir = 0; dir < 2; dir++) {
+      SliceIO& io = c->ios[dir][i];
+      io.in_off = d.in_off; io.in_size = d.in_size;
+      io.out_off = c->out_total[dir];
+      io.out_cap = dir == 0 ? d.in_size + d.in_size / 8 + 256 : d.payload_size + 64;
+      c->out_total[dir] += align_up(io.out_cap, 16);
+    }
+    c->max_mbw = std::max<uint32_t>(c->max_mbw, d.mb_width);
+    c->max_frame_bytes = std::max<uint32_t>(c->max_frame_bytes, uint32_t(d.mb_width) * d.mb_height * NNZ_STRIDE);
+    if (i == 0 || (d.flags & AVR_SLICE_NEW_MODEL)) {
+      JobDesc j; memset(&j, 0, sizeof j);
+      j.first_slice = uint32_t(i); j.n_slices = 0;
+      c->jobs.push_back(j);
+    }
+    c->jobs.back().n_slices++;
+    c->jobs.back().reserved += d.in_size > 0x7FFFFFFFu - c->jobs.back().reserved ? 0 : d.in_size;  // job weight
+  }
+  // longest jobs first (LPT order for the dynamic hand-out)
+  std::stable_sort(c->jobs.begin(), c->jobs.end(), [](const JobDesc& a, const JobDesc& b) { return a.reserved > b.reserved; });
+  c->n_jobs = int(c->jobs.size());
+  c->max_frame_bytes = uint32_t(align_up(c->max_frame_bytes, 16));
+
+  // grid: one warp per block; enough blocks to cover the jobs, capped by residency
+  size_t smem = sizeof(SharedTables) + sizeof(WarpState) + size_t(c->max_mbw) * sizeof(MbCtx);
+  int per_sm = c->cfg_warps > 0 ? c->cfg_warps : 16;
+  int by_smem = int(size_t(200 * 1024) / smem);
+  per_sm = std::max(1, std::min(per_sm, by_smem));
+  c->grid = std::max(1, std::min(c->n_jobs, c->sm_count * per_sm));
+
+  // device memory
+  const uint64_t work_stride = align_up(size_t(MODEL_COUNTERS) * 2 + 2 * size_t(c->max_frame_bytes), 256);
+  int rc;
+  if ((rc = grow_dev(&c->d_in, &c->d_in_cap, size_t(in_bytes) + 64))) return rc;
+  if ((rc = grow_dev(&c->d_out, &c->d_out_cap, size_t(std::max(c->out_total[0], c->out_total[1])) + 64))) return rc;
+  if ((rc = grow_dev(&c->d_work, &c->d_work_cap, size_t(work_stride) * c->grid + 256))) return rc;
+  c->off_descs = 0;
+  c->off_ios = align_up(c->off_descs + sizeof(avr_slice_desc) * n, 256);
+  c->off_jobs = align_up(c->off_ios + 2 * sizeof(SliceIO) * n, 256);
+  c->off_res = align_up(c->off_jobs + sizeof(JobDesc) * c->jobs.size(), 256);
+  c->off_counter = align_up(c->off_res + sizeof(avr_slice_result) * n, 256);
+  size_t meta_bytes = c->off_counter + 256;
+  if ((rc = grow_dev(&c->d_meta, &c->d_meta_cap, meta_bytes))) return rc;
+  if ((rc = grow_pinned(&c->h_meta, &c->h_meta_cap, meta_bytes))) return rc;
+  if (n > 0) {
+    memcpy(c->h_meta + c->off_descs, descs, sizeof(avr_slice_desc) * n);
+    memcpy(c->h_meta + c->off_ios, c->ios[0].data(), sizeof(SliceIO) * n);
+    memcpy(c->h_meta + c->off_ios + sizeof(SliceIO) * n, c->ios[1].data(), sizeof(SliceIO) * n);
+    memcpy(c->h_meta + c->off_jobs, c->jobs.data(), sizeof(JobDesc) * c->jobs.size());
+    CK(cudaMemcpyAsync(c->d_meta, c->h_meta, c->off_res, cudaMemcpyHostToDevice, c->stream));
+    CK(cudaMemcpyAsync(c->d_in, in, size_t(in_bytes), cudaMemcpyHostToDevice, c->stream));
+  }
+  c->staged = true;
+  return AVR_OK;
+}
+
+int avr_launch(avr_ctx* c, int direction) {
+  if (!c || (direction != 0 && direction != 1)) return AVR_ERR_ARG;
+  if (!c->staged) return AVR_ERR_STATE;
+  CK(cudaSetDevice(c->device));
+  c->direction = direction;
+  c->launched = true;
+  if (c->n_slices == 0) return AVR_OK;
+  const int n = c->n_slices;
+  KernelArgs k;
+  k.a.descs = reinterpret_cast<const avr_slice_desc*>(c->d_meta + c->off_descs);
+  k.a.ios = reinterpret_cast<const SliceIO*>(c->d_meta + c->off_ios) + (direction ? n : 0);
+  k.a.in_arena = c->d_in;
+  k.a.out_arena = c->d_out;
+  k.a.results = reinterpret_cast<avr_slice_result*>(c->d_meta + c->off_res);
+  k.a.workspace = c->d_work;
+  k.jobs = reinterpret_cast<const JobDesc*>(c->d_meta + c->off_jobs);
+  k.n_jobs = uint32_t(c->n_jobs);
+  k.counter = reinterpret_cast<uint32_t*>(c->d_meta + c->off_counter);
+  k.work_stride = align_up(size_t(MODEL_COUNTERS) * 2 + 2 * size_t(c->max_frame_bytes), 256);
+  k.nnz_frame_bytes = c->max_frame_bytes;
+  k.max_mbw = c->max_mbw;
+  size_t smem = sizeof(SharedTables) + sizeof(WarpState) + size_t(c->max_mbw) * sizeof(MbCtx);
+  if (int(smem) > c->max_smem_optin) return AVR_ERR_ARG;
+  CK(cudaMemsetAsync(k.counter, 0, sizeof(uint32_t), c->stream));
+  CK(cudaEventRecord(c->ev0, c->stream));
+  if (direction == 0) {
+    if (smem > 48 * 1024) CK(cudaFuncSetAttribute(avr_job_kernel<Compress>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+    avr_job_kernel<Compress><<<c->grid, 32, smem, c->stream>>>(k);
+  } else {
+    if (smem > 48 * 1024) CK(cudaFuncSetAttribute(avr_job_kernel<Decompress>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+    avr_job_kernel<Decompress><<<c->grid, 32, smem, c->stream>>>(k);
+  }
+  CK(cudaGetLastError());
+  CK(cudaEventRecord(c->ev1, c->stream));
+  c->launches++;
+  return AVR_OK;
+}
+
+int avr_sync(avr_ctx* c) {
+  if (!c) return AVR_ERR_ARG;
+  CK(cudaSetDevice(c->device));
+  CK(cudaStreamSynchronize(c->stream));
+  if (c->launched && c->n_slices > 0) CK(cudaEventElapsedTime(&c->last_ms, c->ev0, c->ev1));
+  return AVR_OK;
+}
+
+int avr_collect(avr_ctx* c, avr_slice_result* results, const uint8_t** out, uint64_t* out_bytes) {
+  if (!c || !results || !out || !out_bytes) return AVR_ERR_ARG;
+  if (!c->launched) return AVR_ERR_STATE;
+  CK(cudaSetDevice(c->device));
+  const int n = c->n_slices;
+  const size_t total = size_t(c->out_total[c->direction]);
+  int rc;
+  if ((rc = grow_pinned(&c->h_out, &c->h_out_cap, total + 64))) return rc;
+  if (n > 0) {
+    CK(cudaMemcpyAsync(c->h_meta + c->off_res, c->d_meta + c->off_res, sizeof(avr_slice_result) * n, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaMemcpyAsync(c->h_out, c->d_out, total, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    memcpy(results, c->h_meta + c->off_res, sizeof(avr_slice_result) * n);
+  }
+  *out = c->h_out;
+  *out_bytes = total;
+  return AVR_OK;
+}
+
+int avr_last_kernel_ms(avr_ctx* c, float* ms) {
+  if (!c || !ms) return AVR_ERR_ARG;
+  *ms = c->last_ms;
+  return AVR_OK;
+}
+
+int avr_launch_count(avr_ctx* c, uint64_t* n) {
+  if (!c || !n) return AVR_ERR_ARG;
+  *n = c->launches;
+  return AVR_OK;
+}
+
+int avr_flush_l2(avr_ctx* c) {
+  if (!c) return AVR_ERR_ARG;
+  CK(cudaSetDevice(c->device));
+  if (!c->d_flush) {
+    c->flush_bytes = size_t(256) << 20;   // > 126 MB L2
+    if (!ck(cudaMalloc(reinterpret_cast<void**>(&c->d_flush), c->flush_bytes), "cudaMalloc flush")) return AVR_ERR_NOMEM;
+  }
+  avr_fill_kernel<<<c->sm_count * 8, 256, 0, c->stream>>>(reinterpret_cast<uint4*>(c->d_flush), c->flush_bytes / 16, uint32_t(c->launches));
+  CK(cudaGetLastError());
+  return AVR_OK;
+}
+
+static int run_oneshot(avr_ctx* c, int direction, const avr_slice_desc* descs, int n, const uint8_t* in, uint64_t in_bytes,
+                       avr_slice_result* results, const uint8_t** out, uint64_t* out_bytes) {
+  int rc;
+  if ((rc = avr_stage(c, descs, n, in, in_bytes))) return rc;
+  if ((rc = avr_launch(c, direction))) return rc;
+  if ((rc = avr_sync(c))) return rc;
+  return avr_collect(c, results, out, out_bytes);
+}
+
+int avr_compress(avr_ctx* c, const avr_slice_desc* descs, int n, const uint8_t* in, uint64_t in_bytes,
+                 avr_slice_result* results, const uint8_t** out, uint64_t* out_bytes) {
+  return run_oneshot(c, 0, descs, n, in, in_bytes, results, out, out_bytes);
+}
+
+int avr_decompress(avr_ctx* c, const avr_slice_desc* descs, int n, const uint8_t* in, uint64_t in_bytes,
+                   avr_slice_result* results, const uint8_t** out, uint64_t* out_bytes) {
+  return run_oneshot(c, 1, descs, n, in, in_bytes, results, out, out_bytes);
+}
+
+}  // extern "C"

@@ -1,0 +1,120 @@
+"""Test-side helpers: stream synthesis (build/h264gen), oracle + emulation bindings, slice batches.
+
+Only tests/, bench.py's cpu_baseline leg and __graft_entry__.smoke() import this; the product
+package never does."""
+import ctypes as C
+import os
+import subprocess
+import tempfile
+
+from avrecode_b200 import _abi
+from avrecode_b200._abi import SliceDesc, SliceResult, copy_desc
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+H264GEN = os.path.join(ROOT, "build", "h264gen")
+REF_DIR = os.path.join(ROOT, "oracle", "_ref")
+
+_oracle = None
+_emu = None
+
+
+def oracle_lib():
+    global _oracle
+    if _oracle is None:
+        _oracle = C.CDLL(os.path.join(ROOT, "oracle", "_build", "libavr_oracle.so"))
+    return _oracle
+
+
+def emu_lib():
+    global _emu
+    if _emu is None:
+        _emu = C.CDLL(os.path.join(ROOT, "build", "libavr_emu.so"))
+    return _emu
+
+
+def gen_stream(**kw):
+    """Runs build/h264gen; keyword names are its long options (width=..., high=True, ...)."""
+    fd, path = tempfile.mkstemp(suffix=".h264")
+    os.close(fd)
+    cmd = [H264GEN, "-o", path]
+    for k, v in kw.items():
+        opt = "--" + k.replace("_", "-")
+        if v is True:
+            cmd.append(opt)
+        elif v is not False and v is not None:
+            cmd += [opt, str(v)]
+    try:
+        subprocess.run(cmd, check=True, capture_output=True)
+        with open(path, "rb") as f:
+            return f.read()
+    finally:
+        os.unlink(path)
+
+
+def batch_descs(entries, mode_file):
+    """Index entries -> slice descs for one file in file (shared model) or slice (chunk) mode."""
+    descs = []
+    for e in entries:
+        if not e.recodable:
+            continue
+        d = copy_desc(e.desc)
+        if not descs or not mode_file:
+            d.flags |= _abi.AVR_SLICE_NEW_MODEL
+        descs.append(d)
+    return descs
+
+
+def _call(fn, descs, data, *extra):
+    n = len(descs)
+    arr = (SliceDesc * n)(*descs)
+    res = (SliceResult * n)()
+    out = C.POINTER(C.c_uint8)()
+    nb = C.c_uint64()
+    buf = (C.c_uint8 * max(1, len(data))).from_buffer_copy(data if data else b"\0")
+    rc = fn(arr, n, buf, C.c_uint64(len(data)), res, C.byref(out), C.byref(nb), *extra)
+    assert rc == 0, rc
+    blob = C.string_at(out, nb.value)
+    return list(res), blob
+
+
+def oracle_compress(descs, data):
+    return _call(oracle_lib().avr_oracle_compress, descs, data)
+
+
+def oracle_decompress(descs, data, mirror_compressor=1):
+    return _call(oracle_lib().avr_oracle_decompress, descs, data, C.c_int(mirror_compressor))
+
+
+def emu_compress(descs, data):
+    return _call(emu_lib().avr_emu_compress, descs, data)
+
+
+def emu_decompress(descs, data):
+    return _call(emu_lib().avr_emu_decompress, descs, data)
+
+
+def coded_descs(descs, results):
+    """Descs for the decompress direction: input = the coded bytes described by `results`."""
+    out = []
+    for d, r in zip(descs, results):
+        d2 = copy_desc(d)
+        d2.in_off = r.out_off
+        d2.in_size = r.out_size
+        out.append(d2)
+    return out
+
+
+def slices_of(results, blob):
+    return [blob[r.out_off:r.out_off + r.out_size] for r in results]
+
+
+def fix_tail(got, payload):
+    """x264 padding fix-up of recode.cpp:1347-1354 using the original payload's parity / last byte."""
+    if (len(got) & 1) != (len(payload) & 1):
+        return got + payload[-1:]
+    return got[:-1] + payload[-1:]
+
+
+def ref_binary(name="recode_ref"):
+    p = os.path.join(REF_DIR, name)
+    return p if os.path.exists(p) else None
