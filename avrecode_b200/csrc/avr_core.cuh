@@ -131,12 +131,18 @@ AVR_DEV uint64_t div_small(const SharedTables& t, uint64_t n, uint32_t d) {
 enum : uint32_t { WIN_BYTES = 1024, WIN_HALF = 512 };
 
 struct ByteWindow {
-  const uint8_t* base;   // slice bytes in global memory (16-byte aligned arena offset not required)
-  uint8_t* win;          // WIN_BYTES of shared memory
+  const uint8_t* base;   // slice bytes in global memory (any alignment)
+  uint8_t* win;          // WIN_BYTES of shared memory, 16-byte aligned
   uint32_t size;         // valid bytes
-  uint32_t win_start;    // the ring holds stream bytes [win_start, win_start + WIN_BYTES); multiple of WIN_HALF
+  uint32_t skew;         // base & 15: ring positions are counted from the 16-byte aligned address below base
+  uint32_t win_start;    // the ring holds aligned positions [win_start, win_start + WIN_BYTES); multiple of WIN_HALF
+  AVR_DEV void attach(const uint8_t* src, uint32_t n, uint8_t* window) {
+    base = src; size = n; win = window; win_start = 0;
+    skew = uint32_t(reinterpret_cast<uintptr_t>(src) & 15);
+  }
   AVR_DEV uint32_t byte(uint32_t pos) const {
-    if (pos - win_start < WIN_BYTES) return win[pos & (WIN_BYTES - 1)];
+    const uint32_t a = pos + skew;
+    if (a - win_start < WIN_BYTES) return win[a & (WIN_BYTES - 1)];
     return pos < size ? base[pos] : 0;   // slow path: ran ahead of the window inside one macroblock
   }
   AVR_DEV uint32_t be16(uint32_t pos) const { return (byte(pos) << 8) | byte(pos + 1); }
@@ -362,10 +368,11 @@ enum : uint16_t {
 };
 
 struct WarpState {
+  alignas(16) uint8_t window[WIN_BYTES];
   uint32_t ctx[1024];      // state | pos << 8 | neg << 16  per ctxIdx (KS_CTX estimators of recode.cpp:679-683)
   uint32_t bypass_cnt;     // pos | neg << 8 (recode.cpp:1183)
   uint32_t term_cnt;       // (recode.cpp:1190)
-  uint8_t window[WIN_BYTES];
+  uint32_t pad_[2];
 };
 
 AVR_DEV void est_update(uint32_t& pos, uint32_t& neg, int bit, uint32_t limit) {  // recode.cpp:1035-1045
@@ -407,7 +414,7 @@ struct Compress {
   CabacIn cabac;
   RangeEnc rc;
   AVR_DEV void begin(const uint8_t* src, uint32_t src_size, uint8_t* dst, uint32_t dst_cap, uint8_t* window) {
-    in.base = src; in.size = src_size; in.win = window; in.win_start = 0;
+    in.attach(src, src_size, window);
     rc.init(dst, dst_cap);
   }
   AVR_DEV void start_bins() { cabac.init(in); }

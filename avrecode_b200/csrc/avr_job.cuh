@@ -52,19 +52,21 @@ AVR_DEV void fill_u32(uint32_t* p, uint64_t n_words, uint32_t v, int lane) {
   for (uint64_t i = uint64_t(lane); i < n_words; i += AVR_LANES) p[i] = v;
 }
 
-// loads stream bytes [from, from + WIN_HALF) into their ring slots, 16 bytes per lane, zero past the end
+// loads aligned positions [from, from + WIN_HALF) into their ring slots, one aligned 16-byte load per
+// lane; bytes past the end of the slice read as zero, the <= 15 bytes before its start are don't-care
 AVR_DEV void window_load_half(const ByteWindow& w, uint32_t from, int lane) {
+  const uint8_t* abase = w.base - w.skew;
+  const uint32_t aend = w.size + w.skew;
   for (uint32_t o = uint32_t(lane) * 16; o < WIN_HALF; o += AVR_LANES * 16) {
-    uint32_t pos = from + o;
-    uint8_t* dst = w.win + (pos & (WIN_BYTES - 1));
-    const uint8_t* src = w.base + pos;
+    uint32_t apos = from + o;
+    uint8_t* dst = w.win + (apos & (WIN_BYTES - 1));
 #if defined(__CUDA_ARCH__)
-    if (pos + 16 <= w.size && ((reinterpret_cast<uintptr_t>(src) & 15) == 0)) {
-      *reinterpret_cast<uint4*>(dst) = *reinterpret_cast<const uint4*>(src);
+    if (apos + 16 <= aend) {
+      *reinterpret_cast<uint4*>(dst) = *reinterpret_cast<const uint4*>(abase + apos);
       continue;
     }
 #endif
-    for (int k = 0; k < 16; k++) dst[k] = pos + k < w.size ? src[k] : 0;
+    for (uint32_t k = 0; k < 16; k++) dst[k] = (apos + k >= w.skew && apos + k < aend) ? abase[apos + k] : 0;
   }
 }
 
@@ -83,7 +85,7 @@ struct JobArgs {
 };
 
 AVR_DEV ByteWindow& window_of(Compress& c) { return c.in; }
-AVR_DEV uint32_t window_limit(const Compress& c) { return c.in.win_start + WIN_HALF; }
+AVR_DEV uint32_t window_limit(const Compress& c) { return c.in.win_start + WIN_HALF - c.in.skew; }
 AVR_DEV uint32_t window_limit(const Decompress&) { return 0xFFFFFFFFu; }
 
 // Runs one job on the calling warp.
@@ -161,7 +163,7 @@ AVR_DEV_NOINLINE void run_job(const JobArgs& a, const JobDesc& job, const Shared
         if constexpr (!Dir::kDecompress) {
           ByteWindow& bw = window_of(wk.dir);
           AVR_SYNCWARP();
-          while (in_pos >= bw.win_start + WIN_HALF) {   // the consumed half is free: load the next 512 bytes into it
+          while (in_pos + bw.skew >= bw.win_start + WIN_HALF) {   // the consumed half is free: load the next 512 bytes into it
             window_load_half(bw, bw.win_start + WIN_BYTES, lane);
             bw.win_start += WIN_HALF;
           }

@@ -1,0 +1,189 @@
+"""Parity tests proper: the CUDA path, called through the C ABI, against the reference compressor's
+golden containers, against the CPU oracle on seeded streams, and -- at BASELINE sizes -- through the
+round-trip property.  Bit-exact everywhere (this is integer/byte work)."""
+import os
+import subprocess
+import tempfile
+
+import pytest
+
+import helpers as H
+import recproto
+import avrecode_b200 as A
+from avrecode_b200 import _abi
+from test_oracle_pin import CASES, load_case, container_from
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def ctx(built):
+    c = A.Context()
+    yield c
+    c.close()
+
+
+def check_roundtrip(ctx, descs, data, res, blob):
+    r_d, b_d = ctx.decompress(H.coded_descs(descs, res), blob)
+    assert [r.status for r in r_d] == [0] * len(descs)
+    for d, got in zip(descs, H.slices_of(r_d, b_d)):
+        payload = data[d.in_off:d.in_off + d.payload_size]
+        assert H.fix_tail(got, payload) == payload
+    assert [r.n_bins for r in r_d] == [r.n_bins for r in res]
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_file_mode_equals_reference_compressor(ctx, name):
+    """Block.cabac of every slice and the whole container == bytes written by the unmodified reference."""
+    data, ref_rec = load_case(name)
+    entries = A.index_h264(data)
+    descs = H.batch_descs(entries, True)
+    res, blob = ctx.compress(descs, data)
+    assert [r.status for r in res] == [0] * len(descs)
+    _, ref_blocks = recproto.parse(ref_rec)
+    assert H.slices_of(res, blob) == [b["cabac"] for b in ref_blocks if "cabac" in b]
+    assert container_from(data, entries, res, blob) == ref_rec
+    assert ctx.file_compress(data, A.MODE_FILE) == ref_rec
+    check_roundtrip(ctx, descs, data, res, blob)
+    # the reference's own container decodes on the device
+    assert ctx.file_decompress(ref_rec) == data
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_slice_mode_equals_oracle(ctx, name):
+    data, _ = load_case(name)
+    descs = H.batch_descs(A.index_h264(data), False)
+    res, blob = ctx.compress(descs, data)
+    r_o, b_o = H.oracle_compress(descs, data)
+    assert [r.status for r in res] == [0] * len(descs)
+    assert H.slices_of(res, blob) == H.slices_of(r_o, b_o)
+    assert [(r.n_bins, r.n_mbs) for r in res] == [(r.n_bins, r.n_mbs) for r in r_o]
+    check_roundtrip(ctx, descs, data, res, blob)
+    rec = ctx.file_compress(data, A.MODE_SLICE)
+    assert recproto.parse(rec)[0] == b"avr-b200/slice"
+    assert ctx.file_decompress(rec) == data
+
+
+SEEDED = [
+    dict(width=480, height=272, frames=6, slices=4, seed=2),
+    dict(width=640, height=368, frames=5, high=True, seed=3, ragged=True, slices=3),
+    dict(width=1280, height=720, frames=3, seed=11, kbps=4000),
+    dict(width=720, height=480, frames=4, seed=12, high=True, p8x8=0.9, density=2.5, qp=18),
+    dict(width=400, height=240, frames=12, seed=13, refs=4, pskip=0.7, pintra=0.2),
+    dict(mbw=1, mbh=1, frames=9, seed=14),
+    dict(mbw=255, mbh=2, frames=2, seed=15, slices=2),
+]
+
+
+@pytest.mark.parametrize("kw", SEEDED, ids=lambda k: "seed%d" % k["seed"])
+@pytest.mark.parametrize("mode_file", [True, False], ids=["file", "slice"])
+def test_seeded_streams_equal_oracle(ctx, kw, mode_file):
+    data = H.gen_stream(**kw)
+    descs = H.batch_descs(A.index_h264(data), mode_file)
+    assert descs
+    res, blob = ctx.compress(descs, data)
+    r_o, b_o = H.oracle_compress(descs, data)
+    assert [r.status for r in res] == [r.status for r in r_o] == [0] * len(descs)
+    assert H.slices_of(res, blob) == H.slices_of(r_o, b_o)
+    check_roundtrip(ctx, descs, data, res, blob)
+
+
+def test_decompress_equals_oracle_decompress(ctx):
+    data, _ = load_case("high_8x8_ragged")
+    descs = H.batch_descs(A.index_h264(data), True)
+    res, blob = ctx.compress(descs, data)
+    dd = H.coded_descs(descs, res)
+    r_g, b_g = ctx.decompress(dd, blob)
+    r_o, b_o = H.oracle_decompress(dd, blob)
+    assert H.slices_of(r_g, b_g) == H.slices_of(r_o, b_o)
+
+
+def test_empty_and_degenerate_batches(ctx):
+    res, blob = ctx.compress([], b"\0")
+    assert res == [] and blob == b""
+    data, _ = load_case(CASES[0])
+    ents = A.index_h264(data)
+    # unsupported slice kinds are reported per slice, never crash, and cost nothing else
+    d = _abi.copy_desc(ents[0].desc)
+    d.flags |= _abi.AVR_SLICE_NEW_MODEL | _abi.AVR_SLICE_MBAFF
+    res, _ = ctx.compress([d], data)
+    assert res[0].status == _abi.AVR_SLICE_UNSUPPORTED and res[0].out_size == 0
+    d = _abi.copy_desc(ents[0].desc)
+    d.flags |= _abi.AVR_SLICE_NEW_MODEL
+    d.slice_type = _abi.AVR_SLICE_B
+    res, _ = ctx.compress([d], data)
+    assert res[0].status == _abi.AVR_SLICE_UNSUPPORTED
+    # a payload of garbage must end as CORRUPT/OK-with-different-size, not hang or fault
+    junk = os.urandom(4096)
+    d = _abi.copy_desc(ents[0].desc)
+    d.flags |= _abi.AVR_SLICE_NEW_MODEL
+    d.in_off, d.in_size, d.payload_size = 0, len(junk), len(junk)
+    res, _ = ctx.compress([d], junk)
+    assert res[0].status in (_abi.AVR_SLICE_OK, _abi.AVR_SLICE_CORRUPT, _abi.AVR_SLICE_UNSUPPORTED)
+    # truncated coded input on decompress: status, not a fault
+    descs = H.batch_descs(ents, False)[:1]
+    res, blob = ctx.compress(descs, data)
+    dd = H.coded_descs(descs, res)
+    dd[0].in_size = max(1, dd[0].in_size // 3)
+    r_d, _ = ctx.decompress(dd, blob)
+    assert r_d[0].status in (_abi.AVR_SLICE_OK, _abi.AVR_SLICE_CORRUPT, _abi.AVR_SLICE_OVERFLOW)
+    # bad arguments
+    bad = _abi.copy_desc(ents[0].desc)
+    bad.in_off = len(data)
+    with pytest.raises(A.AvrError):
+        ctx.compress([bad], data)
+
+
+def test_staged_pipeline_and_counters(ctx):
+    data = H.gen_stream(width=640, height=368, frames=8, seed=21, slices=2)
+    descs = H.batch_descs(A.index_h264(data), False)
+    n0 = ctx.launch_count()
+    ctx.stage(descs, data)
+    for _ in range(2):          # re-launchable on the same staged input
+        ctx.flush_l2()
+        ctx.launch(0)
+        ctx.sync()
+    assert ctx.last_kernel_ms() > 0
+    assert ctx.launch_count() == n0 + 2
+    res, blob = ctx.collect()
+    r_o, b_o = H.oracle_compress(descs, data)
+    assert H.slices_of(res, blob) == H.slices_of(r_o, b_o)
+
+
+def test_cli_roundtrip_verbs(ctx):
+    cli = os.path.join(ROOT, "avrecode_b200", "recode")
+    src = os.path.join(ROOT, "tests", "golden", "main_ip_4slices.h264")
+    data, ref_rec = load_case("main_ip_4slices")
+    with tempfile.TemporaryDirectory() as td:
+        p = subprocess.run([cli, "roundtrip", src, os.path.join(td, "rt.rec")], capture_output=True, text=True)
+        assert p.returncode == 0, p.stderr
+        assert "Compress-decompress roundtrip succeeded:" in p.stdout and " compression ratio: " in p.stdout \
+            and " protobuf overhead: " in p.stdout           # recode.cpp:1616-1618
+        env = dict(os.environ, AVR_MODE="file")
+        rec = os.path.join(td, "f.rec")
+        subprocess.run([cli, "compress", src, rec], check=True, env=env)
+        assert open(rec, "rb").read() == ref_rec
+        out = os.path.join(td, "f.h264")
+        subprocess.run([cli, "decompress", rec, out], check=True)
+        assert open(out, "rb").read() == data
+        p = subprocess.run([cli, "decompress", src], capture_output=True)   # not a container
+        assert p.returncode == 1 and b"Exception" in p.stderr
+
+
+@pytest.mark.parametrize("kw", [
+    dict(width=1920, height=1088, frames=12, high=True, seed=31, kbps=30000, fps=60),          # cfg2 shape
+    dict(width=1920, height=1088, frames=4, intra_period=1, slices=8, seed=32, kbps=60000),   # cfg3 shape
+    dict(width=3840, height=2160, frames=2, high=True, p8x8=0.85, seed=33, density=2.0, qp=20),  # cfg4 shape
+], ids=["cfg2", "cfg3", "cfg4"])
+def test_full_size_roundtrip_property(ctx, kw):
+    """BASELINE-sized pictures: size-independent properties (file round trip is the identity, bins agree
+    in both directions, first slice equals the oracle's bytes)."""
+    data = H.gen_stream(**kw)
+    rec = ctx.file_compress(data, A.MODE_SLICE)
+    assert ctx.file_decompress(rec) == data
+    assert len(rec) < len(data)
+    descs = H.batch_descs(A.index_h264(data), False)
+    res, blob = ctx.compress(descs, data)
+    r_o, b_o = H.oracle_compress(descs[:1], data)
+    assert H.slices_of(res, blob)[0] == H.slices_of(r_o, b_o)[0]

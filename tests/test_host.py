@@ -1,0 +1,134 @@
+"""CPU-side checks: the C-ABI library loads and exports what include/avrecode_b200.h declares, fails
+loudly without a device, the host slice indexer agrees with the reference's segmentation, the device
+code compiled as plain C++ (tests/emu, debugging aid) matches the oracle, and the product never
+touches oracle/.  No GPU needed."""
+import ctypes as C
+import os
+import re
+import subprocess
+
+import pytest
+
+import helpers as H
+import recproto
+import avrecode_b200 as A
+from avrecode_b200 import _abi
+from test_oracle_pin import CASES, load_case, MANIFEST
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _has_gpu():
+    try:
+        import torch
+        return torch.cuda.is_available()
+    except Exception:
+        return False
+
+
+def test_library_exports_every_declared_symbol(built):
+    hdr = open(os.path.join(ROOT, "include", "avrecode_b200.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    names = set(re.findall(r"\b(avr_[a-z0-9_]+)\s*\(", hdr))
+    assert {"avr_create", "avr_compress", "avr_decompress", "avr_stage", "avr_launch", "avr_collect",
+            "avr_index_h264", "avr_file_compress", "avr_file_decompress"} <= names
+    lib = A.load_library()
+    for n in sorted(names):
+        assert hasattr(lib, n), "missing export " + n
+    assert lib.avr_abi_version() == 1
+    assert b"no CPU fallback" in lib.avr_strerror(_abi.AVR_ERR_NO_DEVICE)
+
+
+def test_struct_layouts_match_header(built):
+    assert C.sizeof(_abi.SliceDesc) == 40 and C.sizeof(_abi.SliceResult) == 32 and C.sizeof(_abi.IndexEntry) == 48
+
+
+@pytest.mark.skipif(_has_gpu(), reason="only meaningful on a machine without a CUDA device")
+def test_no_device_fails_loudly(built):
+    with pytest.raises(A.NoDeviceError):
+        A.Context()
+    cli = os.path.join(ROOT, "avrecode_b200", "recode")
+    src = os.path.join(ROOT, "tests", "golden", CASES[0] + ".h264")
+    p = subprocess.run([cli, "roundtrip", src], capture_output=True)
+    assert p.returncode == 1 and b"Exception" in p.stderr and b"no CPU fallback" in p.stderr
+
+
+def test_cli_usage_matches_reference(built):
+    cli = os.path.join(ROOT, "avrecode_b200", "recode")
+    p = subprocess.run([cli], capture_output=True)
+    assert p.returncode == 1
+    assert b"[compress|decompress|roundtrip] <input> [output]" in p.stderr   # recode.cpp:1631-1635
+
+
+def test_product_never_touches_the_oracle():
+    pkg = os.path.join(ROOT, "avrecode_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for fn in files:
+            if not fn.endswith((".py", ".cu", ".cuh", ".cpp", ".h")):
+                continue
+            text = open(os.path.join(dirpath, fn), errors="replace").read()
+            for line in text.splitlines():
+                code = line.split("//")[0].split("#")[0] if not line.lstrip().startswith(("#include", "#if", "#define", "#else", "#endif", "#pragma")) else line
+                assert "avr_oracle" not in code and "oracle/" not in code or fn == "build.py", (fn, line)
+    out = subprocess.run(["nm", "-D", "--defined-only", A.lib_path()], capture_output=True, text=True).stdout
+    assert "oracle" not in out and "emu" not in out
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_index_agrees_with_reference_segmentation(built, name):
+    data, ref_rec = load_case(name)
+    entries = A.index_h264(data)
+    _, blocks = recproto.parse(ref_rec)
+    coded = [b for b in blocks if "cabac" in b or "skip_coded" in b]
+    assert len(coded) == len(entries)
+    pos = 0
+    k = 0
+    for b in blocks:
+        if "literal" in b:
+            pos += len(b["literal"])
+        elif "cabac" in b:
+            e = entries[k]
+            k += 1
+            assert e.recodable and e.desc.in_off == pos and e.desc.payload_size == b["size"]
+            pos += b["size"]
+        else:
+            assert not entries[k].recodable and entries[k].desc.payload_size == b["size"]
+            k += 1
+    assert pos == len(data)
+
+
+def test_index_edge_cases(built):
+    assert A.index_h264(b"") == []
+    assert A.index_h264(b"\x00" * 64) == []
+    assert A.index_h264(os.urandom(4096)) is not None        # garbage must not crash
+    data, _ = load_case(CASES[0])
+    for cut in (5, 40, len(data) // 2, len(data) - 1):       # truncated streams must not crash
+        A.index_h264(data[:cut])
+    ents = A.index_h264(data)
+    assert ents[0].desc.flags & _abi.AVR_SLICE_NEW_PICTURE
+    assert all(e.desc.chroma_format_idc == 1 for e in ents)
+
+
+@pytest.mark.parametrize("name", CASES)
+@pytest.mark.parametrize("mode_file", [True, False])
+def test_device_logic_on_host_matches_oracle(built, name, mode_file):
+    """avr_core.cuh / avr_job.cuh compiled as plain C++ (one emulated lane): same bytes as the oracle."""
+    data, _ = load_case(name)
+    descs = H.batch_descs(A.index_h264(data), mode_file)
+    r_o, b_o = H.oracle_compress(descs, data)
+    r_e, b_e = H.emu_compress(descs, data)
+    assert [r.status for r in r_e] == [0] * len(descs)
+    assert H.slices_of(r_e, b_e) == H.slices_of(r_o, b_o)
+    assert [r.n_bins for r in r_e] == [r.n_bins for r in r_o]
+    r_d, b_d = H.emu_decompress(H.coded_descs(descs, r_e), b_e)
+    assert [r.status for r in r_d] == [0] * len(descs)
+    for d, got in zip(descs, H.slices_of(r_d, b_d)):
+        payload = data[d.in_off:d.in_off + d.payload_size]
+        assert H.fix_tail(got, payload) == payload
+
+
+def test_manifest_matches_files():
+    import hashlib
+    for name, m in MANIFEST.items():
+        data, rec = load_case(name)
+        assert hashlib.sha256(data).hexdigest() == m["sha256"] and hashlib.sha256(rec).hexdigest() == m["rec_sha256"]
