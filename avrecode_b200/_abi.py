@@ -11,6 +11,8 @@ AVR_SLICE_NEW_PICTURE = 0x04
 AVR_SLICE_MBAFF = 0x08
 AVR_SLICE_FIELD = 0x10
 AVR_SLICE_NEW_MODEL = 0x20
+AVR_SLICE_STOP_BYTE = 0x40
+AVR_SLICE_SKIP = 0x80
 
 AVR_SLICE_OK, AVR_SLICE_UNSUPPORTED, AVR_SLICE_CORRUPT, AVR_SLICE_OVERFLOW = 0, 1, 2, 3
 AVR_MODE_FILE, AVR_MODE_SLICE = 0, 1

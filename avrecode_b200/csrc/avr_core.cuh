@@ -134,16 +134,17 @@ struct ByteWindow {
   const uint8_t* base;   // slice bytes in global memory (any alignment)
   uint8_t* win;          // WIN_BYTES of shared memory, 16-byte aligned
   uint32_t size;         // valid bytes
+  uint32_t tail;         // value of the byte at position `size` (0x80 with AVR_SLICE_STOP_BYTE, else 0); zero after it
   uint32_t skew;         // base & 15: ring positions are counted from the 16-byte aligned address below base
   uint32_t win_start;    // the ring holds aligned positions [win_start, win_start + WIN_BYTES); multiple of WIN_HALF
-  AVR_DEV void attach(const uint8_t* src, uint32_t n, uint8_t* window) {
-    base = src; size = n; win = window; win_start = 0;
+  AVR_DEV void attach(const uint8_t* src, uint32_t n, uint8_t* window, uint32_t tail_byte) {
+    base = src; size = n; win = window; win_start = 0; tail = tail_byte;
     skew = uint32_t(reinterpret_cast<uintptr_t>(src) & 15);
   }
   AVR_DEV uint32_t byte(uint32_t pos) const {
     const uint32_t a = pos + skew;
     if (a - win_start < WIN_BYTES) return win[a & (WIN_BYTES - 1)];
-    return pos < size ? base[pos] : 0;   // slow path: ran ahead of the window inside one macroblock
+    return pos < size ? base[pos] : (pos == size ? tail : 0);   // slow path: ran ahead of the window inside one macroblock
   }
   AVR_DEV uint32_t be16(uint32_t pos) const { return (byte(pos) << 8) | byte(pos + 1); }
 };
@@ -413,8 +414,8 @@ struct Compress {
   ByteWindow in;
   CabacIn cabac;
   RangeEnc rc;
-  AVR_DEV void begin(const uint8_t* src, uint32_t src_size, uint8_t* dst, uint32_t dst_cap, uint8_t* window) {
-    in.attach(src, src_size, window);
+  AVR_DEV void begin(const uint8_t* src, uint32_t src_size, uint8_t* dst, uint32_t dst_cap, uint8_t* window, uint32_t tail_byte) {
+    in.attach(src, src_size, window, tail_byte);
     rc.init(dst, dst_cap);
   }
   AVR_DEV void start_bins() { cabac.init(in); }
@@ -454,7 +455,7 @@ struct Decompress {
   static constexpr bool kDecompress = true;
   RangeDec rc;
   CabacOut cabac;
-  AVR_DEV void begin(const uint8_t* src, uint32_t src_size, uint8_t* dst, uint32_t dst_cap, uint8_t*) {
+  AVR_DEV void begin(const uint8_t* src, uint32_t src_size, uint8_t* dst, uint32_t dst_cap, uint8_t*, uint32_t) {
     rc.init(src, src_size);
     cabac.init(dst, dst_cap);
   }

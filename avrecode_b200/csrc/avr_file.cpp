@@ -143,8 +143,12 @@ int avr_file_compress(avr_ctx* ctx, const uint8_t* file, uint64_t file_bytes, in
     std::vector<avr_slice_desc> descs;
     map.clear();
     for (int i = 0; i < n_ents; i++) {
-      if (!coded[i]) continue;
+      if (!coded[i] && mode == AVR_MODE_SLICE) continue;
       avr_slice_desc d = ents[i].desc;
+      if (!coded[i]) {   // stays skip_coded + literal, but its frame_spec still flips the shared model's buffers
+        d.flags |= AVR_SLICE_SKIP;
+        d.in_off = 0; d.in_size = 0;
+      }
       if (map.empty() || mode == AVR_MODE_SLICE) d.flags |= AVR_SLICE_NEW_MODEL;
       descs.push_back(d);
       map.push_back(i);
@@ -154,7 +158,7 @@ int avr_file_compress(avr_ctx* ctx, const uint8_t* file, uint64_t file_bytes, in
     if (rc) { free(ents); return rc; }
     bool retry = false;
     for (size_t k = 0; k < descs.size(); k++) {
-      if (res[k].status != AVR_SLICE_OK) {
+      if (res[k].status != AVR_SLICE_OK && coded[map[k]]) {
         coded[map[k]] = 0;
         if (mode == AVR_MODE_FILE) { retry = true; break; }
       }
@@ -172,7 +176,7 @@ int avr_file_compress(avr_ctx* ctx, const uint8_t* file, uint64_t file_bytes, in
   for (int i = 0; i < n_ents; i++) {
     const avr_slice_desc& d = ents[i].desc;
     bool on_device = k < map.size() && map[k] == i;
-    bool ok = on_device && res[k].status == AVR_SLICE_OK;
+    bool ok = on_device && coded[i] && res[k].status == AVR_SLICE_OK;
     std::string body;
     if (ok) {
       std::string lit;
@@ -241,13 +245,14 @@ int avr_file_decompress(avr_ctx* ctx, const uint8_t* rec, uint64_t rec_bytes, ui
   for (int i = 0; i < n_ents; i++) {
     const Block& b = blocks[coded[i].block];
     if (uint64_t(b.size) != ents[i].desc.payload_size) { free(ents); return AVR_ERR_FORMAT; }   // "Invalid surrogate block size"
-    if (!coded[i].is_cabac) continue;
-    if (ents[i].desc.in_off != coded[i].off) { free(ents); return AVR_ERR_FORMAT; }
+    if (!coded[i].is_cabac && slice_mode) continue;
+    if (coded[i].is_cabac && ents[i].desc.in_off != coded[i].off) { free(ents); return AVR_ERR_FORMAT; }
     avr_slice_desc d = ents[i].desc;
     d.in_off = in.size();
-    d.in_size = uint32_t(b.cabac_n);
+    d.in_size = coded[i].is_cabac ? uint32_t(b.cabac_n) : 0;
+    if (!coded[i].is_cabac) d.flags |= AVR_SLICE_SKIP;
     if (descs.empty() || slice_mode) d.flags |= AVR_SLICE_NEW_MODEL;
-    in.append(reinterpret_cast<const char*>(b.cabac), b.cabac_n);
+    if (coded[i].is_cabac) in.append(reinterpret_cast<const char*>(b.cabac), b.cabac_n);
     descs.push_back(d);
     which.push_back(size_t(i));
   }
@@ -261,6 +266,7 @@ int avr_file_decompress(avr_ctx* ctx, const uint8_t* rec, uint64_t rec_bytes, ui
   // 3. splice the rebuilt payloads in, with the x264 padding fix-up of recode.cpp:1345-1354
   for (size_t k = 0; k < descs.size(); k++) {
     if (res[k].status != AVR_SLICE_OK) return AVR_ERR_FORMAT;   // "Not all blocks were decoded."
+    if (descs[k].flags & AVR_SLICE_SKIP) continue;
     const Block& b = blocks[coded[which[k]].block];
     std::string bytes(reinterpret_cast<const char*>(out + res[k].out_off), res[k].out_size);
     if (b.has_parity && b.has_last && b.last_n > 0) {

@@ -66,7 +66,8 @@ AVR_DEV void window_load_half(const ByteWindow& w, uint32_t from, int lane) {
       continue;
     }
 #endif
-    for (uint32_t k = 0; k < 16; k++) dst[k] = (apos + k >= w.skew && apos + k < aend) ? abase[apos + k] : 0;
+    for (uint32_t k = 0; k < 16; k++)
+      dst[k] = uint8_t((apos + k >= w.skew && apos + k < aend) ? abase[apos + k] : (apos + k == aend ? w.tail : 0));
   }
 }
 
@@ -102,12 +103,14 @@ AVR_DEV_NOINLINE void run_job(const JobArgs& a, const JobDesc& job, const Shared
   wk.mm.cur = 0;
   FrameTags ft;
   ft.w[0] = ft.w[1] = ft.h[0] = ft.h[1] = 0; ft.num[0] = ft.num[1] = 0; ft.cur = 0;
+  bool ctx_counters_stale = false;
   bool poisoned = false;   // a failed slice leaves the shared model undefined: fail the rest of the job
 
   for (uint32_t s = job.first_slice; s < job.first_slice + job.n_slices; s++) {
     const avr_slice_desc d = a.descs[s];
     const SliceIO io = a.ios[s];
     const bool fresh = s == job.first_slice || (d.flags & AVR_SLICE_NEW_MODEL);
+    const bool skip = (d.flags & AVR_SLICE_SKIP) != 0;   // frame_spec bookkeeping only
     const uint32_t frame_bytes = uint32_t(d.mb_width) * d.mb_height * NNZ_STRIDE;
     bool usable = !poisoned && frame_bytes <= job.nnz_frame_bytes && d.mb_width > 0 && d.mb_height > 0;
     if (usable) {
@@ -136,9 +139,14 @@ AVR_DEV_NOINLINE void run_job(const JobArgs& a, const JobDesc& job, const Shared
         }
       }
       wk.mm.cur = ft.cur;
-      init_contexts(ws, d, fresh, lane);
+      if (fresh && skip) ctx_counters_stale = true;   // the ctxIdx estimators are reset by the next walked slice
+    }
+    if (usable && !skip) {
+      init_contexts(ws, d, fresh || ctx_counters_stale, lane);
+      ctx_counters_stale = false;
       wk.d = d;
-      wk.dir.begin(a.in_arena + io.in_off, io.in_size, a.out_arena + io.out_off, io.out_cap, ws->window);
+      wk.dir.begin(a.in_arena + io.in_off, io.in_size, a.out_arena + io.out_off, io.out_cap, ws->window,
+                   (d.flags & AVR_SLICE_STOP_BYTE) ? 0x80u : 0u);
       if constexpr (!Dir::kDecompress) {
         ByteWindow& bw = window_of(wk.dir);
         window_load_half(bw, 0, lane);
@@ -147,7 +155,7 @@ AVR_DEV_NOINLINE void run_job(const JobArgs& a, const JobDesc& job, const Shared
     }
     AVR_SYNCWARP();
     int done = 1;
-    if (usable) {
+    if (usable && !skip) {
       if (lane == 0) wk.start();
       for (;;) {
         uint32_t in_pos = 0;
@@ -176,6 +184,7 @@ AVR_DEV_NOINLINE void run_job(const JobArgs& a, const JobDesc& job, const Shared
       r.out_off = io.out_off;
       r.reserved = 0;
       if (!usable) { r.status = poisoned ? AVR_SLICE_CORRUPT : AVR_SLICE_UNSUPPORTED; r.out_size = 0; r.n_mbs = 0; r.n_bins = 0; }
+      else if (skip) { r.status = AVR_SLICE_OK; r.out_size = 0; r.n_mbs = 0; r.n_bins = 0; }
       else {
         r.status = wk.status;
         r.out_size = wk.status == WALK_OK ? wk.dir.out_bytes() : 0;

@@ -303,6 +303,7 @@ extern "C" int avr_index_h264(const uint8_t* file, uint64_t file_bytes, avr_inde
               if (pp->transform_8x8_mode) fl |= AVR_SLICE_TRANSFORM_8X8;
               if (sp->direct_8x8_inference) fl |= AVR_SLICE_DIRECT_8X8_INFERENCE;
               if (new_picture) fl |= AVR_SLICE_NEW_PICTURE;
+              if (lastb == 0x80) fl |= AVR_SLICE_STOP_BYTE;
               if (field_pic) fl |= AVR_SLICE_FIELD;
               if (sp->mbaff && !field_pic) fl |= AVR_SLICE_MBAFF;
               if (unsupported || st >= 3 || sp->bit_depth_luma != 8) fl |= AVR_SLICE_FIELD;  // routed to "unsupported"

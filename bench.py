@@ -259,10 +259,7 @@ def run_ours(args):
     cd.launch(1); cd.sync()
     res_d, blob_d = cd.collect()
     # parity gate before any timing: round trip is the identity, first slices equal the CPU oracle's bytes
-    ok = all(r.status == 0 for r in res_d)
-    for d, got in zip(descs, H.slices_of(res_d, blob_d)):
-        p = data[d.in_off:d.in_off + d.payload_size]
-        ok = ok and H.fix_tail(got, p) == p
+    ok = H.roundtrip_ok(descs, res_d, blob_d, data)
     n_chk = min(2, len(descs))
     r_o, b_o = H.oracle_compress(descs[:n_chk], data)
     ok = ok and H.slices_of(res[:n_chk], blob) == H.slices_of(r_o, b_o)

@@ -38,6 +38,16 @@ extern "C" {
 #define AVR_SLICE_NEW_PICTURE          0x04 /* frame_spec hook fires before this slice (h264_slice.c:568-573) */
 #define AVR_SLICE_MBAFF                0x08 /* unsupported on device -> status AVR_SLICE_UNSUPPORTED */
 #define AVR_SLICE_FIELD                0x10 /* unsupported on device */
+#define AVR_SLICE_STOP_BYTE            0x40 /* the rbsp_stop_one_bit sits alone in the byte right after the payload
+                                               (payload rule h264.c:1298-1315): the reference's bin decoder, which reads the
+                                               whole NAL, sees 0x80 there and zero padding after it; without the flag every
+                                               byte past the payload reads as zero.  Compress direction only. */
+#define AVR_SLICE_SKIP                 0x80 /* a CABAC slice the host leaves as skip_coded + literal (recode.cpp:1289-1296).
+                                               The reference disables its bin hooks for it (recode.cpp:1139-1145) but the
+                                               model hooks still fire, so the FrameBuffer flip of frame_spec
+                                               (recode.cpp:824-843) must still happen: the device applies that and nothing
+                                               else (in_size = 0, result out_size = 0, status OK).  Only meaningful when
+                                               slices share a model (file mode). */
 #define AVR_SLICE_NEW_MODEL            0x20 /* chunk boundary: a fresh h264_model (recode.cpp:618-1059)
                                                -- estimators {1,1}, both FrameBuffers empty -- starts here.
                                                Reference-parity ("file") mode sets it on the first slice of a

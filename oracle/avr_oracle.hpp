@@ -14,6 +14,8 @@
 #pragma once
 #include <stdint.h>
 #include <string.h>
+#include <stdio.h>
+#include <stdlib.h>
 #include <map>
 #include <tuple>
 #include <vector>
@@ -202,8 +204,8 @@ class CabacEncoder {
 // ---------------------------------------------------------------------------------------------
 class CabacDecoder {
  public:
-  void init(const uint8_t* buf, int size) {  // cabac.c:193-218, 3-byte ("unaligned") prime
-    buf_ = buf; size_ = size; pos_ = 0;
+  void init(const uint8_t* buf, int size, int tail_byte = 0) {  // cabac.c:193-218, 3-byte ("unaligned") prime
+    buf_ = buf; size_ = size; pos_ = 0; tail_ = tail_byte;
     low_ = byte() << 18;
     low_ += byte() << 10;
     low_ += (byte() << 2) + 2;
@@ -251,7 +253,9 @@ class CabacDecoder {
   }
 
  private:
-  int byte() { int v = pos_ < size_ ? buf_[pos_] : 0; pos_++; return v; }
+  // past the payload the reference reads the rest of the NAL: a lone stop-bit byte 0x80 (when the
+  // slice has one, AVR_SLICE_STOP_BYTE) and then libavcodec's zero padding (h264.c:299-302)
+  int byte() { int v = pos_ < size_ ? buf_[pos_] : (pos_ == size_ ? tail_ : 0); pos_++; return v; }
   void refill() {  // cabac_functions.h:56-68
     int b0 = byte(), b1 = byte();
     low_ += (b0 << 9) + (b1 << 1);
@@ -264,7 +268,7 @@ class CabacDecoder {
     low_ += x * (1 << i);
   }
   static int norm_of(int v) { int s = 0; while ((v << s) < 0x100) s++; return s; }  // norm_shift[]
-  const uint8_t* buf_; int size_, pos_;
+  const uint8_t* buf_; int size_, pos_, tail_ = 0;
   int low_, range_;
 };
 
@@ -315,6 +319,11 @@ inline bool neighbor_sub_mb(bool above, int sub_mb_size, int mx, int my, int n, 
   if (sub_mb_size >= 32) nn = (nn / 4) * 4;  // :463-466
   *omx = mx; *omy = my; *on = nn;
   return true;
+}
+
+inline FILE* trace_file() {  // debugging aid: AVR_ORACLE_TRACE=<path> logs every model-coded bin
+  static FILE* f = getenv("AVR_ORACLE_TRACE") ? fopen(getenv("AVR_ORACLE_TRACE"), "w") : nullptr;
+  return f;
 }
 
 class Model {
@@ -375,6 +384,8 @@ class Model {
   // recode.cpp:1030-1047
   void update(int symbol, const ModelKey& k) {
     Estimator& e = estimators_[k];
+    if (FILE* tf = trace_file())  // same columns as oracle/_ref/recode_ref_trace: type, key identity, ints, symbol, counters
+      fprintf(tf, "%d %d %d %d %d %d %d\n", int(coding_type), std::get<0>(k) * 4096 + std::get<1>(k), std::get<2>(k), std::get<3>(k), symbol, e.pos, e.neg);
     if (symbol) e.pos++; else e.neg++;
     int limit = coding_type == CT_SIGMAP ? 0x50 : 0x60;
     if (e.pos + e.neg > limit) { e.pos = (e.pos + 1) / 2; e.neg = (e.neg + 1) / 2; }
@@ -482,8 +493,8 @@ inline int mk_hint(int kind, int arg = 0) { return kind | (arg << 8); }
 // compressor::cabac_decoder -- recode.cpp:1134-1268 (+ h264_symbol::execute :1061-1100)
 class CompressIO {
  public:
-  CompressIO(Model* m, const uint8_t* payload, int size, std::vector<uint8_t>* out)
-      : model_(m), enc_(out), out_(out) { dec_.init(payload, size); }
+  CompressIO(Model* m, const uint8_t* payload, int size, std::vector<uint8_t>* out, int tail_byte = 0)
+      : model_(m), enc_(out), out_(out) { dec_.init(payload, size, tail_byte); }
   uint8_t state[1024];
   uint64_t n_bins = 0;
 

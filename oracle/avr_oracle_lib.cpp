@@ -31,9 +31,10 @@ int run_all(const avr_slice_desc* descs, int n, const uint8_t* in, uint64_t in_b
       s->model.update_frame_spec(d.frame_num, d.mb_width, d.mb_height);  // frame_spec hook, h264_slice.c:568-573
       s->pic.start(d.mb_width, d.mb_height);
     }
+    if (d.flags & AVR_SLICE_SKIP) continue;  // model hooks only (recode.cpp:1139-1145): the frame flip above
     std::vector<uint8_t> bytes;
     try {
-      IO io = make_io(&s->model, in + d.in_off, int(d.in_size), &bytes);
+      IO io = make_io(&s->model, in + d.in_off, int(d.in_size), &bytes, (d.flags & AVR_SLICE_STOP_BYTE) ? 0x80 : 0);
       SliceWalker<IO> w(&io, &s->pic, d);
       r.n_mbs = uint32_t(w.run());
       r.n_bins = io.n_bins;
@@ -55,7 +56,7 @@ extern "C" {
 int avr_oracle_compress(const avr_slice_desc* descs, int n, const uint8_t* in, uint64_t in_bytes, avr_slice_result* res,
                         uint8_t** out, uint64_t* out_bytes) {
   return run_all<CompressIO>(descs, n, in, in_bytes, res, out, out_bytes,
-                             [](Model* m, const uint8_t* p, int sz, std::vector<uint8_t>* o) { return CompressIO(m, p, sz, o); });
+                             [](Model* m, const uint8_t* p, int sz, std::vector<uint8_t>* o, int tail) { return CompressIO(m, p, sz, o, tail); });
 }
 
 // mirror_compressor = 1: the format as the reference COMPRESSOR defines it (SURVEY hazards H8/H9);
@@ -63,7 +64,7 @@ int avr_oracle_compress(const avr_slice_desc* descs, int n, const uint8_t* in, u
 int avr_oracle_decompress(const avr_slice_desc* descs, int n, const uint8_t* in, uint64_t in_bytes, avr_slice_result* res,
                           uint8_t** out, uint64_t* out_bytes, int mirror_compressor) {
   return run_all<DecompressIO>(descs, n, in, in_bytes, res, out, out_bytes,
-                               [mirror_compressor](Model* m, const uint8_t* p, int sz, std::vector<uint8_t>* o) {
+                               [mirror_compressor](Model* m, const uint8_t* p, int sz, std::vector<uint8_t>* o, int) {
                                  DecompressIO io(m, p, sz, o);
                                  io.mirror_compressor = mirror_compressor != 0;
                                  return io;

@@ -55,9 +55,12 @@ def batch_descs(entries, mode_file):
     """Index entries -> slice descs for one file in file (shared model) or slice (chunk) mode."""
     descs = []
     for e in entries:
-        if not e.recodable:
+        if not e.recodable and not mode_file:
             continue
         d = copy_desc(e.desc)
+        if not e.recodable:   # skip_coded: only its frame_spec reaches the shared model (recode.cpp:1139-1145)
+            d.flags |= _abi.AVR_SLICE_SKIP
+            d.in_off, d.in_size = 0, 0
         if not descs or not mode_file:
             d.flags |= _abi.AVR_SLICE_NEW_MODEL
         descs.append(d)
@@ -106,6 +109,19 @@ def coded_descs(descs, results):
 
 def slices_of(results, blob):
     return [blob[r.out_off:r.out_off + r.out_size] for r in results]
+
+
+def roundtrip_ok(descs, results, blob, data):
+    """True when every rebuilt payload (after the x264 fix-up) equals the original slice_data bytes."""
+    for d, r in zip(descs, results):
+        if d.flags & _abi.AVR_SLICE_SKIP:
+            if r.status != 0 or r.out_size != 0:
+                return False
+            continue
+        payload = data[d.in_off:d.in_off + d.payload_size]
+        if r.status != 0 or fix_tail(blob[r.out_off:r.out_off + r.out_size], payload) != payload:
+            return False
+    return True
 
 
 def fix_tail(got, payload):

@@ -30,6 +30,8 @@ CASES = {
     "main_p_3refs": dict(width=352, height=288, frames=8, refs=3, seed=5, density=0.5),
     "high_no8x8": dict(width=256, height=144, frames=4, high=True, p8x8=0.0, seed=6),
     "tiny_1mb_rows": dict(mbw=3, mbh=2, frames=6, slices=2, seed=7, density=1.5),
+    # 1x1-macroblock pictures: slices whose rbsp_stop_one_bit sits alone in the next byte (AVR_SLICE_STOP_BYTE)
+    "one_mb_stop_byte": dict(mbw=1, mbh=1, frames=9, seed=14),
 }
 
 

@@ -26,10 +26,7 @@ def ctx(built):
 
 def check_roundtrip(ctx, descs, data, res, blob):
     r_d, b_d = ctx.decompress(H.coded_descs(descs, res), blob)
-    assert [r.status for r in r_d] == [0] * len(descs)
-    for d, got in zip(descs, H.slices_of(r_d, b_d)):
-        payload = data[d.in_off:d.in_off + d.payload_size]
-        assert H.fix_tail(got, payload) == payload
+    assert H.roundtrip_ok(descs, r_d, b_d, data)
     assert [r.n_bins for r in r_d] == [r.n_bins for r in res]
 
 
@@ -42,7 +39,8 @@ def test_file_mode_equals_reference_compressor(ctx, name):
     res, blob = ctx.compress(descs, data)
     assert [r.status for r in res] == [0] * len(descs)
     _, ref_blocks = recproto.parse(ref_rec)
-    assert H.slices_of(res, blob) == [b["cabac"] for b in ref_blocks if "cabac" in b]
+    assert [s for s, d in zip(H.slices_of(res, blob), descs) if not d.flags & _abi.AVR_SLICE_SKIP] == \
+        [b["cabac"] for b in ref_blocks if "cabac" in b]
     assert container_from(data, entries, res, blob) == ref_rec
     assert ctx.file_compress(data, A.MODE_FILE) == ref_rec
     check_roundtrip(ctx, descs, data, res, blob)

@@ -121,10 +121,7 @@ def test_device_logic_on_host_matches_oracle(built, name, mode_file):
     assert H.slices_of(r_e, b_e) == H.slices_of(r_o, b_o)
     assert [r.n_bins for r in r_e] == [r.n_bins for r in r_o]
     r_d, b_d = H.emu_decompress(H.coded_descs(descs, r_e), b_e)
-    assert [r.status for r in r_d] == [0] * len(descs)
-    for d, got in zip(descs, H.slices_of(r_d, b_d)):
-        payload = data[d.in_off:d.in_off + d.payload_size]
-        assert H.fix_tail(got, payload) == payload
+    assert H.roundtrip_ok(descs, r_d, b_d, data)
 
 
 def test_manifest_matches_files():
