@@ -35,7 +35,7 @@ def build(force=False, with_ref=True):
     os.makedirs(os.path.join(ROOT, "build"), exist_ok=True)
     os.makedirs(os.path.join(ROOT, "oracle", "_build"), exist_ok=True)
     hdrs = [os.path.join(ROOT, "include", "avrecode_b200.h")] + [
-        os.path.join(CSRC, f) for f in ("avr_core.cuh", "avr_job.cuh", "avr_tables.h")]
+        os.path.join(CSRC, f) for f in ("avr_core.cuh", "avr_walk.cuh", "avr_job.cuh", "avr_tables.h")]
     lib = os.path.join(ROOT, "avrecode_b200", "libavrecode_b200.so")
     lib_src = [os.path.join(CSRC, f) for f in ("avr_lib.cu", "avr_file.cpp", "h264_index.cpp")]
     if force or _newer(lib, lib_src + hdrs):

@@ -1,64 +1,99 @@
-// avr_job.cuh -- what one warp does with one job: cooperative set-up, lane-0 serial walk,
-// cooperative window refills.  Shared by the CUDA kernels (avr_kernels.cu) and by the host
-// emulation used for debugging in the GPU-less container (tests/emu/avr_emu.cpp, never shipped).
+// avr_job.cuh -- what one thread block (parser warp + coder warp) does with one job: cooperative
+// set-up, the two lane-0 serial roles joined by the symbol ring, cooperative window refills.
+// Shared by the CUDA kernels (avr_lib.cu) and by the host emulation used for debugging in the
+// GPU-less container (tests/emu/avr_emu.cpp, never shipped).
 //
-// Lane abstraction: on the device `lane` = threadIdx.x & 31 and AVR_LANES = 32; under
-// AVR_HOST_EMULATION there is a single lane, so every "for (i = lane; i < n; i += AVR_LANES)" loop
+// Thread abstraction: on the device a block has AVR_THREADS = 64 threads (warp 0 = parser, warp 1 =
+// coder); under AVR_HOST_EMULATION there is one thread that plays the parser for a whole slice into
+// an unbounded queue and then the coder, so every "for (i = tid; i < n; i += nthreads)" loop
 // degenerates to a plain loop and the sync / broadcast primitives are no-ops.
 #pragma once
-#include "avr_core.cuh"
+#include "avr_walk.cuh"
 
 #if defined(__CUDACC__) && !defined(AVR_HOST_EMULATION)
+#define AVR_THREADS 64
 #define AVR_LANES 32
 #define AVR_SYNCWARP() __syncwarp()
+#define AVR_SYNCBLOCK() __syncthreads()
 #define AVR_BCAST(v) __shfl_sync(0xFFFFFFFFu, (v), 0)
 #else
+#define AVR_THREADS 1
 #define AVR_LANES 1
 #define AVR_SYNCWARP() ((void)0)
+#define AVR_SYNCBLOCK() ((void)0)
 #define AVR_BCAST(v) (v)
 #endif
 
 namespace avr {
 
-AVR_DEV void fill_shared_tables(SharedTables* t, int tid, int nthreads) {
-  for (int i = tid; i < 100; i += nthreads) t->recip[i] = i >= 2 ? ~uint64_t(0) / uint64_t(i) : 0;  // floor((2^64-1)/d) == floor(2^64/d) unless d | 2^64
-  for (int i = tid; i < 256; i += nthreads) t->range_lps[i] = avr_range_lps[i];
-  for (int i = tid; i < 64; i += nthreads) {
-    t->trans_lps[i] = avr_trans_lps[i];
-    t->sig8[i] = i < 63 ? avr_sig8x8_inc[i] : 0;
-    t->last8[i] = i < 63 ? avr_last8x8_inc[i] : 0;
-  }
-}
+struct JobDesc {        // one block's work: slices [first, first + count) share one model
+  uint32_t first_slice;
+  uint32_t n_slices;
+  uint32_t weight;      // host-side ordering key (input bytes)
+  uint32_t reserved;
+};
 
-// CABAC context initialisation (H.264 9.3.1.1; h264_cabac.c:1267-1286): 1024 states per slice.
-// The avrecode counters packed in the same word survive unless `reset_counters`.
-AVR_DEV void init_contexts(WarpState* ws, const avr_slice_desc& d, bool reset_counters, int lane) {
+struct SliceIO {        // device-side view of one slice's buffers
+  uint64_t in_off;      // into the input arena
+  uint64_t out_off;     // into the output arena
+  uint32_t in_size;
+  uint32_t out_cap;
+};
+
+// Fixed part of a block's shared memory; the neighbour row and (when resident) the estimators follow.
+struct BlockShared {
+  SharedTables tab;
+  RingShared ring;
+  alignas(16) uint8_t window[WIN_BYTES];
+  U2 cstate[N_CTX_PAD];     // CABAC context states {state, rangeTabLPS row}
+  uint32_t job;             // job handed out by the atomic counter
+  uint32_t final_status;    // status of the slice just finished (coder writes, everyone reads)
+  uint32_t pad_[2];
+};
+
+struct JobArgs {
+  const avr_slice_desc* descs;
+  const SliceIO* ios;
+  const uint8_t* in_arena;
+  uint8_t* out_arena;
+  avr_slice_result* results;
+};
+
+struct JobMem {             // where this block keeps its state
+  BlockShared* sh;
+  MbCtx* row;               // [max_mbw], shared memory
+  uint16_t* cnt;            // MODEL_COUNTERS estimators: shared memory (resident) or global workspace
+  uint8_t* nnz[2];          // two FrameBuffer nnz planes, global workspace
+  uint32_t nnz_frame_bytes; // capacity of one plane
+};
+
+// CABAC context initialisation (H.264 9.3.1.1; h264_cabac.c:1267-1286) for the contexts in use.
+AVR_DEV void init_contexts(U2* cstate, const avr_slice_desc& d, int tid, int nthreads) {
   const int set = d.slice_type == AVR_SLICE_I ? 0 : 1 + d.cabac_init_idc;
   const int qp = d.slice_qp < 0 ? 0 : (d.slice_qp > 51 ? 51 : d.slice_qp);
-  for (int i = lane; i < 1024; i += AVR_LANES) {
-    uint32_t mn = avr_ctx_init_mn[set * 1024 + i];
-    int m = int(int8_t(mn >> 8)), n = int(int8_t(mn & 0xFF));
+  for (int i = tid; i < N_CTX; i += nthreads) {
+    const uint32_t mn = avr_ctx_init_mn[set * 1024 + ctx_idx_of_dense(i)];
+    const int m = int(int8_t(mn >> 8)), n = int(int8_t(mn & 0xFF));
     int pre = ((m * qp) >> 4) + n;
     pre = pre < 1 ? 1 : (pre > 126 ? 126 : pre);
     // pStateIdx / valMPS from preCtxState; same numbers as libavcodec's 2*(..)-127 folding
-    uint32_t state = pre <= 63 ? uint32_t((63 - pre) << 1) : uint32_t(((pre - 64) << 1) | 1);
-    uint32_t w = ws->ctx[i];
-    ws->ctx[i] = reset_counters ? (state | (1u << 8) | (1u << 16)) : ((w & ~0xFFu) | state);
+    const uint32_t state = pre <= 63 ? uint32_t((63 - pre) << 1) : uint32_t(((pre - 64) << 1) | 1);
+    cstate[i].x = state;
+    cstate[i].y = rlps4_of(state >> 1);
   }
-  if (lane == 0 && reset_counters) { ws->bypass_cnt = 1 | (1 << 8); ws->term_cnt = 1 | (1 << 8); }
 }
 
-AVR_DEV void fill_u32(uint32_t* p, uint64_t n_words, uint32_t v, int lane) {
-  for (uint64_t i = uint64_t(lane); i < n_words; i += AVR_LANES) p[i] = v;
+AVR_DEV void fill_u32(uint32_t* p, uint32_t n_words, uint32_t v, int tid, int nthreads) {
+  for (uint32_t i = uint32_t(tid); i < n_words; i += uint32_t(nthreads)) p[i] = v;
 }
 
 // loads aligned positions [from, from + WIN_HALF) into their ring slots, one aligned 16-byte load per
-// lane; bytes past the end of the slice read as zero, the <= 15 bytes before its start are don't-care
+// lane; past the end of the slice: the tail byte, then zeros; the <= 15 bytes before its start are don't-care
 AVR_DEV void window_load_half(const ByteWindow& w, uint32_t from, int lane) {
   const uint8_t* abase = w.base - w.skew;
   const uint32_t aend = w.size + w.skew;
   for (uint32_t o = uint32_t(lane) * 16; o < WIN_HALF; o += AVR_LANES * 16) {
-    uint32_t apos = from + o;
+    const uint32_t apos = from + o;
     uint8_t* dst = w.win + (apos & (WIN_BYTES - 1));
 #if defined(__CUDA_ARCH__)
     if (apos + 16 <= aend) {
@@ -76,34 +111,83 @@ struct FrameTags {
   int w[2], h[2], num[2], cur;
 };
 
-struct JobArgs {
-  const avr_slice_desc* descs;
-  const SliceIO* ios;
-  const uint8_t* in_arena;
-  uint8_t* out_arena;
-  avr_slice_result* results;
-  uint8_t* workspace;
-};
-
-AVR_DEV ByteWindow& window_of(Compress& c) { return c.in; }
-AVR_DEV uint32_t window_limit(const Compress& c) { return c.in.win_start + WIN_HALF - c.in.skew; }
-AVR_DEV uint32_t window_limit(const Decompress&) { return 0xFFFFFFFFu; }
-
-// Runs one job on the calling warp.
+// ---- parser warp: lane 0 walks the slice, all 32 lanes keep its input window filled ---------------
 template <class Dir>
-AVR_DEV_NOINLINE void run_job(const JobArgs& a, const JobDesc& job, const SharedTables* tab, WarpState* ws, MbCtx* row, int lane) {
+AVR_DEV void parser_role(const JobArgs& a, const JobMem& m, const avr_slice_desc& d, const SliceIO& io, int cur_frame, int lane) {
   Walker<Dir> wk;
-  wk.tab = tab;
-  wk.ws = ws;
-  wk.row = row;
-  wk.mm.sig = reinterpret_cast<uint16_t*>(a.workspace + job.model_off);
-  wk.mm.nz = wk.mm.sig + SIG_ENTRIES;
-  wk.mm.nnz[0] = a.workspace + job.nnz_off;
-  wk.mm.nnz[1] = a.workspace + job.nnz_off + job.nnz_frame_bytes;
-  wk.mm.cur = 0;
+  wk.tab = &m.sh->tab;
+  wk.row = m.row;
+  wk.mm.nnz[0] = m.nnz[0]; wk.mm.nnz[1] = m.nnz[1]; wk.mm.cur = cur_frame;
+  wk.d = d;
+  wk.dir.begin(a.in_arena + io.in_off, io.in_size, m.sh->window, (d.flags & AVR_SLICE_STOP_BYTE) ? 0x80u : 0u, &m.sh->ring,
+               m.cnt, m.sh->cstate);
+  window_load_half(wk.dir.in, 0, lane);
+  window_load_half(wk.dir.in, WIN_HALF, lane);
+  AVR_SYNCWARP();
+  if (lane == 0) wk.start();
+  for (;;) {
+    int done = 1;
+    uint32_t in_pos = 0;
+    if (lane == 0) {
+      const uint32_t limit = wk.dir.in.limit();
+      while (!wk.done && wk.dir.in_pos() < limit) wk.step();
+      done = wk.done;
+      in_pos = wk.dir.in_pos();
+    }
+    done = AVR_BCAST(done);
+    if (done) break;
+    in_pos = AVR_BCAST(in_pos);
+    ByteWindow& bw = wk.dir.in;
+    AVR_SYNCWARP();
+    while (in_pos + bw.skew >= bw.win_start + WIN_HALF) {   // the consumed half is free: load the next 512 bytes into it
+      window_load_half(bw, bw.win_start + WIN_BYTES, lane);
+      bw.win_start += WIN_HALF;
+    }
+    AVR_SYNCWARP();
+  }
+  if (lane == 0) {
+    RingShared* r = &m.sh->ring;
+    r->end_status = uint32_t(wk.status);
+    r->end_mbs = wk.n_mbs;
+    r->end_bins_lo = uint32_t(wk.n_bins);
+    r->end_bins_hi = uint32_t(wk.n_bins >> 32);
+    wk.dir.q.push(SYM_END);
+    wk.dir.q.publish();
+  }
+  AVR_SYNCWARP();
+}
+
+// ---- coder warp: lane 0 drains the ring and owns the output bytes and the slice result -------------
+template <class Dir>
+AVR_DEV void coder_role(const JobArgs& a, const JobMem& m, const SliceIO& io, uint32_t s, int lane) {
+  if (lane == 0) {
+    typename Dir::Coder c;
+    c.begin(a.out_arena + io.out_off, io.out_cap);
+    Consumer q;
+    q.init(&m.sh->ring);
+    c.run(q, m.sh->tab, m.cnt, m.sh->cstate);
+    const volatile RingShared* r = &m.sh->ring;
+    avr_slice_result res;
+    res.out_off = io.out_off;
+    res.status = int32_t(r->end_status);
+    if (res.status == AVR_SLICE_OK && c.overflowed()) res.status = AVR_SLICE_OVERFLOW;
+    res.out_size = res.status == AVR_SLICE_OK ? c.out_bytes() : 0;
+    res.n_mbs = r->end_mbs;
+    res.reserved = 0;
+    res.n_bins = uint64_t(r->end_bins_lo) | uint64_t(r->end_bins_hi) << 32;
+    a.results[s] = res;
+    m.sh->final_status = uint32_t(res.status);
+  }
+  AVR_SYNCWARP();
+}
+
+// Runs one job on the calling block.
+template <class Dir>
+AVR_DEV_NOINLINE void run_job(const JobArgs& a, const JobDesc& job, const JobMem& m, int tid) {
+  const int nthreads = AVR_THREADS;
+  const int lane = tid & (AVR_LANES - 1);
   FrameTags ft;
   ft.w[0] = ft.w[1] = ft.h[0] = ft.h[1] = 0; ft.num[0] = ft.num[1] = 0; ft.cur = 0;
-  bool ctx_counters_stale = false;
   bool poisoned = false;   // a failed slice leaves the shared model undefined: fail the rest of the job
 
   for (uint32_t s = job.first_slice; s < job.first_slice + job.n_slices; s++) {
@@ -112,90 +196,54 @@ AVR_DEV_NOINLINE void run_job(const JobArgs& a, const JobDesc& job, const Shared
     const bool fresh = s == job.first_slice || (d.flags & AVR_SLICE_NEW_MODEL);
     const bool skip = (d.flags & AVR_SLICE_SKIP) != 0;   // frame_spec bookkeeping only
     const uint32_t frame_bytes = uint32_t(d.mb_width) * d.mb_height * NNZ_STRIDE;
-    bool usable = !poisoned && frame_bytes <= job.nnz_frame_bytes && d.mb_width > 0 && d.mb_height > 0;
+    const bool usable = !poisoned && frame_bytes <= m.nnz_frame_bytes && d.mb_width > 0 && d.mb_height > 0;
     if (usable) {
       if (fresh) {
         // a brand-new h264_model: every estimator {1,1} (recode.cpp:1057), no frame buffers yet
-        fill_u32(reinterpret_cast<uint32_t*>(wk.mm.sig), MODEL_COUNTERS / 2, 0x01010101u, lane);
+        fill_u32(reinterpret_cast<uint32_t*>(m.cnt), MODEL_COUNTERS / 2, 0x01010101u, tid, nthreads);
         ft.w[0] = ft.w[1] = ft.h[0] = ft.h[1] = 0; ft.cur = 0;
       }
       if ((d.flags & AVR_SLICE_NEW_PICTURE) || fresh || ft.w[ft.cur] != d.mb_width || ft.h[ft.cur] != d.mb_height) {
         // update_frame_spec (recode.cpp:824-843): flip + clear unless same frame_num and size
-        bool same = ft.num[ft.cur] == d.frame_num && ft.w[ft.cur] != 0 && ft.h[ft.cur] != 0;
+        const bool same = ft.num[ft.cur] == d.frame_num && ft.w[ft.cur] != 0 && ft.h[ft.cur] != 0;
         if (ft.w[ft.cur] != d.mb_width || ft.h[ft.cur] != d.mb_height || !same) {
           ft.cur ^= 1;
           const int c = ft.cur;
+          fill_u32(reinterpret_cast<uint32_t*>(m.nnz[c]), frame_bytes / 4, 0, tid, nthreads);
           if (ft.w[c] != d.mb_width || ft.h[c] != d.mb_height) {
             ft.w[c] = d.mb_width; ft.h[c] = d.mb_height;
-            fill_u32(reinterpret_cast<uint32_t*>(wk.mm.nnz[c]), frame_bytes / 4, 0, lane);
             if (ft.w[c ^ 1] != d.mb_width || ft.h[c ^ 1] != d.mb_height) {
               ft.w[c ^ 1] = d.mb_width; ft.h[c ^ 1] = d.mb_height;
-              fill_u32(reinterpret_cast<uint32_t*>(wk.mm.nnz[c ^ 1]), frame_bytes / 4, 0, lane);
+              fill_u32(reinterpret_cast<uint32_t*>(m.nnz[c ^ 1]), frame_bytes / 4, 0, tid, nthreads);
             }
-          } else {
-            fill_u32(reinterpret_cast<uint32_t*>(wk.mm.nnz[c]), frame_bytes / 4, 0, lane);
           }
           ft.num[c] = d.frame_num;
         }
       }
-      wk.mm.cur = ft.cur;
-      if (fresh && skip) ctx_counters_stale = true;   // the ctxIdx estimators are reset by the next walked slice
     }
-    if (usable && !skip) {
-      init_contexts(ws, d, fresh || ctx_counters_stale, lane);
-      ctx_counters_stale = false;
-      wk.d = d;
-      wk.dir.begin(a.in_arena + io.in_off, io.in_size, a.out_arena + io.out_off, io.out_cap, ws->window,
-                   (d.flags & AVR_SLICE_STOP_BYTE) ? 0x80u : 0u);
-      if constexpr (!Dir::kDecompress) {
-        ByteWindow& bw = window_of(wk.dir);
-        window_load_half(bw, 0, lane);
-        window_load_half(bw, WIN_HALF, lane);
-      }
+    const bool walk = usable && !skip;
+    if (walk) {
+      init_contexts(m.sh->cstate, d, tid, nthreads);
+      if (tid == 0) ring_reset(&m.sh->ring);
     }
-    AVR_SYNCWARP();
-    int done = 1;
-    if (usable && !skip) {
-      if (lane == 0) wk.start();
-      for (;;) {
-        uint32_t in_pos = 0;
-        if (lane == 0) {
-          const uint32_t limit = window_limit(wk.dir);
-          while (!wk.done && wk.dir.in_pos() < limit) wk.step();
-          done = wk.done;
-          in_pos = wk.dir.in_pos();
-        }
-        done = AVR_BCAST(done);
-        if (done) break;
-        in_pos = AVR_BCAST(in_pos);
-        if constexpr (!Dir::kDecompress) {
-          ByteWindow& bw = window_of(wk.dir);
-          AVR_SYNCWARP();
-          while (in_pos + bw.skew >= bw.win_start + WIN_HALF) {   // the consumed half is free: load the next 512 bytes into it
-            window_load_half(bw, bw.win_start + WIN_BYTES, lane);
-            bw.win_start += WIN_HALF;
-          }
-          AVR_SYNCWARP();
-        }
-      }
-    }
-    if (lane == 0) {
+    AVR_SYNCBLOCK();
+    if (walk) {
+#if defined(__CUDACC__) && !defined(AVR_HOST_EMULATION)
+      if (tid < 32) parser_role<Dir>(a, m, d, io, ft.cur, lane);
+      else coder_role<Dir>(a, m, io, s, lane);
+#else
+      parser_role<Dir>(a, m, d, io, ft.cur, lane);
+      coder_role<Dir>(a, m, io, s, lane);
+#endif
+    } else if (tid == 0) {
       avr_slice_result r;
-      r.out_off = io.out_off;
-      r.reserved = 0;
-      if (!usable) { r.status = poisoned ? AVR_SLICE_CORRUPT : AVR_SLICE_UNSUPPORTED; r.out_size = 0; r.n_mbs = 0; r.n_bins = 0; }
-      else if (skip) { r.status = AVR_SLICE_OK; r.out_size = 0; r.n_mbs = 0; r.n_bins = 0; }
-      else {
-        r.status = wk.status;
-        r.out_size = wk.status == WALK_OK ? wk.dir.out_bytes() : 0;
-        r.n_mbs = wk.n_mbs;
-        r.n_bins = wk.n_bins;
-      }
+      r.out_off = io.out_off; r.out_size = 0; r.n_mbs = 0; r.reserved = 0; r.n_bins = 0;
+      r.status = usable ? AVR_SLICE_OK : (poisoned ? AVR_SLICE_CORRUPT : AVR_SLICE_UNSUPPORTED);
       a.results[s] = r;
-      if (r.status != AVR_SLICE_OK) poisoned = true;
+      m.sh->final_status = uint32_t(r.status);
     }
-    poisoned = AVR_BCAST(int(poisoned)) != 0;
-    AVR_SYNCWARP();
+    AVR_SYNCBLOCK();
+    if (m.sh->final_status != AVR_SLICE_OK) poisoned = true;
   }
 }
 

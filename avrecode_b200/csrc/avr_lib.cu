@@ -22,32 +22,44 @@ struct KernelArgs {
   const JobDesc* jobs;
   uint32_t n_jobs;
   uint32_t* counter;        // next job to hand out
-  uint64_t work_stride;     // bytes of workspace per resident warp
-  uint32_t nnz_frame_bytes; // bytes of one model frame buffer inside a workspace slot
-  uint32_t max_mbw;         // row buffer entries per warp
+  uint8_t* workspace;       // per-block slots: [estimators unless resident] [nnz plane 0] [nnz plane 1]
+  uint64_t work_stride;     // bytes of workspace per resident block
+  uint32_t nnz_frame_bytes; // bytes of one nnz plane inside a slot
+  uint32_t max_mbw;         // neighbour-row entries per block
 };
 
-// Block = one warp.  Shared memory: SharedTables | WarpState | MbCtx row[max_mbw].
-template <class Dir>
-__global__ void __launch_bounds__(32, 8) avr_job_kernel(KernelArgs k) {
+size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+size_t row_bytes(uint32_t max_mbw) { return align_up(size_t(max_mbw) * sizeof(MbCtx), 16); }
+size_t counters_bytes() { return align_up(size_t(MODEL_COUNTERS) * 2, 256); }
+size_t smem_bytes(uint32_t max_mbw, bool resident) {
+  return sizeof(BlockShared) + row_bytes(max_mbw) + (resident ? size_t(MODEL_COUNTERS) * 2 : 0);
+}
+
+// Block = parser warp + coder warp.  Shared memory: BlockShared | MbCtx row[max_mbw] | estimators (RESIDENT).
+// Persistent blocks take jobs from an atomic counter (longest first).
+template <class Dir, bool RESIDENT>
+__global__ void __launch_bounds__(AVR_THREADS, RESIDENT ? 2 : 8) avr_job_kernel(KernelArgs k) {
   extern __shared__ __align__(16) uint8_t smem[];
-  SharedTables* tab = reinterpret_cast<SharedTables*>(smem);
-  WarpState* ws = reinterpret_cast<WarpState*>(smem + sizeof(SharedTables));
-  MbCtx* row = reinterpret_cast<MbCtx*>(smem + sizeof(SharedTables) + sizeof(WarpState));
-  const int lane = threadIdx.x & 31;
-  fill_shared_tables(tab, lane, 32);
-  __syncwarp();
-  const uint64_t slot = uint64_t(blockIdx.x) * k.work_stride;
+  JobMem m;
+  m.sh = reinterpret_cast<BlockShared*>(smem);
+  m.row = reinterpret_cast<MbCtx*>(smem + sizeof(BlockShared));
+  uint8_t* slot = k.workspace + uint64_t(blockIdx.x) * k.work_stride;
+  const size_t rb = (size_t(k.max_mbw) * sizeof(MbCtx) + 15) / 16 * 16;
+  if (RESIDENT) m.cnt = reinterpret_cast<uint16_t*>(smem + sizeof(BlockShared) + rb);
+  else { m.cnt = reinterpret_cast<uint16_t*>(slot); slot += (size_t(MODEL_COUNTERS) * 2 + 255) / 256 * 256; }
+  m.nnz[0] = slot;
+  m.nnz[1] = slot + k.nnz_frame_bytes;
+  m.nnz_frame_bytes = k.nnz_frame_bytes;
+  const int tid = threadIdx.x;
+  fill_shared_tables(&m.sh->tab, tid, AVR_THREADS);
+  __syncthreads();
   for (;;) {
-    uint32_t j = 0;
-    if (lane == 0) j = atomicAdd(k.counter, 1u);
-    j = __shfl_sync(0xFFFFFFFFu, j, 0);
+    if (tid == 0) m.sh->job = atomicAdd(k.counter, 1u);
+    __syncthreads();
+    const uint32_t j = m.sh->job;
+    __syncthreads();
     if (j >= k.n_jobs) break;
-    JobDesc job = k.jobs[j];
-    job.model_off = slot;
-    job.nnz_off = slot + uint64_t(MODEL_COUNTERS) * 2;
-    job.nnz_frame_bytes = k.nnz_frame_bytes;
-    run_job<Dir>(k.a, job, tab, ws, row, lane);
+    run_job<Dir>(k.a, k.jobs[j], m, tid);
   }
 }
 
@@ -86,8 +98,12 @@ struct avr_ctx {
   size_t in_bytes = 0;
   uint32_t max_mbw = 1, max_frame_bytes = 0;
   int grid = 0;
+  bool resident = true;
+  int force_resident = -1;   // AVR_RESIDENT env: 0 / 1, -1 = heuristic
   // meta offsets
   size_t off_descs = 0, off_ios = 0, off_jobs = 0, off_res = 0, off_counter = 0;
+  uint64_t work_stride = 0;
+  int max_smem_sm = 0;
   float last_ms = 0.f;
   uint64_t launches = 0;
   int cfg_warps = 0;
@@ -120,8 +136,6 @@ int grow_pinned(uint8_t** p, size_t* cap, size_t need) {
   *cap = want;
   return AVR_OK;
 }
-size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
-
 }  // namespace
 
 extern "C" {
@@ -158,6 +172,8 @@ int avr_create(const avr_config* cfg, avr_ctx** out) {
   if (!ck(cudaGetDeviceProperties(&prop, dev), "cudaGetDeviceProperties")) { delete c; return AVR_ERR_CUDA; }
   c->sm_count = prop.multiProcessorCount;
   c->max_smem_optin = int(prop.sharedMemPerBlockOptin);
+  c->max_smem_sm = int(prop.sharedMemPerMultiprocessor);
+  if (const char* e = getenv("AVR_RESIDENT")) c->force_resident = atoi(e) ? 1 : 0;
   if (!ck(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking), "cudaStreamCreate") ||
       !ck(cudaEventCreate(&c->ev0), "cudaEventCreate") || !ck(cudaEventCreate(&c->ev1), "cudaEventCreate")) {
     avr_destroy(c);
@@ -219,22 +235,32 @@ int avr_stage(avr_ctx* c, const avr_slice_desc* descs, int n, const uint8_t* in,
       c->jobs.push_back(j);
     }
     c->jobs.back().n_slices++;
-    c->jobs.back().reserved += d.in_size > 0x7FFFFFFFu - c->jobs.back().reserved ? 0 : d.in_size;  // job weight
+    c->jobs.back().weight += d.in_size > 0x7FFFFFFFu - c->jobs.back().weight ? 0 : d.in_size;
   }
   // longest jobs first (LPT order for the dynamic hand-out)
-  std::stable_sort(c->jobs.begin(), c->jobs.end(), [](const JobDesc& a, const JobDesc& b) { return a.reserved > b.reserved; });
+  std::stable_sort(c->jobs.begin(), c->jobs.end(), [](const JobDesc& a, const JobDesc& b) { return a.weight > b.weight; });
   c->n_jobs = int(c->jobs.size());
   c->max_frame_bytes = uint32_t(align_up(c->max_frame_bytes, 16));
 
-  // grid: one warp per block; enough blocks to cover the jobs, capped by residency
-  size_t smem = sizeof(SharedTables) + sizeof(WarpState) + size_t(c->max_mbw) * sizeof(MbCtx);
-  int per_sm = c->cfg_warps > 0 ? c->cfg_warps : 16;
-  int by_smem = int(size_t(200 * 1024) / smem);
-  per_sm = std::max(1, std::min(per_sm, by_smem));
-  c->grid = std::max(1, std::min(c->n_jobs, c->sm_count * per_sm));
+  // Placement of the estimators: in shared memory (<= 2 blocks per SM, every per-bin access at LDS
+  // latency) while the batch is small enough to be latency-bound, in the global workspace with more
+  // blocks per SM once there are enough independent jobs to hide L1/L2 latency instead.
+  const size_t smem_res = smem_bytes(c->max_mbw, true), smem_glb = smem_bytes(c->max_mbw, false);
+  const size_t smem_sm = size_t(c->max_smem_sm);
+  int res_per_sm = smem_res + 1024 <= size_t(c->max_smem_optin) ? int(smem_sm / (smem_res + 1024)) : 0;
+  res_per_sm = std::min(res_per_sm, 2);
+  int glb_per_sm = std::max(1, std::min(c->cfg_warps > 0 ? c->cfg_warps : 8, int(smem_sm / (smem_glb + 1024))));
+  glb_per_sm = std::min(glb_per_sm, 8);
+  if (smem_glb + 1024 > size_t(c->max_smem_optin)) return AVR_ERR_ARG;   // picture too wide for the neighbour row
+  bool resident = res_per_sm > 0 && c->n_jobs <= 3 * res_per_sm * c->sm_count;
+  if (c->force_resident == 0) resident = false;
+  if (c->force_resident == 1 && res_per_sm > 0) resident = true;
+  c->resident = resident;
+  c->grid = std::max(1, std::min(c->n_jobs, c->sm_count * (resident ? res_per_sm : glb_per_sm)));
 
   // device memory
-  const uint64_t work_stride = align_up(size_t(MODEL_COUNTERS) * 2 + 2 * size_t(c->max_frame_bytes), 256);
+  const uint64_t work_stride = align_up((resident ? 0 : counters_bytes()) + 2 * size_t(c->max_frame_bytes), 256);
+  c->work_stride = work_stride;
   int rc;
   if ((rc = grow_dev(&c->d_in, &c->d_in_cap, size_t(in_bytes) + 64))) return rc;
   if ((rc = grow_dev(&c->d_out, &c->d_out_cap, size_t(std::max(c->out_total[0], c->out_total[1])) + 64))) return rc;
@@ -273,24 +299,25 @@ int avr_launch(avr_ctx* c, int direction) {
   k.a.in_arena = c->d_in;
   k.a.out_arena = c->d_out;
   k.a.results = reinterpret_cast<avr_slice_result*>(c->d_meta + c->off_res);
-  k.a.workspace = c->d_work;
   k.jobs = reinterpret_cast<const JobDesc*>(c->d_meta + c->off_jobs);
   k.n_jobs = uint32_t(c->n_jobs);
   k.counter = reinterpret_cast<uint32_t*>(c->d_meta + c->off_counter);
-  k.work_stride = align_up(size_t(MODEL_COUNTERS) * 2 + 2 * size_t(c->max_frame_bytes), 256);
+  k.workspace = c->d_work;
+  k.work_stride = c->work_stride;
   k.nnz_frame_bytes = c->max_frame_bytes;
   k.max_mbw = c->max_mbw;
-  size_t smem = sizeof(SharedTables) + sizeof(WarpState) + size_t(c->max_mbw) * sizeof(MbCtx);
+  const size_t smem = smem_bytes(c->max_mbw, c->resident);
   if (int(smem) > c->max_smem_optin) return AVR_ERR_ARG;
   CK(cudaMemsetAsync(k.counter, 0, sizeof(uint32_t), c->stream));
   CK(cudaEventRecord(c->ev0, c->stream));
-  if (direction == 0) {
-    if (smem > 48 * 1024) CK(cudaFuncSetAttribute(avr_job_kernel<Compress>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
-    avr_job_kernel<Compress><<<c->grid, 32, smem, c->stream>>>(k);
-  } else {
-    if (smem > 48 * 1024) CK(cudaFuncSetAttribute(avr_job_kernel<Decompress>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
-    avr_job_kernel<Decompress><<<c->grid, 32, smem, c->stream>>>(k);
-  }
+#define AVR_LAUNCH(DIR, RES)                                                                                              \
+  do {                                                                                                                    \
+    CK(cudaFuncSetAttribute(avr_job_kernel<DIR, RES>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));          \
+    avr_job_kernel<DIR, RES><<<c->grid, AVR_THREADS, smem, c->stream>>>(k);                                               \
+  } while (0)
+  if (direction == 0) { if (c->resident) AVR_LAUNCH(Compress, true); else AVR_LAUNCH(Compress, false); }
+  else { if (c->resident) AVR_LAUNCH(Decompress, true); else AVR_LAUNCH(Decompress, false); }
+#undef AVR_LAUNCH
   CK(cudaGetLastError());
   CK(cudaEventRecord(c->ev1, c->stream));
   c->launches++;

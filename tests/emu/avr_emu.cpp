@@ -28,23 +28,26 @@ static int run(const avr_slice_desc* descs, int n, const uint8_t* in, uint64_t i
     if (descs[i].in_off + descs[i].in_size > in_bytes) return AVR_ERR_ARG;
   }
   std::vector<uint8_t> arena(out_total + 16);
-  std::vector<uint8_t> workspace(size_t(MODEL_COUNTERS) * 2 + 2 * size_t(max_frame) + 64);
-  SharedTables tab;
-  fill_shared_tables(&tab, 0, 1);
-  WarpState* ws = new WarpState();
+  std::vector<uint16_t> counters(MODEL_COUNTERS);
+  max_frame = (max_frame + 15u) & ~15u;
+  std::vector<uint8_t> planes(2 * size_t(max_frame) + 64);
+  BlockShared* sh = new BlockShared();
+  fill_shared_tables(&sh->tab, 0, 1);
   std::vector<MbCtx> row(max_mbw);
-  JobArgs a{descs, ios.data(), in, arena.data(), res, workspace.data()};
+  JobArgs a{descs, ios.data(), in, arena.data(), res};
+  JobMem m;
+  m.sh = sh; m.row = row.data(); m.cnt = counters.data();
+  m.nnz[0] = planes.data(); m.nnz[1] = planes.data() + max_frame; m.nnz_frame_bytes = max_frame;
   int i = 0;
   while (i < n) {
     int j = i + 1;
     while (j < n && !(descs[j].flags & AVR_SLICE_NEW_MODEL)) j++;
     JobDesc job;
-    job.first_slice = uint32_t(i); job.n_slices = uint32_t(j - i);
-    job.model_off = 0; job.nnz_off = uint64_t(MODEL_COUNTERS) * 2; job.nnz_frame_bytes = max_frame; job.reserved = 0;
-    run_job<Dir>(a, job, &tab, ws, row.data(), 0);
+    job.first_slice = uint32_t(i); job.n_slices = uint32_t(j - i); job.weight = 0; job.reserved = 0;
+    run_job<Dir>(a, job, m, 0);
     i = j;
   }
-  delete ws;
+  delete sh;
   // compact
   std::vector<uint8_t> all;
   for (int k = 0; k < n; k++) {
