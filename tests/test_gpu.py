@@ -125,7 +125,8 @@ def test_empty_and_degenerate_batches(ctx):
     dd = H.coded_descs(descs, res)
     dd[0].in_size = max(1, dd[0].in_size // 3)
     r_d, _ = ctx.decompress(dd, blob)
-    assert r_d[0].status in (_abi.AVR_SLICE_OK, _abi.AVR_SLICE_CORRUPT, _abi.AVR_SLICE_OVERFLOW)
+    # (garbage may also decode to an I_PCM macroblock, which the device reports as UNSUPPORTED)
+    assert r_d[0].status in (_abi.AVR_SLICE_OK, _abi.AVR_SLICE_CORRUPT, _abi.AVR_SLICE_OVERFLOW, _abi.AVR_SLICE_UNSUPPORTED)
     # bad arguments
     bad = _abi.copy_desc(ents[0].desc)
     bad.in_off = len(data)

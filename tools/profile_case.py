@@ -1,0 +1,25 @@
+"""Short profiling case (run under gpurun, plain first, then under ncu): one compress launch and one
+decompress launch of a cfg2-shaped stream (1080p High, I+P, 1 slice/frame), parity-checked by round trip."""
+import os, sys
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
+import avrecode_b200 as A
+import helpers as H
+
+frames = int(sys.argv[1]) if len(sys.argv) > 1 else 30
+data = H.gen_stream(width=1920, height=1088, frames=frames, high=True, kbps=30000, fps=60, intra_period=30, seed=2)
+descs = H.batch_descs(A.index_h264(data), False)
+with A.Context() as ctx:
+    ctx.stage(descs, data)
+    ctx.launch(0); ctx.sync()
+    ms_c = ctx.last_kernel_ms()
+    res, blob = ctx.collect()
+    dd = H.coded_descs(descs, res)
+    ctx.stage(dd, blob)
+    ctx.launch(1); ctx.sync()
+    ms_d = ctx.last_kernel_ms()
+    r_d, b_d = ctx.collect()
+    assert H.roundtrip_ok(descs, r_d, b_d, data)
+    pay = sum(d.payload_size for d in descs); coded = sum(r.out_size for r in res); bins = sum(r.n_bins for r in res)
+    print("slices %d payload %d coded %d bins %d max_slice_bins %d compress %.2f ms decompress %.2f ms" %
+          (len(descs), pay, coded, bins, max(r.n_bins for r in res), ms_c, ms_d))
