@@ -46,6 +46,7 @@ struct BlockShared {
   RingShared ring;
   alignas(16) uint8_t window[WIN_BYTES];
   U2 cstate[N_CTX_PAD];     // CABAC context states {state, rangeTabLPS row}
+  WalkShared walk;          // left macroblock + per-macroblock scratch of the walker
   uint32_t job;             // job handed out by the atomic counter
   uint32_t final_status;    // status of the slice just finished (coder writes, everyone reads)
   uint32_t pad_[2];
@@ -63,7 +64,8 @@ struct JobMem {             // where this block keeps its state
   BlockShared* sh;
   MbCtx* row;               // [max_mbw], shared memory
   uint16_t* cnt;            // MODEL_COUNTERS estimators: shared memory (resident) or global workspace
-  uint8_t* nnz[2];          // two FrameBuffer nnz planes, global workspace
+  uint8_t* nnz0;            // two FrameBuffer nnz planes, global workspace (scalars: the struct must stay in registers)
+  uint8_t* nnz1;
   uint32_t nnz_frame_bytes; // capacity of one plane
 };
 
@@ -106,9 +108,16 @@ AVR_DEV void window_load_half(const ByteWindow& w, uint32_t from, int lane) {
   }
 }
 
-// Frame-buffer bookkeeping of h264_model::update_frame_spec (recode.cpp:824-843).
+// Frame-buffer bookkeeping of h264_model::update_frame_spec (recode.cpp:824-843).  Scalars only (no
+// run-time indexed arrays) so that it lives in registers.
 struct FrameTags {
-  int w[2], h[2], num[2], cur;
+  int w0, w1, h0, h1, num0, num1, cur;
+  AVR_DEV int w(int i) const { return i ? w1 : w0; }
+  AVR_DEV int h(int i) const { return i ? h1 : h0; }
+  AVR_DEV int num(int i) const { return i ? num1 : num0; }
+  AVR_DEV void set_size(int i, int ww, int hh) { if (i) { w1 = ww; h1 = hh; } else { w0 = ww; h0 = hh; } }
+  AVR_DEV void set_num(int i, int n) { if (i) num1 = n; else num0 = n; }
+  AVR_DEV void clear() { w0 = w1 = h0 = h1 = 0; cur = 0; }
 };
 
 // ---- parser warp: lane 0 walks the slice, all 32 lanes keep its input window filled ---------------
@@ -117,14 +126,14 @@ AVR_DEV void parser_role(const JobArgs& a, const JobMem& m, const avr_slice_desc
   Walker<Dir> wk;
   wk.tab = &m.sh->tab;
   wk.row = m.row;
-  wk.mm.nnz[0] = m.nnz[0]; wk.mm.nnz[1] = m.nnz[1]; wk.mm.cur = cur_frame;
-  wk.d = d;
+  wk.ws = &m.sh->walk;
+  wk.nnz_cur = cur_frame ? m.nnz1 : m.nnz0; wk.nnz_prev = cur_frame ? m.nnz0 : m.nnz1;
   wk.dir.begin(a.in_arena + io.in_off, io.in_size, m.sh->window, (d.flags & AVR_SLICE_STOP_BYTE) ? 0x80u : 0u, &m.sh->ring,
                m.cnt, m.sh->cstate);
   window_load_half(wk.dir.in, 0, lane);
   window_load_half(wk.dir.in, WIN_HALF, lane);
   AVR_SYNCWARP();
-  if (lane == 0) wk.start();
+  if (lane == 0) wk.start(d);
   for (;;) {
     int done = 1;
     uint32_t in_pos = 0;
@@ -149,8 +158,8 @@ AVR_DEV void parser_role(const JobArgs& a, const JobMem& m, const avr_slice_desc
     RingShared* r = &m.sh->ring;
     r->end_status = uint32_t(wk.status);
     r->end_mbs = wk.n_mbs;
-    r->end_bins_lo = uint32_t(wk.n_bins);
-    r->end_bins_hi = uint32_t(wk.n_bins >> 32);
+    r->end_bins_lo = wk.n_bins_lo;
+    r->end_bins_hi = wk.n_bins_hi;
     wk.dir.q.push(SYM_END);
     wk.dir.q.publish();
   }
@@ -183,11 +192,11 @@ AVR_DEV void coder_role(const JobArgs& a, const JobMem& m, const SliceIO& io, ui
 
 // Runs one job on the calling block.
 template <class Dir>
-AVR_DEV_NOINLINE void run_job(const JobArgs& a, const JobDesc& job, const JobMem& m, int tid) {
+AVR_DEV void run_job(const JobArgs& a, const JobDesc& job, const JobMem& m, int tid) {
   const int nthreads = AVR_THREADS;
   const int lane = tid & (AVR_LANES - 1);
   FrameTags ft;
-  ft.w[0] = ft.w[1] = ft.h[0] = ft.h[1] = 0; ft.num[0] = ft.num[1] = 0; ft.cur = 0;
+  ft.clear(); ft.num0 = ft.num1 = 0;
   bool poisoned = false;   // a failed slice leaves the shared model undefined: fail the rest of the job
 
   for (uint32_t s = job.first_slice; s < job.first_slice + job.n_slices; s++) {
@@ -201,23 +210,24 @@ AVR_DEV_NOINLINE void run_job(const JobArgs& a, const JobDesc& job, const JobMem
       if (fresh) {
         // a brand-new h264_model: every estimator {1,1} (recode.cpp:1057), no frame buffers yet
         fill_u32(reinterpret_cast<uint32_t*>(m.cnt), MODEL_COUNTERS / 2, 0x01010101u, tid, nthreads);
-        ft.w[0] = ft.w[1] = ft.h[0] = ft.h[1] = 0; ft.cur = 0;
+        ft.clear();
       }
-      if ((d.flags & AVR_SLICE_NEW_PICTURE) || fresh || ft.w[ft.cur] != d.mb_width || ft.h[ft.cur] != d.mb_height) {
+      const int mw = d.mb_width, mh = d.mb_height;
+      if ((d.flags & AVR_SLICE_NEW_PICTURE) || fresh || ft.w(ft.cur) != mw || ft.h(ft.cur) != mh) {
         // update_frame_spec (recode.cpp:824-843): flip + clear unless same frame_num and size
-        const bool same = ft.num[ft.cur] == d.frame_num && ft.w[ft.cur] != 0 && ft.h[ft.cur] != 0;
-        if (ft.w[ft.cur] != d.mb_width || ft.h[ft.cur] != d.mb_height || !same) {
+        const bool same = ft.num(ft.cur) == d.frame_num && ft.w(ft.cur) != 0 && ft.h(ft.cur) != 0;
+        if (ft.w(ft.cur) != mw || ft.h(ft.cur) != mh || !same) {
           ft.cur ^= 1;
           const int c = ft.cur;
-          fill_u32(reinterpret_cast<uint32_t*>(m.nnz[c]), frame_bytes / 4, 0, tid, nthreads);
-          if (ft.w[c] != d.mb_width || ft.h[c] != d.mb_height) {
-            ft.w[c] = d.mb_width; ft.h[c] = d.mb_height;
-            if (ft.w[c ^ 1] != d.mb_width || ft.h[c ^ 1] != d.mb_height) {
-              ft.w[c ^ 1] = d.mb_width; ft.h[c ^ 1] = d.mb_height;
-              fill_u32(reinterpret_cast<uint32_t*>(m.nnz[c ^ 1]), frame_bytes / 4, 0, tid, nthreads);
+          fill_u32(reinterpret_cast<uint32_t*>(c ? m.nnz1 : m.nnz0), frame_bytes / 4, 0, tid, nthreads);
+          if (ft.w(c) != mw || ft.h(c) != mh) {
+            ft.set_size(c, mw, mh);
+            if (ft.w(c ^ 1) != mw || ft.h(c ^ 1) != mh) {
+              ft.set_size(c ^ 1, mw, mh);
+              fill_u32(reinterpret_cast<uint32_t*>(c ? m.nnz0 : m.nnz1), frame_bytes / 4, 0, tid, nthreads);
             }
           }
-          ft.num[c] = d.frame_num;
+          ft.set_num(c, d.frame_num);
         }
       }
     }

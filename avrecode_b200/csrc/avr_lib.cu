@@ -47,8 +47,8 @@ __global__ void __launch_bounds__(AVR_THREADS, RESIDENT ? 2 : 8) avr_job_kernel(
   const size_t rb = (size_t(k.max_mbw) * sizeof(MbCtx) + 15) / 16 * 16;
   if (RESIDENT) m.cnt = reinterpret_cast<uint16_t*>(smem + sizeof(BlockShared) + rb);
   else { m.cnt = reinterpret_cast<uint16_t*>(slot); slot += (size_t(MODEL_COUNTERS) * 2 + 255) / 256 * 256; }
-  m.nnz[0] = slot;
-  m.nnz[1] = slot + k.nnz_frame_bytes;
+  m.nnz0 = slot;
+  m.nnz1 = slot + k.nnz_frame_bytes;
   m.nnz_frame_bytes = k.nnz_frame_bytes;
   const int tid = threadIdx.x;
   fill_shared_tables(&m.sh->tab, tid, AVR_THREADS);

@@ -37,7 +37,7 @@ static int run(const avr_slice_desc* descs, int n, const uint8_t* in, uint64_t i
   JobArgs a{descs, ios.data(), in, arena.data(), res};
   JobMem m;
   m.sh = sh; m.row = row.data(); m.cnt = counters.data();
-  m.nnz[0] = planes.data(); m.nnz[1] = planes.data() + max_frame; m.nnz_frame_bytes = max_frame;
+  m.nnz0 = planes.data(); m.nnz1 = planes.data() + max_frame; m.nnz_frame_bytes = max_frame;
   int i = 0;
   while (i < n) {
     int j = i + 1;
