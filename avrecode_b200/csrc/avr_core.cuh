@@ -99,10 +99,10 @@ AVR_DEV uint32_t sig_slab(int cat, uint32_t key_nnz) {   // index of [observed =
 // Small read-only tables in shared memory (per thread block).
 // ------------------------------------------------------------------------------------------------
 struct U2 { uint32_t x, y; };
+struct alignas(16) DivMagic { uint64_t magic; uint32_t shift, pad; };   // one 16-byte load per division
 struct SharedTables {
-  uint64_t magic[100];     // ceil(2^(63+l) / d), l = ceil(log2 d): exact floor(n/d) for n <= 2^63 by one high multiply
+  DivMagic div[100];       // magic = ceil(2^(63+l) / d), l = ceil(log2 d), shift = l - 1: exact floor(n/d) for n <= 2^63
   U2 trans[256];           // [state * 2 + lps] -> {next state, the four rangeTabLPS bytes of the next state}
-  uint8_t mshift[104];     // l - 1
   uint8_t sig8[64];        // significant_coeff_flag ctxIdxInc, 8x8 frame blocks
   uint8_t last8[64];
 };
@@ -123,7 +123,8 @@ AVR_DEV int clz32(uint32_t x) {
 }
 
 // exact floor(n / d) for 2 <= d < 100, n <= 2^63 (Granlund-Montgomery round-up reciprocal)
-AVR_DEV uint64_t div_small(const SharedTables& t, uint64_t n, uint32_t d) { return mulhi64(n, t.magic[d]) >> t.mshift[d]; }
+AVR_DEV uint64_t div_magic(uint64_t n, const DivMagic& m) { return mulhi64(n, m.magic) >> m.shift; }
+AVR_DEV uint64_t div_small(const SharedTables& t, uint64_t n, uint32_t d) { return div_magic(n, t.div[d]); }
 
 AVR_DEV uint32_t rlps4_of(uint32_t p) {
   return uint32_t(avr_range_lps[p * 4]) | uint32_t(avr_range_lps[p * 4 + 1]) << 8 | uint32_t(avr_range_lps[p * 4 + 2]) << 16 |
@@ -139,8 +140,9 @@ AVR_DEV void fill_shared_tables(SharedTables* t, int tid, int nthreads) {
       const uint64_t num = r << l;
       m = (q << l) + num / uint64_t(d) + (num % uint64_t(d) ? 1 : 0);
     }
-    t->magic[d] = m;
-    t->mshift[d] = uint8_t(l > 0 ? l - 1 : 0);
+    t->div[d].magic = m;
+    t->div[d].shift = uint32_t(l > 0 ? l - 1 : 0);
+    t->div[d].pad = 0;
   }
   for (int i = tid; i < 256; i += nthreads) {
     const uint32_t s = uint32_t(i) >> 1, p = s >> 1, mps = s & 1;
@@ -281,8 +283,8 @@ struct RangeEnc {
     range <<= 8;
     sink.push(digit, carry);
   }
-  AVR_DEV void put(const SharedTables& t, int bit, uint32_t pos, uint32_t neg) {
-    const uint64_t r1 = div_small(t, range, pos + neg) * pos;
+  AVR_DEV void put(const DivMagic& mg, int bit, uint32_t pos) {   // mg = t.div[pos + neg]
+    const uint64_t r1 = div_magic(range, mg) * pos;
     const uint64_t r0 = range - r1;
     if (bit) { low += r0; range = r1; } else range = r0;
     if (range < AVR_MIN_RANGE) { do shift_byte(); while (range < AVR_NORM_RANGE); }
@@ -391,12 +393,14 @@ AVR_DEV void est_update(uint32_t& pos, uint32_t& neg, int bit, uint32_t limit) {
 // publishes its head every RING_PUBLISH entries.
 // ------------------------------------------------------------------------------------------------
 enum : uint32_t {
-  RING_ENTRIES = 1024, RING_PUBLISH = 64,
+  RING_ENTRIES = 1024, RING_PUBLISH = 64, RING_BATCH = 128,
   SYM_BIT_SHIFT = 16, SYM_KIND_SHIFT = 20, SYM_DECISION = 0u << 20, SYM_BYPASS = 1u << 20, SYM_TERMINATE = 2u << 20,
   SYM_END = 1u << 31,
 };
 
 #if defined(__CUDACC__) && !defined(AVR_HOST_EMULATION)
+// release/acquire at block scope is all the ring needs (entries before the published index)
+AVR_DEV void ring_fence() { asm volatile("fence.acq_rel.cta;" ::: "memory"); }
 struct RingShared {
   uint32_t e[RING_ENTRIES];
   uint32_t tail_pub, head_pub;
@@ -409,7 +413,7 @@ struct Producer {
   uint32_t tail, limit, pub, head_seen;
   AVR_DEV void init(RingShared* ring) { r = ring; tail = pub = head_seen = 0; limit = RING_PUBLISH; }
   AVR_DEV void publish() {
-    __threadfence_block();
+    ring_fence();
     *reinterpret_cast<volatile uint32_t*>(&r->tail_pub) = tail;
     pub = tail;
   }
@@ -428,13 +432,25 @@ struct Consumer {
   RingShared* r;
   uint32_t head, tail_seen;
   AVR_DEV void init(RingShared* ring) { r = ring; head = tail_seen = 0; }
+  // batch interface: wait for published entries, read them in place, release them in one go
+  AVR_DEV uint32_t wait_avail() {
+    while (head == tail_seen) tail_seen = *reinterpret_cast<volatile uint32_t*>(&r->tail_pub);
+    const uint32_t n = tail_seen - head;
+    return n < RING_BATCH ? n : uint32_t(RING_BATCH);   // bounded, so the producer gets its slots back early
+  }
+  AVR_DEV uint32_t peek(uint32_t k) const { return r->e[(head + k) & (RING_ENTRIES - 1)]; }
+  AVR_DEV void release(uint32_t n) {
+    head += n;
+    ring_fence();
+    *reinterpret_cast<volatile uint32_t*>(&r->head_pub) = head;
+  }
   AVR_DEV uint32_t pop() {
     if (head == tail_seen) {
       do tail_seen = *reinterpret_cast<volatile uint32_t*>(&r->tail_pub); while (head == tail_seen);
     }
     const uint32_t e = reinterpret_cast<volatile uint32_t*>(r->e)[head & (RING_ENTRIES - 1)];
     if ((++head & (RING_PUBLISH - 1)) == 0) {
-      __threadfence_block();
+      ring_fence();
       *reinterpret_cast<volatile uint32_t*>(&r->head_pub) = head;
     }
     return e;
@@ -460,6 +476,9 @@ struct Consumer {
   RingShared* r;
   size_t head;
   void init(RingShared* ring) { r = ring; head = 0; }
+  uint32_t wait_avail() { return head < r->e.size() ? uint32_t(r->e.size() - head > 64 ? 64 : r->e.size() - head) : 1u; }
+  uint32_t peek(uint32_t k) const { return head + k < r->e.size() ? r->e[head + k] : uint32_t(SYM_END); }
+  void release(uint32_t n) { head += n; }
   uint32_t pop() { return head < r->e.size() ? r->e[head++] : uint32_t(SYM_END); }
 };
 #endif
@@ -470,18 +489,39 @@ struct Consumer {
 struct CoderCompress {     // estimators + range encoder (recode.cpp:1068-1096 h264_symbol::execute)
   RangeEnc rc;
   AVR_DEV void begin(uint8_t* dst, uint32_t cap) { rc.init(dst, cap); }
+  // Software-pipelined: entry k+1, its estimator and its reciprocal are loaded while entry k goes
+  // through the coder, so the loop-carried chain is the range recurrence alone (one 64x64 high
+  // multiply, a shift, a multiply, a subtract, a select).  The estimator of entry k+1 is read BEFORE
+  // entry k's update is stored; when both use the same estimator the updated value is forwarded.
   AVR_DEV void run(Consumer& q, const SharedTables& t, uint16_t* cnt, U2*) {
     for (;;) {
-      const uint32_t e = q.pop();
-      if (e & SYM_END) break;
-      const uint32_t idx = e & 0xFFFF;
-      const int bit = int((e >> SYM_BIT_SHIFT) & 1);
-      const uint32_t c = cnt[idx];
-      uint32_t pos = c & 0xFF, neg = c >> 8;
-      rc.put(t, bit, pos, neg);
-      est_update(pos, neg, bit, idx >= CNT_SIG ? 0x50u : 0x60u);   // recode.cpp:1041-1042
-      cnt[idx] = uint16_t(pos | (neg << 8));
-      if (idx == CNT_TERM && bit) rc.finish();                      // recode.cpp:1092-1095
+      const uint32_t n = q.wait_avail();
+      uint32_t e = q.peek(0);
+      uint32_t c = cnt[e & 0xFFFF];
+      DivMagic mg = t.div[(c & 0xFF) + (c >> 8)];
+      bool end = false;
+      uint32_t k = 0;
+#pragma unroll 1
+      for (; k < n; k++) {
+        if (e & SYM_END) { end = true; break; }
+        const uint32_t idx = e & 0xFFFF;
+        const int bit = int((e >> SYM_BIT_SHIFT) & 1);
+        const uint32_t e_n = q.peek(k + 1 < n ? k + 1 : k);
+        const uint32_t idx_n = e_n & 0xFFFF;
+        uint32_t c_n = cnt[idx_n];
+        uint32_t pos = c & 0xFF, neg = c >> 8;
+        const uint32_t pos0 = pos;
+        est_update(pos, neg, bit, idx >= CNT_SIG ? 0x50u : 0x60u);   // recode.cpp:1041-1042
+        const uint32_t c2 = pos | (neg << 8);
+        cnt[idx] = uint16_t(c2);
+        if (idx_n == idx) c_n = c2;
+        const DivMagic mg_n = t.div[(c_n & 0xFF) + (c_n >> 8)];
+        rc.put(mg, bit, pos0);
+        if (idx == CNT_TERM && bit) rc.finish();                      // recode.cpp:1092-1095
+        e = e_n; c = c_n; mg = mg_n;
+      }
+      q.release(k);
+      if (end) break;
     }
   }
   AVR_DEV uint32_t out_bytes() const { return rc.sink.n; }
