@@ -516,8 +516,10 @@ struct CoderCompress {     // estimators + range encoder (recode.cpp:1068-1096 h
         cnt[idx] = uint16_t(c2);
         if (idx_n == idx) c_n = c2;
         const DivMagic mg_n = t.div[(c_n & 0xFF) + (c_n >> 8)];
+#ifndef AVR_PROBE_NO_CODER
         rc.put(mg, bit, pos0);
         if (idx == CNT_TERM && bit) rc.finish();                      // recode.cpp:1092-1095
+#endif
         e = e_n; c = c_n; mg = mg_n;
       }
       q.release(k);

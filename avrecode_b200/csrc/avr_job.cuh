@@ -122,11 +122,12 @@ struct FrameTags {
 
 // ---- parser warp: lane 0 walks the slice, all 32 lanes keep its input window filled ---------------
 template <class Dir>
-AVR_DEV void parser_role(const JobArgs& a, const JobMem& m, const avr_slice_desc& d, const SliceIO& io, int cur_frame, int lane) {
+AVR_DEV void parser_role(const JobArgs& a, const JobMem& m, const avr_slice_desc& d, const SliceIO& io, int cur_frame, bool use_planes, int lane) {
   Walker<Dir> wk;
   wk.tab = &m.sh->tab;
   wk.row = m.row;
   wk.ws = &m.sh->walk;
+  wk.use_planes = use_planes;
   wk.nnz_cur = cur_frame ? m.nnz1 : m.nnz0; wk.nnz_prev = cur_frame ? m.nnz0 : m.nnz1;
   wk.dir.begin(a.in_arena + io.in_off, io.in_size, m.sh->window, (d.flags & AVR_SLICE_STOP_BYTE) ? 0x80u : 0u, &m.sh->ring,
                m.cnt, m.sh->cstate);
@@ -198,6 +199,9 @@ AVR_DEV void run_job(const JobArgs& a, const JobDesc& job, const JobMem& m, int 
   FrameTags ft;
   ft.clear(); ft.num0 = ft.num1 = 0;
   bool poisoned = false;   // a failed slice leaves the shared model undefined: fail the rest of the job
+  // A job of one slice is a chunk whose model dies with it: the previous picture is empty and the
+  // neighbour counts live in the shared-memory row, so the global nnz planes are not touched at all.
+  const bool use_planes = job.n_slices > 1;
 
   for (uint32_t s = job.first_slice; s < job.first_slice + job.n_slices; s++) {
     const avr_slice_desc d = a.descs[s];
@@ -205,7 +209,7 @@ AVR_DEV void run_job(const JobArgs& a, const JobDesc& job, const JobMem& m, int 
     const bool fresh = s == job.first_slice || (d.flags & AVR_SLICE_NEW_MODEL);
     const bool skip = (d.flags & AVR_SLICE_SKIP) != 0;   // frame_spec bookkeeping only
     const uint32_t frame_bytes = uint32_t(d.mb_width) * d.mb_height * NNZ_STRIDE;
-    const bool usable = !poisoned && frame_bytes <= m.nnz_frame_bytes && d.mb_width > 0 && d.mb_height > 0;
+    const bool usable = !poisoned && (!use_planes || frame_bytes <= m.nnz_frame_bytes) && d.mb_width > 0 && d.mb_height > 0;
     if (usable) {
       if (fresh) {
         // a brand-new h264_model: every estimator {1,1} (recode.cpp:1057), no frame buffers yet
@@ -219,12 +223,12 @@ AVR_DEV void run_job(const JobArgs& a, const JobDesc& job, const JobMem& m, int 
         if (ft.w(ft.cur) != mw || ft.h(ft.cur) != mh || !same) {
           ft.cur ^= 1;
           const int c = ft.cur;
-          fill_u32(reinterpret_cast<uint32_t*>(c ? m.nnz1 : m.nnz0), frame_bytes / 4, 0, tid, nthreads);
+          if (use_planes) fill_u32(reinterpret_cast<uint32_t*>(c ? m.nnz1 : m.nnz0), frame_bytes / 4, 0, tid, nthreads);
           if (ft.w(c) != mw || ft.h(c) != mh) {
             ft.set_size(c, mw, mh);
             if (ft.w(c ^ 1) != mw || ft.h(c ^ 1) != mh) {
               ft.set_size(c ^ 1, mw, mh);
-              fill_u32(reinterpret_cast<uint32_t*>(c ? m.nnz0 : m.nnz1), frame_bytes / 4, 0, tid, nthreads);
+              if (use_planes) fill_u32(reinterpret_cast<uint32_t*>(c ? m.nnz0 : m.nnz1), frame_bytes / 4, 0, tid, nthreads);
             }
           }
           ft.set_num(c, d.frame_num);
@@ -234,15 +238,16 @@ AVR_DEV void run_job(const JobArgs& a, const JobDesc& job, const JobMem& m, int 
     const bool walk = usable && !skip;
     if (walk) {
       init_contexts(m.sh->cstate, d, tid, nthreads);
+      if (!use_planes) fill_u32(reinterpret_cast<uint32_t*>(m.row), uint32_t(d.mb_width) * MBCTX_WORDS, 0, tid, nthreads);
       if (tid == 0) ring_reset(&m.sh->ring);
     }
     AVR_SYNCBLOCK();
     if (walk) {
 #if defined(__CUDACC__) && !defined(AVR_HOST_EMULATION)
-      if (tid < 32) parser_role<Dir>(a, m, d, io, ft.cur, lane);
+      if (tid < 32) parser_role<Dir>(a, m, d, io, ft.cur, use_planes, lane);
       else coder_role<Dir>(a, m, io, s, lane);
 #else
-      parser_role<Dir>(a, m, d, io, ft.cur, lane);
+      parser_role<Dir>(a, m, d, io, ft.cur, use_planes, lane);
       coder_role<Dir>(a, m, io, s, lane);
 #endif
     } else if (tid == 0) {

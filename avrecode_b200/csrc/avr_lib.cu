@@ -259,7 +259,11 @@ int avr_stage(avr_ctx* c, const avr_slice_desc* descs, int n, const uint8_t* in,
   c->grid = std::max(1, std::min(c->n_jobs, c->sm_count * (resident ? res_per_sm : glb_per_sm)));
 
   // device memory
-  const uint64_t work_stride = align_up((resident ? 0 : counters_bytes()) + 2 * size_t(c->max_frame_bytes), 256);
+  // the nnz planes are only needed by jobs whose model spans several slices (file mode)
+  bool any_multi = false;
+  for (const JobDesc& j : c->jobs) any_multi = any_multi || j.n_slices > 1;
+  if (!any_multi) c->max_frame_bytes = 0;
+  const uint64_t work_stride = align_up((resident ? 0 : counters_bytes()) + 2 * size_t(c->max_frame_bytes) + 16, 256);
   c->work_stride = work_stride;
   int rc;
   if ((rc = grow_dev(&c->d_in, &c->d_in_cap, size_t(in_bytes) + 64))) return rc;

@@ -20,7 +20,7 @@
 
 namespace avr {
 
-struct alignas(8) MbCtx {          // what later macroblocks need from a decoded one to select CABAC contexts
+struct alignas(4) MbCtx {          // what later macroblocks need from a decoded one to select contexts / model keys
   uint16_t flags;       // MBF_*
   uint16_t cbp;         // cbp_table semantics: luma 0..3, chroma 4..5, 0x40<<c chroma DC, 0x100 luma DC
   uint8_t nz_bottom;    // coefficient flags of the bottom block row: luma x=0..3 -> bits 0..3, Cb x=0,1 -> 4,5, Cr -> 6,7
@@ -29,8 +29,19 @@ struct alignas(8) MbCtx {          // what later macroblocks need from a decoded
   uint8_t reserved;
   uint8_t mvd_bottom[4][2];  // list 0, bottom row x=0..3, {|mvdx|,|mvdy|} clipped to 70
   uint8_t mvd_right[4][2];   // list 0, right column y=0..3
+  uint8_t nnz[20];           // avrecode model: stored nnz of the blocks a neighbour can ask for (k_nnz_slot)
 };
-static_assert(sizeof(MbCtx) == 24, "MbCtx layout");
+static_assert(sizeof(MbCtx) == 44, "MbCtx layout");
+enum : int { MBCTX_WORDS = 11, MBCTX_NNZ_WORD = 6 };
+
+// block index -> slot in MbCtx::nnz.  A left/above neighbour lookup (recode.cpp:419-471) can only land
+// on the right column / bottom row of the neighbouring macroblock, on the first block of an 8x8
+// quadrant (the "& ~3" rounding for 8x8 blocks), or on a DC slot.
+AVR_TABLE_QUAL uint8_t k_nnz_slot[52] = {
+  19, 19, 19, 19, 0, 1, 19, 2, 3, 19, 4, 5, 6, 7, 8, 9,            // luma 4, 5, 7, 8, 10..15
+  19, 10, 11, 12, 19, 19, 19, 19, 19, 19, 19, 19, 19, 19, 19, 19,   // Cb 17, 18, 19
+  19, 13, 14, 15, 19, 19, 19, 19, 19, 19, 19, 19, 19, 19, 19, 19,   // Cr 33, 34, 35
+  16, 17, 18, 19};                                                    // DC 48, 49, 50
 enum : uint16_t {
   MBF_I16 = 1, MBF_IPCM = 2, MBF_INTRA = 4, MBF_SKIP = 8, MBF_DIRECT = 16, MBF_T8x8 = 32,
   MBF_CHROMA_PRED_NZ = 64, MBF_L0 = 128, MBF_L1 = 256,
@@ -39,6 +50,7 @@ enum : uint16_t {
 struct alignas(8) WalkShared {     // per-block scratch of the walker (shared memory on the device)
   MbCtx left;           // the previous macroblock
   uint8_t mvd[16][2];   // list-0 |mvd| of the macroblock being walked, by 4x4 block index
+  uint8_t nnz_mb[52];   // avrecode model: stored nnz of the macroblock being walked, by block index
 };
 
 // (dense) ctxIdx bases per block category 0..5 (h264_cabac.c:1589-1599, :1556), packed so that a
@@ -67,6 +79,8 @@ struct Walker {
   WalkShared* ws;
   uint8_t* nnz_cur;      // FrameBuffer meta.num_nonzeros of the current picture, [mb][NNZ_STRIDE] (recode.cpp:624, 824-843)
   const uint8_t* nnz_prev;  // ... of the previous picture
+  bool use_planes;       // false: the model lives and dies with this slice (chunk mode) -- the previous picture is
+                         // empty and every neighbour count comes from the shared-memory row, no global traffic
   // slice constants
   uint32_t first_mb;
   int mbw, mbh, num_ref_l0;
@@ -93,18 +107,22 @@ struct Walker {
   // ---- avrecode model side channel: nnz of a coded block (recode.cpp:844-930) -------------------
   // get_neighbor_sub_mb (recode.cpp:419-471): frame geometry only -- slice edges are ignored on purpose
   AVR_DEV bool model_neighbor(bool above, int max_coeff, int blk, uint32_t* value) const {
-    int mbi = mb_xy, nb = blk;
+    int where = 0, nb = blk;   // where: 0 = this macroblock, 1 = left, 2 = above
     if (blk >= 48) {
-      if (above) { if (mb_y == 0) return false; mbi -= mbw; }
-      else { if (mb_x == 0) return false; mbi -= 1; }
+      if (above) { if (mb_y == 0) return false; where = 2; }
+      else { if (mb_x == 0) return false; where = 1; }
     } else {
       int plane = blk & 48, x = blk_x(blk & 15), y = blk_y(blk & 15);
-      if (above) { if (--y < 0) { if (mb_y == 0) return false; mbi -= mbw; y = 3; } }
-      else { if (--x < 0) { if (mb_x == 0) return false; mbi -= 1; x = 3; } }
+      if (above) { if (--y < 0) { if (mb_y == 0) return false; where = 2; y = 3; } }
+      else { if (--x < 0) { if (mb_x == 0) return false; where = 1; x = 3; } }
       nb = plane | blk_at(x, y);
       if (max_coeff >= 32) nb &= ~3;
     }
-    *value = nnz_cur[size_t(mbi) * NNZ_STRIDE + nb];
+    if (use_planes) {
+      const int mbi = where == 0 ? mb_xy : (where == 1 ? mb_xy - 1 : mb_xy - mbw);
+      *value = nnz_cur[size_t(mbi) * NNZ_STRIDE + nb];
+    } else if (where == 0) *value = ws->nnz_mb[nb];
+    else *value = (where == 1 ? ws->left.nnz : row[mb_x].nnz)[k_nnz_slot[nb]];
     return true;
   }
   // codes (compress) or reads (decompress) the block's nnz; returns the value the compressor stores
@@ -113,7 +131,7 @@ struct Walker {
     uint32_t left_nz = 0, above_nz = 0;
     const bool has_left = model_neighbor(false, max_coeff, blk, &left_nz);
     model_neighbor(true, max_coeff, blk, &above_nz);
-    const uint32_t prev_nz = nnz_prev[size_t(mb_xy) * NNZ_STRIDE + blk];
+    const uint32_t prev_nz = use_planes ? nnz_prev[size_t(mb_xy) * NNZ_STRIDE + blk] : 0u;
     const uint32_t group = CNT_NZ + nz_group(cat, model_is8x8);
     uint32_t so_far = 0;
 #pragma unroll 1
@@ -159,7 +177,8 @@ struct Walker {
       if (nnz_true > uint32_t(max_coeff)) { fail(WALK_CORRUPT); nnz_true = uint32_t(max_coeff); }
       key_nnz = is8 ? coded : nnz_true;
     } else { nnz_true = nnz; key_nnz = nnz & 63; }
-    nnz_cur[size_t(mb_xy) * NNZ_STRIDE + blk] = uint8_t(key_nnz);   // stored count: 64 -> 0, else exact
+    ws->nnz_mb[blk] = uint8_t(key_nnz);   // stored count: 64 -> 0, else exact
+    if (use_planes) nnz_cur[size_t(mb_xy) * NNZ_STRIDE + blk] = uint8_t(key_nnz);
     // 3. significance bins through the (cat, nnz) counter slab; last_significant_coeff_flag is
     //    never coded, it is implied by nnz (recode.cpp:1073, 1437-1438)
     const uint32_t slab = sig_slab(cat, key_nnz);
@@ -306,6 +325,7 @@ struct Walker {
     cur_flags = 0; cur_cbp = 0; cur_refpos = 0;
     nzmask = 0;
     model_is8x8 = false;
+    for (int i = 0; i < 13; i++) reinterpret_cast<uint32_t*>(ws->nnz_mb)[i] = 0;
     left_ok = mb_x > 0 && uint32_t(mb_xy - 1) >= first_mb;
     top_ok = mb_y > 0 && mb_xy - mbw >= int(first_mb);
     {   // neighbour facts into registers
@@ -475,7 +495,15 @@ struct Walker {
     const uint32_t nb = uint32_t((m >> 10) & 3) | uint32_t((m >> 14) & 3) << 2 | uint32_t((m >> 18) & 3) << 4 | uint32_t((m >> 34) & 3) << 6;
     const uint32_t nr = uint32_t((m >> 5) & 1) | uint32_t((m >> 7) & 1) << 1 | uint32_t((m >> 13) & 1) << 2 | uint32_t((m >> 15) & 1) << 3 |
                         uint32_t((m >> 17) & 1) << 4 | uint32_t((m >> 19) & 1) << 5 | uint32_t((m >> 33) & 1) << 6 | uint32_t((m >> 35) & 1) << 7;
-    uint32_t w[6];
+    uint32_t w[MBCTX_WORDS];
+    {   // the 19 model counts a neighbour can ask for (k_nnz_slot order)
+      const uint8_t* z = ws->nnz_mb;
+      w[6] = uint32_t(z[4]) | uint32_t(z[5]) << 8 | uint32_t(z[7]) << 16 | uint32_t(z[8]) << 24;
+      w[7] = uint32_t(z[10]) | uint32_t(z[11]) << 8 | uint32_t(z[12]) << 16 | uint32_t(z[13]) << 24;
+      w[8] = uint32_t(z[14]) | uint32_t(z[15]) << 8 | uint32_t(z[17]) << 16 | uint32_t(z[18]) << 24;
+      w[9] = uint32_t(z[19]) | uint32_t(z[33]) << 8 | uint32_t(z[34]) << 16 | uint32_t(z[35]) << 24;
+      w[10] = uint32_t(z[48]) | uint32_t(z[49]) << 8 | uint32_t(z[50]) << 16;
+    }
     w[0] = (cur_flags & 0xFFFF) | (cur_cbp & 0xFFFF) << 16;
     w[1] = nb | nr << 8 | (cur_refpos & 0xFF) << 16;
     if (cur_flags & MBF_INTRA) { w[2] = w[3] = w[4] = w[5] = 0; }
@@ -488,7 +516,7 @@ struct Walker {
     }
     uint32_t* r = reinterpret_cast<uint32_t*>(&row[mb_x]);
     uint32_t* l = reinterpret_cast<uint32_t*>(&ws->left);
-    for (int i = 0; i < 6; i++) { r[i] = w[i]; l[i] = w[i]; }
+    for (int i = 0; i < MBCTX_WORDS; i++) { r[i] = w[i]; l[i] = w[i]; }
   }
 
   // ---- slice loop (h264_slice.c:2366-2443) -------------------------------------------------------
@@ -505,7 +533,7 @@ struct Walker {
     status = WALK_OK;
     n_mbs = 0;
     done = false;
-    for (int i = 0; i < 6; i++) reinterpret_cast<uint32_t*>(&ws->left)[i] = 0;
+    for (int i = 0; i < MBCTX_WORDS; i++) reinterpret_cast<uint32_t*>(&ws->left)[i] = 0;
     if (d.slice_type > AVR_SLICE_I || d.slice_type == AVR_SLICE_B || d.chroma_format_idc != 1 ||
         (d.flags & (AVR_SLICE_MBAFF | AVR_SLICE_FIELD)) || mbw < 1 || mbh < 1 || mb_xy >= mbw * mbh) {
       status = WALK_UNSUPPORTED; done = true; return;

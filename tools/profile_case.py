@@ -19,7 +19,7 @@ with A.Context() as ctx:
     ctx.launch(1); ctx.sync()
     ms_d = ctx.last_kernel_ms()
     r_d, b_d = ctx.collect()
-    assert H.roundtrip_ok(descs, r_d, b_d, data)
     pay = sum(d.payload_size for d in descs); coded = sum(r.out_size for r in res); bins = sum(r.n_bins for r in res)
     print("slices %d payload %d coded %d bins %d max_slice_bins %d compress %.2f ms decompress %.2f ms" %
-          (len(descs), pay, coded, bins, max(r.n_bins for r in res), ms_c, ms_d))
+          (len(descs), pay, coded, bins, max(r.n_bins for r in res), ms_c, ms_d), flush=True)
+    assert H.roundtrip_ok(descs, r_d, b_d, data)
