@@ -192,6 +192,15 @@ struct ByteWindow {
 // A context is one 8-byte shared-memory entry {state, rangeTabLPS[state][0..3]}: one load gives
 // everything the decision needs; the transition is one more 8-byte table load off the critical path.
 // ------------------------------------------------------------------------------------------------
+// rangeTabLPS[state][(range >> 6) & 3] out of the four bytes packed in a context entry: one byte permute
+AVR_DEV uint32_t rlps_byte(uint32_t four, uint32_t range) {
+#if defined(__CUDA_ARCH__)
+  return __byte_perm(four, 0u, ((range >> 6) & 3u) | 0x4440u);
+#else
+  return (four >> ((range >> 3) & 24)) & 0xFF;
+#endif
+}
+
 struct CabacIn {
   uint32_t val, range, pos;
   int nbits;
@@ -202,9 +211,10 @@ struct CabacIn {
   AVR_DEV void refill(const ByteWindow& w) {
     if (nbits < 8) { val = (val << 16) | w.be16(pos); pos += 2; nbits += 16; }
   }
-  AVR_DEV int decision(const ByteWindow& w, const SharedTables& t, U2* ctx) {
-    const U2 e = *ctx;
-    const uint32_t rlps = (e.y >> ((range >> 3) & 24)) & 0xFF;   // byte (range >> 6) & 3
+  // decides one bin from a context entry `e` that was loaded earlier (the caller may have prefetched
+  // it while the previous bin was being decoded) and writes the successor state to *ctx
+  AVR_DEV int decide(const ByteWindow& w, const SharedTables& t, const U2 e, U2* ctx) {
+    const uint32_t rlps = rlps_byte(e.y, range);
     range -= rlps;
     const uint32_t scaled = range << nbits;
     const uint32_t lps = val >= scaled ? 1u : 0u;
@@ -216,6 +226,7 @@ struct CabacIn {
     refill(w);
     return int((e.x & 1) ^ lps);
   }
+  AVR_DEV int decision(const ByteWindow& w, const SharedTables& t, U2* ctx) { return decide(w, t, *ctx, ctx); }
   AVR_DEV int bypass(const ByteWindow& w) {
     nbits -= 1;
     const uint32_t scaled = range << nbits;
@@ -316,8 +327,8 @@ struct RangeDec {
     range = 128;
     for (int i = 0; i < 7; i++) consume(w);
   }
-  AVR_DEV int get(const ByteWindow& w, const SharedTables& t, uint32_t pos_, uint32_t neg_) {
-    const uint64_t r1 = div_small(t, range, pos_ + neg_) * pos_;
+  AVR_DEV int get(const ByteWindow& w, const DivMagic& mg, uint32_t pos_) {   // mg = t.div[pos + neg]
+    const uint64_t r1 = div_magic(range, mg) * pos_;
     const uint64_t r0 = range - r1;
     const int bit = low >= r0;
     if (bit) { low -= r0; range = r1; } else range = r0;
@@ -346,7 +357,7 @@ struct CabacOut {
   }
   AVR_DEV void decision(const SharedTables& t, int bin, U2* ctx) {
     const U2 e = *ctx;
-    const uint32_t rlps = (e.y >> ((range >> 3) & 24)) & 0xFF;
+    const uint32_t rlps = rlps_byte(e.y, range);
     range -= rlps;
     const uint32_t lps = uint32_t(bin) != (e.x & 1) ? 1u : 0u;
     if (lps) { low += range; range = rlps; }
@@ -561,7 +572,11 @@ struct Compress {
   AVR_DEV void begin(const uint8_t* src, uint32_t n, uint8_t* window, uint32_t tail_byte, RingShared* ring, uint16_t*, U2* states) {
     in.attach(src, n, window, tail_byte); q.init(ring); cstate = states;
   }
-  AVR_DEV void start_bins() { cabac.init(in); }
+  AVR_DEV void start_bins(const SharedTables&) { cabac.init(in); }
+  AVR_DEV void finish_bins() {}
+  struct SigEntry { uint32_t c; };
+  AVR_DEV SigEntry sig_fetch(const SharedTables&, uint32_t) const { return SigEntry(); }
+  AVR_DEV int sig_decode(const SigEntry&, uint32_t) { return 0; }
   AVR_DEV int bin(const SharedTables& t, int ctx) {
     const int b = cabac.decision(in, t, &cstate[ctx]);
     q.push(uint32_t(CNT_CTX + ctx) | uint32_t(b) << SYM_BIT_SHIFT);
@@ -570,6 +585,8 @@ struct Compress {
   AVR_DEV int bypass(const SharedTables&) { const int b = cabac.bypass(in); q.push(CNT_BYPASS | uint32_t(b) << SYM_BIT_SHIFT); return b; }
   AVR_DEV int terminate(const SharedTables&) { const int b = cabac.terminate(in); q.push(CNT_TERM | uint32_t(b) << SYM_BIT_SHIFT); return b; }
   AVR_DEV int sig_get(const SharedTables& t, int ctx) { return cabac.decision(in, t, &cstate[ctx]); }   // CABAC side only
+  AVR_DEV U2 sig_peek(int ctx) const { return cstate[ctx]; }
+  AVR_DEV int sig_get_pre(const SharedTables& t, const U2 e, int ctx) { return cabac.decide(in, t, e, &cstate[ctx]); }
   AVR_DEV void sig_put(int, int) {}
   AVR_DEV int model_bit(const SharedTables&, uint32_t idx, int bit) { q.push(idx | uint32_t(bit) << SYM_BIT_SHIFT); return bit; }
   AVR_DEV uint32_t in_pos() const { return cabac.pos; }
@@ -585,11 +602,20 @@ struct Decompress {
   AVR_DEV void begin(const uint8_t* src, uint32_t n, uint8_t* window, uint32_t, RingShared* ring, uint16_t* counters, U2*) {
     in.attach(src, n, window, 0); q.init(ring); cnt = counters;
   }
-  AVR_DEV void start_bins() { rc.init(in); }
+  // The bypass estimator codes every sign and escape bit: it is kept in registers together with its
+  // reciprocal for the length of a slice (read at start_bins, written back by finish_bins).
+  uint32_t byp_c;
+  DivMagic byp_mg;
+  AVR_DEV void start_bins(const SharedTables& t) {
+    rc.init(in);
+    byp_c = cnt[CNT_BYPASS];
+    byp_mg = t.div[(byp_c & 0xFF) + (byp_c >> 8)];
+  }
+  AVR_DEV void finish_bins() { cnt[CNT_BYPASS] = uint16_t(byp_c); }
   AVR_DEV int coded(const SharedTables& t, uint32_t idx, uint32_t limit) {
     const uint32_t c = cnt[idx];
     uint32_t pos = c & 0xFF, neg = c >> 8;
-    const int b = rc.get(in, t, pos, neg);
+    const int b = rc.get(in, t.div[pos + neg], pos);
     est_update(pos, neg, b, limit);
     cnt[idx] = uint16_t(pos | (neg << 8));
     return b;
@@ -599,9 +625,31 @@ struct Decompress {
     q.push(uint32_t(ctx) | uint32_t(b) << SYM_BIT_SHIFT | SYM_DECISION);
     return b;
   }
-  AVR_DEV int bypass(const SharedTables& t) { const int b = coded(t, CNT_BYPASS, 0x60); q.push(uint32_t(b) << SYM_BIT_SHIFT | SYM_BYPASS); return b; }
+  AVR_DEV int bypass(const SharedTables& t) {
+    uint32_t pos = byp_c & 0xFF, neg = byp_c >> 8;
+    const int b = rc.get(in, byp_mg, pos);
+    est_update(pos, neg, b, 0x60);
+    byp_c = pos | (neg << 8);
+    byp_mg = t.div[pos + neg];
+    q.push(uint32_t(b) << SYM_BIT_SHIFT | SYM_BYPASS);
+    return b;
+  }
   AVR_DEV int terminate(const SharedTables& t) { const int b = coded(t, CNT_TERM, 0x60); q.push(uint32_t(b) << SYM_BIT_SHIFT | SYM_TERMINATE); return b; }
+  // significance-map bins with both possible successors prefetched (see Walker::residual)
+  struct SigEntry { uint32_t c; DivMagic mg; };
+  AVR_DEV SigEntry sig_fetch(const SharedTables& t, uint32_t idx) const {
+    SigEntry e; e.c = cnt[idx]; e.mg = t.div[(e.c & 0xFF) + (e.c >> 8)]; return e;
+  }
+  AVR_DEV int sig_decode(const SigEntry& e, uint32_t idx) {
+    uint32_t pos = e.c & 0xFF, neg = e.c >> 8;
+    const int b = rc.get(in, e.mg, pos);
+    est_update(pos, neg, b, 0x50);
+    cnt[idx] = uint16_t(pos | (neg << 8));
+    return b;
+  }
   AVR_DEV int sig_get(const SharedTables&, int) { return 0; }
+  AVR_DEV U2 sig_peek(int) const { return U2(); }
+  AVR_DEV int sig_get_pre(const SharedTables&, const U2, int) { return 0; }
   AVR_DEV void sig_put(int ctx, int bit) { q.push(uint32_t(ctx) | uint32_t(bit) << SYM_BIT_SHIFT | SYM_DECISION); }   // CABAC side only
   AVR_DEV int model_bit(const SharedTables& t, uint32_t idx, int) { return coded(t, idx, idx >= CNT_SIG ? 0x50u : 0x60u); }
   AVR_DEV uint32_t in_pos() const { return rc.pos; }

@@ -156,6 +156,7 @@ AVR_DEV void parser_role(const JobArgs& a, const JobMem& m, const avr_slice_desc
     AVR_SYNCWARP();
   }
   if (lane == 0) {
+    wk.dir.finish_bins();
     RingShared* r = &m.sh->ring;
     r->end_status = uint32_t(wk.status);
     r->end_mbs = wk.n_mbs;

@@ -157,14 +157,33 @@ struct Walker {
     if (!Dir::kDecompress) {
       // 1. pull the significance map out of the CABAC stream (h264_cabac.c:1667-1681)
       int last;
+      if (!is8) {
+        // 4x4-class blocks: the context of position i is base + i, all distinct, so the two contexts
+        // that can come next (last[i], sig[i+1]) are loaded while sig[i] is still being decided
+        U2 e_sig = dir.sig_peek(sig_base);
 #pragma unroll 1
-      for (last = 0; last < coefs; last++) {
-        count_bin();
-        if (dir.sig_get(*tab, sig_base + (is8 ? tab->sig8[last] : last))) {
-          mask |= uint64_t(1) << last;
-          nnz++;
+        for (last = 0; last < coefs; last++) {
+          const U2 e_last = dir.sig_peek(last_base + last);
+          const U2 e_next = dir.sig_peek(sig_base + last + 1);   // one past the block at the end: loaded, never used
           count_bin();
-          if (dir.sig_get(*tab, last_base + (is8 ? tab->last8[last] : last))) { last = max_coeff; break; }
+          if (dir.sig_get_pre(*tab, e_sig, sig_base + last)) {
+            mask |= uint64_t(1) << last;
+            nnz++;
+            count_bin();
+            if (dir.sig_get_pre(*tab, e_last, last_base + last)) { last = max_coeff; break; }
+          }
+          e_sig = e_next;
+        }
+      } else {
+#pragma unroll 1
+        for (last = 0; last < coefs; last++) {
+          count_bin();
+          if (dir.sig_get(*tab, sig_base + tab->sig8[last])) {
+            mask |= uint64_t(1) << last;
+            nnz++;
+            count_bin();
+            if (dir.sig_get(*tab, last_base + tab->last8[last])) { last = max_coeff; break; }
+          }
         }
       }
       if (last == max_coeff - 1) { mask |= uint64_t(1) << last; nnz++; }
@@ -184,16 +203,37 @@ struct Walker {
     const uint32_t slab = sig_slab(cat, key_nnz);
     uint32_t observed = 0;
     int zz = 0;
+    if (Dir::kDecompress && !is8) {
+      // decompress, 4x4-class blocks: the estimator (and its reciprocal) of BOTH possible successors
+      // -- next position with the same / with one more coefficient seen -- is fetched while the
+      // current bin is being range-decoded; the three indices are always distinct, so no forwarding
+      typename Dir::SigEntry e_cur = dir.sig_fetch(*tab, slab);
 #pragma unroll 1
-    while (observed < nnz_true && zz < coefs) {
-      const int inc = is8 ? tab->sig8[zz] : zz;
-      const int s = dir.model_bit(*tab, slab + observed * SIG_ZZ + uint32_t(inc), int((mask >> zz) & 1));
-      if (Dir::kDecompress) { count_bin(); dir.sig_put(sig_base + inc, s); }
-      if (s) {
-        observed++;
-        if (Dir::kDecompress) { count_bin(); dir.sig_put(last_base + (is8 ? tab->last8[zz] : zz), observed == nnz_true); }
+      while (observed < nnz_true && zz < coefs) {
+        const uint32_t idx = slab + observed * SIG_ZZ + uint32_t(zz);
+        const typename Dir::SigEntry e0 = dir.sig_fetch(*tab, idx + 1);
+        const typename Dir::SigEntry e1 = dir.sig_fetch(*tab, idx + 1 + SIG_ZZ);
+        const int s = dir.sig_decode(e_cur, idx);
+        count_bin(); dir.sig_put(sig_base + zz, s);
+        if (s) {
+          observed++;
+          count_bin(); dir.sig_put(last_base + zz, observed == nnz_true);
+          e_cur = e1;
+        } else e_cur = e0;
+        zz++;
       }
-      zz++;
+    } else {
+#pragma unroll 1
+      while (observed < nnz_true && zz < coefs) {
+        const int inc = is8 ? tab->sig8[zz] : zz;
+        const int s = dir.model_bit(*tab, slab + observed * SIG_ZZ + uint32_t(inc), int((mask >> zz) & 1));
+        if (Dir::kDecompress) { count_bin(); dir.sig_put(sig_base + inc, s); }
+        if (s) {
+          observed++;
+          if (Dir::kDecompress) { count_bin(); dir.sig_put(last_base + (is8 ? tab->last8[zz] : zz), observed == nnz_true); }
+        }
+        zz++;
+      }
     }
     // 4. coefficient levels (h264_cabac.c:1724-1765): ordinary context bins + bypass
     int node = 0;
@@ -538,7 +578,7 @@ struct Walker {
         (d.flags & (AVR_SLICE_MBAFF | AVR_SLICE_FIELD)) || mbw < 1 || mbh < 1 || mb_xy >= mbw * mbh) {
       status = WALK_UNSUPPORTED; done = true; return;
     }
-    dir.start_bins();
+    dir.start_bins(*tab);
   }
   AVR_DEV void step() {
     if (mb_y >= mbh) { fail(WALK_CORRUPT); done = true; return; }
