@@ -225,22 +225,19 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    from avrecode_b200 import shard
+
     def max_over_ranks(x):
-        if world == 1:
-            return x
-        t = torch.tensor([x], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
+        return shard.max_over_ranks(x, device="cuda")
 
     def sum_over_ranks(x):
-        if world == 1:
-            return x
-        t = torch.tensor([x], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.SUM)
-        return float(t.item())
+        return shard.sum_over_ranks(x, device="cuda")
 
     # file-level sharding: rank r owns stream r (same shape, different seed) -- per-GPU work is fixed
-    data, _ = gen_workload(args.workload, rank)
+    #   (avrecode_b200.shard.assign: the same LPT table on every rank, nothing exchanged)
+    stream_ids = shard.my_items([1] * world, rank, world)
+    assert len(stream_ids) == 1
+    data, _ = gen_workload(args.workload, stream_ids[0])
     entries = A.index_h264(data)
     descs = H.batch_descs(entries, mode_file=False)
     payload = sum(d.payload_size for d in descs)
