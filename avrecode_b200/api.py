@@ -57,6 +57,9 @@ def load_library():
     lib.avr_launch_count.argtypes = [C.c_void_p, C.POINTER(C.c_uint64)]
     lib.avr_flush_l2.argtypes = [C.c_void_p]
     lib.avr_index_h264.argtypes = [C.c_void_p, C.c_uint64, C.POINTER(C.POINTER(IndexEntry)), C.POINTER(C.c_int)]
+    many = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_uint64), C.c_int]
+    lib.avr_files_compress.argtypes = many + [C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]
+    lib.avr_files_decompress.argtypes = many + [C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]
     lib.avr_file_compress.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]
     lib.avr_file_decompress.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]
     lib.avr_free.argtypes = [C.c_void_p]
@@ -206,3 +209,24 @@ class Context:
         blob = C.string_at(out, nout.value)
         self._lib.avr_free(out)
         return blob
+
+    # ---- corpora: many independent files in one device batch (BASELINE config 5) ------------------
+    def _many(self, fn, name, blobs, *extra):
+        n = len(blobs)
+        bufs = [_buf(b) for b in blobs]
+        ptrs = (C.c_void_p * max(1, n))(*[b[0] for b in bufs])
+        sizes = (C.c_uint64 * max(1, n))(*[b[1] for b in bufs])
+        outs = (C.c_void_p * max(1, n))()
+        nouts = (C.c_uint64 * max(1, n))()
+        _check(fn(self._h, ptrs, sizes, n, *extra, outs, nouts), name)
+        res = []
+        for i in range(n):
+            res.append(C.string_at(outs[i], nouts[i]))
+            self._lib.avr_free(outs[i])
+        return res
+
+    def files_compress(self, files, mode=MODE_SLICE):
+        return self._many(self._lib.avr_files_compress, "avr_files_compress", files, C.c_int(mode))
+
+    def files_decompress(self, recs):
+        return self._many(self._lib.avr_files_decompress, "avr_files_decompress", recs)

@@ -125,158 +125,242 @@ extern "C" {
 
 void avr_free(void* p) { free(p); }
 
-int avr_file_compress(avr_ctx* ctx, const uint8_t* file, uint64_t file_bytes, int mode, uint8_t** rec, uint64_t* rec_bytes) {
-  if (!ctx || !file || !rec || !rec_bytes || (mode != AVR_MODE_FILE && mode != AVR_MODE_SLICE)) return AVR_ERR_ARG;
-  avr_index_entry* ents = nullptr;
-  int n_ents = 0;
-  int rc = avr_index_h264(file, file_bytes, &ents, &n_ents);
-  if (rc) return rc;
-  std::vector<char> coded(size_t(n_ents), 0);   // 1 = goes to the device
-  for (int i = 0; i < n_ents; i++) coded[i] = ents[i].recodable ? 1 : 0;
+// Shared driver of avr_file_compress / avr_files_compress: all CABAC slices of all files go to the
+// device as ONE batch (files are independent, so in either mode every file starts a fresh model).
+static int compress_many(avr_ctx* ctx, const uint8_t* const* files, const uint64_t* sizes, int n_files, int mode,
+                         uint8_t** recs, uint64_t* rec_sizes) {
+  struct Plan {
+    avr_index_entry* ents = nullptr;
+    int n_ents = 0;
+    std::vector<char> coded;      // 1 = goes to the device
+    std::vector<int> map;         // batch position -> entry, for this file
+    size_t first = 0;             // first batch position of this file
+    uint64_t base = 0;            // offset of the file in the arena
+  };
+  std::vector<Plan> plans;
+  plans.resize(size_t(n_files));
+  auto cleanup = [&]() { for (Plan& p : plans) free(p.ents); };
+  // one contiguous arena (a single file is used in place)
+  std::vector<uint8_t> arena_store;
+  const uint8_t* arena = n_files == 1 ? files[0] : nullptr;
+  uint64_t arena_bytes = n_files == 1 ? sizes[0] : 0;
+  if (n_files != 1) {
+    uint64_t total = 0;
+    for (int f = 0; f < n_files; f++) { plans[f].base = total; total += (sizes[f] + 15) & ~uint64_t(15); }
+    arena_store.resize(size_t(total) + 16);
+    for (int f = 0; f < n_files; f++) memcpy(arena_store.data() + plans[f].base, files[f], size_t(sizes[f]));
+    arena = arena_store.data(); arena_bytes = total;
+  }
+  for (int f = 0; f < n_files; f++) {
+    Plan& p = plans[f];
+    int rc = avr_index_h264(files[f], sizes[f], &p.ents, &p.n_ents);
+    if (rc) { cleanup(); return rc; }
+    p.coded.assign(size_t(p.n_ents), 0);
+    for (int i = 0; i < p.n_ents; i++) p.coded[i] = p.ents[i].recodable ? 1 : 0;
+  }
   std::vector<avr_slice_result> res;
-  std::vector<int> map;
   const uint8_t* out = nullptr;
   uint64_t out_bytes = 0;
-  // In file mode the slices share one model, so a slice the device rejects poisons everything after
-  // it; drop it (it becomes skip_coded + literal, recode.cpp:1289-1296) and run again.
+  // In file mode the slices of a file share one model, so a slice the device rejects poisons everything
+  // after it; drop it (it becomes skip_coded + literal, recode.cpp:1289-1296) and run again.
   for (int attempt = 0; attempt < 64; attempt++) {
     std::vector<avr_slice_desc> descs;
-    map.clear();
-    for (int i = 0; i < n_ents; i++) {
-      if (!coded[i] && mode == AVR_MODE_SLICE) continue;
-      avr_slice_desc d = ents[i].desc;
-      if (!coded[i]) {   // stays skip_coded + literal, but its frame_spec still flips the shared model's buffers
-        d.flags |= AVR_SLICE_SKIP;
-        d.in_off = 0; d.in_size = 0;
+    for (Plan& p : plans) {
+      p.map.clear();
+      p.first = descs.size();
+      for (int i = 0; i < p.n_ents; i++) {
+        if (!p.coded[i] && mode == AVR_MODE_SLICE) continue;
+        avr_slice_desc d = p.ents[i].desc;
+        d.in_off += p.base;
+        if (!p.coded[i]) {   // stays skip_coded + literal, but its frame_spec still flips the shared model's buffers
+          d.flags |= AVR_SLICE_SKIP;
+          d.in_off = 0; d.in_size = 0;
+        }
+        if (p.map.empty() || mode == AVR_MODE_SLICE) d.flags |= AVR_SLICE_NEW_MODEL;
+        descs.push_back(d);
+        p.map.push_back(i);
       }
-      if (map.empty() || mode == AVR_MODE_SLICE) d.flags |= AVR_SLICE_NEW_MODEL;
-      descs.push_back(d);
-      map.push_back(i);
     }
     res.assign(descs.size(), avr_slice_result());
-    rc = avr_compress(ctx, descs.data(), int(descs.size()), file, file_bytes, res.data(), &out, &out_bytes);
-    if (rc) { free(ents); return rc; }
+    int rc = avr_compress(ctx, descs.data(), int(descs.size()), arena ? arena : reinterpret_cast<const uint8_t*>(""),
+                          arena_bytes, res.data(), &out, &out_bytes);
+    if (rc) { cleanup(); return rc; }
     bool retry = false;
-    for (size_t k = 0; k < descs.size(); k++) {
-      if (res[k].status != AVR_SLICE_OK && coded[map[k]]) {
-        coded[map[k]] = 0;
-        if (mode == AVR_MODE_FILE) { retry = true; break; }
-      }
-    }
+    for (Plan& p : plans)
+      for (size_t k = 0; k < p.map.size(); k++)
+        if (res[p.first + k].status != AVR_SLICE_OK && p.coded[p.map[k]]) {
+          p.coded[p.map[k]] = 0;
+          if (mode == AVR_MODE_FILE) { retry = true; break; }
+        }
     if (!retry) break;
   }
-  std::string o;
-  if (mode == AVR_MODE_SLICE) {
-    std::string meta;
-    put_len(meta, 1, reinterpret_cast<const uint8_t*>(kSliceModeTag), sizeof(kSliceModeTag) - 1);
-    put_len(o, 1, reinterpret_cast<const uint8_t*>(meta.data()), meta.size());
-  }
-  uint64_t prev = 0;
-  size_t k = 0;
-  for (int i = 0; i < n_ents; i++) {
-    const avr_slice_desc& d = ents[i].desc;
-    bool on_device = k < map.size() && map[k] == i;
-    bool ok = on_device && coded[i] && res[k].status == AVR_SLICE_OK;
-    std::string body;
-    if (ok) {
-      std::string lit;
-      put_len(lit, 2, file + prev, size_t(d.in_off - prev));
-      emit_block(o, lit);
-      put_var(body, 1, d.payload_size);
-      put_len(body, 4, out + res[k].out_off, res[k].out_size);
-      put_var(body, 5, d.payload_size & 1);
-      if (d.payload_size > 1) put_len(body, 6, file + d.in_off + d.payload_size - 1, 1);
-      prev = d.in_off + d.payload_size;
-    } else {
-      put_var(body, 1, d.payload_size);
-      put_var(body, 3, 1);
+  int rc_all = AVR_OK;
+  for (int f = 0; f < n_files; f++) {
+    const Plan& p = plans[f];
+    const uint8_t* file = files[f];
+    std::string o;
+    if (mode == AVR_MODE_SLICE) {
+      std::string meta;
+      put_len(meta, 1, reinterpret_cast<const uint8_t*>(kSliceModeTag), sizeof(kSliceModeTag) - 1);
+      put_len(o, 1, reinterpret_cast<const uint8_t*>(meta.data()), meta.size());
     }
-    // field-number order inside the block: size(1) literal(2) skip_coded(3) cabac(4) parity(5) last(6)
-    if (!ok) {   // {size, skip_coded}
-      std::string b2;
-      put_var(b2, 1, d.payload_size);
-      put_var(b2, 3, 1);
-      body = b2;
+    uint64_t prev = 0;
+    size_t k = 0;
+    for (int i = 0; i < p.n_ents; i++) {
+      const avr_slice_desc& d = p.ents[i].desc;
+      const bool on_device = k < p.map.size() && p.map[k] == i;
+      const avr_slice_result* r = on_device ? &res[p.first + k] : nullptr;
+      const bool ok = on_device && p.coded[i] && r->status == AVR_SLICE_OK;
+      std::string body;   // field-number order inside the block: size(1) literal(2) skip_coded(3) cabac(4) parity(5) last(6)
+      if (ok) {
+        std::string lit;
+        put_len(lit, 2, file + prev, size_t(d.in_off - prev));
+        emit_block(o, lit);
+        put_var(body, 1, d.payload_size);
+        put_len(body, 4, out + r->out_off, r->out_size);
+        put_var(body, 5, d.payload_size & 1);
+        if (d.payload_size > 1) put_len(body, 6, file + d.in_off + d.payload_size - 1, 1);
+        prev = d.in_off + d.payload_size;
+      } else {   // {size, skip_coded}: the bytes stay in the surrounding literal
+        put_var(body, 1, d.payload_size);
+        put_var(body, 3, 1);
+      }
+      emit_block(o, body);
+      if (on_device) k++;
     }
-    emit_block(o, body);
-    if (on_device) k++;
+    std::string lit;
+    put_len(lit, 2, file + prev, size_t(sizes[f] - prev));
+    emit_block(o, lit);
+    int rc = to_malloc(o, &recs[f], &rec_sizes[f]);
+    if (rc) rc_all = rc;
   }
-  std::string lit;
-  put_len(lit, 2, file + prev, size_t(file_bytes - prev));
-  emit_block(o, lit);
-  free(ents);
-  return to_malloc(o, rec, rec_bytes);
+  cleanup();
+  return rc_all;
 }
 
-int avr_file_decompress(avr_ctx* ctx, const uint8_t* rec, uint64_t rec_bytes, uint8_t** file, uint64_t* file_bytes) {
-  if (!ctx || !rec || !file || !file_bytes) return AVR_ERR_ARG;
-  std::vector<Block> blocks;
-  std::string version;
-  if (!parse_container(rec, size_t(rec_bytes), &blocks, &version)) return AVR_ERR_FORMAT;
-  const bool slice_mode = version == kSliceModeTag;
-  if (!version.empty() && !slice_mode) return AVR_ERR_FORMAT;
-  // 1. rebuild the stream with surrogate payloads (recode.cpp:1359-1409, 1537-1544) so the slice
-  //    headers can be indexed exactly as on the compress side
-  std::string stream;
+int avr_file_compress(avr_ctx* ctx, const uint8_t* file, uint64_t file_bytes, int mode, uint8_t** rec, uint64_t* rec_bytes) {
+  if (!ctx || !file || !rec || !rec_bytes || (mode != AVR_MODE_FILE && mode != AVR_MODE_SLICE)) return AVR_ERR_ARG;
+  return compress_many(ctx, &file, &file_bytes, 1, mode, rec, rec_bytes);
+}
+
+int avr_files_compress(avr_ctx* ctx, const uint8_t* const* files, const uint64_t* file_bytes, int n_files, int mode,
+                       uint8_t** recs, uint64_t* rec_bytes) {
+  if (!ctx || n_files < 0 || (n_files > 0 && (!files || !file_bytes || !recs || !rec_bytes)) ||
+      (mode != AVR_MODE_FILE && mode != AVR_MODE_SLICE)) return AVR_ERR_ARG;
+  for (int f = 0; f < n_files; f++) { if (!files[f]) return AVR_ERR_ARG; recs[f] = nullptr; rec_bytes[f] = 0; }
+  if (n_files == 0) return AVR_OK;
+  int rc = compress_many(ctx, files, file_bytes, n_files, mode, recs, rec_bytes);
+  if (rc) for (int f = 0; f < n_files; f++) { free(recs[f]); recs[f] = nullptr; rec_bytes[f] = 0; }
+  return rc;
+}
+
+// Shared driver of avr_file_decompress / avr_files_decompress: every Block.cabac of every container in one batch.
+static int decompress_many(avr_ctx* ctx, const uint8_t* const* recs, const uint64_t* rec_sizes, int n_files,
+                           uint8_t** files, uint64_t* file_sizes) {
   struct CodedRef { size_t block; uint64_t off; bool is_cabac; };
-  std::vector<CodedRef> coded;
-  for (size_t i = 0; i < blocks.size(); i++) {
-    const Block& b = blocks[i];
-    if (int(b.has_literal) + int(b.has_cabac) + int(b.has_skip) != 1) return AVR_ERR_FORMAT;   // recode.cpp:1364-1366
-    if (b.has_literal) stream.append(reinterpret_cast<const char*>(b.literal), b.literal_n);
-    else if (b.has_cabac) {
-      if (!b.has_size || b.size < 8 || b.size > (int64_t(1) << 31)) return AVR_ERR_FORMAT;   // :1377-1379, 1538-1540
-      coded.push_back(CodedRef{i, stream.size(), true});
-      stream.append(size_t(b.size), 'X');
-    } else {
-      if (!b.has_size) return AVR_ERR_FORMAT;
-      coded.push_back(CodedRef{i, 0, false});
-    }
-  }
-  avr_index_entry* ents = nullptr;
-  int n_ents = 0;
-  int rc = avr_index_h264(reinterpret_cast<const uint8_t*>(stream.data()), stream.size(), &ents, &n_ents);
-  if (rc) return rc;
-  // 2. pair index entries with coded blocks in order (recognize_coded_block, recode.cpp:1546-1573)
-  if (size_t(n_ents) != coded.size()) { free(ents); return AVR_ERR_FORMAT; }
+  struct Plan {
+    std::vector<Block> blocks;
+    std::string stream;               // the file being rebuilt, surrogate payloads first
+    std::vector<CodedRef> coded;
+    std::vector<size_t> which;        // batch position (relative to first) -> coded index
+    size_t first = 0, count = 0;
+  };
+  std::vector<Plan> plans;
+  plans.resize(size_t(n_files));
   std::vector<avr_slice_desc> descs;
-  std::vector<size_t> which;
   std::string in;   // all Block.cabac bytes back to back
-  for (int i = 0; i < n_ents; i++) {
-    const Block& b = blocks[coded[i].block];
-    if (uint64_t(b.size) != ents[i].desc.payload_size) { free(ents); return AVR_ERR_FORMAT; }   // "Invalid surrogate block size"
-    if (!coded[i].is_cabac && slice_mode) continue;
-    if (coded[i].is_cabac && ents[i].desc.in_off != coded[i].off) { free(ents); return AVR_ERR_FORMAT; }
-    avr_slice_desc d = ents[i].desc;
-    d.in_off = in.size();
-    d.in_size = coded[i].is_cabac ? uint32_t(b.cabac_n) : 0;
-    if (!coded[i].is_cabac) d.flags |= AVR_SLICE_SKIP;
-    if (descs.empty() || slice_mode) d.flags |= AVR_SLICE_NEW_MODEL;
-    if (coded[i].is_cabac) in.append(reinterpret_cast<const char*>(b.cabac), b.cabac_n);
-    descs.push_back(d);
-    which.push_back(size_t(i));
+  for (int f = 0; f < n_files; f++) {
+    Plan& p = plans[f];
+    std::string version;
+    if (!parse_container(recs[f], size_t(rec_sizes[f]), &p.blocks, &version)) return AVR_ERR_FORMAT;
+    const bool slice_mode = version == kSliceModeTag;
+    if (!version.empty() && !slice_mode) return AVR_ERR_FORMAT;
+    // 1. rebuild the stream with surrogate payloads (recode.cpp:1359-1409, 1537-1544) so the slice
+    //    headers can be indexed exactly as on the compress side
+    for (size_t i = 0; i < p.blocks.size(); i++) {
+      const Block& b = p.blocks[i];
+      if (int(b.has_literal) + int(b.has_cabac) + int(b.has_skip) != 1) return AVR_ERR_FORMAT;   // recode.cpp:1364-1366
+      if (b.has_literal) p.stream.append(reinterpret_cast<const char*>(b.literal), b.literal_n);
+      else if (b.has_cabac) {
+        if (!b.has_size || b.size < 8 || b.size > (int64_t(1) << 31)) return AVR_ERR_FORMAT;   // :1377-1379, 1538-1540
+        p.coded.push_back(CodedRef{i, p.stream.size(), true});
+        p.stream.append(size_t(b.size), 'X');
+      } else {
+        if (!b.has_size) return AVR_ERR_FORMAT;
+        p.coded.push_back(CodedRef{i, 0, false});
+      }
+    }
+    avr_index_entry* ents = nullptr;
+    int n_ents = 0;
+    int rc = avr_index_h264(reinterpret_cast<const uint8_t*>(p.stream.data()), p.stream.size(), &ents, &n_ents);
+    if (rc) return rc;
+    // 2. pair index entries with coded blocks in order (recognize_coded_block, recode.cpp:1546-1573)
+    if (size_t(n_ents) != p.coded.size()) { free(ents); return AVR_ERR_FORMAT; }
+    p.first = descs.size();
+    for (int i = 0; i < n_ents; i++) {
+      const Block& b = p.blocks[p.coded[i].block];
+      if (uint64_t(b.size) != ents[i].desc.payload_size) { free(ents); return AVR_ERR_FORMAT; }   // "Invalid surrogate block size"
+      if (!p.coded[i].is_cabac && slice_mode) continue;
+      if (p.coded[i].is_cabac && ents[i].desc.in_off != p.coded[i].off) { free(ents); return AVR_ERR_FORMAT; }
+      avr_slice_desc d = ents[i].desc;
+      d.in_off = in.size();
+      d.in_size = p.coded[i].is_cabac ? uint32_t(b.cabac_n) : 0;
+      if (!p.coded[i].is_cabac) d.flags |= AVR_SLICE_SKIP;
+      if (p.which.empty() || slice_mode) d.flags |= AVR_SLICE_NEW_MODEL;
+      if (p.coded[i].is_cabac) in.append(reinterpret_cast<const char*>(b.cabac), b.cabac_n);
+      descs.push_back(d);
+      p.which.push_back(size_t(i));
+    }
+    p.count = p.which.size();
+    free(ents);
   }
-  free(ents);
   std::vector<avr_slice_result> res(descs.size());
   const uint8_t* out = nullptr;
   uint64_t out_bytes = 0;
   if (in.empty()) in.push_back(0);
-  rc = avr_decompress(ctx, descs.data(), int(descs.size()), reinterpret_cast<const uint8_t*>(in.data()), in.size(), res.data(), &out, &out_bytes);
+  int rc = avr_decompress(ctx, descs.data(), int(descs.size()), reinterpret_cast<const uint8_t*>(in.data()), in.size(),
+                          res.data(), &out, &out_bytes);
   if (rc) return rc;
   // 3. splice the rebuilt payloads in, with the x264 padding fix-up of recode.cpp:1345-1354
-  for (size_t k = 0; k < descs.size(); k++) {
-    if (res[k].status != AVR_SLICE_OK) return AVR_ERR_FORMAT;   // "Not all blocks were decoded."
-    if (descs[k].flags & AVR_SLICE_SKIP) continue;
-    const Block& b = blocks[coded[which[k]].block];
-    std::string bytes(reinterpret_cast<const char*>(out + res[k].out_off), res[k].out_size);
-    if (b.has_parity && b.has_last && b.last_n > 0) {
-      if (int(b.parity) != int(bytes.size() & 1)) bytes.push_back(char(b.last[0]));
-      else if (!bytes.empty()) bytes[bytes.size() - 1] = char(b.last[0]);
+  for (int f = 0; f < n_files; f++) {
+    Plan& p = plans[f];
+    for (size_t k = 0; k < p.count; k++) {
+      const avr_slice_result& r = res[p.first + k];
+      if (r.status != AVR_SLICE_OK) return AVR_ERR_FORMAT;   // "Not all blocks were decoded."
+      if (descs[p.first + k].flags & AVR_SLICE_SKIP) continue;
+      const CodedRef& cr = p.coded[p.which[k]];
+      const Block& b = p.blocks[cr.block];
+      std::string bytes(reinterpret_cast<const char*>(out + r.out_off), r.out_size);
+      if (b.has_parity && b.has_last && b.last_n > 0) {
+        if (int(b.parity) != int(bytes.size() & 1)) bytes.push_back(char(b.last[0]));
+        else if (!bytes.empty()) bytes[bytes.size() - 1] = char(b.last[0]);
+      }
+      if (bytes.size() != size_t(b.size)) return AVR_ERR_FORMAT;
+      memcpy(&p.stream[cr.off], bytes.data(), bytes.size());
     }
-    if (bytes.size() != size_t(b.size)) return AVR_ERR_FORMAT;
-    memcpy(&stream[coded[which[k]].off], bytes.data(), bytes.size());
   }
-  return to_malloc(stream, file, file_bytes);
+  int rc_all = AVR_OK;
+  for (int f = 0; f < n_files; f++) {
+    int r2 = to_malloc(plans[f].stream, &files[f], &file_sizes[f]);
+    if (r2) rc_all = r2;
+  }
+  return rc_all;
+}
+
+int avr_file_decompress(avr_ctx* ctx, const uint8_t* rec, uint64_t rec_bytes, uint8_t** file, uint64_t* file_bytes) {
+  if (!ctx || !rec || !file || !file_bytes) return AVR_ERR_ARG;
+  *file = nullptr; *file_bytes = 0;
+  return decompress_many(ctx, &rec, &rec_bytes, 1, file, file_bytes);
+}
+
+int avr_files_decompress(avr_ctx* ctx, const uint8_t* const* recs, const uint64_t* rec_bytes, int n_files,
+                         uint8_t** files, uint64_t* file_bytes) {
+  if (!ctx || n_files < 0 || (n_files > 0 && (!recs || !rec_bytes || !files || !file_bytes))) return AVR_ERR_ARG;
+  for (int f = 0; f < n_files; f++) { if (!recs[f]) return AVR_ERR_ARG; files[f] = nullptr; file_bytes[f] = 0; }
+  if (n_files == 0) return AVR_OK;
+  int rc = decompress_many(ctx, recs, rec_bytes, n_files, files, file_bytes);
+  if (rc) for (int f = 0; f < n_files; f++) { free(files[f]); files[f] = nullptr; file_bytes[f] = 0; }
+  return rc;
 }
 
 }  // extern "C"

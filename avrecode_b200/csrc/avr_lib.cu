@@ -337,8 +337,9 @@ int avr_sync(avr_ctx* c) {
 }
 
 int avr_collect(avr_ctx* c, avr_slice_result* results, const uint8_t** out, uint64_t* out_bytes) {
-  if (!c || !results || !out || !out_bytes) return AVR_ERR_ARG;
+  if (!c || !out || !out_bytes) return AVR_ERR_ARG;
   if (!c->launched) return AVR_ERR_STATE;
+  if (!results && c->n_slices > 0) return AVR_ERR_ARG;   // an empty batch has no results to return
   CK(cudaSetDevice(c->device));
   const int n = c->n_slices;
   const size_t total = size_t(c->out_total[c->direction]);

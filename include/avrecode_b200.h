@@ -169,6 +169,13 @@ int  avr_file_compress(avr_ctx* ctx, const uint8_t* file, uint64_t file_bytes, i
                        uint8_t** rec, uint64_t* rec_bytes);
 int  avr_file_decompress(avr_ctx* ctx, const uint8_t* rec, uint64_t rec_bytes,
                          uint8_t** file, uint64_t* file_bytes);
+/* The same for a corpus of independent files in ONE device batch (BASELINE config 5: many clips per GPU).
+ * Files never share a model, so the result for file i is byte-identical to avr_file_compress /
+ * avr_file_decompress of that file alone; recs[i] / files[i] are malloc'ed (avr_free each). */
+int  avr_files_compress(avr_ctx* ctx, const uint8_t* const* files, const uint64_t* file_bytes, int n_files, int mode,
+                        uint8_t** recs, uint64_t* rec_bytes);
+int  avr_files_decompress(avr_ctx* ctx, const uint8_t* const* recs, const uint64_t* rec_bytes, int n_files,
+                          uint8_t** files, uint64_t* file_bytes);
 void avr_free(void* p);
 
 #ifdef __cplusplus

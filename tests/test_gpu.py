@@ -186,3 +186,20 @@ def test_full_size_roundtrip_property(ctx, kw):
     res, blob = ctx.compress(descs, data)
     r_o, b_o = H.oracle_compress(descs[:1], data)
     assert H.slices_of(res, blob)[0] == H.slices_of(r_o, b_o)[0]
+
+
+def test_corpus_batch_equals_per_file(ctx):
+    """BASELINE config 5 shape: many independent clips in one device batch == each clip alone, both modes."""
+    clips = [H.gen_stream(width=320 + 64 * (i % 3), height=192 + 48 * (i % 2), frames=3 + i % 4, seed=400 + i,
+                          high=bool(i & 1), slices=1 + i % 3) for i in range(9)]
+    clips.append(b"")                                    # an empty file is a legal corpus member
+    clips.append(b"\x00\x00\x01\x09\x10not a video")     # no CABAC slice at all: one literal block
+    for mode in (A.MODE_SLICE, A.MODE_FILE):
+        recs = ctx.files_compress(clips, mode)
+        assert recs == [ctx.file_compress(c, mode) for c in clips]
+        assert ctx.files_decompress(recs) == clips
+    assert ctx.files_compress([], A.MODE_SLICE) == []
+    # containers written by the reference decode in a batch too
+    names = CASES[:3]
+    pairs = [load_case(n) for n in names]
+    assert ctx.files_decompress([r for _, r in pairs]) == [d for d, _ in pairs]
