@@ -582,6 +582,14 @@ struct Compress {
     q.push(uint32_t(CNT_CTX + ctx) | uint32_t(b) << SYM_BIT_SHIFT);
     return b;
   }
+  // a bin whose context entry was fetched ahead of time (the caller guarantees no update of that context in between)
+  typedef U2 BinEntry;
+  AVR_DEV BinEntry bin_fetch(const SharedTables&, int ctx) const { return cstate[ctx]; }
+  AVR_DEV int bin_pre(const SharedTables& t, const BinEntry e, int ctx) {
+    const int b = cabac.decide(in, t, e, &cstate[ctx]);
+    q.push(uint32_t(CNT_CTX + ctx) | uint32_t(b) << SYM_BIT_SHIFT);
+    return b;
+  }
   AVR_DEV int bypass(const SharedTables&) { const int b = cabac.bypass(in); q.push(CNT_BYPASS | uint32_t(b) << SYM_BIT_SHIFT); return b; }
   AVR_DEV int terminate(const SharedTables&) { const int b = cabac.terminate(in); q.push(CNT_TERM | uint32_t(b) << SYM_BIT_SHIFT); return b; }
   AVR_DEV int sig_get(const SharedTables& t, int ctx) { return cabac.decision(in, t, &cstate[ctx]); }   // CABAC side only
@@ -645,6 +653,17 @@ struct Decompress {
     const int b = rc.get(in, e.mg, pos);
     est_update(pos, neg, b, 0x50);
     cnt[idx] = uint16_t(pos | (neg << 8));
+    return b;
+  }
+  // an ordinary bin whose estimator + reciprocal were fetched ahead of time (no update of it in between)
+  typedef SigEntry BinEntry;
+  AVR_DEV BinEntry bin_fetch(const SharedTables& t, int ctx) const { return sig_fetch(t, uint32_t(CNT_CTX + ctx)); }
+  AVR_DEV int bin_pre(const SharedTables&, const BinEntry& e, int ctx) {
+    uint32_t pos = e.c & 0xFF, neg = e.c >> 8;
+    const int b = rc.get(in, e.mg, pos);
+    est_update(pos, neg, b, 0x60);
+    cnt[CNT_CTX + ctx] = uint16_t(pos | (neg << 8));
+    q.push(uint32_t(ctx) | uint32_t(b) << SYM_BIT_SHIFT | SYM_DECISION);
     return b;
   }
   AVR_DEV int sig_get(const SharedTables&, int) { return 0; }

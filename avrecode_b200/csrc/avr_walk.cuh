@@ -236,11 +236,15 @@ struct Walker {
       }
     }
     // 4. coefficient levels (h264_cabac.c:1724-1765): ordinary context bins + bypass
+    // The first context of the NEXT coefficient is known as soon as this one's magnitude class is, so
+    // it is fetched before the sign bin and has arrived when the sign is done.
     int node = 0;
+    typename Dir::BinEntry e1 = dir.bin_fetch(*tab, abs_base + 1);
 #pragma unroll 1
     for (uint32_t c = nnz_true; c > 0; c--) {
       const int l1 = node < 4 ? node + 1 : 0;                     // coeff_abs_level1_ctx
-      if (bin(abs_base + l1) == 0) {
+      count_bin();
+      if (dir.bin_pre(*tab, e1, abs_base + l1) == 0) {
         node = node < 3 ? node + 1 : node;                         // transition after |level| == 1
       } else {
         const int gctx = abs_base + (node < 4 ? 5 : (node + 2 < 9 ? node + 2 : 9));  // coeff_abs_levelgt1_ctx
@@ -256,6 +260,7 @@ struct Walker {
           while (j--) bypass();
         }
       }
+      e1 = dir.bin_fetch(*tab, abs_base + (node < 4 ? node + 1 : 0));
       bypass();   // sign
     }
   }
