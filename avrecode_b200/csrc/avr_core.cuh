@@ -130,6 +130,14 @@ AVR_DEV uint32_t rlps4_of(uint32_t p) {
   return uint32_t(avr_range_lps[p * 4]) | uint32_t(avr_range_lps[p * 4 + 1]) << 8 | uint32_t(avr_range_lps[p * 4 + 2]) << 16 |
          uint32_t(avr_range_lps[p * 4 + 3]) << 24;
 }
+// Context entry word x: bits 0..7 the state (2 * pStateIdx + valMPS), bits 8..19 the renormalisation
+// shift of an LPS in each of the four range classes (clz(rangeTabLPS) - 23, 1..7, three bits each), so
+// that the bin decoder needs no count-leading-zeros on its critical path.
+AVR_DEV uint32_t ctx_word_x(uint32_t state) {
+  uint32_t x = state & 0xFF;
+  for (int q = 0; q < 4; q++) x |= uint32_t(clz32(avr_range_lps[(state >> 1) * 4 + q]) - 23) << (8 + 3 * q);
+  return x;
+}
 AVR_DEV void fill_shared_tables(SharedTables* t, int tid, int nthreads) {
   for (int d = tid; d < 100; d += nthreads) {
     uint64_t m = 0; int l = 0;
@@ -149,7 +157,7 @@ AVR_DEV void fill_shared_tables(SharedTables* t, int tid, int nthreads) {
     uint32_t ns;
     if (i & 1) ns = (uint32_t(avr_trans_lps[p]) << 1) | (mps ^ (p == 0 ? 1u : 0u));
     else ns = p < 62 ? s + 2 : s;
-    t->trans[i].x = ns;
+    t->trans[i].x = ctx_word_x(ns);
     t->trans[i].y = rlps4_of(ns >> 1);
   }
   for (int i = tid; i < 64; i += nthreads) {
@@ -164,7 +172,7 @@ AVR_DEV void fill_shared_tables(SharedTables* t, int tid, int nthreads) {
 // each (512 B per refill).  Past the payload a lone stop-bit byte may follow (AVR_SLICE_STOP_BYTE),
 // then zeros -- exactly what the reference's decoder sees in libavcodec's padded NAL buffer.
 // ------------------------------------------------------------------------------------------------
-enum : uint32_t { WIN_BYTES = 1024, WIN_HALF = 512 };
+enum : uint32_t { WIN_BYTES = 2048, WIN_HALF = 1024, WIN_GUARD = 16 };
 
 struct ByteWindow {
   const uint8_t* base;   // bytes in global memory (any alignment)
@@ -177,11 +185,11 @@ struct ByteWindow {
     base = src; size = n; win = window; win_start = 0; tail = tail_byte;
     skew = uint32_t(reinterpret_cast<uintptr_t>(src) & 15);
   }
-  AVR_DEV uint32_t byte(uint32_t pos) const {
-    const uint32_t a = pos + skew;
-    if (a - win_start < WIN_BYTES) return win[a & (WIN_BYTES - 1)];
-    return pos < size ? base[pos] : (pos == size ? tail : 0);   // slow path: ran ahead of the window inside one macroblock
-  }
+  // No range check on the hot path: between two refills the reader may run at most WIN_HALF - WIN_GUARD
+  // bytes ahead (a conformant macroblock is <= 400 bytes: 3200 bits, H.264 A.3.1); the parser verifies
+  // that after every macroblock (ran_past) and gives the slice up as unsupported otherwise.
+  AVR_DEV uint32_t byte(uint32_t pos) const { return win[(pos + skew) & (WIN_BYTES - 1)]; }
+  AVR_DEV bool ran_past(uint32_t pos) const { return pos + skew + WIN_GUARD > win_start + WIN_BYTES; }
   AVR_DEV uint32_t be16(uint32_t pos) const { return (byte(pos) << 8) | byte(pos + 1); }
   AVR_DEV uint32_t limit() const { return win_start + WIN_HALF - skew; }   // consume up to here, then refill
 };
@@ -193,13 +201,14 @@ struct ByteWindow {
 // everything the decision needs; the transition is one more 8-byte table load off the critical path.
 // ------------------------------------------------------------------------------------------------
 // rangeTabLPS[state][(range >> 6) & 3] out of the four bytes packed in a context entry: one byte permute
-AVR_DEV uint32_t rlps_byte(uint32_t four, uint32_t range) {
+AVR_DEV uint32_t rlps_sel(uint32_t four, uint32_t q) {
 #if defined(__CUDA_ARCH__)
-  return __byte_perm(four, 0u, ((range >> 6) & 3u) | 0x4440u);
+  return __byte_perm(four, 0u, q | 0x4440u);
 #else
-  return (four >> ((range >> 3) & 24)) & 0xFF;
+  return (four >> (q * 8)) & 0xFF;
 #endif
 }
+AVR_DEV uint32_t rlps_byte(uint32_t four, uint32_t range) { return rlps_sel(four, (range >> 6) & 3u); }
 
 struct CabacIn {
   uint32_t val, range, pos;
@@ -214,13 +223,16 @@ struct CabacIn {
   // decides one bin from a context entry `e` that was loaded earlier (the caller may have prefetched
   // it while the previous bin was being decoded) and writes the successor state to *ctx
   AVR_DEV int decide(const ByteWindow& w, const SharedTables& t, const U2 e, U2* ctx) {
-    const uint32_t rlps = rlps_byte(e.y, range);
+    const uint32_t q = (range >> 6) & 3;
+    const uint32_t rlps = rlps_sel(e.y, q);
+    const uint32_t sh_lps = (e.x >> (8 + 3 * q)) & 7;      // renormalisation shift if this bin is the LPS
     range -= rlps;
+    const uint32_t sh_mps = (range >> 8) ^ 1;               // range in [128, 510]: one shift iff below 256
     const uint32_t scaled = range << nbits;
     const uint32_t lps = val >= scaled ? 1u : 0u;
     if (lps) { val -= scaled; range = rlps; }
-    *ctx = t.trans[e.x * 2 + lps];
-    const int shift = clz32(range) - 23;
+    const int shift = int(lps ? sh_lps : sh_mps);
+    *ctx = t.trans[(e.x & 0xFF) * 2 + lps];
     range <<= shift;
     nbits -= shift;
     refill(w);
@@ -361,7 +373,7 @@ struct CabacOut {
     range -= rlps;
     const uint32_t lps = uint32_t(bin) != (e.x & 1) ? 1u : 0u;
     if (lps) { low += range; range = rlps; }
-    *ctx = t.trans[e.x * 2 + lps];
+    *ctx = t.trans[(e.x & 0xFF) * 2 + lps];
     const int shift = clz32(range) - 23;
     range <<= shift; low <<= shift; queue += shift;
     put_bytes();

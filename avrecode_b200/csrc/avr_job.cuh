@@ -80,7 +80,7 @@ AVR_DEV void init_contexts(U2* cstate, const avr_slice_desc& d, int tid, int nth
     pre = pre < 1 ? 1 : (pre > 126 ? 126 : pre);
     // pStateIdx / valMPS from preCtxState; same numbers as libavcodec's 2*(..)-127 folding
     const uint32_t state = pre <= 63 ? uint32_t((63 - pre) << 1) : uint32_t(((pre - 64) << 1) | 1);
-    cstate[i].x = state;
+    cstate[i].x = ctx_word_x(state);
     cstate[i].y = rlps4_of(state >> 1);
   }
 }
@@ -140,7 +140,10 @@ AVR_DEV void parser_role(const JobArgs& a, const JobMem& m, const avr_slice_desc
     uint32_t in_pos = 0;
     if (lane == 0) {
       const uint32_t limit = wk.dir.in.limit();
-      while (!wk.done && wk.dir.in_pos() < limit) wk.step();
+      while (!wk.done && wk.dir.in_pos() < limit) {
+        wk.step();
+        if (wk.dir.in.ran_past(wk.dir.in_pos())) { wk.fail(WALK_UNSUPPORTED); wk.done = true; }   // macroblock > window
+      }
       done = wk.done;
       in_pos = wk.dir.in_pos();
     }
