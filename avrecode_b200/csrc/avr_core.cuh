@@ -447,6 +447,9 @@ struct Producer {
     limit = int32_t(a - b) < 0 ? a : b;
   }
   AVR_DEV void push(uint32_t e) {
+#ifdef AVR_PROBE_NO_PUSH
+    if (!(e & SYM_END)) return;
+#endif
     reinterpret_cast<volatile uint32_t*>(r->e)[tail & (RING_ENTRIES - 1)] = e;
     if (++tail == limit) slow();
   }

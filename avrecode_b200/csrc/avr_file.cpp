@@ -199,6 +199,7 @@ static int compress_many(avr_ctx* ctx, const uint8_t* const* files, const uint64
     const Plan& p = plans[f];
     const uint8_t* file = files[f];
     std::string o;
+    o.reserve(size_t(sizes[f]) + size_t(sizes[f]) / 16 + 64 * size_t(p.n_ents) + 256);
     if (mode == AVR_MODE_SLICE) {
       std::string meta;
       put_len(meta, 1, reinterpret_cast<const uint8_t*>(kSliceModeTag), sizeof(kSliceModeTag) - 1);
@@ -275,6 +276,8 @@ static int decompress_many(avr_ctx* ctx, const uint8_t* const* recs, const uint6
     if (!parse_container(recs[f], size_t(rec_sizes[f]), &p.blocks, &version)) return AVR_ERR_FORMAT;
     const bool slice_mode = version == kSliceModeTag;
     if (!version.empty() && !slice_mode) return AVR_ERR_FORMAT;
+    p.stream.reserve(size_t(rec_sizes[f]) + size_t(rec_sizes[f]) / 8 + 4096);
+    in.reserve(in.size() + size_t(rec_sizes[f]));
     // 1. rebuild the stream with surrogate payloads (recode.cpp:1359-1409, 1537-1544) so the slice
     //    headers can be indexed exactly as on the compress side
     for (size_t i = 0; i < p.blocks.size(); i++) {

@@ -180,9 +180,16 @@ extern "C" int avr_index_h264(const uint8_t* file, uint64_t file_bytes, avr_inde
   uint32_t last_first_mb = 0;
   size_t n = size_t(file_bytes), i = 0;
   // locate the first start code
+  // 00 00 01 by memchr on the 0x01 (SIMD in libc; 0x01 is rare in entropy-coded data), then two bytes back
   auto find_sc = [&](size_t from) -> size_t {
-    for (size_t k = from; k + 2 < n; k++)
-      if (file[k] == 0 && file[k + 1] == 0 && file[k + 2] == 1) return k;
+    size_t k = from + 2;
+    while (k < n) {
+      const void* hit = memchr(file + k, 1, n - k);
+      if (!hit) break;
+      k = size_t(static_cast<const uint8_t*>(hit) - file);
+      if (file[k - 1] == 0 && file[k - 2] == 0) return k - 2;
+      k++;
+    }
     return n;
   };
   i = find_sc(0);
@@ -273,11 +280,18 @@ extern "C" int avr_index_h264(const uint8_t* file, uint64_t file_bytes, avr_inde
           size_t end = body_n;
           while (end > pay_raw && body[end - 1] == 0) end--;
           bool escaped = false;
-          {
-            int z = b.zeros();
-            for (size_t k = pay_raw; k < end; k++) {
-              if (z >= 2 && body[k] == 3) { escaped = true; break; }
-              z = body[k] == 0 ? z + 1 : 0;
+          {   // an emulation-prevention byte: 0x03 after two zero bytes (the zeros may end the slice header)
+            const int z = b.zeros();
+            size_t k = pay_raw;
+            while (k < end) {
+              const void* hit = memchr(body + k, 3, end - k);
+              if (!hit) break;
+              k = size_t(static_cast<const uint8_t*>(hit) - body);
+              const size_t back = k - pay_raw;   // payload bytes before the 0x03
+              const bool z1 = back >= 1 ? body[k - 1] == 0 : z >= 1;
+              const bool z2 = back >= 2 ? body[k - 2] == 0 : (back == 1 ? z >= 1 : z >= 2);
+              if (z1 && z2) { escaped = true; break; }
+              k++;
             }
           }
           if (end > pay_raw) {
