@@ -99,10 +99,11 @@ AVR_DEV uint32_t sig_slab(int cat, uint32_t key_nnz) {   // index of [observed =
 // Small read-only tables in shared memory (per thread block).
 // ------------------------------------------------------------------------------------------------
 struct U2 { uint32_t x, y; };
+struct alignas(16) U4 { uint32_t x, y, z, w; };   // two U2 side by side: one 16-byte load
 struct alignas(16) DivMagic { uint64_t magic; uint32_t shift, pad; };   // one 16-byte load per division
 struct SharedTables {
   DivMagic div[100];       // magic = ceil(2^(63+l) / d), l = ceil(log2 d), shift = l - 1: exact floor(n/d) for n <= 2^63
-  U2 trans[256];           // [state * 2 + lps] -> {next state, the four rangeTabLPS bytes of the next state}
+  alignas(16) U2 trans[256];   // [state * 2 + lps] -> successor entry; the MPS/LPS pair of a state is one 16-byte load
   uint8_t sig8[64];        // significant_coeff_flag ctxIdxInc, 8x8 frame blocks
   uint8_t last8[64];
 };
@@ -222,7 +223,11 @@ struct CabacIn {
   }
   // decides one bin from a context entry `e` that was loaded earlier (the caller may have prefetched
   // it while the previous bin was being decoded) and writes the successor state to *ctx
-  AVR_DEV int decide(const ByteWindow& w, const SharedTables& t, const U2 e, U2* ctx) {
+  // core of a decision: consumes entry e, returns the bin and leaves the successor entry in `next`.
+  // Both successors (MPS / LPS) are fetched with ONE 16-byte load whose address only needs the state,
+  // so the transition is a select, not a load, once the bin is known.
+  AVR_DEV int decide_core(const ByteWindow& w, const SharedTables& t, const U2 e, U2* next) {
+    const U4 pair = reinterpret_cast<const U4*>(t.trans)[e.x & 0xFF];
     const uint32_t q = (range >> 6) & 3;
     const uint32_t rlps = rlps_sel(e.y, q);
     const uint32_t sh_lps = (e.x >> (8 + 3 * q)) & 7;      // renormalisation shift if this bin is the LPS
@@ -232,11 +237,20 @@ struct CabacIn {
     const uint32_t lps = val >= scaled ? 1u : 0u;
     if (lps) { val -= scaled; range = rlps; }
     const int shift = int(lps ? sh_lps : sh_mps);
-    *ctx = t.trans[(e.x & 0xFF) * 2 + lps];
+    next->x = lps ? pair.z : pair.x;
+    next->y = lps ? pair.w : pair.y;
     range <<= shift;
     nbits -= shift;
     refill(w);
     return int((e.x & 1) ^ lps);
+  }
+  // decides one bin from a context entry `e` that was loaded earlier (the caller may have prefetched
+  // it while the previous bin was being decoded) and writes the successor state to *ctx
+  AVR_DEV int decide(const ByteWindow& w, const SharedTables& t, const U2 e, U2* ctx) {
+    U2 n;
+    const int b = decide_core(w, t, e, &n);
+    *ctx = n;
+    return b;
   }
   AVR_DEV int decision(const ByteWindow& w, const SharedTables& t, U2* ctx) { return decide(w, t, *ctx, ctx); }
   AVR_DEV int bypass(const ByteWindow& w) {
@@ -605,6 +619,15 @@ struct Compress {
     q.push(uint32_t(CNT_CTX + ctx) | uint32_t(b) << SYM_BIT_SHIFT);
     return b;
   }
+  // a run of bins on ONE context: the entry stays in registers (bin_run), written back once (bin_store)
+  AVR_DEV int bin_run(const SharedTables& t, BinEntry& e, int ctx) {
+    BinEntry n;
+    const int b = cabac.decide_core(in, t, e, &n);
+    e = n;
+    q.push(uint32_t(CNT_CTX + ctx) | uint32_t(b) << SYM_BIT_SHIFT);
+    return b;
+  }
+  AVR_DEV void bin_store(const BinEntry& e, int ctx) { cstate[ctx] = e; }
   AVR_DEV int bypass(const SharedTables&) { const int b = cabac.bypass(in); q.push(CNT_BYPASS | uint32_t(b) << SYM_BIT_SHIFT); return b; }
   AVR_DEV int terminate(const SharedTables&) { const int b = cabac.terminate(in); q.push(CNT_TERM | uint32_t(b) << SYM_BIT_SHIFT); return b; }
   AVR_DEV int sig_get(const SharedTables& t, int ctx) { return cabac.decision(in, t, &cstate[ctx]); }   // CABAC side only
@@ -681,6 +704,21 @@ struct Decompress {
     q.push(uint32_t(ctx) | uint32_t(b) << SYM_BIT_SHIFT | SYM_DECISION);
     return b;
   }
+  // a run of bins on ONE context: estimator and reciprocal stay in registers; the next reciprocal is
+  // div[total + 1], known before the bin is, unless the update halves the counts (rare: reloaded)
+  AVR_DEV int bin_run(const SharedTables& t, BinEntry& e, int ctx) {
+    uint32_t pos = e.c & 0xFF, neg = e.c >> 8;
+    const uint32_t tot = pos + neg;
+    const DivMagic mg_next = t.div[tot + 1];
+    const int b = rc.get(in, e.mg, pos);
+    est_update(pos, neg, b, 0x60);
+    e.c = pos | (neg << 8);
+    e.mg = mg_next;
+    if (tot + 1 > 0x60) e.mg = t.div[pos + neg];
+    q.push(uint32_t(ctx) | uint32_t(b) << SYM_BIT_SHIFT | SYM_DECISION);
+    return b;
+  }
+  AVR_DEV void bin_store(const BinEntry& e, int ctx) { cnt[CNT_CTX + ctx] = uint16_t(e.c); }
   AVR_DEV int sig_get(const SharedTables&, int) { return 0; }
   AVR_DEV U2 sig_peek(int) const { return U2(); }
   AVR_DEV int sig_get_pre(const SharedTables&, const U2, int) { return 0; }

@@ -250,8 +250,10 @@ struct Walker {
         const int gctx = abs_base + (node < 4 ? 5 : (node + 2 < 9 ? node + 2 : 9));  // coeff_abs_levelgt1_ctx
         node = node < 4 ? 4 : (node < 7 ? node + 1 : 7);           // transition after |level| > 1
         int abs = 2;
+        typename Dir::BinEntry g = dir.bin_fetch(*tab, gctx);   // a run on one context: state kept in registers
 #pragma unroll 1
-        while (abs < 15 && bin(gctx)) abs++;
+        while (abs < 15) { count_bin(); if (!dir.bin_run(*tab, g, gctx)) break; abs++; }
+        dir.bin_store(g, gctx);
         if (abs >= 15) {
           int j = 0;
 #pragma unroll 1
