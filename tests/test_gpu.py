@@ -203,3 +203,20 @@ def test_corpus_batch_equals_per_file(ctx):
     names = CASES[:3]
     pairs = [load_case(n) for n in names]
     assert ctx.files_decompress([r for _, r in pairs]) == [d for d, _ in pairs]
+
+
+@pytest.mark.parametrize("resident", ["1", "0"], ids=["shared-estimators", "global-estimators"])
+def test_both_estimator_placements_equal_oracle(built, resident, monkeypatch):
+    """The kernel has two variants (estimators resident in shared memory / in the global workspace); the
+    heuristic picks by batch size, AVR_RESIDENT forces one.  Both must give the oracle's bytes."""
+    monkeypatch.setenv("AVR_RESIDENT", resident)
+    with A.Context() as c:
+        for kw in (dict(width=320, height=192, frames=3, seed=1, slices=2),
+                   dict(width=352, height=288, frames=4, high=True, seed=3, p8x8=0.7, refs=2)):
+            data = H.gen_stream(**kw)
+            for mode_file in (True, False):
+                descs = H.batch_descs(A.index_h264(data), mode_file)
+                res, blob = c.compress(descs, data)
+                r_o, b_o = H.oracle_compress(descs, data)
+                assert H.slices_of(res, blob) == H.slices_of(r_o, b_o)
+                check_roundtrip(c, descs, data, res, blob)
