@@ -430,7 +430,7 @@ AVR_DEV void est_update(uint32_t& pos, uint32_t& neg, int bit, uint32_t limit) {
 // publishes its head every RING_PUBLISH entries.
 // ------------------------------------------------------------------------------------------------
 enum : uint32_t {
-  RING_ENTRIES = 1024, RING_PUBLISH = 64, RING_BATCH = 128,
+  RING_ENTRIES = 512, RING_PUBLISH = 64, RING_BATCH = 128,
   SYM_BIT_SHIFT = 16, SYM_KIND_SHIFT = 20, SYM_DECISION = 0u << 20, SYM_BYPASS = 1u << 20, SYM_TERMINATE = 2u << 20,
   SYM_END = 1u << 31,
 };

@@ -1,6 +1,6 @@
 // avr_walk.cuh -- the H.264 slice_data context-selection state machine (parser warp, lane 0).
 //
-// Restates, for frame macroblocks in 4:2:0 / 8 bit / I and P slices, what libavcodec does between
+// Restates, for frame macroblocks in 4:2:0 / 8 bit / I, P and B slices, what libavcodec does between
 // two per-bin hook calls: ffmpeg/libavcodec/h264_cabac.c:1926-2480 (ff_h264_decode_mb_cabac and its
 // syntax-element decoders), :1550-1780 (coded_block_flag contexts, residual blocks), the neighbour
 // plumbing of h264_mvpred.h:356-834 reduced to the syntax-level facts context selection reads, and
@@ -25,14 +25,16 @@ struct alignas(4) MbCtx {          // what later macroblocks need from a decoded
   uint16_t cbp;         // cbp_table semantics: luma 0..3, chroma 4..5, 0x40<<c chroma DC, 0x100 luma DC
   uint8_t nz_bottom;    // coefficient flags of the bottom block row: luma x=0..3 -> bits 0..3, Cb x=0,1 -> 4,5, Cr -> 6,7
   uint8_t nz_right;     // right block column: luma y=0..3 -> bits 0..3, Cb y=0,1 -> 4,5, Cr -> 6,7
-  uint8_t ref_pos;      // bit b8: ref_idx (list 0) > 0
-  uint8_t reserved;
+  uint8_t ref_pos;      // bit (4 * list + b8): ref_idx > 0
+  uint8_t dir8;         // bit b8: that 8x8 is direct-predicted (0xF for B_Skip / B_Direct_16x16), h264_mvpred.h:723-753
   uint8_t mvd_bottom[4][2];  // list 0, bottom row x=0..3, {|mvdx|,|mvdy|} clipped to 70
   uint8_t mvd_right[4][2];   // list 0, right column y=0..3
   uint8_t nnz[20];           // avrecode model: stored nnz of the blocks a neighbour can ask for (k_nnz_slot)
+  uint8_t mvd1_bottom[4][2]; // list 1 (B slices)
+  uint8_t mvd1_right[4][2];
 };
-static_assert(sizeof(MbCtx) == 44, "MbCtx layout");
-enum : int { MBCTX_WORDS = 11, MBCTX_NNZ_WORD = 6 };
+static_assert(sizeof(MbCtx) == 60, "MbCtx layout");
+enum : int { MBCTX_WORDS = 15, MBCTX_NNZ_WORD = 6 };
 
 // block index -> slot in MbCtx::nnz.  A left/above neighbour lookup (recode.cpp:419-471) can only land
 // on the right column / bottom row of the neighbouring macroblock, on the first block of an 8x8
@@ -49,7 +51,7 @@ enum : uint16_t {
 
 struct alignas(8) WalkShared {     // per-block scratch of the walker (shared memory on the device)
   MbCtx left;           // the previous macroblock
-  uint8_t mvd[16][2];   // list-0 |mvd| of the macroblock being walked, by 4x4 block index
+  uint8_t mvd[2][16][2];  // |mvd| of the macroblock being walked, [list][4x4 block index][x, y]
   uint8_t nnz_mb[52];   // avrecode model: stored nnz of the macroblock being walked, by block index
 };
 
@@ -60,6 +62,14 @@ AVR_TABLE_QUAL int16_t k_last_base[6] = {166, 181, 195, 210, 213, dctx(417)};
 AVR_TABLE_QUAL int16_t k_abs_base[6] = {227, 237, 247, 257, 266, dctx(426)};
 AVR_TABLE_QUAL int16_t k_cbf_base[6] = {85, 89, 93, 97, 101, dctx(1012)};
 enum : int { CTX_T8X8 = dctx(399) };
+// B macroblock types 0..22 (h264data.h:127-151 b_mb_type_info): partition shape (0 direct, 1 16x16, 2 16x8,
+// 3 8x16, 4 8x8) and the prediction lists of partition 0 / 1 (bit 0 = list 0, bit 1 = list 1)
+AVR_TABLE_QUAL uint8_t k_b_shape[23] = {0, 1, 1, 1, 2, 3, 2, 3, 2, 3, 2, 3, 2, 3, 2, 3, 2, 3, 2, 3, 2, 3, 4};
+AVR_TABLE_QUAL uint8_t k_b_p0[23] = {0, 1, 2, 3, 1, 1, 2, 2, 1, 1, 2, 2, 1, 1, 2, 2, 3, 3, 3, 3, 3, 3, 3};
+AVR_TABLE_QUAL uint8_t k_b_p1[23] = {0, 0, 0, 0, 1, 1, 2, 2, 2, 2, 1, 1, 3, 3, 3, 3, 1, 1, 2, 2, 3, 3, 3};
+// B sub-macroblock types 0..12 (h264data.h:153-170): shape (0 direct, 1 8x8, 2 8x4, 3 4x8, 4 4x4) and lists
+AVR_TABLE_QUAL uint8_t k_bsub_shape[13] = {0, 1, 1, 1, 2, 3, 2, 3, 2, 3, 4, 4, 4};
+AVR_TABLE_QUAL uint8_t k_bsub_pred[13] = {0, 1, 2, 3, 1, 1, 2, 2, 3, 3, 1, 2, 3};
 
 // block index <-> 4x4 raster position (h264.h:1004-1024 scan8 geometry)
 AVR_DEV int blk_x(int n) { return (n & 1) + ((n >> 1) & 2); }
@@ -83,8 +93,8 @@ struct Walker {
                          // empty and every neighbour count comes from the shared-memory row, no global traffic
   // slice constants
   uint32_t first_mb;
-  int mbw, mbh, num_ref_l0;
-  bool is_p, t8_mode;
+  int mbw, mbh, num_ref_l0, num_ref_l1;
+  bool is_p, is_b, t8_mode, d8inf;
   // running state
   int mb_x, mb_y, mb_xy;
   int last_qp_delta;
@@ -93,8 +103,8 @@ struct Walker {
   bool done;
   // per macroblock
   bool left_ok, top_ok, model_is8x8;
-  uint32_t left_cbp, top_cbp, left_flags, top_flags, left_nzr, top_nzb, left_refpos, top_refpos;
-  uint32_t cur_flags, cur_cbp, cur_refpos;
+  uint32_t left_cbp, top_cbp, left_flags, top_flags, left_nzr, top_nzb, left_refpos, top_refpos, left_dir8, top_dir8;
+  uint32_t cur_flags, cur_cbp, cur_refpos, cur_dir8;
   uint64_t nzmask;       // coefficient presence of the current macroblock, bit = block index (cbf contexts)
 
   AVR_DEV void count_bin() { n_bins_lo++; }
@@ -288,13 +298,14 @@ struct Walker {
     else { a = nz_neighbor(blk, false, intra); b = nz_neighbor(blk, true, intra); }
     return k_cbf_base[cat] + a + 2 * b;
   }
-  AVR_DEV int mvd_sum(int n, int comp) const {   // h264_cabac.c:1539-1548
+  AVR_DEV int mvd_sum(int list, int n, int comp) const {   // h264_cabac.c:1539-1548
     const int x = blk_x(n), y = blk_y(n);
+    const uint32_t uses = list ? MBF_L1 : MBF_L0;
     int a = 0, b = 0;
-    if (x > 0) a = ws->mvd[blk_at(x - 1, y)][comp];
-    else if (left_ok && (left_flags & MBF_L0)) a = ws->left.mvd_right[y][comp];
-    if (y > 0) b = ws->mvd[blk_at(x, y - 1)][comp];
-    else if (top_ok && (top_flags & MBF_L0)) b = row[mb_x].mvd_bottom[x][comp];
+    if (x > 0) a = ws->mvd[list][blk_at(x - 1, y)][comp];
+    else if (left_ok && (left_flags & uses)) a = list ? ws->left.mvd1_right[y][comp] : ws->left.mvd_right[y][comp];
+    if (y > 0) b = ws->mvd[list][blk_at(x, y - 1)][comp];
+    else if (top_ok && (top_flags & uses)) b = list ? row[mb_x].mvd1_bottom[x][comp] : row[mb_x].mvd_bottom[x][comp];
     return a + b;
   }
   AVR_DEV int mvd_component(int ctxbase, int amvd) {   // h264_cabac.c:1502-1537; returns stored |mvd|
@@ -313,32 +324,36 @@ struct Walker {
     bypass();   // sign
     return mvd < 70 ? mvd : 70;
   }
-  AVR_DEV void mvd_part(int n, int w, int h) {
+  AVR_DEV void mvd_part(int list, int n, int w, int h) {
     int s[2];
 #pragma unroll 1
     for (int comp = 0; comp < 2; comp++) {
-      const int v = mvd_component(40 + 7 * comp, mvd_sum(n, comp));
+      const int v = mvd_component(40 + 7 * comp, mvd_sum(list, n, comp));
       if (comp == 0) s[0] = v; else s[1] = v;
     }
     const int x = blk_x(n), y = blk_y(n);
     for (int j = 0; j < h; j++)
-      for (int i = 0; i < w; i++) { uint8_t* m = ws->mvd[blk_at(x + i, y + j)]; m[0] = uint8_t(s[0]); m[1] = uint8_t(s[1]); }
+      for (int i = 0; i < w; i++) { uint8_t* m = ws->mvd[list][blk_at(x + i, y + j)]; m[0] = uint8_t(s[0]); m[1] = uint8_t(s[1]); }
   }
-  AVR_DEV int ref_pos_neighbor(int n, bool above) const {   // "refa > 0" of h264_cabac.c:1475-1490 (P slices)
+  // "refa > 0 [&& !direct]" of h264_cabac.c:1475-1490: the 8x8 left of / above 4x4 block n
+  AVR_DEV int ref_pos_neighbor(int list, int n, bool above) const {
     const int x = blk_x(n), y = blk_y(n);
+    uint32_t refpos, dir8;
+    int b8;
     if (above) {
-      if (y > 0) return int((cur_refpos >> ((x >> 1) + 2 * ((y - 1) >> 1))) & 1);
-      if (!top_ok) return 0;
-      return int((top_refpos >> (2 + (x >> 1))) & 1);
+      if (y > 0) { refpos = cur_refpos; dir8 = cur_dir8; b8 = (x >> 1) + 2 * ((y - 1) >> 1); }
+      else { if (!top_ok) return 0; refpos = top_refpos; dir8 = top_dir8; b8 = 2 + (x >> 1); }
+    } else {
+      if (x > 0) { refpos = cur_refpos; dir8 = cur_dir8; b8 = ((x - 1) >> 1) + 2 * (y >> 1); }
+      else { if (!left_ok) return 0; refpos = left_refpos; dir8 = left_dir8; b8 = 1 + 2 * (y >> 1); }
     }
-    if (x > 0) return int((cur_refpos >> (((x - 1) >> 1) + 2 * (y >> 1))) & 1);
-    if (!left_ok) return 0;
-    return int((left_refpos >> (1 + 2 * (y >> 1))) & 1);
+    if (is_b && ((dir8 >> b8) & 1)) return 0;
+    return int((refpos >> (4 * list + b8)) & 1);
   }
-  AVR_DEV int read_ref(int n) {   // h264_cabac.c:1473-1500 with the rc > 1 guard of :2232-2240
-    const int rc = num_ref_l0;
+  AVR_DEV int read_ref(int list, int n) {   // h264_cabac.c:1473-1500 with the rc > 1 guard of :2232-2240
+    const int rc = list ? num_ref_l1 : num_ref_l0;
     if (rc <= 1) return 0;
-    int ctx = ref_pos_neighbor(n, false) + 2 * ref_pos_neighbor(n, true);
+    int ctx = ref_pos_neighbor(list, n, false) + 2 * ref_pos_neighbor(list, n, true);
     int ref = 0;
 #pragma unroll 1
     while (bin(54 + ctx)) {
@@ -369,7 +384,7 @@ struct Walker {
 
   // ---- one macroblock (h264_cabac.c:1926-2480, frame macroblocks, 4:2:0) --------------------------
   AVR_DEV void macroblock() {
-    cur_flags = 0; cur_cbp = 0; cur_refpos = 0;
+    cur_flags = 0; cur_cbp = 0; cur_refpos = 0; cur_dir8 = 0;
     nzmask = 0;
     model_is8x8 = false;
     for (int i = 0; i < 13; i++) reinterpret_cast<uint32_t*>(ws->nnz_mb)[i] = 0;
@@ -378,28 +393,58 @@ struct Walker {
     {   // neighbour facts into registers
       const MbCtx* l = &ws->left;
       const MbCtx* t = &row[mb_x];
-      left_flags = l->flags; left_cbp = l->cbp; left_nzr = l->nz_right; left_refpos = l->ref_pos;
-      top_flags = t->flags; top_cbp = t->cbp; top_nzb = t->nz_bottom; top_refpos = t->ref_pos;
+      left_flags = l->flags; left_cbp = l->cbp; left_nzr = l->nz_right; left_refpos = l->ref_pos; left_dir8 = l->dir8;
+      top_flags = t->flags; top_cbp = t->cbp; top_nzb = t->nz_bottom; top_refpos = t->ref_pos; top_dir8 = t->dir8;
     }
-    if (is_p) {   // mb_skip_flag, h264_cabac.c:1332-1367
-      int ctx = 0;
+    const bool inter_slice = is_p || is_b;
+    if (inter_slice) {   // mb_skip_flag, h264_cabac.c:1332-1367
+      int ctx = is_b ? 13 : 0;
       if (left_ok && !(left_flags & MBF_SKIP)) ctx++;
       if (top_ok && !(top_flags & MBF_SKIP)) ctx++;
-      if (bin(11 + ctx)) {
-        cur_flags = MBF_SKIP | MBF_L0;
+      if (bin(11 + ctx)) {   // decode_mb_skip (h264_mvpred.h:803-834): P_Skip, or B_Skip = direct with both lists
+        cur_flags = is_b ? uint32_t(MBF_SKIP | MBF_DIRECT | MBF_L0 | MBF_L1) : uint32_t(MBF_SKIP | MBF_L0);
+        cur_dir8 = is_b ? 0xFu : 0u;
         last_qp_delta = 0;
-        for (int i = 0; i < 8; i++) reinterpret_cast<uint32_t*>(ws->mvd)[i] = 0;
+        for (int i = 0; i < 16; i++) reinterpret_cast<uint32_t*>(ws->mvd)[i] = 0;
         return;
       }
     }
-    int itype = -1, ptype = -1;
+    // macroblock type.  Inter macroblocks are reduced to: shape (0 direct 16x16, 1 16x16, 2 16x8, 3 8x16,
+    // 4 8x8) and the prediction lists of partition 0 / 1 (bit 0 = list 0, bit 1 = list 1).
+    int itype = -1, shape = -1;
+    uint32_t pred0 = 1, pred1 = 1;
     bool want_intra = true;
-    if (is_p && !bin(14)) {   // h264_cabac.c:2008-2023
+    if (is_b) {   // h264_cabac.c:1973-2007
+      int ctx = 0;
+      if (left_ok && !(left_flags & MBF_DIRECT)) ctx++;
+      if (top_ok && !(top_flags & MBF_DIRECT)) ctx++;
+      int t = -1;
+      if (!bin(27 + ctx)) t = 0;
+      else if (!bin(27 + 3)) t = 1 + bin(27 + 5);
+      else {
+        int bits = bin(27 + 4) << 3;
+        bits += bin(27 + 5) << 2;
+        bits += bin(27 + 5) << 1;
+        bits += bin(27 + 5);
+        if (bits < 8) t = bits + 3;
+        else if (bits == 13) t = -1;
+        else if (bits == 14) t = 11;
+        else if (bits == 15) t = 22;
+        else { bits = (bits << 1) + bin(27 + 5); t = bits - 4; }
+      }
+      if (t >= 0) {
+        want_intra = false;
+        if (t > 22) { fail(WALK_CORRUPT); return; }
+        shape = k_b_shape[t]; pred0 = k_b_p0[t]; pred1 = k_b_p1[t];
+      }
+    } else if (is_p && !bin(14)) {   // h264_cabac.c:2008-2023
       want_intra = false;
+      int ptype;
       if (!bin(15)) ptype = 3 * bin(16);
       else ptype = 2 - bin(17);
+      shape = ptype + 1;
     }
-    if (want_intra) itype = intra_mb_type(is_p ? 17 : 3, !is_p);
+    if (want_intra) itype = intra_mb_type(is_b ? 32 : is_p ? 17 : 3, !inter_slice);
 
     const bool intra = itype >= 0;
     bool i16 = false;
@@ -413,7 +458,7 @@ struct Walker {
         cbp = (k >= 12 ? 15 : 0) + 16 * chroma;
       }
       cur_flags = uint32_t(MBF_INTRA | (i16 ? MBF_I16 : 0));
-    } else cur_flags = MBF_L0;
+    }
 
     // neighbour cbp with libavcodec's "unavailable" defaults (h264_mvpred.h:589-603)
     top_cbp = top_ok ? top_cbp : (intra ? 0x7CFu : 0x00Fu);
@@ -442,39 +487,82 @@ struct Walker {
         if (bin(67)) bin(67);
       }
     } else {
-      for (int i = 0; i < 8; i++) reinterpret_cast<uint32_t*>(ws->mvd)[i] = 0;
-      uint32_t subs = 0;   // 2 bits per 8x8 quadrant: 0 = 8x8, 1 = 8x4, 2 = 4x8, 3 = 4x4
-      if (ptype == 3) {    // P_8x8: decode_cabac_p_mb_sub_type, h264_cabac.c:1445-1454
+      for (int i = 0; i < 16; i++) reinterpret_cast<uint32_t*>(ws->mvd)[i] = 0;
+      const int lists = is_b ? 2 : 1;
+      if (shape == 0) {   // B_Direct_16x16 (h264_cabac.c:2221-2225): nothing coded, everything inferred
+        cur_flags = MBF_DIRECT | MBF_L0 | MBF_L1;
+        cur_dir8 = 0xF;
+        t8_allowed = t8_allowed && d8inf;
+      } else {
+        uint32_t subs = 0;      // 8x8 only, 2 bits per quadrant: 0 = 8x8, 1 = 8x4, 2 = 4x8, 3 = 4x4
+        uint32_t subpred = 0;   // 8x8 only, 2 bits per quadrant: prediction lists (0 for a direct quadrant)
+        if (shape == 4) {
 #pragma unroll 1
-        for (int i = 0; i < 4; i++) {
-          int sub;
-          if (bin(21)) sub = 0;
-          else if (!bin(22)) sub = 1;
-          else sub = bin(23) ? 2 : 3;
-          subs |= uint32_t(sub) << (2 * i);
+          for (int i = 0; i < 4; i++) {
+            int sub, pr = 1;
+            if (is_b) {   // decode_cabac_b_mb_sub_type, h264_cabac.c:1455-1471
+              int t;
+              if (!bin(36)) t = 0;
+              else if (!bin(37)) t = 1 + bin(39);
+              else {
+                t = 3;
+                bool done13 = false;
+                if (bin(38)) {
+                  if (bin(39)) { t = 11 + bin(39); done13 = true; }
+                  else t += 4;
+                }
+                if (!done13) { t += 2 * bin(39); t += bin(39); }
+              }
+              const int sh = k_bsub_shape[t];
+              pr = k_bsub_pred[t];
+              if (sh == 0) { cur_dir8 |= 1u << i; sub = 0; pr = 0; if (!d8inf) t8_allowed = false; }
+              else sub = sh - 1;
+            } else {      // decode_cabac_p_mb_sub_type, h264_cabac.c:1445-1454
+              if (bin(21)) sub = 0;
+              else if (!bin(22)) sub = 1;
+              else sub = bin(23) ? 2 : 3;
+            }
+            subs |= uint32_t(sub) << (2 * i);
+            subpred |= uint32_t(pr) << (2 * i);
+          }
+          if (subs) t8_allowed = false;   // get_dct8x8_allowed, h264.h:1165-1177
+          cur_flags = is_b ? uint32_t(MBF_L0 | MBF_L1) : uint32_t(MBF_L0);   // B_8x8 counts as using both lists
+        } else {
+          const uint32_t any = pred0 | (shape == 1 ? 0u : pred1);
+          cur_flags = ((any & 1) ? uint32_t(MBF_L0) : 0u) | ((any & 2) ? uint32_t(MBF_L1) : 0u);
         }
-        if (subs) t8_allowed = false;   // get_dct8x8_allowed, h264.h:1165-1177
-      }
-      // partitions: P_L0_16x16 one, 16x8 / 8x16 two, P_8x8 four quadrants (h264_cabac.c:2114-2330)
-      const int nq = ptype == 3 ? 4 : (ptype == 0 ? 1 : 2);
+        // partitions: 16x16 one, 16x8 / 8x16 two, 8x8 four quadrants (h264_cabac.c:2114-2330); for every
+        // list all reference indices first, then for every list all motion vector differences
+        const int nq = shape == 4 ? 4 : (shape == 1 ? 1 : 2);
 #pragma unroll 1
-      for (int q = 0; q < nq; q++) {   // all reference indices first
-        const int n = ptype == 1 ? 8 * q : (ptype == 0 ? 0 : 4 * q);
-        const uint32_t covers = ptype == 0 ? 0xFu : ptype == 1 ? (3u << (2 * q)) : ptype == 2 ? (5u << q) : (1u << q);
-        if (read_ref(n) > 0) cur_refpos |= covers;
-      }
+        for (int list = 0; list < lists; list++) {
 #pragma unroll 1
-      for (int q = 0; q < nq; q++) {   // then the motion vector differences
-        int base, w, h, cnt = 1, stride = 0;
-        if (ptype == 3) {
-          const int s = int((subs >> (2 * q)) & 3);
-          base = 4 * q; w = s < 2 ? 2 : 1; h = (s == 0 || s == 2) ? 2 : 1;
-          cnt = s == 0 ? 1 : (s == 3 ? 4 : 2); stride = s == 1 ? 2 : 1;
-        } else if (ptype == 0) { base = 0; w = 4; h = 4; }
-        else if (ptype == 1) { base = 8 * q; w = 4; h = 2; }
-        else { base = 4 * q; w = 2; h = 4; }
+          for (int q = 0; q < nq; q++) {
+            const uint32_t pr = shape == 4 ? ((subpred >> (2 * q)) & 3) : (q ? pred1 : pred0);
+            if (!((pr >> list) & 1)) continue;
+            const int n = shape == 2 ? 8 * q : (shape == 1 ? 0 : 4 * q);
+            const uint32_t covers = shape == 1 ? 0xFu : shape == 2 ? (3u << (2 * q)) : shape == 3 ? (5u << q) : (1u << q);
+            if (read_ref(list, n) > 0) cur_refpos |= covers << (4 * list);
+          }
+        }
 #pragma unroll 1
-        for (int j = 0; j < cnt; j++) mvd_part(base + j * stride, w, h);
+        for (int list = 0; list < lists; list++) {
+#pragma unroll 1
+          for (int q = 0; q < nq; q++) {
+            const uint32_t pr = shape == 4 ? ((subpred >> (2 * q)) & 3) : (q ? pred1 : pred0);
+            if (!((pr >> list) & 1)) continue;
+            int base, w, h, cnt = 1, stride = 0;
+            if (shape == 4) {
+              const int sb = int((subs >> (2 * q)) & 3);
+              base = 4 * q; w = sb < 2 ? 2 : 1; h = (sb == 0 || sb == 2) ? 2 : 1;
+              cnt = sb == 0 ? 1 : (sb == 3 ? 4 : 2); stride = sb == 1 ? 2 : 1;
+            } else if (shape == 1) { base = 0; w = 4; h = 4; }
+            else if (shape == 2) { base = 8 * q; w = 4; h = 2; }
+            else { base = 4 * q; w = 2; h = 4; }
+#pragma unroll 1
+            for (int j = 0; j < cnt; j++) mvd_part(list, base + j * stride, w, h);
+          }
+        }
       }
     }
 
@@ -552,14 +640,18 @@ struct Walker {
       w[10] = uint32_t(z[48]) | uint32_t(z[49]) << 8 | uint32_t(z[50]) << 16;
     }
     w[0] = (cur_flags & 0xFFFF) | (cur_cbp & 0xFFFF) << 16;
-    w[1] = nb | nr << 8 | (cur_refpos & 0xFF) << 16;
-    if (cur_flags & MBF_INTRA) { w[2] = w[3] = w[4] = w[5] = 0; }
+    w[1] = nb | nr << 8 | (cur_refpos & 0xFF) << 16 | (cur_dir8 & 0xF) << 24;
+    if (cur_flags & MBF_INTRA) { w[2] = w[3] = w[4] = w[5] = 0; w[11] = w[12] = w[13] = w[14] = 0; }
     else {
-      const uint16_t* mv = reinterpret_cast<const uint16_t*>(ws->mvd);   // one u16 = {|mvdx|, |mvdy|} of a 4x4 block
+      const uint16_t* mv = reinterpret_cast<const uint16_t*>(ws->mvd);   // one u16 = {|mvdx|, |mvdy|} of a 4x4 block; list 1 at +16
       w[2] = uint32_t(mv[10]) | uint32_t(mv[11]) << 16;   // bottom row x = 0..3: blocks 10, 11, 14, 15
       w[3] = uint32_t(mv[14]) | uint32_t(mv[15]) << 16;
       w[4] = uint32_t(mv[5]) | uint32_t(mv[7]) << 16;     // right column y = 0..3: blocks 5, 7, 13, 15
       w[5] = uint32_t(mv[13]) | uint32_t(mv[15]) << 16;
+      w[11] = uint32_t(mv[16 + 10]) | uint32_t(mv[16 + 11]) << 16;
+      w[12] = uint32_t(mv[16 + 14]) | uint32_t(mv[16 + 15]) << 16;
+      w[13] = uint32_t(mv[16 + 5]) | uint32_t(mv[16 + 7]) << 16;
+      w[14] = uint32_t(mv[16 + 13]) | uint32_t(mv[16 + 15]) << 16;
     }
     uint32_t* r = reinterpret_cast<uint32_t*>(&row[mb_x]);
     uint32_t* l = reinterpret_cast<uint32_t*>(&ws->left);
@@ -571,8 +663,11 @@ struct Walker {
     mbw = d.mb_width; mbh = d.mb_height;
     first_mb = d.first_mb;
     is_p = d.slice_type == AVR_SLICE_P;
+    is_b = d.slice_type == AVR_SLICE_B;
+    d8inf = (d.flags & AVR_SLICE_DIRECT_8X8_INFERENCE) != 0;
     t8_mode = (d.flags & AVR_SLICE_TRANSFORM_8X8) != 0;
     num_ref_l0 = d.num_ref_idx_l0;
+    num_ref_l1 = d.num_ref_idx_l1;
     mb_xy = int(d.first_mb);
     mb_x = mb_xy % (mbw > 0 ? mbw : 1); mb_y = mb_xy / (mbw > 0 ? mbw : 1);
     last_qp_delta = 0;
@@ -581,7 +676,7 @@ struct Walker {
     n_mbs = 0;
     done = false;
     for (int i = 0; i < MBCTX_WORDS; i++) reinterpret_cast<uint32_t*>(&ws->left)[i] = 0;
-    if (d.slice_type > AVR_SLICE_I || d.slice_type == AVR_SLICE_B || d.chroma_format_idc != 1 ||
+    if (d.slice_type > AVR_SLICE_I || d.chroma_format_idc != 1 ||
         (d.flags & (AVR_SLICE_MBAFF | AVR_SLICE_FIELD)) || mbw < 1 || mbh < 1 || mb_xy >= mbw * mbh) {
       status = WALK_UNSUPPORTED; done = true; return;
     }

@@ -32,6 +32,10 @@ CASES = {
     "tiny_1mb_rows": dict(mbw=3, mbh=2, frames=6, slices=2, seed=7, density=1.5),
     # 1x1-macroblock pictures: slices whose rbsp_stop_one_bit sits alone in the next byte (AVR_SLICE_STOP_BYTE)
     "one_mb_stop_byte": dict(mbw=1, mbh=1, frames=9, seed=14),
+    # B slices (kept as reference pictures with increasing frame_num, SURVEY hazard H2): B mb/sub-mb types,
+    # direct, both reference lists, 8x8 transform under direct_8x8_inference
+    "main_b_2refs": dict(width=320, height=192, frames=8, bpics=0.6, refs=2, seed=5),
+    "high_b_8x8_slices": dict(width=352, height=288, frames=8, bpics=0.6, refs=3, high=True, slices=2, seed=16, pskip=0.3),
 }
 
 

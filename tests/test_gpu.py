@@ -71,6 +71,8 @@ SEEDED = [
     dict(width=400, height=240, frames=12, seed=13, refs=4, pskip=0.7, pintra=0.2),
     dict(mbw=1, mbh=1, frames=9, seed=14),
     dict(mbw=255, mbh=2, frames=2, seed=15, slices=2),
+    dict(width=480, height=272, frames=12, bpics=0.8, seed=17, refs=4, high=True, p8x8=0.8, pskip=0.5),   # B slices
+    dict(width=640, height=368, frames=10, bpics=0.5, seed=18, refs=3, slices=3, ragged=True),
 ]
 
 
@@ -109,7 +111,7 @@ def test_empty_and_degenerate_batches(ctx):
     assert res[0].status == _abi.AVR_SLICE_UNSUPPORTED and res[0].out_size == 0
     d = _abi.copy_desc(ents[0].desc)
     d.flags |= _abi.AVR_SLICE_NEW_MODEL
-    d.slice_type = _abi.AVR_SLICE_B
+    d.slice_type = 3   # SP / SI slices are not walked
     res, _ = ctx.compress([d], data)
     assert res[0].status == _abi.AVR_SLICE_UNSUPPORTED
     # a payload of garbage must end as CORRUPT/OK-with-different-size, not hang or fault

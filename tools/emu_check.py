@@ -12,6 +12,8 @@ CASES = [
     dict(mbw=1, mbh=1, frames=9, seed=14),
     dict(mbw=255, mbh=2, frames=2, seed=15, slices=2),
     dict(width=1920, height=1088, frames=4, high=True, seed=31, kbps=30000, fps=60),
+    dict(width=480, height=272, frames=12, bpics=0.8, seed=17, refs=4, high=True, p8x8=0.8, pskip=0.5),
+    dict(width=640, height=368, frames=10, bpics=0.5, seed=18, refs=3, slices=3, ragged=True),
 ]
 bad = 0
 for kw in CASES:

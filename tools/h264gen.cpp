@@ -105,6 +105,7 @@ struct GenConfig {
   double p_skip = 0.35, p_intra_in_p = 0.08;
   double p_dense = 0.0;    // P(4x4 block forced fully significant) -- exercises SURVEY hazard H1
   int num_refs = 2;
+  double p_bpic = 0.0;     // P(a non-intra picture is coded as B slices); B pictures stay reference pictures
   bool ragged_slices = false;  // slice boundaries at arbitrary macroblocks instead of row starts
   uint64_t seed = 1;
 };
@@ -271,6 +272,7 @@ static std::vector<uint8_t> generate(const GenConfig& c, GenStats* st) {
   for (int f = 0; f < c.frames; f++) {
     bool intra = f == 0 || c.intra_period == 1 || (c.intra_period > 1 && f % c.intra_period == 0);
     bool idr = f == 0;
+    const bool bpic = !intra && f >= 2 && c.num_refs >= 2 && c.p_bpic > 0 && rng.bern(c.p_bpic);
     // smooth activity field, correlated in space and time, so that avrecode's priors have something to learn
     for (int y = 0; y < c.mbh; y++)
       for (int x = 0; x < c.mbw; x++) {
@@ -296,13 +298,16 @@ static std::vector<uint8_t> generate(const GenConfig& c, GenStats* st) {
       int refs_avail = f < c.num_refs ? f : c.num_refs;
       int nref = intra ? 0 : (refs_avail < 1 ? 1 : refs_avail);
       b.ue(uint32_t(first));
-      b.ue(intra ? 7 : 5);    // slice_type (all slices of the picture alike)
+      b.ue(bpic ? 6 : intra ? 7 : 5);    // slice_type (all slices of the picture alike)
       b.ue(0);                // pps id
       b.u(4, uint32_t(f & 15));  // frame_num
       if (idr) b.ue(0);       // idr_pic_id
+      if (bpic) b.u(1, 1);    // direct_spatial_mv_pred_flag
       if (!intra) {
         b.u(1, 1); b.ue(uint32_t(nref - 1));  // num_ref_idx_active_override
+        if (bpic) b.ue(uint32_t(nref - 1));   // num_ref_idx_l1_active_minus1
         b.u(1, 0);            // ref_pic_list_modification_flag_l0
+        if (bpic) b.u(1, 0);  // ref_pic_list_modification_flag_l1
       }
       if (idr) { b.u(1, 0); b.u(1, 0); }  // no_output_of_prior_pics, long_term_reference_flag
       else b.u(1, 0);                     // adaptive_ref_pic_marking_mode_flag
@@ -317,9 +322,9 @@ static std::vector<uint8_t> generate(const GenConfig& c, GenStats* st) {
       avr_slice_desc d;
       memset(&d, 0, sizeof d);
       d.first_mb = uint32_t(first); d.mb_width = uint16_t(c.mbw); d.mb_height = uint16_t(c.mbh);
-      d.slice_type = intra ? AVR_SLICE_I : AVR_SLICE_P;
+      d.slice_type = bpic ? AVR_SLICE_B : intra ? AVR_SLICE_I : AVR_SLICE_P;
       d.cabac_init_idc = uint8_t(cabac_init_idc); d.slice_qp = int8_t(qp);
-      d.num_ref_idx_l0 = uint8_t(nref); d.num_ref_idx_l1 = 0; d.chroma_format_idc = 1;
+      d.num_ref_idx_l0 = uint8_t(nref); d.num_ref_idx_l1 = uint8_t(bpic ? nref : 0); d.chroma_format_idc = 1;
       d.flags = uint8_t((c.high ? AVR_SLICE_TRANSFORM_8X8 : 0) | AVR_SLICE_DIRECT_8X8_INFERENCE);
       GeneratorIO io(c, &rng, &b, end - first, &act, c.mbw, density);
       SliceWalker<GeneratorIO> w(&io, &pic, d);
@@ -346,7 +351,7 @@ static void usage() {
   fprintf(stderr,
           "usage: h264gen -o out.h264 [--width W --height H | --mbw N --mbh N] [--frames N] [--slices N]\n"
           "       [--high] [--p8x8 P] [--intra-period N] [--qp Q] [--density D] [--kbps K --fps F]\n"
-          "       [--pskip P] [--pintra P] [--pdense P] [--refs N] [--ragged] [--seed S]\n");
+          "       [--pskip P] [--pintra P] [--pdense P] [--refs N] [--bpics P] [--ragged] [--seed S]\n");
 }
 
 int main(int argc, char** argv) {
@@ -374,6 +379,7 @@ int main(int argc, char** argv) {
     else if (a == "--pintra") c.p_intra_in_p = atof(next());
     else if (a == "--pdense") c.p_dense = atof(next());
     else if (a == "--refs") c.num_refs = atoi(next());
+    else if (a == "--bpics") c.p_bpic = atof(next());
     else if (a == "--ragged") c.ragged_slices = true;
     else if (a == "--seed") c.seed = strtoull(next(), nullptr, 10);
     else { usage(); return 2; }
