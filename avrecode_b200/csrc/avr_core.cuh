@@ -433,7 +433,15 @@ enum : uint32_t {
   RING_ENTRIES = 512, RING_PUBLISH = 64, RING_BATCH = 128,
   SYM_BIT_SHIFT = 16, SYM_KIND_SHIFT = 20, SYM_DECISION = 0u << 20, SYM_BYPASS = 1u << 20, SYM_TERMINATE = 2u << 20,
   SYM_END = 1u << 31,
+  // Decompression sends one coefficient level as ONE entry (per-bin pushes were ~10 % of its parser):
+  //   bits 0..8 first context, 9 its bin, 10..18 the "greater than one" context, 19..22 how many 1-bins it
+  //   coded, 23 whether a 0-bin ended that run, 24 whether the sign follows, 25 the sign (bypass).
+  SYM_LEVEL = 1u << 30, LVL_BIT1 = 9, LVL_GCTX = 10, LVL_RUN = 19, LVL_TERM = 23, LVL_HAS_SIGN = 24, LVL_SIGN = 25,
 };
+AVR_DEV uint32_t lvl_entry(int ctx1, int b1, int gctx, int run, int term, int has_sign, int sign) {
+  return SYM_LEVEL | uint32_t(ctx1) | uint32_t(b1) << LVL_BIT1 | uint32_t(gctx) << LVL_GCTX | uint32_t(run) << LVL_RUN |
+         uint32_t(term) << LVL_TERM | uint32_t(has_sign) << LVL_HAS_SIGN | uint32_t(sign) << LVL_SIGN;
+}
 
 #if defined(__CUDACC__) && !defined(AVR_HOST_EMULATION)
 // release/acquire at block scope is all the ring needs (entries before the published index)
@@ -577,6 +585,15 @@ struct CoderDecompress {   // CABAC re-encoder (cabac_code.h:16-86; recode.cpp:1
     for (;;) {
       const uint32_t e = q.pop();
       if (e & SYM_END) break;
+      if (e & SYM_LEVEL) {   // one coefficient level: first bin, run of "greater than one" bins, sign
+        const uint32_t g = (e >> LVL_GCTX) & 0x1FF;
+        cabac.decision(t, int((e >> LVL_BIT1) & 1), &cstate[e & 0x1FF]);
+#pragma unroll 1
+        for (uint32_t r = (e >> LVL_RUN) & 15; r > 0; r--) cabac.decision(t, 1, &cstate[g]);
+        if ((e >> LVL_TERM) & 1) cabac.decision(t, 0, &cstate[g]);
+        if ((e >> LVL_HAS_SIGN) & 1) cabac.bypass(int((e >> LVL_SIGN) & 1));
+        continue;
+      }
       const int bit = int((e >> SYM_BIT_SHIFT) & 1);
       const uint32_t kind = e & (3u << SYM_KIND_SHIFT);
       if (kind == SYM_DECISION) cabac.decision(t, bit, &cstate[e & 0xFFFF]);
@@ -628,6 +645,12 @@ struct Compress {
     return b;
   }
   AVR_DEV void bin_store(const BinEntry& e, int ctx) { cstate[ctx] = e; }
+  // coefficient levels: this direction keeps one entry per bin (its coder is a software-pipelined loop over
+  // plain entries, and composite entries cost it more than they save the parser); lvl_push is a no-op here
+  AVR_DEV int lvl_first(const SharedTables& t, const BinEntry e, int ctx) { return bin_pre(t, e, ctx); }
+  AVR_DEV int lvl_run(const SharedTables& t, BinEntry& e, int ctx) { return bin_run(t, e, ctx); }
+  AVR_DEV int lvl_sign(const SharedTables& t) { return bypass(t); }
+  AVR_DEV void lvl_push(uint32_t) {}
   AVR_DEV int bypass(const SharedTables&) { const int b = cabac.bypass(in); q.push(CNT_BYPASS | uint32_t(b) << SYM_BIT_SHIFT); return b; }
   AVR_DEV int terminate(const SharedTables&) { const int b = cabac.terminate(in); q.push(CNT_TERM | uint32_t(b) << SYM_BIT_SHIFT); return b; }
   AVR_DEV int sig_get(const SharedTables& t, int ctx) { return cabac.decision(in, t, &cstate[ctx]); }   // CABAC side only
@@ -719,6 +742,34 @@ struct Decompress {
     return b;
   }
   AVR_DEV void bin_store(const BinEntry& e, int ctx) { cnt[CNT_CTX + ctx] = uint16_t(e.c); }
+  // coefficient levels: the same decoders without the per-bin push; lvl_push sends the whole level at once
+  AVR_DEV int lvl_first(const SharedTables&, const BinEntry& e, int ctx) {
+    uint32_t pos = e.c & 0xFF, neg = e.c >> 8;
+    const int b = rc.get(in, e.mg, pos);
+    est_update(pos, neg, b, 0x60);
+    cnt[CNT_CTX + ctx] = uint16_t(pos | (neg << 8));
+    return b;
+  }
+  AVR_DEV int lvl_run(const SharedTables& t, BinEntry& e, int) {
+    uint32_t pos = e.c & 0xFF, neg = e.c >> 8;
+    const uint32_t tot = pos + neg;
+    const DivMagic mg_next = t.div[tot + 1];
+    const int b = rc.get(in, e.mg, pos);
+    est_update(pos, neg, b, 0x60);
+    e.c = pos | (neg << 8);
+    e.mg = mg_next;
+    if (tot + 1 > 0x60) e.mg = t.div[pos + neg];
+    return b;
+  }
+  AVR_DEV int lvl_sign(const SharedTables& t) {
+    uint32_t pos = byp_c & 0xFF, neg = byp_c >> 8;
+    const int b = rc.get(in, byp_mg, pos);
+    est_update(pos, neg, b, 0x60);
+    byp_c = pos | (neg << 8);
+    byp_mg = t.div[pos + neg];
+    return b;
+  }
+  AVR_DEV void lvl_push(uint32_t entry) { q.push(entry); }
   AVR_DEV int sig_get(const SharedTables&, int) { return 0; }
   AVR_DEV U2 sig_peek(int) const { return U2(); }
   AVR_DEV int sig_get_pre(const SharedTables&, const U2, int) { return 0; }

@@ -252,28 +252,36 @@ struct Walker {
     typename Dir::BinEntry e1 = dir.bin_fetch(*tab, abs_base + 1);
 #pragma unroll 1
     for (uint32_t c = nnz_true; c > 0; c--) {
-      const int l1 = node < 4 ? node + 1 : 0;                     // coeff_abs_level1_ctx
+      const int ctx1 = abs_base + (node < 4 ? node + 1 : 0);      // coeff_abs_level1_ctx
+      int gctx = abs_base + 5, run = 0, term = 0;
+      bool escape = false;
       count_bin();
-      if (dir.bin_pre(*tab, e1, abs_base + l1) == 0) {
+      const int b1 = dir.lvl_first(*tab, e1, ctx1);
+      if (b1 == 0) {
         node = node < 3 ? node + 1 : node;                         // transition after |level| == 1
       } else {
-        const int gctx = abs_base + (node < 4 ? 5 : (node + 2 < 9 ? node + 2 : 9));  // coeff_abs_levelgt1_ctx
+        gctx = abs_base + (node < 4 ? 5 : (node + 2 < 9 ? node + 2 : 9));  // coeff_abs_levelgt1_ctx
         node = node < 4 ? 4 : (node < 7 ? node + 1 : 7);           // transition after |level| > 1
-        int abs = 2;
-        typename Dir::BinEntry g = dir.bin_fetch(*tab, gctx);   // a run on one context: state kept in registers
+        typename Dir::BinEntry g = dir.bin_fetch(*tab, gctx);      // a run on one context: state kept in registers
 #pragma unroll 1
-        while (abs < 15) { count_bin(); if (!dir.bin_run(*tab, g, gctx)) break; abs++; }
+        while (run < 13) { count_bin(); if (!dir.lvl_run(*tab, g, gctx)) { term = 1; break; } run++; }
         dir.bin_store(g, gctx);
-        if (abs >= 15) {
-          int j = 0;
-#pragma unroll 1
-          while (bypass() && j < 30) j++;
-#pragma unroll 1
-          while (j--) bypass();
-        }
+        escape = !term;                                             // |level| >= 15: Exp-Golomb suffix follows
       }
       e1 = dir.bin_fetch(*tab, abs_base + (node < 4 ? node + 1 : 0));
-      bypass();   // sign
+      if (!escape) {
+        count_bin();
+        const int sg = dir.lvl_sign(*tab);
+        dir.lvl_push(lvl_entry(ctx1, b1, gctx, run, term, 1, sg));   // the whole level as one ring entry
+      } else {
+        dir.lvl_push(lvl_entry(ctx1, b1, gctx, run, term, 0, 0));
+        int j = 0;
+#pragma unroll 1
+        while (bypass() && j < 30) j++;
+#pragma unroll 1
+        while (j--) bypass();
+        bypass();   // sign
+      }
     }
   }
 
