@@ -37,7 +37,7 @@ class SliceDesc(C.Structure):
         ("num_ref_idx_l1", C.c_uint8),
         ("chroma_format_idc", C.c_uint8),
         ("flags", C.c_uint8),
-        ("reserved", C.c_uint8),
+        ("n_streams", C.c_uint8),
     ]
 
 

@@ -381,16 +381,28 @@ struct CabacOut {
       sink.push(o & 0xFF, o >> 8);
     }
   }
-  AVR_DEV void decision(const SharedTables& t, int bin, U2* ctx) {
-    const U2 e = *ctx;
-    const uint32_t rlps = rlps_byte(e.y, range);
+  // core of a decision, the mirror image of CabacIn::decide_core: consumes context entry e, leaves the successor
+  // in `next`.  Both successors come with ONE 16-byte load addressed by the state alone, and the renormalisation
+  // shift comes out of the entry (LPS) or of range's top bit (MPS): no count-leading-zeros, no dependent load.
+  AVR_DEV void encode_core(const SharedTables& t, const U2 e, int bin, U2* next) {
+    const U4 pair = reinterpret_cast<const U4*>(t.trans)[e.x & 0xFF];
+    const uint32_t q = (range >> 6) & 3;
+    const uint32_t rlps = rlps_sel(e.y, q);
+    const uint32_t sh_lps = (e.x >> (8 + 3 * q)) & 7;
     range -= rlps;
+    const uint32_t sh_mps = (range >> 8) ^ 1;
     const uint32_t lps = uint32_t(bin) != (e.x & 1) ? 1u : 0u;
     if (lps) { low += range; range = rlps; }
-    *ctx = t.trans[(e.x & 0xFF) * 2 + lps];
-    const int shift = clz32(range) - 23;
+    const int shift = int(lps ? sh_lps : sh_mps);
+    next->x = lps ? pair.z : pair.x;
+    next->y = lps ? pair.w : pair.y;
     range <<= shift; low <<= shift; queue += shift;
     put_bytes();
+  }
+  AVR_DEV void decision(const SharedTables& t, int bin, U2* ctx) {
+    U2 n;
+    encode_core(t, *ctx, bin, &n);
+    *ctx = n;
   }
   AVR_DEV void bypass(int bin) {
     low <<= 1;
@@ -433,6 +445,13 @@ enum : uint32_t {
   RING_ENTRIES = 512, RING_PUBLISH = 64, RING_BATCH = 128,
   SYM_BIT_SHIFT = 16, SYM_KIND_SHIFT = 20, SYM_DECISION = 0u << 20, SYM_BYPASS = 1u << 20, SYM_TERMINATE = 2u << 20,
   SYM_END = 1u << 31,
+  // Wide slices only (one slice spread over several range-coder streams, macroblock row r in stream
+  // r mod K): kind 3 entries hand a row over between the parser warps of a decompression --
+  //   SP_ROW_END  a row is complete; bit 0 = "the last macroblock coded a non-zero mb_qp_delta"
+  //   SP_QPD      first mb_qp_delta bin of a row: its CABAC context (60 + that bit) is only known to the
+  //               re-encoder, which sees the rows in order; the bin value sits at SYM_BIT_SHIFT
+  SYM_SPECIAL = 3u << 20, SP_ROW_END = 1u << 8, SP_QPD = 2u << 8,
+  WIDE_MAX = 2,          // most streams per wide slice: every stream's estimators are resident in shared memory
   // Decompression sends one coefficient level as ONE entry (per-bin pushes were ~10 % of its parser):
   //   bits 0..8 first context, 9 its bin, 10..18 the "greater than one" context, 19..22 how many 1-bins it
   //   coded, 23 whether a 0-bin ended that run, 24 whether the sign follows, 25 the sign (bypass).
@@ -446,17 +465,28 @@ AVR_DEV uint32_t lvl_entry(int ctx1, int b1, int gctx, int run, int term, int ha
 #if defined(__CUDACC__) && !defined(AVR_HOST_EMULATION)
 // release/acquire at block scope is all the ring needs (entries before the published index)
 AVR_DEV void ring_fence() { asm volatile("fence.acq_rel.cta;" ::: "memory"); }
+// Waits of the wide-slice kernel are long (a coder warp idles while the rows of the other streams are parsed, a
+// parser warp idles behind the row above), and a warp that polls flat out takes issue slots and shared-memory
+// cycles from the warps of its block that do the serial work: poll a few times, then sleep between polls.
+#define AVR_SYNCWARP_CORE() __syncwarp()
+AVR_DEV void wide_backoff(uint32_t& polls) { if (++polls > 32) __nanosleep(polls > 256 ? 1000 : 100); }
 struct RingShared {
   uint32_t e[RING_ENTRIES];
   uint32_t tail_pub, head_pub;
   uint32_t end_status, end_mbs, end_bins_lo, end_bins_hi;   // written by the parser before SYM_END
-  uint32_t pad_[2];
+  uint32_t prod_tail, cons_head;   // wide slices: where a producer / consumer that moved to another ring left off
 };
-AVR_DEV void ring_reset(RingShared* r) { r->tail_pub = 0; r->head_pub = 0; }
+AVR_DEV void ring_reset(RingShared* r) { r->tail_pub = 0; r->head_pub = 0; r->prod_tail = 0; r->cons_head = 0; }
 struct Producer {
   RingShared* r;
+  volatile uint32_t* ents;   // the entries: r->e, or (wide decompression) a much longer ring in global memory
+  uint32_t cap;              // entries in ents, a power of two
   uint32_t tail, limit, pub, head_seen;
-  AVR_DEV void init(RingShared* ring) { r = ring; tail = pub = head_seen = 0; limit = RING_PUBLISH; }
+  AVR_DEV void init(RingShared* ring, uint32_t* far_entries = nullptr, uint32_t far_cap = 0) {
+    r = ring; tail = pub = head_seen = 0; limit = RING_PUBLISH;
+    ents = far_entries ? far_entries : ring->e;
+    cap = far_entries ? far_cap : uint32_t(RING_ENTRIES);
+  }
   AVR_DEV void publish() {
     ring_fence();
     *reinterpret_cast<volatile uint32_t*>(&r->tail_pub) = tail;
@@ -464,25 +494,40 @@ struct Producer {
   }
   AVR_DEV void slow() {
     publish();
-    while (tail - head_seen >= RING_ENTRIES) head_seen = *reinterpret_cast<volatile uint32_t*>(&r->head_pub);
-    const uint32_t a = head_seen + RING_ENTRIES, b = pub + RING_PUBLISH;
+    while (tail - head_seen >= cap) head_seen = *reinterpret_cast<volatile uint32_t*>(&r->head_pub);
+    const uint32_t a = head_seen + cap, b = pub + RING_PUBLISH;
     limit = int32_t(a - b) < 0 ? a : b;
+  }
+  AVR_DEV void switch_to(RingShared* next) {   // wide compression: the next macroblock row goes to another ring
+    publish();
+    r->prod_tail = tail;
+    r = next;
+    ents = next->e;
+    tail = pub = r->prod_tail;
+    head_seen = *reinterpret_cast<volatile uint32_t*>(&r->head_pub);
+    slow();
   }
   AVR_DEV void push(uint32_t e) {
 #ifdef AVR_PROBE_NO_PUSH
     if (!(e & SYM_END)) return;
 #endif
-    reinterpret_cast<volatile uint32_t*>(r->e)[tail & (RING_ENTRIES - 1)] = e;
+    ents[tail & (cap - 1)] = e;
     if (++tail == limit) slow();
   }
 };
 struct Consumer {
   RingShared* r;
   uint32_t head, tail_seen;
-  AVR_DEV void init(RingShared* ring) { r = ring; head = tail_seen = 0; }
+  bool patient;   // wide slices: long waits, see wide_backoff
+  AVR_DEV void init(RingShared* ring, bool long_waits = false) { r = ring; head = tail_seen = 0; patient = long_waits; }
   // batch interface: wait for published entries, read them in place, release them in one go
   AVR_DEV uint32_t wait_avail() {
+    if (patient) {
+      uint32_t polls = 0;
+      while (head == (tail_seen = *reinterpret_cast<volatile uint32_t*>(&r->tail_pub))) wide_backoff(polls);
+    }
     while (head == tail_seen) tail_seen = *reinterpret_cast<volatile uint32_t*>(&r->tail_pub);
+    ring_fence();   // acquire: peek() reads the entries with plain loads, which must not be hoisted above the spin
     const uint32_t n = tail_seen - head;
     return n < RING_BATCH ? n : uint32_t(RING_BATCH);   // bounded, so the producer gets its slots back early
   }
@@ -491,6 +536,13 @@ struct Consumer {
     head += n;
     ring_fence();
     *reinterpret_cast<volatile uint32_t*>(&r->head_pub) = head;
+  }
+  AVR_DEV void switch_to(RingShared* next) {   // wide slices: the next macroblock row comes from another ring
+    ring_fence();
+    *reinterpret_cast<volatile uint32_t*>(&r->head_pub) = head;
+    r->cons_head = head;
+    r = next;
+    head = tail_seen = r->cons_head;
   }
   AVR_DEV uint32_t pop() {
     if (head == tail_seen) {
@@ -509,24 +561,29 @@ struct Consumer {
 #include <vector>
 namespace avr {
 // host emulation: the parser runs a whole slice into an unbounded queue, then the coder drains it
+inline void ring_fence() {}
+#define AVR_SYNCWARP_CORE() ((void)0)
 struct RingShared {
   std::vector<uint32_t> e;
   uint32_t end_status, end_mbs, end_bins_lo, end_bins_hi;
+  size_t cons_head;
 };
-inline void ring_reset(RingShared* r) { r->e.clear(); }
+inline void ring_reset(RingShared* r) { r->e.clear(); r->cons_head = 0; }
 struct Producer {
   RingShared* r;
-  void init(RingShared* ring) { r = ring; }
+  void init(RingShared* ring, uint32_t* = nullptr, uint32_t = 0) { r = ring; }
   void publish() {}
+  void switch_to(RingShared* next) { r = next; }
   void push(uint32_t e) { r->e.push_back(e); }
 };
 struct Consumer {
   RingShared* r;
   size_t head;
-  void init(RingShared* ring) { r = ring; head = 0; }
+  void init(RingShared* ring, bool = false) { r = ring; head = 0; }
   uint32_t wait_avail() { return head < r->e.size() ? uint32_t(r->e.size() - head > 64 ? 64 : r->e.size() - head) : 1u; }
   uint32_t peek(uint32_t k) const { return head + k < r->e.size() ? r->e[head + k] : uint32_t(SYM_END); }
   void release(uint32_t n) { head += n; }
+  void switch_to(RingShared* next) { r->cons_head = head; r = next; head = r->cons_head; }
   uint32_t pop() { return head < r->e.size() ? r->e[head++] : uint32_t(SYM_END); }
 };
 #endif
@@ -581,24 +638,90 @@ struct CoderCompress {     // estimators + range encoder (recode.cpp:1068-1096 h
 struct CoderDecompress {   // CABAC re-encoder (cabac_code.h:16-86; recode.cpp:1443, 1455, 1466)
   CabacOut cabac;
   AVR_DEV void begin(uint8_t* dst, uint32_t cap) { cabac.init(dst, cap); }
+  AVR_DEV void entry(const SharedTables& t, U2* cstate, uint32_t e) {
+    if (e & SYM_LEVEL) {   // one coefficient level: first bin, run of "greater than one" bins, sign
+      const uint32_t g = (e >> LVL_GCTX) & 0x1FF;
+      const int b1 = int((e >> LVL_BIT1) & 1);
+      U2 eg = cstate[g];                      // both contexts are loaded up front (they differ); the run keeps its
+      cabac.decision(t, b1, &cstate[e & 0x1FF]);   // context entry in registers and writes it back once
+      if (b1) {
+#pragma unroll 1
+        for (uint32_t r = (e >> LVL_RUN) & 15; r > 0; r--) cabac.encode_core(t, eg, 1, &eg);
+        if ((e >> LVL_TERM) & 1) cabac.encode_core(t, eg, 0, &eg);
+        cstate[g] = eg;
+      }
+      if ((e >> LVL_HAS_SIGN) & 1) cabac.bypass(int((e >> LVL_SIGN) & 1));
+      return;
+    }
+    const int bit = int((e >> SYM_BIT_SHIFT) & 1);
+    const uint32_t kind = e & (3u << SYM_KIND_SHIFT);
+    if (kind == SYM_DECISION) cabac.decision(t, bit, &cstate[e & 0xFFFF]);
+    else if (kind == SYM_BYPASS) cabac.bypass(bit);
+    else cabac.terminate(bit);
+  }
   AVR_DEV void run(Consumer& q, const SharedTables& t, uint16_t*, U2* cstate) {
     for (;;) {
       const uint32_t e = q.pop();
       if (e & SYM_END) break;
-      if (e & SYM_LEVEL) {   // one coefficient level: first bin, run of "greater than one" bins, sign
-        const uint32_t g = (e >> LVL_GCTX) & 0x1FF;
-        cabac.decision(t, int((e >> LVL_BIT1) & 1), &cstate[e & 0x1FF]);
+      entry(t, cstate, e);
+    }
+  }
+  // Wide slices: ring j (entries in global memory, far[j * far_cap ...]; indices in rings[j]) carries the
+  // macroblock rows j, j + K, ... and every row ends in SP_ROW_END.  ALL lanes of the warp call this: they
+  // fetch a batch of entries with one coalesced load, lane 0 encodes them one by one.  Leaves on the
+  // first SYM_END and then drains the other rings so that their parser warps can finish.
+  AVR_DEV void run_wide(RingShared* rings, uint32_t n_rings, const uint32_t* far, uint32_t far_cap, const SharedTables& t, U2* cstate,
+                        uint32_t* stage, int lane) {
+    // stage[0..31]: the batch; stage[32]: entries used; stage[33]: 0 go on, 1 row end, 2 SYM_END
+    uint32_t cur = 0, qpd = 0, head = 0;
+    bool draining = false;
+    for (;;) {
+      RingShared* r = &rings[cur];
+      uint32_t n;
+#if defined(__CUDACC__) && !defined(AVR_HOST_EMULATION)
+      uint32_t avail;
+      for (uint32_t polls = 0; (avail = *reinterpret_cast<volatile uint32_t*>(&r->tail_pub) - head) == 0;) wide_backoff(polls);
+      ring_fence();
+      n = avail < 32u ? avail : 32u;
+      const volatile uint32_t* src = far + size_t(cur) * far_cap;
+      if (uint32_t(lane) < n) stage[lane] = src[(head + uint32_t(lane)) & (far_cap - 1)];
+      __syncwarp();
+#else
+      (void)far; (void)far_cap;
+      n = 1;
+      stage[0] = head < r->e.size() ? r->e[head] : uint32_t(SYM_END);
+#endif
+      if (lane == 0) {   // the serial part: plain single-lane code, nothing warp-wide per entry (a warp-wide loop with
+        // lane 0 predicated per entry cost 2x: every entry paid for the divergence and reconvergence)
+        uint32_t used = 0, why = 0;
 #pragma unroll 1
-        for (uint32_t r = (e >> LVL_RUN) & 15; r > 0; r--) cabac.decision(t, 1, &cstate[g]);
-        if ((e >> LVL_TERM) & 1) cabac.decision(t, 0, &cstate[g]);
-        if ((e >> LVL_HAS_SIGN) & 1) cabac.bypass(int((e >> LVL_SIGN) & 1));
-        continue;
+        while (used < n) {
+          const uint32_t e = stage[used++];
+          if (e & SYM_END) { why = 2; break; }
+          if (draining) continue;
+          if (!(e & SYM_LEVEL) && (e & (3u << SYM_KIND_SHIFT)) == SYM_SPECIAL) {
+            if (e & SP_ROW_END) { qpd = e & 1; why = 1; break; }
+            cabac.decision(t, int((e >> SYM_BIT_SHIFT) & 1), &cstate[60 + qpd]);
+          } else entry(t, cstate, e);
+        }
+        stage[32] = used; stage[33] = why;
+#if defined(__CUDACC__) && !defined(AVR_HOST_EMULATION)
+        ring_fence();
+        *reinterpret_cast<volatile uint32_t*>(&r->head_pub) = head + used;
+#endif
       }
-      const int bit = int((e >> SYM_BIT_SHIFT) & 1);
-      const uint32_t kind = e & (3u << SYM_KIND_SHIFT);
-      if (kind == SYM_DECISION) cabac.decision(t, bit, &cstate[e & 0xFFFF]);
-      else if (kind == SYM_BYPASS) cabac.bypass(bit);
-      else cabac.terminate(bit);
+      AVR_SYNCWARP_CORE();
+      head += stage[32];
+      const uint32_t why = stage[33];
+      AVR_SYNCWARP_CORE();
+      if (why == 0) continue;
+      if (why == 2) { draining = true; r->cons_head = 0xFFFFFFFFu; }
+      else r->cons_head = head;
+      // next ring: the next row's, or (draining) the next one that has not delivered SYM_END yet
+      uint32_t tries = 0;
+      do { cur = cur + 1 == n_rings ? 0 : cur + 1; tries++; } while (draining && tries <= n_rings && rings[cur].cons_head == 0xFFFFFFFFu);
+      if (draining && tries > n_rings) break;
+      head = uint32_t(rings[cur].cons_head);
     }
   }
   AVR_DEV uint32_t out_bytes() const { return cabac.sink.n; }
@@ -615,7 +738,8 @@ struct Compress {
   CabacIn cabac;
   Producer q;
   U2* cstate;        // parser owns the CABAC context states
-  AVR_DEV void begin(const uint8_t* src, uint32_t n, uint8_t* window, uint32_t tail_byte, RingShared* ring, uint16_t*, U2* states) {
+  AVR_DEV void begin(const uint8_t* src, uint32_t n, uint8_t* window, uint32_t tail_byte, RingShared* ring, uint16_t*, U2* states,
+                     uint32_t* = nullptr, uint32_t = 0) {
     in.attach(src, n, window, tail_byte); q.init(ring); cstate = states;
   }
   AVR_DEV void start_bins(const SharedTables&) { cabac.init(in); }
@@ -651,6 +775,14 @@ struct Compress {
   AVR_DEV int lvl_run(const SharedTables& t, BinEntry& e, int ctx) { return bin_run(t, e, ctx); }
   AVR_DEV int lvl_sign(const SharedTables& t) { return bypass(t); }
   AVR_DEV void lvl_push(uint32_t) {}
+  // wide slices: first mb_qp_delta bin of a macroblock row -- decoded with its true context, modelled with
+  // the estimator of context 60 whatever the previous row ended on (the rows are decoded in parallel)
+  AVR_DEV int bin_row_qpd(const SharedTables& t, int true_ctx) {
+    const int b = cabac.decision(in, t, &cstate[true_ctx]);
+    q.push(uint32_t(CNT_CTX + 60) | uint32_t(b) << SYM_BIT_SHIFT);
+    return b;
+  }
+  AVR_DEV void row_end(int) {}
   AVR_DEV int bypass(const SharedTables&) { const int b = cabac.bypass(in); q.push(CNT_BYPASS | uint32_t(b) << SYM_BIT_SHIFT); return b; }
   AVR_DEV int terminate(const SharedTables&) { const int b = cabac.terminate(in); q.push(CNT_TERM | uint32_t(b) << SYM_BIT_SHIFT); return b; }
   AVR_DEV int sig_get(const SharedTables& t, int ctx) { return cabac.decision(in, t, &cstate[ctx]); }   // CABAC side only
@@ -668,8 +800,10 @@ struct Decompress {
   RangeDec rc;
   Producer q;
   uint16_t* cnt;     // parser owns the estimators
-  AVR_DEV void begin(const uint8_t* src, uint32_t n, uint8_t* window, uint32_t, RingShared* ring, uint16_t* counters, U2*) {
-    in.attach(src, n, window, 0); q.init(ring); cnt = counters;
+  AVR_DEV void begin(const uint8_t* src, uint32_t n, uint8_t* window, uint32_t, RingShared* ring, uint16_t* counters, U2*,
+                     uint32_t* far_entries = nullptr, uint32_t far_cap = 0) {
+    in.attach(src, n, window, 0); q.init(ring, far_entries, far_cap); cnt = counters;
+    byp_c = 0x0101;
   }
   // The bypass estimator codes every sign and escape bit: it is kept in registers together with its
   // reciprocal for the length of a slice (read at start_bins, written back by finish_bins).
@@ -694,6 +828,12 @@ struct Decompress {
     q.push(uint32_t(ctx) | uint32_t(b) << SYM_BIT_SHIFT | SYM_DECISION);
     return b;
   }
+  AVR_DEV int bin_row_qpd(const SharedTables& t, int) {   // see Compress::bin_row_qpd
+    const int b = coded(t, uint32_t(CNT_CTX + 60), 0x60);
+    q.push(uint32_t(b) << SYM_BIT_SHIFT | SYM_SPECIAL | SP_QPD);
+    return b;
+  }
+  AVR_DEV void row_end(int qpd_nonzero) { q.push(SYM_SPECIAL | SP_ROW_END | uint32_t(qpd_nonzero)); }
   AVR_DEV int bypass(const SharedTables& t) {
     uint32_t pos = byp_c & 0xFF, neg = byp_c >> 8;
     const int b = rc.get(in, byp_mg, pos);

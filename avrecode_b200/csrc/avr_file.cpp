@@ -41,6 +41,7 @@ bool get_varint(const uint8_t*& p, const uint8_t* e, uint64_t* v) {
 struct Block {   // Recoded.Block (recode.proto:9-18)
   bool has_size = false, has_literal = false, has_skip = false, has_cabac = false, has_parity = false, has_last = false;
   int64_t size = 0;
+  uint64_t streams = 0;   // field 7, chunked mode only: range-coder streams of a wide slice (avr_slice_desc.n_streams)
   bool skip = false, parity = false;
   const uint8_t* literal = nullptr; size_t literal_n = 0;
   const uint8_t* cabac = nullptr; size_t cabac_n = 0;
@@ -58,6 +59,7 @@ bool parse_block(const uint8_t* p, const uint8_t* e, Block* b) {
       if (field == 1) { b->size = int64_t(v); b->has_size = true; }
       else if (field == 3) { b->skip = v != 0; b->has_skip = true; }
       else if (field == 5) { b->parity = v != 0; b->has_parity = true; }
+      else if (field == 7) b->streams = v;
     } else if (wt == 2) {
       uint64_t n;
       if (!get_varint(p, e, &n) || n > uint64_t(e - p)) return false;
@@ -103,6 +105,21 @@ bool parse_container(const uint8_t* p, size_t n, std::vector<Block>* blocks, std
     else return false;
   }
   return true;
+}
+
+// Chunked mode: a slice whose payload is at least two of these becomes a wide slice, one stream per this many
+// bytes (AVR_WIDE_STREAM_BYTES overrides; 0 = never).  Long slices set the time of a batch -- see avr_job.cuh.
+uint32_t wide_stream_bytes() {
+  if (const char* e = getenv("AVR_WIDE_STREAM_BYTES")) return uint32_t(strtoul(e, nullptr, 10));
+  return 32768;
+}
+uint8_t streams_for(const avr_slice_desc& d, uint32_t per_stream) {
+  if (per_stream == 0 || d.mb_width < 1 || d.mb_width > 256) return 0;
+  uint32_t k = d.payload_size / per_stream;
+  const uint32_t rows = d.first_mb / d.mb_width < d.mb_height ? d.mb_height - d.first_mb / d.mb_width : 1;
+  if (k > rows) k = rows;
+  if (k > AVR_MAX_STREAMS) k = AVR_MAX_STREAMS;
+  return k >= 2 ? uint8_t(k) : uint8_t(0);
 }
 
 void emit_block(std::string& out, const std::string& body) {
@@ -158,13 +175,15 @@ static int compress_many(avr_ctx* ctx, const uint8_t* const* files, const uint64
     p.coded.assign(size_t(p.n_ents), 0);
     for (int i = 0; i < p.n_ents; i++) p.coded[i] = p.ents[i].recodable ? 1 : 0;
   }
+  const uint32_t per_stream = mode == AVR_MODE_SLICE ? wide_stream_bytes() : 0;
+  std::vector<avr_slice_desc> descs;
   std::vector<avr_slice_result> res;
   const uint8_t* out = nullptr;
   uint64_t out_bytes = 0;
   // In file mode the slices of a file share one model, so a slice the device rejects poisons everything
   // after it; drop it (it becomes skip_coded + literal, recode.cpp:1289-1296) and run again.
   for (int attempt = 0; attempt < 64; attempt++) {
-    std::vector<avr_slice_desc> descs;
+    descs.clear();
     for (Plan& p : plans) {
       p.map.clear();
       p.first = descs.size();
@@ -177,6 +196,7 @@ static int compress_many(avr_ctx* ctx, const uint8_t* const* files, const uint64
           d.in_off = 0; d.in_size = 0;
         }
         if (p.map.empty() || mode == AVR_MODE_SLICE) d.flags |= AVR_SLICE_NEW_MODEL;
+        d.n_streams = p.coded[i] ? streams_for(d, per_stream) : 0;
         descs.push_back(d);
         p.map.push_back(i);
       }
@@ -221,6 +241,7 @@ static int compress_many(avr_ctx* ctx, const uint8_t* const* files, const uint64
         put_len(body, 4, out + r->out_off, r->out_size);
         put_var(body, 5, d.payload_size & 1);
         if (d.payload_size > 1) put_len(body, 6, file + d.in_off + d.payload_size - 1, 1);
+        if (descs[p.first + k].n_streams >= 2) put_var(body, 7, descs[p.first + k].n_streams);
         prev = d.in_off + d.payload_size;
       } else {   // {size, skip_coded}: the bytes stay in the surrounding literal
         put_var(body, 1, d.payload_size);
@@ -310,6 +331,10 @@ static int decompress_many(avr_ctx* ctx, const uint8_t* const* recs, const uint6
       d.in_size = p.coded[i].is_cabac ? uint32_t(b.cabac_n) : 0;
       if (!p.coded[i].is_cabac) d.flags |= AVR_SLICE_SKIP;
       if (p.which.empty() || slice_mode) d.flags |= AVR_SLICE_NEW_MODEL;
+      if (b.streams) {
+        if (!slice_mode || !p.coded[i].is_cabac || b.streams < 2 || b.streams > AVR_MAX_STREAMS) { free(ents); return AVR_ERR_FORMAT; }
+        d.n_streams = uint8_t(b.streams);
+      }
       if (p.coded[i].is_cabac) in.append(reinterpret_cast<const char*>(b.cabac), b.cabac_n);
       descs.push_back(d);
       p.which.push_back(size_t(i));

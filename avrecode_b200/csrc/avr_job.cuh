@@ -121,20 +121,39 @@ struct FrameTags {
 };
 
 // ---- parser warp: lane 0 walks the slice, all 32 lanes keep its input window filled ---------------
+struct Lane {               // what one parser warp works with
+  const SharedTables* tab;
+  RingShared* ring;
+  uint8_t* window;
+  U2* cstate;
+  WalkShared* walk;
+  MbCtx* row;
+  uint16_t* cnt;
+  uint32_t* far;            // wide decompression: this warp's symbol ring in global memory (else null)
+  uint32_t far_cap;
+};
+
+// stream / total_mbs: wide decompression only (the caller has set wk.wide_k and what goes with it)
 template <class Dir>
-AVR_DEV void parser_role(const JobArgs& a, const JobMem& m, const avr_slice_desc& d, const SliceIO& io, int cur_frame, bool use_planes, int lane) {
-  Walker<Dir> wk;
-  wk.tab = &m.sh->tab;
-  wk.row = m.row;
-  wk.ws = &m.sh->walk;
+AVR_DEV void parser_begin(Walker<Dir>& wk, const Lane& ln, const uint8_t* src, uint32_t n, const avr_slice_desc& d,
+                          uint8_t* nnz_cur, const uint8_t* nnz_prev, bool use_planes, int lane, uint32_t stream, uint32_t total_mbs) {
+  wk.tab = ln.tab;
+  wk.row = ln.row;
+  wk.row_top = ln.row;
+  wk.ws = ln.walk;
   wk.use_planes = use_planes;
-  wk.nnz_cur = cur_frame ? m.nnz1 : m.nnz0; wk.nnz_prev = cur_frame ? m.nnz0 : m.nnz1;
-  wk.dir.begin(a.in_arena + io.in_off, io.in_size, m.sh->window, (d.flags & AVR_SLICE_STOP_BYTE) ? 0x80u : 0u, &m.sh->ring,
-               m.cnt, m.sh->cstate);
+  wk.nnz_cur = nnz_cur; wk.nnz_prev = nnz_prev;
+  wk.dir.begin(src, n, ln.window, (d.flags & AVR_SLICE_STOP_BYTE) ? 0x80u : 0u, ln.ring, ln.cnt, ln.cstate, ln.far, ln.far_cap);
   window_load_half(wk.dir.in, 0, lane);
   window_load_half(wk.dir.in, WIN_HALF, lane);
   AVR_SYNCWARP();
-  if (lane == 0) wk.start(d);
+  if (lane == 0) wk.start(d, stream, total_mbs);
+}
+
+// Runs until the slice (or this warp's share of a wide slice) is done.  Host emulation of a wide
+// decompression also returns when the walker has to wait for the row above (wk.blocked).
+template <class Dir>
+AVR_DEV void parser_run(Walker<Dir>& wk, int lane) {
   for (;;) {
     int done = 1;
     uint32_t in_pos = 0;
@@ -142,9 +161,10 @@ AVR_DEV void parser_role(const JobArgs& a, const JobMem& m, const avr_slice_desc
       const uint32_t limit = wk.dir.in.limit();
       while (!wk.done && wk.dir.in_pos() < limit) {
         wk.step();
+        if (wk.blocked) break;
         if (wk.dir.in.ran_past(wk.dir.in_pos())) { wk.fail(WALK_UNSUPPORTED); wk.done = true; }   // macroblock > window
       }
-      done = wk.done;
+      done = wk.done || wk.blocked;
       in_pos = wk.dir.in_pos();
     }
     done = AVR_BCAST(done);
@@ -158,17 +178,57 @@ AVR_DEV void parser_role(const JobArgs& a, const JobMem& m, const avr_slice_desc
     }
     AVR_SYNCWARP();
   }
+}
+
+AVR_DEV void ring_end_record(RingShared* r, int status, uint32_t mbs, uint32_t bins_lo, uint32_t bins_hi) {
+  r->end_status = uint32_t(status);
+  r->end_mbs = mbs;
+  r->end_bins_lo = bins_lo;
+  r->end_bins_hi = bins_hi;
+}
+
+template <class Dir>
+AVR_DEV void parser_end(Walker<Dir>& wk, int lane) {
   if (lane == 0) {
     wk.dir.finish_bins();
-    RingShared* r = &m.sh->ring;
-    r->end_status = uint32_t(wk.status);
-    r->end_mbs = wk.n_mbs;
-    r->end_bins_lo = wk.n_bins_lo;
-    r->end_bins_hi = wk.n_bins_hi;
+    if (wk.wide_k && Dir::kDecompress) {   // nobody may wait for this warp any more
+      if (wk.status != WALK_OK) *wk.abort_flag = 1;
+      ring_fence();
+      *wk.prog_mine = 0xFFFFFFFFu;
+    }
+    ring_end_record(wk.dir.q.r, wk.status, wk.n_mbs, wk.n_bins_lo, wk.n_bins_hi);
     wk.dir.q.push(SYM_END);
     wk.dir.q.publish();
+    if (wk.wide_k && !Dir::kDecompress) {
+      // Wide compression: every stream ends in a terminate bin, which flushes its range coder -- the
+      // slice's own end_of_slice bin in the stream of the last row, one extra bin in each of the others.
+      RingShared* first = wk.rings;
+      ring_end_record(first, wk.status, wk.n_mbs, wk.n_bins_lo, wk.n_bins_hi);
+#pragma unroll 1
+      for (uint32_t j = 0; j < wk.wide_k; j++) {
+        if (j == wk.cur_ring) continue;
+        wk.dir.q.switch_to(&wk.rings[j]);
+        if (wk.status == WALK_OK) wk.dir.q.push(CNT_TERM | 1u << SYM_BIT_SHIFT);
+        wk.dir.q.push(SYM_END);
+        wk.dir.q.publish();
+      }
+    }
   }
   AVR_SYNCWARP();
+}
+
+template <class Dir>
+AVR_DEV void parser_role(const JobArgs& a, const JobMem& m, const avr_slice_desc& d, const SliceIO& io, int cur_frame, bool use_planes, int lane) {
+  Walker<Dir> wk;
+  wk.wide_k = 0;
+  wk.top_copy = false;
+  Lane ln;
+  ln.tab = &m.sh->tab; ln.ring = &m.sh->ring; ln.window = m.sh->window; ln.cstate = m.sh->cstate;
+  ln.walk = &m.sh->walk; ln.row = m.row; ln.cnt = m.cnt; ln.far = nullptr; ln.far_cap = 0;
+  parser_begin<Dir>(wk, ln, a.in_arena + io.in_off, io.in_size, d, cur_frame ? m.nnz1 : m.nnz0, cur_frame ? m.nnz0 : m.nnz1,
+                    use_planes, lane, 0, 0);
+  parser_run<Dir>(wk, lane);
+  parser_end<Dir>(wk, lane);
 }
 
 // ---- coder warp: lane 0 drains the ring and owns the output bytes and the slice result -------------
@@ -264,6 +324,272 @@ AVR_DEV void run_job(const JobArgs& a, const JobDesc& job, const JobMem& m, int 
     AVR_SYNCBLOCK();
     if (m.sh->final_status != AVR_SLICE_OK) poisoned = true;
   }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Wide slices (container mode "avr-b200/slice" only; avr_slice_desc.n_streams = K >= 2).
+//
+// A slice that is much longer than the rest of its batch sets the time of the whole batch, because one
+// slice is one serial CABAC stream.  The CABAC side cannot be split, but OUR side of the format can: the
+// compressor writes macroblock row r into range-coder stream (r - first row) mod K, each stream with its
+// own estimators.  Decompression then runs K parser warps as a wavefront -- the contexts of a macroblock
+// need its left and top neighbours only, so row r at column x waits for row r - 1 to be through column
+// x -- and one warp re-encodes the CABAC stream from the K rings in row order.  The single piece of
+// state that crosses a row boundary in decoding order, "previous macroblock had a non-zero mb_qp_delta",
+// is resolved by the re-encoder (SP_QPD / SP_ROW_END) and left out of the model (context 60).
+//
+// Blob layout (Block.cabac of a wide slice): u32 macroblocks | K x u32 stream bytes | streams.
+// Block = 1 + WIDE_MAX warps.  compress: warp 0 parser, warps 1..K coders;  decompress: warp 0 CABAC
+// re-encoder, warps 1..K parsers.  Estimators: one set per stream, all in shared memory -- which is what
+// limits K to WIDE_MAX = 2 (2 x 96 KB); the neighbour rows and the long symbol rings are in the global workspace.
+// ------------------------------------------------------------------------------------------------
+#if defined(__CUDACC__) && !defined(AVR_HOST_EMULATION)
+#define AVR_WIDE_THREADS ((WIDE_MAX + 1) * 32)
+#else
+#define AVR_WIDE_THREADS 1
+#endif
+
+struct WideShared {
+  SharedTables tab;
+  RingShared ring[WIDE_MAX];
+  alignas(16) uint8_t window[WIDE_MAX][WIN_BYTES];
+  U2 cstate[N_CTX_PAD];
+  WalkShared walk[WIDE_MAX];
+  uint32_t prog[WIDE_MAX];       // decompress: wavefront progress of each parser warp
+  uint32_t abort_flag;
+  uint32_t out_size[WIDE_MAX];   // compress: bytes of each stream;  decompress: [0] = bytes of the slice
+  uint32_t overflow;
+  uint32_t job;
+  uint32_t stage[34];            // decompress: the re-encoder's current batch of entries (CoderDecompress::run_wide)
+};
+
+struct WideMem {
+  WideShared* sh;
+  MbCtx* rows;      // [WIDE_MAX][max_mbw] (compress uses one): shared memory when they fit beside the estimators, else
+  bool rows_global; //   the global workspace -- slower: every publication fence then waits for the row stores
+  uint16_t* cnt;    // [WIDE_MAX][MODEL_COUNTERS], shared memory
+  uint32_t* far;    // [WIDE_MAX][far_cap] symbol rings of a decompression, global workspace: a parser warp may run a
+  uint32_t far_cap; //   whole macroblock row ahead of the re-encoder, far more than a shared-memory ring holds
+  uint32_t max_mbw;
+};
+
+AVR_DEV uint32_t load_le32(const uint8_t* p) { return uint32_t(p[0]) | uint32_t(p[1]) << 8 | uint32_t(p[2]) << 16 | uint32_t(p[3]) << 24; }
+AVR_DEV void store_le32(uint8_t* p, uint32_t v) { p[0] = uint8_t(v); p[1] = uint8_t(v >> 8); p[2] = uint8_t(v >> 16); p[3] = uint8_t(v >> 24); }
+
+template <class Dir>
+AVR_DEV void wide_fail(const JobArgs& a, uint32_t s, const SliceIO& io, int status, int tid) {
+  if (tid == 0) {
+    avr_slice_result r;
+    r.out_off = io.out_off; r.out_size = 0; r.n_mbs = 0; r.reserved = 0; r.n_bins = 0; r.status = status;
+    a.results[s] = r;
+  }
+  AVR_SYNCBLOCK();
+}
+
+template <class Dir>
+AVR_DEV void wide_lane(Lane& ln, const WideMem& m, uint32_t j, uint32_t mbw) {
+  WideShared* sh = m.sh;
+  ln.tab = &sh->tab; ln.ring = &sh->ring[j]; ln.window = sh->window[j]; ln.cstate = sh->cstate;
+  ln.walk = &sh->walk[j]; ln.row = m.rows + size_t(j) * mbw; ln.cnt = m.cnt + size_t(j) * MODEL_COUNTERS;
+  ln.far = Dir::kDecompress ? m.far + size_t(j) * m.far_cap : nullptr;
+  ln.far_cap = Dir::kDecompress ? m.far_cap : 0;
+}
+
+template <class Dir>
+AVR_DEV void wide_walker(Walker<Dir>& wk, const WideMem& m, uint32_t K, uint32_t j) {
+  WideShared* sh = m.sh;
+  wk.wide_k = K;
+  wk.top_copy = m.rows_global;
+  wk.rings = sh->ring;
+  wk.rows_base = m.rows;
+  wk.prog_mine = &sh->prog[j];
+  wk.prog_above = &sh->prog[j == 0 ? K - 1 : j - 1];
+  wk.abort_flag = &sh->abort_flag;
+}
+
+template <class Dir>
+AVR_DEV void run_wide_job(const JobArgs& a, uint32_t s, const WideMem& m, int tid) {
+  const int nthreads = AVR_WIDE_THREADS;
+  const int lane = tid & (AVR_LANES - 1);
+  WideShared* sh = m.sh;
+  const avr_slice_desc d = a.descs[s];
+  const SliceIO io = a.ios[s];
+  const uint32_t K = d.n_streams;
+  const uint32_t mbw = d.mb_width;
+  const uint32_t hdr = 4 + 4 * K;
+  if (K < 2 || K > WIDE_MAX || mbw < 1 || d.mb_height < 1 || mbw > m.max_mbw) { wide_fail<Dir>(a, s, io, AVR_SLICE_UNSUPPORTED, tid); return; }
+  const uint8_t* blob = a.in_arena + io.in_off;
+  uint8_t* out = a.out_arena + io.out_off;
+  uint32_t total_mbs = 0;
+  uint32_t subcap = 0;
+  if (Dir::kDecompress) {
+    bool ok = io.in_size >= hdr;
+    uint64_t sum = hdr;
+    if (ok) {
+      total_mbs = load_le32(blob);
+      for (uint32_t j = 0; j < K; j++) sum += load_le32(blob + 4 + 4 * j);
+      const uint32_t mbs_left = uint32_t(d.mb_width) * d.mb_height - (d.first_mb < uint32_t(d.mb_width) * d.mb_height ? d.first_mb : 0);
+      ok = sum == io.in_size && total_mbs >= 1 && total_mbs <= mbs_left && d.first_mb < uint32_t(d.mb_width) * d.mb_height;
+    }
+    if (!ok) { wide_fail<Dir>(a, s, io, AVR_SLICE_CORRUPT, tid); return; }
+  } else {
+    if (io.out_cap < hdr + 64 * K) { wide_fail<Dir>(a, s, io, AVR_SLICE_OVERFLOW, tid); return; }
+    subcap = ((io.out_cap - hdr) / K) & ~15u;
+  }
+  init_contexts(sh->cstate, d, tid, nthreads);
+  fill_u32(reinterpret_cast<uint32_t*>(m.rows), (Dir::kDecompress ? K : 1u) * mbw * MBCTX_WORDS, 0, tid, nthreads);   // compress walks in place: one row
+  fill_u32(reinterpret_cast<uint32_t*>(m.cnt), K * (MODEL_COUNTERS / 2), 0x01010101u, tid, nthreads);
+  for (uint32_t j = uint32_t(tid); j < K; j += uint32_t(nthreads)) { ring_reset(&sh->ring[j]); sh->prog[j] = d.first_mb; sh->out_size[j] = 0; }
+  if (tid == 0) { sh->abort_flag = 0; sh->overflow = 0; }
+  AVR_SYNCBLOCK();
+
+#if defined(__CUDACC__) && !defined(AVR_HOST_EMULATION)
+  const uint32_t warp = uint32_t(tid) >> 5;
+  if constexpr (!Dir::kDecompress) {
+    if (warp == 0) {
+      Walker<Dir> wk;
+      wide_walker<Dir>(wk, m, K, 0);
+      Lane ln;
+      wide_lane<Dir>(ln, m, 0, mbw);
+      parser_begin<Dir>(wk, ln, blob, io.in_size, d, nullptr, nullptr, false, lane, 0, 0);
+      parser_run<Dir>(wk, lane);
+      parser_end<Dir>(wk, lane);
+    } else if (warp <= K) {
+      const uint32_t j = warp - 1;
+      if (lane == 0) {
+        typename Dir::Coder c;
+        c.begin(out + hdr + size_t(j) * subcap, subcap);
+        Consumer q;
+        q.init(&sh->ring[j], false);
+        c.run(q, sh->tab, m.cnt + size_t(j) * MODEL_COUNTERS, sh->cstate);
+        sh->out_size[j] = c.out_bytes();
+        if (c.overflowed()) sh->overflow = 1;
+      }
+      AVR_SYNCWARP();   // the other lanes must not run ahead into the block barrier
+    }
+  } else {
+    if (warp == 0) {
+      typename Dir::Coder c;
+      c.begin(out, io.out_cap);
+      c.run_wide(sh->ring, K, m.far, m.far_cap, sh->tab, sh->cstate, sh->stage, lane);
+      if (lane == 0) {
+        sh->out_size[0] = c.out_bytes();
+        if (c.overflowed()) sh->overflow = 1;
+      }
+      AVR_SYNCWARP();
+    } else if (warp <= K) {
+      const uint32_t j = warp - 1;
+      Walker<Dir> wk;
+      wide_walker<Dir>(wk, m, K, j);
+      Lane ln;
+      wide_lane<Dir>(ln, m, j, mbw);
+      uint32_t off = hdr;
+      for (uint32_t i = 0; i < j; i++) off += load_le32(blob + 4 + 4 * i);
+      parser_begin<Dir>(wk, ln, blob + off, load_le32(blob + 4 + 4 * j), d, nullptr, nullptr, false, lane, j, total_mbs);
+      parser_run<Dir>(wk, lane);
+      parser_end<Dir>(wk, lane);
+    }
+  }
+#else
+  if constexpr (!Dir::kDecompress) {
+    Walker<Dir> wk;
+    wide_walker<Dir>(wk, m, K, 0);
+    Lane ln;
+    wide_lane<Dir>(ln, m, 0, mbw);
+    parser_begin<Dir>(wk, ln, blob, io.in_size, d, nullptr, nullptr, false, lane, 0, 0);
+    parser_run<Dir>(wk, lane);
+    parser_end<Dir>(wk, lane);
+    for (uint32_t j = 0; j < K; j++) {
+      typename Dir::Coder c;
+      c.begin(out + hdr + size_t(j) * subcap, subcap);
+      Consumer q;
+      q.init(&sh->ring[j]);
+      c.run(q, sh->tab, m.cnt + size_t(j) * MODEL_COUNTERS, sh->cstate);
+      sh->out_size[j] = c.out_bytes();
+      if (c.overflowed()) sh->overflow = 1;
+    }
+  } else {
+    Walker<Dir>* wk = new Walker<Dir>[WIDE_MAX];
+    uint32_t off = hdr;
+    for (uint32_t j = 0; j < K; j++) {
+      wide_walker<Dir>(wk[j], m, K, j);
+      Lane ln;
+      wide_lane<Dir>(ln, m, j, mbw);
+      const uint32_t sz = load_le32(blob + 4 + 4 * j);
+      parser_begin<Dir>(wk[j], ln, blob + off, sz, d, nullptr, nullptr, false, lane, j, total_mbs);
+      off += sz;
+    }
+    for (bool busy = true; busy;) {   // round robin: a walker runs until it has to wait for the row above
+      busy = false;
+      for (uint32_t j = 0; j < K; j++)
+        if (!wk[j].done) { parser_run<Dir>(wk[j], lane); busy = true; }
+    }
+    for (uint32_t j = 0; j < K; j++) parser_end<Dir>(wk[j], lane);
+    delete[] wk;
+    typename Dir::Coder c;
+    c.begin(out, io.out_cap);
+    c.run_wide(sh->ring, K, m.far, m.far_cap, sh->tab, sh->cstate, sh->stage, lane);
+    sh->out_size[0] = c.out_bytes();
+    if (c.overflowed()) sh->overflow = 1;
+  }
+#endif
+  AVR_SYNCBLOCK();
+
+  // result (and, compressing, the blob: header + the K streams moved up against each other)
+  int status;
+  uint32_t mbs = 0, out_size = 0;
+  uint64_t bins = 0;
+  if (!Dir::kDecompress) {
+    const volatile RingShared* r = &sh->ring[0];
+    status = int(r->end_status);
+    mbs = r->end_mbs;
+    bins = uint64_t(r->end_bins_lo) | uint64_t(r->end_bins_hi) << 32;
+    if (status == AVR_SLICE_OK && sh->overflow) status = AVR_SLICE_OVERFLOW;
+    if (status == AVR_SLICE_OK) {
+      uint32_t dst = hdr + sh->out_size[0];
+#pragma unroll 1
+      for (uint32_t j = 1; j < K; j++) {
+        const uint8_t* src = out + hdr + size_t(j) * subcap;
+        const uint32_t n = sh->out_size[j];
+#pragma unroll 1
+        for (uint32_t o = 0; o < n; o += uint32_t(nthreads)) {   // dst <= src: chunk by chunk, read before write
+          const uint32_t i = o + uint32_t(tid);
+          const uint8_t v = i < n ? src[i] : uint8_t(0);
+          AVR_SYNCBLOCK();
+          if (i < n) out[dst + i] = v;
+          AVR_SYNCBLOCK();
+        }
+        dst += n;
+      }
+      out_size = dst;
+      if (tid == 0) {
+        store_le32(out, mbs);
+        for (uint32_t j = 0; j < K; j++) store_le32(out + 4 + 4 * j, sh->out_size[j]);
+      }
+    }
+  } else {
+    status = AVR_SLICE_OK;
+    for (uint32_t j = 0; j < K; j++) {
+      const volatile RingShared* r = &sh->ring[j];
+      if (status == AVR_SLICE_OK && r->end_status != AVR_SLICE_OK) status = int(r->end_status);
+      mbs += r->end_mbs;
+      bins += uint64_t(r->end_bins_lo) | uint64_t(r->end_bins_hi) << 32;
+    }
+    if (status == AVR_SLICE_OK && mbs != total_mbs) status = AVR_SLICE_CORRUPT;
+    if (status == AVR_SLICE_OK && sh->overflow) status = AVR_SLICE_OVERFLOW;
+    out_size = sh->out_size[0];
+  }
+  if (tid == 0) {
+    avr_slice_result res;
+    res.out_off = io.out_off;
+    res.status = status;
+    res.out_size = status == AVR_SLICE_OK ? out_size : 0;
+    res.n_mbs = mbs;
+    res.reserved = 0;
+    res.n_bins = bins;
+    a.results[s] = res;
+  }
+  AVR_SYNCBLOCK();
 }
 
 }  // namespace avr

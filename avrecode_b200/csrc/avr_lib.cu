@@ -63,6 +63,50 @@ __global__ void __launch_bounds__(AVR_THREADS, RESIDENT ? 2 : 8) avr_job_kernel(
   }
 }
 
+// Wide slices (avr_job.cuh, run_wide_job): one slice per block of 1 + WIDE_MAX warps.
+// Shared memory: WideShared | WIDE_MAX estimator sets.  Workspace slot: MbCtx rows[WIDE_MAX][max_mbw] |
+// WIDE_MAX symbol rings of far_cap entries (decompression).
+struct WideKernelArgs {
+  JobArgs a;
+  const uint32_t* slices;   // the wide slices of the batch, longest first
+  uint32_t n_jobs;
+  uint32_t* counter;
+  uint8_t* workspace;
+  uint64_t work_stride;
+  uint32_t max_mbw;
+  uint32_t far_cap;
+  uint32_t rows_in_shared;  // the neighbour rows follow the estimators in shared memory (else: start of the workspace slot)
+};
+enum : uint32_t { WIDE_FAR_CAP = 1u << 16 };
+size_t wide_rows_bytes(uint32_t max_mbw) { return align_up(size_t(WIDE_MAX) * max_mbw * sizeof(MbCtx), 256); }
+size_t wide_smem_bytes() { return align_up(sizeof(WideShared), 16) + align_up(size_t(WIDE_MAX) * MODEL_COUNTERS * 2, 16); }
+
+template <class Dir>
+__global__ void __launch_bounds__(AVR_WIDE_THREADS, 1) avr_wide_kernel(WideKernelArgs k) {
+  extern __shared__ __align__(16) uint8_t smem[];
+  WideMem m;
+  m.sh = reinterpret_cast<WideShared*>(smem);
+  m.cnt = reinterpret_cast<uint16_t*>(smem + (sizeof(WideShared) + 15) / 16 * 16);
+  uint8_t* slot = k.workspace + uint64_t(blockIdx.x) * k.work_stride;
+  m.rows = k.rows_in_shared ? reinterpret_cast<MbCtx*>(smem + (sizeof(WideShared) + 15) / 16 * 16 + (size_t(WIDE_MAX) * MODEL_COUNTERS * 2 + 15) / 16 * 16)
+                            : reinterpret_cast<MbCtx*>(slot);
+  m.rows_global = !k.rows_in_shared;
+  m.far = reinterpret_cast<uint32_t*>(slot + (size_t(WIDE_MAX) * k.max_mbw * sizeof(MbCtx) + 255) / 256 * 256);
+  m.far_cap = k.far_cap;
+  m.max_mbw = k.max_mbw;
+  const int tid = threadIdx.x;
+  fill_shared_tables(&m.sh->tab, tid, AVR_WIDE_THREADS);
+  __syncthreads();
+  for (;;) {
+    if (tid == 0) m.sh->job = atomicAdd(k.counter, 1u);
+    __syncthreads();
+    const uint32_t j = m.sh->job;
+    __syncthreads();
+    if (j >= k.n_jobs) break;
+    run_wide_job<Dir>(k.a, k.slices[j], m, tid);
+  }
+}
+
 __global__ void avr_fill_kernel(uint4* p, size_t n, uint32_t v) {
   size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x;
   size_t stride = size_t(gridDim.x) * blockDim.x;
@@ -77,11 +121,13 @@ struct avr_ctx {
   int sm_count = 0;
   int max_smem_optin = 0;
   cudaStream_t stream = nullptr;
-  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  cudaStream_t stream_wide = nullptr;   // the wide-slice kernel runs beside the ordinary one
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_fork = nullptr, ev_join = nullptr;
   // device buffers, grown on demand
   uint8_t* d_in = nullptr; size_t d_in_cap = 0;
   uint8_t* d_out = nullptr; size_t d_out_cap = 0;
   uint8_t* d_work = nullptr; size_t d_work_cap = 0;
+  uint8_t* d_wide = nullptr; size_t d_wide_cap = 0;   // workspace of the wide-slice kernel
   uint8_t* d_meta = nullptr; size_t d_meta_cap = 0;   // descs | ios | jobs | results | counter
   uint8_t* d_flush = nullptr; size_t flush_bytes = 0;
   // pinned host buffers
@@ -94,6 +140,11 @@ struct avr_ctx {
   std::vector<avr_slice_desc> descs;
   std::vector<SliceIO> ios[2];       // per direction
   std::vector<JobDesc> jobs;
+  std::vector<uint32_t> wide;        // slices with n_streams >= 2, longest first
+  int grid_wide = 0;
+  uint32_t max_mbw_wide = 1;
+  uint64_t wide_stride = 0;
+  size_t off_wide = 0;
   uint64_t out_total[2] = {0, 0};
   size_t in_bytes = 0;
   uint32_t max_mbw = 1, max_frame_bytes = 0;
@@ -175,6 +226,9 @@ int avr_create(const avr_config* cfg, avr_ctx** out) {
   c->max_smem_sm = int(prop.sharedMemPerMultiprocessor);
   if (const char* e = getenv("AVR_RESIDENT")) c->force_resident = atoi(e) ? 1 : 0;
   if (!ck(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking), "cudaStreamCreate") ||
+      !ck(cudaStreamCreateWithFlags(&c->stream_wide, cudaStreamNonBlocking), "cudaStreamCreate") ||
+      !ck(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming), "cudaEventCreate") ||
+      !ck(cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming), "cudaEventCreate") ||
       !ck(cudaEventCreate(&c->ev0), "cudaEventCreate") || !ck(cudaEventCreate(&c->ev1), "cudaEventCreate")) {
     avr_destroy(c);
     return AVR_ERR_CUDA;
@@ -190,6 +244,10 @@ void avr_destroy(avr_ctx* c) {
   if (c->d_in) cudaFree(c->d_in);
   if (c->d_out) cudaFree(c->d_out);
   if (c->d_work) cudaFree(c->d_work);
+  if (c->d_wide) cudaFree(c->d_wide);
+  if (c->stream_wide) { cudaStreamSynchronize(c->stream_wide); cudaStreamDestroy(c->stream_wide); }
+  if (c->ev_fork) cudaEventDestroy(c->ev_fork);
+  if (c->ev_join) cudaEventDestroy(c->ev_join);
   if (c->d_meta) cudaFree(c->d_meta);
   if (c->d_flush) cudaFree(c->d_flush);
   if (c->h_out) cudaFreeHost(c->h_out);
@@ -215,7 +273,8 @@ int avr_stage(avr_ctx* c, const avr_slice_desc* descs, int n, const uint8_t* in,
   c->n_slices = n; c->in_bytes = size_t(in_bytes);
   c->descs.assign(descs, descs + n);
   c->jobs.clear();
-  c->max_mbw = 1; c->max_frame_bytes = 0;
+  c->wide.clear();
+  c->max_mbw = 1; c->max_frame_bytes = 0; c->max_mbw_wide = 1;
   for (int dir = 0; dir < 2; dir++) { c->ios[dir].resize(n); c->out_total[dir] = 0; }
   for (int i = 0; i < n; i++) {
     const avr_slice_desc& d = descs[i];
@@ -225,7 +284,17 @@ int avr_stage(avr_ctx* c, const avr_slice_desc* descs, int n, const uint8_t* in,
       io.in_off = d.in_off; io.in_size = d.in_size;
       io.out_off = c->out_total[dir];
       io.out_cap = dir == 0 ? d.in_size + d.in_size / 8 + 256 : d.payload_size + 64;
+      // wide slice: header + n_streams slots, any one of which may end up with (nearly) all of the slice
+      if (dir == 0 && d.n_streams >= 2) io.out_cap = 64 + d.n_streams * uint32_t(align_up(size_t(d.in_size) + d.in_size / 8 + 512, 16));
       c->out_total[dir] += align_up(io.out_cap, 16);
+    }
+    if (d.n_streams >= 2) {
+      // a wide slice is a chunk of its own (its K streams have K models of their own)
+      const bool own_model = (i == 0 || (d.flags & AVR_SLICE_NEW_MODEL)) && (i + 1 == n || (descs[i + 1].flags & AVR_SLICE_NEW_MODEL));
+      if (d.n_streams > AVR_MAX_STREAMS || !own_model || (d.flags & AVR_SLICE_SKIP)) return AVR_ERR_ARG;
+      c->wide.push_back(uint32_t(i));
+      c->max_mbw_wide = std::max<uint32_t>(c->max_mbw_wide, d.mb_width);
+      continue;
     }
     c->max_mbw = std::max<uint32_t>(c->max_mbw, d.mb_width);
     c->max_frame_bytes = std::max<uint32_t>(c->max_frame_bytes, uint32_t(d.mb_width) * d.mb_height * NNZ_STRIDE);
@@ -240,6 +309,13 @@ int avr_stage(avr_ctx* c, const avr_slice_desc* descs, int n, const uint8_t* in,
   // longest jobs first (LPT order for the dynamic hand-out)
   std::stable_sort(c->jobs.begin(), c->jobs.end(), [](const JobDesc& a, const JobDesc& b) { return a.weight > b.weight; });
   c->n_jobs = int(c->jobs.size());
+  std::stable_sort(c->wide.begin(), c->wide.end(), [&](uint32_t a, uint32_t b) { return descs[a].in_size > descs[b].in_size; });
+  c->grid_wide = 0;
+  if (!c->wide.empty()) {
+    if (wide_smem_bytes() > size_t(c->max_smem_optin)) return AVR_ERR_ARG;
+    c->grid_wide = std::min<int>(int(c->wide.size()), c->sm_count);   // one block fills an SM's shared memory
+    c->wide_stride = align_up(wide_rows_bytes(c->max_mbw_wide) + size_t(WIDE_MAX) * WIDE_FAR_CAP * 4, 256);
+  }
   c->max_frame_bytes = uint32_t(align_up(c->max_frame_bytes, 16));
 
   // Placement of the estimators: in shared memory (<= 2 blocks per SM, every per-bin access at LDS
@@ -269,10 +345,12 @@ int avr_stage(avr_ctx* c, const avr_slice_desc* descs, int n, const uint8_t* in,
   if ((rc = grow_dev(&c->d_in, &c->d_in_cap, size_t(in_bytes) + 64))) return rc;
   if ((rc = grow_dev(&c->d_out, &c->d_out_cap, size_t(std::max(c->out_total[0], c->out_total[1])) + 64))) return rc;
   if ((rc = grow_dev(&c->d_work, &c->d_work_cap, size_t(work_stride) * c->grid + 256))) return rc;
+  if (c->grid_wide && (rc = grow_dev(&c->d_wide, &c->d_wide_cap, size_t(c->wide_stride) * c->grid_wide + 256))) return rc;
   c->off_descs = 0;
   c->off_ios = align_up(c->off_descs + sizeof(avr_slice_desc) * n, 256);
   c->off_jobs = align_up(c->off_ios + 2 * sizeof(SliceIO) * n, 256);
-  c->off_res = align_up(c->off_jobs + sizeof(JobDesc) * c->jobs.size(), 256);
+  c->off_wide = align_up(c->off_jobs + sizeof(JobDesc) * c->jobs.size(), 256);
+  c->off_res = align_up(c->off_wide + sizeof(uint32_t) * c->wide.size(), 256);
   c->off_counter = align_up(c->off_res + sizeof(avr_slice_result) * n, 256);
   size_t meta_bytes = c->off_counter + 256;
   if ((rc = grow_dev(&c->d_meta, &c->d_meta_cap, meta_bytes))) return rc;
@@ -282,6 +360,7 @@ int avr_stage(avr_ctx* c, const avr_slice_desc* descs, int n, const uint8_t* in,
     memcpy(c->h_meta + c->off_ios, c->ios[0].data(), sizeof(SliceIO) * n);
     memcpy(c->h_meta + c->off_ios + sizeof(SliceIO) * n, c->ios[1].data(), sizeof(SliceIO) * n);
     memcpy(c->h_meta + c->off_jobs, c->jobs.data(), sizeof(JobDesc) * c->jobs.size());
+    memcpy(c->h_meta + c->off_wide, c->wide.data(), sizeof(uint32_t) * c->wide.size());
     CK(cudaMemcpyAsync(c->d_meta, c->h_meta, c->off_res, cudaMemcpyHostToDevice, c->stream));
     CK(cudaMemcpyAsync(c->d_in, in, size_t(in_bytes), cudaMemcpyHostToDevice, c->stream));
   }
@@ -312,19 +391,50 @@ int avr_launch(avr_ctx* c, int direction) {
   k.max_mbw = c->max_mbw;
   const size_t smem = smem_bytes(c->max_mbw, c->resident);
   if (int(smem) > c->max_smem_optin) return AVR_ERR_ARG;
-  CK(cudaMemsetAsync(k.counter, 0, sizeof(uint32_t), c->stream));
+  CK(cudaMemsetAsync(k.counter, 0, 2 * sizeof(uint32_t), c->stream));
   CK(cudaEventRecord(c->ev0, c->stream));
+  if (c->grid_wide > 0) {   // the longest slices first, on their own stream, so that they start at once
+    WideKernelArgs w;
+    w.a = k.a;
+    w.slices = reinterpret_cast<const uint32_t*>(c->d_meta + c->off_wide);
+    w.n_jobs = uint32_t(c->wide.size());
+    w.counter = k.counter + 1;
+    w.workspace = c->d_wide;
+    w.work_stride = c->wide_stride;
+    w.max_mbw = c->max_mbw_wide;
+    w.far_cap = WIDE_FAR_CAP;
+    // neighbour rows: one (compress) or WIDE_MAX (decompress), in shared memory when they fit
+    size_t wsmem = wide_smem_bytes();
+    const size_t rows_bytes = size_t(direction == 0 ? 1 : WIDE_MAX) * c->max_mbw_wide * sizeof(MbCtx);
+    w.rows_in_shared = wsmem + rows_bytes + 1024 <= size_t(c->max_smem_optin) ? 1u : 0u;
+    if (w.rows_in_shared) wsmem += rows_bytes;
+    CK(cudaEventRecord(c->ev_fork, c->stream));
+    CK(cudaStreamWaitEvent(c->stream_wide, c->ev_fork, 0));
+    if (direction == 0) {
+      CK(cudaFuncSetAttribute(avr_wide_kernel<Compress>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(wsmem)));
+      avr_wide_kernel<Compress><<<c->grid_wide, AVR_WIDE_THREADS, wsmem, c->stream_wide>>>(w);
+    } else {
+      CK(cudaFuncSetAttribute(avr_wide_kernel<Decompress>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(wsmem)));
+      avr_wide_kernel<Decompress><<<c->grid_wide, AVR_WIDE_THREADS, wsmem, c->stream_wide>>>(w);
+    }
+    CK(cudaGetLastError());
+    CK(cudaEventRecord(c->ev_join, c->stream_wide));
+    c->launches++;
+  }
 #define AVR_LAUNCH(DIR, RES)                                                                                              \
   do {                                                                                                                    \
     CK(cudaFuncSetAttribute(avr_job_kernel<DIR, RES>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));          \
     avr_job_kernel<DIR, RES><<<c->grid, AVR_THREADS, smem, c->stream>>>(k);                                               \
   } while (0)
-  if (direction == 0) { if (c->resident) AVR_LAUNCH(Compress, true); else AVR_LAUNCH(Compress, false); }
-  else { if (c->resident) AVR_LAUNCH(Decompress, true); else AVR_LAUNCH(Decompress, false); }
+  if (c->n_jobs > 0) {
+    if (direction == 0) { if (c->resident) AVR_LAUNCH(Compress, true); else AVR_LAUNCH(Compress, false); }
+    else { if (c->resident) AVR_LAUNCH(Decompress, true); else AVR_LAUNCH(Decompress, false); }
+    c->launches++;
+  }
 #undef AVR_LAUNCH
   CK(cudaGetLastError());
+  if (c->grid_wide > 0) CK(cudaStreamWaitEvent(c->stream, c->ev_join, 0));
   CK(cudaEventRecord(c->ev1, c->stream));
-  c->launches++;
   return AVR_OK;
 }
 

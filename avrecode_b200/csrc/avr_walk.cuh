@@ -51,6 +51,7 @@ enum : uint16_t {
 
 struct alignas(8) WalkShared {     // per-block scratch of the walker (shared memory on the device)
   MbCtx left;           // the previous macroblock
+  MbCtx top;            // wide slices: copy of the macroblock above (their rows are in global memory)
   uint8_t mvd[2][16][2];  // |mvd| of the macroblock being walked, [list][4x4 block index][x, y]
   uint8_t nnz_mb[52];   // avrecode model: stored nnz of the macroblock being walked, by block index
 };
@@ -86,6 +87,21 @@ struct Walker {
   Dir dir;
   const SharedTables* tab;
   MbCtx* row;            // [mb_width] most recent macroblock of every column (shared memory)
+  const MbCtx* top_mb;   // the macroblock above the current one (row_top[mb_x], or its copy in ws->top)
+  MbCtx* row_top;        // the row above: the same array, except in a wide decompression (one buffer per parser warp)
+  // Wide slices: one slice over K range-coder streams, macroblock row r in stream (r - first row) mod K, so that
+  // K parser warps can decompress it as a wavefront -- row r at column x needs row r - 1 through column x only.
+  uint32_t wide_k;       // 0: ordinary slice
+  bool top_copy;         // the rows are in global memory, not in shared memory
+  RingShared* rings;     // compress: the K rings (one coder warp each); cur_ring = ring of the current row
+  uint32_t cur_ring;
+  MbCtx* rows_base;      // decompress: K row buffers, row r in buffer r mod K
+  int first_row, last_row;
+  volatile uint32_t* prog_mine;          // decompress: macroblocks of the picture (raster order) this warp has got past
+  const volatile uint32_t* prog_above;   // ... and the warp that decodes the row above
+  volatile uint32_t* abort_flag;
+  uint32_t above_seen;
+  bool blocked;          // host emulation only: the row above is not far enough yet
   WalkShared* ws;
   uint8_t* nnz_cur;      // FrameBuffer meta.num_nonzeros of the current picture, [mb][NNZ_STRIDE] (recode.cpp:624, 824-843)
   const uint8_t* nnz_prev;  // ... of the previous picture
@@ -132,7 +148,7 @@ struct Walker {
       const int mbi = where == 0 ? mb_xy : (where == 1 ? mb_xy - 1 : mb_xy - mbw);
       *value = nnz_cur[size_t(mbi) * NNZ_STRIDE + nb];
     } else if (where == 0) *value = ws->nnz_mb[nb];
-    else *value = (where == 1 ? ws->left.nnz : row[mb_x].nnz)[k_nnz_slot[nb]];
+    else *value = (where == 1 ? ws->left.nnz : top_mb->nnz)[k_nnz_slot[nb]];
     return true;
   }
   // codes (compress) or reads (decompress) the block's nnz; returns the value the compressor stores
@@ -313,7 +329,7 @@ struct Walker {
     if (x > 0) a = ws->mvd[list][blk_at(x - 1, y)][comp];
     else if (left_ok && (left_flags & uses)) a = list ? ws->left.mvd1_right[y][comp] : ws->left.mvd_right[y][comp];
     if (y > 0) b = ws->mvd[list][blk_at(x, y - 1)][comp];
-    else if (top_ok && (top_flags & uses)) b = list ? row[mb_x].mvd1_bottom[x][comp] : row[mb_x].mvd_bottom[x][comp];
+    else if (top_ok && (top_flags & uses)) b = list ? top_mb->mvd1_bottom[x][comp] : top_mb->mvd_bottom[x][comp];
     return a + b;
   }
   AVR_DEV int mvd_component(int ctxbase, int amvd) {   // h264_cabac.c:1502-1537; returns stored |mvd|
@@ -400,7 +416,14 @@ struct Walker {
     top_ok = mb_y > 0 && mb_xy - mbw >= int(first_mb);
     {   // neighbour facts into registers
       const MbCtx* l = &ws->left;
-      const MbCtx* t = &row[mb_x];
+      if (top_copy) {   // rows in global memory (a wide slice of a very wide picture): one burst into shared memory per macroblock
+        const uint32_t* g = reinterpret_cast<const uint32_t*>(&row_top[mb_x]);
+        uint32_t w[MBCTX_WORDS];
+        for (int i = 0; i < MBCTX_WORDS; i++) w[i] = g[i];
+        for (int i = 0; i < MBCTX_WORDS; i++) reinterpret_cast<uint32_t*>(&ws->top)[i] = w[i];
+        top_mb = &ws->top;
+      } else top_mb = &row_top[mb_x];
+      const MbCtx* t = top_mb;
       left_flags = l->flags; left_cbp = l->cbp; left_nzr = l->nz_right; left_refpos = l->ref_pos; left_dir8 = l->dir8;
       top_flags = t->flags; top_cbp = t->cbp; top_nzb = t->nz_bottom; top_refpos = t->ref_pos; top_dir8 = t->dir8;
     }
@@ -591,7 +614,12 @@ struct Walker {
 
     if (cbp || i16) {
       // mb_qp_delta (h264_cabac.c:2388-2416)
-      if (bin(60 + (last_qp_delta != 0))) {
+      // first bin: in a wide slice the first macroblock of a row cannot see how the previous row ended
+      const int qctx = 60 + (last_qp_delta != 0);
+      int q1;
+      if (wide_k && mb_x == 0) { count_bin(); q1 = dir.bin_row_qpd(*tab, qctx); }
+      else q1 = bin(qctx);
+      if (q1) {
         int val = 1, ctx = 2;
 #pragma unroll 1
         while (bin(60 + ctx)) { ctx = 3; val++; if (val > 102) { fail(WALK_CORRUPT); break; } }
@@ -667,7 +695,30 @@ struct Walker {
   }
 
   // ---- slice loop (h264_slice.c:2366-2443) -------------------------------------------------------
-  AVR_DEV void start(const avr_slice_desc& d) {
+  // wide decompression: may macroblock (mb_x, mb_y) start, i.e. is the row above done through column mb_x?
+  AVR_DEV bool top_ready() {
+    if (mb_y <= first_row) return true;
+    const uint32_t need = uint32_t((mb_y - 1) * mbw + mb_x + 1);
+    if (above_seen >= need) return true;
+#if defined(__CUDACC__) && !defined(AVR_HOST_EMULATION)
+    for (uint32_t polls = 0;;) {
+      above_seen = *prog_above;
+      if (*abort_flag) { fail(WALK_CORRUPT); done = true; return false; }
+      if (above_seen >= need) break;
+      wide_backoff(polls);
+    }
+    ring_fence();
+    return true;
+#else
+    above_seen = *prog_above;
+    if (above_seen >= need) return true;
+    if (*abort_flag) { fail(WALK_CORRUPT); done = true; return false; }
+    blocked = true;
+    return false;
+#endif
+  }
+  // stream: wide decompression only -- which of the K streams this walker decodes; total_mbs from the blob header
+  AVR_DEV void start(const avr_slice_desc& d, uint32_t stream = 0, uint32_t total_mbs = 0) {
     mbw = d.mb_width; mbh = d.mb_height;
     first_mb = d.first_mb;
     is_p = d.slice_type == AVR_SLICE_P;
@@ -683,6 +734,17 @@ struct Walker {
     status = WALK_OK;
     n_mbs = 0;
     done = false;
+    blocked = false;
+    first_row = mb_y;
+    cur_ring = 0;
+    above_seen = 0;
+    if (Dir::kDecompress && wide_k) {
+      last_row = int((d.first_mb + (total_mbs ? total_mbs : 1u) - 1) / uint32_t(mbw > 0 ? mbw : 1));
+      if (stream > 0) { mb_x = 0; mb_y = first_row + int(stream); mb_xy = mb_y * mbw; }
+      row = rows_base + (uint32_t(mb_y) % wide_k) * uint32_t(mbw);
+      row_top = rows_base + ((uint32_t(mb_y) + wide_k - 1) % wide_k) * uint32_t(mbw);
+      if (mb_y > last_row) { done = true; return; }   // more streams than rows: nothing in this one
+    }
     for (int i = 0; i < MBCTX_WORDS; i++) reinterpret_cast<uint32_t*>(&ws->left)[i] = 0;
     if (d.slice_type > AVR_SLICE_I || d.chroma_format_idc != 1 ||
         (d.flags & (AVR_SLICE_MBAFF | AVR_SLICE_FIELD)) || mbw < 1 || mbh < 1 || mb_xy >= mbw * mbh) {
@@ -692,6 +754,7 @@ struct Walker {
   }
   AVR_DEV void step() {
     if (mb_y >= mbh) { fail(WALK_CORRUPT); done = true; return; }
+    if (Dir::kDecompress && wide_k) { blocked = false; if (!top_ready()) return; }
     const uint32_t bins_before = n_bins_lo;
     macroblock();
     n_mbs++;
@@ -700,10 +763,25 @@ struct Walker {
     if (n_bins_lo < bins_before) n_bins_hi++;
     store_mb();
     mb_xy++;
-    if (++mb_x >= mbw) { mb_x = 0; mb_y++; }
+    bool wrapped = false;
+    if (++mb_x >= mbw) { mb_x = 0; mb_y++; wrapped = true; }
+    if (Dir::kDecompress && wide_k) { ring_fence(); *prog_mine = uint32_t(mb_xy); }   // the row below may use this macroblock
     dir.q.publish();
     if (status != WALK_OK) { done = true; return; }
     if (eos) { done = true; return; }
+    if (wide_k && wrapped) {
+      if (!Dir::kDecompress) {   // next row -> next stream
+        cur_ring = cur_ring + 1 == wide_k ? 0 : cur_ring + 1;
+        dir.q.switch_to(&rings[cur_ring]);
+      } else {                   // on to this warp's next row, K - 1 rows further down
+        dir.row_end(last_qp_delta != 0);
+        mb_y += int(wide_k) - 1;
+        mb_xy += (int(wide_k) - 1) * mbw;
+        if (mb_y > last_row) { done = true; return; }
+        row = rows_base + (uint32_t(mb_y) % wide_k) * uint32_t(mbw);
+        row_top = rows_base + (uint32_t(mb_y - 1) % wide_k) * uint32_t(mbw);
+      }
+    }
     if (mb_y >= mbh) { fail(WALK_CORRUPT); done = true; }   // picture full without end_of_slice: reference asserts here
   }
 };

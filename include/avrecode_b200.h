@@ -71,8 +71,14 @@ typedef struct avr_slice_desc {
   uint8_t  num_ref_idx_l1;/* sl->ref_count[1] */
   uint8_t  chroma_format_idc; /* 1 = 4:2:0 (the only format the kernels walk) */
   uint8_t  flags;         /* AVR_SLICE_* */
-  uint8_t  reserved;
+  uint8_t  n_streams;     /* 0 or 1: an ordinary slice.  2..AVR_MAX_STREAMS: a "wide" slice of the chunked container
+                             mode -- macroblock row r is coded in range-coder stream (r - first row) mod n_streams, so
+                             that the slice decompresses as a wavefront of n_streams rows.  Block.cabac of such a slice
+                             is: u32 macroblocks | n_streams x u32 stream bytes | the streams (little endian).  Only
+                             for slices that carry AVR_SLICE_NEW_MODEL and are followed by one (a model of their own);
+                             the format is this library's own, the reference has no counterpart. */
 } avr_slice_desc;
+#define AVR_MAX_STREAMS 2   /* what this build runs (two estimator sets fill an SM's shared memory); the blob format allows more */
 
 /* avr_slice_result.status */
 #define AVR_SLICE_OK           0

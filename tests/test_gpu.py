@@ -222,3 +222,78 @@ def test_both_estimator_placements_equal_oracle(built, resident, monkeypatch):
                 r_o, b_o = H.oracle_compress(descs, data)
                 assert H.slices_of(res, blob) == H.slices_of(r_o, b_o)
                 check_roundtrip(c, descs, data, res, blob)
+
+
+# ---- wide slices (chunked mode only: a slice over two range-coder streams, decompressed as a wavefront) ----
+WIDE = [
+    dict(width=480, height=272, frames=6, slices=4, seed=2),
+    dict(width=640, height=368, frames=5, high=True, seed=3, ragged=True, slices=3),     # slices that start mid-row
+    dict(mbw=255, mbh=2, frames=2, seed=15, slices=2),                                  # fewer rows than streams
+    dict(mbw=1, mbh=1, frames=3, seed=14),
+    dict(width=480, height=272, frames=12, bpics=0.8, seed=17, refs=4, high=True, p8x8=0.8, pskip=0.5),
+    dict(width=1920, height=1088, frames=3, high=True, seed=31, kbps=30000, fps=60),
+]
+
+
+@pytest.mark.parametrize("kw", WIDE, ids=lambda k: "seed%d" % k["seed"])
+def test_wide_slices_equal_emulation_and_round_trip(ctx, kw):
+    """The format is this library's own (no reference counterpart): the device must write the bytes of the
+    host emulation of the same code, walk the bins of the ordinary path, and round-trip exactly."""
+    data = H.gen_stream(**kw)
+    plain = H.batch_descs(A.index_h264(data), False)
+    r_p, _ = ctx.compress(plain, data)
+    descs = H.batch_descs(A.index_h264(data), False)
+    for i, d in enumerate(descs):
+        d.n_streams = 0 if i % 3 == 2 else 2          # wide and ordinary slices in one batch
+    res, blob = ctx.compress(descs, data)
+    r_e, b_e = H.emu_compress(descs, data)
+    assert [r.status for r in res] == [0] * len(descs)
+    assert H.slices_of(res, blob) == H.slices_of(r_e, b_e)
+    assert [(r.n_bins, r.n_mbs) for r in res] == [(r.n_bins, r.n_mbs) for r in r_p]
+    check_roundtrip(ctx, descs, data, res, blob)
+    # the emulation decodes what the device wrote
+    r_d, b_d = H.emu_decompress(H.coded_descs(descs, res), blob)
+    assert H.roundtrip_ok(descs, r_d, b_d, data)
+
+
+def test_wide_slices_in_the_container(ctx, monkeypatch):
+    data = H.gen_stream(width=640, height=368, frames=6, high=True, seed=41, kbps=6000)
+    monkeypatch.setenv("AVR_WIDE_STREAM_BYTES", "2048")
+    rec_w = ctx.file_compress(data, A.MODE_SLICE)
+    monkeypatch.setenv("AVR_WIDE_STREAM_BYTES", "0")
+    rec_0 = ctx.file_compress(data, A.MODE_SLICE)
+    monkeypatch.delenv("AVR_WIDE_STREAM_BYTES")
+    _, blocks_w = recproto.parse(rec_w)
+    _, blocks_0 = recproto.parse(rec_0)
+    assert any(b.get("streams") == 2 for b in blocks_w) and not any("streams" in b for b in blocks_0)
+    assert ctx.file_decompress(rec_w) == data and ctx.file_decompress(rec_0) == data
+    assert len(rec_w) < len(rec_0) * 1.02        # two models instead of one cost little
+    # file mode (the reference's format) never uses them
+    monkeypatch.setenv("AVR_WIDE_STREAM_BYTES", "2048")
+    assert not any("streams" in b for b in recproto.parse(ctx.file_compress(data, A.MODE_FILE))[1])
+
+
+def test_wide_slice_errors(ctx):
+    data = H.gen_stream(width=480, height=272, frames=2, seed=2)
+    descs = H.batch_descs(A.index_h264(data), False)
+    descs[0].n_streams = 3                                   # more than this build runs
+    with pytest.raises(A.AvrError):
+        ctx.compress(descs, data)
+    descs = H.batch_descs(A.index_h264(data), True)          # file mode: the slices share one model
+    descs[0].n_streams = 2
+    with pytest.raises(A.AvrError):
+        ctx.compress(descs, data)
+    # damaged blob headers are reported per slice, not crashed on
+    descs = H.batch_descs(A.index_h264(data), False)
+    for d in descs:
+        d.n_streams = 2
+    res, blob = ctx.compress(descs, data)
+    dd = H.coded_descs(descs, res)
+    for damage in (lambda b: b[:4] + bytes([b[4] ^ 1]) + b[5:],       # stream size
+                   lambda b: bytes(4) + b[4:],                        # zero macroblocks
+                   lambda b: b[:8]):                                  # header cut short
+        bad = damage(blob[res[0].out_off:res[0].out_off + res[0].out_size])
+        d0 = _abi.copy_desc(dd[0])
+        d0.in_off, d0.in_size = 0, len(bad)
+        r_d, _ = ctx.decompress([d0], bad)
+        assert r_d[0].status != 0

@@ -124,6 +124,25 @@ def test_device_logic_on_host_matches_oracle(built, name, mode_file):
     assert H.roundtrip_ok(descs, r_d, b_d, data)
 
 
+@pytest.mark.parametrize("kw", [dict(width=480, height=272, frames=4, slices=2, seed=2),
+                                dict(width=352, height=288, frames=6, bpics=0.6, seed=19, refs=3, high=True),
+                                dict(mbw=3, mbh=1, frames=2, seed=20)], ids=["ip", "b", "one-row"])
+def test_wide_slices_on_host_round_trip(built, kw):
+    """Wide slices (two range-coder streams per slice, rows interleaved) in the host emulation of the device
+    code: exact round trip, the bins of the ordinary path, and a size within a few percent of it."""
+    data = H.gen_stream(**kw)
+    plain = H.batch_descs(A.index_h264(data), False)
+    r_1, _ = H.emu_compress(plain, data)
+    descs = H.batch_descs(A.index_h264(data), False)
+    for d in descs:
+        d.n_streams = 2
+    r_e, b_e = H.emu_compress(descs, data)
+    assert [(r.status, r.n_bins, r.n_mbs) for r in r_e] == [(r.status, r.n_bins, r.n_mbs) for r in r_1]
+    r_d, b_d = H.emu_decompress(H.coded_descs(descs, r_e), b_e)
+    assert H.roundtrip_ok(descs, r_d, b_d, data)
+    assert sum(r.out_size for r in r_e) < 1.5 * sum(r.out_size for r in r_1) + 64 * len(descs)
+
+
 def test_manifest_matches_files():
     import hashlib
     for name, m in MANIFEST.items():

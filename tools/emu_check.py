@@ -27,5 +27,22 @@ for kw in CASES:
         rt = H.roundtrip_ok(descs, r_d, b_d, data)
         print(kw, "file" if mode_file else "slice", "compress==oracle", same, "roundtrip", rt, flush=True)
         bad += (not same) + (not rt)
+# wide slices (our own chunked format: K streams per slice): no oracle counterpart, exact round trip required,
+# and the bins walked must be those of the ordinary path
+for kw in CASES:
+    data = H.gen_stream(**kw)
+    base = H.batch_descs(A.index_h264(data), False)
+    r_1, _ = H.emu_compress(base, data)
+    for k in (2,):
+        descs = H.batch_descs(A.index_h264(data), False)
+        for d in descs:
+            d.n_streams = k
+        r_e, b_e = H.emu_compress(descs, data)
+        same = [(r.status, r.n_bins, r.n_mbs) for r in r_e] == [(r.status, r.n_bins, r.n_mbs) for r in r_1]
+        r_d, b_d = H.emu_decompress(H.coded_descs(descs, r_e), b_e)
+        rt = H.roundtrip_ok(descs, r_d, b_d, data)
+        grow = sum(r.out_size for r in r_e) / max(1, sum(r.out_size for r in r_1))
+        print(kw, "wide", k, "bins==plain", same, "roundtrip", rt, "size x%.4f" % grow, flush=True)
+        bad += (not same) + (not rt)
 print("ALL OK" if not bad else "FAILURES %d" % bad)
 sys.exit(1 if bad else 0)
