@@ -94,6 +94,14 @@ def _buf(data):
     raise TypeError("unsupported buffer type %r" % type(data))
 
 
+def slice_streams(desc):
+    """n_streams the file calls would give this slice in MODE_SLICE (0 = ordinary slice, 2 = wide slice)."""
+    lib = load_library()
+    lib.avr_slice_streams.argtypes = [C.POINTER(SliceDesc)]
+    lib.avr_slice_streams.restype = C.c_int
+    return int(lib.avr_slice_streams(C.byref(desc)))
+
+
 def index_h264(data):
     """Slice index of an Annex-B H.264 stream (host only, no GPU): list of IndexEntry."""
     lib = load_library()

@@ -142,6 +142,8 @@ extern "C" {
 
 void avr_free(void* p) { free(p); }
 
+int avr_slice_streams(const avr_slice_desc* desc) { return desc ? streams_for(*desc, wide_stream_bytes()) : 0; }
+
 // Shared driver of avr_file_compress / avr_files_compress: all CABAC slices of all files go to the
 // device as ONE batch (files are independent, so in either mode every file starts a fresh model).
 static int compress_many(avr_ctx* ctx, const uint8_t* const* files, const uint64_t* sizes, int n_files, int mode,

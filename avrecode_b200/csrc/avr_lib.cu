@@ -61,6 +61,9 @@ __global__ void __launch_bounds__(AVR_THREADS, RESIDENT ? 2 : 8) avr_job_kernel(
     if (j >= k.n_jobs) break;
     run_job<Dir>(k.a, k.jobs[j], m, tid);
   }
+  // When this grid was launched as the programmatic dependent of the wide-slice kernel (see avr_launch), it must not
+  // complete before that one has: later work in the stream is ordered after THIS grid only.  No-op otherwise.
+  asm volatile("griddepcontrol.wait;" ::: "memory");
 }
 
 // Wide slices (avr_job.cuh, run_wide_job): one slice per block of 1 + WIDE_MAX warps.
@@ -95,6 +98,10 @@ __global__ void __launch_bounds__(AVR_WIDE_THREADS, 1) avr_wide_kernel(WideKerne
   m.far_cap = k.far_cap;
   m.max_mbw = k.max_mbw;
   const int tid = threadIdx.x;
+  // every block of this grid is now resident: the ordinary kernel, queued behind it as a programmatic dependent,
+  // may start filling the remaining SMs (launched the other way round its blocks would take the shared memory
+  // of every SM and the wide blocks -- a whole SM each -- would wait for them)
+  asm volatile("griddepcontrol.launch_dependents;");
   fill_shared_tables(&m.sh->tab, tid, AVR_WIDE_THREADS);
   __syncthreads();
   for (;;) {
@@ -121,8 +128,7 @@ struct avr_ctx {
   int sm_count = 0;
   int max_smem_optin = 0;
   cudaStream_t stream = nullptr;
-  cudaStream_t stream_wide = nullptr;   // the wide-slice kernel runs beside the ordinary one
-  cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_fork = nullptr, ev_join = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   // device buffers, grown on demand
   uint8_t* d_in = nullptr; size_t d_in_cap = 0;
   uint8_t* d_out = nullptr; size_t d_out_cap = 0;
@@ -226,9 +232,6 @@ int avr_create(const avr_config* cfg, avr_ctx** out) {
   c->max_smem_sm = int(prop.sharedMemPerMultiprocessor);
   if (const char* e = getenv("AVR_RESIDENT")) c->force_resident = atoi(e) ? 1 : 0;
   if (!ck(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking), "cudaStreamCreate") ||
-      !ck(cudaStreamCreateWithFlags(&c->stream_wide, cudaStreamNonBlocking), "cudaStreamCreate") ||
-      !ck(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming), "cudaEventCreate") ||
-      !ck(cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming), "cudaEventCreate") ||
       !ck(cudaEventCreate(&c->ev0), "cudaEventCreate") || !ck(cudaEventCreate(&c->ev1), "cudaEventCreate")) {
     avr_destroy(c);
     return AVR_ERR_CUDA;
@@ -245,9 +248,6 @@ void avr_destroy(avr_ctx* c) {
   if (c->d_out) cudaFree(c->d_out);
   if (c->d_work) cudaFree(c->d_work);
   if (c->d_wide) cudaFree(c->d_wide);
-  if (c->stream_wide) { cudaStreamSynchronize(c->stream_wide); cudaStreamDestroy(c->stream_wide); }
-  if (c->ev_fork) cudaEventDestroy(c->ev_fork);
-  if (c->ev_join) cudaEventDestroy(c->ev_join);
   if (c->d_meta) cudaFree(c->d_meta);
   if (c->d_flush) cudaFree(c->d_flush);
   if (c->h_out) cudaFreeHost(c->h_out);
@@ -408,23 +408,29 @@ int avr_launch(avr_ctx* c, int direction) {
     const size_t rows_bytes = size_t(direction == 0 ? 1 : WIDE_MAX) * c->max_mbw_wide * sizeof(MbCtx);
     w.rows_in_shared = wsmem + rows_bytes + 1024 <= size_t(c->max_smem_optin) ? 1u : 0u;
     if (w.rows_in_shared) wsmem += rows_bytes;
-    CK(cudaEventRecord(c->ev_fork, c->stream));
-    CK(cudaStreamWaitEvent(c->stream_wide, c->ev_fork, 0));
     if (direction == 0) {
       CK(cudaFuncSetAttribute(avr_wide_kernel<Compress>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(wsmem)));
-      avr_wide_kernel<Compress><<<c->grid_wide, AVR_WIDE_THREADS, wsmem, c->stream_wide>>>(w);
+      avr_wide_kernel<Compress><<<c->grid_wide, AVR_WIDE_THREADS, wsmem, c->stream>>>(w);
     } else {
       CK(cudaFuncSetAttribute(avr_wide_kernel<Decompress>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(wsmem)));
-      avr_wide_kernel<Decompress><<<c->grid_wide, AVR_WIDE_THREADS, wsmem, c->stream_wide>>>(w);
+      avr_wide_kernel<Decompress><<<c->grid_wide, AVR_WIDE_THREADS, wsmem, c->stream>>>(w);
     }
     CK(cudaGetLastError());
-    CK(cudaEventRecord(c->ev_join, c->stream_wide));
     c->launches++;
   }
+  // The ordinary kernel follows in the same stream; behind a wide kernel it is a programmatic dependent launch
+  // (it starts as soon as every wide block has started and runs beside them).
+  cudaLaunchAttribute pdl;
+  pdl.id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  pdl.val.programmaticStreamSerializationAllowed = 1;
+  cudaLaunchConfig_t lc;
+  memset(&lc, 0, sizeof lc);
+  lc.gridDim = dim3(unsigned(c->grid)); lc.blockDim = dim3(AVR_THREADS); lc.dynamicSmemBytes = smem; lc.stream = c->stream;
+  lc.attrs = &pdl; lc.numAttrs = c->grid_wide > 0 ? 1 : 0;
 #define AVR_LAUNCH(DIR, RES)                                                                                              \
   do {                                                                                                                    \
     CK(cudaFuncSetAttribute(avr_job_kernel<DIR, RES>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));          \
-    avr_job_kernel<DIR, RES><<<c->grid, AVR_THREADS, smem, c->stream>>>(k);                                               \
+    CK(cudaLaunchKernelEx(&lc, avr_job_kernel<DIR, RES>, k));                                                             \
   } while (0)
   if (c->n_jobs > 0) {
     if (direction == 0) { if (c->resident) AVR_LAUNCH(Compress, true); else AVR_LAUNCH(Compress, false); }
@@ -433,7 +439,6 @@ int avr_launch(avr_ctx* c, int direction) {
   }
 #undef AVR_LAUNCH
   CK(cudaGetLastError());
-  if (c->grid_wide > 0) CK(cudaStreamWaitEvent(c->stream, c->ev_join, 0));
   CK(cudaEventRecord(c->ev1, c->stream));
   return AVR_OK;
 }

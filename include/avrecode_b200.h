@@ -162,6 +162,9 @@ typedef struct avr_index_entry {
 } avr_index_entry;
 
 int  avr_index_h264(const uint8_t* file, uint64_t file_bytes, avr_index_entry** entries, int* n_entries);
+/* The n_streams the file calls give this slice in AVR_MODE_SLICE: 2 when its payload is at least two stream
+ * quanta (32 KiB each; environment AVR_WIDE_STREAM_BYTES overrides, 0 = never), else 0.  No reference counterpart. */
+int  avr_slice_streams(const avr_slice_desc* desc);
 
 /* chunking mode of the container produced by avr_file_compress */
 #define AVR_MODE_FILE   0  /* reference parity: one model for the whole file -- output is byte-identical

@@ -8,6 +8,7 @@ import helpers as H
 
 frames = int(sys.argv[1]) if len(sys.argv) > 1 else 30
 REPS = int(os.environ.get("PROFILE_REPS", "2"))
+FLUSH = int(os.environ.get("PROFILE_FLUSH", "0"))   # 1: L2 flush kernel queued right before each launch; 2: and waited for
 per_stream = int(sys.argv[2]) if len(sys.argv) > 2 else 0   # > 0: slices of >= 2 * per_stream bytes become wide slices
 data = H.gen_stream(width=1920, height=1088, frames=frames, high=True, kbps=30000, fps=60, intra_period=30, seed=2)
 descs = H.batch_descs(A.index_h264(data), False)
@@ -18,12 +19,16 @@ if per_stream:
 with A.Context() as ctx:
     ctx.stage(descs, data)
     for _ in range(REPS):   # the first launch of a kernel also loads it (lazily), which can serialise two kernels
+        if FLUSH: ctx.flush_l2()
+        if FLUSH > 1: ctx.sync()
         ctx.launch(0); ctx.sync()
     ms_c = ctx.last_kernel_ms()
     res, blob = ctx.collect()
     dd = H.coded_descs(descs, res)
     ctx.stage(dd, blob)
     for _ in range(REPS):
+        if FLUSH: ctx.flush_l2()
+        if FLUSH > 1: ctx.sync()
         ctx.launch(1); ctx.sync()
     ms_d = ctx.last_kernel_ms()
     r_d, b_d = ctx.collect()
