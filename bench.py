@@ -331,7 +331,8 @@ def run_ours(args):
         "gpu_launches": int(launches),
         "e2e": {"value": total_bytes / e2e_s / 1e6, "unit": UNIT, "h2d_bytes_per_step": len(data) + coded + 80 * len(descs),
                 "d2h_bytes_per_step": coded + payload + 64 * len(descs), "api": "avr_file_compress + avr_file_decompress (host buffers)"},
-        "roofline": {"bound": "hbm", "kernel": "avr_job_kernel<%s>" % dom.capitalize(), "achieved": achieved, "peak": peak,
+        "roofline": {"bound": "hbm", "kernel": ("avr_wide_kernel<%s> + avr_job_kernel<%s> (one launch pair, concurrent)" if n_wide else "avr_job_kernel<%s>%s") % (dom.capitalize(), "" if not n_wide else dom.capitalize()),
+                     "achieved": achieved, "peak": peak,
                      "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                      "note": "serial integer recurrence per slice: latency-bound, not HBM-bound; see DESIGN.md for the per-bin latency bound"},
         "clocks": clocks,
