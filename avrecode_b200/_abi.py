@@ -11,6 +11,9 @@ AVR_SLICE_NEW_PICTURE = 0x04
 AVR_SLICE_MBAFF = 0x08
 AVR_SLICE_FIELD = 0x10
 AVR_SLICE_NEW_MODEL = 0x20
+AVR_STREAMS_MASK = 0x0F      # avr_slice_desc.n_streams: bits 0-3 streams, 4-5 header zeros, 7 escaped
+AVR_ESC_ZEROS_SHIFT = 4
+AVR_SLICE_ESCAPED = 0x80
 AVR_SLICE_STOP_BYTE = 0x40
 AVR_SLICE_SKIP = 0x80
 

@@ -278,9 +278,17 @@ struct ByteSink {
   uint8_t* out;
   uint32_t n, cap, pending;
   int cache;          // -1 = nothing cached yet
+  int esc;            // >= 0: emulation prevention (H.264 7.4.1) is applied on the way out, esc = zero bytes just written
   bool overflow;
-  AVR_DEV void init(uint8_t* o, uint32_t c) { out = o; n = 0; cap = c; pending = 0; cache = -1; overflow = false; }
-  AVR_DEV void raw(uint32_t b) { if (n < cap) out[n] = uint8_t(b); else overflow = true; n++; }
+  AVR_DEV void init(uint8_t* o, uint32_t c, int esc_zeros = -1) { out = o; n = 0; cap = c; pending = 0; cache = -1; esc = esc_zeros; overflow = false; }
+  AVR_DEV void store(uint32_t b) { if (n < cap) out[n] = uint8_t(b); else overflow = true; n++; }
+  AVR_DEV void raw(uint32_t b) {
+    if (esc >= 0) {   // chunked mode, escaped slices: 00 00 0x (x <= 3) becomes 00 00 03 0x
+      if (esc >= 2 && b <= 3) { store(3); esc = 0; }
+      esc = b == 0 ? esc + 1 : 0;
+    }
+    store(b);
+  }
   AVR_DEV void push(uint32_t byte, uint32_t carry) {
     if (carry) {
       raw(uint32_t(cache + 1));
@@ -372,7 +380,7 @@ struct CabacOut {
   uint32_t low, range;
   int queue;
   ByteSink sink;
-  AVR_DEV void init(uint8_t* out, uint32_t cap) { low = 0; range = 510; queue = -9; sink.init(out, cap); }
+  AVR_DEV void init(uint8_t* out, uint32_t cap, int esc_zeros = -1) { low = 0; range = 510; queue = -9; sink.init(out, cap, esc_zeros); }
   AVR_DEV void put_bytes() {
     while (queue >= 0) {
       const uint32_t o = low >> (queue + 10);
@@ -593,7 +601,7 @@ struct Consumer {
 // ------------------------------------------------------------------------------------------------
 struct CoderCompress {     // estimators + range encoder (recode.cpp:1068-1096 h264_symbol::execute)
   RangeEnc rc;
-  AVR_DEV void begin(uint8_t* dst, uint32_t cap) { rc.init(dst, cap); }
+  AVR_DEV void begin(uint8_t* dst, uint32_t cap, int = -1) { rc.init(dst, cap); }
   // Software-pipelined: entry k+1, its estimator and its reciprocal are loaded while entry k goes
   // through the coder, so the loop-carried chain is the range recurrence alone (one 64x64 high
   // multiply, a shift, a multiply, a subtract, a select).  The estimator of entry k+1 is read BEFORE
@@ -637,7 +645,7 @@ struct CoderCompress {     // estimators + range encoder (recode.cpp:1068-1096 h
 
 struct CoderDecompress {   // CABAC re-encoder (cabac_code.h:16-86; recode.cpp:1443, 1455, 1466)
   CabacOut cabac;
-  AVR_DEV void begin(uint8_t* dst, uint32_t cap) { cabac.init(dst, cap); }
+  AVR_DEV void begin(uint8_t* dst, uint32_t cap, int esc_zeros = -1) { cabac.init(dst, cap, esc_zeros); }
   AVR_DEV void entry(const SharedTables& t, U2* cstate, uint32_t e) {
     if (e & SYM_LEVEL) {   // one coefficient level: first bin, run of "greater than one" bins, sign
       const uint32_t g = (e >> LVL_GCTX) & 0x1FF;

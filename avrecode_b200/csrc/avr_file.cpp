@@ -42,6 +42,8 @@ struct Block {   // Recoded.Block (recode.proto:9-18)
   bool has_size = false, has_literal = false, has_skip = false, has_cabac = false, has_parity = false, has_last = false;
   int64_t size = 0;
   uint64_t streams = 0;   // field 7, chunked mode only: range-coder streams of a wide slice (avr_slice_desc.n_streams)
+  uint64_t escaped = 0;   // field 8, chunked mode only: the payload in the file has emulation-prevention bytes, cabac
+                          //   codes the unescaped slice_data (AVR_SLICE_ESCAPED)
   bool skip = false, parity = false;
   const uint8_t* literal = nullptr; size_t literal_n = 0;
   const uint8_t* cabac = nullptr; size_t cabac_n = 0;
@@ -60,6 +62,7 @@ bool parse_block(const uint8_t* p, const uint8_t* e, Block* b) {
       else if (field == 3) { b->skip = v != 0; b->has_skip = true; }
       else if (field == 5) { b->parity = v != 0; b->has_parity = true; }
       else if (field == 7) b->streams = v;
+      else if (field == 8) b->escaped = v;
     } else if (wt == 2) {
       uint64_t n;
       if (!get_varint(p, e, &n) || n > uint64_t(e - p)) return false;
@@ -122,6 +125,24 @@ uint8_t streams_for(const avr_slice_desc& d, uint32_t per_stream) {
   return k >= 2 ? uint8_t(k) : uint8_t(0);
 }
 
+// H.264 7.4.1 on a slice_data payload; z = zero bytes that end the slice header (0..2)
+void unescape_payload(const uint8_t* p, size_t n, int z, std::vector<uint8_t>* out) {
+  for (size_t i = 0; i < n; i++) {
+    if (z >= 2 && p[i] == 3) { z = 0; continue; }
+    out->push_back(p[i]);
+    z = p[i] == 0 ? z + 1 : 0;
+  }
+}
+bool escapes_back_to(const uint8_t* raw, size_t raw_n, int z, const uint8_t* p, size_t n) {   // what the device will write
+  size_t k = 0;
+  for (size_t i = 0; i < raw_n; i++) {
+    if (z >= 2 && raw[i] <= 3) { if (k >= n || p[k++] != 3) return false; z = 0; }
+    if (k >= n || p[k++] != raw[i]) return false;
+    z = raw[i] == 0 ? z + 1 : 0;
+  }
+  return k == n;
+}
+
 void emit_block(std::string& out, const std::string& body) {
   put_varint(out, (2u << 3) | 2);
   put_varint(out, body.size());
@@ -151,7 +172,9 @@ static int compress_many(avr_ctx* ctx, const uint8_t* const* files, const uint64
   struct Plan {
     avr_index_entry* ents = nullptr;
     int n_ents = 0;
-    std::vector<char> coded;      // 1 = goes to the device
+    std::vector<char> coded;      // 1 = goes to the device; 2 = goes there unescaped (chunked mode, escaped payload)
+    std::vector<uint64_t> raw_off; // coded == 2: offset of the unescaped copy in the arena
+    std::vector<uint32_t> raw_size;
     std::vector<int> map;         // batch position -> entry, for this file
     size_t first = 0;             // first batch position of this file
     uint64_t base = 0;            // offset of the file in the arena
@@ -175,7 +198,38 @@ static int compress_many(avr_ctx* ctx, const uint8_t* const* files, const uint64
     int rc = avr_index_h264(files[f], sizes[f], &p.ents, &p.n_ents);
     if (rc) { cleanup(); return rc; }
     p.coded.assign(size_t(p.n_ents), 0);
+    p.raw_off.assign(size_t(p.n_ents), 0);
+    p.raw_size.assign(size_t(p.n_ents), 0);
     for (int i = 0; i < p.n_ents; i++) p.coded[i] = p.ents[i].recodable ? 1 : 0;
+  }
+  // Chunked mode recodes slices whose payload contains emulation-prevention bytes too (the reference leaves
+  // them as literals): the device gets an unescaped copy, appended to the arena, and puts the bytes back when
+  // it decompresses.  Only if escaping the copy gives the file's bytes again.
+  std::vector<uint8_t> raws;
+  if (mode == AVR_MODE_SLICE) {
+    for (int f = 0; f < n_files; f++) {
+      Plan& p = plans[f];
+      for (int i = 0; i < p.n_ents; i++) {
+        const avr_slice_desc& d = p.ents[i].desc;
+        if (p.coded[i] || !(d.n_streams & AVR_SLICE_ESCAPED)) continue;
+        const int z = (d.n_streams >> AVR_ESC_ZEROS_SHIFT) & 3;
+        const size_t at = (raws.size() + 15) & ~size_t(15);
+        raws.resize(at);
+        unescape_payload(files[f] + d.in_off, d.payload_size, z, &raws);
+        if (raws.size() - at >= 8 && escapes_back_to(raws.data() + at, raws.size() - at, z, files[f] + d.in_off, d.payload_size)) {
+          p.coded[i] = 2; p.raw_off[i] = at; p.raw_size[i] = uint32_t(raws.size() - at);
+        } else raws.resize(at);
+      }
+    }
+    if (!raws.empty()) {   // one arena: the files, then the unescaped copies
+      uint64_t total = 0;
+      if (n_files == 1) { plans[0].base = 0; total = (sizes[0] + 15) & ~uint64_t(15); arena_store.resize(size_t(total)); memcpy(arena_store.data(), files[0], size_t(sizes[0])); }
+      else total = arena_bytes;
+      arena_store.resize(size_t(total) + raws.size() + 16);
+      memcpy(arena_store.data() + total, raws.data(), raws.size());
+      for (Plan& p : plans) for (int i = 0; i < p.n_ents; i++) if (p.coded[i] == 2) p.raw_off[i] += total;
+      arena = arena_store.data(); arena_bytes = total + raws.size();
+    }
   }
   const uint32_t per_stream = mode == AVR_MODE_SLICE ? wide_stream_bytes() : 0;
   std::vector<avr_slice_desc> descs;
@@ -198,6 +252,7 @@ static int compress_many(avr_ctx* ctx, const uint8_t* const* files, const uint64
           d.in_off = 0; d.in_size = 0;
         }
         if (p.map.empty() || mode == AVR_MODE_SLICE) d.flags |= AVR_SLICE_NEW_MODEL;
+        if (p.coded[i] == 2) { d.in_off = p.raw_off[i]; d.in_size = p.raw_size[i]; }
         d.n_streams = p.coded[i] ? streams_for(d, per_stream) : 0;
         descs.push_back(d);
         p.map.push_back(i);
@@ -243,7 +298,8 @@ static int compress_many(avr_ctx* ctx, const uint8_t* const* files, const uint64
         put_len(body, 4, out + r->out_off, r->out_size);
         put_var(body, 5, d.payload_size & 1);
         if (d.payload_size > 1) put_len(body, 6, file + d.in_off + d.payload_size - 1, 1);
-        if (descs[p.first + k].n_streams >= 2) put_var(body, 7, descs[p.first + k].n_streams);
+        if ((descs[p.first + k].n_streams & AVR_STREAMS_MASK) >= 2) put_var(body, 7, descs[p.first + k].n_streams & AVR_STREAMS_MASK);
+        if (p.coded[i] == 2) put_var(body, 8, 1);
         prev = d.in_off + d.payload_size;
       } else {   // {size, skip_coded}: the bytes stay in the surrounding literal
         put_var(body, 1, d.payload_size);
@@ -335,7 +391,11 @@ static int decompress_many(avr_ctx* ctx, const uint8_t* const* recs, const uint6
       if (p.which.empty() || slice_mode) d.flags |= AVR_SLICE_NEW_MODEL;
       if (b.streams) {
         if (!slice_mode || !p.coded[i].is_cabac || b.streams < 2 || b.streams > AVR_MAX_STREAMS) { free(ents); return AVR_ERR_FORMAT; }
-        d.n_streams = uint8_t(b.streams);
+        d.n_streams = uint8_t((d.n_streams & ~AVR_STREAMS_MASK) | b.streams);
+      }
+      if (b.escaped) {
+        if (!slice_mode || !p.coded[i].is_cabac) { free(ents); return AVR_ERR_FORMAT; }
+        d.n_streams |= AVR_SLICE_ESCAPED;
       }
       if (p.coded[i].is_cabac) in.append(reinterpret_cast<const char*>(b.cabac), b.cabac_n);
       descs.push_back(d);

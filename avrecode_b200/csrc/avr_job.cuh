@@ -236,7 +236,8 @@ template <class Dir>
 AVR_DEV void coder_role(const JobArgs& a, const JobMem& m, const SliceIO& io, uint32_t s, int lane) {
   if (lane == 0) {
     typename Dir::Coder c;
-    c.begin(a.out_arena + io.out_off, io.out_cap);
+    const uint8_t lay = a.descs[s].n_streams;   // decompress: put emulation-prevention bytes back (escaped slices, chunked mode)
+    c.begin(a.out_arena + io.out_off, io.out_cap, (lay & AVR_SLICE_ESCAPED) ? int((lay >> AVR_ESC_ZEROS_SHIFT) & 3) : -1);
     Consumer q;
     q.init(&m.sh->ring);
     c.run(q, m.sh->tab, m.cnt, m.sh->cstate);
@@ -414,7 +415,9 @@ AVR_DEV void run_wide_job(const JobArgs& a, uint32_t s, const WideMem& m, int ti
   WideShared* sh = m.sh;
   const avr_slice_desc d = a.descs[s];
   const SliceIO io = a.ios[s];
-  const uint32_t K = d.n_streams;
+  const uint32_t K = d.n_streams & AVR_STREAMS_MASK;
+  const int esc_zeros = (Dir::kDecompress && (d.n_streams & AVR_SLICE_ESCAPED)) ? int((d.n_streams >> AVR_ESC_ZEROS_SHIFT) & 3) : -1;
+  (void)esc_zeros;
   const uint32_t mbw = d.mb_width;
   const uint32_t hdr = 4 + 4 * K;
   if (K < 2 || K > WIDE_MAX || mbw < 1 || d.mb_height < 1 || mbw > m.max_mbw) { wide_fail<Dir>(a, s, io, AVR_SLICE_UNSUPPORTED, tid); return; }
@@ -470,7 +473,7 @@ AVR_DEV void run_wide_job(const JobArgs& a, uint32_t s, const WideMem& m, int ti
   } else {
     if (warp == 0) {
       typename Dir::Coder c;
-      c.begin(out, io.out_cap);
+      c.begin(out, io.out_cap, esc_zeros);
       c.run_wide(sh->ring, K, m.far, m.far_cap, sh->tab, sh->cstate, sh->stage, lane);
       if (lane == 0) {
         sh->out_size[0] = c.out_bytes();
@@ -527,7 +530,7 @@ AVR_DEV void run_wide_job(const JobArgs& a, uint32_t s, const WideMem& m, int ti
     for (uint32_t j = 0; j < K; j++) parser_end<Dir>(wk[j], lane);
     delete[] wk;
     typename Dir::Coder c;
-    c.begin(out, io.out_cap);
+    c.begin(out, io.out_cap, esc_zeros);
     c.run_wide(sh->ring, K, m.far, m.far_cap, sh->tab, sh->cstate, sh->stage, lane);
     sh->out_size[0] = c.out_bytes();
     if (c.overflowed()) sh->overflow = 1;

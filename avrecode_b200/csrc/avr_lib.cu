@@ -278,6 +278,7 @@ int avr_stage(avr_ctx* c, const avr_slice_desc* descs, int n, const uint8_t* in,
   for (int dir = 0; dir < 2; dir++) { c->ios[dir].resize(n); c->out_total[dir] = 0; }
   for (int i = 0; i < n; i++) {
     const avr_slice_desc& d = descs[i];
+    const uint32_t n_str = d.n_streams & AVR_STREAMS_MASK;
     if (d.in_off + d.in_size > in_bytes) return AVR_ERR_ARG;
     for (int dir = 0; dir < 2; dir++) {
       SliceIO& io = c->ios[dir][i];
@@ -285,13 +286,13 @@ int avr_stage(avr_ctx* c, const avr_slice_desc* descs, int n, const uint8_t* in,
       io.out_off = c->out_total[dir];
       io.out_cap = dir == 0 ? d.in_size + d.in_size / 8 + 256 : d.payload_size + 64;
       // wide slice: header + n_streams slots, any one of which may end up with (nearly) all of the slice
-      if (dir == 0 && d.n_streams >= 2) io.out_cap = 64 + d.n_streams * uint32_t(align_up(size_t(d.in_size) + d.in_size / 8 + 512, 16));
+      if (dir == 0 && n_str >= 2) io.out_cap = 64 + n_str * uint32_t(align_up(size_t(d.in_size) + d.in_size / 8 + 512, 16));
       c->out_total[dir] += align_up(io.out_cap, 16);
     }
-    if (d.n_streams >= 2) {
+    if (n_str >= 2) {
       // a wide slice is a chunk of its own (its K streams have K models of their own)
       const bool own_model = (i == 0 || (d.flags & AVR_SLICE_NEW_MODEL)) && (i + 1 == n || (descs[i + 1].flags & AVR_SLICE_NEW_MODEL));
-      if (d.n_streams > AVR_MAX_STREAMS || !own_model || (d.flags & AVR_SLICE_SKIP)) return AVR_ERR_ARG;
+      if (n_str > AVR_MAX_STREAMS || !own_model || (d.flags & AVR_SLICE_SKIP)) return AVR_ERR_ARG;
       c->wide.push_back(uint32_t(i));
       c->max_mbw_wide = std::max<uint32_t>(c->max_mbw_wide, d.mb_width);
       continue;

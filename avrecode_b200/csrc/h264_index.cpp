@@ -323,6 +323,11 @@ extern "C" int avr_index_h264(const uint8_t* file, uint64_t file_bytes, avr_inde
               if (unsupported || st >= 3 || sp->bit_depth_luma != 8) fl |= AVR_SLICE_FIELD;  // routed to "unsupported"
               e.desc.flags = fl;
               e.recodable = (!escaped && size >= 8) ? 1 : 0;
+              {   // what a re-escaping decoder needs: the zero bytes that end the header, and whether the payload is escaped
+                const int z = b.zeros();
+                e.desc.n_streams = uint8_t((z > 2 ? 2 : z) << AVR_ESC_ZEROS_SHIFT);
+                if (escaped && size >= 8) e.desc.n_streams |= AVR_SLICE_ESCAPED;
+              }
               e.nal_type = type;
               out.push_back(e);
             }

@@ -71,13 +71,21 @@ typedef struct avr_slice_desc {
   uint8_t  num_ref_idx_l1;/* sl->ref_count[1] */
   uint8_t  chroma_format_idc; /* 1 = 4:2:0 (the only format the kernels walk) */
   uint8_t  flags;         /* AVR_SLICE_* */
-  uint8_t  n_streams;     /* 0 or 1: an ordinary slice.  2..AVR_MAX_STREAMS: a "wide" slice of the chunked container
+  uint8_t  n_streams;     /* bits 0-3 (AVR_STREAMS_MASK): 0 or 1: an ordinary slice.  2..AVR_MAX_STREAMS: a "wide" slice of the chunked container
                              mode -- macroblock row r is coded in range-coder stream (r - first row) mod n_streams, so
                              that the slice decompresses as a wavefront of n_streams rows.  Block.cabac of such a slice
                              is: u32 macroblocks | n_streams x u32 stream bytes | the streams (little endian).  Only
                              for slices that carry AVR_SLICE_NEW_MODEL and are followed by one (a model of their own);
-                             the format is this library's own, the reference has no counterpart. */
+                             the format is this library's own, the reference has no counterpart.
+                             bits 4-5: zero bytes (0..2) that end the slice header right before the payload; bit 7
+                             (AVR_SLICE_ESCAPED), decompress only: the slice_data in the file contains emulation-
+                             prevention bytes -- the coded block describes the UNESCAPED payload and the re-encoder
+                             inserts them again (H.264 7.4.1), payload_size being the escaped size.  Chunked mode only:
+                             the reference leaves such slices as literals (recode.cpp:1289-1296). */
 } avr_slice_desc;
+#define AVR_STREAMS_MASK   0x0F
+#define AVR_ESC_ZEROS_SHIFT 4
+#define AVR_SLICE_ESCAPED  0x80
 #define AVR_MAX_STREAMS 2   /* what this build runs (two estimator sets fill an SM's shared memory); the blob format allows more */
 
 /* avr_slice_result.status */
@@ -157,7 +165,9 @@ int  avr_flush_l2(avr_ctx* ctx);                           /* bench hygiene: wri
  * payload, size < 8, CAVLC never listed). */
 typedef struct avr_index_entry {
   avr_slice_desc desc;     /* in_off = payload offset in the file, in_size = payload_size */
-  int32_t  recodable;
+  int32_t  recodable;      /* 1: the reference would recode it.  0: it would not; when the only reason is emulation-
+                              prevention bytes inside the payload, desc.n_streams carries AVR_SLICE_ESCAPED and the
+                              chunked mode of the file calls recodes it anyway */
   int32_t  nal_type;
 } avr_index_entry;
 

@@ -21,7 +21,8 @@ static int run(const avr_slice_desc* descs, int n, const uint8_t* in, uint64_t i
     ios[i].in_off = descs[i].in_off; ios[i].in_size = descs[i].in_size;
     ios[i].out_off = out_total;
     ios[i].out_cap = Dir::kDecompress ? descs[i].payload_size + 64 : descs[i].in_size + descs[i].in_size / 8 + 256;
-    if (!Dir::kDecompress && descs[i].n_streams >= 2) ios[i].out_cap = 64 + descs[i].n_streams * ((descs[i].in_size + descs[i].in_size / 8 + 512 + 15) & ~15u);   // any one stream may get it all
+    if (!Dir::kDecompress && (descs[i].n_streams & AVR_STREAMS_MASK) >= 2)
+      ios[i].out_cap = 64 + (descs[i].n_streams & AVR_STREAMS_MASK) * ((descs[i].in_size + descs[i].in_size / 8 + 512 + 15) & ~15u);   // any one stream may get it all
     out_total += ios[i].out_cap;
     if (descs[i].mb_width > max_mbw) max_mbw = descs[i].mb_width;
     uint32_t fb = uint32_t(descs[i].mb_width) * descs[i].mb_height * NNZ_STRIDE;
@@ -48,7 +49,7 @@ static int run(const avr_slice_desc* descs, int n, const uint8_t* in, uint64_t i
   wm.sh = wsh; wm.rows = wrows.data(); wm.cnt = wcnt.data(); wm.rows_global = false; wm.far = nullptr; wm.far_cap = 0; wm.max_mbw = uint32_t(max_mbw);
   int i = 0;
   while (i < n) {
-    if (descs[i].n_streams >= 2) {
+    if ((descs[i].n_streams & AVR_STREAMS_MASK) >= 2) {
       if (!(descs[i].flags & AVR_SLICE_NEW_MODEL) || (i + 1 < n && !(descs[i + 1].flags & AVR_SLICE_NEW_MODEL))) return AVR_ERR_ARG;
       run_wide_job<Dir>(a, uint32_t(i), wm, 0);
       i++;

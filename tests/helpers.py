@@ -134,3 +134,31 @@ def fix_tail(got, payload):
 def ref_binary(name="recode_ref"):
     p = os.path.join(REF_DIR, name)
     return p if os.path.exists(p) else None
+
+
+def unescape(payload, zeros=0):
+    """H.264 7.4.1: drop the 0x03 of every 00 00 03; zeros = zero bytes right before the payload."""
+    out = bytearray()
+    z = zeros
+    for b in payload:
+        if z >= 2 and b == 3:
+            z = 0
+            continue
+        out.append(b)
+        z = z + 1 if b == 0 else 0
+    return bytes(out)
+
+
+def escaped_slice_case(data, entries):
+    """For the first slice whose payload contains emulation-prevention bytes: (entry, compress desc over a buffer
+    that holds the unescaped payload, that buffer, decompress flags byte)."""
+    for e in entries:
+        if e.desc.n_streams & _abi.AVR_SLICE_ESCAPED:
+            zeros = (e.desc.n_streams >> _abi.AVR_ESC_ZEROS_SHIFT) & 3
+            raw = unescape(data[e.desc.in_off:e.desc.in_off + e.desc.payload_size], zeros)
+            d = copy_desc(e.desc)
+            d.in_off, d.in_size = 0, len(raw)
+            d.n_streams = 0
+            d.flags |= _abi.AVR_SLICE_NEW_MODEL
+            return e, d, raw, e.desc.n_streams & 0xF0
+    return None

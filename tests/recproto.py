@@ -99,7 +99,7 @@ def parse(buf):
         elif num == 2:
             b = {}
             names = {1: "size", 2: "literal", 3: "skip_coded", 4: "cabac", 5: "length_parity", 6: "last_byte",
-                     7: "streams"}   # 7: this library's chunked mode only (wide slices), not in recode.proto
+                     7: "streams", 8: "escaped"}   # 7, 8: this library's chunked mode only, not in recode.proto
             for n2, v2 in _parse_msg(v):
                 b[names[n2]] = v2
             blocks.append(b)

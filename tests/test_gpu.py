@@ -297,3 +297,30 @@ def test_wide_slice_errors(ctx):
         d0.in_off, d0.in_size = 0, len(bad)
         r_d, _ = ctx.decompress([d0], bad)
         assert r_d[0].status != 0
+
+
+def test_escaped_slices_are_recoded_in_chunked_mode(ctx):
+    """slice_data with emulation-prevention bytes goes to the device unescaped and comes back
+    escaped; the reference's own format (file mode) still leaves such slices as literals."""
+    from test_host import ESCAPED_STREAM
+    data = H.gen_stream(**ESCAPED_STREAM)
+    ents = A.index_h264(data)
+    e, d, raw, lay = H.escaped_slice_case(data, ents)
+    res, blob = ctx.compress([d], raw)
+    r_o, b_o = H.oracle_compress([d], raw)
+    assert res[0].status == 0 and H.slices_of(res, blob) == H.slices_of(r_o, b_o)
+    want = data[e.desc.in_off:e.desc.in_off + e.desc.payload_size]
+    for k in (0, 2):                                           # ordinary and wide
+        d.n_streams = k
+        res, blob = ctx.compress([d], raw)
+        dd = H.coded_descs([d], res)
+        dd[0].n_streams = lay | k
+        r_d, b_d = ctx.decompress(dd, blob)
+        assert r_d[0].status == 0 and H.fix_tail(H.slices_of(r_d, b_d)[0], want) == want
+    rec_s = ctx.file_compress(data, A.MODE_SLICE)
+    rec_f = ctx.file_compress(data, A.MODE_FILE)
+    blocks_s = recproto.parse(rec_s)[1]
+    assert sum(1 for b in blocks_s if b.get("escaped")) == 1 and not any(b.get("skip_coded") for b in blocks_s)
+    assert sum(1 for b in recproto.parse(rec_f)[1] if b.get("skip_coded")) == 1
+    assert ctx.file_decompress(rec_s) == data and ctx.file_decompress(rec_f) == data
+    assert ctx.files_decompress(ctx.files_compress([data, data[:1000], data], A.MODE_SLICE)) == [data, data[:1000], data]

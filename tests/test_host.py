@@ -143,6 +143,38 @@ def test_wide_slices_on_host_round_trip(built, kw):
     assert sum(r.out_size for r in r_e) < 1.5 * sum(r.out_size for r in r_1) + 64 * len(descs)
 
 
+ESCAPED_STREAM = dict(width=640, height=368, frames=6, high=True, seed=108, kbps=9000)   # slice 4 has a 00 00 03 in its payload
+
+
+def test_escaped_slice_on_host_round_trips(built):
+    """Chunked mode recodes slices with emulation-prevention bytes (the reference leaves them literal): the
+    coder sees the unescaped slice_data -- same bytes as the oracle gives for it -- and decompression puts the
+    0x03 bytes back."""
+    data = H.gen_stream(**ESCAPED_STREAM)
+    ents = A.index_h264(data)
+    case = H.escaped_slice_case(data, ents)
+    assert case is not None and sum(1 for e in ents if not e.recodable) >= 1
+    e, d, raw, lay = case
+    assert not e.recodable                                    # file mode keeps the reference's behaviour
+    assert len(raw) < e.desc.payload_size
+    r_e, b_e = H.emu_compress([d], raw)
+    r_o, b_o = H.oracle_compress([d], raw)
+    assert r_e[0].status == 0 and H.slices_of(r_e, b_e) == H.slices_of(r_o, b_o)
+    dd = H.coded_descs([d], r_e)
+    dd[0].n_streams = lay                                     # header zeros + AVR_SLICE_ESCAPED
+    r_d, b_d = H.emu_decompress(dd, b_e)
+    want = data[e.desc.in_off:e.desc.in_off + e.desc.payload_size]
+    assert r_d[0].status == 0
+    assert H.fix_tail(H.slices_of(r_d, b_d)[0], want) == want
+    # and as a wide slice
+    d.n_streams = 2
+    r_e, b_e = H.emu_compress([d], raw)
+    dd = H.coded_descs([d], r_e)
+    dd[0].n_streams = lay | 2
+    r_d, b_d = H.emu_decompress(dd, b_e)
+    assert H.fix_tail(H.slices_of(r_d, b_d)[0], want) == want
+
+
 def test_manifest_matches_files():
     import hashlib
     for name, m in MANIFEST.items():
