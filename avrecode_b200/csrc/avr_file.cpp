@@ -223,10 +223,18 @@ static int compress_many(avr_ctx* ctx, const uint8_t* const* files, const uint64
     }
     if (!raws.empty()) {   // one arena: the files, then the unescaped copies
       uint64_t total = 0;
-      if (n_files == 1) { plans[0].base = 0; total = (sizes[0] + 15) & ~uint64_t(15); arena_store.resize(size_t(total)); memcpy(arena_store.data(), files[0], size_t(sizes[0])); }
-      else total = arena_bytes;
-      arena_store.resize(size_t(total) + raws.size() + 16);
-      memcpy(arena_store.data() + total, raws.data(), raws.size());
+      if (n_files == 1) {   // the file was going to be used in place: one copy, no zero fill first
+        plans[0].base = 0;
+        total = (sizes[0] + 15) & ~uint64_t(15);
+        arena_store.reserve(size_t(total) + raws.size() + 16);
+        arena_store.insert(arena_store.end(), files[0], files[0] + sizes[0]);
+        arena_store.resize(size_t(total));
+      } else {
+        total = arena_bytes;
+        arena_store.resize(size_t(total));
+      }
+      arena_store.insert(arena_store.end(), raws.begin(), raws.end());
+      arena_store.resize(arena_store.size() + 16);
       for (Plan& p : plans) for (int i = 0; i < p.n_ents; i++) if (p.coded[i] == 2) p.raw_off[i] += total;
       arena = arena_store.data(); arena_bytes = total + raws.size();
     }
