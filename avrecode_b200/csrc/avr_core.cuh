@@ -487,13 +487,15 @@ struct RingShared {
 AVR_DEV void ring_reset(RingShared* r) { r->tail_pub = 0; r->head_pub = 0; r->prod_tail = 0; r->cons_head = 0; }
 struct Producer {
   RingShared* r;
-  volatile uint32_t* ents;   // the entries: r->e, or (wide decompression) a much longer ring in global memory
+  volatile uint32_t* ents;   // the entries: r->e, or (wide slices) a much longer ring in global memory
   uint32_t cap;              // entries in ents, a power of two
+  uint32_t* far_base;        // wide compression: ring j lives at far_base + j * cap (null: the rings' own e[])
   uint32_t tail, limit, pub, head_seen;
   AVR_DEV void init(RingShared* ring, uint32_t* far_entries = nullptr, uint32_t far_cap = 0) {
     r = ring; tail = pub = head_seen = 0; limit = RING_PUBLISH;
     ents = far_entries ? far_entries : ring->e;
     cap = far_entries ? far_cap : uint32_t(RING_ENTRIES);
+    far_base = far_entries;
   }
   AVR_DEV void publish() {
     ring_fence();
@@ -506,11 +508,11 @@ struct Producer {
     const uint32_t a = head_seen + cap, b = pub + RING_PUBLISH;
     limit = int32_t(a - b) < 0 ? a : b;
   }
-  AVR_DEV void switch_to(RingShared* next) {   // wide compression: the next macroblock row goes to another ring
+  AVR_DEV void switch_to(RingShared* next, uint32_t index) {   // wide compression: the next macroblock row goes to another ring
     publish();
     r->prod_tail = tail;
     r = next;
-    ents = next->e;
+    ents = far_base ? far_base + size_t(index) * cap : next->e;
     tail = pub = r->prod_tail;
     head_seen = *reinterpret_cast<volatile uint32_t*>(&r->head_pub);
     slow();
@@ -581,7 +583,7 @@ struct Producer {
   RingShared* r;
   void init(RingShared* ring, uint32_t* = nullptr, uint32_t = 0) { r = ring; }
   void publish() {}
-  void switch_to(RingShared* next) { r = next; }
+  void switch_to(RingShared* next, uint32_t) { r = next; }
   void push(uint32_t e) { r->e.push_back(e); }
 };
 struct Consumer {
@@ -636,6 +638,65 @@ struct CoderCompress {     // estimators + range encoder (recode.cpp:1068-1096 h
         e = e_n; c = c_n; mg = mg_n;
       }
       q.release(k);
+      if (end) break;
+    }
+  }
+  // Wide slices: the ring is long and in global memory (far), so that this coder may fall a good part of a
+  // macroblock row behind the parser and catch up while the parser feeds the other stream.  ALL lanes call this:
+  // they stage up to 128 entries with coalesced loads, lane 0 runs the same pipelined loop over the stage.
+  // stage[0..127] entries, stage[128] != 0: SYM_END seen.
+  AVR_DEV void run_far(RingShared* r, const uint32_t* far, uint32_t far_cap, const SharedTables& t, uint16_t* cnt, uint32_t* stage, int lane) {
+    uint32_t head = 0;
+    for (;;) {
+      uint32_t n;
+#if defined(__CUDACC__) && !defined(AVR_HOST_EMULATION)
+      uint32_t avail;
+      for (uint32_t polls = 0; (avail = *reinterpret_cast<volatile uint32_t*>(&r->tail_pub) - head) == 0;) wide_backoff(polls);
+      ring_fence();
+      n = avail < 128u ? avail : 128u;
+      const volatile uint32_t* src = far;
+      for (uint32_t i = uint32_t(lane); i < n; i += 32) stage[i] = src[(head + i) & (far_cap - 1)];
+      __syncwarp();
+#else
+      (void)far; (void)far_cap;
+      n = uint32_t(r->e.size() - head > 128 ? 128 : r->e.size() - head);
+      for (uint32_t i = 0; i < n; i++) stage[i] = r->e[head + i];
+      if (n == 0) { stage[0] = SYM_END; n = 1; }
+#endif
+      if (lane == 0) {
+        uint32_t e = stage[0];
+        uint32_t c = cnt[e & 0xFFFF];
+        DivMagic mg = t.div[(c & 0xFF) + (c >> 8)];
+        uint32_t end = 0;
+#pragma unroll 1
+        for (uint32_t k = 0; k < n; k++) {
+          if (e & SYM_END) { end = 1; break; }
+          const uint32_t idx = e & 0xFFFF;
+          const int bit = int((e >> SYM_BIT_SHIFT) & 1);
+          const uint32_t e_n = stage[k + 1 < n ? k + 1 : k];
+          const uint32_t idx_n = e_n & 0xFFFF;
+          uint32_t c_n = cnt[idx_n];
+          uint32_t pos = c & 0xFF, neg = c >> 8;
+          const uint32_t pos0 = pos;
+          est_update(pos, neg, bit, idx >= CNT_SIG ? 0x50u : 0x60u);   // recode.cpp:1041-1042
+          const uint32_t c2 = pos | (neg << 8);
+          cnt[idx] = uint16_t(c2);
+          if (idx_n == idx) c_n = c2;
+          const DivMagic mg_n = t.div[(c_n & 0xFF) + (c_n >> 8)];
+          rc.put(mg, bit, pos0);
+          if (idx == CNT_TERM && bit) rc.finish();                      // recode.cpp:1092-1095
+          e = e_n; c = c_n; mg = mg_n;
+        }
+        stage[128] = end;
+#if defined(__CUDACC__) && !defined(AVR_HOST_EMULATION)
+        ring_fence();
+        *reinterpret_cast<volatile uint32_t*>(&r->head_pub) = head + n;
+#endif
+      }
+      AVR_SYNCWARP_CORE();
+      head += n;
+      const uint32_t end = stage[128];
+      AVR_SYNCWARP_CORE();
       if (end) break;
     }
   }
@@ -747,8 +808,8 @@ struct Compress {
   Producer q;
   U2* cstate;        // parser owns the CABAC context states
   AVR_DEV void begin(const uint8_t* src, uint32_t n, uint8_t* window, uint32_t tail_byte, RingShared* ring, uint16_t*, U2* states,
-                     uint32_t* = nullptr, uint32_t = 0) {
-    in.attach(src, n, window, tail_byte); q.init(ring); cstate = states;
+                     uint32_t* far_entries = nullptr, uint32_t far_cap = 0) {
+    in.attach(src, n, window, tail_byte); q.init(ring, far_entries, far_cap); cstate = states;
   }
   AVR_DEV void start_bins(const SharedTables&) { cabac.init(in); }
   AVR_DEV void finish_bins() {}

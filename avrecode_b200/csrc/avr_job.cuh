@@ -207,7 +207,7 @@ AVR_DEV void parser_end(Walker<Dir>& wk, int lane) {
 #pragma unroll 1
       for (uint32_t j = 0; j < wk.wide_k; j++) {
         if (j == wk.cur_ring) continue;
-        wk.dir.q.switch_to(&wk.rings[j]);
+        wk.dir.q.switch_to(&wk.rings[j], j);
         if (wk.status == WALK_OK) wk.dir.q.push(CNT_TERM | 1u << SYM_BIT_SHIFT);
         wk.dir.q.push(SYM_END);
         wk.dir.q.publish();
@@ -361,7 +361,7 @@ struct WideShared {
   uint32_t out_size[WIDE_MAX];   // compress: bytes of each stream;  decompress: [0] = bytes of the slice
   uint32_t overflow;
   uint32_t job;
-  uint32_t stage[34];            // decompress: the re-encoder's current batch of entries (CoderDecompress::run_wide)
+  uint32_t stage[WIDE_MAX][132]; // the batch of ring entries a coder warp is working on (decompress: [0] only)
 };
 
 struct WideMem {
@@ -392,8 +392,8 @@ AVR_DEV void wide_lane(Lane& ln, const WideMem& m, uint32_t j, uint32_t mbw) {
   WideShared* sh = m.sh;
   ln.tab = &sh->tab; ln.ring = &sh->ring[j]; ln.window = sh->window[j]; ln.cstate = sh->cstate;
   ln.walk = &sh->walk[j]; ln.row = m.rows + size_t(j) * mbw; ln.cnt = m.cnt + size_t(j) * MODEL_COUNTERS;
-  ln.far = Dir::kDecompress ? m.far + size_t(j) * m.far_cap : nullptr;
-  ln.far_cap = Dir::kDecompress ? m.far_cap : 0;
+  ln.far = m.far ? m.far + size_t(j) * m.far_cap : nullptr;   // compress: ring 0, the parser moves on from there
+  ln.far_cap = m.far ? m.far_cap : 0;
 }
 
 template <class Dir>
@@ -459,12 +459,10 @@ AVR_DEV void run_wide_job(const JobArgs& a, uint32_t s, const WideMem& m, int ti
       parser_end<Dir>(wk, lane);
     } else if (warp <= K) {
       const uint32_t j = warp - 1;
+      typename Dir::Coder c;
+      c.begin(out + hdr + size_t(j) * subcap, subcap);
+      c.run_far(&sh->ring[j], m.far + size_t(j) * m.far_cap, m.far_cap, sh->tab, m.cnt + size_t(j) * MODEL_COUNTERS, sh->stage[j], lane);
       if (lane == 0) {
-        typename Dir::Coder c;
-        c.begin(out + hdr + size_t(j) * subcap, subcap);
-        Consumer q;
-        q.init(&sh->ring[j], false);
-        c.run(q, sh->tab, m.cnt + size_t(j) * MODEL_COUNTERS, sh->cstate);
         sh->out_size[j] = c.out_bytes();
         if (c.overflowed()) sh->overflow = 1;
       }
@@ -474,7 +472,7 @@ AVR_DEV void run_wide_job(const JobArgs& a, uint32_t s, const WideMem& m, int ti
     if (warp == 0) {
       typename Dir::Coder c;
       c.begin(out, io.out_cap, esc_zeros);
-      c.run_wide(sh->ring, K, m.far, m.far_cap, sh->tab, sh->cstate, sh->stage, lane);
+      c.run_wide(sh->ring, K, m.far, m.far_cap, sh->tab, sh->cstate, sh->stage[0], lane);
       if (lane == 0) {
         sh->out_size[0] = c.out_bytes();
         if (c.overflowed()) sh->overflow = 1;
@@ -505,9 +503,7 @@ AVR_DEV void run_wide_job(const JobArgs& a, uint32_t s, const WideMem& m, int ti
     for (uint32_t j = 0; j < K; j++) {
       typename Dir::Coder c;
       c.begin(out + hdr + size_t(j) * subcap, subcap);
-      Consumer q;
-      q.init(&sh->ring[j]);
-      c.run(q, sh->tab, m.cnt + size_t(j) * MODEL_COUNTERS, sh->cstate);
+      c.run_far(&sh->ring[j], nullptr, 0, sh->tab, m.cnt + size_t(j) * MODEL_COUNTERS, sh->stage[j], lane);
       sh->out_size[j] = c.out_bytes();
       if (c.overflowed()) sh->overflow = 1;
     }
@@ -531,7 +527,7 @@ AVR_DEV void run_wide_job(const JobArgs& a, uint32_t s, const WideMem& m, int ti
     delete[] wk;
     typename Dir::Coder c;
     c.begin(out, io.out_cap, esc_zeros);
-    c.run_wide(sh->ring, K, m.far, m.far_cap, sh->tab, sh->cstate, sh->stage, lane);
+    c.run_wide(sh->ring, K, m.far, m.far_cap, sh->tab, sh->cstate, sh->stage[0], lane);
     sh->out_size[0] = c.out_bytes();
     if (c.overflowed()) sh->overflow = 1;
   }

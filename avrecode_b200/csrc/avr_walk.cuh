@@ -772,7 +772,7 @@ struct Walker {
     if (wide_k && wrapped) {
       if (!Dir::kDecompress) {   // next row -> next stream
         cur_ring = cur_ring + 1 == wide_k ? 0 : cur_ring + 1;
-        dir.q.switch_to(&rings[cur_ring]);
+        dir.q.switch_to(&rings[cur_ring], cur_ring);
       } else {                   // on to this warp's next row, K - 1 rows further down
         dir.row_end(last_qp_delta != 0);
         mb_y += int(wide_k) - 1;
