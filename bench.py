@@ -316,7 +316,23 @@ def run_ours(args):
     dom_ms = max(ms_c, ms_d)
     algo_bytes = payload + coded     # N + C per direction
     achieved = algo_bytes / dom_ms / 1e6
-    traffic = load_traffic().get(dom)
+    tr = load_traffic()
+    traffic = tr.get(dom)
+    # the bounds that mean something for a serial integer recurrence, from live numbers
+    f_hz = float((clocks or {}).get("sm_mhz") or 0) * 1e6
+    longest = max(r.n_bins for r in res)
+    inst = (tr.get("warp_inst_per_launch") or {}).get(dom)   # smsp__inst_executed.sum of the committed --set full capture
+    bins_s_dom = bins / dom_ms * 1e3
+    issue_peak = (148 * 4 * f_hz / (inst / bins)) if (inst and f_hz) else None
+    bounds = {
+        "latency": {"longest_slice_bins": int(longest), "mean_slice_bins": bins / max(1, len(descs)),
+                    "cycles_per_bin_on_longest_slice": (dom_ms * 1e-3 * f_hz / longest) if f_hz else None,
+                    "note": "a launch lasts as long as its longest slice; cycles/bin = kernel time x SM clock / its bins"},
+        "issue": {"achieved_bins_per_s": bins_s_dom, "peak_bins_per_s": issue_peak,
+                  "frac": (bins_s_dom / issue_peak) if issue_peak else None,
+                  "warp_inst_per_bin": (inst / bins) if inst else None,
+                  "note": "148 SM x 4 schedulers x f_SM / warp instructions per bin (ncu, spin-wait included)"},
+    }
     line = {
         "metric": METRIC, "value": total_bytes / dev_ms / 1e3, "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": max(3, args.warmup), "ms_per_step": dev_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -333,7 +349,7 @@ def run_ours(args):
                 "d2h_bytes_per_step": coded + payload + 64 * len(descs), "api": "avr_file_compress + avr_file_decompress (host buffers)"},
         "roofline": {"bound": "hbm", "kernel": ("avr_wide_kernel<%s> + avr_job_kernel<%s> (one launch pair, concurrent)" if n_wide else "avr_job_kernel<%s>%s") % (dom.capitalize(), "" if not n_wide else dom.capitalize()),
                      "achieved": achieved, "peak": peak,
-                     "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
+                     "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src, "bounds": bounds,
                      "note": "serial integer recurrence per slice: latency-bound, not HBM-bound; see DESIGN.md for the per-bin latency bound"},
         "clocks": clocks,
     }
