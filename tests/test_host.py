@@ -180,3 +180,23 @@ def test_manifest_matches_files():
     for name, m in MANIFEST.items():
         data, rec = load_case(name)
         assert hashlib.sha256(data).hexdigest() == m["sha256"] and hashlib.sha256(rec).hexdigest() == m["rec_sha256"]
+
+
+def test_bench_gate_digests_are_the_oracles(built):
+    """bench.py's pre-timing parity gate compares the CUDA bytes with tests/golden/bench_gate.json instead of running the
+    oracle; here (CPU) the pinned digests of the small workload are re-derived from the oracle."""
+    import hashlib, json, sys
+    sys.path.insert(0, H.ROOT)
+    import bench as B
+    with open(os.path.join(H.ROOT, "tests", "golden", "bench_gate.json")) as f:
+        pin = json.load(f)
+    assert set(pin["workloads"]) == set(B.WORKLOADS)
+    w = pin["workloads"]["cfg1"]
+    data, _ = B.gen_workload("cfg1", 0)
+    assert hashlib.sha256(data).hexdigest() == w["stream_sha256"]
+    plain = H.batch_descs(A.index_h264(data), mode_file=False)[:pin["n_slices"]]
+    r_o, b_o = H.oracle_compress(plain, data)
+    h = hashlib.sha256()
+    for s in H.slices_of(r_o, b_o):
+        h.update(len(s).to_bytes(8, "little")); h.update(s)
+    assert h.hexdigest() == w["coded_sha256"] and [int(r.n_bins) for r in r_o] == w["n_bins"]
