@@ -19,6 +19,8 @@ KEEP = [
     ("smsp__average_warps_issue_stalled_long_scoreboard_per_issue_active.ratio", "stalled_long_scoreboard_per_issue"),
     ("smsp__average_warps_issue_stalled_branch_resolving_per_issue_active.ratio", "stalled_branch_resolving_per_issue"),
     ("smsp__average_warps_issue_stalled_wait_per_issue_active.ratio", "stalled_wait_per_issue"),
+    ("smsp__average_warps_issue_stalled_no_instruction_per_issue_active.ratio", "stalled_no_instruction_per_issue"),
+    ("smsp__average_warps_issue_stalled_sleeping_per_issue_active.ratio", "stalled_sleeping_per_issue"),
     ("smsp__average_warp_latency_per_inst_issued.ratio", "warp_latency_per_inst_issued"),
     ("l1tex__t_sector_hit_rate.pct", "l1tex__t_sector_hit_rate"),
     ("lts__t_sector_hit_rate.pct", "lts__t_sector_hit_rate"),
