@@ -194,6 +194,9 @@ def load_peaks():
         return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+_OUT_FD = None
+
+
 def load_traffic():
     """dram bytes per launch of the dominant kernel from the committed ncu --set full capture, if any."""
     try:
@@ -376,7 +379,8 @@ def run_ours(args):
                 line["cpu_baseline"]["bytes_saved_frac"] = m["bytes_saved_frac"]
         except Exception as e:   # the baseline must never sink the GPU number
             line["cpu_baseline"] = {"error": str(e)}
-    print(json.dumps(line))
+    sys.stdout.flush()
+    os.write(_OUT_FD if _OUT_FD is not None else 1, (json.dumps(line) + "\n").encode())
     return 0
 
 
@@ -390,6 +394,12 @@ def main():
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference_arm(args)
+    # stdout carries the ONE JSON line and nothing else: libraries that write to fd 1 (NCCL prints its version there)
+    # are sent to stderr for the length of the run
+    global _OUT_FD
+    sys.stdout.flush()
+    _OUT_FD = os.dup(1)
+    os.dup2(2, 1)
     rc = run_ours(args)
     try:
         import torch.distributed as dist
