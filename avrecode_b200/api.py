@@ -64,6 +64,9 @@ def load_library():
     lib.avr_file_decompress.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]
     lib.avr_free.argtypes = [C.c_void_p]
     lib.avr_free.restype = None
+    lib.avr_probe_name.argtypes = [C.c_int]
+    lib.avr_probe_name.restype = C.c_char_p
+    lib.avr_probe.argtypes = [C.c_int, C.c_int, C.c_uint32, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
     _lib = lib
     return lib
 
@@ -100,6 +103,22 @@ def slice_streams(desc):
     lib.avr_slice_streams.argtypes = [C.POINTER(SliceDesc)]
     lib.avr_slice_streams.restype = C.c_int
     return int(lib.avr_slice_streams(C.byref(desc)))
+
+
+def probes(device=0, iters=20000):
+    """Single-lane microbenchmarks of the per-bin primitives: [(name, cycles per bin, bins)] measured on `device`."""
+    lib = load_library()
+    out = []
+    which = 0
+    while True:
+        name = lib.avr_probe_name(which)
+        if not name:
+            break
+        cyc, bins, chk = C.c_uint64(), C.c_uint64(), C.c_uint64()
+        _check(lib.avr_probe(device, which, iters, C.byref(cyc), C.byref(bins), C.byref(chk)), "avr_probe")
+        out.append((name.decode(), cyc.value / max(1, bins.value), bins.value))
+        which += 1
+    return out
 
 
 def index_h264(data):

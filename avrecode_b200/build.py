@@ -17,6 +17,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 CSRC = os.path.join(ROOT, "avrecode_b200", "csrc")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
+LIB_SOURCES = ("avr_lib.cu", "avr_probe.cu", "avr_file.cpp", "h264_index.cpp")
 
 
 def _newer(target, sources):
@@ -37,10 +38,26 @@ def build(force=False, with_ref=True):
     hdrs = [os.path.join(ROOT, "include", "avrecode_b200.h")] + [
         os.path.join(CSRC, f) for f in ("avr_core.cuh", "avr_walk.cuh", "avr_job.cuh", "avr_tables.h")]
     lib = os.path.join(ROOT, "avrecode_b200", "libavrecode_b200.so")
-    lib_src = [os.path.join(CSRC, f) for f in ("avr_lib.cu", "avr_file.cpp", "h264_index.cpp")]
-    if force or _newer(lib, lib_src + hdrs):
-        _run([NVCC, "-std=c++17", *ARCH, "-lineinfo", "-O3", "-Xcompiler", "-fPIC", "-shared", "-cudart", "static",
-              "-o", lib, *lib_src])
+    lib_src = [os.path.join(CSRC, f) for f in LIB_SOURCES]
+    # one object per source, compiled in parallel (nvcc spends ~40 s on each kernel file), then one link
+    objdir = os.path.join(ROOT, "build", "obj")
+    os.makedirs(objdir, exist_ok=True)
+    objs, jobs = [], []
+    for src in lib_src:
+        obj = os.path.join(objdir, os.path.basename(src) + ".o")
+        objs.append(obj)
+        if force or _newer(obj, [src] + hdrs):
+            if src.endswith(".cu"):
+                cmd = [NVCC, "-std=c++17", *ARCH, "-lineinfo", "-O3", "-Xcompiler", "-fPIC", "-c", "-o", obj, src]
+            else:
+                cmd = ["g++", "-std=c++17", "-O2", "-fPIC", "-c", "-o", obj, src]
+            print("+", " ".join(cmd), flush=True)
+            jobs.append((cmd, subprocess.Popen(cmd, cwd=ROOT)))
+    for cmd, p in jobs:
+        if p.wait() != 0:
+            raise subprocess.CalledProcessError(p.returncode, cmd)
+    if force or jobs or _newer(lib, objs):
+        _run([NVCC, *ARCH, "-shared", "-cudart", "static", "-o", lib, *objs])
     cli = os.path.join(ROOT, "avrecode_b200", "recode")
     cli_src = [os.path.join(CSRC, "recode_main.cpp")]
     if force or _newer(cli, cli_src + [lib]):

@@ -1,0 +1,279 @@
+// avr_probe.cu -- single-lane microbenchmarks of the per-bin primitives (C ABI: avr_probe).
+//
+// The hot path is a serial integer recurrence per slice, so its speed limit is "cycles per bin of one lane".
+// These probes MEASURE that floor on the device instead of asserting it (bench.py reports them as
+// roofline.bounds.latency.floor_cycles_per_bin): each runs ONE lane of ONE warp of ONE block over the exact
+// engine code of avr_core.cuh in a loop and returns clock64() cycles per iteration.  Inputs are pseudo-random
+// bytes / entries in shared memory: the engines do not care whether the bytes are a legal slice.
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "avr_job.cuh"
+
+using namespace avr;
+
+namespace {
+
+struct ProbeShared {
+  SharedTables tab;
+  RingShared ring;
+  alignas(16) uint8_t window[WIN_BYTES];
+  U2 cstate[N_CTX_PAD];
+  uint16_t cnt[4096];
+  uint8_t out[8192];
+};
+
+struct ProbeArgs {
+  uint32_t iters;
+  uint64_t* result;   // [0] cycles, [1] iterations (bins) done, [2] checksum (keeps the work alive)
+};
+
+__device__ __forceinline__ uint32_t lcg(uint32_t& s) { s = s * 1664525u + 1013904223u; return s >> 8; }
+
+__device__ void probe_setup(ProbeShared* sh, int tid, int nthreads) {
+  fill_shared_tables(&sh->tab, tid, nthreads);
+  uint32_t s = 12345u + uint32_t(tid) * 977u;
+  for (int i = tid; i < int(WIN_BYTES); i += nthreads) sh->window[i] = uint8_t(lcg(s));
+  for (int i = tid; i < N_CTX_PAD; i += nthreads) {
+    const uint32_t state = uint32_t(i * 7) % 100u;   // a spread of probabilities
+    sh->cstate[i].x = ctx_word_x(state);
+    sh->cstate[i].y = rlps4_of(state >> 1);
+  }
+  for (int i = tid; i < 4096; i += nthreads) sh->cnt[i] = 0x0101;
+  if (tid == 0) ring_reset(&sh->ring);
+}
+
+// 0: a chain of dependent integer instructions (the price of one instruction when nothing overlaps)
+__device__ void probe_alu(ProbeShared*, const ProbeArgs& a, uint64_t* r) {
+  uint32_t x = a.iters | 1u, y = 0x9E3779B9u;
+  const long long t0 = clock64();
+#pragma unroll 1
+  for (uint32_t i = 0; i < a.iters; i++) {
+#pragma unroll
+    for (int k = 0; k < 16; k++) { x = (x ^ y) + 0x3C6EF372u; x = (x << 1) | (x >> 31); }
+  }
+  const long long t1 = clock64();
+  r[0] = uint64_t(t1 - t0); r[1] = uint64_t(a.iters) * 32; r[2] = x;
+}
+
+// 1: CABAC decision on one context (H.264 9.3.3.2.1): the recurrence alone
+__device__ void probe_decide(ProbeShared* sh, const ProbeArgs& a, uint64_t* r) {
+  ByteWindow w; w.attach(sh->window, 0x7FFFFFFFu, sh->window, 0);
+  CabacIn c; c.init(w);
+  U2 ctx = sh->cstate[5];
+  uint32_t acc = 0;
+  const long long t0 = clock64();
+#pragma unroll 1
+  for (uint32_t i = 0; i < a.iters; i++) { U2 n; acc += uint32_t(c.decide_core(w, sh->tab, ctx, &n)); ctx = n; }
+  const long long t1 = clock64();
+  r[0] = uint64_t(t1 - t0); r[1] = a.iters; r[2] = acc + c.pos;
+}
+
+// 2: the compress-side significance loop of a 4x4 block (distinct contexts, branch on the bin, last flag)
+__device__ void probe_sigloop_c(ProbeShared* sh, const ProbeArgs& a, uint64_t* r) {
+  Compress d;
+  d.in.attach(sh->window, 0x7FFFFFFFu, sh->window, 0);
+  d.cstate = sh->cstate;
+  d.cabac.init(d.in);
+  uint64_t bins = 0, acc = 0;
+  const long long t0 = clock64();
+#pragma unroll 1
+  for (uint32_t i = 0; i < a.iters; i++) {
+    const int sig_base = 134, last_base = 195, coefs = 15;
+    uint64_t mask = 0;
+    int last;
+    U2 e_sig = d.sig_peek(sig_base);
+#pragma unroll 1
+    for (last = 0; last < coefs; last++) {
+      const U2 e_last = d.sig_peek(last_base + last);
+      const U2 e_next = d.sig_peek(sig_base + last + 1);
+      bins++;
+      if (d.sig_get_pre(sh->tab, e_sig, sig_base + last)) {
+        mask |= uint64_t(1) << last;
+        bins++;
+        if (d.sig_get_pre(sh->tab, e_last, last_base + last)) break;
+      }
+      e_sig = e_next;
+    }
+    acc += mask;
+  }
+  const long long t1 = clock64();
+  r[0] = uint64_t(t1 - t0); r[1] = bins; r[2] = acc + d.cabac.pos;
+}
+
+// 3: decompress-side bin: estimator load, exact division, range decode, update, store
+__device__ void probe_coded(ProbeShared* sh, const ProbeArgs& a, uint64_t* r) {
+  Decompress d;
+  d.in.attach(sh->window, 0x7FFFFFFFu, sh->window, 0);
+  d.cnt = sh->cnt;
+  d.rc.init(d.in);
+  uint32_t acc = 0;
+  const long long t0 = clock64();
+#pragma unroll 1
+  for (uint32_t i = 0; i < a.iters; i++) acc += uint32_t(d.coded(sh->tab, (i * 5u) & 63u, 0x60));
+  const long long t1 = clock64();
+  r[0] = uint64_t(t1 - t0); r[1] = a.iters; r[2] = acc + d.rc.pos;
+}
+
+// 4: the decompress-side significance loop (both successors prefetched), without the ring push
+__device__ void probe_sigloop_d(ProbeShared* sh, const ProbeArgs& a, uint64_t* r) {
+  Decompress d;
+  d.in.attach(sh->window, 0x7FFFFFFFu, sh->window, 0);
+  d.cnt = sh->cnt;
+  d.rc.init(d.in);
+  uint64_t bins = 0, acc = 0;
+  const long long t0 = clock64();
+#pragma unroll 1
+  for (uint32_t i = 0; i < a.iters; i++) {
+    const uint32_t slab = 64, nnz_true = 5, coefs = 15;
+    uint32_t observed = 0, zz = 0;
+    Decompress::SigEntry e_cur = d.sig_fetch(sh->tab, slab);
+#pragma unroll 1
+    while (observed < nnz_true && zz < coefs) {
+      const uint32_t idx = slab + observed * SIG_ZZ + zz;
+      const Decompress::SigEntry e0 = d.sig_fetch(sh->tab, idx + 1);
+      const Decompress::SigEntry e1 = d.sig_fetch(sh->tab, idx + 1 + SIG_ZZ);
+      const int s = d.sig_decode(e_cur, idx);
+      bins++;
+      if (s) { observed++; e_cur = e1; acc += zz; } else e_cur = e0;
+      zz++;
+    }
+  }
+  const long long t1 = clock64();
+  r[0] = uint64_t(t1 - t0); r[1] = bins; r[2] = acc + d.rc.pos;
+}
+
+__device__ void fill_ring(ProbeShared* sh, bool decompress) {
+  uint32_t s = 777u;
+  for (uint32_t i = 0; i + 1 < RING_ENTRIES; i++) {
+    const uint32_t rnd = lcg(s);
+    const uint32_t bit = (rnd & 7) < 2 ? 1u : 0u;
+    if (decompress) {
+      const uint32_t kind = (rnd >> 3) % 10 == 0 ? uint32_t(SYM_BYPASS) : uint32_t(SYM_DECISION);
+      sh->ring.e[i] = ((rnd >> 8) % 40u + 100u) | bit << SYM_BIT_SHIFT | kind;
+    } else {
+      sh->ring.e[i] = (CNT_CTX + (rnd >> 8) % 40u + 100u) | bit << SYM_BIT_SHIFT;
+    }
+  }
+  sh->ring.e[RING_ENTRIES - 1] = SYM_END;
+  sh->ring.tail_pub = RING_ENTRIES;
+  sh->ring.head_pub = 0;
+}
+
+// 5: the compress coder warp's loop (estimators + 64-bit range encoder) over a full ring
+__device__ void probe_coder_c(ProbeShared* sh, const ProbeArgs& a, uint64_t* r) {
+  fill_ring(sh, false);
+  uint64_t bins = 0;
+  CoderCompress c;
+  c.begin(sh->out, sizeof sh->out);
+  const long long t0 = clock64();
+#pragma unroll 1
+  for (uint32_t i = 0; i < a.iters; i++) {
+    Consumer q; q.init(&sh->ring);
+    c.run(q, sh->tab, sh->cnt, sh->cstate);
+    c.rc.sink.n = 0;
+    bins += RING_ENTRIES - 1;
+  }
+  const long long t1 = clock64();
+  r[0] = uint64_t(t1 - t0); r[1] = bins; r[2] = c.rc.low;
+}
+
+// 6: the decompress coder warp's loop (CABAC re-encoder) over a full ring
+__device__ void probe_coder_d(ProbeShared* sh, const ProbeArgs& a, uint64_t* r) {
+  fill_ring(sh, true);
+  uint64_t bins = 0;
+  CoderDecompress c;
+  c.begin(sh->out, sizeof sh->out);
+  const long long t0 = clock64();
+#pragma unroll 1
+  for (uint32_t i = 0; i < a.iters; i++) {
+    Consumer q; q.init(&sh->ring);
+    c.run(q, sh->tab, sh->cnt, sh->cstate);
+    c.cabac.sink.n = 0;
+    bins += RING_ENTRIES - 1;
+  }
+  const long long t1 = clock64();
+  r[0] = uint64_t(t1 - t0); r[1] = bins; r[2] = c.cabac.low;
+}
+
+// 7: ring push alone (what the parser pays per entry it hands over)
+__device__ void probe_push(ProbeShared* sh, const ProbeArgs& a, uint64_t* r) {
+  Producer q; q.init(&sh->ring);
+  const long long t0 = clock64();
+#pragma unroll 1
+  for (uint32_t i = 0; i < a.iters; i++) {
+    *reinterpret_cast<volatile uint32_t*>(&sh->ring.head_pub) = q.tail;   // a consumer that always keeps up
+    q.push(i | 1u << SYM_BIT_SHIFT);
+  }
+  const long long t1 = clock64();
+  r[0] = uint64_t(t1 - t0); r[1] = a.iters; r[2] = q.tail;
+}
+
+template <int WHICH>
+__global__ void __launch_bounds__(32, 1) avr_probe_kernel(ProbeArgs a) {
+  __shared__ ProbeShared sh;
+  probe_setup(&sh, threadIdx.x, 32);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint64_t r[3] = {0, 0, 0};
+    if (WHICH == 0) probe_alu(&sh, a, r);
+    if (WHICH == 1) probe_decide(&sh, a, r);
+    if (WHICH == 2) probe_sigloop_c(&sh, a, r);
+    if (WHICH == 3) probe_coded(&sh, a, r);
+    if (WHICH == 4) probe_sigloop_d(&sh, a, r);
+    if (WHICH == 5) probe_coder_c(&sh, a, r);
+    if (WHICH == 6) probe_coder_d(&sh, a, r);
+    if (WHICH == 7) probe_push(&sh, a, r);
+    a.result[0] = r[0]; a.result[1] = r[1]; a.result[2] = r[2];
+  }
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* avr_probe_name(int which) {
+  static const char* const names[] = {
+    "dependent integer instruction (ALU chain)",
+    "CABAC decision, one context (CabacIn::decide_core)",
+    "compress significance loop, 4x4 block (CABAC decode of sig/last bins)",
+    "decompress bin: estimator + exact division + RangeDec::get + update (Decompress::coded)",
+    "decompress significance loop, 4x4 block (both successors prefetched)",
+    "compress coder warp: estimators + RangeEnc::put over a ring (CoderCompress::run)",
+    "decompress coder warp: CABAC re-encoder over a ring (CoderDecompress::run)",
+    "ring push (Producer::push)",
+  };
+  return which >= 0 && which < int(sizeof names / sizeof names[0]) ? names[which] : nullptr;
+}
+
+// Runs probe `which` for `iters` iterations on `device`; returns cycles, bins (iterations) and a checksum.
+int avr_probe(int device, int which, uint32_t iters, uint64_t* cycles, uint64_t* bins, uint64_t* checksum) {
+  if (!cycles || !bins || !avr_probe_name(which)) return AVR_ERR_ARG;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0) { cudaGetLastError(); return AVR_ERR_NO_DEVICE; }
+  if (device < 0 || device >= ndev || cudaSetDevice(device) != cudaSuccess) return AVR_ERR_ARG;
+  uint64_t* d = nullptr;
+  if (cudaMalloc(reinterpret_cast<void**>(&d), 3 * sizeof(uint64_t)) != cudaSuccess) return AVR_ERR_NOMEM;
+  ProbeArgs a; a.iters = iters; a.result = d;
+  for (int rep = 0; rep < 2; rep++) {   // the first run also loads the kernel
+    switch (which) {
+      case 0: avr_probe_kernel<0><<<1, 32>>>(a); break;
+      case 1: avr_probe_kernel<1><<<1, 32>>>(a); break;
+      case 2: avr_probe_kernel<2><<<1, 32>>>(a); break;
+      case 3: avr_probe_kernel<3><<<1, 32>>>(a); break;
+      case 4: avr_probe_kernel<4><<<1, 32>>>(a); break;
+      case 5: avr_probe_kernel<5><<<1, 32>>>(a); break;
+      case 6: avr_probe_kernel<6><<<1, 32>>>(a); break;
+      default: avr_probe_kernel<7><<<1, 32>>>(a); break;
+    }
+    if (cudaDeviceSynchronize() != cudaSuccess) { cudaGetLastError(); cudaFree(d); return AVR_ERR_CUDA; }
+  }
+  uint64_t h[3] = {0, 0, 0};
+  const cudaError_t e = cudaMemcpy(h, d, sizeof h, cudaMemcpyDeviceToHost);
+  cudaFree(d);
+  if (e != cudaSuccess) return AVR_ERR_CUDA;
+  *cycles = h[0]; *bins = h[1];
+  if (checksum) *checksum = h[2];
+  return AVR_OK;
+}
+
+}  // extern "C"

@@ -86,6 +86,7 @@ typedef struct avr_slice_desc {
 #define AVR_STREAMS_MASK   0x0F
 #define AVR_ESC_ZEROS_SHIFT 4
 #define AVR_SLICE_ESCAPED  0x80
+#define AVR_MAX_PICTURE_MBS 139264u /* Level 6.2 MaxFS (H.264 table A-1): larger pictures are reported unsupported */
 #define AVR_MAX_STREAMS 2   /* what this build runs (two estimator sets fill an SM's shared memory); the blob format allows more */
 
 /* avr_slice_result.status */
@@ -160,7 +161,9 @@ int  avr_flush_l2(avr_ctx* ctx);                           /* bench hygiene: wri
 /* ---- host side: slice index + recode.proto container (no GPU needed) --------------------------
  * avr_index_h264 replaces what the reference gets from running libavcodec over the file
  * (recode.cpp:114-134 + find_next_coded_block_and_emit_literal :1275-1297): it scans an Annex-B
- * H.264 byte stream, parses SPS/PPS/slice headers and returns one entry per CABAC slice payload in
+ * H.264 byte stream -- or walks the AVC video track of an ISO base media file (mp4 / mov: avcC parameter
+ * sets, stsz/stsc/stco sample table, length-prefixed NAL units; what the reference gets from libavformat,
+ * recode.cpp:92, 118) -- parses SPS/PPS/slice headers and returns one entry per CABAC slice payload in
  * file order.  recodable == 0 marks payloads the reference would emit as skip_coded (NAL-escaped
  * payload, size < 8, CAVLC never listed). */
 typedef struct avr_index_entry {
@@ -196,6 +199,14 @@ int  avr_files_compress(avr_ctx* ctx, const uint8_t* const* files, const uint64_
 int  avr_files_decompress(avr_ctx* ctx, const uint8_t* const* recs, const uint64_t* rec_bytes, int n_files,
                           uint8_t** files, uint64_t* file_bytes);
 void avr_free(void* p);
+
+/* ---- measurement: single-lane microbenchmarks of the per-bin primitives ------------------------
+ * The path is a serial integer recurrence per slice (cabac_functions.h:113-132 is ~20 dependent operations per
+ * decision), so its speed limit is "cycles per bin of one lane".  avr_probe MEASURES that floor on `device`: probe
+ * `which` runs one lane over the engine code for `iters` iterations and returns clock cycles, bins done and a
+ * checksum.  avr_probe_name(which) describes it (NULL past the last probe).  No reference counterpart. */
+const char* avr_probe_name(int which);
+int  avr_probe(int device, int which, uint32_t iters, uint64_t* cycles, uint64_t* bins, uint64_t* checksum);
 
 #ifdef __cplusplus
 }

@@ -36,6 +36,13 @@ CASES = {
     # direct, both reference lists, 8x8 transform under direct_8x8_inference
     "main_b_2refs": dict(width=320, height=192, frames=8, bpics=0.6, refs=2, seed=5),
     "high_b_8x8_slices": dict(width=352, height=288, frames=8, bpics=0.6, refs=3, high=True, slices=2, seed=16, pskip=0.3),
+    # slice headers with ref_pic_list_modification, pred_weight_table and memory management control operations
+    # 1, 2, 4, 6: the host indexer must land on the same payload byte and slice QP as libavcodec does
+    "rich_headers_b": dict(width=320, height=192, frames=12, refs=3, bpics=0.4, rich_headers=True, slices=2, seed=77),
+    # the same kind of stream inside an mp4 container (avcC parameter sets, 4-byte NAL lengths, 3 samples per chunk):
+    # the reference demuxes it with libavformat (recode.cpp:92, 118), the indexer walks the boxes itself
+    "main_ip_mp4": dict(width=320, height=192, frames=7, slices=2, seed=21, mp4=dict(nal_len=4, chunk=3)),
+    "high_p_mp4_co64": dict(width=352, height=288, frames=5, high=True, refs=2, seed=22, mp4=dict(nal_len=2, chunk=2, co64=True)),
 }
 
 
@@ -52,8 +59,14 @@ def main():
     assert ref and ref_dbg and ref_h8, "build oracle/_ref first (oracle/build_ref.sh)"
     manifest = {}
     for name, kw in CASES.items():
-        data = H.gen_stream(**kw)
-        src = os.path.join(out_dir, name + ".h264")
+        gen_kw = {k: v for k, v in kw.items() if k != "mp4"}
+        data = H.gen_stream(**gen_kw)
+        ext = "h264"
+        if "mp4" in kw:
+            import mp4mux
+            data = mp4mux.mux(data, kw["width"], kw["height"], **kw["mp4"])
+            ext = "mp4"
+        src = os.path.join(out_dir, name + "." + ext)
         rec = os.path.join(out_dir, name + ".ref.rec")
         with open(src, "wb") as f:
             f.write(data)
@@ -63,7 +76,7 @@ def main():
         with open(rec, "rb") as f:
             rec_bytes = f.read()
         manifest[name] = {
-            "gen": kw, "bytes": len(data), "rec_bytes": len(rec_bytes), "sha256": sha(data), "rec_sha256": sha(rec_bytes),
+            "gen": kw, "ext": ext, "bytes": len(data), "rec_bytes": len(rec_bytes), "sha256": sha(data), "rec_sha256": sha(rec_bytes),
             "stock_reference_roundtrips": stock, "h8_patched_reference_roundtrips": h8,
         }
         print(name, manifest[name])

@@ -25,7 +25,7 @@ CASES = sorted(MANIFEST)
 
 
 def load_case(name):
-    with open(os.path.join(GOLD, name + ".h264"), "rb") as f:
+    with open(os.path.join(GOLD, name + "." + MANIFEST[name].get("ext", "h264")), "rb") as f:
         data = f.read()
     with open(os.path.join(GOLD, name + ".ref.rec"), "rb") as f:
         rec = f.read()

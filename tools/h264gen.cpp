@@ -107,6 +107,8 @@ struct GenConfig {
   int num_refs = 2;
   double p_bpic = 0.0;     // P(a non-intra picture is coded as B slices); B pictures stay reference pictures
   bool ragged_slices = false;  // slice boundaries at arbitrary macroblocks instead of row starts
+  bool rich_headers = false;   // slice headers with ref_pic_list_modification, pred_weight_table and memory management
+                               // control operations 1, 2, 4, 6 -- syntax the slice indexer has to get past exactly
   uint64_t seed = 1;
 };
 
@@ -248,7 +250,7 @@ static std::vector<uint8_t> make_pps(const GenConfig& c) {
   b.u(1, 0);   // bottom_field_pic_order_in_frame_present
   b.ue(0);     // slice groups
   b.ue(0); b.ue(0);  // num_ref_idx_default_active_minus1
-  b.u(1, 0); b.u(2, 0);  // weighted pred / bipred
+  b.u(1, c.rich_headers ? 1 : 0); b.u(2, c.rich_headers ? 1 : 0);  // weighted_pred_flag / weighted_bipred_idc (1 = explicit)
   b.se(0); b.se(0); b.se(0);  // pic_init_qp-26, qs, chroma_qp_index_offset
   b.u(1, 1);   // deblocking_filter_control_present
   b.u(1, 0);   // constrained_intra_pred
@@ -306,11 +308,38 @@ static std::vector<uint8_t> generate(const GenConfig& c, GenStats* st) {
       if (!intra) {
         b.u(1, 1); b.ue(uint32_t(nref - 1));  // num_ref_idx_active_override
         if (bpic) b.ue(uint32_t(nref - 1));   // num_ref_idx_l1_active_minus1
-        b.u(1, 0);            // ref_pic_list_modification_flag_l0
-        if (bpic) b.u(1, 0);  // ref_pic_list_modification_flag_l1
+        if (!c.rich_headers) {
+          b.u(1, 0);            // ref_pic_list_modification_flag_l0
+          if (bpic) b.u(1, 0);  // ref_pic_list_modification_flag_l1
+        } else {
+          // H.264 7.3.3.1: "previous picture first" spelled out (idc 0, abs_diff_pic_num_minus1 0, end) -- a no-op reordering
+          for (int l = 0; l < (bpic ? 2 : 1); l++) { b.u(1, 1); b.ue(0); b.ue(0); b.ue(3); }
+          // pred_weight_table (7.3.3.2): denominators, then per reference optional luma / chroma weights
+          b.ue(uint32_t(rng.below(8)));
+          b.ue(uint32_t(rng.below(8)));
+          for (int l = 0; l < (bpic ? 2 : 1); l++)
+            for (int r = 0; r < nref; r++) {
+              const int lf = rng.bern(0.5);
+              b.u(1, uint32_t(lf));
+              if (lf) { b.se(rng.below(255) - 127); b.se(rng.below(255) - 127); }
+              const int cf = rng.bern(0.5);
+              b.u(1, uint32_t(cf));
+              if (cf) for (int k = 0; k < 4; k++) b.se(rng.below(255) - 127);
+            }
+        }
       }
       if (idr) { b.u(1, 0); b.u(1, 0); }  // no_output_of_prior_pics, long_term_reference_flag
-      else b.u(1, 0);                     // adaptive_ref_pic_marking_mode_flag
+      else if (!c.rich_headers || intra) b.u(1, 0);   // adaptive_ref_pic_marking_mode_flag
+      else {
+        // dec_ref_pic_marking (7.3.3.3) with operations 4 + 6 (this picture becomes long-term reference 0), later 2
+        // (long-term picture 0 is dropped) and 1 (the oldest short-term picture is dropped).  The pictures still
+        // reference whatever libavcodec keeps: only the SYNTAX matters to a stream that is never displayed.
+        b.u(1, 1);
+        const int phase = f % 4;
+        if (phase == 1) { b.ue(4); b.ue(2); b.ue(6); b.ue(0); }
+        else if (phase == 3) { b.ue(2); b.ue(0); if (f > c.num_refs + 1 && c.num_refs >= 2) { b.ue(1); b.ue(uint32_t(c.num_refs - 1)); } }
+        b.ue(0);
+      }
       int cabac_init_idc = intra ? 0 : rng.below(3);
       if (!intra) b.ue(uint32_t(cabac_init_idc));
       int qp = c.qp + rng.below(5) - 2;
@@ -351,7 +380,7 @@ static void usage() {
   fprintf(stderr,
           "usage: h264gen -o out.h264 [--width W --height H | --mbw N --mbh N] [--frames N] [--slices N]\n"
           "       [--high] [--p8x8 P] [--intra-period N] [--qp Q] [--density D] [--kbps K --fps F]\n"
-          "       [--pskip P] [--pintra P] [--pdense P] [--refs N] [--bpics P] [--ragged] [--seed S]\n");
+          "       [--pskip P] [--pintra P] [--pdense P] [--refs N] [--bpics P] [--ragged] [--rich-headers] [--seed S]\n");
 }
 
 int main(int argc, char** argv) {
@@ -381,6 +410,7 @@ int main(int argc, char** argv) {
     else if (a == "--refs") c.num_refs = atoi(next());
     else if (a == "--bpics") c.p_bpic = atof(next());
     else if (a == "--ragged") c.ragged_slices = true;
+    else if (a == "--rich-headers") c.rich_headers = true;
     else if (a == "--seed") c.seed = strtoull(next(), nullptr, 10);
     else { usage(); return 2; }
   }
