@@ -29,11 +29,11 @@
 
 #if defined(__CUDACC__) && !defined(AVR_HOST_EMULATION)
 #define AVR_DEV __device__ __forceinline__
-#define AVR_DEV_NOINLINE __device__ __noinline__
+#define AVR_DEV_NOINLINE static __device__ __noinline__
 #define AVR_TABLE_QUAL static __constant__ const
 #else
 #define AVR_DEV inline
-#define AVR_DEV_NOINLINE inline
+#define AVR_DEV_NOINLINE static inline
 #define AVR_TABLE_QUAL static const
 #endif
 #include "avr_tables.h"
@@ -51,8 +51,10 @@ constexpr int dctx(int ctx_idx) { return ctx_idx < 277 ? ctx_idx : ctx_idx < 101
 AVR_DEV int ctx_idx_of_dense(int i) { return i < 277 ? i : i < 314 ? i - 277 + 399 : i - 314 + 1012; }
 
 // ------------------------------------------------------------------------------------------------
-// Estimator tables of one model (recode.cpp:1057-1058), compacted.  One estimator = {pos, neg}
-// bytes packed in a u16 (pos | neg << 8); both start at 1 and never exceed 0x61 (recode.cpp:1030-1047).
+// Estimator tables of one model (recode.cpp:1057-1058), compacted.  One estimator = {pos, pos + neg}
+// bytes packed in a u16 (pos | total << 8): the coders need the total for the reciprocal and pos for the
+// product, and an update is ONE add (bin + 0x100).  pos and neg start at 1 (EST_INIT) and the total never
+// exceeds 0x61 (recode.cpp:1030-1047).
 //
 //   [CNT_CTX, +N_CTX_PAD)  ordinary bins, keyed by (dense) ctxIdx            (recode.cpp:679-683)
 //   CNT_BYPASS, CNT_TERM   the adaptive bypass / terminate estimators         (recode.cpp:1183, 1190)
@@ -80,9 +82,11 @@ enum : uint32_t {
   SIG_CAT_8 = 2080 * SIG_ZZ,                    // key 0 (= 64 coefficients): observed < 64; key n: observed < n
   SIG_ENTRIES = SIG_OFF_CAT5 + SIG_CAT_8,       // 44160
   MODEL_COUNTERS = CNT_SIG + SIG_ENTRIES,       // 47892 estimators = 95784 bytes
+  MODEL_COUNTERS_PAD = MODEL_COUNTERS + 36,     // the coders prefetch the estimator one step past a block (<= +17): allocated, never used
+  EST_INIT = 0x0201,                            // {pos = 1, neg = 1}
   NNZ_STRIDE = 52,                              // FrameBuffer meta: 51 block slots + pad per macroblock
 };
-static_assert(MODEL_COUNTERS % 2 == 0 && MODEL_COUNTERS < 65536, "counter index must fit 16 bits");
+static_assert(MODEL_COUNTERS % 2 == 0 && MODEL_COUNTERS_PAD % 8 == 0 && MODEL_COUNTERS_PAD < 65536, "counter index must fit 16 bits");
 
 AVR_DEV uint32_t nz_group(int cat, bool is8) {
   if (cat == 5) return NZ_OFF_CAT5;
@@ -279,9 +283,9 @@ struct ByteSink {
   uint32_t n, cap, pending;
   int cache;          // -1 = nothing cached yet
   int esc;            // >= 0: emulation prevention (H.264 7.4.1) is applied on the way out, esc = zero bytes just written
-  bool overflow;
-  AVR_DEV void init(uint8_t* o, uint32_t c, int esc_zeros = -1) { out = o; n = 0; cap = c; pending = 0; cache = -1; esc = esc_zeros; overflow = false; }
-  AVR_DEV void store(uint32_t b) { if (n < cap) out[n] = uint8_t(b); else overflow = true; n++; }
+  uint32_t overflow;
+  AVR_DEV void init(uint8_t* o, uint32_t c, int esc_zeros = -1) { out = o; n = 0; cap = c; pending = 0; cache = -1; esc = esc_zeros; overflow = 0; }
+  AVR_DEV void store(uint32_t b) { if (n < cap) out[n] = uint8_t(b); else overflow = 1; n++; }
   AVR_DEV void raw(uint32_t b) {
     if (esc >= 0) {   // chunked mode, escaped slices: 00 00 0x (x <= 3) becomes 00 00 03 0x
       if (esc >= 2 && b <= 3) { store(3); esc = 0; }
@@ -308,6 +312,10 @@ struct ByteSink {
     cache = -1;
   }
 };
+// The sink lives in shared memory and is only touched once per output BYTE (every 8-9 bins), through ONE out-of-line
+// copy of its code: inlined at every bin site it was a third of the kernels' instructions (instruction cache).
+// dc: bits 0..7 the byte, bit 8 the carry into the bytes before it.
+AVR_DEV_NOINLINE void sink_push(ByteSink* s, uint32_t dc) { s->push(dc & 0xFF, dc >> 8); }
 
 // ------------------------------------------------------------------------------------------------
 // avrecode's 64-bit range coder, arithmetic_code<uint64_t, uint8_t> (arithmetic_code.h:31-299):
@@ -319,14 +327,13 @@ struct ByteSink {
 
 struct RangeEnc {
   uint64_t low, range;
-  ByteSink sink;
-  AVR_DEV void init(uint8_t* out, uint32_t cap) { low = 0; range = uint64_t(1) << 63; sink.init(out, cap); }
+  ByteSink* sink;
+  AVR_DEV void init(ByteSink* s, uint8_t* out, uint32_t cap) { low = 0; range = uint64_t(1) << 63; sink = s; s->init(out, cap); }
   AVR_DEV void shift_byte() {
-    const uint32_t carry = uint32_t(low >> 63);
-    const uint32_t digit = uint32_t(low >> 55) & 0xFF;
+    const uint32_t dc = uint32_t(low >> 55);   // digit + carry
     low = (low & ((uint64_t(1) << 55) - 1)) << 8;
     range <<= 8;
-    sink.push(digit, carry);
+    sink_push(sink, dc);
   }
   AVR_DEV void put(const DivMagic& mg, int bit, uint32_t pos) {   // mg = t.div[pos + neg]
     const uint64_t r1 = div_magic(range, mg) * pos;
@@ -334,41 +341,57 @@ struct RangeEnc {
     if (bit) { low += r0; range = r1; } else range = r0;
     if (range < AVR_MIN_RANGE) { do shift_byte(); while (range < AVR_NORM_RANGE); }
   }
-  AVR_DEV void finish() {   // arithmetic_code.h:128-144
-    for (uint64_t stop = uint64_t(1) << 62; stop > 0; stop >>= 1) {
-      const uint64_t x = (low | stop) & ~(stop - 1);
-      if (stop < range && low <= x && x < low + range) { low = x; break; }
-    }
-    while (low != 0) { range = 1; shift_byte(); }
-    sink.flush();
-  }
 };
+// arithmetic_code.h:128-144, once per slice
+AVR_DEV_NOINLINE void range_enc_finish(ByteSink* sink, uint64_t low, uint64_t range) {
+  for (uint64_t stop = uint64_t(1) << 62; stop > 0; stop >>= 1) {
+    const uint64_t x = (low | stop) & ~(stop - 1);
+    if (stop < range && low <= x && x < low + range) { low = x; break; }
+  }
+  while (low != 0) {
+    const uint32_t dc = uint32_t(low >> 55);
+    low = (low & ((uint64_t(1) << 55) - 1)) << 8;
+    sink->push(dc & 0xFF, dc >> 8);
+  }
+  sink->flush();
+}
 
+// The decoder's read position: shared memory, touched once per input byte through ONE out-of-line copy.
+struct DecHome {
+  const uint8_t* win;   // the input window
+  uint32_t skew, pos, next;
+};
+AVR_DEV_NOINLINE uint32_t dec_digit(DecHome* h) {  // arithmetic_code.h:259-275: digits are read one bit off the byte grid
+  const uint32_t b = h->win[(h->pos + h->skew) & (WIN_BYTES - 1)];
+  const uint32_t d = ((h->next << 7) | (b >> 1)) & 0xFF;
+  h->pos++;
+  h->next = b;
+  return d;
+}
 struct RangeDec {
   uint64_t low, range;
-  uint32_t pos, next;
-  AVR_DEV void consume(const ByteWindow& w) {  // arithmetic_code.h:259-275: digits are read one bit off the byte grid
-    const uint32_t b = w.byte(pos++);
-    const uint32_t d = ((next << 7) | (b >> 1)) & 0xFF;
-    next = b;
-    low = (low << 8) | d;
+  DecHome* home;
+  AVR_DEV void consume() {
+    low = (low << 8) | dec_digit(home);
     range <<= 8;
   }
-  AVR_DEV void init(const ByteWindow& w) {  // arithmetic_code.h:218-230
-    pos = 0;
-    next = w.byte(pos++);
-    low = next >> 1;
+  AVR_DEV void init(DecHome* h, const ByteWindow& w) {  // arithmetic_code.h:218-230
+    home = h;
+    h->win = w.win; h->skew = w.skew; h->pos = 1;
+    h->next = w.byte(0);
+    low = h->next >> 1;
     range = 128;
-    for (int i = 0; i < 7; i++) consume(w);
+    for (int i = 0; i < 7; i++) consume();
   }
-  AVR_DEV int get(const ByteWindow& w, const DivMagic& mg, uint32_t pos_) {   // mg = t.div[pos + neg]
+  AVR_DEV int get(const DivMagic& mg, uint32_t pos_) {   // mg = t.div[pos + neg]
     const uint64_t r1 = div_magic(range, mg) * pos_;
     const uint64_t r0 = range - r1;
     const int bit = low >= r0;
     if (bit) { low -= r0; range = r1; } else range = r0;
-    if (range < AVR_MIN_RANGE) { do consume(w); while (range < AVR_NORM_RANGE); }
+    if (range < AVR_MIN_RANGE) { do consume(); while (range < AVR_NORM_RANGE); }
     return bit;
   }
+  AVR_DEV uint32_t pos() const { return home->pos; }
 };
 
 // ------------------------------------------------------------------------------------------------
@@ -379,14 +402,14 @@ struct RangeDec {
 struct CabacOut {
   uint32_t low, range;
   int queue;
-  ByteSink sink;
-  AVR_DEV void init(uint8_t* out, uint32_t cap, int esc_zeros = -1) { low = 0; range = 510; queue = -9; sink.init(out, cap, esc_zeros); }
+  ByteSink* sink;
+  AVR_DEV void init(ByteSink* s, uint8_t* out, uint32_t cap, int esc_zeros = -1) { low = 0; range = 510; queue = -9; sink = s; s->init(out, cap, esc_zeros); }
   AVR_DEV void put_bytes() {
     while (queue >= 0) {
       const uint32_t o = low >> (queue + 10);
       low &= (0x400u << queue) - 1;
       queue -= 8;
-      sink.push(o & 0xFF, o >> 8);
+      sink_push(sink, o & 0x1FF);
     }
   }
   // core of a decision, the mirror image of CabacIn::decide_core: consumes context entry e, leaves the successor
@@ -427,9 +450,9 @@ struct CabacOut {
       queue += 10;
       put_bytes();
       if (queue > -8) { low <<= -queue; queue = 0; put_bytes(); }  // rbsp_alignment_zero_bits
-      sink.flush();
+      sink->flush();
       // "Omit trailing byte if it's only a stop bit" (recode.cpp:1501-1505)
-      if (sink.n > 0 && sink.n <= sink.cap && sink.out[sink.n - 1] == 0x80) sink.n--;
+      if (sink->n > 0 && sink->n <= sink->cap && sink->out[sink->n - 1] == 0x80) sink->n--;
     } else if (range < 256) {
       range <<= 1; low <<= 1; queue += 1;
       put_bytes();
@@ -437,20 +460,53 @@ struct CabacOut {
   }
 };
 
-AVR_DEV void est_update(uint32_t& pos, uint32_t& neg, int bit, uint32_t limit) {  // recode.cpp:1035-1045
-  if (bit) pos++; else neg++;
-  if (pos + neg > limit) { pos = (pos + 1) >> 1; neg = (neg + 1) >> 1; }
+// Estimator update (recode.cpp:1035-1045): count the bin, halve both counts (rounding up) past the limit.
+AVR_DEV uint32_t est_halve(uint32_t c) {
+  uint32_t pos = c & 0xFF, neg = (c >> 8) - pos;
+  pos = (pos + 1) >> 1; neg = (neg + 1) >> 1;
+  return pos | (pos + neg) << 8;
 }
+AVR_DEV uint32_t est_next(uint32_t c, uint32_t bit, uint32_t limit) {
+  uint32_t c2 = c + bit + 0x100u;
+  if (c2 >= ((limit + 1u) << 8)) c2 = est_halve(c2);
+  return c2;
+}
+// limits: 0x50 while the bin is a significance-map bin, else 0x60 (recode.cpp:1041-1042)
+enum : uint32_t { LIMIT_SIG = 0x50, LIMIT_ANY = 0x60 };
+
+// (dense) ctxIdx bases per block category 0..5 (h264_cabac.c:1589-1599, :1556)
+enum : int { CTX_SIG8 = 402 - 399 + 277, CTX_LAST8 = 417 - 399 + 277, CTX_ABS8 = 426 - 399 + 277, CTX_CBF8 = 1012 - 1012 + 314 };
+AVR_TABLE_QUAL int16_t k_sig_base[6] = {105, 120, 134, 149, 152, CTX_SIG8};
+AVR_TABLE_QUAL int16_t k_last_base[6] = {166, 181, 195, 210, 213, CTX_LAST8};
+AVR_TABLE_QUAL int16_t k_abs_base[6] = {227, 237, 247, 257, 266, CTX_ABS8};
+AVR_TABLE_QUAL int16_t k_cbf_base[6] = {85, 89, 93, 97, 101, CTX_CBF8};
+
+// coefficients of a residual block by category (h264_cabac.c:1813-1818)
+AVR_TABLE_QUAL uint8_t k_maxc[8] = {16, 15, 16, 4, 15, 64, 0, 0};
 
 // ------------------------------------------------------------------------------------------------
 // Symbol ring between the parser warp and the coder warp of a block (single producer, single
-// consumer, shared memory).  Entry: bits 0..15 index (estimator index when compressing, dense ctx
-// when decompressing), bit 16 the bin, bits 20..21 the CABAC primitive (decompress), bit 31 = END.
-// The producer publishes its tail every RING_PUBLISH entries and at macroblock ends; the consumer
-// publishes its head every RING_PUBLISH entries.
+// consumer).  The unit is an ENTRY of 1..4 words; what crosses is syntax, not bins:
+//
+//   plain bin   bits 0..15 index (estimator index when compressing, dense ctx when decompressing),
+//               bit 16 the bin, bits 20..21 the CABAC primitive (decompress)
+//   SYM_LEVEL   one coefficient level: bits 0..8 first context, 9 its bin, 10..18 the "greater than one"
+//               context, 19..22 how many 1-bins it coded, 23 whether a 0-bin ended that run, 24 whether
+//               the sign follows, 25 the sign (bypass)
+//   SYM_BLOCK   one residual block's significance map: bits 0..2 category, 8..14 coefficients (1..64);
+//               compress adds bit 15 "the macroblock has an 8x8 block" (NZ key, recode.cpp:884), bit 16
+//               "left neighbour exists" and a word {left, above, previous-picture count} for the nnz side
+//               channel (recode.cpp:844-930); then the 64-bit significance mask, one word unless category 5.
+//               The coder derives every bin from it: the compress coder the nnz bits and the model-coded
+//               significance bins (last_significant_coeff_flag is never coded, recode.cpp:1073), the
+//               decompress coder the CABAC significant_coeff_flag / last_significant_coeff_flag bins.
+//   SYM_END     end of the slice
+//
+// The producer publishes its tail between entries only (every RING_PUBLISH words and at macroblock
+// ends), so an entry the consumer can see the first word of is complete.
 // ------------------------------------------------------------------------------------------------
 enum : uint32_t {
-  RING_ENTRIES = 512, RING_PUBLISH = 64, RING_BATCH = 128,
+  RING_ENTRIES = 512, RING_PUBLISH = 64, RING_BATCH = 128, ENTRY_MAX_WORDS = 4,
   SYM_BIT_SHIFT = 16, SYM_KIND_SHIFT = 20, SYM_DECISION = 0u << 20, SYM_BYPASS = 1u << 20, SYM_TERMINATE = 2u << 20,
   SYM_END = 1u << 31,
   // Wide slices only (one slice spread over several range-coder streams, macroblock row r in stream
@@ -460,10 +516,8 @@ enum : uint32_t {
   //               re-encoder, which sees the rows in order; the bin value sits at SYM_BIT_SHIFT
   SYM_SPECIAL = 3u << 20, SP_ROW_END = 1u << 8, SP_QPD = 2u << 8,
   WIDE_MAX = 2,          // most streams per wide slice: every stream's estimators are resident in shared memory
-  // Decompression sends one coefficient level as ONE entry (per-bin pushes were ~10 % of its parser):
-  //   bits 0..8 first context, 9 its bin, 10..18 the "greater than one" context, 19..22 how many 1-bins it
-  //   coded, 23 whether a 0-bin ended that run, 24 whether the sign follows, 25 the sign (bypass).
   SYM_LEVEL = 1u << 30, LVL_BIT1 = 9, LVL_GCTX = 10, LVL_RUN = 19, LVL_TERM = 23, LVL_HAS_SIGN = 24, LVL_SIGN = 25,
+  SYM_BLOCK = 1u << 29, BLK_NNZ = 8, BLK_MB8 = 15, BLK_HAS_LEFT = 16,
 };
 AVR_DEV uint32_t lvl_entry(int ctx1, int b1, int gctx, int run, int term, int has_sign, int sign) {
   return SYM_LEVEL | uint32_t(ctx1) | uint32_t(b1) << LVL_BIT1 | uint32_t(gctx) << LVL_GCTX | uint32_t(run) << LVL_RUN |
@@ -485,14 +539,24 @@ struct RingShared {
   uint32_t prod_tail, cons_head;   // wide slices: where a producer / consumer that moved to another ring left off
 };
 AVR_DEV void ring_reset(RingShared* r) { r->tail_pub = 0; r->head_pub = 0; r->prod_tail = 0; r->cons_head = 0; }
+// makes room for an entry of n words: publishes what is complete, waits for the consumer if the ring is full; returns
+// the tail value up to which the producer may go on without looking again.  One out-of-line copy (instruction cache).
+AVR_DEV_NOINLINE uint32_t ring_slow(RingShared* r, uint32_t tail, uint32_t n, uint32_t cap) {
+  ring_fence();
+  *reinterpret_cast<volatile uint32_t*>(&r->tail_pub) = tail;
+  uint32_t head_seen;
+  do head_seen = *reinterpret_cast<volatile uint32_t*>(&r->head_pub); while (tail + n - head_seen > cap);
+  const uint32_t a = head_seen + cap, b = tail + RING_PUBLISH;
+  return int32_t(a - b) < 0 ? a : b;
+}
 struct Producer {
   RingShared* r;
-  volatile uint32_t* ents;   // the entries: r->e, or (wide slices) a much longer ring in global memory
-  uint32_t cap;              // entries in ents, a power of two
+  uint32_t* ents;            // the entries: r->e, or (wide slices) a much longer ring in global memory
+  uint32_t cap;              // words in ents, a power of two
   uint32_t* far_base;        // wide compression: ring j lives at far_base + j * cap (null: the rings' own e[])
-  uint32_t tail, limit, pub, head_seen;
+  uint32_t tail, limit;
   AVR_DEV void init(RingShared* ring, uint32_t* far_entries = nullptr, uint32_t far_cap = 0) {
-    r = ring; tail = pub = head_seen = 0; limit = RING_PUBLISH;
+    r = ring; tail = 0; limit = RING_PUBLISH;
     ents = far_entries ? far_entries : ring->e;
     cap = far_entries ? far_cap : uint32_t(RING_ENTRIES);
     far_base = far_entries;
@@ -500,29 +564,23 @@ struct Producer {
   AVR_DEV void publish() {
     ring_fence();
     *reinterpret_cast<volatile uint32_t*>(&r->tail_pub) = tail;
-    pub = tail;
   }
-  AVR_DEV void slow() {
-    publish();
-    while (tail - head_seen >= cap) head_seen = *reinterpret_cast<volatile uint32_t*>(&r->head_pub);
-    const uint32_t a = head_seen + cap, b = pub + RING_PUBLISH;
-    limit = int32_t(a - b) < 0 ? a : b;
+  AVR_DEV void reserve(uint32_t n) { if (int32_t(limit - tail) < int32_t(n)) limit = ring_slow(r, tail, n, cap); }
+  AVR_DEV void put(uint32_t w) {
+#ifdef AVR_PROBE_NO_PUSH
+    if (!(w & SYM_END)) return;
+#endif
+    ents[tail & (cap - 1)] = w;
+    tail++;
   }
+  AVR_DEV void push(uint32_t e) { reserve(1); put(e); }
   AVR_DEV void switch_to(RingShared* next, uint32_t index) {   // wide compression: the next macroblock row goes to another ring
     publish();
     r->prod_tail = tail;
     r = next;
     ents = far_base ? far_base + size_t(index) * cap : next->e;
-    tail = pub = r->prod_tail;
-    head_seen = *reinterpret_cast<volatile uint32_t*>(&r->head_pub);
-    slow();
-  }
-  AVR_DEV void push(uint32_t e) {
-#ifdef AVR_PROBE_NO_PUSH
-    if (!(e & SYM_END)) return;
-#endif
-    ents[tail & (cap - 1)] = e;
-    if (++tail == limit) slow();
+    tail = r->prod_tail;
+    limit = ring_slow(r, tail, ENTRY_MAX_WORDS, cap);
   }
 };
 struct Consumer {
@@ -530,40 +588,21 @@ struct Consumer {
   uint32_t head, tail_seen;
   bool patient;   // wide slices: long waits, see wide_backoff
   AVR_DEV void init(RingShared* ring, bool long_waits = false) { r = ring; head = tail_seen = 0; patient = long_waits; }
-  // batch interface: wait for published entries, read them in place, release them in one go
+  // waits for published words; every entry that starts inside the returned count is complete
   AVR_DEV uint32_t wait_avail() {
     if (patient) {
       uint32_t polls = 0;
       while (head == (tail_seen = *reinterpret_cast<volatile uint32_t*>(&r->tail_pub))) wide_backoff(polls);
     }
     while (head == tail_seen) tail_seen = *reinterpret_cast<volatile uint32_t*>(&r->tail_pub);
-    ring_fence();   // acquire: peek() reads the entries with plain loads, which must not be hoisted above the spin
+    ring_fence();   // acquire: take() reads the entries with plain loads, which must not be hoisted above the spin
     const uint32_t n = tail_seen - head;
     return n < RING_BATCH ? n : uint32_t(RING_BATCH);   // bounded, so the producer gets its slots back early
   }
-  AVR_DEV uint32_t peek(uint32_t k) const { return r->e[(head + k) & (RING_ENTRIES - 1)]; }
-  AVR_DEV void release(uint32_t n) {
-    head += n;
+  AVR_DEV uint32_t take() { return r->e[head++ & (RING_ENTRIES - 1)]; }
+  AVR_DEV void release() {
     ring_fence();
     *reinterpret_cast<volatile uint32_t*>(&r->head_pub) = head;
-  }
-  AVR_DEV void switch_to(RingShared* next) {   // wide slices: the next macroblock row comes from another ring
-    ring_fence();
-    *reinterpret_cast<volatile uint32_t*>(&r->head_pub) = head;
-    r->cons_head = head;
-    r = next;
-    head = tail_seen = r->cons_head;
-  }
-  AVR_DEV uint32_t pop() {
-    if (head == tail_seen) {
-      do tail_seen = *reinterpret_cast<volatile uint32_t*>(&r->tail_pub); while (head == tail_seen);
-    }
-    const uint32_t e = reinterpret_cast<volatile uint32_t*>(r->e)[head & (RING_ENTRIES - 1)];
-    if ((++head & (RING_PUBLISH - 1)) == 0) {
-      ring_fence();
-      *reinterpret_cast<volatile uint32_t*>(&r->head_pub) = head;
-    }
-    return e;
   }
 };
 #else
@@ -583,6 +622,8 @@ struct Producer {
   RingShared* r;
   void init(RingShared* ring, uint32_t* = nullptr, uint32_t = 0) { r = ring; }
   void publish() {}
+  void reserve(uint32_t) {}
+  void put(uint32_t w) { r->e.push_back(w); }
   void switch_to(RingShared* next, uint32_t) { r = next; }
   void push(uint32_t e) { r->e.push_back(e); }
 };
@@ -591,60 +632,136 @@ struct Consumer {
   size_t head;
   void init(RingShared* ring, bool = false) { r = ring; head = 0; }
   uint32_t wait_avail() { return head < r->e.size() ? uint32_t(r->e.size() - head > 64 ? 64 : r->e.size() - head) : 1u; }
-  uint32_t peek(uint32_t k) const { return head + k < r->e.size() ? r->e[head + k] : uint32_t(SYM_END); }
-  void release(uint32_t n) { head += n; }
-  void switch_to(RingShared* next) { r->cons_head = head; r = next; head = r->cons_head; }
-  uint32_t pop() { return head < r->e.size() ? r->e[head++] : uint32_t(SYM_END); }
+  uint32_t take() { return head < r->e.size() ? r->e[head++] : uint32_t(SYM_END); }
+  void release() {}
 };
 #endif
+// entries that a coder warp staged from a ring in global memory (wide slices)
+struct StageSrc {
+  const uint32_t* w;
+  uint32_t k;
+  AVR_DEV uint32_t take() { return w[k++]; }
+};
 
 // ------------------------------------------------------------------------------------------------
 // Coder-warp roles (lane 0): drain the ring until SYM_END.
 // ------------------------------------------------------------------------------------------------
 struct CoderCompress {     // estimators + range encoder (recode.cpp:1068-1096 h264_symbol::execute)
   RangeEnc rc;
-  AVR_DEV void begin(uint8_t* dst, uint32_t cap, int = -1) { rc.init(dst, cap); }
-  // Software-pipelined: entry k+1, its estimator and its reciprocal are loaded while entry k goes
-  // through the coder, so the loop-carried chain is the range recurrence alone (one 64x64 high
-  // multiply, a shift, a multiply, a subtract, a select).  The estimator of entry k+1 is read BEFORE
-  // entry k's update is stored; when both use the same estimator the updated value is forwarded.
+  AVR_DEV void begin(ByteSink* sink, uint8_t* dst, uint32_t cap, int = -1) { rc.init(sink, dst, cap); }
+  // one bin through the model and the range coder
+  AVR_DEV void code(const SharedTables& t, uint16_t* cnt, uint32_t idx, uint32_t bit, uint32_t limit) {
+    const uint32_t c = cnt[idx];
+    rc.put(t.div[c >> 8], int(bit), c & 0xFF);
+    cnt[idx] = uint16_t(est_next(c, bit, limit));
+  }
+  // a run of bins on ONE estimator (coefficient levels, bypass): it stays in registers
+  AVR_DEV uint32_t code_reg(const SharedTables& t, uint32_t c, uint32_t bit, uint32_t limit) {
+    rc.put(t.div[c >> 8], int(bit), c & 0xFF);
+    return est_next(c, bit, limit);
+  }
+  // Significance bins of a 4x4-class block: the estimator index only ever grows inside a block (+1, or +17 after a
+  // coefficient), so the next estimator and its reciprocal are fetched while the current bin is in the coder and
+  // the loop-carried chain is the range recurrence alone.
+  AVR_DEV void sig_bins4(const SharedTables& t, uint16_t* cnt, uint32_t slab, uint32_t mask, uint32_t nnz_true, uint32_t coefs) {
+    uint32_t idx = slab, zz = 0, observed = 0;
+    uint32_t c = cnt[idx];
+    DivMagic mg = t.div[c >> 8];
+#pragma unroll 1
+    for (;;) {
+      const uint32_t bit = (mask >> zz) & 1u;
+      const uint32_t idx_n = idx + 1u + (bit << 4);
+      const uint32_t c_n = cnt[idx_n];
+      const DivMagic mg_n = t.div[c_n >> 8];
+      rc.put(mg, int(bit), c & 0xFF);
+      cnt[idx] = uint16_t(est_next(c, bit, LIMIT_SIG));
+      observed += bit; zz++;
+      if (observed >= nnz_true || zz >= coefs) break;
+      idx = idx_n; c = c_n; mg = mg_n;
+    }
+  }
+  // 8x8 blocks: several positions share an estimator (sig_coeff_flag_offset_8x8), so no lookahead
+  AVR_DEV void sig_bins8(const SharedTables& t, uint16_t* cnt, uint32_t slab, uint64_t mask, uint32_t nnz_true) {
+    uint32_t zz = 0, observed = 0;
+#pragma unroll 1
+    while (observed < nnz_true && zz < 63) {
+      const uint32_t bit = uint32_t(mask >> zz) & 1u;
+      code(t, cnt, slab + observed * SIG_ZZ + t.sig8[zz], bit, LIMIT_SIG);
+      observed += bit; zz++;
+    }
+  }
+  // nnz of a block as 2 / 4 / 6 model-coded bits, least significant first (recode.cpp:858, 874-888)
+  AVR_DEV void nnz_bits(const SharedTables& t, uint16_t* cnt, uint32_t cat, uint32_t w0, uint32_t w1) {
+    const uint32_t maxc = k_maxc[cat];
+    const int nbits = maxc > 16 ? 6 : maxc > 4 ? 4 : 2;
+    const uint32_t left_nz = w1 & 0xFF, above_nz = (w1 >> 8) & 0xFF, prev_nz = (w1 >> 16) & 0xFF;
+    const bool has_left = (w0 >> BLK_HAS_LEFT) & 1;
+    const uint32_t nnz = (w0 >> BLK_NNZ) & 63;   // 64 is coded as 0
+    const uint32_t group = CNT_NZ + nz_group(int(cat), (w0 >> BLK_MB8) & 1);
+    uint32_t so_far = 0;
+#pragma unroll 1
+    for (int i = 0; i < nbits; i++) {
+      const uint32_t cur_bit = 1u << i;
+      const uint32_t lb = has_left ? (left_nz >= cur_bit) : 2;
+      const uint32_t ab = above_nz ? (above_nz >= cur_bit) : 2;   // sic: value test (recode.cpp:881)
+      const uint32_t idx = group + ((cur_bit - 1 + so_far) * 2 + (prev_nz >= cur_bit)) * 9 + lb * 3 + ab;
+      const uint32_t bit = (nnz >> i) & 1;
+      code(t, cnt, idx, bit, LIMIT_ANY);
+      so_far |= bit << i;
+    }
+  }
+  // one entry; returns true on SYM_END
+  template <class Src>
+  AVR_DEV bool entry(Src& s, const SharedTables& t, uint16_t* cnt) {
+    const uint32_t e = s.take();
+    if (e & (SYM_END | SYM_LEVEL | SYM_BLOCK)) {
+      if (e & SYM_END) return true;
+      if (e & SYM_BLOCK) {
+        const uint32_t cat = e & 7, nnz_true = (e >> BLK_NNZ) & 0x7F;
+        const uint32_t w1 = s.take();
+        const uint32_t mlo = s.take();
+        nnz_bits(t, cnt, cat, e, w1);
+        const uint32_t slab = sig_slab(int(cat), nnz_true & 63);
+        if (cat == 5) {
+          const uint32_t mhi = s.take();
+          sig_bins8(t, cnt, slab, uint64_t(mlo) | uint64_t(mhi) << 32, nnz_true);
+        } else sig_bins4(t, cnt, slab, mlo, nnz_true, uint32_t(k_maxc[cat]) - 1);
+        return false;
+      }
+      // one coefficient level: first bin, run of "greater than one" bins, sign
+      const uint32_t b1 = (e >> LVL_BIT1) & 1;
+      code(t, cnt, CNT_CTX + (e & 0x1FF), b1, LIMIT_ANY);
+      if (b1) {
+        const uint32_t g = CNT_CTX + ((e >> LVL_GCTX) & 0x1FF);
+        uint32_t c = cnt[g];
+#pragma unroll 1
+        for (uint32_t r = (e >> LVL_RUN) & 15; r > 0; r--) c = code_reg(t, c, 1, LIMIT_ANY);
+        if ((e >> LVL_TERM) & 1) c = code_reg(t, c, 0, LIMIT_ANY);
+        cnt[g] = uint16_t(c);
+      }
+      if ((e >> LVL_HAS_SIGN) & 1) code(t, cnt, CNT_BYPASS, (e >> LVL_SIGN) & 1, LIMIT_ANY);
+      return false;
+    }
+    const uint32_t idx = e & 0xFFFF, bit = (e >> SYM_BIT_SHIFT) & 1;
+    code(t, cnt, idx, bit, LIMIT_ANY);
+    if (idx == CNT_TERM && bit) range_enc_finish(rc.sink, rc.low, rc.range);                      // recode.cpp:1092-1095
+    return false;
+  }
   AVR_DEV void run(Consumer& q, const SharedTables& t, uint16_t* cnt, U2*) {
     for (;;) {
-      const uint32_t n = q.wait_avail();
-      uint32_t e = q.peek(0);
-      uint32_t c = cnt[e & 0xFFFF];
-      DivMagic mg = t.div[(c & 0xFF) + (c >> 8)];
-      bool end = false;
-      uint32_t k = 0;
+      const uint32_t end = q.head + q.wait_avail();
+      bool done = false;
 #pragma unroll 1
-      for (; k < n; k++) {
-        if (e & SYM_END) { end = true; break; }
-        const uint32_t idx = e & 0xFFFF;
-        const int bit = int((e >> SYM_BIT_SHIFT) & 1);
-        const uint32_t e_n = q.peek(k + 1 < n ? k + 1 : k);
-        const uint32_t idx_n = e_n & 0xFFFF;
-        uint32_t c_n = cnt[idx_n];
-        uint32_t pos = c & 0xFF, neg = c >> 8;
-        const uint32_t pos0 = pos;
-        est_update(pos, neg, bit, idx >= CNT_SIG ? 0x50u : 0x60u);   // recode.cpp:1041-1042
-        const uint32_t c2 = pos | (neg << 8);
-        cnt[idx] = uint16_t(c2);
-        if (idx_n == idx) c_n = c2;
-        const DivMagic mg_n = t.div[(c_n & 0xFF) + (c_n >> 8)];
-#ifndef AVR_PROBE_NO_CODER
-        rc.put(mg, bit, pos0);
-        if (idx == CNT_TERM && bit) rc.finish();                      // recode.cpp:1092-1095
-#endif
-        e = e_n; c = c_n; mg = mg_n;
-      }
-      q.release(k);
-      if (end) break;
+      while (!done && int32_t(end - uint32_t(q.head)) > 0) done = entry(q, t, cnt);
+      q.release();
+      if (done) break;
     }
   }
   // Wide slices: the ring is long and in global memory (far), so that this coder may fall a good part of a
   // macroblock row behind the parser and catch up while the parser feeds the other stream.  ALL lanes call this:
-  // they stage up to 128 entries with coalesced loads, lane 0 runs the same pipelined loop over the stage.
-  // stage[0..127] entries, stage[128] != 0: SYM_END seen.
+  // they stage up to 128 words with coalesced loads, lane 0 works through the entries of the stage.
+  // stage[0..127 + ENTRY_MAX_WORDS] words, stage[STAGE_FLAG] != 0: SYM_END seen, stage[STAGE_USED]: words consumed.
+  enum : uint32_t { STAGE_WORDS = 128, STAGE_FLAG = 136, STAGE_USED = 137 };
   AVR_DEV void run_far(RingShared* r, const uint32_t* far, uint32_t far_cap, const SharedTables& t, uint16_t* cnt, uint32_t* stage, int lane) {
     uint32_t head = 0;
     for (;;) {
@@ -653,62 +770,94 @@ struct CoderCompress {     // estimators + range encoder (recode.cpp:1068-1096 h
       uint32_t avail;
       for (uint32_t polls = 0; (avail = *reinterpret_cast<volatile uint32_t*>(&r->tail_pub) - head) == 0;) wide_backoff(polls);
       ring_fence();
-      n = avail < 128u ? avail : 128u;
+      n = avail < uint32_t(STAGE_WORDS) ? avail : uint32_t(STAGE_WORDS);
       const volatile uint32_t* src = far;
       for (uint32_t i = uint32_t(lane); i < n; i += 32) stage[i] = src[(head + i) & (far_cap - 1)];
       __syncwarp();
+      const bool more = avail > n;   // the stage may end inside an entry: stop ENTRY_MAX_WORDS short of it
 #else
       (void)far; (void)far_cap;
-      n = uint32_t(r->e.size() - head > 128 ? 128 : r->e.size() - head);
+      n = uint32_t(r->e.size() - head > STAGE_WORDS ? STAGE_WORDS : r->e.size() - head);
       for (uint32_t i = 0; i < n; i++) stage[i] = r->e[head + i];
       if (n == 0) { stage[0] = SYM_END; n = 1; }
+      const bool more = r->e.size() - head > n;
 #endif
       if (lane == 0) {
-        uint32_t e = stage[0];
-        uint32_t c = cnt[e & 0xFFFF];
-        DivMagic mg = t.div[(c & 0xFF) + (c >> 8)];
-        uint32_t end = 0;
+        StageSrc s; s.w = stage; s.k = 0;
+        const uint32_t stop = more ? n - (ENTRY_MAX_WORDS - 1) : n;
+        bool done = false;
 #pragma unroll 1
-        for (uint32_t k = 0; k < n; k++) {
-          if (e & SYM_END) { end = 1; break; }
-          const uint32_t idx = e & 0xFFFF;
-          const int bit = int((e >> SYM_BIT_SHIFT) & 1);
-          const uint32_t e_n = stage[k + 1 < n ? k + 1 : k];
-          const uint32_t idx_n = e_n & 0xFFFF;
-          uint32_t c_n = cnt[idx_n];
-          uint32_t pos = c & 0xFF, neg = c >> 8;
-          const uint32_t pos0 = pos;
-          est_update(pos, neg, bit, idx >= CNT_SIG ? 0x50u : 0x60u);   // recode.cpp:1041-1042
-          const uint32_t c2 = pos | (neg << 8);
-          cnt[idx] = uint16_t(c2);
-          if (idx_n == idx) c_n = c2;
-          const DivMagic mg_n = t.div[(c_n & 0xFF) + (c_n >> 8)];
-          rc.put(mg, bit, pos0);
-          if (idx == CNT_TERM && bit) rc.finish();                      // recode.cpp:1092-1095
-          e = e_n; c = c_n; mg = mg_n;
-        }
-        stage[128] = end;
+        while (!done && s.k < stop) done = entry(s, t, cnt);
+        stage[STAGE_FLAG] = done ? 1u : 0u;
+        stage[STAGE_USED] = s.k;
 #if defined(__CUDACC__) && !defined(AVR_HOST_EMULATION)
         ring_fence();
-        *reinterpret_cast<volatile uint32_t*>(&r->head_pub) = head + n;
+        *reinterpret_cast<volatile uint32_t*>(&r->head_pub) = head + s.k;
 #endif
       }
       AVR_SYNCWARP_CORE();
-      head += n;
-      const uint32_t end = stage[128];
+      head += stage[STAGE_USED];
+      const uint32_t end = stage[STAGE_FLAG];
       AVR_SYNCWARP_CORE();
       if (end) break;
     }
   }
-  AVR_DEV uint32_t out_bytes() const { return rc.sink.n; }
-  AVR_DEV bool overflowed() const { return rc.sink.overflow; }
+  AVR_DEV uint32_t out_bytes() const { return rc.sink->n; }
+  AVR_DEV bool overflowed() const { return rc.sink->overflow != 0; }
 };
 
 struct CoderDecompress {   // CABAC re-encoder (cabac_code.h:16-86; recode.cpp:1443, 1455, 1466)
   CabacOut cabac;
-  AVR_DEV void begin(uint8_t* dst, uint32_t cap, int esc_zeros = -1) { cabac.init(dst, cap, esc_zeros); }
-  AVR_DEV void entry(const SharedTables& t, U2* cstate, uint32_t e) {
-    if (e & SYM_LEVEL) {   // one coefficient level: first bin, run of "greater than one" bins, sign
+  AVR_DEV void begin(ByteSink* sink, uint8_t* dst, uint32_t cap, int esc_zeros = -1) { cabac.init(sink, dst, cap, esc_zeros); }
+  // significant_coeff_flag / last_significant_coeff_flag bins of a block out of its mask (h264_cabac.c:1667-1703);
+  // the last coefficient of a full scan is inferred, not coded.  4x4-class blocks: position i uses contexts
+  // sig_base + i and last_base + i, all distinct, so the entries of the next position are fetched ahead.
+  AVR_DEV void sig_bins4(const SharedTables& t, U2* sig, U2* last, uint32_t mask, uint32_t nnz_true, uint32_t coefs) {
+    uint32_t zz = 0, observed = 0;
+    U2 es = sig[0], el = last[0];
+#pragma unroll 1
+    for (;;) {
+      const uint32_t bit = (mask >> zz) & 1u;
+      const U2 es_n = sig[zz + 1], el_n = last[zz + 1];   // one past the block at the end: loaded, never used
+      U2 n;
+      cabac.encode_core(t, es, int(bit), &n);
+      sig[zz] = n;
+      if (bit) {
+        observed++;
+        cabac.encode_core(t, el, observed == nnz_true, &n);
+        last[zz] = n;
+      }
+      zz++;
+      if (observed >= nnz_true || zz >= coefs) break;
+      es = es_n; el = el_n;
+    }
+  }
+  AVR_DEV void sig_bins8(const SharedTables& t, U2* sig, U2* last, uint64_t mask, uint32_t nnz_true) {
+    uint32_t zz = 0, observed = 0;
+#pragma unroll 1
+    while (observed < nnz_true && zz < 63) {
+      const uint32_t bit = uint32_t(mask >> zz) & 1u;
+      cabac.decision(t, int(bit), &sig[t.sig8[zz]]);
+      if (bit) { observed++; cabac.decision(t, observed == nnz_true, &last[t.last8[zz]]); }
+      zz++;
+    }
+  }
+  // everything but SYM_END and the wide-slice specials
+  template <class Src>
+  AVR_DEV void entry(Src& s, const SharedTables& t, U2* cstate, uint32_t e) {
+    if (e & (SYM_LEVEL | SYM_BLOCK)) {
+      if (e & SYM_BLOCK) {
+        const uint32_t cat = e & 7, nnz_true = (e >> BLK_NNZ) & 0x7F;
+        const uint32_t mlo = s.take();
+        U2* sig = cstate + k_sig_base[cat];
+        U2* last = cstate + k_last_base[cat];
+        if (cat == 5) {
+          const uint32_t mhi = s.take();
+          sig_bins8(t, sig, last, uint64_t(mlo) | uint64_t(mhi) << 32, nnz_true);
+        } else sig_bins4(t, sig, last, mlo, nnz_true, uint32_t(k_maxc[cat]) - 1);
+        return;
+      }
+      // one coefficient level: first bin, run of "greater than one" bins, sign
       const uint32_t g = (e >> LVL_GCTX) & 0x1FF;
       const int b1 = int((e >> LVL_BIT1) & 1);
       U2 eg = cstate[g];                      // both contexts are loaded up front (they differ); the run keeps its
@@ -730,18 +879,26 @@ struct CoderDecompress {   // CABAC re-encoder (cabac_code.h:16-86; recode.cpp:1
   }
   AVR_DEV void run(Consumer& q, const SharedTables& t, uint16_t*, U2* cstate) {
     for (;;) {
-      const uint32_t e = q.pop();
-      if (e & SYM_END) break;
-      entry(t, cstate, e);
+      const uint32_t end = q.head + q.wait_avail();
+      bool done = false;
+#pragma unroll 1
+      while (int32_t(end - uint32_t(q.head)) > 0) {
+        const uint32_t e = q.take();
+        if (e & SYM_END) { done = true; break; }
+        entry(q, t, cstate, e);
+      }
+      q.release();
+      if (done) break;
     }
   }
   // Wide slices: ring j (entries in global memory, far[j * far_cap ...]; indices in rings[j]) carries the
   // macroblock rows j, j + K, ... and every row ends in SP_ROW_END.  ALL lanes of the warp call this: they
-  // fetch a batch of entries with one coalesced load, lane 0 encodes them one by one.  Leaves on the
+  // fetch a batch of words with one coalesced load, lane 0 encodes the entries in it.  Leaves on the
   // first SYM_END and then drains the other rings so that their parser warps can finish.
+  enum : uint32_t { STAGE_WORDS = 64, STAGE_USED = 72, STAGE_WHY = 73 };
   AVR_DEV void run_wide(RingShared* rings, uint32_t n_rings, const uint32_t* far, uint32_t far_cap, const SharedTables& t, U2* cstate,
                         uint32_t* stage, int lane) {
-    // stage[0..31]: the batch; stage[32]: entries used; stage[33]: 0 go on, 1 row end, 2 SYM_END
+    // stage[0..63 + ENTRY_MAX_WORDS]: the batch; stage[STAGE_USED]: words used; stage[STAGE_WHY]: 0 go on, 1 row end, 2 SYM_END
     uint32_t cur = 0, qpd = 0, head = 0;
     bool draining = false;
     for (;;) {
@@ -751,37 +908,45 @@ struct CoderDecompress {   // CABAC re-encoder (cabac_code.h:16-86; recode.cpp:1
       uint32_t avail;
       for (uint32_t polls = 0; (avail = *reinterpret_cast<volatile uint32_t*>(&r->tail_pub) - head) == 0;) wide_backoff(polls);
       ring_fence();
-      n = avail < 32u ? avail : 32u;
+      n = avail < uint32_t(STAGE_WORDS) ? avail : uint32_t(STAGE_WORDS);
       const volatile uint32_t* src = far + size_t(cur) * far_cap;
-      if (uint32_t(lane) < n) stage[lane] = src[(head + uint32_t(lane)) & (far_cap - 1)];
+      for (uint32_t i = uint32_t(lane); i < n; i += 32) stage[i] = src[(head + i) & (far_cap - 1)];
       __syncwarp();
+      const bool more = avail > n;
 #else
       (void)far; (void)far_cap;
-      n = 1;
-      stage[0] = head < r->e.size() ? r->e[head] : uint32_t(SYM_END);
+      n = uint32_t(r->e.size() - head > STAGE_WORDS ? STAGE_WORDS : r->e.size() - head);
+      for (uint32_t i = 0; i < n; i++) stage[i] = r->e[head + i];
+      if (n == 0) { stage[0] = SYM_END; n = 1; }
+      const bool more = r->e.size() - head > n;
 #endif
       if (lane == 0) {   // the serial part: plain single-lane code, nothing warp-wide per entry (a warp-wide loop with
         // lane 0 predicated per entry cost 2x: every entry paid for the divergence and reconvergence)
-        uint32_t used = 0, why = 0;
+        StageSrc s; s.w = stage; s.k = 0;
+        const uint32_t stop = more ? n - (ENTRY_MAX_WORDS - 1) : n;
+        uint32_t why = 0;
 #pragma unroll 1
-        while (used < n) {
-          const uint32_t e = stage[used++];
+        while (s.k < stop) {
+          const uint32_t e = s.take();
           if (e & SYM_END) { why = 2; break; }
-          if (draining) continue;
-          if (!(e & SYM_LEVEL) && (e & (3u << SYM_KIND_SHIFT)) == SYM_SPECIAL) {
+          if (draining) {   // skip the payload words of a block entry
+            if (e & SYM_BLOCK) s.k += (e & 7) == 5 ? 2 : 1;
+            continue;
+          }
+          if (!(e & (SYM_LEVEL | SYM_BLOCK)) && (e & (3u << SYM_KIND_SHIFT)) == SYM_SPECIAL) {
             if (e & SP_ROW_END) { qpd = e & 1; why = 1; break; }
             cabac.decision(t, int((e >> SYM_BIT_SHIFT) & 1), &cstate[60 + qpd]);
-          } else entry(t, cstate, e);
+          } else entry(s, t, cstate, e);
         }
-        stage[32] = used; stage[33] = why;
+        stage[STAGE_USED] = s.k; stage[STAGE_WHY] = why;
 #if defined(__CUDACC__) && !defined(AVR_HOST_EMULATION)
         ring_fence();
-        *reinterpret_cast<volatile uint32_t*>(&r->head_pub) = head + used;
+        *reinterpret_cast<volatile uint32_t*>(&r->head_pub) = head + s.k;
 #endif
       }
       AVR_SYNCWARP_CORE();
-      head += stage[32];
-      const uint32_t why = stage[33];
+      head += stage[STAGE_USED];
+      const uint32_t why = stage[STAGE_WHY];
       AVR_SYNCWARP_CORE();
       if (why == 0) continue;
       if (why == 2) { draining = true; r->cons_head = 0xFFFFFFFFu; }
@@ -793,8 +958,8 @@ struct CoderDecompress {   // CABAC re-encoder (cabac_code.h:16-86; recode.cpp:1
       head = uint32_t(rings[cur].cons_head);
     }
   }
-  AVR_DEV uint32_t out_bytes() const { return cabac.sink.n; }
-  AVR_DEV bool overflowed() const { return cabac.sink.overflow; }
+  AVR_DEV uint32_t out_bytes() const { return cabac.sink->n; }
+  AVR_DEV bool overflowed() const { return cabac.sink->overflow != 0; }
 };
 
 // ------------------------------------------------------------------------------------------------
@@ -811,39 +976,27 @@ struct Compress {
                      uint32_t* far_entries = nullptr, uint32_t far_cap = 0) {
     in.attach(src, n, window, tail_byte); q.init(ring, far_entries, far_cap); cstate = states;
   }
+  AVR_DEV void set_home(DecHome*) {}
   AVR_DEV void start_bins(const SharedTables&) { cabac.init(in); }
   AVR_DEV void finish_bins() {}
-  struct SigEntry { uint32_t c; };
-  AVR_DEV SigEntry sig_fetch(const SharedTables&, uint32_t) const { return SigEntry(); }
-  AVR_DEV int sig_decode(const SigEntry&, uint32_t) { return 0; }
   AVR_DEV int bin(const SharedTables& t, int ctx) {
     const int b = cabac.decision(in, t, &cstate[ctx]);
     q.push(uint32_t(CNT_CTX + ctx) | uint32_t(b) << SYM_BIT_SHIFT);
     return b;
   }
-  // a bin whose context entry was fetched ahead of time (the caller guarantees no update of that context in between)
+  // coefficient levels: CABAC side only, the whole level crosses the ring as one entry (lvl_push)
   typedef U2 BinEntry;
   AVR_DEV BinEntry bin_fetch(const SharedTables&, int ctx) const { return cstate[ctx]; }
-  AVR_DEV int bin_pre(const SharedTables& t, const BinEntry e, int ctx) {
-    const int b = cabac.decide(in, t, e, &cstate[ctx]);
-    q.push(uint32_t(CNT_CTX + ctx) | uint32_t(b) << SYM_BIT_SHIFT);
-    return b;
-  }
-  // a run of bins on ONE context: the entry stays in registers (bin_run), written back once (bin_store)
-  AVR_DEV int bin_run(const SharedTables& t, BinEntry& e, int ctx) {
+  AVR_DEV void bin_store(const BinEntry& e, int ctx) { cstate[ctx] = e; }
+  AVR_DEV int lvl_first(const SharedTables& t, const BinEntry e, int ctx) { return cabac.decide(in, t, e, &cstate[ctx]); }
+  AVR_DEV int lvl_run(const SharedTables& t, BinEntry& e, int) {
     BinEntry n;
     const int b = cabac.decide_core(in, t, e, &n);
     e = n;
-    q.push(uint32_t(CNT_CTX + ctx) | uint32_t(b) << SYM_BIT_SHIFT);
     return b;
   }
-  AVR_DEV void bin_store(const BinEntry& e, int ctx) { cstate[ctx] = e; }
-  // coefficient levels: this direction keeps one entry per bin (its coder is a software-pipelined loop over
-  // plain entries, and composite entries cost it more than they save the parser); lvl_push is a no-op here
-  AVR_DEV int lvl_first(const SharedTables& t, const BinEntry e, int ctx) { return bin_pre(t, e, ctx); }
-  AVR_DEV int lvl_run(const SharedTables& t, BinEntry& e, int ctx) { return bin_run(t, e, ctx); }
-  AVR_DEV int lvl_sign(const SharedTables& t) { return bypass(t); }
-  AVR_DEV void lvl_push(uint32_t) {}
+  AVR_DEV int lvl_sign(const SharedTables&) { return cabac.bypass(in); }
+  AVR_DEV void lvl_push(uint32_t entry) { q.push(entry); }
   // wide slices: first mb_qp_delta bin of a macroblock row -- decoded with its true context, modelled with
   // the estimator of context 60 whatever the previous row ended on (the rows are decoded in parallel)
   AVR_DEV int bin_row_qpd(const SharedTables& t, int true_ctx) {
@@ -854,11 +1007,18 @@ struct Compress {
   AVR_DEV void row_end(int) {}
   AVR_DEV int bypass(const SharedTables&) { const int b = cabac.bypass(in); q.push(CNT_BYPASS | uint32_t(b) << SYM_BIT_SHIFT); return b; }
   AVR_DEV int terminate(const SharedTables&) { const int b = cabac.terminate(in); q.push(CNT_TERM | uint32_t(b) << SYM_BIT_SHIFT); return b; }
-  AVR_DEV int sig_get(const SharedTables& t, int ctx) { return cabac.decision(in, t, &cstate[ctx]); }   // CABAC side only
+  // significance map: CABAC side (the model side is derived from the block entry by the coder warp)
   AVR_DEV U2 sig_peek(int ctx) const { return cstate[ctx]; }
+  AVR_DEV int sig_get(const SharedTables& t, int ctx) { return cabac.decision(in, t, &cstate[ctx]); }
   AVR_DEV int sig_get_pre(const SharedTables& t, const U2 e, int ctx) { return cabac.decide(in, t, e, &cstate[ctx]); }
-  AVR_DEV void sig_put(int, int) {}
-  AVR_DEV int model_bit(const SharedTables&, uint32_t idx, int bit) { q.push(idx | uint32_t(bit) << SYM_BIT_SHIFT); return bit; }
+  // nnz: count of this block; left / above / previous-picture counts of the NZ key; mb8: the macroblock has an 8x8 block
+  AVR_DEV void block_push(int cat, uint32_t nnz, bool mb8, bool has_left, uint32_t left_nz, uint32_t above_nz, uint32_t prev_nz, uint64_t mask) {
+    q.reserve(4);
+    q.put(SYM_BLOCK | uint32_t(cat) | nnz << BLK_NNZ | (mb8 ? 1u << BLK_MB8 : 0u) | (has_left ? 1u << BLK_HAS_LEFT : 0u));
+    q.put(left_nz | above_nz << 8 | prev_nz << 16);
+    q.put(uint32_t(mask));
+    if (cat == 5) q.put(uint32_t(mask >> 32));
+  }
   AVR_DEV uint32_t in_pos() const { return cabac.pos; }
 };
 
@@ -869,122 +1029,94 @@ struct Decompress {
   RangeDec rc;
   Producer q;
   uint16_t* cnt;     // parser owns the estimators
+  DecHome* home;     // read position of the range decoder (shared memory)
   AVR_DEV void begin(const uint8_t* src, uint32_t n, uint8_t* window, uint32_t, RingShared* ring, uint16_t* counters, U2*,
                      uint32_t* far_entries = nullptr, uint32_t far_cap = 0) {
     in.attach(src, n, window, 0); q.init(ring, far_entries, far_cap); cnt = counters;
-    byp_c = 0x0101;
+    byp_c = EST_INIT;
   }
+  AVR_DEV void set_home(DecHome* h) { home = h; }
   // The bypass estimator codes every sign and escape bit: it is kept in registers together with its
   // reciprocal for the length of a slice (read at start_bins, written back by finish_bins).
   uint32_t byp_c;
   DivMagic byp_mg;
   AVR_DEV void start_bins(const SharedTables& t) {
-    rc.init(in);
+    rc.init(home, in);
     byp_c = cnt[CNT_BYPASS];
-    byp_mg = t.div[(byp_c & 0xFF) + (byp_c >> 8)];
+    byp_mg = t.div[byp_c >> 8];
   }
   AVR_DEV void finish_bins() { cnt[CNT_BYPASS] = uint16_t(byp_c); }
   AVR_DEV int coded(const SharedTables& t, uint32_t idx, uint32_t limit) {
     const uint32_t c = cnt[idx];
-    uint32_t pos = c & 0xFF, neg = c >> 8;
-    const int b = rc.get(in, t.div[pos + neg], pos);
-    est_update(pos, neg, b, limit);
-    cnt[idx] = uint16_t(pos | (neg << 8));
+    const int b = rc.get(t.div[c >> 8], c & 0xFF);
+    cnt[idx] = uint16_t(est_next(c, uint32_t(b), limit));
     return b;
   }
   AVR_DEV int bin(const SharedTables& t, int ctx) {
-    const int b = coded(t, uint32_t(CNT_CTX + ctx), 0x60);
+    const int b = coded(t, uint32_t(CNT_CTX + ctx), LIMIT_ANY);
     q.push(uint32_t(ctx) | uint32_t(b) << SYM_BIT_SHIFT | SYM_DECISION);
     return b;
   }
   AVR_DEV int bin_row_qpd(const SharedTables& t, int) {   // see Compress::bin_row_qpd
-    const int b = coded(t, uint32_t(CNT_CTX + 60), 0x60);
+    const int b = coded(t, uint32_t(CNT_CTX + 60), LIMIT_ANY);
     q.push(uint32_t(b) << SYM_BIT_SHIFT | SYM_SPECIAL | SP_QPD);
     return b;
   }
   AVR_DEV void row_end(int qpd_nonzero) { q.push(SYM_SPECIAL | SP_ROW_END | uint32_t(qpd_nonzero)); }
+  AVR_DEV int byp_bin(const SharedTables& t) {
+    const int b = rc.get(byp_mg, byp_c & 0xFF);
+    byp_c = est_next(byp_c, uint32_t(b), LIMIT_ANY);
+    byp_mg = t.div[byp_c >> 8];
+    return b;
+  }
   AVR_DEV int bypass(const SharedTables& t) {
-    uint32_t pos = byp_c & 0xFF, neg = byp_c >> 8;
-    const int b = rc.get(in, byp_mg, pos);
-    est_update(pos, neg, b, 0x60);
-    byp_c = pos | (neg << 8);
-    byp_mg = t.div[pos + neg];
+    const int b = byp_bin(t);
     q.push(uint32_t(b) << SYM_BIT_SHIFT | SYM_BYPASS);
     return b;
   }
-  AVR_DEV int terminate(const SharedTables& t) { const int b = coded(t, CNT_TERM, 0x60); q.push(uint32_t(b) << SYM_BIT_SHIFT | SYM_TERMINATE); return b; }
+  AVR_DEV int terminate(const SharedTables& t) { const int b = coded(t, CNT_TERM, LIMIT_ANY); q.push(uint32_t(b) << SYM_BIT_SHIFT | SYM_TERMINATE); return b; }
   // significance-map bins with both possible successors prefetched (see Walker::residual)
   struct SigEntry { uint32_t c; DivMagic mg; };
   AVR_DEV SigEntry sig_fetch(const SharedTables& t, uint32_t idx) const {
-    SigEntry e; e.c = cnt[idx]; e.mg = t.div[(e.c & 0xFF) + (e.c >> 8)]; return e;
+    SigEntry e; e.c = cnt[idx]; e.mg = t.div[e.c >> 8]; return e;
   }
   AVR_DEV int sig_decode(const SigEntry& e, uint32_t idx) {
-    uint32_t pos = e.c & 0xFF, neg = e.c >> 8;
-    const int b = rc.get(in, e.mg, pos);
-    est_update(pos, neg, b, 0x50);
-    cnt[idx] = uint16_t(pos | (neg << 8));
+    const int b = rc.get(e.mg, e.c & 0xFF);
+    cnt[idx] = uint16_t(est_next(e.c, uint32_t(b), LIMIT_SIG));
     return b;
   }
   // an ordinary bin whose estimator + reciprocal were fetched ahead of time (no update of it in between)
   typedef SigEntry BinEntry;
   AVR_DEV BinEntry bin_fetch(const SharedTables& t, int ctx) const { return sig_fetch(t, uint32_t(CNT_CTX + ctx)); }
-  AVR_DEV int bin_pre(const SharedTables&, const BinEntry& e, int ctx) {
-    uint32_t pos = e.c & 0xFF, neg = e.c >> 8;
-    const int b = rc.get(in, e.mg, pos);
-    est_update(pos, neg, b, 0x60);
-    cnt[CNT_CTX + ctx] = uint16_t(pos | (neg << 8));
-    q.push(uint32_t(ctx) | uint32_t(b) << SYM_BIT_SHIFT | SYM_DECISION);
+  AVR_DEV void bin_store(const BinEntry& e, int ctx) { cnt[CNT_CTX + ctx] = uint16_t(e.c); }
+  // coefficient levels: no per-bin push; lvl_push sends the whole level at once
+  AVR_DEV int lvl_first(const SharedTables&, const BinEntry& e, int ctx) {
+    const int b = rc.get(e.mg, e.c & 0xFF);
+    cnt[CNT_CTX + ctx] = uint16_t(est_next(e.c, uint32_t(b), LIMIT_ANY));
     return b;
   }
   // a run of bins on ONE context: estimator and reciprocal stay in registers; the next reciprocal is
   // div[total + 1], known before the bin is, unless the update halves the counts (rare: reloaded)
-  AVR_DEV int bin_run(const SharedTables& t, BinEntry& e, int ctx) {
-    uint32_t pos = e.c & 0xFF, neg = e.c >> 8;
-    const uint32_t tot = pos + neg;
-    const DivMagic mg_next = t.div[tot + 1];
-    const int b = rc.get(in, e.mg, pos);
-    est_update(pos, neg, b, 0x60);
-    e.c = pos | (neg << 8);
-    e.mg = mg_next;
-    if (tot + 1 > 0x60) e.mg = t.div[pos + neg];
-    q.push(uint32_t(ctx) | uint32_t(b) << SYM_BIT_SHIFT | SYM_DECISION);
-    return b;
-  }
-  AVR_DEV void bin_store(const BinEntry& e, int ctx) { cnt[CNT_CTX + ctx] = uint16_t(e.c); }
-  // coefficient levels: the same decoders without the per-bin push; lvl_push sends the whole level at once
-  AVR_DEV int lvl_first(const SharedTables&, const BinEntry& e, int ctx) {
-    uint32_t pos = e.c & 0xFF, neg = e.c >> 8;
-    const int b = rc.get(in, e.mg, pos);
-    est_update(pos, neg, b, 0x60);
-    cnt[CNT_CTX + ctx] = uint16_t(pos | (neg << 8));
-    return b;
-  }
   AVR_DEV int lvl_run(const SharedTables& t, BinEntry& e, int) {
-    uint32_t pos = e.c & 0xFF, neg = e.c >> 8;
-    const uint32_t tot = pos + neg;
+    const uint32_t tot = e.c >> 8;
     const DivMagic mg_next = t.div[tot + 1];
-    const int b = rc.get(in, e.mg, pos);
-    est_update(pos, neg, b, 0x60);
-    e.c = pos | (neg << 8);
+    const int b = rc.get(e.mg, e.c & 0xFF);
+    e.c = est_next(e.c, uint32_t(b), LIMIT_ANY);
     e.mg = mg_next;
-    if (tot + 1 > 0x60) e.mg = t.div[pos + neg];
+    if (tot + 1 > LIMIT_ANY) e.mg = t.div[e.c >> 8];
     return b;
   }
-  AVR_DEV int lvl_sign(const SharedTables& t) {
-    uint32_t pos = byp_c & 0xFF, neg = byp_c >> 8;
-    const int b = rc.get(in, byp_mg, pos);
-    est_update(pos, neg, b, 0x60);
-    byp_c = pos | (neg << 8);
-    byp_mg = t.div[pos + neg];
-    return b;
-  }
+  AVR_DEV int lvl_sign(const SharedTables& t) { return byp_bin(t); }
   AVR_DEV void lvl_push(uint32_t entry) { q.push(entry); }
-  AVR_DEV int sig_get(const SharedTables&, int) { return 0; }
-  AVR_DEV U2 sig_peek(int) const { return U2(); }
-  AVR_DEV int sig_get_pre(const SharedTables&, const U2, int) { return 0; }
-  AVR_DEV void sig_put(int ctx, int bit) { q.push(uint32_t(ctx) | uint32_t(bit) << SYM_BIT_SHIFT | SYM_DECISION); }   // CABAC side only
-  AVR_DEV int model_bit(const SharedTables& t, uint32_t idx, int) { return coded(t, idx, idx >= CNT_SIG ? 0x50u : 0x60u); }
-  AVR_DEV uint32_t in_pos() const { return rc.pos; }
+  AVR_DEV int model_bit(const SharedTables& t, uint32_t idx) { return coded(t, idx, idx >= CNT_SIG ? uint32_t(LIMIT_SIG) : uint32_t(LIMIT_ANY)); }
+  // the block's significance map for the CABAC re-encoder
+  AVR_DEV void block_push(int cat, uint32_t nnz_true, uint64_t mask) {
+    q.reserve(3);
+    q.put(SYM_BLOCK | uint32_t(cat) | nnz_true << BLK_NNZ);
+    q.put(uint32_t(mask));
+    if (cat == 5) q.put(uint32_t(mask >> 32));
+  }
+  AVR_DEV uint32_t in_pos() const { return rc.pos(); }
 };
 
 }  // namespace avr

@@ -47,6 +47,8 @@ struct BlockShared {
   alignas(16) uint8_t window[WIN_BYTES];
   U2 cstate[N_CTX_PAD];     // CABAC context states {state, rangeTabLPS row}
   WalkShared walk;          // left macroblock + per-macroblock scratch of the walker
+  ByteSink sink;            // output bytes of the coder warp (touched once per byte, out of line)
+  DecHome dec_home;         // read position of the range decoder (decompress parser)
   uint32_t job;             // job handed out by the atomic counter
   uint32_t final_status;    // status of the slice just finished (coder writes, everyone reads)
   uint32_t pad_[2];
@@ -131,6 +133,7 @@ struct Lane {               // what one parser warp works with
   uint16_t* cnt;
   uint32_t* far;            // wide decompression: this warp's symbol ring in global memory (else null)
   uint32_t far_cap;
+  DecHome* home;
 };
 
 // stream / total_mbs: wide decompression only (the caller has set wk.wide_k and what goes with it)
@@ -143,6 +146,7 @@ AVR_DEV void parser_begin(Walker<Dir>& wk, const Lane& ln, const uint8_t* src, u
   wk.ws = ln.walk;
   wk.use_planes = use_planes;
   wk.nnz_cur = nnz_cur; wk.nnz_prev = nnz_prev;
+  wk.dir.set_home(ln.home);
   wk.dir.begin(src, n, ln.window, (d.flags & AVR_SLICE_STOP_BYTE) ? 0x80u : 0u, ln.ring, ln.cnt, ln.cstate, ln.far, ln.far_cap);
   window_load_half(wk.dir.in, 0, lane);
   window_load_half(wk.dir.in, WIN_HALF, lane);
@@ -224,7 +228,7 @@ AVR_DEV void parser_role(const JobArgs& a, const JobMem& m, const avr_slice_desc
   wk.top_copy = false;
   Lane ln;
   ln.tab = &m.sh->tab; ln.ring = &m.sh->ring; ln.window = m.sh->window; ln.cstate = m.sh->cstate;
-  ln.walk = &m.sh->walk; ln.row = m.row; ln.cnt = m.cnt; ln.far = nullptr; ln.far_cap = 0;
+  ln.walk = &m.sh->walk; ln.row = m.row; ln.cnt = m.cnt; ln.far = nullptr; ln.far_cap = 0; ln.home = &m.sh->dec_home;
   parser_begin<Dir>(wk, ln, a.in_arena + io.in_off, io.in_size, d, cur_frame ? m.nnz1 : m.nnz0, cur_frame ? m.nnz0 : m.nnz1,
                     use_planes, lane, 0, 0);
   parser_run<Dir>(wk, lane);
@@ -237,7 +241,7 @@ AVR_DEV void coder_role(const JobArgs& a, const JobMem& m, const SliceIO& io, ui
   if (lane == 0) {
     typename Dir::Coder c;
     const uint8_t lay = a.descs[s].n_streams;   // decompress: put emulation-prevention bytes back (escaped slices, chunked mode)
-    c.begin(a.out_arena + io.out_off, io.out_cap, (lay & AVR_SLICE_ESCAPED) ? int((lay >> AVR_ESC_ZEROS_SHIFT) & 3) : -1);
+    c.begin(&m.sh->sink, a.out_arena + io.out_off, io.out_cap, (lay & AVR_SLICE_ESCAPED) ? int((lay >> AVR_ESC_ZEROS_SHIFT) & 3) : -1);
     Consumer q;
     q.init(&m.sh->ring);
     c.run(q, m.sh->tab, m.cnt, m.sh->cstate);
@@ -278,7 +282,7 @@ AVR_DEV void run_job(const JobArgs& a, const JobDesc& job, const JobMem& m, int 
     if (usable) {
       if (fresh) {
         // a brand-new h264_model: every estimator {1,1} (recode.cpp:1057), no frame buffers yet
-        fill_u32(reinterpret_cast<uint32_t*>(m.cnt), MODEL_COUNTERS / 2, 0x01010101u, tid, nthreads);
+        fill_u32(reinterpret_cast<uint32_t*>(m.cnt), MODEL_COUNTERS_PAD / 2, EST_INIT * 0x10001u, tid, nthreads);
         ft.clear();
       }
       const int mw = d.mb_width, mh = d.mb_height;
@@ -361,14 +365,16 @@ struct WideShared {
   uint32_t out_size[WIDE_MAX];   // compress: bytes of each stream;  decompress: [0] = bytes of the slice
   uint32_t overflow;
   uint32_t job;
-  uint32_t stage[WIDE_MAX][132]; // the batch of ring entries a coder warp is working on (decompress: [0] only)
+  uint32_t stage[WIDE_MAX][144]; // the batch of ring entries a coder warp is working on (decompress: [0] only)
+  ByteSink sink[WIDE_MAX];       // compress: one per coder warp; decompress: [0]
+  DecHome dec_home[WIDE_MAX];    // decompress: one per parser warp
 };
 
 struct WideMem {
   WideShared* sh;
   MbCtx* rows;      // [WIDE_MAX][max_mbw] (compress uses one): shared memory when they fit beside the estimators, else
   bool rows_global; //   the global workspace -- slower: every publication fence then waits for the row stores
-  uint16_t* cnt;    // [WIDE_MAX][MODEL_COUNTERS], shared memory
+  uint16_t* cnt;    // [WIDE_MAX][MODEL_COUNTERS_PAD], shared memory
   uint32_t* far;    // [WIDE_MAX][far_cap] symbol rings of a decompression, global workspace: a parser warp may run a
   uint32_t far_cap; //   whole macroblock row ahead of the re-encoder, far more than a shared-memory ring holds
   uint32_t max_mbw;
@@ -391,9 +397,10 @@ template <class Dir>
 AVR_DEV void wide_lane(Lane& ln, const WideMem& m, uint32_t j, uint32_t mbw) {
   WideShared* sh = m.sh;
   ln.tab = &sh->tab; ln.ring = &sh->ring[j]; ln.window = sh->window[j]; ln.cstate = sh->cstate;
-  ln.walk = &sh->walk[j]; ln.row = m.rows + size_t(j) * mbw; ln.cnt = m.cnt + size_t(j) * MODEL_COUNTERS;
+  ln.walk = &sh->walk[j]; ln.row = m.rows + size_t(j) * mbw; ln.cnt = m.cnt + size_t(j) * MODEL_COUNTERS_PAD;
   ln.far = m.far ? m.far + size_t(j) * m.far_cap : nullptr;   // compress: ring 0, the parser moves on from there
   ln.far_cap = m.far ? m.far_cap : 0;
+  ln.home = &sh->dec_home[j];
 }
 
 template <class Dir>
@@ -441,7 +448,7 @@ AVR_DEV void run_wide_job(const JobArgs& a, uint32_t s, const WideMem& m, int ti
   }
   init_contexts(sh->cstate, d, tid, nthreads);
   fill_u32(reinterpret_cast<uint32_t*>(m.rows), (Dir::kDecompress ? K : 1u) * mbw * MBCTX_WORDS, 0, tid, nthreads);   // compress walks in place: one row
-  fill_u32(reinterpret_cast<uint32_t*>(m.cnt), K * (MODEL_COUNTERS / 2), 0x01010101u, tid, nthreads);
+  fill_u32(reinterpret_cast<uint32_t*>(m.cnt), K * (MODEL_COUNTERS_PAD / 2), EST_INIT * 0x10001u, tid, nthreads);
   for (uint32_t j = uint32_t(tid); j < K; j += uint32_t(nthreads)) { ring_reset(&sh->ring[j]); sh->prog[j] = d.first_mb; sh->out_size[j] = 0; }
   if (tid == 0) { sh->abort_flag = 0; sh->overflow = 0; }
   AVR_SYNCBLOCK();
@@ -460,8 +467,8 @@ AVR_DEV void run_wide_job(const JobArgs& a, uint32_t s, const WideMem& m, int ti
     } else if (warp <= K) {
       const uint32_t j = warp - 1;
       typename Dir::Coder c;
-      c.begin(out + hdr + size_t(j) * subcap, subcap);
-      c.run_far(&sh->ring[j], m.far + size_t(j) * m.far_cap, m.far_cap, sh->tab, m.cnt + size_t(j) * MODEL_COUNTERS, sh->stage[j], lane);
+      c.begin(&sh->sink[j], out + hdr + size_t(j) * subcap, subcap);
+      c.run_far(&sh->ring[j], m.far + size_t(j) * m.far_cap, m.far_cap, sh->tab, m.cnt + size_t(j) * MODEL_COUNTERS_PAD, sh->stage[j], lane);
       if (lane == 0) {
         sh->out_size[j] = c.out_bytes();
         if (c.overflowed()) sh->overflow = 1;
@@ -471,7 +478,7 @@ AVR_DEV void run_wide_job(const JobArgs& a, uint32_t s, const WideMem& m, int ti
   } else {
     if (warp == 0) {
       typename Dir::Coder c;
-      c.begin(out, io.out_cap, esc_zeros);
+      c.begin(&sh->sink[0], out, io.out_cap, esc_zeros);
       c.run_wide(sh->ring, K, m.far, m.far_cap, sh->tab, sh->cstate, sh->stage[0], lane);
       if (lane == 0) {
         sh->out_size[0] = c.out_bytes();
@@ -502,8 +509,8 @@ AVR_DEV void run_wide_job(const JobArgs& a, uint32_t s, const WideMem& m, int ti
     parser_end<Dir>(wk, lane);
     for (uint32_t j = 0; j < K; j++) {
       typename Dir::Coder c;
-      c.begin(out + hdr + size_t(j) * subcap, subcap);
-      c.run_far(&sh->ring[j], nullptr, 0, sh->tab, m.cnt + size_t(j) * MODEL_COUNTERS, sh->stage[j], lane);
+      c.begin(&sh->sink[j], out + hdr + size_t(j) * subcap, subcap);
+      c.run_far(&sh->ring[j], nullptr, 0, sh->tab, m.cnt + size_t(j) * MODEL_COUNTERS_PAD, sh->stage[j], lane);
       sh->out_size[j] = c.out_bytes();
       if (c.overflowed()) sh->overflow = 1;
     }
@@ -526,7 +533,7 @@ AVR_DEV void run_wide_job(const JobArgs& a, uint32_t s, const WideMem& m, int ti
     for (uint32_t j = 0; j < K; j++) parser_end<Dir>(wk[j], lane);
     delete[] wk;
     typename Dir::Coder c;
-    c.begin(out, io.out_cap, esc_zeros);
+    c.begin(&sh->sink[0], out, io.out_cap, esc_zeros);
     c.run_wide(sh->ring, K, m.far, m.far_cap, sh->tab, sh->cstate, sh->stage[0], lane);
     sh->out_size[0] = c.out_bytes();
     if (c.overflowed()) sh->overflow = 1;

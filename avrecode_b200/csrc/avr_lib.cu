@@ -30,9 +30,9 @@ struct KernelArgs {
 
 size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 size_t row_bytes(uint32_t max_mbw) { return align_up(size_t(max_mbw) * sizeof(MbCtx), 16); }
-size_t counters_bytes() { return align_up(size_t(MODEL_COUNTERS) * 2, 256); }
+size_t counters_bytes() { return align_up(size_t(MODEL_COUNTERS_PAD) * 2, 256); }
 size_t smem_bytes(uint32_t max_mbw, bool resident) {
-  return sizeof(BlockShared) + row_bytes(max_mbw) + (resident ? size_t(MODEL_COUNTERS) * 2 : 0);
+  return sizeof(BlockShared) + row_bytes(max_mbw) + (resident ? size_t(MODEL_COUNTERS_PAD) * 2 : 0);
 }
 
 // Block = parser warp + coder warp.  Shared memory: BlockShared | MbCtx row[max_mbw] | estimators (RESIDENT).
@@ -46,7 +46,7 @@ __global__ void __launch_bounds__(AVR_THREADS, RESIDENT ? 2 : 8) avr_job_kernel(
   uint8_t* slot = k.workspace + uint64_t(blockIdx.x) * k.work_stride;
   const size_t rb = (size_t(k.max_mbw) * sizeof(MbCtx) + 15) / 16 * 16;
   if (RESIDENT) m.cnt = reinterpret_cast<uint16_t*>(smem + sizeof(BlockShared) + rb);
-  else { m.cnt = reinterpret_cast<uint16_t*>(slot); slot += (size_t(MODEL_COUNTERS) * 2 + 255) / 256 * 256; }
+  else { m.cnt = reinterpret_cast<uint16_t*>(slot); slot += (size_t(MODEL_COUNTERS_PAD) * 2 + 255) / 256 * 256; }
   m.nnz0 = slot;
   m.nnz1 = slot + k.nnz_frame_bytes;
   m.nnz_frame_bytes = k.nnz_frame_bytes;
@@ -82,7 +82,7 @@ struct WideKernelArgs {
 };
 enum : uint32_t { WIDE_FAR_CAP = 1u << 16 };
 size_t wide_rows_bytes(uint32_t max_mbw) { return align_up(size_t(WIDE_MAX) * max_mbw * sizeof(MbCtx), 256); }
-size_t wide_smem_bytes() { return align_up(sizeof(WideShared), 16) + align_up(size_t(WIDE_MAX) * MODEL_COUNTERS * 2, 16); }
+size_t wide_smem_bytes() { return align_up(sizeof(WideShared), 16) + align_up(size_t(WIDE_MAX) * MODEL_COUNTERS_PAD * 2, 16); }
 
 template <class Dir>
 __global__ void __launch_bounds__(AVR_WIDE_THREADS, 1) avr_wide_kernel(WideKernelArgs k) {
@@ -91,7 +91,7 @@ __global__ void __launch_bounds__(AVR_WIDE_THREADS, 1) avr_wide_kernel(WideKerne
   m.sh = reinterpret_cast<WideShared*>(smem);
   m.cnt = reinterpret_cast<uint16_t*>(smem + (sizeof(WideShared) + 15) / 16 * 16);
   uint8_t* slot = k.workspace + uint64_t(blockIdx.x) * k.work_stride;
-  m.rows = k.rows_in_shared ? reinterpret_cast<MbCtx*>(smem + (sizeof(WideShared) + 15) / 16 * 16 + (size_t(WIDE_MAX) * MODEL_COUNTERS * 2 + 15) / 16 * 16)
+  m.rows = k.rows_in_shared ? reinterpret_cast<MbCtx*>(smem + (sizeof(WideShared) + 15) / 16 * 16 + (size_t(WIDE_MAX) * MODEL_COUNTERS_PAD * 2 + 15) / 16 * 16)
                             : reinterpret_cast<MbCtx*>(slot);
   m.rows_global = !k.rows_in_shared;
   m.far = reinterpret_cast<uint32_t*>(slot + (size_t(WIDE_MAX) * k.max_mbw * sizeof(MbCtx) + 255) / 256 * 256);

@@ -18,8 +18,10 @@ struct ProbeShared {
   RingShared ring;
   alignas(16) uint8_t window[WIN_BYTES];
   U2 cstate[N_CTX_PAD];
-  uint16_t cnt[4096];
+  uint16_t cnt[10240];
   uint8_t out[8192];
+  ByteSink sink;
+  DecHome home;
 };
 
 struct ProbeArgs {
@@ -38,7 +40,7 @@ __device__ void probe_setup(ProbeShared* sh, int tid, int nthreads) {
     sh->cstate[i].x = ctx_word_x(state);
     sh->cstate[i].y = rlps4_of(state >> 1);
   }
-  for (int i = tid; i < 4096; i += nthreads) sh->cnt[i] = 0x0101;
+  for (int i = tid; i < 10240; i += nthreads) sh->cnt[i] = EST_INIT;
   if (tid == 0) ring_reset(&sh->ring);
 }
 
@@ -105,13 +107,13 @@ __device__ void probe_coded(ProbeShared* sh, const ProbeArgs& a, uint64_t* r) {
   Decompress d;
   d.in.attach(sh->window, 0x7FFFFFFFu, sh->window, 0);
   d.cnt = sh->cnt;
-  d.rc.init(d.in);
+  d.rc.init(&sh->home, d.in);
   uint32_t acc = 0;
   const long long t0 = clock64();
 #pragma unroll 1
-  for (uint32_t i = 0; i < a.iters; i++) acc += uint32_t(d.coded(sh->tab, (i * 5u) & 63u, 0x60));
+  for (uint32_t i = 0; i < a.iters; i++) acc += uint32_t(d.coded(sh->tab, (i * 5u) & 63u, LIMIT_ANY));
   const long long t1 = clock64();
-  r[0] = uint64_t(t1 - t0); r[1] = a.iters; r[2] = acc + d.rc.pos;
+  r[0] = uint64_t(t1 - t0); r[1] = a.iters; r[2] = acc + d.rc.pos();
 }
 
 // 4: the decompress-side significance loop (both successors prefetched), without the ring push
@@ -119,7 +121,7 @@ __device__ void probe_sigloop_d(ProbeShared* sh, const ProbeArgs& a, uint64_t* r
   Decompress d;
   d.in.attach(sh->window, 0x7FFFFFFFu, sh->window, 0);
   d.cnt = sh->cnt;
-  d.rc.init(d.in);
+  d.rc.init(&sh->home, d.in);
   uint64_t bins = 0, acc = 0;
   const long long t0 = clock64();
 #pragma unroll 1
@@ -139,39 +141,57 @@ __device__ void probe_sigloop_d(ProbeShared* sh, const ProbeArgs& a, uint64_t* r
     }
   }
   const long long t1 = clock64();
-  r[0] = uint64_t(t1 - t0); r[1] = bins; r[2] = acc + d.rc.pos;
+  r[0] = uint64_t(t1 - t0); r[1] = bins; r[2] = acc + d.rc.pos();
 }
 
-__device__ void fill_ring(ProbeShared* sh, bool decompress) {
-  uint32_t s = 777u;
-  for (uint32_t i = 0; i + 1 < RING_ENTRIES; i++) {
-    const uint32_t rnd = lcg(s);
-    const uint32_t bit = (rnd & 7) < 2 ? 1u : 0u;
+// Fills the ring with a residual-heavy mix of entries (4x4 blocks with their levels, a few plain bins), ends it with
+// SYM_END and returns how many bins the coder warp will derive from it.
+__device__ uint32_t fill_ring(ProbeShared* sh, bool decompress) {
+  uint32_t s = 777u, n = 0, bins = 0;
+  uint32_t* e = sh->ring.e;
+  while (n + 24 < RING_ENTRIES) {
+    // one block of category 2 (luma 4x4): a few coefficients in the first positions
+    const uint32_t nnz = 1 + lcg(s) % 5;
+    uint32_t mask = 0, placed = 0, zz = 0;
+    while (placed < nnz && zz < 15) { if (lcg(s) % 3 == 0 || 15 - zz == nnz - placed) { mask |= 1u << zz; placed++; } zz++; }
+    const uint32_t scanned = zz;   // positions up to and including the last coefficient
     if (decompress) {
-      const uint32_t kind = (rnd >> 3) % 10 == 0 ? uint32_t(SYM_BYPASS) : uint32_t(SYM_DECISION);
-      sh->ring.e[i] = ((rnd >> 8) % 40u + 100u) | bit << SYM_BIT_SHIFT | kind;
+      e[n++] = SYM_BLOCK | 2u | nnz << BLK_NNZ;
+      e[n++] = mask;
+      bins += scanned + nnz;                 // sig + last bins
     } else {
-      sh->ring.e[i] = (CNT_CTX + (rnd >> 8) % 40u + 100u) | bit << SYM_BIT_SHIFT;
+      e[n++] = SYM_BLOCK | 2u | nnz << BLK_NNZ | 1u << BLK_HAS_LEFT;
+      e[n++] = (lcg(s) % 6) | (lcg(s) % 6) << 8;
+      e[n++] = mask;
+      bins += 4 + scanned;                   // nnz bits + model-coded sig bins
     }
+    for (uint32_t c = 0; c < nnz; c++) {     // levels: mostly 1, sometimes a short run
+      const uint32_t b1 = lcg(s) % 4 == 0, run = b1 ? lcg(s) % 3 : 0;
+      e[n++] = lvl_entry(227 + 1 + int(c % 4), int(b1), 227 + 5, int(run), int(b1), 1, int(lcg(s) & 1));
+      bins += 1 + (b1 ? run + 1 : 0) + 1;
+    }
+    e[n++] = (decompress ? 85u | SYM_DECISION : CNT_CTX + 85u) | (lcg(s) & 1) << SYM_BIT_SHIFT;   // a coded_block_flag
+    bins += 1;
   }
-  sh->ring.e[RING_ENTRIES - 1] = SYM_END;
-  sh->ring.tail_pub = RING_ENTRIES;
+  e[n++] = SYM_END;
+  sh->ring.tail_pub = n;
   sh->ring.head_pub = 0;
+  return bins;
 }
 
 // 5: the compress coder warp's loop (estimators + 64-bit range encoder) over a full ring
 __device__ void probe_coder_c(ProbeShared* sh, const ProbeArgs& a, uint64_t* r) {
-  fill_ring(sh, false);
+  const uint32_t per = fill_ring(sh, false);
   uint64_t bins = 0;
   CoderCompress c;
-  c.begin(sh->out, sizeof sh->out);
+  c.begin(&sh->sink, sh->out, sizeof sh->out);
   const long long t0 = clock64();
 #pragma unroll 1
   for (uint32_t i = 0; i < a.iters; i++) {
     Consumer q; q.init(&sh->ring);
     c.run(q, sh->tab, sh->cnt, sh->cstate);
-    c.rc.sink.n = 0;
-    bins += RING_ENTRIES - 1;
+    sh->sink.n = 0;
+    bins += per;
   }
   const long long t1 = clock64();
   r[0] = uint64_t(t1 - t0); r[1] = bins; r[2] = c.rc.low;
@@ -179,17 +199,17 @@ __device__ void probe_coder_c(ProbeShared* sh, const ProbeArgs& a, uint64_t* r) 
 
 // 6: the decompress coder warp's loop (CABAC re-encoder) over a full ring
 __device__ void probe_coder_d(ProbeShared* sh, const ProbeArgs& a, uint64_t* r) {
-  fill_ring(sh, true);
+  const uint32_t per = fill_ring(sh, true);
   uint64_t bins = 0;
   CoderDecompress c;
-  c.begin(sh->out, sizeof sh->out);
+  c.begin(&sh->sink, sh->out, sizeof sh->out);
   const long long t0 = clock64();
 #pragma unroll 1
   for (uint32_t i = 0; i < a.iters; i++) {
     Consumer q; q.init(&sh->ring);
     c.run(q, sh->tab, sh->cnt, sh->cstate);
-    c.cabac.sink.n = 0;
-    bins += RING_ENTRIES - 1;
+    sh->sink.n = 0;
+    bins += per;
   }
   const long long t1 = clock64();
   r[0] = uint64_t(t1 - t0); r[1] = bins; r[2] = c.cabac.low;

@@ -56,12 +56,6 @@ struct alignas(8) WalkShared {     // per-block scratch of the walker (shared me
   uint8_t nnz_mb[52];   // avrecode model: stored nnz of the macroblock being walked, by block index
 };
 
-// (dense) ctxIdx bases per block category 0..5 (h264_cabac.c:1589-1599, :1556), packed so that a
-// category's four bases come from one constant-bank load
-AVR_TABLE_QUAL int16_t k_sig_base[6] = {105, 120, 134, 149, 152, dctx(402)};
-AVR_TABLE_QUAL int16_t k_last_base[6] = {166, 181, 195, 210, 213, dctx(417)};
-AVR_TABLE_QUAL int16_t k_abs_base[6] = {227, 237, 247, 257, 266, dctx(426)};
-AVR_TABLE_QUAL int16_t k_cbf_base[6] = {85, 89, 93, 97, 101, dctx(1012)};
 enum : int { CTX_T8X8 = dctx(399) };
 // B macroblock types 0..22 (h264data.h:127-151 b_mb_type_info): partition shape (0 direct, 1 16x16, 2 16x8,
 // 3 8x16, 4 8x8) and the prediction lists of partition 0 / 1 (bit 0 = list 0, bit 1 = list 1)
@@ -151,8 +145,8 @@ struct Walker {
     else *value = (where == 1 ? ws->left.nnz : top_mb->nnz)[k_nnz_slot[nb]];
     return true;
   }
-  // codes (compress) or reads (decompress) the block's nnz; returns the value the compressor stores
-  AVR_DEV uint32_t code_nnz(int cat, int blk, int max_coeff, uint32_t nnz) {
+  // decompress: reads the block's nnz, 2 / 4 / 6 model-coded bits, least significant first (recode.cpp:858, 874-888)
+  AVR_DEV uint32_t read_nnz(int cat, int blk, int max_coeff) {
     const int nbits = max_coeff > 16 ? 6 : max_coeff > 4 ? 4 : 2;
     uint32_t left_nz = 0, above_nz = 0;
     const bool has_left = model_neighbor(false, max_coeff, blk, &left_nz);
@@ -166,101 +160,111 @@ struct Walker {
       const uint32_t lb = has_left ? (left_nz >= cur_bit) : 2;
       const uint32_t ab = above_nz ? (above_nz >= cur_bit) : 2;   // sic: value test (recode.cpp:881)
       const uint32_t idx = group + ((cur_bit - 1 + so_far) * 2 + (prev_nz >= cur_bit)) * 9 + lb * 3 + ab;
-      if (dir.model_bit(*tab, idx, int((nnz >> i) & 1))) so_far |= cur_bit;
+      if (dir.model_bit(*tab, idx)) so_far |= cur_bit;
     }
-    if (Dir::kDecompress) return so_far;
-    return nnz;
+    return so_far;
   }
 
   // ---- one residual block (h264_cabac.c:1582-1780 + recode.cpp queueing 1160-1255 / 1435-1492) --
+  // The significance map crosses to the coder warp as ONE entry (category, count, mask): the compress
+  // coder derives the nnz bits and the model-coded significance bins from it, the decompress coder the
+  // CABAC sig / last bins.  What stays here is what is serial by nature: pulling the map out of the
+  // CABAC stream (compress) or out of the range coder (decompress).
   AVR_DEV void residual(int cat, int blk, int max_coeff) {
     const bool is8 = max_coeff == 64;
     const int coefs = max_coeff - 1;
-    const int sig_base = k_sig_base[cat], last_base = k_last_base[cat], abs_base = k_abs_base[cat];
+    const int abs_base = k_abs_base[cat];
     if (is8) model_is8x8 = true;          // before the nnz bits, as the compressor does
-    uint32_t nnz = 0;
-    uint64_t mask = 0;
-    if (!Dir::kDecompress) {
+    uint32_t nnz_true, key_nnz;
+    if constexpr (!Dir::kDecompress) {
       // 1. pull the significance map out of the CABAC stream (h264_cabac.c:1667-1681)
+      const int sig_base = k_sig_base[cat], last_base = k_last_base[cat];
+      uint64_t mask = 0;
+      uint32_t nnz = 0;
       int last;
+      bool ended = false;   // by last_significant_coeff_flag = 1
       if (!is8) {
         // 4x4-class blocks: the context of position i is base + i, all distinct, so the two contexts
         // that can come next (last[i], sig[i+1]) are loaded while sig[i] is still being decided
+        uint32_t m32 = 0;
         U2 e_sig = dir.sig_peek(sig_base);
 #pragma unroll 1
         for (last = 0; last < coefs; last++) {
           const U2 e_last = dir.sig_peek(last_base + last);
           const U2 e_next = dir.sig_peek(sig_base + last + 1);   // one past the block at the end: loaded, never used
-          count_bin();
           if (dir.sig_get_pre(*tab, e_sig, sig_base + last)) {
-            mask |= uint64_t(1) << last;
+            m32 |= 1u << last;
             nnz++;
-            count_bin();
-            if (dir.sig_get_pre(*tab, e_last, last_base + last)) { last = max_coeff; break; }
+            if (dir.sig_get_pre(*tab, e_last, last_base + last)) { ended = true; last++; break; }
           }
           e_sig = e_next;
         }
+        n_bins_lo += uint32_t(last) + nnz;   // one sig bin per position scanned, one last bin per coefficient found
+        mask = m32;
       } else {
 #pragma unroll 1
         for (last = 0; last < coefs; last++) {
-          count_bin();
           if (dir.sig_get(*tab, sig_base + tab->sig8[last])) {
             mask |= uint64_t(1) << last;
             nnz++;
-            count_bin();
-            if (dir.sig_get(*tab, last_base + tab->last8[last])) { last = max_coeff; break; }
+            if (dir.sig_get(*tab, last_base + tab->last8[last])) { ended = true; last++; break; }
           }
         }
+        n_bins_lo += uint32_t(last) + nnz;
       }
-      if (last == max_coeff - 1) { mask |= uint64_t(1) << last; nnz++; }
-    }
-    // 2. nnz side channel
-    const uint32_t coded = code_nnz(cat, blk, max_coeff, nnz & 63);
-    uint32_t nnz_true, key_nnz;
-    if (Dir::kDecompress) {
+      // a scan that never met last_significant_coeff_flag = 1 ends in an inferred coefficient at the last position
+      if (!ended) { mask |= uint64_t(1) << coefs; nnz++; }
+      nnz_true = nnz; key_nnz = nnz & 63;   // stored count: 64 -> 0, else exact
+      // 2. nnz side channel + 3. significance bins: both derived by the coder warp from this entry
+      uint32_t left_nz = 0, above_nz = 0;
+      const bool has_left = model_neighbor(false, max_coeff, blk, &left_nz);
+      model_neighbor(true, max_coeff, blk, &above_nz);
+      const uint32_t prev_nz = use_planes ? nnz_prev[size_t(mb_xy) * NNZ_STRIDE + blk] : 0u;
+      dir.block_push(cat, nnz, model_is8x8, has_left, left_nz, above_nz, prev_nz, mask);
+    } else {
+      // 2. nnz side channel
+      const uint32_t coded = read_nnz(cat, blk, max_coeff);
       nnz_true = coded == 0 ? uint32_t(max_coeff) : coded;
       if (nnz_true > uint32_t(max_coeff)) { fail(WALK_CORRUPT); nnz_true = uint32_t(max_coeff); }
       key_nnz = is8 ? coded : nnz_true;
-    } else { nnz_true = nnz; key_nnz = nnz & 63; }
-    ws->nnz_mb[blk] = uint8_t(key_nnz);   // stored count: 64 -> 0, else exact
-    if (use_planes) nnz_cur[size_t(mb_xy) * NNZ_STRIDE + blk] = uint8_t(key_nnz);
-    // 3. significance bins through the (cat, nnz) counter slab; last_significant_coeff_flag is
-    //    never coded, it is implied by nnz (recode.cpp:1073, 1437-1438)
-    const uint32_t slab = sig_slab(cat, key_nnz);
-    uint32_t observed = 0;
-    int zz = 0;
-    if (Dir::kDecompress && !is8) {
-      // decompress, 4x4-class blocks: the estimator (and its reciprocal) of BOTH possible successors
-      // -- next position with the same / with one more coefficient seen -- is fetched while the
-      // current bin is being range-decoded; the three indices are always distinct, so no forwarding
-      typename Dir::SigEntry e_cur = dir.sig_fetch(*tab, slab);
+      // 3. significance bins through the (cat, nnz) counter slab; last_significant_coeff_flag is
+      //    never coded, it is implied by nnz (recode.cpp:1073, 1437-1438)
+      const uint32_t slab = sig_slab(cat, key_nnz);
+      uint32_t observed = 0;
+      int zz = 0;
+      uint64_t mask = 0;
+      if (!is8) {
+        // 4x4-class blocks: the estimator (and its reciprocal) of BOTH possible successors -- next position
+        // with the same / with one more coefficient seen -- is fetched while the current bin is being
+        // range-decoded; the three indices are always distinct, so no forwarding
+        uint32_t m32 = 0;
+        typename Dir::SigEntry e_cur = dir.sig_fetch(*tab, slab);
 #pragma unroll 1
-      while (observed < nnz_true && zz < coefs) {
-        const uint32_t idx = slab + observed * SIG_ZZ + uint32_t(zz);
-        const typename Dir::SigEntry e0 = dir.sig_fetch(*tab, idx + 1);
-        const typename Dir::SigEntry e1 = dir.sig_fetch(*tab, idx + 1 + SIG_ZZ);
-        const int s = dir.sig_decode(e_cur, idx);
-        count_bin(); dir.sig_put(sig_base + zz, s);
-        if (s) {
-          observed++;
-          count_bin(); dir.sig_put(last_base + zz, observed == nnz_true);
-          e_cur = e1;
-        } else e_cur = e0;
-        zz++;
-      }
-    } else {
-#pragma unroll 1
-      while (observed < nnz_true && zz < coefs) {
-        const int inc = is8 ? tab->sig8[zz] : zz;
-        const int s = dir.model_bit(*tab, slab + observed * SIG_ZZ + uint32_t(inc), int((mask >> zz) & 1));
-        if (Dir::kDecompress) { count_bin(); dir.sig_put(sig_base + inc, s); }
-        if (s) {
-          observed++;
-          if (Dir::kDecompress) { count_bin(); dir.sig_put(last_base + (is8 ? tab->last8[zz] : zz), observed == nnz_true); }
+        while (observed < nnz_true && zz < coefs) {
+          const uint32_t idx = slab + observed * SIG_ZZ + uint32_t(zz);
+          const typename Dir::SigEntry e0 = dir.sig_fetch(*tab, idx + 1);
+          const typename Dir::SigEntry e1 = dir.sig_fetch(*tab, idx + 1 + SIG_ZZ);
+          const int s = dir.sig_decode(e_cur, idx);
+          m32 |= uint32_t(s) << zz;
+          observed += uint32_t(s);
+          e_cur = s ? e1 : e0;
+          zz++;
         }
-        zz++;
+        mask = m32;
+      } else {
+#pragma unroll 1
+        while (observed < nnz_true && zz < coefs) {
+          const int s = dir.model_bit(*tab, slab + observed * SIG_ZZ + uint32_t(tab->sig8[zz]));
+          mask |= uint64_t(s) << zz;
+          observed += uint32_t(s);
+          zz++;
+        }
       }
+      n_bins_lo += uint32_t(zz) + observed;   // the CABAC bins the re-encoder derives from the entry
+      dir.block_push(cat, nnz_true, mask);
     }
+    ws->nnz_mb[blk] = uint8_t(key_nnz);
+    if (use_planes) nnz_cur[size_t(mb_xy) * NNZ_STRIDE + blk] = uint8_t(key_nnz);
     // 4. coefficient levels (h264_cabac.c:1724-1765): ordinary context bins + bypass
     // The first context of the NEXT coefficient is known as soon as this one's magnitude class is, so
     // it is fetched before the sign bin and has arrived when the sign is done.

@@ -30,7 +30,7 @@ static int run(const avr_slice_desc* descs, int n, const uint8_t* in, uint64_t i
     if (descs[i].in_off + descs[i].in_size > in_bytes) return AVR_ERR_ARG;
   }
   std::vector<uint8_t> arena(out_total + 16);
-  std::vector<uint16_t> counters(MODEL_COUNTERS);
+  std::vector<uint16_t> counters(MODEL_COUNTERS_PAD);
   max_frame = (max_frame + 15u) & ~15u;
   std::vector<uint8_t> planes(2 * size_t(max_frame) + 64);
   BlockShared* sh = new BlockShared();
@@ -44,7 +44,7 @@ static int run(const avr_slice_desc* descs, int n, const uint8_t* in, uint64_t i
   WideShared* wsh = new WideShared();
   fill_shared_tables(&wsh->tab, 0, 1);
   std::vector<MbCtx> wrows(size_t(WIDE_MAX) * max_mbw);
-  std::vector<uint16_t> wcnt(size_t(WIDE_MAX) * MODEL_COUNTERS);
+  std::vector<uint16_t> wcnt(size_t(WIDE_MAX) * MODEL_COUNTERS_PAD);
   WideMem wm;
   wm.sh = wsh; wm.rows = wrows.data(); wm.cnt = wcnt.data(); wm.rows_global = false; wm.far = nullptr; wm.far_cap = 0; wm.max_mbw = uint32_t(max_mbw);
   int i = 0;

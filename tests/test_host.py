@@ -183,8 +183,8 @@ def test_manifest_matches_files():
 
 
 def test_bench_gate_digests_are_the_oracles(built):
-    """bench.py's pre-timing parity gate compares the CUDA bytes with tests/golden/bench_gate.json instead of running the
-    oracle; here (CPU) the pinned digests of the small workload are re-derived from the oracle."""
+    """bench.py's pre-timing parity gate compares the CUDA bytes of ALL ordinary slices with tests/golden/bench_gate.json
+    instead of running the oracle; here (CPU) the pinned digest of the small workload is re-derived from the oracle."""
     import hashlib, json, sys
     sys.path.insert(0, H.ROOT)
     import bench as B
@@ -194,9 +194,34 @@ def test_bench_gate_digests_are_the_oracles(built):
     w = pin["workloads"]["cfg1"]
     data, _ = B.gen_workload("cfg1", 0)
     assert hashlib.sha256(data).hexdigest() == w["stream_sha256"]
-    plain = H.batch_descs(A.index_h264(data), mode_file=False)[:pin["n_slices"]]
+    plain = H.batch_descs(A.index_h264(data), mode_file=False)
+    assert len(plain) == w["n_slices"] == len(w["n_bins"])
     r_o, b_o = H.oracle_compress(plain, data)
     h = hashlib.sha256()
     for s in H.slices_of(r_o, b_o):
         h.update(len(s).to_bytes(8, "little")); h.update(s)
     assert h.hexdigest() == w["coded_sha256"] and [int(r.n_bins) for r in r_o] == w["n_bins"]
+    for name, ww in pin["workloads"].items():   # every workload is pinned on all of its slices, and against the reference's size
+        assert ww["n_slices"] == len(ww["n_bins"]) > 0 and ww["ref_rec_bytes"] and ww["ref_rec_bytes"] < ww["stream_bytes"], name
+
+
+def test_reference_arm_segments_tile_the_file(built):
+    """bench.py --impl reference times closed groups of pictures of the workload file: they must be byte ranges that tile it
+    (same-config with the GPU arm), each a stream the indexer reads on its own."""
+    import sys
+    sys.path.insert(0, H.ROOT)
+    import bench as B
+    data = H.gen_stream(width=320, height=192, frames=10, intra_period=4, seed=9)
+    ents = A.index_h264(data)
+    segs = B.gop_segments(data, ents)
+    assert len(segs) == 3
+    # pieces after the first start with the SPS/PPS of the stream; without that prefix they tile the file
+    first_slice = data.index(b"\x00\x00\x01", data.index(b"\x00\x00\x01", 4) + 3)   # third start code = first slice NAL (4-byte codes)
+    prefix = data[:first_slice - 1] if data[first_slice - 1] == 0 else data[:first_slice]
+    assert all(s.startswith(prefix) for s in segs)
+    assert segs[0] + b"".join(s[len(prefix):] for s in segs[1:]) == data
+    n = [len(A.index_h264(s)) for s in segs]
+    assert n == [4, 4, 2] and sum(n) == len(ents)
+    specs = B.corpus_spec(8)
+    assert [s["seed"] for s in specs] == list(range(1000, 1008)) and {s["width"] for s in specs} == {1280, 1920}
+    assert all(30 <= s["frames"] <= 120 and 5000 <= s["kbps"] <= 30000 for s in B.corpus_spec(256))
