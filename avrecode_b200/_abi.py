@@ -56,7 +56,8 @@ class SliceResult(C.Structure):
 
 
 class Config(C.Structure):
-    _fields_ = [("abi_version", C.c_int32), ("device", C.c_int32), ("warps_per_block", C.c_int32), ("reserved", C.c_int32)]
+    _fields_ = [("abi_version", C.c_int32), ("device", C.c_int32), ("blocks_per_sm", C.c_int32), ("wide_stream_bytes", C.c_int32),
+                ("resident", C.c_int32), ("wide_batch_limit", C.c_int32), ("reserved", C.c_int32 * 2)]
 
 
 class IndexEntry(C.Structure):

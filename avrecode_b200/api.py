@@ -98,7 +98,7 @@ def _buf(data):
 
 
 def slice_streams(desc):
-    """n_streams the file calls would give this slice in MODE_SLICE (0 = ordinary slice, 2 = wide slice)."""
+    """n_streams the file calls would give this slice in MODE_SLICE in a small batch (0 = ordinary slice, 2 = wide slice)."""
     lib = load_library()
     lib.avr_slice_streams.argtypes = [C.POINTER(SliceDesc)]
     lib.avr_slice_streams.restype = C.c_int
@@ -141,10 +141,12 @@ def index_h264(data):
 class Context:
     """One CUDA device.  Raises NoDeviceError when there is none: no CPU fallback exists."""
 
-    def __init__(self, device=0, warps_per_sm=0):
+    def __init__(self, device=0, blocks_per_sm=0, wide_stream_bytes=-1, resident=-1, wide_batch_limit=-1):
         self._lib = load_library()
-        cfg = Config(_abi.AVR_OK + 1, device, warps_per_sm, 0)
+        cfg = Config()
         cfg.abi_version = self._lib.avr_abi_version()
+        cfg.device, cfg.blocks_per_sm, cfg.wide_stream_bytes = device, blocks_per_sm, wide_stream_bytes
+        cfg.resident, cfg.wide_batch_limit = resident, wide_batch_limit
         h = C.c_void_p()
         _check(self._lib.avr_create(C.byref(cfg), C.byref(h)), "avr_create")
         self._h = h
@@ -162,6 +164,11 @@ class Context:
 
     def __exit__(self, *a):
         self.close()
+
+    def slice_streams(self, desc, n_batch_slices):
+        """n_streams the file calls of THIS context give the slice in a batch of n_batch_slices CABAC slices."""
+        self._lib.avr_ctx_slice_streams.argtypes = [C.c_void_p, C.POINTER(SliceDesc), C.c_int]
+        return int(self._lib.avr_ctx_slice_streams(self._h, C.byref(desc), n_batch_slices))
 
     # ---- slice batches -------------------------------------------------------------------------
     def _batch(self, fn, what, descs, data):

@@ -127,6 +127,14 @@ AVR_DEV int clz32(uint32_t x) {
 #endif
 }
 
+AVR_DEV uint32_t clz64(uint64_t x) {
+#if defined(__CUDA_ARCH__)
+  return uint32_t(__clzll((long long)x));
+#else
+  return x ? uint32_t(__builtin_clzll(x)) : 64u;
+#endif
+}
+
 // exact floor(n / d) for 2 <= d < 100, n <= 2^63 (Granlund-Montgomery round-up reciprocal)
 AVR_DEV uint64_t div_magic(uint64_t n, const DivMagic& m) { return mulhi64(n, m.magic) >> m.shift; }
 AVR_DEV uint64_t div_small(const SharedTables& t, uint64_t n, uint32_t d) { return div_magic(n, t.div[d]); }
@@ -135,12 +143,14 @@ AVR_DEV uint32_t rlps4_of(uint32_t p) {
   return uint32_t(avr_range_lps[p * 4]) | uint32_t(avr_range_lps[p * 4 + 1]) << 8 | uint32_t(avr_range_lps[p * 4 + 2]) << 16 |
          uint32_t(avr_range_lps[p * 4 + 3]) << 24;
 }
-// Context entry word x: bits 0..7 the state (2 * pStateIdx + valMPS), bits 8..19 the renormalisation
-// shift of an LPS in each of the four range classes (clz(rangeTabLPS) - 23, 1..7, three bits each), so
-// that the bin decoder needs no count-leading-zeros on its critical path.
+// Context entry word x: bit 0 valMPS, bits 4..10 the state (2 * pStateIdx + valMPS) -- times 16, the byte offset of
+// its row in the transition table --, bits 16..27 the renormalisation shift of an LPS in each of the four range
+// classes (clz(rangeTabLPS) - 23, 1..7, three bits each), so that the bin decoder needs no count-leading-zeros
+// on its critical path.
+enum : uint32_t { CTX_STATE_MASK = 0x7F0, CTX_SHLPS_SHIFT = 16 };
 AVR_DEV uint32_t ctx_word_x(uint32_t state) {
-  uint32_t x = state & 0xFF;
-  for (int q = 0; q < 4; q++) x |= uint32_t(clz32(avr_range_lps[(state >> 1) * 4 + q]) - 23) << (8 + 3 * q);
+  uint32_t x = (state & 0x7F) << 4 | (state & 1);
+  for (int q = 0; q < 4; q++) x |= uint32_t(clz32(avr_range_lps[(state >> 1) * 4 + q]) - 23) << (CTX_SHLPS_SHIFT + 3 * q);
   return x;
 }
 AVR_DEV void fill_shared_tables(SharedTables* t, int tid, int nthreads) {
@@ -214,6 +224,18 @@ AVR_DEV uint32_t rlps_sel(uint32_t four, uint32_t q) {
 #endif
 }
 AVR_DEV uint32_t rlps_byte(uint32_t four, uint32_t range) { return rlps_sel(four, (range >> 6) & 3u); }
+// the same with t = range >> 6 (4..7 for a normalised range 256..510): as a PRMT selector 4 + q picks byte q of the
+// SECOND operand and the zero nibbles above it pick byte 0 of the first (zero) -- no masking, no or
+AVR_DEV uint32_t rlps_by_t(uint32_t four, uint32_t t) {
+#if defined(__CUDA_ARCH__)
+  return __byte_perm(0u, four, t);
+#else
+  return (four >> ((t & 3) * 8)) & 0xFF;
+#endif
+}
+AVR_DEV const U4& ctx_trans_row(const SharedTables& t, uint32_t x) {
+  return *reinterpret_cast<const U4*>(reinterpret_cast<const char*>(t.trans) + (x & CTX_STATE_MASK));
+}
 
 struct CabacIn {
   uint32_t val, range, pos;
@@ -231,10 +253,10 @@ struct CabacIn {
   // Both successors (MPS / LPS) are fetched with ONE 16-byte load whose address only needs the state,
   // so the transition is a select, not a load, once the bin is known.
   AVR_DEV int decide_core(const ByteWindow& w, const SharedTables& t, const U2 e, U2* next) {
-    const U4 pair = reinterpret_cast<const U4*>(t.trans)[e.x & 0xFF];
-    const uint32_t q = (range >> 6) & 3;
-    const uint32_t rlps = rlps_sel(e.y, q);
-    const uint32_t sh_lps = (e.x >> (8 + 3 * q)) & 7;      // renormalisation shift if this bin is the LPS
+    const U4 pair = ctx_trans_row(t, e.x);
+    const uint32_t tq = range >> 6;                         // 4 + quantile
+    const uint32_t rlps = rlps_by_t(e.y, tq);
+    const uint32_t sh_lps = (e.x >> (3 * tq + (CTX_SHLPS_SHIFT - 12))) & 7;   // renormalisation shift if this bin is the LPS
     range -= rlps;
     const uint32_t sh_mps = (range >> 8) ^ 1;               // range in [128, 510]: one shift iff below 256
     const uint32_t scaled = range << nbits;
@@ -416,10 +438,10 @@ struct CabacOut {
   // in `next`.  Both successors come with ONE 16-byte load addressed by the state alone, and the renormalisation
   // shift comes out of the entry (LPS) or of range's top bit (MPS): no count-leading-zeros, no dependent load.
   AVR_DEV void encode_core(const SharedTables& t, const U2 e, int bin, U2* next) {
-    const U4 pair = reinterpret_cast<const U4*>(t.trans)[e.x & 0xFF];
-    const uint32_t q = (range >> 6) & 3;
-    const uint32_t rlps = rlps_sel(e.y, q);
-    const uint32_t sh_lps = (e.x >> (8 + 3 * q)) & 7;
+    const U4 pair = ctx_trans_row(t, e.x);
+    const uint32_t tq = range >> 6;                         // 4 + quantile
+    const uint32_t rlps = rlps_by_t(e.y, tq);
+    const uint32_t sh_lps = (e.x >> (3 * tq + (CTX_SHLPS_SHIFT - 12))) & 7;
     range -= rlps;
     const uint32_t sh_mps = (range >> 8) ^ 1;
     const uint32_t lps = uint32_t(bin) != (e.x & 1) ? 1u : 0u;
@@ -461,7 +483,7 @@ struct CabacOut {
 };
 
 // Estimator update (recode.cpp:1035-1045): count the bin, halve both counts (rounding up) past the limit.
-AVR_DEV uint32_t est_halve(uint32_t c) {
+AVR_DEV_NOINLINE uint32_t est_halve(uint32_t c) {   // out of line: rare, and inlined it is 7 predicated instructions on every bin
   uint32_t pos = c & 0xFF, neg = (c >> 8) - pos;
   pos = (pos + 1) >> 1; neg = (neg + 1) >> 1;
   return pos | (pos + neg) << 8;
@@ -531,80 +553,30 @@ AVR_DEV void ring_fence() { asm volatile("fence.acq_rel.cta;" ::: "memory"); }
 // parser warp idles behind the row above), and a warp that polls flat out takes issue slots and shared-memory
 // cycles from the warps of its block that do the serial work: poll a few times, then sleep between polls.
 #define AVR_SYNCWARP_CORE() __syncwarp()
+#define AVR_BCAST_CORE(v) __shfl_sync(0xFFFFFFFFu, (v), 0)
 AVR_DEV void wide_backoff(uint32_t& polls) { if (++polls > 32) __nanosleep(polls > 256 ? 1000 : 100); }
 struct RingShared {
   uint32_t e[RING_ENTRIES];
   uint32_t tail_pub, head_pub;
   uint32_t end_status, end_mbs, end_bins_lo, end_bins_hi;   // written by the parser before SYM_END
   uint32_t prod_tail, cons_head;   // wide slices: where a producer / consumer that moved to another ring left off
+  uint32_t prod_wait, cons_wait;   // cycles / 256 the producer waited for room, the consumer for entries (which stage is the limit)
 };
-AVR_DEV void ring_reset(RingShared* r) { r->tail_pub = 0; r->head_pub = 0; r->prod_tail = 0; r->cons_head = 0; }
+AVR_DEV void ring_reset(RingShared* r) { r->tail_pub = 0; r->head_pub = 0; r->prod_tail = 0; r->cons_head = 0; r->prod_wait = 0; r->cons_wait = 0; }
 // makes room for an entry of n words: publishes what is complete, waits for the consumer if the ring is full; returns
 // the tail value up to which the producer may go on without looking again.  One out-of-line copy (instruction cache).
 AVR_DEV_NOINLINE uint32_t ring_slow(RingShared* r, uint32_t tail, uint32_t n, uint32_t cap) {
   ring_fence();
   *reinterpret_cast<volatile uint32_t*>(&r->tail_pub) = tail;
-  uint32_t head_seen;
-  do head_seen = *reinterpret_cast<volatile uint32_t*>(&r->head_pub); while (tail + n - head_seen > cap);
+  uint32_t head_seen = *reinterpret_cast<volatile uint32_t*>(&r->head_pub);
+  if (tail + n - head_seen > cap) {
+    const long long t0 = clock64();
+    do head_seen = *reinterpret_cast<volatile uint32_t*>(&r->head_pub); while (tail + n - head_seen > cap);
+    r->prod_wait += uint32_t((clock64() - t0) >> 8);
+  }
   const uint32_t a = head_seen + cap, b = tail + RING_PUBLISH;
   return int32_t(a - b) < 0 ? a : b;
 }
-struct Producer {
-  RingShared* r;
-  uint32_t* ents;            // the entries: r->e, or (wide slices) a much longer ring in global memory
-  uint32_t cap;              // words in ents, a power of two
-  uint32_t* far_base;        // wide compression: ring j lives at far_base + j * cap (null: the rings' own e[])
-  uint32_t tail, limit;
-  AVR_DEV void init(RingShared* ring, uint32_t* far_entries = nullptr, uint32_t far_cap = 0) {
-    r = ring; tail = 0; limit = RING_PUBLISH;
-    ents = far_entries ? far_entries : ring->e;
-    cap = far_entries ? far_cap : uint32_t(RING_ENTRIES);
-    far_base = far_entries;
-  }
-  AVR_DEV void publish() {
-    ring_fence();
-    *reinterpret_cast<volatile uint32_t*>(&r->tail_pub) = tail;
-  }
-  AVR_DEV void reserve(uint32_t n) { if (int32_t(limit - tail) < int32_t(n)) limit = ring_slow(r, tail, n, cap); }
-  AVR_DEV void put(uint32_t w) {
-#ifdef AVR_PROBE_NO_PUSH
-    if (!(w & SYM_END)) return;
-#endif
-    ents[tail & (cap - 1)] = w;
-    tail++;
-  }
-  AVR_DEV void push(uint32_t e) { reserve(1); put(e); }
-  AVR_DEV void switch_to(RingShared* next, uint32_t index) {   // wide compression: the next macroblock row goes to another ring
-    publish();
-    r->prod_tail = tail;
-    r = next;
-    ents = far_base ? far_base + size_t(index) * cap : next->e;
-    tail = r->prod_tail;
-    limit = ring_slow(r, tail, ENTRY_MAX_WORDS, cap);
-  }
-};
-struct Consumer {
-  RingShared* r;
-  uint32_t head, tail_seen;
-  bool patient;   // wide slices: long waits, see wide_backoff
-  AVR_DEV void init(RingShared* ring, bool long_waits = false) { r = ring; head = tail_seen = 0; patient = long_waits; }
-  // waits for published words; every entry that starts inside the returned count is complete
-  AVR_DEV uint32_t wait_avail() {
-    if (patient) {
-      uint32_t polls = 0;
-      while (head == (tail_seen = *reinterpret_cast<volatile uint32_t*>(&r->tail_pub))) wide_backoff(polls);
-    }
-    while (head == tail_seen) tail_seen = *reinterpret_cast<volatile uint32_t*>(&r->tail_pub);
-    ring_fence();   // acquire: take() reads the entries with plain loads, which must not be hoisted above the spin
-    const uint32_t n = tail_seen - head;
-    return n < RING_BATCH ? n : uint32_t(RING_BATCH);   // bounded, so the producer gets its slots back early
-  }
-  AVR_DEV uint32_t take() { return r->e[head++ & (RING_ENTRIES - 1)]; }
-  AVR_DEV void release() {
-    ring_fence();
-    *reinterpret_cast<volatile uint32_t*>(&r->head_pub) = head;
-  }
-};
 #else
 }  // namespace avr
 #include <vector>
@@ -612,40 +584,86 @@ namespace avr {
 // host emulation: the parser runs a whole slice into an unbounded queue, then the coder drains it
 inline void ring_fence() {}
 #define AVR_SYNCWARP_CORE() ((void)0)
+#define AVR_BCAST_CORE(v) (v)
 struct RingShared {
   std::vector<uint32_t> e;
   uint32_t end_status, end_mbs, end_bins_lo, end_bins_hi;
   size_t cons_head;
+  uint32_t prod_wait = 0, cons_wait = 0;
 };
 inline void ring_reset(RingShared* r) { r->e.clear(); r->cons_head = 0; }
-struct Producer {
-  RingShared* r;
-  void init(RingShared* ring, uint32_t* = nullptr, uint32_t = 0) { r = ring; }
-  void publish() {}
-  void reserve(uint32_t) {}
-  void put(uint32_t w) { r->e.push_back(w); }
-  void switch_to(RingShared* next, uint32_t) { r = next; }
-  void push(uint32_t e) { r->e.push_back(e); }
+#endif
+// ------------------------------------------------------------------------------------------------
+// Coder warp.  All lanes fetch a batch of ring words (a poll of the published tail; for a ring in global
+// memory a coalesced copy into shared memory), lane 0 works through the entries of the batch: every bin of
+// an entry is derived from the entry alone, so the estimators / contexts an entry will touch are known
+// up front and are loaded before the serial recurrence (range coder / CABAC encoder) needs them.
+// Tried and dropped (profiles/r2d_probes.txt): expanding the entries into one item per bin with all 32
+// lanes and running one software-pipelined loop over the items -- 369 / 358 cycles per bin against
+// 297 / 187 for deriving the bins in place: a warp instruction costs a lone warp the same 3-5 cycles
+// whether 1 or 32 lanes execute it, so the expansion only pays for entries with many bins.
+// ------------------------------------------------------------------------------------------------
+struct WordSrc {       // words of a batch: the shared-memory ring itself (mask 511) or a staged copy (mask ~0)
+  const uint32_t* e;
+  uint32_t at, mask;
+  AVR_DEV uint32_t take() { return e[at++ & mask]; }
 };
-struct Consumer {
+
+#if defined(__CUDACC__) && !defined(AVR_HOST_EMULATION)
+// the consumer side of a ring as the coder warp (all lanes) sees it
+struct RingReader {
+  RingShared* r;
+  uint32_t head;
+  bool patient;
+  AVR_DEV void init(RingShared* ring, bool long_waits = false) { r = ring; head = 0; patient = long_waits; }
+  AVR_DEV uint32_t wait_avail() {   // all lanes poll the same word: a broadcast, no divergence
+    uint32_t tail = *reinterpret_cast<volatile uint32_t*>(&r->tail_pub);
+    if (head == tail) {
+      const long long t0 = clock64();
+      uint32_t polls = 0;
+      while (head == (tail = *reinterpret_cast<volatile uint32_t*>(&r->tail_pub))) { if (patient) wide_backoff(polls); }
+      const uint32_t w = uint32_t((clock64() - t0) >> 8);
+      if ((threadIdx.x & 31) == 0) r->cons_wait += w;
+    }
+    ring_fence();
+    return tail - head;   // every entry that starts inside this count is complete
+  }
+  AVR_DEV void release(uint32_t n, int lane) {
+    head += n;
+    __syncwarp();
+    if (lane == 0) { ring_fence(); *reinterpret_cast<volatile uint32_t*>(&r->head_pub) = head; }
+  }
+};
+#else
+struct RingReader {
   RingShared* r;
   size_t head;
   void init(RingShared* ring, bool = false) { r = ring; head = 0; }
-  uint32_t wait_avail() { return head < r->e.size() ? uint32_t(r->e.size() - head > 64 ? 64 : r->e.size() - head) : 1u; }
-  uint32_t take() { return head < r->e.size() ? r->e[head++] : uint32_t(SYM_END); }
-  void release() {}
+  uint32_t wait_avail() { return uint32_t(r->e.size() - head); }
+  void release(uint32_t n, int) { head += n; }
 };
 #endif
-// entries that a coder warp staged from a ring in global memory (wide slices)
-struct StageSrc {
-  const uint32_t* w;
-  uint32_t k;
-  AVR_DEV uint32_t take() { return w[k++]; }
-};
+// Brings the next batch of a ring into reach of lane 0: returns the words to work through (entries that START
+// inside them are complete) and points `src` at them.  ALL lanes call this.
+AVR_DEV uint32_t coder_fetch(RingReader& q, const uint32_t* far, uint32_t far_cap, uint32_t* stage, int lane, WordSrc* src) {
+  const uint32_t avail = q.wait_avail();
+  const uint32_t n = avail < RING_BATCH ? avail : uint32_t(RING_BATCH);
+#if defined(__CUDACC__) && !defined(AVR_HOST_EMULATION)
+  if (far) {
+    const uint32_t ns = avail < RING_BATCH + ENTRY_MAX_WORDS ? avail : uint32_t(RING_BATCH + ENTRY_MAX_WORDS);
+    const volatile uint32_t* g = far;
+    for (uint32_t i = uint32_t(lane); i < ns; i += 32) stage[i] = g[(q.head + i) & (far_cap - 1)];
+    __syncwarp();
+    src->e = stage; src->at = 0; src->mask = 0xFFFFFFFFu;
+  } else { src->e = q.r->e; src->at = q.head; src->mask = RING_ENTRIES - 1; }
+#else
+  (void)far; (void)far_cap; (void)lane;
+  for (uint32_t i = 0; i < n + ENTRY_MAX_WORDS; i++) stage[i] = q.head + i < q.r->e.size() ? q.r->e[q.head + i] : uint32_t(SYM_END);
+  src->e = stage; src->at = 0; src->mask = 0xFFFFFFFFu;
+#endif
+  return n;
+}
 
-// ------------------------------------------------------------------------------------------------
-// Coder-warp roles (lane 0): drain the ring until SYM_END.
-// ------------------------------------------------------------------------------------------------
 struct CoderCompress {     // estimators + range encoder (recode.cpp:1068-1096 h264_symbol::execute)
   RangeEnc rc;
   AVR_DEV void begin(ByteSink* sink, uint8_t* dst, uint32_t cap, int = -1) { rc.init(sink, dst, cap); }
@@ -655,10 +673,10 @@ struct CoderCompress {     // estimators + range encoder (recode.cpp:1068-1096 h
     rc.put(t.div[c >> 8], int(bit), c & 0xFF);
     cnt[idx] = uint16_t(est_next(c, bit, limit));
   }
-  // a run of bins on ONE estimator (coefficient levels, bypass): it stays in registers
-  AVR_DEV uint32_t code_reg(const SharedTables& t, uint32_t c, uint32_t bit, uint32_t limit) {
-    rc.put(t.div[c >> 8], int(bit), c & 0xFF);
-    return est_next(c, bit, limit);
+  // ... with its estimator and reciprocal loaded earlier (no update of that estimator in between)
+  AVR_DEV void code_pre(uint16_t* cnt, uint32_t idx, uint32_t c, const DivMagic& mg, uint32_t bit, uint32_t limit) {
+    rc.put(mg, int(bit), c & 0xFF);
+    cnt[idx] = uint16_t(est_next(c, bit, limit));
   }
   // Significance bins of a 4x4-class block: the estimator index only ever grows inside a block (+1, or +17 after a
   // coefficient), so the next estimator and its reciprocal are fetched while the current bin is in the coder and
@@ -680,39 +698,55 @@ struct CoderCompress {     // estimators + range encoder (recode.cpp:1068-1096 h
       idx = idx_n; c = c_n; mg = mg_n;
     }
   }
-  // 8x8 blocks: several positions share an estimator (sig_coeff_flag_offset_8x8), so no lookahead
+  // 8x8 blocks: several positions share an estimator (sig_coeff_flag_offset_8x8): the next estimator is fetched
+  // ahead and the update forwarded when it is the same one
   AVR_DEV void sig_bins8(const SharedTables& t, uint16_t* cnt, uint32_t slab, uint64_t mask, uint32_t nnz_true) {
     uint32_t zz = 0, observed = 0;
+    uint32_t idx = slab + t.sig8[0];
+    uint32_t c = cnt[idx];
 #pragma unroll 1
-    while (observed < nnz_true && zz < 63) {
+    for (;;) {
       const uint32_t bit = uint32_t(mask >> zz) & 1u;
-      code(t, cnt, slab + observed * SIG_ZZ + t.sig8[zz], bit, LIMIT_SIG);
+      const DivMagic mg = t.div[c >> 8];
+      const uint32_t idx_n = slab + (observed + bit) * SIG_ZZ + t.sig8[zz + 1];   // sig8[63] exists (0)
+      uint32_t c_n = cnt[idx_n];
+      const uint32_t c2 = est_next(c, bit, LIMIT_SIG);
+      cnt[idx] = uint16_t(c2);
+      if (idx_n == idx) c_n = c2;
+      rc.put(mg, int(bit), c & 0xFF);
       observed += bit; zz++;
+      if (observed >= nnz_true || zz >= 63) break;
+      idx = idx_n; c = c_n;
     }
   }
-  // nnz of a block as 2 / 4 / 6 model-coded bits, least significant first (recode.cpp:858, 874-888)
+  // nnz of a block as 2 / 4 / 6 model-coded bits, least significant first (recode.cpp:858, 874-888).  The estimators
+  // of the bits are distinct and depend on the entry alone: they are fetched in pairs ahead of the coder.
   AVR_DEV void nnz_bits(const SharedTables& t, uint16_t* cnt, uint32_t cat, uint32_t w0, uint32_t w1) {
     const uint32_t maxc = k_maxc[cat];
-    const int nbits = maxc > 16 ? 6 : maxc > 4 ? 4 : 2;
+    const uint32_t nbits = maxc > 16 ? 6 : maxc > 4 ? 4 : 2;
     const uint32_t left_nz = w1 & 0xFF, above_nz = (w1 >> 8) & 0xFF, prev_nz = (w1 >> 16) & 0xFF;
     const bool has_left = (w0 >> BLK_HAS_LEFT) & 1;
     const uint32_t nnz = (w0 >> BLK_NNZ) & 63;   // 64 is coded as 0
     const uint32_t group = CNT_NZ + nz_group(int(cat), (w0 >> BLK_MB8) & 1);
-    uint32_t so_far = 0;
 #pragma unroll 1
-    for (int i = 0; i < nbits; i++) {
-      const uint32_t cur_bit = 1u << i;
-      const uint32_t lb = has_left ? (left_nz >= cur_bit) : 2;
-      const uint32_t ab = above_nz ? (above_nz >= cur_bit) : 2;   // sic: value test (recode.cpp:881)
-      const uint32_t idx = group + ((cur_bit - 1 + so_far) * 2 + (prev_nz >= cur_bit)) * 9 + lb * 3 + ab;
-      const uint32_t bit = (nnz >> i) & 1;
-      code(t, cnt, idx, bit, LIMIT_ANY);
-      so_far |= bit << i;
+    for (uint32_t i = 0; i < nbits; i += 2) {
+      uint32_t idx[2], c[2];
+#pragma unroll
+      for (uint32_t k = 0; k < 2; k++) {
+        const uint32_t cur_bit = 1u << (i + k);
+        const uint32_t so_far = nnz & (cur_bit - 1);
+        const uint32_t lb = has_left ? (left_nz >= cur_bit) : 2;
+        const uint32_t ab = above_nz ? (above_nz >= cur_bit) : 2;   // sic: value test (recode.cpp:881)
+        idx[k] = group + ((cur_bit - 1 + so_far) * 2 + (prev_nz >= cur_bit)) * 9 + lb * 3 + ab;
+        c[k] = cnt[idx[k]];
+      }
+      const DivMagic m0 = t.div[c[0] >> 8], m1 = t.div[c[1] >> 8];
+      code_pre(cnt, idx[0], c[0], m0, (nnz >> i) & 1, LIMIT_ANY);
+      code_pre(cnt, idx[1], c[1], m1, (nnz >> (i + 1)) & 1, LIMIT_ANY);
     }
   }
   // one entry; returns true on SYM_END
-  template <class Src>
-  AVR_DEV bool entry(Src& s, const SharedTables& t, uint16_t* cnt) {
+  AVR_DEV bool entry(WordSrc& s, const SharedTables& t, uint16_t* cnt) {
     const uint32_t e = s.take();
     if (e & (SYM_END | SYM_LEVEL | SYM_BLOCK)) {
       if (e & SYM_END) return true;
@@ -728,78 +762,48 @@ struct CoderCompress {     // estimators + range encoder (recode.cpp:1068-1096 h
         } else sig_bins4(t, cnt, slab, mlo, nnz_true, uint32_t(k_maxc[cat]) - 1);
         return false;
       }
-      // one coefficient level: first bin, run of "greater than one" bins, sign
-      const uint32_t b1 = (e >> LVL_BIT1) & 1;
-      code(t, cnt, CNT_CTX + (e & 0x1FF), b1, LIMIT_ANY);
+      // one coefficient level: first bin, run of "greater than one" bins, sign -- three distinct estimators, all
+      // fetched before the first bin goes through the coder
+      const uint32_t b1 = (e >> LVL_BIT1) & 1, has_sign = (e >> LVL_HAS_SIGN) & 1;
+      const uint32_t i1 = CNT_CTX + (e & 0x1FF), g = CNT_CTX + ((e >> LVL_GCTX) & 0x1FF);
+      const uint32_t c1 = cnt[i1];
+      uint32_t cg = cnt[g];
+      const uint32_t cs = cnt[CNT_BYPASS];
+      const DivMagic m1 = t.div[c1 >> 8], ms = t.div[cs >> 8];
+      code_pre(cnt, i1, c1, m1, b1, LIMIT_ANY);
       if (b1) {
-        const uint32_t g = CNT_CTX + ((e >> LVL_GCTX) & 0x1FF);
-        uint32_t c = cnt[g];
 #pragma unroll 1
-        for (uint32_t r = (e >> LVL_RUN) & 15; r > 0; r--) c = code_reg(t, c, 1, LIMIT_ANY);
-        if ((e >> LVL_TERM) & 1) c = code_reg(t, c, 0, LIMIT_ANY);
-        cnt[g] = uint16_t(c);
+        for (uint32_t r = (e >> LVL_RUN) & 15; r > 0; r--) { rc.put(t.div[cg >> 8], 1, cg & 0xFF); cg = est_next(cg, 1, LIMIT_ANY); }
+        if ((e >> LVL_TERM) & 1) { rc.put(t.div[cg >> 8], 0, cg & 0xFF); cg = est_next(cg, 0, LIMIT_ANY); }
+        cnt[g] = uint16_t(cg);
       }
-      if ((e >> LVL_HAS_SIGN) & 1) code(t, cnt, CNT_BYPASS, (e >> LVL_SIGN) & 1, LIMIT_ANY);
+      if (has_sign) code_pre(cnt, CNT_BYPASS, cs, ms, (e >> LVL_SIGN) & 1, LIMIT_ANY);
       return false;
     }
     const uint32_t idx = e & 0xFFFF, bit = (e >> SYM_BIT_SHIFT) & 1;
     code(t, cnt, idx, bit, LIMIT_ANY);
-    if (idx == CNT_TERM && bit) range_enc_finish(rc.sink, rc.low, rc.range);                      // recode.cpp:1092-1095
+    if (idx == CNT_TERM && bit) range_enc_finish(rc.sink, rc.low, rc.range);   // recode.cpp:1092-1095
     return false;
   }
-  AVR_DEV void run(Consumer& q, const SharedTables& t, uint16_t* cnt, U2*) {
+  // Drains a ring until SYM_END.  ALL lanes of the coder warp call this.  far: nullptr = the ring's own shared-memory
+  // entries; else (wide slices) the ring's entries are in global memory at `far`, staged through `stage`, so that this
+  // coder may fall a good part of a macroblock row behind the parser and catch up while the parser feeds another stream.
+  AVR_DEV void run(RingShared* r, const uint32_t* far, uint32_t far_cap, bool patient, const SharedTables& t, uint16_t* cnt,
+                   uint32_t* stage, int lane) {
+    RingReader q; q.init(r, patient);
     for (;;) {
-      const uint32_t end = q.head + q.wait_avail();
-      bool done = false;
-#pragma unroll 1
-      while (!done && int32_t(end - uint32_t(q.head)) > 0) done = entry(q, t, cnt);
-      q.release();
-      if (done) break;
-    }
-  }
-  // Wide slices: the ring is long and in global memory (far), so that this coder may fall a good part of a
-  // macroblock row behind the parser and catch up while the parser feeds the other stream.  ALL lanes call this:
-  // they stage up to 128 words with coalesced loads, lane 0 works through the entries of the stage.
-  // stage[0..127 + ENTRY_MAX_WORDS] words, stage[STAGE_FLAG] != 0: SYM_END seen, stage[STAGE_USED]: words consumed.
-  enum : uint32_t { STAGE_WORDS = 128, STAGE_FLAG = 136, STAGE_USED = 137 };
-  AVR_DEV void run_far(RingShared* r, const uint32_t* far, uint32_t far_cap, const SharedTables& t, uint16_t* cnt, uint32_t* stage, int lane) {
-    uint32_t head = 0;
-    for (;;) {
-      uint32_t n;
-#if defined(__CUDACC__) && !defined(AVR_HOST_EMULATION)
-      uint32_t avail;
-      for (uint32_t polls = 0; (avail = *reinterpret_cast<volatile uint32_t*>(&r->tail_pub) - head) == 0;) wide_backoff(polls);
-      ring_fence();
-      n = avail < uint32_t(STAGE_WORDS) ? avail : uint32_t(STAGE_WORDS);
-      const volatile uint32_t* src = far;
-      for (uint32_t i = uint32_t(lane); i < n; i += 32) stage[i] = src[(head + i) & (far_cap - 1)];
-      __syncwarp();
-      const bool more = avail > n;   // the stage may end inside an entry: stop ENTRY_MAX_WORDS short of it
-#else
-      (void)far; (void)far_cap;
-      n = uint32_t(r->e.size() - head > STAGE_WORDS ? STAGE_WORDS : r->e.size() - head);
-      for (uint32_t i = 0; i < n; i++) stage[i] = r->e[head + i];
-      if (n == 0) { stage[0] = SYM_END; n = 1; }
-      const bool more = r->e.size() - head > n;
-#endif
+      WordSrc src;
+      const uint32_t n = coder_fetch(q, far, far_cap, stage, lane, &src);
+      uint32_t used = 0, done = 0;
       if (lane == 0) {
-        StageSrc s; s.w = stage; s.k = 0;
-        const uint32_t stop = more ? n - (ENTRY_MAX_WORDS - 1) : n;
-        bool done = false;
+        const uint32_t at0 = src.at;
 #pragma unroll 1
-        while (!done && s.k < stop) done = entry(s, t, cnt);
-        stage[STAGE_FLAG] = done ? 1u : 0u;
-        stage[STAGE_USED] = s.k;
-#if defined(__CUDACC__) && !defined(AVR_HOST_EMULATION)
-        ring_fence();
-        *reinterpret_cast<volatile uint32_t*>(&r->head_pub) = head + s.k;
-#endif
+        while (!done && src.at - at0 < n) done = entry(src, t, cnt) ? 1u : 0u;
+        used = src.at - at0;
       }
-      AVR_SYNCWARP_CORE();
-      head += stage[STAGE_USED];
-      const uint32_t end = stage[STAGE_FLAG];
-      AVR_SYNCWARP_CORE();
-      if (end) break;
+      used = AVR_BCAST_CORE(used); done = AVR_BCAST_CORE(done);
+      q.release(used, lane);
+      if (done) break;
     }
   }
   AVR_DEV uint32_t out_bytes() const { return rc.sink->n; }
@@ -843,8 +847,7 @@ struct CoderDecompress {   // CABAC re-encoder (cabac_code.h:16-86; recode.cpp:1
     }
   }
   // everything but SYM_END and the wide-slice specials
-  template <class Src>
-  AVR_DEV void entry(Src& s, const SharedTables& t, U2* cstate, uint32_t e) {
+  AVR_DEV void entry(WordSrc& s, const SharedTables& t, U2* cstate, uint32_t e) {
     if (e & (SYM_LEVEL | SYM_BLOCK)) {
       if (e & SYM_BLOCK) {
         const uint32_t cat = e & 7, nnz_true = (e >> BLK_NNZ) & 0x7F;
@@ -877,85 +880,67 @@ struct CoderDecompress {   // CABAC re-encoder (cabac_code.h:16-86; recode.cpp:1
     else if (kind == SYM_BYPASS) cabac.bypass(bit);
     else cabac.terminate(bit);
   }
-  AVR_DEV void run(Consumer& q, const SharedTables& t, uint16_t*, U2* cstate) {
+  // Ordinary slices: drains the shared-memory ring until SYM_END.  ALL lanes call this.
+  AVR_DEV void run(RingShared* r, const SharedTables& t, U2* cstate, uint32_t* stage, int lane) {
+    RingReader q; q.init(r, false);
     for (;;) {
-      const uint32_t end = q.head + q.wait_avail();
-      bool done = false;
+      WordSrc src;
+      const uint32_t n = coder_fetch(q, nullptr, 0, stage, lane, &src);
+      uint32_t used = 0, done = 0;
+      if (lane == 0) {
+        const uint32_t at0 = src.at;
 #pragma unroll 1
-      while (int32_t(end - uint32_t(q.head)) > 0) {
-        const uint32_t e = q.take();
-        if (e & SYM_END) { done = true; break; }
-        entry(q, t, cstate, e);
+        while (src.at - at0 < n) {
+          const uint32_t e = src.take();
+          if (e & SYM_END) { done = 1; break; }
+          entry(src, t, cstate, e);
+        }
+        used = src.at - at0;
       }
-      q.release();
+      used = AVR_BCAST_CORE(used); done = AVR_BCAST_CORE(done);
+      q.release(used, lane);
       if (done) break;
     }
   }
   // Wide slices: ring j (entries in global memory, far[j * far_cap ...]; indices in rings[j]) carries the
   // macroblock rows j, j + K, ... and every row ends in SP_ROW_END.  ALL lanes of the warp call this: they
-  // fetch a batch of words with one coalesced load, lane 0 encodes the entries in it.  Leaves on the
+  // stage a batch of words with coalesced loads, lane 0 encodes the entries in it.  Leaves on the
   // first SYM_END and then drains the other rings so that their parser warps can finish.
-  enum : uint32_t { STAGE_WORDS = 64, STAGE_USED = 72, STAGE_WHY = 73 };
   AVR_DEV void run_wide(RingShared* rings, uint32_t n_rings, const uint32_t* far, uint32_t far_cap, const SharedTables& t, U2* cstate,
                         uint32_t* stage, int lane) {
-    // stage[0..63 + ENTRY_MAX_WORDS]: the batch; stage[STAGE_USED]: words used; stage[STAGE_WHY]: 0 go on, 1 row end, 2 SYM_END
-    uint32_t cur = 0, qpd = 0, head = 0;
+    uint32_t cur = 0, qpd = 0;
     bool draining = false;
+    RingReader q; q.init(&rings[0], true);
     for (;;) {
-      RingShared* r = &rings[cur];
-      uint32_t n;
-#if defined(__CUDACC__) && !defined(AVR_HOST_EMULATION)
-      uint32_t avail;
-      for (uint32_t polls = 0; (avail = *reinterpret_cast<volatile uint32_t*>(&r->tail_pub) - head) == 0;) wide_backoff(polls);
-      ring_fence();
-      n = avail < uint32_t(STAGE_WORDS) ? avail : uint32_t(STAGE_WORDS);
-      const volatile uint32_t* src = far + size_t(cur) * far_cap;
-      for (uint32_t i = uint32_t(lane); i < n; i += 32) stage[i] = src[(head + i) & (far_cap - 1)];
-      __syncwarp();
-      const bool more = avail > n;
-#else
-      (void)far; (void)far_cap;
-      n = uint32_t(r->e.size() - head > STAGE_WORDS ? STAGE_WORDS : r->e.size() - head);
-      for (uint32_t i = 0; i < n; i++) stage[i] = r->e[head + i];
-      if (n == 0) { stage[0] = SYM_END; n = 1; }
-      const bool more = r->e.size() - head > n;
-#endif
-      if (lane == 0) {   // the serial part: plain single-lane code, nothing warp-wide per entry (a warp-wide loop with
-        // lane 0 predicated per entry cost 2x: every entry paid for the divergence and reconvergence)
-        StageSrc s; s.w = stage; s.k = 0;
-        const uint32_t stop = more ? n - (ENTRY_MAX_WORDS - 1) : n;
-        uint32_t why = 0;
+      WordSrc src;
+      const uint32_t n = coder_fetch(q, far ? far + size_t(cur) * far_cap : nullptr, far_cap, stage, lane, &src);
+      uint32_t used = 0, why = 0;   // why: 0 go on, 1 row end, 2 SYM_END
+      if (lane == 0) {   // the serial part: plain single-lane code, nothing warp-wide per entry
+        const uint32_t at0 = src.at;
 #pragma unroll 1
-        while (s.k < stop) {
-          const uint32_t e = s.take();
+        while (src.at - at0 < n) {
+          const uint32_t e = src.take();
           if (e & SYM_END) { why = 2; break; }
-          if (draining) {   // skip the payload words of a block entry
-            if (e & SYM_BLOCK) s.k += (e & 7) == 5 ? 2 : 1;
-            continue;
-          }
+          if (draining) { if (e & SYM_BLOCK) src.at += (e & 7) == 5 ? 2 : 1; continue; }   // skip a block's mask words
           if (!(e & (SYM_LEVEL | SYM_BLOCK)) && (e & (3u << SYM_KIND_SHIFT)) == SYM_SPECIAL) {
             if (e & SP_ROW_END) { qpd = e & 1; why = 1; break; }
             cabac.decision(t, int((e >> SYM_BIT_SHIFT) & 1), &cstate[60 + qpd]);
-          } else entry(s, t, cstate, e);
+          } else entry(src, t, cstate, e);
         }
-        stage[STAGE_USED] = s.k; stage[STAGE_WHY] = why;
-#if defined(__CUDACC__) && !defined(AVR_HOST_EMULATION)
-        ring_fence();
-        *reinterpret_cast<volatile uint32_t*>(&r->head_pub) = head + s.k;
-#endif
+        used = src.at - at0;
       }
-      AVR_SYNCWARP_CORE();
-      head += stage[STAGE_USED];
-      const uint32_t why = stage[STAGE_WHY];
-      AVR_SYNCWARP_CORE();
+      used = AVR_BCAST_CORE(used); why = AVR_BCAST_CORE(why);
+      q.release(used, lane);
       if (why == 0) continue;
-      if (why == 2) { draining = true; r->cons_head = 0xFFFFFFFFu; }
-      else r->cons_head = head;
+      if (why == 2) { draining = true; q.r->cons_head = 0xFFFFFFFFu; }
+      else q.r->cons_head = uint32_t(q.head);
+      AVR_SYNCWARP_CORE();
       // next ring: the next row's, or (draining) the next one that has not delivered SYM_END yet
       uint32_t tries = 0;
       do { cur = cur + 1 == n_rings ? 0 : cur + 1; tries++; } while (draining && tries <= n_rings && rings[cur].cons_head == 0xFFFFFFFFu);
       if (draining && tries > n_rings) break;
-      head = uint32_t(rings[cur].cons_head);
+      q.r = &rings[cur];
+      q.head = uint32_t(rings[cur].cons_head);
     }
   }
   AVR_DEV uint32_t out_bytes() const { return cabac.sink->n; }
@@ -963,25 +948,192 @@ struct CoderDecompress {   // CABAC re-encoder (cabac_code.h:16-86; recode.cpp:1
 };
 
 // ------------------------------------------------------------------------------------------------
-// Parser-warp direction policies (lane 0): the three bin primitives + the model-coded side bits.
+// Where a parser warp keeps its engines BETWEEN residual blocks: shared memory.  Macroblock-level syntax
+// (a tenth of the bins, but 57 call sites in the walker) goes through ONE out-of-line copy of each bin
+// primitive that works on this state; Walker::residual() loads the state into registers (enter), runs
+// its loops with everything inlined, and stores it back (leave).  With every primitive inlined at
+// every site the decompression kernels were 230-250 KB of SASS and stalled one cycle per issued
+// instruction on instruction fetch (profiles/r1k_ncu_full_summary.txt).
+// ------------------------------------------------------------------------------------------------
+struct ParserHome {
+  RingShared* r;            // ring, producer side
+  uint32_t* ents;           //   the words: r->e, or (wide slices) a much longer ring in global memory
+  uint32_t* far_base;       //   wide compression: ring j lives at far_base + j * cap (null: the rings' own e[])
+  uint32_t cap, tail, limit;
+  const SharedTables* tab;
+  U2* cstate;
+  uint16_t* cnt;
+  const uint8_t* win;       // input window
+  uint32_t skew;
+  uint32_t val, range, pos; // compress: CabacIn
+  int32_t nbits;
+  uint64_t low, drange;     // decompress: RangeDec (its read position: dec)
+  DecHome dec;
+  uint32_t n_bins;          // bins walked so far (low word)
+};
+
+#if defined(__CUDACC__) && !defined(AVR_HOST_EMULATION)
+AVR_DEV void home_ring_init(ParserHome* h, RingShared* ring, uint32_t* far_entries, uint32_t far_cap) {
+  h->r = ring; h->tail = 0; h->limit = RING_PUBLISH;
+  h->ents = far_entries ? far_entries : ring->e;
+  h->cap = far_entries ? far_cap : uint32_t(RING_ENTRIES);
+  h->far_base = far_entries;
+}
+AVR_DEV void home_push(ParserHome* h, uint32_t e) {
+  uint32_t tail = h->tail;
+  if (int32_t(h->limit - tail) < 1) h->limit = ring_slow(h->r, tail, 1, h->cap);
+  h->ents[tail & (h->cap - 1)] = e;
+  h->tail = tail + 1;
+}
+AVR_DEV void home_publish(ParserHome* h) {
+  ring_fence();
+  *reinterpret_cast<volatile uint32_t*>(&h->r->tail_pub) = h->tail;
+}
+AVR_DEV void home_switch_to(ParserHome* h, RingShared* next, uint32_t index) {   // wide compression: the next macroblock row goes to another ring
+  home_publish(h);
+  h->r->prod_tail = h->tail;
+  h->r = next;
+  h->ents = h->far_base ? h->far_base + size_t(index) * h->cap : next->e;
+  h->tail = next->prod_tail;
+  h->limit = ring_slow(next, h->tail, ENTRY_MAX_WORDS, h->cap);
+}
+#else
+inline void home_ring_init(ParserHome* h, RingShared* ring, uint32_t*, uint32_t) { h->r = ring; }
+inline void home_push(ParserHome* h, uint32_t e) { h->r->e.push_back(e); }
+inline void home_publish(ParserHome*) {}
+inline void home_switch_to(ParserHome* h, RingShared* next, uint32_t) { h->r = next; }
+#endif
+
+// register copy of the ring's producer side, valid between enter() and leave()
+struct RingWriter {
+#if defined(__CUDACC__) && !defined(AVR_HOST_EMULATION)
+  uint32_t* ents;
+  uint32_t cap, tail, limit;
+  AVR_DEV void enter(const ParserHome* h) { ents = h->ents; cap = h->cap; tail = h->tail; limit = h->limit; }
+  AVR_DEV void leave(ParserHome* h) const { h->tail = tail; h->limit = limit; }
+  AVR_DEV void reserve(ParserHome* h, uint32_t n) { if (int32_t(limit - tail) < int32_t(n)) limit = ring_slow(h->r, tail, n, cap); }
+  AVR_DEV void put(ParserHome*, uint32_t w) { ents[tail & (cap - 1)] = w; tail++; }
+#else
+  void enter(const ParserHome*) {}
+  void leave(ParserHome*) const {}
+  void reserve(ParserHome*, uint32_t) {}
+  void put(ParserHome* h, uint32_t w) { h->r->e.push_back(w); }
+#endif
+};
+
+// ---- the out-of-line bin primitives of macroblock-level syntax --------------------------------------
+// What a call costs is its chain of dependent memory operations, so: the caller passes the addresses it already has
+// in registers (context entry / estimator, tables), and every field of the home state is read up front, before the
+// first store (a store through one of these generic pointers could alias any of them as far as the compiler knows).
+AVR_DEV void home_load(const ParserHome* h, CabacIn& c, ByteWindow& w) {
+  c.val = h->val; c.range = h->range; c.pos = h->pos; c.nbits = h->nbits;
+  w.win = const_cast<uint8_t*>(h->win); w.skew = h->skew;
+}
+AVR_DEV void home_store(ParserHome* h, const CabacIn& c) { h->val = c.val; h->range = c.range; h->pos = c.pos; h->nbits = c.nbits; }
+struct HomeRing {   // the producer side of the ring, read in one go
+  RingShared* r; uint32_t* ents; uint32_t cap, tail, limit, n_bins;
+  AVR_DEV void load(const ParserHome* h) { r = h->r; ents = h->ents; cap = h->cap; tail = h->tail; limit = h->limit; n_bins = h->n_bins; }
+  AVR_DEV void push_and_store(ParserHome* h, uint32_t e) {
+#if defined(__CUDACC__) && !defined(AVR_HOST_EMULATION)
+    if (int32_t(limit - tail) < 1) { limit = ring_slow(r, tail, 1, cap); h->limit = limit; }
+    ents[tail & (cap - 1)] = e;
+    h->tail = tail + 1;
+#else
+    h->r->e.push_back(e);
+#endif
+    h->n_bins = n_bins + 1;
+  }
+};
+// compress: CABAC decision on the context entry at `ctx`, modelled with estimator `model_ctx`
+AVR_DEV_NOINLINE uint32_t slow_c_bin(ParserHome* h, U2* ctx, const SharedTables* tab, uint32_t model_ctx) {
+  const U2 e = *ctx;
+  CabacIn c; ByteWindow w; HomeRing q;
+  home_load(h, c, w);
+  q.load(h);
+  U2 n;
+  const int b = c.decide_core(w, *tab, e, &n);
+  *ctx = n;
+  home_store(h, c);
+  q.push_and_store(h, uint32_t(CNT_CTX + model_ctx) | uint32_t(b) << SYM_BIT_SHIFT);
+  return uint32_t(b);
+}
+AVR_DEV_NOINLINE uint32_t slow_c_bypass(ParserHome* h) {
+  CabacIn c; ByteWindow w; HomeRing q;
+  home_load(h, c, w);
+  q.load(h);
+  const int b = c.bypass(w);
+  home_store(h, c);
+  q.push_and_store(h, CNT_BYPASS | uint32_t(b) << SYM_BIT_SHIFT);
+  return uint32_t(b);
+}
+AVR_DEV_NOINLINE uint32_t slow_c_terminate(ParserHome* h) {
+  CabacIn c; ByteWindow w; HomeRing q;
+  home_load(h, c, w);
+  q.load(h);
+  const int b = c.terminate(w);
+  home_store(h, c);
+  q.push_and_store(h, CNT_TERM | uint32_t(b) << SYM_BIT_SHIFT);
+  return uint32_t(b);
+}
+// decompress: one model-coded bin with the estimator at `est`; `entry` (without the bin) goes to the CABAC re-encoder
+AVR_DEV_NOINLINE uint32_t slow_d_bin(ParserHome* h, uint16_t* est, const SharedTables* tab, uint32_t entry) {
+  const uint32_t c = *est;
+  RangeDec rc; rc.low = h->low; rc.range = h->drange; rc.home = &h->dec;
+  HomeRing q;
+  q.load(h);
+  const DivMagic mg = tab->div[c >> 8];
+  const int b = rc.get(mg, c & 0xFF);
+  *est = uint16_t(est_next(c, uint32_t(b), LIMIT_ANY));
+  h->low = rc.low; h->drange = rc.range;
+  q.push_and_store(h, entry | uint32_t(b) << SYM_BIT_SHIFT);
+  return uint32_t(b);
+}
+
+// ------------------------------------------------------------------------------------------------
+// Parser-warp direction policies (lane 0).  bin / bypass / terminate / bin_row_qpd / row_end work on
+// the home state (macroblock-level syntax); everything else is register-resident and only valid
+// between enter() and leave() (Walker::residual).
 // ------------------------------------------------------------------------------------------------
 struct Compress {
   static constexpr bool kDecompress = false;
   typedef CoderCompress Coder;
   ByteWindow in;
-  CabacIn cabac;
-  Producer q;
+  ParserHome* h;
   U2* cstate;        // parser owns the CABAC context states
-  AVR_DEV void begin(const uint8_t* src, uint32_t n, uint8_t* window, uint32_t tail_byte, RingShared* ring, uint16_t*, U2* states,
-                     uint32_t* far_entries = nullptr, uint32_t far_cap = 0) {
-    in.attach(src, n, window, tail_byte); q.init(ring, far_entries, far_cap); cstate = states;
+  const SharedTables* tabp;
+  CabacIn cabac;     // register copy
+  RingWriter q;
+  AVR_DEV void begin(ParserHome* home, const uint8_t* src, uint32_t n, uint8_t* window, uint32_t tail_byte, RingShared* ring,
+                     const SharedTables* tab, uint16_t* counters, U2* states, uint32_t* far_entries = nullptr, uint32_t far_cap = 0) {
+    h = home;
+    in.attach(src, n, window, tail_byte);
+    cstate = states; tabp = tab;
+    home_ring_init(h, ring, far_entries, far_cap);
+    h->tab = tab; h->cstate = states; h->cnt = counters; h->win = window; h->skew = in.skew; h->n_bins = 0;
   }
-  AVR_DEV void set_home(DecHome*) {}
-  AVR_DEV void start_bins(const SharedTables&) { cabac.init(in); }
+  AVR_DEV void start_bins(const SharedTables&) { CabacIn c; c.init(in); home_store(h, c); }
   AVR_DEV void finish_bins() {}
-  AVR_DEV int bin(const SharedTables& t, int ctx) {
+  // ---- home state ----
+  AVR_DEV int bin(int ctx) { return int(slow_c_bin(h, &cstate[ctx], tabp, uint32_t(ctx))); }
+  // wide slices: first mb_qp_delta bin of a macroblock row -- decoded with its true context, modelled with
+  // the estimator of context 60 whatever the previous row ended on (the rows are decoded in parallel)
+  AVR_DEV int bin_row_qpd(int true_ctx) { return int(slow_c_bin(h, &cstate[true_ctx], tabp, 60)); }
+  AVR_DEV void row_end(int) {}
+  AVR_DEV int bypass() { return int(slow_c_bypass(h)); }
+  AVR_DEV int terminate() { return int(slow_c_terminate(h)); }
+  AVR_DEV uint32_t in_pos() const { return h->pos; }
+  // After end_of_slice = 1 the last bit in the arithmetic decoder's offset register is rbsp_stop_one_bit (H.264
+  // 9.3.4.5 writes it as the low bit of the flush), so the bits taken so far minus that one are exactly the payload
+  // -- the byte of a stop bit that sits alone being outside it (h264.c:1298-1315).  A slice that ends anywhere
+  // else was mis-located or carries junk: it would decompress to another size and lose the whole file, so it is
+  // reported corrupt and stays a literal (recode.cpp:1289-1296).
+  AVR_DEV bool consumed_all() const { return (h->pos * 8u - uint32_t(h->nbits) + 6u) / 8u == in.size; }
+  // ---- registers ----
+  AVR_DEV void enter(const SharedTables&) { ByteWindow w; home_load(h, cabac, w); q.enter(h); }
+  AVR_DEV void leave(uint32_t bins) { home_store(h, cabac); q.leave(h); h->n_bins += bins; }
+  AVR_DEV int fast_bin(const SharedTables& t, int ctx) {   // an ordinary bin in register mode
     const int b = cabac.decision(in, t, &cstate[ctx]);
-    q.push(uint32_t(CNT_CTX + ctx) | uint32_t(b) << SYM_BIT_SHIFT);
+    q.reserve(h, 1); q.put(h, uint32_t(CNT_CTX + ctx) | uint32_t(b) << SYM_BIT_SHIFT);
     return b;
   }
   // coefficient levels: CABAC side only, the whole level crosses the ring as one entry (lvl_push)
@@ -996,85 +1148,90 @@ struct Compress {
     return b;
   }
   AVR_DEV int lvl_sign(const SharedTables&) { return cabac.bypass(in); }
-  AVR_DEV void lvl_push(uint32_t entry) { q.push(entry); }
-  // wide slices: first mb_qp_delta bin of a macroblock row -- decoded with its true context, modelled with
-  // the estimator of context 60 whatever the previous row ended on (the rows are decoded in parallel)
-  AVR_DEV int bin_row_qpd(const SharedTables& t, int true_ctx) {
-    const int b = cabac.decision(in, t, &cstate[true_ctx]);
-    q.push(uint32_t(CNT_CTX + 60) | uint32_t(b) << SYM_BIT_SHIFT);
+  AVR_DEV void lvl_push(uint32_t entry) { q.reserve(h, 1); q.put(h, entry); }
+  AVR_DEV int lvl_bypass(const SharedTables&) {   // Exp-Golomb escape bins
+    const int b = cabac.bypass(in);
+    q.reserve(h, 1); q.put(h, CNT_BYPASS | uint32_t(b) << SYM_BIT_SHIFT);
     return b;
   }
-  AVR_DEV void row_end(int) {}
-  AVR_DEV int bypass(const SharedTables&) { const int b = cabac.bypass(in); q.push(CNT_BYPASS | uint32_t(b) << SYM_BIT_SHIFT); return b; }
-  AVR_DEV int terminate(const SharedTables&) { const int b = cabac.terminate(in); q.push(CNT_TERM | uint32_t(b) << SYM_BIT_SHIFT); return b; }
   // significance map: CABAC side (the model side is derived from the block entry by the coder warp)
   AVR_DEV U2 sig_peek(int ctx) const { return cstate[ctx]; }
   AVR_DEV int sig_get(const SharedTables& t, int ctx) { return cabac.decision(in, t, &cstate[ctx]); }
   AVR_DEV int sig_get_pre(const SharedTables& t, const U2 e, int ctx) { return cabac.decide(in, t, e, &cstate[ctx]); }
   // nnz: count of this block; left / above / previous-picture counts of the NZ key; mb8: the macroblock has an 8x8 block
   AVR_DEV void block_push(int cat, uint32_t nnz, bool mb8, bool has_left, uint32_t left_nz, uint32_t above_nz, uint32_t prev_nz, uint64_t mask) {
-    q.reserve(4);
-    q.put(SYM_BLOCK | uint32_t(cat) | nnz << BLK_NNZ | (mb8 ? 1u << BLK_MB8 : 0u) | (has_left ? 1u << BLK_HAS_LEFT : 0u));
-    q.put(left_nz | above_nz << 8 | prev_nz << 16);
-    q.put(uint32_t(mask));
-    if (cat == 5) q.put(uint32_t(mask >> 32));
+    q.reserve(h, 4);
+    q.put(h, SYM_BLOCK | uint32_t(cat) | nnz << BLK_NNZ | (mb8 ? 1u << BLK_MB8 : 0u) | (has_left ? 1u << BLK_HAS_LEFT : 0u));
+    q.put(h, left_nz | above_nz << 8 | prev_nz << 16);
+    q.put(h, uint32_t(mask));
+    if (cat == 5) q.put(h, uint32_t(mask >> 32));
   }
-  AVR_DEV uint32_t in_pos() const { return cabac.pos; }
 };
 
 struct Decompress {
   static constexpr bool kDecompress = true;
   typedef CoderDecompress Coder;
   ByteWindow in;
-  RangeDec rc;
-  Producer q;
+  ParserHome* h;
   uint16_t* cnt;     // parser owns the estimators
-  DecHome* home;     // read position of the range decoder (shared memory)
-  AVR_DEV void begin(const uint8_t* src, uint32_t n, uint8_t* window, uint32_t, RingShared* ring, uint16_t* counters, U2*,
-                     uint32_t* far_entries = nullptr, uint32_t far_cap = 0) {
-    in.attach(src, n, window, 0); q.init(ring, far_entries, far_cap); cnt = counters;
-    byp_c = EST_INIT;
-  }
-  AVR_DEV void set_home(DecHome* h) { home = h; }
-  // The bypass estimator codes every sign and escape bit: it is kept in registers together with its
-  // reciprocal for the length of a slice (read at start_bins, written back by finish_bins).
+  const SharedTables* tabp;
+  RangeDec rc;       // register copy
+  RingWriter q;
+  // The bypass estimator codes every sign and escape bit: inside a residual block it is kept in registers
+  // together with its reciprocal.
   uint32_t byp_c;
   DivMagic byp_mg;
-  AVR_DEV void start_bins(const SharedTables& t) {
-    rc.init(home, in);
+  AVR_DEV void begin(ParserHome* home, const uint8_t* src, uint32_t n, uint8_t* window, uint32_t, RingShared* ring,
+                     const SharedTables* tab, uint16_t* counters, U2* states, uint32_t* far_entries = nullptr, uint32_t far_cap = 0) {
+    h = home;
+    in.attach(src, n, window, 0);
+    cnt = counters; tabp = tab;
+    home_ring_init(h, ring, far_entries, far_cap);
+    h->tab = tab; h->cstate = states; h->cnt = counters; h->win = window; h->skew = in.skew; h->n_bins = 0;
+  }
+  AVR_DEV void start_bins(const SharedTables&) {
+    RangeDec d; d.init(&h->dec, in);
+    h->low = d.low; h->drange = d.range;
+  }
+  AVR_DEV void finish_bins() {}
+  // ---- home state ----
+  AVR_DEV int bin(int ctx) { return int(slow_d_bin(h, &cnt[CNT_CTX + ctx], tabp, uint32_t(ctx) | SYM_DECISION)); }
+  AVR_DEV int bin_row_qpd(int) { return int(slow_d_bin(h, &cnt[CNT_CTX + 60], tabp, SYM_SPECIAL | SP_QPD)); }   // see Compress::bin_row_qpd
+  AVR_DEV void row_end(int qpd_nonzero) { home_push(h, SYM_SPECIAL | SP_ROW_END | uint32_t(qpd_nonzero)); }
+  AVR_DEV int bypass() { return int(slow_d_bin(h, &cnt[CNT_BYPASS], tabp, SYM_BYPASS)); }
+  AVR_DEV int terminate() { return int(slow_d_bin(h, &cnt[CNT_TERM], tabp, SYM_TERMINATE)); }
+  AVR_DEV uint32_t in_pos() const { return h->dec.pos; }
+  AVR_DEV bool consumed_all() const { return true; }   // the rebuilt size is checked by the host against Block.size
+  // ---- registers ----
+  AVR_DEV void enter(const SharedTables& t) {
+    rc.low = h->low; rc.range = h->drange; rc.home = &h->dec;
+    q.enter(h);
     byp_c = cnt[CNT_BYPASS];
     byp_mg = t.div[byp_c >> 8];
   }
-  AVR_DEV void finish_bins() { cnt[CNT_BYPASS] = uint16_t(byp_c); }
+  AVR_DEV void leave(uint32_t bins) {
+    h->low = rc.low; h->drange = rc.range;
+    q.leave(h);
+    cnt[CNT_BYPASS] = uint16_t(byp_c);
+    h->n_bins += bins;
+  }
   AVR_DEV int coded(const SharedTables& t, uint32_t idx, uint32_t limit) {
     const uint32_t c = cnt[idx];
     const int b = rc.get(t.div[c >> 8], c & 0xFF);
     cnt[idx] = uint16_t(est_next(c, uint32_t(b), limit));
     return b;
   }
-  AVR_DEV int bin(const SharedTables& t, int ctx) {
+  AVR_DEV int fast_bin(const SharedTables& t, int ctx) {   // an ordinary bin in register mode
     const int b = coded(t, uint32_t(CNT_CTX + ctx), LIMIT_ANY);
-    q.push(uint32_t(ctx) | uint32_t(b) << SYM_BIT_SHIFT | SYM_DECISION);
+    q.reserve(h, 1); q.put(h, uint32_t(ctx) | uint32_t(b) << SYM_BIT_SHIFT | SYM_DECISION);
     return b;
   }
-  AVR_DEV int bin_row_qpd(const SharedTables& t, int) {   // see Compress::bin_row_qpd
-    const int b = coded(t, uint32_t(CNT_CTX + 60), LIMIT_ANY);
-    q.push(uint32_t(b) << SYM_BIT_SHIFT | SYM_SPECIAL | SP_QPD);
-    return b;
-  }
-  AVR_DEV void row_end(int qpd_nonzero) { q.push(SYM_SPECIAL | SP_ROW_END | uint32_t(qpd_nonzero)); }
   AVR_DEV int byp_bin(const SharedTables& t) {
     const int b = rc.get(byp_mg, byp_c & 0xFF);
     byp_c = est_next(byp_c, uint32_t(b), LIMIT_ANY);
     byp_mg = t.div[byp_c >> 8];
     return b;
   }
-  AVR_DEV int bypass(const SharedTables& t) {
-    const int b = byp_bin(t);
-    q.push(uint32_t(b) << SYM_BIT_SHIFT | SYM_BYPASS);
-    return b;
-  }
-  AVR_DEV int terminate(const SharedTables& t) { const int b = coded(t, CNT_TERM, LIMIT_ANY); q.push(uint32_t(b) << SYM_BIT_SHIFT | SYM_TERMINATE); return b; }
   // significance-map bins with both possible successors prefetched (see Walker::residual)
   struct SigEntry { uint32_t c; DivMagic mg; };
   AVR_DEV SigEntry sig_fetch(const SharedTables& t, uint32_t idx) const {
@@ -1107,16 +1264,20 @@ struct Decompress {
     return b;
   }
   AVR_DEV int lvl_sign(const SharedTables& t) { return byp_bin(t); }
-  AVR_DEV void lvl_push(uint32_t entry) { q.push(entry); }
+  AVR_DEV void lvl_push(uint32_t entry) { q.reserve(h, 1); q.put(h, entry); }
+  AVR_DEV int lvl_bypass(const SharedTables& t) {   // Exp-Golomb escape bins
+    const int b = byp_bin(t);
+    q.reserve(h, 1); q.put(h, uint32_t(b) << SYM_BIT_SHIFT | SYM_BYPASS);
+    return b;
+  }
   AVR_DEV int model_bit(const SharedTables& t, uint32_t idx) { return coded(t, idx, idx >= CNT_SIG ? uint32_t(LIMIT_SIG) : uint32_t(LIMIT_ANY)); }
   // the block's significance map for the CABAC re-encoder
   AVR_DEV void block_push(int cat, uint32_t nnz_true, uint64_t mask) {
-    q.reserve(3);
-    q.put(SYM_BLOCK | uint32_t(cat) | nnz_true << BLK_NNZ);
-    q.put(uint32_t(mask));
-    if (cat == 5) q.put(uint32_t(mask >> 32));
+    q.reserve(h, 3);
+    q.put(h, SYM_BLOCK | uint32_t(cat) | nnz_true << BLK_NNZ);
+    q.put(h, uint32_t(mask));
+    if (cat == 5) q.put(h, uint32_t(mask >> 32));
   }
-  AVR_DEV uint32_t in_pos() const { return rc.pos(); }
 };
 
 }  // namespace avr

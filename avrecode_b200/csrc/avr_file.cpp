@@ -111,10 +111,22 @@ bool parse_container(const uint8_t* p, size_t n, std::vector<Block>* blocks, std
 }
 
 // Chunked mode: a slice whose payload is at least two of these becomes a wide slice, one stream per this many
-// bytes (AVR_WIDE_STREAM_BYTES overrides; 0 = never).  Long slices set the time of a batch -- see avr_job.cuh.
-uint32_t wide_stream_bytes() {
+// bytes (avr_config.wide_stream_bytes; 0 = never).  Long slices set the time of a small batch -- see avr_job.cuh;
+// a batch with more slices than avr_config.wide_batch_limit is a throughput job and gets none.
+extern "C" int avr_ctx_wide_stream_bytes(avr_ctx* c);
+extern "C" int avr_ctx_wide_batch_limit(avr_ctx* c);
+uint32_t wide_stream_bytes(avr_ctx* ctx, size_t n_batch_slices) {
+  const int limit = ctx ? avr_ctx_wide_batch_limit(ctx) : 0;
+  if (limit > 0 && n_batch_slices > size_t(limit)) return 0;
+  if (ctx) return uint32_t(avr_ctx_wide_stream_bytes(ctx));
   if (const char* e = getenv("AVR_WIDE_STREAM_BYTES")) return uint32_t(strtoul(e, nullptr, 10));
   return 32768;
+}
+// what the device walker rejects whatever the bytes say (avr_walk.cuh Walker::start): known from the descriptor alone
+bool statically_unsupported(const avr_slice_desc& d) {
+  return d.slice_type > AVR_SLICE_I || d.chroma_format_idc != 1 || (d.flags & (AVR_SLICE_MBAFF | AVR_SLICE_FIELD)) ||
+         d.mb_width < 1 || d.mb_height < 1 || uint64_t(d.mb_width) * d.mb_height > AVR_MAX_PICTURE_MBS ||
+         d.first_mb >= uint32_t(d.mb_width) * d.mb_height;
 }
 uint8_t streams_for(const avr_slice_desc& d, uint32_t per_stream) {
   if (per_stream == 0 || d.mb_width < 1 || d.mb_width > 256) return 0;
@@ -163,7 +175,10 @@ extern "C" {
 
 void avr_free(void* p) { free(p); }
 
-int avr_slice_streams(const avr_slice_desc* desc) { return desc ? streams_for(*desc, wide_stream_bytes()) : 0; }
+int avr_slice_streams(const avr_slice_desc* desc) { return desc ? streams_for(*desc, wide_stream_bytes(nullptr, 0)) : 0; }
+int avr_ctx_slice_streams(avr_ctx* ctx, const avr_slice_desc* desc, int n_batch_slices) {
+  return desc ? streams_for(*desc, wide_stream_bytes(ctx, size_t(n_batch_slices < 0 ? 0 : n_batch_slices))) : 0;
+}
 
 // Shared driver of avr_file_compress / avr_files_compress: all CABAC slices of all files go to the
 // device as ONE batch (files are independent, so in either mode every file starts a fresh model).
@@ -200,7 +215,9 @@ static int compress_many(avr_ctx* ctx, const uint8_t* const* files, const uint64
     p.coded.assign(size_t(p.n_ents), 0);
     p.raw_off.assign(size_t(p.n_ents), 0);
     p.raw_size.assign(size_t(p.n_ents), 0);
-    for (int i = 0; i < p.n_ents; i++) p.coded[i] = p.ents[i].recodable ? 1 : 0;
+    // slices the device would only hand back as unsupported stay literals from the start (in file mode every failed
+    // attempt costs a whole pass: the slices of a file share one model)
+    for (int i = 0; i < p.n_ents; i++) p.coded[i] = (p.ents[i].recodable && !statically_unsupported(p.ents[i].desc)) ? 1 : 0;
   }
   // Chunked mode recodes slices whose payload contains emulation-prevention bytes too (the reference leaves
   // them as literals): the device gets an unescaped copy, appended to the arena, and puts the bytes back when
@@ -211,7 +228,7 @@ static int compress_many(avr_ctx* ctx, const uint8_t* const* files, const uint64
       Plan& p = plans[f];
       for (int i = 0; i < p.n_ents; i++) {
         const avr_slice_desc& d = p.ents[i].desc;
-        if (p.coded[i] || !(d.n_streams & AVR_SLICE_ESCAPED)) continue;
+        if (p.coded[i] || !(d.n_streams & AVR_SLICE_ESCAPED) || statically_unsupported(d)) continue;
         const int z = (d.n_streams >> AVR_ESC_ZEROS_SHIFT) & 3;
         const size_t at = (raws.size() + 15) & ~size_t(15);
         raws.resize(at);
@@ -239,7 +256,9 @@ static int compress_many(avr_ctx* ctx, const uint8_t* const* files, const uint64
       arena = arena_store.data(); arena_bytes = total + raws.size();
     }
   }
-  const uint32_t per_stream = mode == AVR_MODE_SLICE ? wide_stream_bytes() : 0;
+  size_t n_batch = 0;
+  for (const Plan& p : plans) for (int i = 0; i < p.n_ents; i++) n_batch += p.coded[i] ? 1 : 0;
+  const uint32_t per_stream = mode == AVR_MODE_SLICE ? wide_stream_bytes(ctx, n_batch) : 0;
   std::vector<avr_slice_desc> descs;
   std::vector<avr_slice_result> res;
   const uint8_t* out = nullptr;
@@ -270,13 +289,20 @@ static int compress_many(avr_ctx* ctx, const uint8_t* const* files, const uint64
     int rc = avr_compress(ctx, descs.data(), int(descs.size()), arena ? arena : reinterpret_cast<const uint8_t*>(""),
                           arena_bytes, res.data(), &out, &out_bytes);
     if (rc) { cleanup(); return rc; }
+    // slice mode: a failed slice becomes a literal, done.  File mode: the first slice of a file that fails poisons the
+    // model of everything behind it (those come back CORRUPT whatever they are): drop it, and with it every slice the
+    // device called UNSUPPORTED on its own account (the walker checks that before it touches the model), and run again
     bool retry = false;
-    for (Plan& p : plans)
-      for (size_t k = 0; k < p.map.size(); k++)
-        if (res[p.first + k].status != AVR_SLICE_OK && p.coded[p.map[k]]) {
-          p.coded[p.map[k]] = 0;
-          if (mode == AVR_MODE_FILE) { retry = true; break; }
-        }
+    for (Plan& p : plans) {
+      bool first_failure = true;
+      for (size_t k = 0; k < p.map.size(); k++) {
+        const int st = res[p.first + k].status;
+        if (st == AVR_SLICE_OK || !p.coded[p.map[k]]) continue;
+        if (mode == AVR_MODE_SLICE) { p.coded[p.map[k]] = 0; continue; }
+        if (first_failure || st == AVR_SLICE_UNSUPPORTED) { p.coded[p.map[k]] = 0; retry = true; }
+        first_failure = false;
+      }
+    }
     if (!retry) break;
   }
   int rc_all = AVR_OK;
@@ -372,7 +398,9 @@ static int decompress_many(avr_ctx* ctx, const uint8_t* const* recs, const uint6
       if (int(b.has_literal) + int(b.has_cabac) + int(b.has_skip) != 1) return AVR_ERR_FORMAT;   // recode.cpp:1364-1366
       if (b.has_literal) p.stream.append(reinterpret_cast<const char*>(b.literal), b.literal_n);
       else if (b.has_cabac) {
-        if (!b.has_size || b.size < 8 || b.size > (int64_t(1) << 31)) return AVR_ERR_FORMAT;   // :1377-1379, 1538-1540
+        // :1377-1379, 1538-1540; and no honest block is 4096x its coded size (an estimator never goes below 1/97:
+        // a bin costs > 0.01 bit), so a few bytes of container cannot demand gigabytes of output
+        if (!b.has_size || b.size < 8 || b.size > (int64_t(1) << 31) || uint64_t(b.size) > (uint64_t(b.cabac_n) + 16) * 4096) return AVR_ERR_FORMAT;
         p.coded.push_back(CodedRef{i, p.stream.size(), true});
         p.stream.append(size_t(b.size), 'X');
       } else {

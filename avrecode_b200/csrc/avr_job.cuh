@@ -47,8 +47,9 @@ struct BlockShared {
   alignas(16) uint8_t window[WIN_BYTES];
   U2 cstate[N_CTX_PAD];     // CABAC context states {state, rangeTabLPS row}
   WalkShared walk;          // left macroblock + per-macroblock scratch of the walker
+  uint32_t stage[RING_BATCH + 2 * ENTRY_MAX_WORDS];   // host emulation only: the coder's view of a batch (the device reads the ring in place)
   ByteSink sink;            // output bytes of the coder warp (touched once per byte, out of line)
-  DecHome dec_home;         // read position of the range decoder (decompress parser)
+  ParserHome phome;         // the parser's engines between residual blocks
   uint32_t job;             // job handed out by the atomic counter
   uint32_t final_status;    // status of the slice just finished (coder writes, everyone reads)
   uint32_t pad_[2];
@@ -69,6 +70,7 @@ struct JobMem {             // where this block keeps its state
   uint8_t* nnz0;            // two FrameBuffer nnz planes, global workspace (scalars: the struct must stay in registers)
   uint8_t* nnz1;
   uint32_t nnz_frame_bytes; // capacity of one plane
+  uint32_t max_mbw;         // capacity of the neighbour row
 };
 
 // CABAC context initialisation (H.264 9.3.1.1; h264_cabac.c:1267-1286) for the contexts in use.
@@ -133,7 +135,7 @@ struct Lane {               // what one parser warp works with
   uint16_t* cnt;
   uint32_t* far;            // wide decompression: this warp's symbol ring in global memory (else null)
   uint32_t far_cap;
-  DecHome* home;
+  ParserHome* home;
 };
 
 // stream / total_mbs: wide decompression only (the caller has set wk.wide_k and what goes with it)
@@ -146,8 +148,7 @@ AVR_DEV void parser_begin(Walker<Dir>& wk, const Lane& ln, const uint8_t* src, u
   wk.ws = ln.walk;
   wk.use_planes = use_planes;
   wk.nnz_cur = nnz_cur; wk.nnz_prev = nnz_prev;
-  wk.dir.set_home(ln.home);
-  wk.dir.begin(src, n, ln.window, (d.flags & AVR_SLICE_STOP_BYTE) ? 0x80u : 0u, ln.ring, ln.cnt, ln.cstate, ln.far, ln.far_cap);
+  wk.dir.begin(ln.home, src, n, ln.window, (d.flags & AVR_SLICE_STOP_BYTE) ? 0x80u : 0u, ln.ring, ln.tab, ln.cnt, ln.cstate, ln.far, ln.far_cap);
   window_load_half(wk.dir.in, 0, lane);
   window_load_half(wk.dir.in, WIN_HALF, lane);
   AVR_SYNCWARP();
@@ -200,21 +201,21 @@ AVR_DEV void parser_end(Walker<Dir>& wk, int lane) {
       ring_fence();
       *wk.prog_mine = 0xFFFFFFFFu;
     }
-    ring_end_record(wk.dir.q.r, wk.status, wk.n_mbs, wk.n_bins_lo, wk.n_bins_hi);
-    wk.dir.q.push(SYM_END);
-    wk.dir.q.publish();
+    ring_end_record(wk.dir.h->r, wk.status, wk.n_mbs, wk.n_bins_lo(), wk.n_bins_hi);
+    home_push(wk.dir.h, SYM_END);
+    home_publish(wk.dir.h);
     if (wk.wide_k && !Dir::kDecompress) {
       // Wide compression: every stream ends in a terminate bin, which flushes its range coder -- the
       // slice's own end_of_slice bin in the stream of the last row, one extra bin in each of the others.
       RingShared* first = wk.rings;
-      ring_end_record(first, wk.status, wk.n_mbs, wk.n_bins_lo, wk.n_bins_hi);
+      ring_end_record(first, wk.status, wk.n_mbs, wk.n_bins_lo(), wk.n_bins_hi);
 #pragma unroll 1
       for (uint32_t j = 0; j < wk.wide_k; j++) {
         if (j == wk.cur_ring) continue;
-        wk.dir.q.switch_to(&wk.rings[j], j);
-        if (wk.status == WALK_OK) wk.dir.q.push(CNT_TERM | 1u << SYM_BIT_SHIFT);
-        wk.dir.q.push(SYM_END);
-        wk.dir.q.publish();
+        home_switch_to(wk.dir.h, &wk.rings[j], j);
+        if (wk.status == WALK_OK) home_push(wk.dir.h, CNT_TERM | 1u << SYM_BIT_SHIFT);
+        home_push(wk.dir.h, SYM_END);
+        home_publish(wk.dir.h);
       }
     }
   }
@@ -228,7 +229,7 @@ AVR_DEV void parser_role(const JobArgs& a, const JobMem& m, const avr_slice_desc
   wk.top_copy = false;
   Lane ln;
   ln.tab = &m.sh->tab; ln.ring = &m.sh->ring; ln.window = m.sh->window; ln.cstate = m.sh->cstate;
-  ln.walk = &m.sh->walk; ln.row = m.row; ln.cnt = m.cnt; ln.far = nullptr; ln.far_cap = 0; ln.home = &m.sh->dec_home;
+  ln.walk = &m.sh->walk; ln.row = m.row; ln.cnt = m.cnt; ln.far = nullptr; ln.far_cap = 0; ln.home = &m.sh->phome;
   parser_begin<Dir>(wk, ln, a.in_arena + io.in_off, io.in_size, d, cur_frame ? m.nnz1 : m.nnz0, cur_frame ? m.nnz0 : m.nnz1,
                     use_planes, lane, 0, 0);
   parser_run<Dir>(wk, lane);
@@ -238,13 +239,12 @@ AVR_DEV void parser_role(const JobArgs& a, const JobMem& m, const avr_slice_desc
 // ---- coder warp: lane 0 drains the ring and owns the output bytes and the slice result -------------
 template <class Dir>
 AVR_DEV void coder_role(const JobArgs& a, const JobMem& m, const SliceIO& io, uint32_t s, int lane) {
+  typename Dir::Coder c;
+  const uint8_t lay = a.descs[s].n_streams;   // decompress: put emulation-prevention bytes back (escaped slices, chunked mode)
+  c.begin(&m.sh->sink, a.out_arena + io.out_off, io.out_cap, (lay & AVR_SLICE_ESCAPED) ? int((lay >> AVR_ESC_ZEROS_SHIFT) & 3) : -1);
+  if constexpr (Dir::kDecompress) c.run(&m.sh->ring, m.sh->tab, m.sh->cstate, m.sh->stage, lane);
+  else c.run(&m.sh->ring, nullptr, 0, false, m.sh->tab, m.cnt, m.sh->stage, lane);
   if (lane == 0) {
-    typename Dir::Coder c;
-    const uint8_t lay = a.descs[s].n_streams;   // decompress: put emulation-prevention bytes back (escaped slices, chunked mode)
-    c.begin(&m.sh->sink, a.out_arena + io.out_off, io.out_cap, (lay & AVR_SLICE_ESCAPED) ? int((lay >> AVR_ESC_ZEROS_SHIFT) & 3) : -1);
-    Consumer q;
-    q.init(&m.sh->ring);
-    c.run(q, m.sh->tab, m.cnt, m.sh->cstate);
     const volatile RingShared* r = &m.sh->ring;
     avr_slice_result res;
     res.out_off = io.out_off;
@@ -252,7 +252,10 @@ AVR_DEV void coder_role(const JobArgs& a, const JobMem& m, const SliceIO& io, ui
     if (res.status == AVR_SLICE_OK && c.overflowed()) res.status = AVR_SLICE_OVERFLOW;
     res.out_size = res.status == AVR_SLICE_OK ? c.out_bytes() : 0;
     res.n_mbs = r->end_mbs;
-    res.reserved = 0;
+    {   // which stage waited: parser for ring room (low half), coder for entries (high half), in units of 65536 cycles
+      const uint32_t pw = r->prod_wait >> 8, cw = r->cons_wait >> 8;
+      res.reserved = (pw < 0xFFFF ? pw : 0xFFFFu) | (cw < 0xFFFF ? cw : 0xFFFFu) << 16;
+    }
     res.n_bins = uint64_t(r->end_bins_lo) | uint64_t(r->end_bins_hi) << 32;
     a.results[s] = res;
     m.sh->final_status = uint32_t(res.status);
@@ -277,8 +280,10 @@ AVR_DEV void run_job(const JobArgs& a, const JobDesc& job, const JobMem& m, int 
     const SliceIO io = a.ios[s];
     const bool fresh = s == job.first_slice || (d.flags & AVR_SLICE_NEW_MODEL);
     const bool skip = (d.flags & AVR_SLICE_SKIP) != 0;   // frame_spec bookkeeping only
-    const uint32_t frame_bytes = uint32_t(d.mb_width) * d.mb_height * NNZ_STRIDE;
-    const bool usable = !poisoned && (!use_planes || frame_bytes <= m.nnz_frame_bytes) && d.mb_width > 0 && d.mb_height > 0;
+    const uint64_t picture_mbs = uint64_t(d.mb_width) * d.mb_height;   // Level 6.2 at most: frame_bytes cannot wrap
+    const uint32_t frame_bytes = picture_mbs <= AVR_MAX_PICTURE_MBS ? uint32_t(picture_mbs) * NNZ_STRIDE : 0xFFFFFFFFu;
+    const bool usable = !poisoned && picture_mbs > 0 && picture_mbs <= AVR_MAX_PICTURE_MBS && d.mb_width <= m.max_mbw &&
+                        (!use_planes || frame_bytes <= m.nnz_frame_bytes);
     if (usable) {
       if (fresh) {
         // a brand-new h264_model: every estimator {1,1} (recode.cpp:1057), no frame buffers yet
@@ -365,9 +370,9 @@ struct WideShared {
   uint32_t out_size[WIDE_MAX];   // compress: bytes of each stream;  decompress: [0] = bytes of the slice
   uint32_t overflow;
   uint32_t job;
-  uint32_t stage[WIDE_MAX][144]; // the batch of ring entries a coder warp is working on (decompress: [0] only)
+  uint32_t stage[WIDE_MAX][144]; // the batch of ring words a coder warp is working on (decompress: [0] only)
   ByteSink sink[WIDE_MAX];       // compress: one per coder warp; decompress: [0]
-  DecHome dec_home[WIDE_MAX];    // decompress: one per parser warp
+  ParserHome phome[WIDE_MAX];    // one per parser warp (compress: [0])
 };
 
 struct WideMem {
@@ -400,7 +405,7 @@ AVR_DEV void wide_lane(Lane& ln, const WideMem& m, uint32_t j, uint32_t mbw) {
   ln.walk = &sh->walk[j]; ln.row = m.rows + size_t(j) * mbw; ln.cnt = m.cnt + size_t(j) * MODEL_COUNTERS_PAD;
   ln.far = m.far ? m.far + size_t(j) * m.far_cap : nullptr;   // compress: ring 0, the parser moves on from there
   ln.far_cap = m.far ? m.far_cap : 0;
-  ln.home = &sh->dec_home[j];
+  ln.home = &sh->phome[j];
 }
 
 template <class Dir>
@@ -468,7 +473,7 @@ AVR_DEV void run_wide_job(const JobArgs& a, uint32_t s, const WideMem& m, int ti
       const uint32_t j = warp - 1;
       typename Dir::Coder c;
       c.begin(&sh->sink[j], out + hdr + size_t(j) * subcap, subcap);
-      c.run_far(&sh->ring[j], m.far + size_t(j) * m.far_cap, m.far_cap, sh->tab, m.cnt + size_t(j) * MODEL_COUNTERS_PAD, sh->stage[j], lane);
+      c.run(&sh->ring[j], m.far + size_t(j) * m.far_cap, m.far_cap, true, sh->tab, m.cnt + size_t(j) * MODEL_COUNTERS_PAD, sh->stage[j], lane);
       if (lane == 0) {
         sh->out_size[j] = c.out_bytes();
         if (c.overflowed()) sh->overflow = 1;
@@ -510,7 +515,7 @@ AVR_DEV void run_wide_job(const JobArgs& a, uint32_t s, const WideMem& m, int ti
     for (uint32_t j = 0; j < K; j++) {
       typename Dir::Coder c;
       c.begin(&sh->sink[j], out + hdr + size_t(j) * subcap, subcap);
-      c.run_far(&sh->ring[j], nullptr, 0, sh->tab, m.cnt + size_t(j) * MODEL_COUNTERS_PAD, sh->stage[j], lane);
+      c.run(&sh->ring[j], nullptr, 0, true, sh->tab, m.cnt + size_t(j) * MODEL_COUNTERS_PAD, sh->stage[j], lane);
       sh->out_size[j] = c.out_bytes();
       if (c.overflowed()) sh->overflow = 1;
     }

@@ -50,6 +50,7 @@ __global__ void __launch_bounds__(AVR_THREADS, RESIDENT ? 2 : 8) avr_job_kernel(
   m.nnz0 = slot;
   m.nnz1 = slot + k.nnz_frame_bytes;
   m.nnz_frame_bytes = k.nnz_frame_bytes;
+  m.max_mbw = k.max_mbw;
   const int tid = threadIdx.x;
   fill_shared_tables(&m.sh->tab, tid, AVR_THREADS);
   __syncthreads();
@@ -156,7 +157,9 @@ struct avr_ctx {
   uint32_t max_mbw = 1, max_frame_bytes = 0;
   int grid = 0;
   bool resident = true;
-  int force_resident = -1;   // AVR_RESIDENT env: 0 / 1, -1 = heuristic
+  int force_resident = -1;   // avr_config.resident / AVR_RESIDENT env: 0 / 1, -1 = per batch
+  int wide_stream_bytes = 32768;   // avr_config.wide_stream_bytes / AVR_WIDE_STREAM_BYTES env
+  int wide_batch_limit = -1;       // avr_config.wide_batch_limit (-1: 4 x SMs, 0: none)
   // meta offsets
   size_t off_descs = 0, off_ios = 0, off_jobs = 0, off_res = 0, off_counter = 0;
   uint64_t work_stride = 0;
@@ -212,6 +215,13 @@ const char* avr_strerror(int code) {
 
 int avr_abi_version(void) { return AVR_ABI_VERSION; }
 
+void avr_config_init(avr_config* cfg) {
+  if (!cfg) return;
+  memset(cfg, 0, sizeof *cfg);
+  cfg->abi_version = AVR_ABI_VERSION;
+  cfg->wide_stream_bytes = -1; cfg->resident = -1; cfg->wide_batch_limit = -1;
+}
+
 int avr_create(const avr_config* cfg, avr_ctx** out) {
   if (!out) return AVR_ERR_ARG;
   *out = nullptr;
@@ -223,7 +233,13 @@ int avr_create(const avr_config* cfg, avr_ctx** out) {
   avr_ctx* c = new (std::nothrow) avr_ctx();
   if (!c) return AVR_ERR_NOMEM;
   c->device = dev;
-  c->cfg_warps = cfg ? cfg->warps_per_block : 0;
+  c->cfg_warps = cfg ? cfg->blocks_per_sm : 0;
+  if (cfg) {
+    c->force_resident = cfg->resident < 0 ? -1 : (cfg->resident ? 1 : 0);
+    if (cfg->wide_stream_bytes >= 0) c->wide_stream_bytes = cfg->wide_stream_bytes;
+    c->wide_batch_limit = cfg->wide_batch_limit;
+  }
+  if (const char* e = getenv("AVR_WIDE_STREAM_BYTES")) c->wide_stream_bytes = int(strtoul(e, nullptr, 10));
   if (!ck(cudaSetDevice(dev), "cudaSetDevice")) { delete c; return AVR_ERR_NO_DEVICE; }
   cudaDeviceProp prop;
   if (!ck(cudaGetDeviceProperties(&prop, dev), "cudaGetDeviceProperties")) { delete c; return AVR_ERR_CUDA; }
@@ -294,11 +310,15 @@ int avr_stage(avr_ctx* c, const avr_slice_desc* descs, int n, const uint8_t* in,
       const bool own_model = (i == 0 || (d.flags & AVR_SLICE_NEW_MODEL)) && (i + 1 == n || (descs[i + 1].flags & AVR_SLICE_NEW_MODEL));
       if (n_str > AVR_MAX_STREAMS || !own_model || (d.flags & AVR_SLICE_SKIP)) return AVR_ERR_ARG;
       c->wide.push_back(uint32_t(i));
-      c->max_mbw_wide = std::max<uint32_t>(c->max_mbw_wide, d.mb_width);
+      if (d.mb_width <= 1024) c->max_mbw_wide = std::max<uint32_t>(c->max_mbw_wide, d.mb_width);
       continue;
     }
-    c->max_mbw = std::max<uint32_t>(c->max_mbw, d.mb_width);
-    c->max_frame_bytes = std::max<uint32_t>(c->max_frame_bytes, uint32_t(d.mb_width) * d.mb_height * NNZ_STRIDE);
+    // pictures beyond Level 6.2 are reported unsupported by the device (run_job) and size nothing here
+    const bool sane = uint64_t(d.mb_width) * d.mb_height <= AVR_MAX_PICTURE_MBS && d.mb_width <= 1024;
+    if (sane) {
+      c->max_mbw = std::max<uint32_t>(c->max_mbw, d.mb_width);
+      c->max_frame_bytes = std::max<uint32_t>(c->max_frame_bytes, uint32_t(d.mb_width) * d.mb_height * NNZ_STRIDE);
+    }
     if (i == 0 || (d.flags & AVR_SLICE_NEW_MODEL)) {
       JobDesc j; memset(&j, 0, sizeof j);
       j.first_slice = uint32_t(i); j.n_slices = 0;
@@ -329,7 +349,18 @@ int avr_stage(avr_ctx* c, const avr_slice_desc* descs, int n, const uint8_t* in,
   int glb_per_sm = std::max(1, std::min(c->cfg_warps > 0 ? c->cfg_warps : 8, int(smem_sm / (smem_glb + 1024))));
   glb_per_sm = std::min(glb_per_sm, 8);
   if (smem_glb + 1024 > size_t(c->max_smem_optin)) return AVR_ERR_ARG;   // picture too wide for the neighbour row
-  bool resident = res_per_sm > 0 && c->n_jobs <= 3 * res_per_sm * c->sm_count;
+  // Which placement finishes the batch sooner?  A launch lasts max(total work / slots, longest job) x cycles per bin of
+  // the variant; the global-memory variant has 4x the slots but every estimator access is an L1 / L2 access on the
+  // serial chain (measured ~2.1x the cycles per bin, profiles/r1d_corpus_case.txt vs r1k_bench.json), so it only
+  // wins when there are many jobs AND none of them is long.
+  uint64_t total_w = 0, longest_w = 0;
+  for (const JobDesc& j : c->jobs) { total_w += j.weight; longest_w = std::max<uint64_t>(longest_w, j.weight); }
+  bool resident = res_per_sm > 0;
+  if (resident) {
+    const double t_res = double(std::max<uint64_t>(total_w / uint64_t(res_per_sm * c->sm_count), longest_w));
+    const double t_glb = 2.1 * double(std::max<uint64_t>(total_w / uint64_t(glb_per_sm * c->sm_count), longest_w));
+    resident = t_res <= t_glb;
+  }
   if (c->force_resident == 0) resident = false;
   if (c->force_resident == 1 && res_per_sm > 0) resident = true;
   c->resident = resident;
@@ -471,6 +502,10 @@ int avr_collect(avr_ctx* c, avr_slice_result* results, const uint8_t** out, uint
   *out_bytes = total;
   return AVR_OK;
 }
+
+// what the host file layer (avr_file.cpp) needs to know about the context
+int avr_ctx_wide_stream_bytes(avr_ctx* c) { return c ? c->wide_stream_bytes : 32768; }
+int avr_ctx_wide_batch_limit(avr_ctx* c) { return !c ? 0 : c->wide_batch_limit < 0 ? 4 * c->sm_count : c->wide_batch_limit; }
 
 int avr_last_kernel_ms(avr_ctx* c, float* ms) {
   if (!c || !ms) return AVR_ERR_ARG;

@@ -20,8 +20,9 @@ struct ProbeShared {
   U2 cstate[N_CTX_PAD];
   uint16_t cnt[10240];
   uint8_t out[8192];
+  uint32_t stage[RING_BATCH + 2 * ENTRY_MAX_WORDS];
   ByteSink sink;
-  DecHome home;
+  ParserHome home;
 };
 
 struct ProbeArgs {
@@ -73,9 +74,9 @@ __device__ void probe_decide(ProbeShared* sh, const ProbeArgs& a, uint64_t* r) {
 // 2: the compress-side significance loop of a 4x4 block (distinct contexts, branch on the bin, last flag)
 __device__ void probe_sigloop_c(ProbeShared* sh, const ProbeArgs& a, uint64_t* r) {
   Compress d;
-  d.in.attach(sh->window, 0x7FFFFFFFu, sh->window, 0);
-  d.cstate = sh->cstate;
-  d.cabac.init(d.in);
+  d.begin(&sh->home, sh->window, 0x7FFFFFFFu, sh->window, 0, &sh->ring, &sh->tab, sh->cnt, sh->cstate);
+  d.start_bins(sh->tab);
+  d.enter(sh->tab);
   uint64_t bins = 0, acc = 0;
   const long long t0 = clock64();
 #pragma unroll 1
@@ -105,23 +106,23 @@ __device__ void probe_sigloop_c(ProbeShared* sh, const ProbeArgs& a, uint64_t* r
 // 3: decompress-side bin: estimator load, exact division, range decode, update, store
 __device__ void probe_coded(ProbeShared* sh, const ProbeArgs& a, uint64_t* r) {
   Decompress d;
-  d.in.attach(sh->window, 0x7FFFFFFFu, sh->window, 0);
-  d.cnt = sh->cnt;
-  d.rc.init(&sh->home, d.in);
+  d.begin(&sh->home, sh->window, 0x7FFFFFFFu, sh->window, 0, &sh->ring, &sh->tab, sh->cnt, sh->cstate);
+  d.start_bins(sh->tab);
+  d.enter(sh->tab);
   uint32_t acc = 0;
   const long long t0 = clock64();
 #pragma unroll 1
   for (uint32_t i = 0; i < a.iters; i++) acc += uint32_t(d.coded(sh->tab, (i * 5u) & 63u, LIMIT_ANY));
   const long long t1 = clock64();
-  r[0] = uint64_t(t1 - t0); r[1] = a.iters; r[2] = acc + d.rc.pos();
+  r[0] = uint64_t(t1 - t0); r[1] = a.iters; r[2] = acc + d.rc.pos() + uint32_t(d.rc.low);
 }
 
 // 4: the decompress-side significance loop (both successors prefetched), without the ring push
 __device__ void probe_sigloop_d(ProbeShared* sh, const ProbeArgs& a, uint64_t* r) {
   Decompress d;
-  d.in.attach(sh->window, 0x7FFFFFFFu, sh->window, 0);
-  d.cnt = sh->cnt;
-  d.rc.init(&sh->home, d.in);
+  d.begin(&sh->home, sh->window, 0x7FFFFFFFu, sh->window, 0, &sh->ring, &sh->tab, sh->cnt, sh->cstate);
+  d.start_bins(sh->tab);
+  d.enter(sh->tab);
   uint64_t bins = 0, acc = 0;
   const long long t0 = clock64();
 #pragma unroll 1
@@ -141,7 +142,7 @@ __device__ void probe_sigloop_d(ProbeShared* sh, const ProbeArgs& a, uint64_t* r
     }
   }
   const long long t1 = clock64();
-  r[0] = uint64_t(t1 - t0); r[1] = bins; r[2] = acc + d.rc.pos();
+  r[0] = uint64_t(t1 - t0); r[1] = bins; r[2] = acc + d.rc.pos() + uint32_t(d.rc.low);
 }
 
 // Fills the ring with a residual-heavy mix of entries (4x4 blocks with their levels, a few plain bins), ends it with
@@ -179,53 +180,63 @@ __device__ uint32_t fill_ring(ProbeShared* sh, bool decompress) {
   return bins;
 }
 
-// 5: the compress coder warp's loop (estimators + 64-bit range encoder) over a full ring
-__device__ void probe_coder_c(ProbeShared* sh, const ProbeArgs& a, uint64_t* r) {
-  const uint32_t per = fill_ring(sh, false);
+// 5: the compress coder warp (all lanes expand the entries, lane 0 runs estimators + 64-bit range encoder) over a full ring
+__device__ void probe_coder_c(ProbeShared* sh, const ProbeArgs& a, uint64_t* r, int lane) {
+  uint32_t per = 0;
+  if (lane == 0) per = fill_ring(sh, false);
+  per = __shfl_sync(0xFFFFFFFFu, per, 0);
   uint64_t bins = 0;
   CoderCompress c;
   c.begin(&sh->sink, sh->out, sizeof sh->out);
+  __syncwarp();
   const long long t0 = clock64();
 #pragma unroll 1
   for (uint32_t i = 0; i < a.iters; i++) {
-    Consumer q; q.init(&sh->ring);
-    c.run(q, sh->tab, sh->cnt, sh->cstate);
-    sh->sink.n = 0;
+    c.run(&sh->ring, nullptr, 0, false, sh->tab, sh->cnt, sh->stage, lane);
+    if (lane == 0) sh->sink.n = 0;
     bins += per;
+    __syncwarp();
   }
   const long long t1 = clock64();
   r[0] = uint64_t(t1 - t0); r[1] = bins; r[2] = c.rc.low;
 }
 
-// 6: the decompress coder warp's loop (CABAC re-encoder) over a full ring
-__device__ void probe_coder_d(ProbeShared* sh, const ProbeArgs& a, uint64_t* r) {
-  const uint32_t per = fill_ring(sh, true);
+// 6: the decompress coder warp (all lanes expand, lane 0 runs the CABAC re-encoder) over a full ring
+__device__ void probe_coder_d(ProbeShared* sh, const ProbeArgs& a, uint64_t* r, int lane) {
+  uint32_t per = 0;
+  if (lane == 0) per = fill_ring(sh, true);
+  per = __shfl_sync(0xFFFFFFFFu, per, 0);
   uint64_t bins = 0;
   CoderDecompress c;
   c.begin(&sh->sink, sh->out, sizeof sh->out);
+  __syncwarp();
   const long long t0 = clock64();
 #pragma unroll 1
   for (uint32_t i = 0; i < a.iters; i++) {
-    Consumer q; q.init(&sh->ring);
-    c.run(q, sh->tab, sh->cnt, sh->cstate);
-    sh->sink.n = 0;
+    c.run(&sh->ring, sh->tab, sh->cstate, sh->stage, lane);
+    if (lane == 0) sh->sink.n = 0;
     bins += per;
+    __syncwarp();
   }
   const long long t1 = clock64();
   r[0] = uint64_t(t1 - t0); r[1] = bins; r[2] = c.cabac.low;
 }
 
-// 7: ring push alone (what the parser pays per entry it hands over)
+// 7: one macroblock-level bin through the out-of-line primitive (compress: CABAC decision on the shared-memory copy
+//    of the engine + plain ring entry)
 __device__ void probe_push(ProbeShared* sh, const ProbeArgs& a, uint64_t* r) {
-  Producer q; q.init(&sh->ring);
+  Compress d;
+  d.begin(&sh->home, sh->window, 0x7FFFFFFFu, sh->window, 0, &sh->ring, &sh->tab, sh->cnt, sh->cstate);
+  d.start_bins(sh->tab);
+  uint32_t acc = 0;
   const long long t0 = clock64();
 #pragma unroll 1
   for (uint32_t i = 0; i < a.iters; i++) {
-    *reinterpret_cast<volatile uint32_t*>(&sh->ring.head_pub) = q.tail;   // a consumer that always keeps up
-    q.push(i | 1u << SYM_BIT_SHIFT);
+    *reinterpret_cast<volatile uint32_t*>(&sh->ring.head_pub) = sh->home.tail;   // a consumer that always keeps up
+    acc += uint32_t(d.bin(int(11 + (i & 7))));
   }
   const long long t1 = clock64();
-  r[0] = uint64_t(t1 - t0); r[1] = a.iters; r[2] = q.tail;
+  r[0] = uint64_t(t1 - t0); r[1] = a.iters; r[2] = acc;
 }
 
 template <int WHICH>
@@ -233,15 +244,18 @@ __global__ void __launch_bounds__(32, 1) avr_probe_kernel(ProbeArgs a) {
   __shared__ ProbeShared sh;
   probe_setup(&sh, threadIdx.x, 32);
   __syncthreads();
-  if (threadIdx.x == 0) {
+  if (WHICH == 5 || WHICH == 6) {   // warp-wide roles
+    uint64_t r[3] = {0, 0, 0};
+    if (WHICH == 5) probe_coder_c(&sh, a, r, int(threadIdx.x));
+    if (WHICH == 6) probe_coder_d(&sh, a, r, int(threadIdx.x));
+    if (threadIdx.x == 0) { a.result[0] = r[0]; a.result[1] = r[1]; a.result[2] = r[2]; }
+  } else if (threadIdx.x == 0) {
     uint64_t r[3] = {0, 0, 0};
     if (WHICH == 0) probe_alu(&sh, a, r);
     if (WHICH == 1) probe_decide(&sh, a, r);
     if (WHICH == 2) probe_sigloop_c(&sh, a, r);
     if (WHICH == 3) probe_coded(&sh, a, r);
     if (WHICH == 4) probe_sigloop_d(&sh, a, r);
-    if (WHICH == 5) probe_coder_c(&sh, a, r);
-    if (WHICH == 6) probe_coder_d(&sh, a, r);
     if (WHICH == 7) probe_push(&sh, a, r);
     a.result[0] = r[0]; a.result[1] = r[1]; a.result[2] = r[2];
   }
@@ -258,9 +272,9 @@ const char* avr_probe_name(int which) {
     "compress significance loop, 4x4 block (CABAC decode of sig/last bins)",
     "decompress bin: estimator + exact division + RangeDec::get + update (Decompress::coded)",
     "decompress significance loop, 4x4 block (both successors prefetched)",
-    "compress coder warp: estimators + RangeEnc::put over a ring (CoderCompress::run)",
-    "decompress coder warp: CABAC re-encoder over a ring (CoderDecompress::run)",
-    "ring push (Producer::push)",
+    "compress coder warp: estimators + RangeEnc::put over a ring of block / level entries (CoderCompress::run)",
+    "decompress coder warp: CABAC re-encoder over a ring of block / level entries (CoderDecompress::run)",
+    "macroblock-level bin, compress: out-of-line CABAC decision on the shared-memory engine copy + ring entry",
   };
   return which >= 0 && which < int(sizeof names / sizeof names[0]) ? names[which] : nullptr;
 }

@@ -108,7 +108,7 @@ struct Walker {
   // running state
   int mb_x, mb_y, mb_xy;
   int last_qp_delta;
-  uint32_t n_bins_lo, n_bins_hi, n_mbs;
+  uint32_t n_bins_hi, n_mbs;
   int status;
   bool done;
   // per macroblock
@@ -117,12 +117,13 @@ struct Walker {
   uint32_t cur_flags, cur_cbp, cur_refpos, cur_dir8;
   uint64_t nzmask;       // coefficient presence of the current macroblock, bit = block index (cbf contexts)
 
-  AVR_DEV void count_bin() { n_bins_lo++; }
-  AVR_DEV int bin(int ctx) { count_bin(); return dir.bin(*tab, ctx); }   // ctx = dense ctxIdx
-  AVR_DEV int bypass() { count_bin(); return dir.bypass(*tab); }
-  AVR_DEV int terminate() { count_bin(); return dir.terminate(*tab); }
+  // macroblock-level syntax: out-of-line primitives on the shared-memory copy of the engines (they count the bins)
+  AVR_DEV int bin(int ctx) { return dir.bin(ctx); }   // ctx = dense ctxIdx
+  AVR_DEV int bypass() { return dir.bypass(); }
+  AVR_DEV int terminate() { return dir.terminate(); }
   AVR_DEV void fail(int s) { if (status == WALK_OK) status = s; }
-  AVR_DEV uint64_t n_bins() const { return uint64_t(n_bins_lo) | uint64_t(n_bins_hi) << 32; }
+  AVR_DEV uint32_t n_bins_lo() const { return dir.h->n_bins; }
+  AVR_DEV uint64_t n_bins() const { return uint64_t(n_bins_lo()) | uint64_t(n_bins_hi) << 32; }
 
   // ---- avrecode model side channel: nnz of a coded block (recode.cpp:844-930) -------------------
   // get_neighbor_sub_mb (recode.cpp:419-471): frame geometry only -- slice edges are ignored on purpose
@@ -170,12 +171,14 @@ struct Walker {
   // coder derives the nnz bits and the model-coded significance bins from it, the decompress coder the
   // CABAC sig / last bins.  What stays here is what is serial by nature: pulling the map out of the
   // CABAC stream (compress) or out of the range coder (decompress).
-  AVR_DEV void residual(int cat, int blk, int max_coeff) {
+  // Runs between dir.enter() and dir.leave(): returns the bins of the block.
+  AVR_DEV uint32_t residual(int cat, int blk, int max_coeff) {
     const bool is8 = max_coeff == 64;
     const int coefs = max_coeff - 1;
     const int abs_base = k_abs_base[cat];
     if (is8) model_is8x8 = true;          // before the nnz bits, as the compressor does
     uint32_t nnz_true, key_nnz;
+    uint32_t bins = 0;                    // bins of this block
     if constexpr (!Dir::kDecompress) {
       // 1. pull the significance map out of the CABAC stream (h264_cabac.c:1667-1681)
       const int sig_base = k_sig_base[cat], last_base = k_last_base[cat];
@@ -199,7 +202,7 @@ struct Walker {
           }
           e_sig = e_next;
         }
-        n_bins_lo += uint32_t(last) + nnz;   // one sig bin per position scanned, one last bin per coefficient found
+        bins += uint32_t(last) + nnz;   // one sig bin per position scanned, one last bin per coefficient found
         mask = m32;
       } else {
 #pragma unroll 1
@@ -210,7 +213,7 @@ struct Walker {
             if (dir.sig_get(*tab, last_base + tab->last8[last])) { ended = true; last++; break; }
           }
         }
-        n_bins_lo += uint32_t(last) + nnz;
+        bins += uint32_t(last) + nnz;
       }
       // a scan that never met last_significant_coeff_flag = 1 ends in an inferred coefficient at the last position
       if (!ended) { mask |= uint64_t(1) << coefs; nnz++; }
@@ -260,7 +263,7 @@ struct Walker {
           zz++;
         }
       }
-      n_bins_lo += uint32_t(zz) + observed;   // the CABAC bins the re-encoder derives from the entry
+      bins += uint32_t(zz) + observed;   // the CABAC bins the re-encoder derives from the entry
       dir.block_push(cat, nnz_true, mask);
     }
     ws->nnz_mb[blk] = uint8_t(key_nnz);
@@ -275,7 +278,7 @@ struct Walker {
       const int ctx1 = abs_base + (node < 4 ? node + 1 : 0);      // coeff_abs_level1_ctx
       int gctx = abs_base + 5, run = 0, term = 0;
       bool escape = false;
-      count_bin();
+      bins++;
       const int b1 = dir.lvl_first(*tab, e1, ctx1);
       if (b1 == 0) {
         node = node < 3 ? node + 1 : node;                         // transition after |level| == 1
@@ -284,25 +287,28 @@ struct Walker {
         node = node < 4 ? 4 : (node < 7 ? node + 1 : 7);           // transition after |level| > 1
         typename Dir::BinEntry g = dir.bin_fetch(*tab, gctx);      // a run on one context: state kept in registers
 #pragma unroll 1
-        while (run < 13) { count_bin(); if (!dir.lvl_run(*tab, g, gctx)) { term = 1; break; } run++; }
+        while (run < 13) { bins++; if (!dir.lvl_run(*tab, g, gctx)) { term = 1; break; } run++; }
         dir.bin_store(g, gctx);
         escape = !term;                                             // |level| >= 15: Exp-Golomb suffix follows
       }
       e1 = dir.bin_fetch(*tab, abs_base + (node < 4 ? node + 1 : 0));
       if (!escape) {
-        count_bin();
+        bins++;
         const int sg = dir.lvl_sign(*tab);
         dir.lvl_push(lvl_entry(ctx1, b1, gctx, run, term, 1, sg));   // the whole level as one ring entry
       } else {
         dir.lvl_push(lvl_entry(ctx1, b1, gctx, run, term, 0, 0));
         int j = 0;
 #pragma unroll 1
-        while (bypass() && j < 30) j++;
+        while (dir.lvl_bypass(*tab) && j < 30) j++;
+        bins += uint32_t(2 * j + 2);   // prefix (j ones and the zero -- or 30 ones), j suffix bits, sign
+        if (j >= 30) bins--;
 #pragma unroll 1
-        while (j--) bypass();
-        bypass();   // sign
+        while (j--) dir.lvl_bypass(*tab);
+        dir.lvl_bypass(*tab);   // sign
       }
     }
+    return bins;
   }
 
   // ---- context helpers --------------------------------------------------------------------------
@@ -506,12 +512,19 @@ struct Walker {
       if (!i16) {   // I_NxN: transform_size_8x8_flag + prediction modes (h264_cabac.c:2081-2099, 1369-1381)
         int nmodes = 16;
         if (t8_allowed && bin(CTX_T8X8 + nts)) { t8 = true; nmodes = 4; }
+        // up to 64 bins on two contexts: register mode, two inlined sites
+        dir.enter(*tab);
+        uint32_t bins = 0;
 #pragma unroll 1
-        for (int i = 0; i < nmodes; i++)
-          if (!bin(68)) {
+        for (int i = 0; i < nmodes; i++) {
+          bins++;
+          if (!dir.fast_bin(*tab, 68)) {
+            bins += 3;
 #pragma unroll 1
-            for (int r = 0; r < 3; r++) bin(69);
+            for (int r = 0; r < 3; r++) dir.fast_bin(*tab, 69);
           }
+        }
+        dir.leave(bins);
       }
       // intra_chroma_pred_mode (h264_cabac.c:1383-1406)
       int ctx = 0;
@@ -621,7 +634,7 @@ struct Walker {
       // first bin: in a wide slice the first macroblock of a row cannot see how the previous row ended
       const int qctx = 60 + (last_qp_delta != 0);
       int q1;
-      if (wide_k && mb_x == 0) { count_bin(); q1 = dir.bin_row_qpd(*tab, qctx); }
+      if (wide_k && mb_x == 0) q1 = dir.bin_row_qpd(qctx);
       else q1 = bin(qctx);
       if (q1) {
         int val = 1, ctx = 2;
@@ -634,6 +647,9 @@ struct Walker {
       //   k = 1..16    luma 4x4 blocks 0..15  cat 1 (I16 AC) / 2 (4x4) / 5 (8x8, first block of a quadrant only)
       //   k = 17,18    chroma DC Cb, Cr       cat 3, blocks 49, 50
       //   k = 19..26   chroma AC              cat 4, blocks 16..19, 32..35
+      // the whole loop runs in register mode: coded_block_flag bins (one inlined site) and the blocks
+      dir.enter(*tab);
+      uint32_t bins = 0;
 #pragma unroll 1
       for (int k = i16 ? 0 : 1; k < 27; k++) {
         int cat, blk, maxc;
@@ -653,13 +669,14 @@ struct Walker {
           const int j = k - 19;
           cat = 4; blk = 16 + 16 * (j >> 2) + (j & 3); maxc = 15;
         }
-        if (has_cbf && !bin(cbf_ctx(cat, blk, intra))) continue;
-        residual(cat, blk, maxc);
+        if (has_cbf) { bins++; if (!dir.fast_bin(*tab, cbf_ctx(cat, blk, intra))) continue; }
+        bins += residual(cat, blk, maxc);
         if (cat == 0) cur_cbp |= 0x100;
         else if (cat == 3) cur_cbp |= uint32_t(0x40) << (blk - 49);
         else if (cat == 5) nzmask |= uint64_t(0xF) << blk;
         else nzmask |= uint64_t(1) << blk;
       }
+      dir.leave(bins);
     } else last_qp_delta = 0;
   }
 
@@ -734,7 +751,7 @@ struct Walker {
     mb_xy = int(d.first_mb);
     mb_x = mb_xy % (mbw > 0 ? mbw : 1); mb_y = mb_xy / (mbw > 0 ? mbw : 1);
     last_qp_delta = 0;
-    n_bins_lo = n_bins_hi = 0;
+    n_bins_hi = 0;
     status = WALK_OK;
     n_mbs = 0;
     done = false;
@@ -759,24 +776,25 @@ struct Walker {
   AVR_DEV void step() {
     if (mb_y >= mbh) { fail(WALK_CORRUPT); done = true; return; }
     if (Dir::kDecompress && wide_k) { blocked = false; if (!top_ready()) return; }
-    const uint32_t bins_before = n_bins_lo;
+    const uint32_t bins_before = n_bins_lo();
     macroblock();
     n_mbs++;
     int eos = 0;
     if (status == WALK_OK) eos = terminate();
-    if (n_bins_lo < bins_before) n_bins_hi++;
+    if (eos && !dir.consumed_all()) fail(WALK_CORRUPT);
+    if (n_bins_lo() < bins_before) n_bins_hi++;
     store_mb();
     mb_xy++;
     bool wrapped = false;
     if (++mb_x >= mbw) { mb_x = 0; mb_y++; wrapped = true; }
     if (Dir::kDecompress && wide_k) { ring_fence(); *prog_mine = uint32_t(mb_xy); }   // the row below may use this macroblock
-    dir.q.publish();
+    home_publish(dir.h);
     if (status != WALK_OK) { done = true; return; }
     if (eos) { done = true; return; }
     if (wide_k && wrapped) {
       if (!Dir::kDecompress) {   // next row -> next stream
         cur_ring = cur_ring + 1 == wide_k ? 0 : cur_ring + 1;
-        dir.q.switch_to(&rings[cur_ring], cur_ring);
+        home_switch_to(dir.h, &rings[cur_ring], cur_ring);
       } else {                   // on to this warp's next row, K - 1 rows further down
         dir.row_end(last_qp_delta != 0);
         mb_y += int(wide_k) - 1;

@@ -31,8 +31,7 @@ struct Ctx {
   avr_ctx* c = nullptr;
   Ctx() {
     avr_config cfg;
-    memset(&cfg, 0, sizeof cfg);
-    cfg.abi_version = AVR_ABI_VERSION;
+    avr_config_init(&cfg);
     cfg.device = getenv("AVR_DEVICE") ? atoi(getenv("AVR_DEVICE")) : 0;
     check(avr_create(&cfg, &c), "avr_create");
   }

@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define AVR_ABI_VERSION 1
+#define AVR_ABI_VERSION 2
 
 /* slice_type % 5 (H.264 7.4.3); SP/SI are reported unsupported */
 #define AVR_SLICE_P 0
@@ -105,11 +105,21 @@ typedef struct avr_slice_result {
 } avr_slice_result;
 
 typedef struct avr_config {
-  int32_t abi_version;     /* AVR_ABI_VERSION */
-  int32_t device;          /* CUDA device ordinal */
-  int32_t warps_per_block; /* 0 = default */
-  int32_t reserved;
+  int32_t abi_version;       /* AVR_ABI_VERSION */
+  int32_t device;            /* CUDA device ordinal */
+  int32_t blocks_per_sm;     /* 0 = default: thread blocks per SM of the kernel variant that keeps the estimators in global memory (1..8) */
+  int32_t wide_stream_bytes; /* chunked mode of the file calls: a slice of at least 2 x this many payload bytes becomes a wide slice.
+                                -1 = default (32768), 0 = never.  Environment AVR_WIDE_STREAM_BYTES overrides (debugging aid). */
+  int32_t resident;          /* where a block keeps its estimators: -1 = choose per batch (estimated makespan), 1 = shared memory
+                                (2 blocks per SM, fastest per slice), 0 = global memory (more blocks per SM).  Environment
+                                AVR_RESIDENT overrides (debugging aid). */
+  int32_t wide_batch_limit;  /* wide slices are a latency device: the file calls only use them while a batch has at most this many
+                                CABAC slices.  -1 = default (4 x the device's SM count), 0 = no limit. */
+  int32_t reserved[2];
 } avr_config;
+
+/* fills *cfg with the defaults (abi_version set, device 0, everything else "choose for me") */
+void avr_config_init(avr_config* cfg);
 
 typedef struct avr_ctx avr_ctx;
 
@@ -175,9 +185,11 @@ typedef struct avr_index_entry {
 } avr_index_entry;
 
 int  avr_index_h264(const uint8_t* file, uint64_t file_bytes, avr_index_entry** entries, int* n_entries);
-/* The n_streams the file calls give this slice in AVR_MODE_SLICE: 2 when its payload is at least two stream
- * quanta (32 KiB each; environment AVR_WIDE_STREAM_BYTES overrides, 0 = never), else 0.  No reference counterpart. */
+/* The n_streams the file calls give this slice in AVR_MODE_SLICE when the batch is small enough for wide slices
+ * (avr_config.wide_batch_limit): 2 when its payload is at least two stream quanta (avr_config.wide_stream_bytes of
+ * `ctx`; ctx == NULL: the default of 32 KiB each), else 0.  No reference counterpart. */
 int  avr_slice_streams(const avr_slice_desc* desc);
+int  avr_ctx_slice_streams(avr_ctx* ctx, const avr_slice_desc* desc, int n_batch_slices);
 
 /* chunking mode of the container produced by avr_file_compress */
 #define AVR_MODE_FILE   0  /* reference parity: one model for the whole file -- output is byte-identical
@@ -192,8 +204,10 @@ int  avr_file_compress(avr_ctx* ctx, const uint8_t* file, uint64_t file_bytes, i
 int  avr_file_decompress(avr_ctx* ctx, const uint8_t* rec, uint64_t rec_bytes,
                          uint8_t** file, uint64_t* file_bytes);
 /* The same for a corpus of independent files in ONE device batch (BASELINE config 5: many clips per GPU).
- * Files never share a model, so the result for file i is byte-identical to avr_file_compress /
- * avr_file_decompress of that file alone; recs[i] / files[i] are malloc'ed (avr_free each). */
+ * Files never share a model: in AVR_MODE_FILE the result for file i is byte-identical to avr_file_compress of that
+ * file alone; in AVR_MODE_SLICE it is too as long as the batch stays within avr_config.wide_batch_limit (beyond it
+ * long slices are no longer split into streams -- a throughput batch needs no latency device; every container
+ * decompresses to the same file either way).  recs[i] / files[i] are malloc'ed (avr_free each). */
 int  avr_files_compress(avr_ctx* ctx, const uint8_t* const* files, const uint64_t* file_bytes, int n_files, int mode,
                         uint8_t** recs, uint64_t* rec_bytes);
 int  avr_files_decompress(avr_ctx* ctx, const uint8_t* const* recs, const uint64_t* rec_bytes, int n_files,

@@ -39,7 +39,7 @@ static int run(const avr_slice_desc* descs, int n, const uint8_t* in, uint64_t i
   JobArgs a{descs, ios.data(), in, arena.data(), res};
   JobMem m;
   m.sh = sh; m.row = row.data(); m.cnt = counters.data();
-  m.nnz0 = planes.data(); m.nnz1 = planes.data() + max_frame; m.nnz_frame_bytes = max_frame;
+  m.nnz0 = planes.data(); m.nnz1 = planes.data() + max_frame; m.nnz_frame_bytes = max_frame; m.max_mbw = uint32_t(max_mbw);
   // wide slices (n_streams >= 2) get the block state of the wide kernel
   WideShared* wsh = new WideShared();
   fill_shared_tables(&wsh->tab, 0, 1);

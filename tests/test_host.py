@@ -35,7 +35,7 @@ def test_library_exports_every_declared_symbol(built):
     lib = A.load_library()
     for n in sorted(names):
         assert hasattr(lib, n), "missing export " + n
-    assert lib.avr_abi_version() == 1
+    assert lib.avr_abi_version() == 2 and C.sizeof(_abi.Config) == 32
     assert b"no CPU fallback" in lib.avr_strerror(_abi.AVR_ERR_NO_DEVICE)
 
 

@@ -35,4 +35,9 @@ with A.Context() as ctx:
     pay = sum(d.payload_size for d in descs); coded = sum(r.out_size for r in res); bins = sum(r.n_bins for r in res)
     print("slices %d payload %d coded %d bins %d max_slice_bins %d compress %.2f ms decompress %.2f ms" %
           (len(descs), pay, coded, bins, max(r.n_bins for r in res), ms_c, ms_d), flush=True)
+    big = max(range(len(res)), key=lambda i: res[i].n_bins)
+    for name, rr, ms in (("compress", res, ms_c), ("decompress", r_d, ms_d)):
+        w = rr[big].reserved
+        print("  longest slice, %s: parser waited for ring room %.1f ms, coder waited for entries %.1f ms (of ~%.1f ms at 1965 MHz)"
+              % (name, (w & 0xFFFF) * 65536 / 1.965e6, (w >> 16) * 65536 / 1.965e6, ms), flush=True)
     assert H.roundtrip_ok(descs, r_d, b_d, data)
