@@ -212,6 +212,13 @@ class Context:
         blob = C.string_at(out, nout.value) if (copy and nout.value) else b""
         return list(res), blob
 
+    def collect_hist(self):
+        """Per-class bin counts of the last launch: one list of 8 per slice (see avr_collect_hist)."""
+        self._lib.avr_collect_hist.argtypes = [C.c_void_p, C.POINTER(C.c_uint32), C.c_int]
+        buf = (C.c_uint32 * (8 * max(1, self._n)))()
+        _check(self._lib.avr_collect_hist(self._h, buf, self._n), "avr_collect_hist")
+        return [list(buf[8 * i:8 * i + 8]) for i in range(self._n)]
+
     def last_kernel_ms(self):
         ms = C.c_float()
         _check(self._lib.avr_last_kernel_ms(self._h, C.byref(ms)), "avr_last_kernel_ms")

@@ -555,17 +555,19 @@ AVR_DEV void ring_fence() { asm volatile("fence.acq_rel.cta;" ::: "memory"); }
 #define AVR_SYNCWARP_CORE() __syncwarp()
 #define AVR_BCAST_CORE(v) __shfl_sync(0xFFFFFFFFu, (v), 0)
 AVR_DEV void wide_backoff(uint32_t& polls) { if (++polls > 32) __nanosleep(polls > 256 ? 1000 : 100); }
-struct RingShared {
-  uint32_t e[RING_ENTRIES];
+struct RingCtl {
   uint32_t tail_pub, head_pub;
   uint32_t end_status, end_mbs, end_bins_lo, end_bins_hi;   // written by the parser before SYM_END
   uint32_t prod_tail, cons_head;   // wide slices: where a producer / consumer that moved to another ring left off
   uint32_t prod_wait, cons_wait;   // cycles / 256 the producer waited for room, the consumer for entries (which stage is the limit)
 };
-AVR_DEV void ring_reset(RingShared* r) { r->tail_pub = 0; r->head_pub = 0; r->prod_tail = 0; r->cons_head = 0; r->prod_wait = 0; r->cons_wait = 0; }
+enum : uint32_t { REC_ENTRIES = 256 };
+struct RingShared : RingCtl { uint32_t e[RING_ENTRIES]; };   // parser -> the warp behind it
+struct RecRing : RingCtl { uint32_t e[REC_ENTRIES]; };       // compress: estimator warp -> range-coder warp
+AVR_DEV void ring_reset(RingCtl* r) { r->tail_pub = 0; r->head_pub = 0; r->prod_tail = 0; r->cons_head = 0; r->prod_wait = 0; r->cons_wait = 0; }
 // makes room for an entry of n words: publishes what is complete, waits for the consumer if the ring is full; returns
 // the tail value up to which the producer may go on without looking again.  One out-of-line copy (instruction cache).
-AVR_DEV_NOINLINE uint32_t ring_slow(RingShared* r, uint32_t tail, uint32_t n, uint32_t cap) {
+AVR_DEV_NOINLINE uint32_t ring_slow(RingCtl* r, uint32_t tail, uint32_t n, uint32_t cap) {
   ring_fence();
   *reinterpret_cast<volatile uint32_t*>(&r->tail_pub) = tail;
   uint32_t head_seen = *reinterpret_cast<volatile uint32_t*>(&r->head_pub);
@@ -592,6 +594,8 @@ struct RingShared {
   uint32_t prod_wait = 0, cons_wait = 0;
 };
 inline void ring_reset(RingShared* r) { r->e.clear(); r->cons_head = 0; }
+typedef RingShared RecRing;
+typedef RingShared RingCtl;
 #endif
 // ------------------------------------------------------------------------------------------------
 // Coder warp.  All lanes fetch a batch of ring words (a poll of the published tail; for a ring in global
@@ -612,10 +616,12 @@ struct WordSrc {       // words of a batch: the shared-memory ring itself (mask 
 #if defined(__CUDACC__) && !defined(AVR_HOST_EMULATION)
 // the consumer side of a ring as the coder warp (all lanes) sees it
 struct RingReader {
-  RingShared* r;
-  uint32_t head;
+  RingCtl* r;
+  const uint32_t* ents;   // the ring's words when they are in shared memory
+  uint32_t mask, head;
   bool patient;
-  AVR_DEV void init(RingShared* ring, bool long_waits = false) { r = ring; head = 0; patient = long_waits; }
+  AVR_DEV void init(RingShared* ring, bool long_waits = false) { r = ring; ents = ring->e; mask = RING_ENTRIES - 1; head = 0; patient = long_waits; }
+  AVR_DEV void init_rec(RecRing* ring, bool long_waits = false) { r = ring; ents = ring->e; mask = REC_ENTRIES - 1; head = 0; patient = long_waits; }
   AVR_DEV uint32_t wait_avail() {   // all lanes poll the same word: a broadcast, no divergence
     uint32_t tail = *reinterpret_cast<volatile uint32_t*>(&r->tail_pub);
     if (head == tail) {
@@ -639,6 +645,7 @@ struct RingReader {
   RingShared* r;
   size_t head;
   void init(RingShared* ring, bool = false) { r = ring; head = 0; }
+  void init_rec(RingShared* ring, bool = false) { r = ring; head = 0; }
   uint32_t wait_avail() { return uint32_t(r->e.size() - head); }
   void release(uint32_t n, int) { head += n; }
 };
@@ -655,7 +662,7 @@ AVR_DEV uint32_t coder_fetch(RingReader& q, const uint32_t* far, uint32_t far_ca
     for (uint32_t i = uint32_t(lane); i < ns; i += 32) stage[i] = g[(q.head + i) & (far_cap - 1)];
     __syncwarp();
     src->e = stage; src->at = 0; src->mask = 0xFFFFFFFFu;
-  } else { src->e = q.r->e; src->at = q.head; src->mask = RING_ENTRIES - 1; }
+  } else { src->e = q.ents; src->at = q.head; src->mask = q.mask; }
 #else
   (void)far; (void)far_cap; (void)lane;
   for (uint32_t i = 0; i < n + ENTRY_MAX_WORDS; i++) stage[i] = q.head + i < q.r->e.size() ? q.r->e[q.head + i] : uint32_t(SYM_END);
@@ -664,64 +671,68 @@ AVR_DEV uint32_t coder_fetch(RingReader& q, const uint32_t* far, uint32_t far_ca
   return n;
 }
 
-struct CoderCompress {     // estimators + range encoder (recode.cpp:1068-1096 h264_symbol::execute)
-  RangeEnc rc;
-  AVR_DEV void begin(ByteSink* sink, uint8_t* dst, uint32_t cap, int = -1) { rc.init(sink, dst, cap); }
-  // one bin through the model and the range coder
-  AVR_DEV void code(const SharedTables& t, uint16_t* cnt, uint32_t idx, uint32_t bit, uint32_t limit) {
-    const uint32_t c = cnt[idx];
-    rc.put(t.div[c >> 8], int(bit), c & 0xFF);
-    cnt[idx] = uint16_t(est_next(c, bit, limit));
+// Compression has TWO recurrences behind the parser: the estimators (serial per estimator) and the 64-bit range
+// coder (serial per slice, ~35 instructions of multi-word arithmetic per bin).  One warp doing both was the slowest
+// stage of the direction (320-340 cycles per bin against 225 for the parser, profiles/r2e_*), so they are two warps
+// joined by a second ring of one RECORD per bin: the estimator as it stood before the bin {pos, total} (bits 0..15),
+// the bin (16), REC_FINISH = flush the range coder after this bin (end_of_slice = 1, recode.cpp:1092-1095); SYM_END.
+enum : uint32_t { REC_BIT_SHIFT = 16, REC_FINISH = 1u << 17 };
+struct RecWriter {     // producer side of the record ring, in registers (lane 0 of the estimator warp)
+  RecRing* r;
+#if defined(__CUDACC__) && !defined(AVR_HOST_EMULATION)
+  uint32_t tail, limit;
+  AVR_DEV void init(RecRing* ring) { r = ring; tail = 0; limit = RING_PUBLISH; }
+  AVR_DEV void put(uint32_t w) {
+    if (int32_t(limit - tail) < 1) limit = ring_slow(r, tail, 1, REC_ENTRIES);
+    r->e[tail & (REC_ENTRIES - 1)] = w;
+    tail++;
   }
-  // ... with its estimator and reciprocal loaded earlier (no update of that estimator in between)
-  AVR_DEV void code_pre(uint16_t* cnt, uint32_t idx, uint32_t c, const DivMagic& mg, uint32_t bit, uint32_t limit) {
-    rc.put(mg, int(bit), c & 0xFF);
+  AVR_DEV void publish() { ring_fence(); *reinterpret_cast<volatile uint32_t*>(&r->tail_pub) = tail; }
+#else
+  void init(RecRing* ring) { r = ring; }
+  void put(uint32_t w) { r->e.push_back(w); }
+  void publish() {}
+#endif
+};
+
+struct CoderCompress {     // the estimator warp (recode.cpp:1030-1047 + the model keys of 676-815 as indices)
+  RecWriter out;
+  AVR_DEV void begin(RecRing* records) { out.init(records); }
+  // one bin: the estimator's state goes to the range-coder warp, its update stays here
+  AVR_DEV void code(uint16_t* cnt, uint32_t idx, uint32_t bit, uint32_t limit, uint32_t flags = 0) {
+    const uint32_t c = cnt[idx];
+    out.put(c | bit << REC_BIT_SHIFT | flags);
     cnt[idx] = uint16_t(est_next(c, bit, limit));
   }
   // Significance bins of a 4x4-class block: the estimator index only ever grows inside a block (+1, or +17 after a
-  // coefficient), so the next estimator and its reciprocal are fetched while the current bin is in the coder and
-  // the loop-carried chain is the range recurrence alone.
-  AVR_DEV void sig_bins4(const SharedTables& t, uint16_t* cnt, uint32_t slab, uint32_t mask, uint32_t nnz_true, uint32_t coefs) {
+  // coefficient), so the next estimator is fetched while the current one is updated.
+  AVR_DEV void sig_bins4(uint16_t* cnt, uint32_t slab, uint32_t mask, uint32_t nnz_true, uint32_t coefs) {
     uint32_t idx = slab, zz = 0, observed = 0;
     uint32_t c = cnt[idx];
-    DivMagic mg = t.div[c >> 8];
 #pragma unroll 1
     for (;;) {
       const uint32_t bit = (mask >> zz) & 1u;
       const uint32_t idx_n = idx + 1u + (bit << 4);
       const uint32_t c_n = cnt[idx_n];
-      const DivMagic mg_n = t.div[c_n >> 8];
-      rc.put(mg, int(bit), c & 0xFF);
+      out.put(c | bit << REC_BIT_SHIFT);
       cnt[idx] = uint16_t(est_next(c, bit, LIMIT_SIG));
       observed += bit; zz++;
       if (observed >= nnz_true || zz >= coefs) break;
-      idx = idx_n; c = c_n; mg = mg_n;
-    }
-  }
-  // 8x8 blocks: several positions share an estimator (sig_coeff_flag_offset_8x8): the next estimator is fetched
-  // ahead and the update forwarded when it is the same one
-  AVR_DEV void sig_bins8(const SharedTables& t, uint16_t* cnt, uint32_t slab, uint64_t mask, uint32_t nnz_true) {
-    uint32_t zz = 0, observed = 0;
-    uint32_t idx = slab + t.sig8[0];
-    uint32_t c = cnt[idx];
-#pragma unroll 1
-    for (;;) {
-      const uint32_t bit = uint32_t(mask >> zz) & 1u;
-      const DivMagic mg = t.div[c >> 8];
-      const uint32_t idx_n = slab + (observed + bit) * SIG_ZZ + t.sig8[zz + 1];   // sig8[63] exists (0)
-      uint32_t c_n = cnt[idx_n];
-      const uint32_t c2 = est_next(c, bit, LIMIT_SIG);
-      cnt[idx] = uint16_t(c2);
-      if (idx_n == idx) c_n = c2;
-      rc.put(mg, int(bit), c & 0xFF);
-      observed += bit; zz++;
-      if (observed >= nnz_true || zz >= 63) break;
       idx = idx_n; c = c_n;
     }
   }
-  // nnz of a block as 2 / 4 / 6 model-coded bits, least significant first (recode.cpp:858, 874-888).  The estimators
-  // of the bits are distinct and depend on the entry alone: they are fetched in pairs ahead of the coder.
-  AVR_DEV void nnz_bits(const SharedTables& t, uint16_t* cnt, uint32_t cat, uint32_t w0, uint32_t w1) {
+  // 8x8 blocks: several positions share an estimator (sig_coeff_flag_offset_8x8)
+  AVR_DEV void sig_bins8(const SharedTables& t, uint16_t* cnt, uint32_t slab, uint64_t mask, uint32_t nnz_true) {
+    uint32_t zz = 0, observed = 0;
+#pragma unroll 1
+    while (observed < nnz_true && zz < 63) {
+      const uint32_t bit = uint32_t(mask >> zz) & 1u;
+      code(cnt, slab + observed * SIG_ZZ + t.sig8[zz], bit, LIMIT_SIG);
+      observed += bit; zz++;
+    }
+  }
+  // nnz of a block as 2 / 4 / 6 model-coded bits, least significant first (recode.cpp:858, 874-888)
+  AVR_DEV void nnz_bits(uint16_t* cnt, uint32_t cat, uint32_t w0, uint32_t w1) {
     const uint32_t maxc = k_maxc[cat];
     const uint32_t nbits = maxc > 16 ? 6 : maxc > 4 ? 4 : 2;
     const uint32_t left_nz = w1 & 0xFF, above_nz = (w1 >> 8) & 0xFF, prev_nz = (w1 >> 16) & 0xFF;
@@ -729,65 +740,59 @@ struct CoderCompress {     // estimators + range encoder (recode.cpp:1068-1096 h
     const uint32_t nnz = (w0 >> BLK_NNZ) & 63;   // 64 is coded as 0
     const uint32_t group = CNT_NZ + nz_group(int(cat), (w0 >> BLK_MB8) & 1);
 #pragma unroll 1
-    for (uint32_t i = 0; i < nbits; i += 2) {
-      uint32_t idx[2], c[2];
-#pragma unroll
-      for (uint32_t k = 0; k < 2; k++) {
-        const uint32_t cur_bit = 1u << (i + k);
-        const uint32_t so_far = nnz & (cur_bit - 1);
-        const uint32_t lb = has_left ? (left_nz >= cur_bit) : 2;
-        const uint32_t ab = above_nz ? (above_nz >= cur_bit) : 2;   // sic: value test (recode.cpp:881)
-        idx[k] = group + ((cur_bit - 1 + so_far) * 2 + (prev_nz >= cur_bit)) * 9 + lb * 3 + ab;
-        c[k] = cnt[idx[k]];
-      }
-      const DivMagic m0 = t.div[c[0] >> 8], m1 = t.div[c[1] >> 8];
-      code_pre(cnt, idx[0], c[0], m0, (nnz >> i) & 1, LIMIT_ANY);
-      code_pre(cnt, idx[1], c[1], m1, (nnz >> (i + 1)) & 1, LIMIT_ANY);
+    for (uint32_t i = 0; i < nbits; i++) {
+      const uint32_t cur_bit = 1u << i;
+      const uint32_t so_far = nnz & (cur_bit - 1);
+      const uint32_t lb = has_left ? (left_nz >= cur_bit) : 2;
+      const uint32_t ab = above_nz ? (above_nz >= cur_bit) : 2;   // sic: value test (recode.cpp:881)
+      code(cnt, group + ((cur_bit - 1 + so_far) * 2 + (prev_nz >= cur_bit)) * 9 + lb * 3 + ab, (nnz >> i) & 1, LIMIT_ANY);
     }
   }
   // one entry; returns true on SYM_END
   AVR_DEV bool entry(WordSrc& s, const SharedTables& t, uint16_t* cnt) {
     const uint32_t e = s.take();
     if (e & (SYM_END | SYM_LEVEL | SYM_BLOCK)) {
-      if (e & SYM_END) return true;
+      if (e & SYM_END) { out.put(SYM_END); return true; }
       if (e & SYM_BLOCK) {
         const uint32_t cat = e & 7, nnz_true = (e >> BLK_NNZ) & 0x7F;
         const uint32_t w1 = s.take();
         const uint32_t mlo = s.take();
-        nnz_bits(t, cnt, cat, e, w1);
+        nnz_bits(cnt, cat, e, w1);
         const uint32_t slab = sig_slab(int(cat), nnz_true & 63);
         if (cat == 5) {
           const uint32_t mhi = s.take();
           sig_bins8(t, cnt, slab, uint64_t(mlo) | uint64_t(mhi) << 32, nnz_true);
-        } else sig_bins4(t, cnt, slab, mlo, nnz_true, uint32_t(k_maxc[cat]) - 1);
+        } else sig_bins4(cnt, slab, mlo, nnz_true, uint32_t(k_maxc[cat]) - 1);
         return false;
       }
-      // one coefficient level: first bin, run of "greater than one" bins, sign -- three distinct estimators, all
-      // fetched before the first bin goes through the coder
+      // one coefficient level: first bin, run of "greater than one" bins, sign -- three distinct estimators
       const uint32_t b1 = (e >> LVL_BIT1) & 1, has_sign = (e >> LVL_HAS_SIGN) & 1;
       const uint32_t i1 = CNT_CTX + (e & 0x1FF), g = CNT_CTX + ((e >> LVL_GCTX) & 0x1FF);
       const uint32_t c1 = cnt[i1];
       uint32_t cg = cnt[g];
       const uint32_t cs = cnt[CNT_BYPASS];
-      const DivMagic m1 = t.div[c1 >> 8], ms = t.div[cs >> 8];
-      code_pre(cnt, i1, c1, m1, b1, LIMIT_ANY);
+      out.put(c1 | b1 << REC_BIT_SHIFT);
+      cnt[i1] = uint16_t(est_next(c1, b1, LIMIT_ANY));
       if (b1) {
 #pragma unroll 1
-        for (uint32_t r = (e >> LVL_RUN) & 15; r > 0; r--) { rc.put(t.div[cg >> 8], 1, cg & 0xFF); cg = est_next(cg, 1, LIMIT_ANY); }
-        if ((e >> LVL_TERM) & 1) { rc.put(t.div[cg >> 8], 0, cg & 0xFF); cg = est_next(cg, 0, LIMIT_ANY); }
+        for (uint32_t r = (e >> LVL_RUN) & 15; r > 0; r--) { out.put(cg | 1u << REC_BIT_SHIFT); cg = est_next(cg, 1, LIMIT_ANY); }
+        if ((e >> LVL_TERM) & 1) { out.put(cg); cg = est_next(cg, 0, LIMIT_ANY); }
         cnt[g] = uint16_t(cg);
       }
-      if (has_sign) code_pre(cnt, CNT_BYPASS, cs, ms, (e >> LVL_SIGN) & 1, LIMIT_ANY);
+      if (has_sign) {
+        const uint32_t sg = (e >> LVL_SIGN) & 1;
+        out.put(cs | sg << REC_BIT_SHIFT);
+        cnt[CNT_BYPASS] = uint16_t(est_next(cs, sg, LIMIT_ANY));
+      }
       return false;
     }
     const uint32_t idx = e & 0xFFFF, bit = (e >> SYM_BIT_SHIFT) & 1;
-    code(t, cnt, idx, bit, LIMIT_ANY);
-    if (idx == CNT_TERM && bit) range_enc_finish(rc.sink, rc.low, rc.range);   // recode.cpp:1092-1095
+    code(cnt, idx, bit, LIMIT_ANY, (idx == CNT_TERM && bit) ? uint32_t(REC_FINISH) : 0u);
     return false;
   }
-  // Drains a ring until SYM_END.  ALL lanes of the coder warp call this.  far: nullptr = the ring's own shared-memory
+  // Drains a ring until SYM_END.  ALL lanes of the estimator warp call this.  far: nullptr = the ring's own shared-memory
   // entries; else (wide slices) the ring's entries are in global memory at `far`, staged through `stage`, so that this
-  // coder may fall a good part of a macroblock row behind the parser and catch up while the parser feeds another stream.
+  // warp may fall a good part of a macroblock row behind the parser and catch up while the parser feeds another stream.
   AVR_DEV void run(RingShared* r, const uint32_t* far, uint32_t far_cap, bool patient, const SharedTables& t, uint16_t* cnt,
                    uint32_t* stage, int lane) {
     RingReader q; q.init(r, patient);
@@ -800,9 +805,44 @@ struct CoderCompress {     // estimators + range encoder (recode.cpp:1068-1096 h
 #pragma unroll 1
         while (!done && src.at - at0 < n) done = entry(src, t, cnt) ? 1u : 0u;
         used = src.at - at0;
+        out.publish();
       }
       used = AVR_BCAST_CORE(used); done = AVR_BCAST_CORE(done);
       q.release(used, lane);
+      if (done) break;
+    }
+  }
+};
+
+// the range-coder warp of a compression (recode.cpp:1074-1075 -> arithmetic_code.h:106-126): one record per bin
+struct RangeWarp {
+  RangeEnc rc;
+  AVR_DEV void begin(ByteSink* sink, uint8_t* dst, uint32_t cap) { rc.init(sink, dst, cap); }
+  AVR_DEV void run(RecRing* records, bool patient, const SharedTables& t, uint32_t* stage, int lane) {
+    RingReader q; q.init_rec(records, patient);
+    for (;;) {
+      WordSrc src;
+      const uint32_t n = coder_fetch(q, nullptr, 0, stage, lane, &src);
+      uint32_t done = 0;
+      if (lane == 0) {
+        // records never change once written: record k + 2 and the reciprocal of record k + 1 are fetched while record k
+        // goes through the coder, so that no load sits on the range recurrence
+        uint32_t rec = src.take();
+        uint32_t rec1 = n > 1 ? src.take() : uint32_t(SYM_END);
+        DivMagic mg = t.div[(rec >> 8) & 0xFF];
+#pragma unroll 2
+        for (uint32_t k = 2;; k++) {
+          if (rec & SYM_END) { done = 1; break; }
+          const uint32_t rec2 = k < n ? src.take() : uint32_t(SYM_END);
+          const DivMagic mg1 = t.div[(rec1 >> 8) & 0xFF];
+          rc.put(mg, int((rec >> REC_BIT_SHIFT) & 1), rec & 0xFF);
+          if (rec & REC_FINISH) range_enc_finish(rc.sink, rc.low, rc.range);
+          if (k > n) break;
+          rec = rec1; rec1 = rec2; mg = mg1;
+        }
+      }
+      done = AVR_BCAST_CORE(done);
+      q.release(n, lane);
       if (done) break;
     }
   }
@@ -940,6 +980,9 @@ struct CoderDecompress {   // CABAC re-encoder (cabac_code.h:16-86; recode.cpp:1
       do { cur = cur + 1 == n_rings ? 0 : cur + 1; tries++; } while (draining && tries <= n_rings && rings[cur].cons_head == 0xFFFFFFFFu);
       if (draining && tries > n_rings) break;
       q.r = &rings[cur];
+#if defined(__CUDACC__) && !defined(AVR_HOST_EMULATION)
+      q.ents = rings[cur].e;
+#endif
       q.head = uint32_t(rings[cur].cons_head);
     }
   }
@@ -955,6 +998,14 @@ struct CoderDecompress {   // CABAC re-encoder (cabac_code.h:16-86; recode.cpp:1
 // every site the decompression kernels were 230-250 KB of SASS and stalled one cycle per issued
 // instruction on instruction fetch (profiles/r1k_ncu_full_summary.txt).
 // ------------------------------------------------------------------------------------------------
+// Per-class bin counts of a slice (the reference's per-CodingType bills, recode.cpp:635-655, as counts): the fast
+// regions of the walker keep them in registers and add them to the home state when they leave.
+enum : int { HIST_MB = 0, HIST_CBF = 1, HIST_SIG = 2, HIST_LEVEL = 3, HIST_BYPASS = 4, HIST_NNZ = 5, HIST_PRED = 6, HIST_TERM = 7 };
+struct ResBins {
+  uint32_t cbf, sig, level, bypass, nnz, pred;
+  AVR_DEV void clear() { cbf = sig = level = bypass = nnz = pred = 0; }
+  AVR_DEV uint32_t cabac_bins() const { return cbf + sig + level + bypass + pred; }   // nnz bits are model-only bins
+};
 struct ParserHome {
   RingShared* r;            // ring, producer side
   uint32_t* ents;           //   the words: r->e, or (wide slices) a much longer ring in global memory
@@ -970,7 +1021,13 @@ struct ParserHome {
   uint64_t low, drange;     // decompress: RangeDec (its read position: dec)
   DecHome dec;
   uint32_t n_bins;          // bins walked so far (low word)
+  uint32_t hist[8];         // per class, HIST_*: [HIST_MB] and [HIST_TERM] are filled in at the end of the slice
 };
+AVR_DEV void home_add_bins(ParserHome* h, const ResBins& b) {
+  h->n_bins += b.cabac_bins();
+  h->hist[HIST_CBF] += b.cbf; h->hist[HIST_SIG] += b.sig; h->hist[HIST_LEVEL] += b.level;
+  h->hist[HIST_BYPASS] += b.bypass; h->hist[HIST_NNZ] += b.nnz; h->hist[HIST_PRED] += b.pred;
+}
 
 #if defined(__CUDACC__) && !defined(AVR_HOST_EMULATION)
 AVR_DEV void home_ring_init(ParserHome* h, RingShared* ring, uint32_t* far_entries, uint32_t far_cap) {
@@ -1110,6 +1167,7 @@ struct Compress {
     cstate = states; tabp = tab;
     home_ring_init(h, ring, far_entries, far_cap);
     h->tab = tab; h->cstate = states; h->cnt = counters; h->win = window; h->skew = in.skew; h->n_bins = 0;
+    for (int i = 0; i < 8; i++) h->hist[i] = 0;
   }
   AVR_DEV void start_bins(const SharedTables&) { CabacIn c; c.init(in); home_store(h, c); }
   AVR_DEV void finish_bins() {}
@@ -1130,7 +1188,7 @@ struct Compress {
   AVR_DEV bool consumed_all() const { return (h->pos * 8u - uint32_t(h->nbits) + 6u) / 8u == in.size; }
   // ---- registers ----
   AVR_DEV void enter(const SharedTables&) { ByteWindow w; home_load(h, cabac, w); q.enter(h); }
-  AVR_DEV void leave(uint32_t bins) { home_store(h, cabac); q.leave(h); h->n_bins += bins; }
+  AVR_DEV void leave(const ResBins& bins) { home_store(h, cabac); q.leave(h); home_add_bins(h, bins); }
   AVR_DEV int fast_bin(const SharedTables& t, int ctx) {   // an ordinary bin in register mode
     const int b = cabac.decision(in, t, &cstate[ctx]);
     q.reserve(h, 1); q.put(h, uint32_t(CNT_CTX + ctx) | uint32_t(b) << SYM_BIT_SHIFT);
@@ -1188,6 +1246,7 @@ struct Decompress {
     cnt = counters; tabp = tab;
     home_ring_init(h, ring, far_entries, far_cap);
     h->tab = tab; h->cstate = states; h->cnt = counters; h->win = window; h->skew = in.skew; h->n_bins = 0;
+    for (int i = 0; i < 8; i++) h->hist[i] = 0;
   }
   AVR_DEV void start_bins(const SharedTables&) {
     RangeDec d; d.init(&h->dec, in);
@@ -1209,11 +1268,11 @@ struct Decompress {
     byp_c = cnt[CNT_BYPASS];
     byp_mg = t.div[byp_c >> 8];
   }
-  AVR_DEV void leave(uint32_t bins) {
+  AVR_DEV void leave(const ResBins& bins) {
     h->low = rc.low; h->drange = rc.range;
     q.leave(h);
     cnt[CNT_BYPASS] = uint16_t(byp_c);
-    h->n_bins += bins;
+    home_add_bins(h, bins);
   }
   AVR_DEV int coded(const SharedTables& t, uint32_t idx, uint32_t limit) {
     const uint32_t c = cnt[idx];

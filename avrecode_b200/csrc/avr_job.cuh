@@ -3,21 +3,23 @@
 // Shared by the CUDA kernels (avr_lib.cu) and by the host emulation used for debugging in the
 // GPU-less container (tests/emu/avr_emu.cpp, never shipped).
 //
-// Thread abstraction: on the device a block has AVR_THREADS = 64 threads (warp 0 = parser, warp 1 =
-// coder); under AVR_HOST_EMULATION there is one thread that plays the parser for a whole slice into
+// Thread abstraction: on the device a block has 64 threads when decompressing (warp 0 = parser, warp 1 = CABAC
+// re-encoder) and 96 when compressing (parser, estimator warp, range-coder warp); under AVR_HOST_EMULATION there is one thread that plays the parser for a whole slice into
 // an unbounded queue and then the coder, so every "for (i = tid; i < n; i += nthreads)" loop
 // degenerates to a plain loop and the sync / broadcast primitives are no-ops.
 #pragma once
 #include "avr_walk.cuh"
 
 #if defined(__CUDACC__) && !defined(AVR_HOST_EMULATION)
-#define AVR_THREADS 64
+#define AVR_THREADS_OF(Dir) ((Dir::kDecompress) ? 64 : 96)   // compress: parser + estimator warp + range-coder warp
+#define AVR_HOST_STAGE(x) nullptr   // the device reads a shared-memory ring in place
 #define AVR_LANES 32
 #define AVR_SYNCWARP() __syncwarp()
 #define AVR_SYNCBLOCK() __syncthreads()
 #define AVR_BCAST(v) __shfl_sync(0xFFFFFFFFu, (v), 0)
 #else
-#define AVR_THREADS 1
+#define AVR_THREADS_OF(Dir) 1
+#define AVR_HOST_STAGE(x) (x)
 #define AVR_LANES 1
 #define AVR_SYNCWARP() ((void)0)
 #define AVR_SYNCBLOCK() ((void)0)
@@ -47,8 +49,14 @@ struct BlockShared {
   alignas(16) uint8_t window[WIN_BYTES];
   U2 cstate[N_CTX_PAD];     // CABAC context states {state, rangeTabLPS row}
   WalkShared walk;          // left macroblock + per-macroblock scratch of the walker
-  uint32_t stage[RING_BATCH + 2 * ENTRY_MAX_WORDS];   // host emulation only: the coder's view of a batch (the device reads the ring in place)
-  ByteSink sink;            // output bytes of the coder warp (touched once per byte, out of line)
+#if !defined(__CUDACC__) || defined(AVR_HOST_EMULATION)
+  uint32_t stage[RING_BATCH + 2 * ENTRY_MAX_WORDS];   // host emulation: the coder's view of a batch (the device reads the ring in place)
+#endif
+  RecRing records;          // compress: estimator warp -> range-coder warp, one word per bin
+#if !defined(__CUDACC__) || defined(AVR_HOST_EMULATION)
+  uint32_t stage2[RING_BATCH + 2 * ENTRY_MAX_WORDS];  // host emulation: the range-coder's view of a batch
+#endif
+  ByteSink sink;            // output bytes of the last warp (touched once per byte, out of line)
   ParserHome phome;         // the parser's engines between residual blocks
   uint32_t job;             // job handed out by the atomic counter
   uint32_t final_status;    // status of the slice just finished (coder writes, everyone reads)
@@ -61,6 +69,7 @@ struct JobArgs {
   const uint8_t* in_arena;
   uint8_t* out_arena;
   avr_slice_result* results;
+  uint32_t* hist;           // [n_slices][8] per-class bin counts (HIST_*), or null
 };
 
 struct JobMem {             // where this block keeps its state
@@ -236,37 +245,66 @@ AVR_DEV void parser_role(const JobArgs& a, const JobMem& m, const avr_slice_desc
   parser_end<Dir>(wk, lane);
 }
 
-// ---- coder warp: lane 0 drains the ring and owns the output bytes and the slice result -------------
+// ---- the warps behind the parser ---------------------------------------------------------------------------------
+// which stage waited for which: four bytes in units of 2^22 cycles (2.1 ms at 1965 MHz) -- parser for room in its ring,
+// the warp behind it for entries, estimator warp for room in the record ring, range-coder warp for records
+AVR_DEV uint32_t wait_bytes(const volatile RingCtl* a, const volatile RingCtl* b) {
+  uint32_t v = 0;
+  const uint32_t w[4] = {a->prod_wait, a->cons_wait, b ? b->prod_wait : 0u, b ? b->cons_wait : 0u};
+  for (int i = 0; i < 4; i++) { const uint32_t u = w[i] >> 14; v |= (u < 255 ? u : 255u) << (8 * i); }
+  return v;
+}
+// per-class bin counts of slice s out of the parser homes that walked it
+AVR_DEV void write_hist(const JobArgs& a, uint32_t s, const ParserHome* homes, uint32_t n_homes, uint32_t n_mbs, uint64_t n_bins) {
+  if (!a.hist) return;
+  uint32_t h[8];
+  for (int i = 0; i < 8; i++) { h[i] = 0; for (uint32_t j = 0; j < n_homes; j++) h[i] += homes[j].hist[i]; }
+  h[HIST_TERM] = n_mbs;   // one end_of_slice bin per macroblock
+  h[HIST_MB] = uint32_t(n_bins) - (h[HIST_CBF] + h[HIST_SIG] + h[HIST_LEVEL] + h[HIST_BYPASS] + h[HIST_PRED] + h[HIST_TERM]);
+  for (int i = 0; i < 8; i++) a.hist[size_t(s) * 8 + i] = h[i];
+}
+AVR_DEV void write_result(const JobArgs& a, const JobMem& m, const SliceIO& io, uint32_t s, uint32_t out_bytes, bool overflowed, bool two_rings) {
+  const volatile RingShared* r = &m.sh->ring;
+  avr_slice_result res;
+  res.out_off = io.out_off;
+  res.status = int32_t(r->end_status);
+  if (res.status == AVR_SLICE_OK && overflowed) res.status = AVR_SLICE_OVERFLOW;
+  res.out_size = res.status == AVR_SLICE_OK ? out_bytes : 0;
+  res.n_mbs = r->end_mbs;
+  res.reserved = wait_bytes(r, two_rings ? &m.sh->records : nullptr);
+  res.n_bins = uint64_t(r->end_bins_lo) | uint64_t(r->end_bins_hi) << 32;
+  a.results[s] = res;
+  write_hist(a, s, &m.sh->phome, 1, res.n_mbs, res.n_bins);
+  m.sh->final_status = uint32_t(res.status);
+}
+// decompress: the CABAC re-encoder, which owns the output bytes and the slice result; compress: the estimator warp
 template <class Dir>
 AVR_DEV void coder_role(const JobArgs& a, const JobMem& m, const SliceIO& io, uint32_t s, int lane) {
   typename Dir::Coder c;
-  const uint8_t lay = a.descs[s].n_streams;   // decompress: put emulation-prevention bytes back (escaped slices, chunked mode)
-  c.begin(&m.sh->sink, a.out_arena + io.out_off, io.out_cap, (lay & AVR_SLICE_ESCAPED) ? int((lay >> AVR_ESC_ZEROS_SHIFT) & 3) : -1);
-  if constexpr (Dir::kDecompress) c.run(&m.sh->ring, m.sh->tab, m.sh->cstate, m.sh->stage, lane);
-  else c.run(&m.sh->ring, nullptr, 0, false, m.sh->tab, m.cnt, m.sh->stage, lane);
-  if (lane == 0) {
-    const volatile RingShared* r = &m.sh->ring;
-    avr_slice_result res;
-    res.out_off = io.out_off;
-    res.status = int32_t(r->end_status);
-    if (res.status == AVR_SLICE_OK && c.overflowed()) res.status = AVR_SLICE_OVERFLOW;
-    res.out_size = res.status == AVR_SLICE_OK ? c.out_bytes() : 0;
-    res.n_mbs = r->end_mbs;
-    {   // which stage waited: parser for ring room (low half), coder for entries (high half), in units of 65536 cycles
-      const uint32_t pw = r->prod_wait >> 8, cw = r->cons_wait >> 8;
-      res.reserved = (pw < 0xFFFF ? pw : 0xFFFFu) | (cw < 0xFFFF ? cw : 0xFFFFu) << 16;
-    }
-    res.n_bins = uint64_t(r->end_bins_lo) | uint64_t(r->end_bins_hi) << 32;
-    a.results[s] = res;
-    m.sh->final_status = uint32_t(res.status);
+  if constexpr (Dir::kDecompress) {
+    const uint8_t lay = a.descs[s].n_streams;   // put emulation-prevention bytes back (escaped slices, chunked mode)
+    c.begin(&m.sh->sink, a.out_arena + io.out_off, io.out_cap, (lay & AVR_SLICE_ESCAPED) ? int((lay >> AVR_ESC_ZEROS_SHIFT) & 3) : -1);
+    c.run(&m.sh->ring, m.sh->tab, m.sh->cstate, AVR_HOST_STAGE(m.sh->stage), lane);
+    if (lane == 0) write_result(a, m, io, s, c.out_bytes(), c.overflowed(), false);
+  } else {
+    c.begin(&m.sh->records);
+    c.run(&m.sh->ring, nullptr, 0, false, m.sh->tab, m.cnt, AVR_HOST_STAGE(m.sh->stage), lane);
   }
+  AVR_SYNCWARP();
+}
+// compress: the range-coder warp, which owns the output bytes and the slice result
+AVR_DEV void range_role(const JobArgs& a, const JobMem& m, const SliceIO& io, uint32_t s, int lane) {
+  RangeWarp c;
+  c.begin(&m.sh->sink, a.out_arena + io.out_off, io.out_cap);
+  c.run(&m.sh->records, false, m.sh->tab, AVR_HOST_STAGE(m.sh->stage2), lane);
+  if (lane == 0) write_result(a, m, io, s, c.out_bytes(), c.overflowed(), true);
   AVR_SYNCWARP();
 }
 
 // Runs one job on the calling block.
 template <class Dir>
 AVR_DEV void run_job(const JobArgs& a, const JobDesc& job, const JobMem& m, int tid) {
-  const int nthreads = AVR_THREADS;
+  const int nthreads = AVR_THREADS_OF(Dir);
   const int lane = tid & (AVR_LANES - 1);
   FrameTags ft;
   ft.clear(); ft.num0 = ft.num1 = 0;
@@ -313,22 +351,25 @@ AVR_DEV void run_job(const JobArgs& a, const JobDesc& job, const JobMem& m, int 
     if (walk) {
       init_contexts(m.sh->cstate, d, tid, nthreads);
       if (!use_planes) fill_u32(reinterpret_cast<uint32_t*>(m.row), uint32_t(d.mb_width) * MBCTX_WORDS, 0, tid, nthreads);
-      if (tid == 0) ring_reset(&m.sh->ring);
+      if (tid == 0) { ring_reset(&m.sh->ring); ring_reset(&m.sh->records); }
     }
     AVR_SYNCBLOCK();
     if (walk) {
 #if defined(__CUDACC__) && !defined(AVR_HOST_EMULATION)
       if (tid < 32) parser_role<Dir>(a, m, d, io, ft.cur, use_planes, lane);
-      else coder_role<Dir>(a, m, io, s, lane);
+      else if (tid < 64) coder_role<Dir>(a, m, io, s, lane);
+      else range_role(a, m, io, s, lane);
 #else
       parser_role<Dir>(a, m, d, io, ft.cur, use_planes, lane);
       coder_role<Dir>(a, m, io, s, lane);
+      if (!Dir::kDecompress) range_role(a, m, io, s, lane);
 #endif
     } else if (tid == 0) {
       avr_slice_result r;
       r.out_off = io.out_off; r.out_size = 0; r.n_mbs = 0; r.reserved = 0; r.n_bins = 0;
       r.status = usable ? AVR_SLICE_OK : (poisoned ? AVR_SLICE_CORRUPT : AVR_SLICE_UNSUPPORTED);
       a.results[s] = r;
+      if (a.hist) for (int i = 0; i < 8; i++) a.hist[size_t(s) * 8 + i] = 0;
       m.sh->final_status = uint32_t(r.status);
     }
     AVR_SYNCBLOCK();
@@ -354,9 +395,9 @@ AVR_DEV void run_job(const JobArgs& a, const JobDesc& job, const JobMem& m, int 
 // limits K to WIDE_MAX = 2 (2 x 96 KB); the neighbour rows and the long symbol rings are in the global workspace.
 // ------------------------------------------------------------------------------------------------
 #if defined(__CUDACC__) && !defined(AVR_HOST_EMULATION)
-#define AVR_WIDE_THREADS ((WIDE_MAX + 1) * 32)
+#define AVR_WIDE_THREADS_OF(Dir) ((Dir::kDecompress) ? (WIDE_MAX + 1) * 32 : (2 * WIDE_MAX + 1) * 32)
 #else
-#define AVR_WIDE_THREADS 1
+#define AVR_WIDE_THREADS_OF(Dir) 1
 #endif
 
 struct WideShared {
@@ -371,7 +412,8 @@ struct WideShared {
   uint32_t overflow;
   uint32_t job;
   uint32_t stage[WIDE_MAX][144]; // the batch of ring words a coder warp is working on (decompress: [0] only)
-  ByteSink sink[WIDE_MAX];       // compress: one per coder warp; decompress: [0]
+  RecRing records[WIDE_MAX];     // compress: estimator warp j -> range-coder warp j
+  ByteSink sink[WIDE_MAX];       // compress: one per range-coder warp; decompress: [0]
   ParserHome phome[WIDE_MAX];    // one per parser warp (compress: [0])
 };
 
@@ -422,7 +464,7 @@ AVR_DEV void wide_walker(Walker<Dir>& wk, const WideMem& m, uint32_t K, uint32_t
 
 template <class Dir>
 AVR_DEV void run_wide_job(const JobArgs& a, uint32_t s, const WideMem& m, int tid) {
-  const int nthreads = AVR_WIDE_THREADS;
+  const int nthreads = AVR_WIDE_THREADS_OF(Dir);
   const int lane = tid & (AVR_LANES - 1);
   WideShared* sh = m.sh;
   const avr_slice_desc d = a.descs[s];
@@ -454,7 +496,7 @@ AVR_DEV void run_wide_job(const JobArgs& a, uint32_t s, const WideMem& m, int ti
   init_contexts(sh->cstate, d, tid, nthreads);
   fill_u32(reinterpret_cast<uint32_t*>(m.rows), (Dir::kDecompress ? K : 1u) * mbw * MBCTX_WORDS, 0, tid, nthreads);   // compress walks in place: one row
   fill_u32(reinterpret_cast<uint32_t*>(m.cnt), K * (MODEL_COUNTERS_PAD / 2), EST_INIT * 0x10001u, tid, nthreads);
-  for (uint32_t j = uint32_t(tid); j < K; j += uint32_t(nthreads)) { ring_reset(&sh->ring[j]); sh->prog[j] = d.first_mb; sh->out_size[j] = 0; }
+  for (uint32_t j = uint32_t(tid); j < K; j += uint32_t(nthreads)) { ring_reset(&sh->ring[j]); ring_reset(&sh->records[j]); sh->prog[j] = d.first_mb; sh->out_size[j] = 0; }
   if (tid == 0) { sh->abort_flag = 0; sh->overflow = 0; }
   AVR_SYNCBLOCK();
 
@@ -469,16 +511,22 @@ AVR_DEV void run_wide_job(const JobArgs& a, uint32_t s, const WideMem& m, int ti
       parser_begin<Dir>(wk, ln, blob, io.in_size, d, nullptr, nullptr, false, lane, 0, 0);
       parser_run<Dir>(wk, lane);
       parser_end<Dir>(wk, lane);
-    } else if (warp <= K) {
+    } else if (warp <= K) {   // estimator warp of stream j
       const uint32_t j = warp - 1;
       typename Dir::Coder c;
-      c.begin(&sh->sink[j], out + hdr + size_t(j) * subcap, subcap);
+      c.begin(&sh->records[j]);
       c.run(&sh->ring[j], m.far + size_t(j) * m.far_cap, m.far_cap, true, sh->tab, m.cnt + size_t(j) * MODEL_COUNTERS_PAD, sh->stage[j], lane);
+      AVR_SYNCWARP();   // the other lanes must not run ahead into the block barrier
+    } else if (warp <= 2 * K) {   // range-coder warp of stream j
+      const uint32_t j = warp - 1 - K;
+      RangeWarp c;
+      c.begin(&sh->sink[j], out + hdr + size_t(j) * subcap, subcap);
+      c.run(&sh->records[j], true, sh->tab, nullptr, lane);
       if (lane == 0) {
         sh->out_size[j] = c.out_bytes();
         if (c.overflowed()) sh->overflow = 1;
       }
-      AVR_SYNCWARP();   // the other lanes must not run ahead into the block barrier
+      AVR_SYNCWARP();
     }
   } else {
     if (warp == 0) {
@@ -514,10 +562,13 @@ AVR_DEV void run_wide_job(const JobArgs& a, uint32_t s, const WideMem& m, int ti
     parser_end<Dir>(wk, lane);
     for (uint32_t j = 0; j < K; j++) {
       typename Dir::Coder c;
-      c.begin(&sh->sink[j], out + hdr + size_t(j) * subcap, subcap);
+      c.begin(&sh->records[j]);
       c.run(&sh->ring[j], nullptr, 0, true, sh->tab, m.cnt + size_t(j) * MODEL_COUNTERS_PAD, sh->stage[j], lane);
-      sh->out_size[j] = c.out_bytes();
-      if (c.overflowed()) sh->overflow = 1;
+      RangeWarp rw;
+      rw.begin(&sh->sink[j], out + hdr + size_t(j) * subcap, subcap);
+      rw.run(&sh->records[j], true, sh->tab, sh->stage[j], lane);
+      sh->out_size[j] = rw.out_bytes();
+      if (rw.overflowed()) sh->overflow = 1;
     }
   } else {
     Walker<Dir>* wk = new Walker<Dir>[WIDE_MAX];
@@ -599,6 +650,7 @@ AVR_DEV void run_wide_job(const JobArgs& a, uint32_t s, const WideMem& m, int ti
     res.reserved = 0;
     res.n_bins = bins;
     a.results[s] = res;
+    write_hist(a, s, sh->phome, Dir::kDecompress ? K : 1u, mbs, bins);
   }
   AVR_SYNCBLOCK();
 }

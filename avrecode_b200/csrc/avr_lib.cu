@@ -38,7 +38,7 @@ size_t smem_bytes(uint32_t max_mbw, bool resident) {
 // Block = parser warp + coder warp.  Shared memory: BlockShared | MbCtx row[max_mbw] | estimators (RESIDENT).
 // Persistent blocks take jobs from an atomic counter (longest first).
 template <class Dir, bool RESIDENT>
-__global__ void __launch_bounds__(AVR_THREADS, RESIDENT ? 2 : 8) avr_job_kernel(KernelArgs k) {
+__global__ void __launch_bounds__(AVR_THREADS_OF(Dir), RESIDENT ? 2 : 8) avr_job_kernel(KernelArgs k) {
   extern __shared__ __align__(16) uint8_t smem[];
   JobMem m;
   m.sh = reinterpret_cast<BlockShared*>(smem);
@@ -52,7 +52,7 @@ __global__ void __launch_bounds__(AVR_THREADS, RESIDENT ? 2 : 8) avr_job_kernel(
   m.nnz_frame_bytes = k.nnz_frame_bytes;
   m.max_mbw = k.max_mbw;
   const int tid = threadIdx.x;
-  fill_shared_tables(&m.sh->tab, tid, AVR_THREADS);
+  fill_shared_tables(&m.sh->tab, tid, AVR_THREADS_OF(Dir));
   __syncthreads();
   for (;;) {
     if (tid == 0) m.sh->job = atomicAdd(k.counter, 1u);
@@ -86,7 +86,7 @@ size_t wide_rows_bytes(uint32_t max_mbw) { return align_up(size_t(WIDE_MAX) * ma
 size_t wide_smem_bytes() { return align_up(sizeof(WideShared), 16) + align_up(size_t(WIDE_MAX) * MODEL_COUNTERS_PAD * 2, 16); }
 
 template <class Dir>
-__global__ void __launch_bounds__(AVR_WIDE_THREADS, 1) avr_wide_kernel(WideKernelArgs k) {
+__global__ void __launch_bounds__(AVR_WIDE_THREADS_OF(Dir), 1) avr_wide_kernel(WideKernelArgs k) {
   extern __shared__ __align__(16) uint8_t smem[];
   WideMem m;
   m.sh = reinterpret_cast<WideShared*>(smem);
@@ -103,7 +103,7 @@ __global__ void __launch_bounds__(AVR_WIDE_THREADS, 1) avr_wide_kernel(WideKerne
   // may start filling the remaining SMs (launched the other way round its blocks would take the shared memory
   // of every SM and the wide blocks -- a whole SM each -- would wait for them)
   asm volatile("griddepcontrol.launch_dependents;");
-  fill_shared_tables(&m.sh->tab, tid, AVR_WIDE_THREADS);
+  fill_shared_tables(&m.sh->tab, tid, AVR_WIDE_THREADS_OF(Dir));
   __syncthreads();
   for (;;) {
     if (tid == 0) m.sh->job = atomicAdd(k.counter, 1u);
@@ -161,7 +161,7 @@ struct avr_ctx {
   int wide_stream_bytes = 32768;   // avr_config.wide_stream_bytes / AVR_WIDE_STREAM_BYTES env
   int wide_batch_limit = -1;       // avr_config.wide_batch_limit (-1: 4 x SMs, 0: none)
   // meta offsets
-  size_t off_descs = 0, off_ios = 0, off_jobs = 0, off_res = 0, off_counter = 0;
+  size_t off_descs = 0, off_ios = 0, off_jobs = 0, off_res = 0, off_hist = 0, off_counter = 0;
   uint64_t work_stride = 0;
   int max_smem_sm = 0;
   float last_ms = 0.f;
@@ -383,7 +383,8 @@ int avr_stage(avr_ctx* c, const avr_slice_desc* descs, int n, const uint8_t* in,
   c->off_jobs = align_up(c->off_ios + 2 * sizeof(SliceIO) * n, 256);
   c->off_wide = align_up(c->off_jobs + sizeof(JobDesc) * c->jobs.size(), 256);
   c->off_res = align_up(c->off_wide + sizeof(uint32_t) * c->wide.size(), 256);
-  c->off_counter = align_up(c->off_res + sizeof(avr_slice_result) * n, 256);
+  c->off_hist = align_up(c->off_res + sizeof(avr_slice_result) * n, 256);
+  c->off_counter = align_up(c->off_hist + 8 * sizeof(uint32_t) * n, 256);
   size_t meta_bytes = c->off_counter + 256;
   if ((rc = grow_dev(&c->d_meta, &c->d_meta_cap, meta_bytes))) return rc;
   if ((rc = grow_pinned(&c->h_meta, &c->h_meta_cap, meta_bytes))) return rc;
@@ -414,6 +415,7 @@ int avr_launch(avr_ctx* c, int direction) {
   k.a.in_arena = c->d_in;
   k.a.out_arena = c->d_out;
   k.a.results = reinterpret_cast<avr_slice_result*>(c->d_meta + c->off_res);
+  k.a.hist = reinterpret_cast<uint32_t*>(c->d_meta + c->off_hist);
   k.jobs = reinterpret_cast<const JobDesc*>(c->d_meta + c->off_jobs);
   k.n_jobs = uint32_t(c->n_jobs);
   k.counter = reinterpret_cast<uint32_t*>(c->d_meta + c->off_counter);
@@ -442,10 +444,10 @@ int avr_launch(avr_ctx* c, int direction) {
     if (w.rows_in_shared) wsmem += rows_bytes;
     if (direction == 0) {
       CK(cudaFuncSetAttribute(avr_wide_kernel<Compress>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(wsmem)));
-      avr_wide_kernel<Compress><<<c->grid_wide, AVR_WIDE_THREADS, wsmem, c->stream>>>(w);
+      avr_wide_kernel<Compress><<<c->grid_wide, AVR_WIDE_THREADS_OF(Compress), wsmem, c->stream>>>(w);
     } else {
       CK(cudaFuncSetAttribute(avr_wide_kernel<Decompress>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(wsmem)));
-      avr_wide_kernel<Decompress><<<c->grid_wide, AVR_WIDE_THREADS, wsmem, c->stream>>>(w);
+      avr_wide_kernel<Decompress><<<c->grid_wide, AVR_WIDE_THREADS_OF(Decompress), wsmem, c->stream>>>(w);
     }
     CK(cudaGetLastError());
     c->launches++;
@@ -457,7 +459,7 @@ int avr_launch(avr_ctx* c, int direction) {
   pdl.val.programmaticStreamSerializationAllowed = 1;
   cudaLaunchConfig_t lc;
   memset(&lc, 0, sizeof lc);
-  lc.gridDim = dim3(unsigned(c->grid)); lc.blockDim = dim3(AVR_THREADS); lc.dynamicSmemBytes = smem; lc.stream = c->stream;
+  lc.gridDim = dim3(unsigned(c->grid)); lc.blockDim = dim3(direction == 0 ? AVR_THREADS_OF(Compress) : AVR_THREADS_OF(Decompress)); lc.dynamicSmemBytes = smem; lc.stream = c->stream;
   lc.attrs = &pdl; lc.numAttrs = c->grid_wide > 0 ? 1 : 0;
 #define AVR_LAUNCH(DIR, RES)                                                                                              \
   do {                                                                                                                    \
@@ -506,6 +508,16 @@ int avr_collect(avr_ctx* c, avr_slice_result* results, const uint8_t** out, uint
 // what the host file layer (avr_file.cpp) needs to know about the context
 int avr_ctx_wide_stream_bytes(avr_ctx* c) { return c ? c->wide_stream_bytes : 32768; }
 int avr_ctx_wide_batch_limit(avr_ctx* c) { return !c ? 0 : c->wide_batch_limit < 0 ? 4 * c->sm_count : c->wide_batch_limit; }
+
+int avr_collect_hist(avr_ctx* c, uint32_t* hist, int n_slices) {
+  if (!c || !hist || n_slices != c->n_slices) return AVR_ERR_ARG;
+  if (!c->launched) return AVR_ERR_STATE;
+  if (n_slices == 0) return AVR_OK;
+  CK(cudaSetDevice(c->device));
+  CK(cudaStreamSynchronize(c->stream));
+  CK(cudaMemcpy(hist, c->d_meta + c->off_hist, size_t(8) * sizeof(uint32_t) * n_slices, cudaMemcpyDeviceToHost));
+  return AVR_OK;
+}
 
 int avr_last_kernel_ms(avr_ctx* c, float* ms) {
   if (!c || !ms) return AVR_ERR_ARG;

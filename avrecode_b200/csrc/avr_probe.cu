@@ -20,7 +20,7 @@ struct ProbeShared {
   U2 cstate[N_CTX_PAD];
   uint16_t cnt[10240];
   uint8_t out[8192];
-  uint32_t stage[RING_BATCH + 2 * ENTRY_MAX_WORDS];
+  RecRing records;
   ByteSink sink;
   ParserHome home;
 };
@@ -180,25 +180,60 @@ __device__ uint32_t fill_ring(ProbeShared* sh, bool decompress) {
   return bins;
 }
 
-// 5: the compress coder warp (all lanes expand the entries, lane 0 runs estimators + 64-bit range encoder) over a full ring
-__device__ void probe_coder_c(ProbeShared* sh, const ProbeArgs& a, uint64_t* r, int lane) {
+// 5: the two warps behind the compress parser as a pipeline: estimator warp (warp 0) -> record ring -> range-coder
+//    warp (warp 1), over a full ring of block / level entries
+__device__ void probe_coder_c(ProbeShared* sh, const ProbeArgs& a, uint64_t* r, int tid) {
+  const int lane = tid & 31;
   uint32_t per = 0;
-  if (lane == 0) per = fill_ring(sh, false);
-  per = __shfl_sync(0xFFFFFFFFu, per, 0);
+  if (tid == 0) per = fill_ring(sh, false);
+  __syncthreads();
   uint64_t bins = 0;
-  CoderCompress c;
-  c.begin(&sh->sink, sh->out, sizeof sh->out);
-  __syncwarp();
   const long long t0 = clock64();
 #pragma unroll 1
   for (uint32_t i = 0; i < a.iters; i++) {
-    c.run(&sh->ring, nullptr, 0, false, sh->tab, sh->cnt, sh->stage, lane);
-    if (lane == 0) sh->sink.n = 0;
+    if (tid == 0) ring_reset(&sh->records);
+    __syncthreads();
+    if (tid < 32) {
+      CoderCompress c;
+      c.begin(&sh->records);
+      c.run(&sh->ring, nullptr, 0, false, sh->tab, sh->cnt, nullptr, lane);
+    } else {
+      RangeWarp w;
+      w.begin(&sh->sink, sh->out, sizeof sh->out);
+      w.run(&sh->records, false, sh->tab, nullptr, lane);
+    }
+    __syncthreads();
     bins += per;
+  }
+  const long long t1 = clock64();
+  r[0] = uint64_t(t1 - t0); r[1] = bins; r[2] = sh->sink.n;
+}
+
+// 8: the range-coder warp alone over a full record ring (RangeWarp::run)
+__device__ void probe_range(ProbeShared* sh, const ProbeArgs& a, uint64_t* r, int lane) {
+  if (lane == 0) {
+    uint32_t s = 4242u;
+    for (uint32_t i = 0; i + 1 < REC_ENTRIES; i++) {
+      const uint32_t tot = 2 + lcg(s) % 90, pos = 1 + lcg(s) % (tot - 1);
+      sh->records.e[i] = pos | tot << 8 | (lcg(s) % 3 == 0 ? 1u : 0u) << REC_BIT_SHIFT;
+    }
+    sh->records.e[REC_ENTRIES - 1] = SYM_END;
+    sh->records.tail_pub = REC_ENTRIES; sh->records.head_pub = 0;
+  }
+  __syncwarp();
+  uint64_t bins = 0;
+  RangeWarp w;
+  w.begin(&sh->sink, sh->out, sizeof sh->out);
+  const long long t0 = clock64();
+#pragma unroll 1
+  for (uint32_t i = 0; i < a.iters; i++) {
+    w.run(&sh->records, false, sh->tab, nullptr, lane);
+    if (lane == 0) sh->sink.n = 0;
+    bins += REC_ENTRIES - 1;
     __syncwarp();
   }
   const long long t1 = clock64();
-  r[0] = uint64_t(t1 - t0); r[1] = bins; r[2] = c.rc.low;
+  r[0] = uint64_t(t1 - t0); r[1] = bins; r[2] = w.rc.low;
 }
 
 // 6: the decompress coder warp (all lanes expand, lane 0 runs the CABAC re-encoder) over a full ring
@@ -213,7 +248,7 @@ __device__ void probe_coder_d(ProbeShared* sh, const ProbeArgs& a, uint64_t* r, 
   const long long t0 = clock64();
 #pragma unroll 1
   for (uint32_t i = 0; i < a.iters; i++) {
-    c.run(&sh->ring, sh->tab, sh->cstate, sh->stage, lane);
+    c.run(&sh->ring, sh->tab, sh->cstate, nullptr, lane);
     if (lane == 0) sh->sink.n = 0;
     bins += per;
     __syncwarp();
@@ -240,14 +275,15 @@ __device__ void probe_push(ProbeShared* sh, const ProbeArgs& a, uint64_t* r) {
 }
 
 template <int WHICH>
-__global__ void __launch_bounds__(32, 1) avr_probe_kernel(ProbeArgs a) {
+__global__ void __launch_bounds__(64, 1) avr_probe_kernel(ProbeArgs a) {
   __shared__ ProbeShared sh;
-  probe_setup(&sh, threadIdx.x, 32);
+  probe_setup(&sh, threadIdx.x, int(blockDim.x));
   __syncthreads();
-  if (WHICH == 5 || WHICH == 6) {   // warp-wide roles
+  if (WHICH == 5 || WHICH == 6 || WHICH == 8) {   // warp-wide roles
     uint64_t r[3] = {0, 0, 0};
     if (WHICH == 5) probe_coder_c(&sh, a, r, int(threadIdx.x));
     if (WHICH == 6) probe_coder_d(&sh, a, r, int(threadIdx.x));
+    if (WHICH == 8) probe_range(&sh, a, r, int(threadIdx.x));
     if (threadIdx.x == 0) { a.result[0] = r[0]; a.result[1] = r[1]; a.result[2] = r[2]; }
   } else if (threadIdx.x == 0) {
     uint64_t r[3] = {0, 0, 0};
@@ -272,9 +308,10 @@ const char* avr_probe_name(int which) {
     "compress significance loop, 4x4 block (CABAC decode of sig/last bins)",
     "decompress bin: estimator + exact division + RangeDec::get + update (Decompress::coded)",
     "decompress significance loop, 4x4 block (both successors prefetched)",
-    "compress coder warp: estimators + RangeEnc::put over a ring of block / level entries (CoderCompress::run)",
+    "compress, the two warps behind the parser as a pipeline: estimator warp -> records -> range-coder warp, over block / level entries",
     "decompress coder warp: CABAC re-encoder over a ring of block / level entries (CoderDecompress::run)",
     "macroblock-level bin, compress: out-of-line CABAC decision on the shared-memory engine copy + ring entry",
+    "compress range-coder warp alone: reciprocal + RangeEnc::put over a ring of records (RangeWarp::run)",
   };
   return which >= 0 && which < int(sizeof names / sizeof names[0]) ? names[which] : nullptr;
 }
@@ -295,9 +332,10 @@ int avr_probe(int device, int which, uint32_t iters, uint64_t* cycles, uint64_t*
       case 2: avr_probe_kernel<2><<<1, 32>>>(a); break;
       case 3: avr_probe_kernel<3><<<1, 32>>>(a); break;
       case 4: avr_probe_kernel<4><<<1, 32>>>(a); break;
-      case 5: avr_probe_kernel<5><<<1, 32>>>(a); break;
+      case 5: avr_probe_kernel<5><<<1, 64>>>(a); break;
       case 6: avr_probe_kernel<6><<<1, 32>>>(a); break;
-      default: avr_probe_kernel<7><<<1, 32>>>(a); break;
+      case 7: avr_probe_kernel<7><<<1, 32>>>(a); break;
+      default: avr_probe_kernel<8><<<1, 32>>>(a); break;
     }
     if (cudaDeviceSynchronize() != cudaSuccess) { cudaGetLastError(); cudaFree(d); return AVR_ERR_CUDA; }
   }

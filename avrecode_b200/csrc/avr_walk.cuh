@@ -171,14 +171,14 @@ struct Walker {
   // coder derives the nnz bits and the model-coded significance bins from it, the decompress coder the
   // CABAC sig / last bins.  What stays here is what is serial by nature: pulling the map out of the
   // CABAC stream (compress) or out of the range coder (decompress).
-  // Runs between dir.enter() and dir.leave(): returns the bins of the block.
-  AVR_DEV uint32_t residual(int cat, int blk, int max_coeff) {
+  // Runs between dir.enter() and dir.leave(): adds the bins of the block to `rb`.
+  AVR_DEV void residual(int cat, int blk, int max_coeff, ResBins& rb) {
     const bool is8 = max_coeff == 64;
     const int coefs = max_coeff - 1;
     const int abs_base = k_abs_base[cat];
     if (is8) model_is8x8 = true;          // before the nnz bits, as the compressor does
     uint32_t nnz_true, key_nnz;
-    uint32_t bins = 0;                    // bins of this block
+    rb.nnz += max_coeff > 16 ? 6 : max_coeff > 4 ? 4 : 2;
     if constexpr (!Dir::kDecompress) {
       // 1. pull the significance map out of the CABAC stream (h264_cabac.c:1667-1681)
       const int sig_base = k_sig_base[cat], last_base = k_last_base[cat];
@@ -202,7 +202,7 @@ struct Walker {
           }
           e_sig = e_next;
         }
-        bins += uint32_t(last) + nnz;   // one sig bin per position scanned, one last bin per coefficient found
+        rb.sig += uint32_t(last) + nnz;   // one sig bin per position scanned, one last bin per coefficient found
         mask = m32;
       } else {
 #pragma unroll 1
@@ -213,7 +213,7 @@ struct Walker {
             if (dir.sig_get(*tab, last_base + tab->last8[last])) { ended = true; last++; break; }
           }
         }
-        bins += uint32_t(last) + nnz;
+        rb.sig += uint32_t(last) + nnz;
       }
       // a scan that never met last_significant_coeff_flag = 1 ends in an inferred coefficient at the last position
       if (!ended) { mask |= uint64_t(1) << coefs; nnz++; }
@@ -263,7 +263,7 @@ struct Walker {
           zz++;
         }
       }
-      bins += uint32_t(zz) + observed;   // the CABAC bins the re-encoder derives from the entry
+      rb.sig += uint32_t(zz) + observed;   // the CABAC bins the re-encoder derives from the entry
       dir.block_push(cat, nnz_true, mask);
     }
     ws->nnz_mb[blk] = uint8_t(key_nnz);
@@ -278,7 +278,7 @@ struct Walker {
       const int ctx1 = abs_base + (node < 4 ? node + 1 : 0);      // coeff_abs_level1_ctx
       int gctx = abs_base + 5, run = 0, term = 0;
       bool escape = false;
-      bins++;
+      rb.level++;
       const int b1 = dir.lvl_first(*tab, e1, ctx1);
       if (b1 == 0) {
         node = node < 3 ? node + 1 : node;                         // transition after |level| == 1
@@ -287,13 +287,13 @@ struct Walker {
         node = node < 4 ? 4 : (node < 7 ? node + 1 : 7);           // transition after |level| > 1
         typename Dir::BinEntry g = dir.bin_fetch(*tab, gctx);      // a run on one context: state kept in registers
 #pragma unroll 1
-        while (run < 13) { bins++; if (!dir.lvl_run(*tab, g, gctx)) { term = 1; break; } run++; }
+        while (run < 13) { rb.level++; if (!dir.lvl_run(*tab, g, gctx)) { term = 1; break; } run++; }
         dir.bin_store(g, gctx);
         escape = !term;                                             // |level| >= 15: Exp-Golomb suffix follows
       }
       e1 = dir.bin_fetch(*tab, abs_base + (node < 4 ? node + 1 : 0));
       if (!escape) {
-        bins++;
+        rb.bypass++;
         const int sg = dir.lvl_sign(*tab);
         dir.lvl_push(lvl_entry(ctx1, b1, gctx, run, term, 1, sg));   // the whole level as one ring entry
       } else {
@@ -301,14 +301,13 @@ struct Walker {
         int j = 0;
 #pragma unroll 1
         while (dir.lvl_bypass(*tab) && j < 30) j++;
-        bins += uint32_t(2 * j + 2);   // prefix (j ones and the zero -- or 30 ones), j suffix bits, sign
-        if (j >= 30) bins--;
+        rb.bypass += uint32_t(2 * j + 2);   // prefix (j ones and the zero -- or 30 ones), j suffix bits, sign
+        if (j >= 30) rb.bypass--;
 #pragma unroll 1
         while (j--) dir.lvl_bypass(*tab);
         dir.lvl_bypass(*tab);   // sign
       }
     }
-    return bins;
   }
 
   // ---- context helpers --------------------------------------------------------------------------
@@ -514,12 +513,12 @@ struct Walker {
         if (t8_allowed && bin(CTX_T8X8 + nts)) { t8 = true; nmodes = 4; }
         // up to 64 bins on two contexts: register mode, two inlined sites
         dir.enter(*tab);
-        uint32_t bins = 0;
+        ResBins bins; bins.clear();
 #pragma unroll 1
         for (int i = 0; i < nmodes; i++) {
-          bins++;
+          bins.pred++;
           if (!dir.fast_bin(*tab, 68)) {
-            bins += 3;
+            bins.pred += 3;
 #pragma unroll 1
             for (int r = 0; r < 3; r++) dir.fast_bin(*tab, 69);
           }
@@ -649,7 +648,7 @@ struct Walker {
       //   k = 19..26   chroma AC              cat 4, blocks 16..19, 32..35
       // the whole loop runs in register mode: coded_block_flag bins (one inlined site) and the blocks
       dir.enter(*tab);
-      uint32_t bins = 0;
+      ResBins bins; bins.clear();
 #pragma unroll 1
       for (int k = i16 ? 0 : 1; k < 27; k++) {
         int cat, blk, maxc;
@@ -669,8 +668,8 @@ struct Walker {
           const int j = k - 19;
           cat = 4; blk = 16 + 16 * (j >> 2) + (j & 3); maxc = 15;
         }
-        if (has_cbf) { bins++; if (!dir.fast_bin(*tab, cbf_ctx(cat, blk, intra))) continue; }
-        bins += residual(cat, blk, maxc);
+        if (has_cbf) { bins.cbf++; if (!dir.fast_bin(*tab, cbf_ctx(cat, blk, intra))) continue; }
+        residual(cat, blk, maxc, bins);
         if (cat == 0) cur_cbp |= 0x100;
         else if (cat == 3) cur_cbp |= uint32_t(0x40) << (blk - 49);
         else if (cat == 5) nzmask |= uint64_t(0xF) << blk;

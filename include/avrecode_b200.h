@@ -164,6 +164,13 @@ int  avr_stage(avr_ctx* ctx, const avr_slice_desc* descs, int n_slices, const ui
 int  avr_launch(avr_ctx* ctx, int direction);
 int  avr_sync(avr_ctx* ctx);
 int  avr_collect(avr_ctx* ctx, avr_slice_result* results, const uint8_t** out, uint64_t* out_bytes);
+/* Per-class bin counts of the last launch, 8 words per slice in batch order (after avr_sync / avr_collect): what the
+ * reference prints as its per-CodingType bills (recode.cpp:635-655), as counts.  [0] macroblock-level syntax (mb_type,
+ * modes, ref_idx, mvd, cbp, qp_delta ...), [1] coded_block_flag, [2] significance map (sig + last), [3] coefficient level
+ * prefixes, [4] bypass bins of residuals (signs, escapes), [5] bits of the nnz side channel (model-only bins, recode.cpp:
+ * 844-930; not part of n_bins), [6] intra prediction modes, [7] end_of_slice (one per macroblock).  [0]+[1]+[2]+[3]+[4]+[6]+[7] = n_bins. */
+#define AVR_HIST_CLASSES 8
+int  avr_collect_hist(avr_ctx* ctx, uint32_t* hist, int n_slices);
 int  avr_last_kernel_ms(avr_ctx* ctx, float* ms);
 int  avr_launch_count(avr_ctx* ctx, uint64_t* n_launches); /* kernels launched by this context so far */
 int  avr_flush_l2(avr_ctx* ctx);                           /* bench hygiene: write > L2-size scratch */

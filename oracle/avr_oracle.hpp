@@ -17,6 +17,7 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <map>
+#include <memory>
 #include <tuple>
 #include <vector>
 #include <stdexcept>
@@ -333,6 +334,9 @@ class Model {
   int nonzeros_observed = 0, sub_mb_cat = -1, sub_mb_size = -1, sub_mb_is_dc = 0, sub_mb_chroma422 = 0;
   FrameBuf frames[2];
   int cur = 0;
+  typedef std::map<ModelKey, Estimator> Estimators;
+  Estimators* est = &estimators_;   // wide slices (not in the reference) switch between several sets; the geometry is shared
+  void use_own_estimators() { est = &estimators_; }
 
   void reset_all() {  // a brand-new h264_model (chunk mode: one per slice)
     estimators_.clear(); frames[0] = FrameBuf(); frames[1] = FrameBuf(); cur = 0; coding_type = CT_UNKNOWN;
@@ -378,12 +382,12 @@ class Model {
   }
   // recode.cpp:816-820 -- divide first, then multiply
   uint64_t probability(uint64_t range, const ModelKey& k) {
-    Estimator& e = estimators_[k];
+    Estimator& e = (*est)[k];
     return (range / uint64_t(e.pos + e.neg)) * uint64_t(e.pos);
   }
   // recode.cpp:1030-1047
   void update(int symbol, const ModelKey& k) {
-    Estimator& e = estimators_[k];
+    Estimator& e = (*est)[k];
     if (FILE* tf = trace_file())  // same columns as oracle/_ref/recode_ref_trace: type, key identity, ints, symbol, counters
       fprintf(tf, "%d %d %d %d %d %d %d\n", int(coding_type), std::get<0>(k) * 4096 + std::get<1>(k), std::get<2>(k), std::get<3>(k), symbol, e.pos, e.neg);
     if (symbol) e.pos++; else e.neg++;
@@ -468,7 +472,7 @@ class Model {
   }
 
  private:
-  std::map<ModelKey, Estimator> estimators_;
+  Estimators estimators_;
 };
 
 
@@ -613,6 +617,180 @@ class DecompressIO {
   CabacEncoder cabac_;
   std::vector<uint8_t>* out_;
   int stored_nnz_ = 0;
+  bool finished_ = false;
+};
+
+// ---------------------------------------------------------------------------------------------
+// Wide slices -- avrecode-b200's own chunked-mode format, NO reference counterpart (include/avrecode_b200.h,
+// avr_slice_desc.n_streams).  Restated here from the format's definition, with the per-bin primitives above:
+//   * a slice is coded as K range-coder streams with K estimator sets; macroblock row r goes to stream
+//     (r - first row of the slice) mod K.  Everything else of the model -- the nnz planes, the significance
+//     tracking -- is the slice's, shared by the streams (a block's neighbours may sit in another stream's row);
+//   * the first bin of mb_qp_delta of the FIRST macroblock of a row is modelled with the estimator of ctxIdx 60
+//     whatever its CABAC context is (60 or 61: "the previous macroblock in decoding order had a non-zero
+//     mb_qp_delta" is not known to a decoder that starts the row before the row above is finished);
+//   * every stream ends with a terminate bin of value 1 that flushes its coder (arithmetic_code.h:128-144): the
+//     slice's own end_of_slice_flag in the stream of the last row, one extra model-coded bin in each other;
+//   * blob = u32 macroblocks | K x u32 stream bytes | the streams, little endian.
+// ---------------------------------------------------------------------------------------------
+inline void put_le32(std::vector<uint8_t>* o, uint32_t v) { for (int i = 0; i < 4; i++) o->push_back(uint8_t(v >> (8 * i))); }
+inline uint32_t get_le32(const uint8_t* p) { return uint32_t(p[0]) | uint32_t(p[1]) << 8 | uint32_t(p[2]) << 16 | uint32_t(p[3]) << 24; }
+
+class WideCompressIO {
+ public:
+  WideCompressIO(Model* m, int k, int first_row, const uint8_t* payload, int size, std::vector<uint8_t>* out, int tail_byte = 0)
+      : model_(m), k_(k), first_row_(first_row), out_(out), ests_(size_t(k)), bytes_(size_t(k)) {
+    dec_.init(payload, size, tail_byte);
+    for (int j = 0; j < k; j++) encs_.emplace_back(new RecodedEncoder(&bytes_[size_t(j)]));
+  }
+  uint8_t state[1024];
+  uint64_t n_bins = 0;
+  int get(int ctx, int hint = 0) {
+    int s = dec_.get(&state[ctx]);
+    const bool row_qpd = (hint & 0xFF) == HK_QPD_NZ && model_->mb_x == 0;
+    symbol(s, KS_CTX, row_qpd ? 60 : ctx);
+    return s;
+  }
+  int bypass(int = 0) { int s = dec_.get_bypass(); symbol(s, KS_BYPASS, 0); return s; }
+  int terminate(int = 0) {
+    int s = dec_.get_terminate();
+    symbol(s, KS_TERMINATE, 0);
+    if (s) {   // the other streams end with a terminate bin of their own; then the blob
+      const int last = cur_;
+      for (int j = 0; j < k_; j++) if (j != last) { select(j); execute(1, KS_TERMINATE, 0); }
+      finished_ = true;
+    }
+    return s;
+  }
+  void mb_xy(int x, int y) { model_->mb_x = x; model_->mb_y = y; mbs_++; select((y - first_row_) % k_); }
+  void begin_block(int cat, int n, int max_coeff, int is_dc) {
+    model_->sub_mb_cat = cat; model_->blk = n; model_->sub_mb_size = max_coeff; model_->sub_mb_is_dc = is_dc; model_->sub_mb_chroma422 = 0;
+  }
+  void end_block() { model_->sub_mb_cat = -1; model_->blk = -1; model_->sub_mb_size = -1; model_->sub_mb_is_dc = 0; }
+  void begin_sigmap() { model_->begin_sigmap(); queueing_ = true; }
+  void end_sigmap() {   // as CompressIO::end_sigmap, into the current stream
+    model_->end_sigmap();
+    queueing_ = false;
+    model_->finished_queueing([&](const ModelKey& k, int* bit) {
+      encs_[size_t(cur_)]->put(*bit, model_->probability(encs_[size_t(cur_)]->range(), k));
+      model_->update(*bit, k);
+    });
+    model_->reset_sig_tracking();
+    for (const Queued& q : queue_) execute(q.symbol, q.space, q.ctx);
+    queue_.clear();
+    model_->coding_type = CT_UNKNOWN;
+  }
+  bool finished() const { return finished_; }
+  void write_blob() {
+    put_le32(out_, uint32_t(mbs_));
+    for (int j = 0; j < k_; j++) put_le32(out_, uint32_t(bytes_[size_t(j)].size()));
+    for (int j = 0; j < k_; j++) out_->insert(out_->end(), bytes_[size_t(j)].begin(), bytes_[size_t(j)].end());
+    model_->use_own_estimators();
+  }
+
+ private:
+  struct Queued { int symbol, space, ctx; };
+  void select(int j) { cur_ = j; model_->est = &ests_[size_t(j)]; }
+  void symbol(int s, int space, int ctx) {
+    n_bins++;
+    if (queueing_ || !queue_.empty()) { queue_.push_back(Queued{s, space, ctx}); model_->update_state_tracking(s); }
+    else execute(s, space, ctx);
+  }
+  void execute(int s, int space, int ctx) {
+    RecodedEncoder& enc = *encs_[size_t(cur_)];
+    ModelKey k = model_->key_for_ctx(space, ctx);
+    if (model_->coding_type != CT_EOB) enc.put(s, model_->probability(enc.range(), k));
+    model_->update(s, k);
+    if (space == KS_TERMINATE && s) enc.finish();
+  }
+  Model* model_;
+  int k_, first_row_, cur_ = 0, mbs_ = 0;
+  CabacDecoder dec_;
+  std::vector<uint8_t>* out_;
+  std::vector<Model::Estimators> ests_;
+  std::vector<std::vector<uint8_t>> bytes_;
+  std::vector<std::unique_ptr<RecodedEncoder>> encs_;
+  std::vector<Queued> queue_;
+  bool queueing_ = false, finished_ = false;
+};
+
+// The inverse, serially: macroblock by macroblock in slice order, each row from its own stream.
+class WideDecompressIO {
+ public:
+  WideDecompressIO(Model* m, int k, int first_row, const uint8_t* blob, int size, std::vector<uint8_t>* out)
+      : model_(m), k_(k), first_row_(first_row), cabac_(out), out_(out), ests_(size_t(k)) {
+    if (size < 4 + 4 * k) throw Corrupt("wide blob header");
+    total_mbs_ = int(get_le32(blob));
+    size_t off = size_t(4 + 4 * k);
+    for (int j = 0; j < k; j++) {
+      const size_t n = get_le32(blob + 4 + 4 * j);
+      if (off + n > size_t(size)) throw Corrupt("wide blob sizes");
+      decs_.emplace_back(new RecodedDecoder(blob + off, blob + off + n));
+      off += n;
+    }
+    if (off != size_t(size)) throw Corrupt("wide blob sizes");
+  }
+  uint8_t state[1024];
+  uint64_t n_bins = 0;
+  int get(int ctx, int hint = 0) {
+    n_bins++;
+    const bool row_qpd = (hint & 0xFF) == HK_QPD_NZ && model_->mb_x == 0;
+    ModelKey k = model_->key_for_ctx(KS_CTX, row_qpd ? 60 : ctx);
+    int s;
+    if (model_->coding_type == CT_EOB) s = std::get<2>(k);
+    else s = dec().get(model_->probability(dec().range(), k));
+    cabac_.put(s, &state[ctx]);
+    model_->update(s, k);
+    return s;
+  }
+  int bypass(int = 0) {
+    n_bins++;
+    ModelKey k = model_->key_for_ctx(KS_BYPASS, 0);
+    int s = dec().get(model_->probability(dec().range(), k));
+    model_->update(s, k);
+    cabac_.put_bypass(s);
+    return s;
+  }
+  int terminate(int = 0) {
+    n_bins++;
+    ModelKey k = model_->key_for_ctx(KS_TERMINATE, 0);
+    int s = dec().get(model_->probability(dec().range(), k));
+    model_->update(s, k);
+    cabac_.put_terminate(s);
+    if (s) {
+      if (!out_->empty() && out_->back() == 0x80) out_->pop_back();
+      finished_ = mbs_ == total_mbs_;
+      model_->use_own_estimators();
+    }
+    return s;
+  }
+  void mb_xy(int x, int y) { model_->mb_x = x; model_->mb_y = y; mbs_++; cur_ = (y - first_row_) % k_; model_->est = &ests_[size_t(cur_)]; }
+  void begin_block(int cat, int n, int max_coeff, int is_dc) {
+    model_->sub_mb_cat = cat; model_->blk = n; model_->sub_mb_size = max_coeff; model_->sub_mb_is_dc = is_dc; model_->sub_mb_chroma422 = 0;
+  }
+  void end_block() { model_->sub_mb_cat = -1; model_->blk = -1; model_->sub_mb_size = -1; model_->sub_mb_is_dc = 0; }
+  void begin_sigmap() {   // as DecompressIO::begin_sigmap with mirror_compressor
+    model_->begin_sigmap();
+    MbMeta& m = model_->meta(); m.is_8x8 = m.is_8x8 || model_->sub_mb_size > 32;
+    model_->finished_queueing([&](const ModelKey& k, int* bit) {
+      *bit = dec().get(model_->probability(dec().range(), k));
+      model_->update(*bit, k);
+    });
+  }
+  void end_sigmap() {
+    model_->end_sigmap();
+    if (model_->sub_mb_size > 32) model_->meta().num_nonzeros[model_->blk] &= 63;
+  }
+  bool finished() const { return finished_; }
+
+ private:
+  RecodedDecoder& dec() { return *decs_[size_t(cur_)]; }
+  Model* model_;
+  int k_, first_row_, cur_ = 0, mbs_ = 0, total_mbs_ = 0;
+  CabacEncoder cabac_;
+  std::vector<uint8_t>* out_;
+  std::vector<Model::Estimators> ests_;
+  std::vector<std::unique_ptr<RecodedDecoder>> decs_;
   bool finished_ = false;
 };
 

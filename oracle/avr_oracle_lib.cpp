@@ -15,9 +15,12 @@ struct Session {  // one h264_model + the picture-level syntax tables, carried a
   PictureSyntax pic;
 };
 
-template <class IO, class Make>
+inline void finish_wide(WideCompressIO* io) { io->write_blob(); }
+inline void finish_wide(WideDecompressIO*) {}
+
+template <class IO, class WideIO, class Make, class MakeWide>
 int run_all(const avr_slice_desc* descs, int n, const uint8_t* in, uint64_t in_bytes, avr_slice_result* res,
-            uint8_t** out, uint64_t* out_bytes, Make make_io) {
+            uint8_t** out, uint64_t* out_bytes, Make make_io, MakeWide make_wide) {
   std::vector<uint8_t> all;
   std::unique_ptr<Session> s;
   for (int i = 0; i < n; i++) {
@@ -33,14 +36,26 @@ int run_all(const avr_slice_desc* descs, int n, const uint8_t* in, uint64_t in_b
     }
     if (d.flags & AVR_SLICE_SKIP) continue;  // model hooks only (recode.cpp:1139-1145): the frame flip above
     std::vector<uint8_t> bytes;
+    const int k_streams = d.n_streams & AVR_STREAMS_MASK;
     try {
-      IO io = make_io(&s->model, in + d.in_off, int(d.in_size), &bytes, (d.flags & AVR_SLICE_STOP_BYTE) ? 0x80 : 0);
-      SliceWalker<IO> w(&io, &s->pic, d);
-      r.n_mbs = uint32_t(w.run());
-      r.n_bins = io.n_bins;
-      r.status = io.finished() ? AVR_SLICE_OK : AVR_SLICE_CORRUPT;
+      if (k_streams >= 2) {   // a wide slice of the chunked format: K range-coder streams, row r in stream (r - first row) mod K
+        if (!(d.flags & AVR_SLICE_NEW_MODEL) || d.mb_width == 0) throw Corrupt("wide slice without a model of its own");
+        WideIO io = make_wide(&s->model, k_streams, int(d.first_mb / d.mb_width), in + d.in_off, int(d.in_size), &bytes,
+                              (d.flags & AVR_SLICE_STOP_BYTE) ? 0x80 : 0);
+        SliceWalker<WideIO> w(&io, &s->pic, d);
+        r.n_mbs = uint32_t(w.run());
+        r.n_bins = io.n_bins;
+        r.status = io.finished() ? AVR_SLICE_OK : AVR_SLICE_CORRUPT;
+        finish_wide(&io);
+      } else {
+        IO io = make_io(&s->model, in + d.in_off, int(d.in_size), &bytes, (d.flags & AVR_SLICE_STOP_BYTE) ? 0x80 : 0);
+        SliceWalker<IO> w(&io, &s->pic, d);
+        r.n_mbs = uint32_t(w.run());
+        r.n_bins = io.n_bins;
+        r.status = io.finished() ? AVR_SLICE_OK : AVR_SLICE_CORRUPT;
+      }
     } catch (const Unsupported&) { r.status = AVR_SLICE_UNSUPPORTED; }
-    catch (const std::exception&) { r.status = AVR_SLICE_CORRUPT; }
+    catch (const std::exception& ex) { if (getenv("AVR_ORACLE_DEBUG")) fprintf(stderr, "oracle: slice %d: %s\n", i, ex.what()); r.status = AVR_SLICE_CORRUPT; }
     if (r.status == AVR_SLICE_OK) { r.out_size = uint32_t(bytes.size()); all.insert(all.end(), bytes.begin(), bytes.end()); }
   }
   *out_bytes = all.size();
@@ -55,20 +70,22 @@ extern "C" {
 
 int avr_oracle_compress(const avr_slice_desc* descs, int n, const uint8_t* in, uint64_t in_bytes, avr_slice_result* res,
                         uint8_t** out, uint64_t* out_bytes) {
-  return run_all<CompressIO>(descs, n, in, in_bytes, res, out, out_bytes,
-                             [](Model* m, const uint8_t* p, int sz, std::vector<uint8_t>* o, int tail) { return CompressIO(m, p, sz, o, tail); });
+  return run_all<CompressIO, WideCompressIO>(descs, n, in, in_bytes, res, out, out_bytes,
+      [](Model* m, const uint8_t* p, int sz, std::vector<uint8_t>* o, int tail) { return CompressIO(m, p, sz, o, tail); },
+      [](Model* m, int k, int row, const uint8_t* p, int sz, std::vector<uint8_t>* o, int tail) { return WideCompressIO(m, k, row, p, sz, o, tail); });
 }
 
 // mirror_compressor = 1: the format as the reference COMPRESSOR defines it (SURVEY hazards H8/H9);
 // 0: bug-compatible with the stock reference decompressor.
 int avr_oracle_decompress(const avr_slice_desc* descs, int n, const uint8_t* in, uint64_t in_bytes, avr_slice_result* res,
                           uint8_t** out, uint64_t* out_bytes, int mirror_compressor) {
-  return run_all<DecompressIO>(descs, n, in, in_bytes, res, out, out_bytes,
-                               [mirror_compressor](Model* m, const uint8_t* p, int sz, std::vector<uint8_t>* o, int) {
-                                 DecompressIO io(m, p, sz, o);
-                                 io.mirror_compressor = mirror_compressor != 0;
-                                 return io;
-                               });
+  return run_all<DecompressIO, WideDecompressIO>(descs, n, in, in_bytes, res, out, out_bytes,
+      [mirror_compressor](Model* m, const uint8_t* p, int sz, std::vector<uint8_t>* o, int) {
+        DecompressIO io(m, p, sz, o);
+        io.mirror_compressor = mirror_compressor != 0;
+        return io;
+      },
+      [](Model* m, int k, int row, const uint8_t* p, int sz, std::vector<uint8_t>* o, int) { return WideDecompressIO(m, k, row, p, sz, o); });
 }
 
 void avr_oracle_free(void* p) { free(p); }

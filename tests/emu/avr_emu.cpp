@@ -11,6 +11,8 @@
 
 using namespace avr;
 
+static std::vector<uint32_t> g_hist;   // per-class bin counts of the last call
+
 template <class Dir>
 static int run(const avr_slice_desc* descs, int n, const uint8_t* in, uint64_t in_bytes, avr_slice_result* res,
                uint8_t** out, uint64_t* out_bytes) {
@@ -36,7 +38,8 @@ static int run(const avr_slice_desc* descs, int n, const uint8_t* in, uint64_t i
   BlockShared* sh = new BlockShared();
   fill_shared_tables(&sh->tab, 0, 1);
   std::vector<MbCtx> row(max_mbw);
-  JobArgs a{descs, ios.data(), in, arena.data(), res};
+  g_hist.assign(size_t(n) * 8, 0);
+  JobArgs a{descs, ios.data(), in, arena.data(), res, g_hist.data()};
   JobMem m;
   m.sh = sh; m.row = row.data(); m.cnt = counters.data();
   m.nnz0 = planes.data(); m.nnz1 = planes.data() + max_frame; m.nnz_frame_bytes = max_frame; m.max_mbw = uint32_t(max_mbw);
@@ -88,4 +91,9 @@ int avr_emu_decompress(const avr_slice_desc* descs, int n, const uint8_t* in, ui
   return run<Decompress>(descs, n, in, in_bytes, res, out, out_bytes);
 }
 void avr_emu_free(void* p) { free(p); }
+int avr_emu_last_hist(uint32_t* dst, int n_slices) {
+  if (size_t(n_slices) * 8 != g_hist.size()) return -1;
+  memcpy(dst, g_hist.data(), g_hist.size() * 4);
+  return 0;
+}
 }

@@ -207,12 +207,62 @@ def test_corpus_batch_equals_per_file(ctx):
     assert ctx.files_decompress([r for _, r in pairs]) == [d for d, _ in pairs]
 
 
-@pytest.mark.parametrize("resident", ["1", "0"], ids=["shared-estimators", "global-estimators"])
-def test_both_estimator_placements_equal_oracle(built, resident, monkeypatch):
-    """The kernel has two variants (estimators resident in shared memory / in the global workspace); the
-    heuristic picks by batch size, AVR_RESIDENT forces one.  Both must give the oracle's bytes."""
-    monkeypatch.setenv("AVR_RESIDENT", resident)
+def test_corpus_every_slice_pinned(built):
+    """BASELINE config 5 shape at a size the box generates in seconds: the first 64 clips of the bench corpus, a sixth of
+    their length (~900 slices), through the kernel variant a large corpus selects -- estimators in GLOBAL memory, forced
+    here by avr_config.resident = 0 -- and every slice's coded bytes against the ORACLE's, pinned per clip in
+    tests/golden/corpus_gate.json (tests/make_bench_gate.py).  Then the batch file calls on the same corpus."""
+    import hashlib, json, sys
+    sys.path.insert(0, ROOT)
+    import bench as B
+    with open(os.path.join(ROOT, "tests", "golden", "corpus_gate.json")) as f:
+        gate = json.load(f)["clips"]
+    specs = B.corpus_spec(64, frame_div=6)
+    clips = []
+    for path in B.gen_corpus(specs):
+        with open(path, "rb") as f:
+            clips.append(f.read())
+    assert [hashlib.sha256(c).hexdigest() for c in clips] == [g["stream_sha256"] for g in gate]
+    with A.Context(resident=0) as c:
+        descs, spans, offs, pieces = [], [], 0, []
+        for clip in clips:
+            ds = H.batch_descs(A.index_h264(clip), False)
+            for d in ds:
+                d.in_off += offs
+            spans.append((len(descs), len(descs) + len(ds)))
+            descs += ds
+            pad = (-len(clip)) % 16
+            pieces += [clip, bytes(pad)]
+            offs += len(clip) + pad
+        arena = b"".join(pieces)
+        assert len(descs) == sum(g["n_slices"] for g in gate) > 800
+        res, blob = c.compress(descs, arena)
+        assert all(r.status == 0 for r in res)
+        coded = H.slices_of(res, blob)
+        for (lo, hi), g in zip(spans, gate):
+            h = hashlib.sha256()
+            for sl in coded[lo:hi]:
+                h.update(len(sl).to_bytes(8, "little")); h.update(sl)
+            assert h.hexdigest() == g["coded_sha256"] and sum(r.n_bins for r in res[lo:hi]) == g["n_bins"]
+        r_d, b_d = c.decompress(H.coded_descs(descs, res), blob)
+        assert H.roundtrip_ok(descs, r_d, b_d, arena)
+        recs = c.files_compress(clips, A.MODE_SLICE)
+        assert c.files_decompress(recs) == clips
+    # a batch this big is a throughput job: no wide slices in its containers (avr_config.wide_batch_limit), while one
+    # clip on its own gets them; both decode to the same bytes
+    big = max(range(len(clips)), key=lambda i: len(clips[i]))
     with A.Context() as c:
+        alone = c.file_compress(clips[big], A.MODE_SLICE)
+        many = c.files_compress(clips, A.MODE_SLICE)
+        assert not any("streams" in b for r in many for b in recproto.parse(r)[1])
+        assert c.file_decompress(alone) == clips[big] == c.file_decompress(many[big])
+
+
+@pytest.mark.parametrize("resident", [1, 0], ids=["shared-estimators", "global-estimators"])
+def test_both_estimator_placements_equal_oracle(built, resident):
+    """The kernel has two variants (estimators resident in shared memory / in the global workspace); the library
+    picks per batch by estimated makespan, avr_config.resident forces one.  Both must give the oracle's bytes."""
+    with A.Context(resident=resident) as c:
         for kw in (dict(width=320, height=192, frames=3, seed=1, slices=2),
                    dict(width=352, height=288, frames=4, high=True, seed=3, p8x8=0.7, refs=2)):
             data = H.gen_stream(**kw)
@@ -236,9 +286,11 @@ WIDE = [
 
 
 @pytest.mark.parametrize("kw", WIDE, ids=lambda k: "seed%d" % k["seed"])
-def test_wide_slices_equal_emulation_and_round_trip(ctx, kw):
-    """The format is this library's own (no reference counterpart): the device must write the bytes of the
-    host emulation of the same code, walk the bins of the ordinary path, and round-trip exactly."""
+def test_wide_slices_equal_oracle_and_round_trip(ctx, kw):
+    """The format is this library's own (no reference counterpart).  Its definition is restated independently in the
+    oracle (oracle/avr_oracle.hpp: WideCompressIO / WideDecompressIO, serial, built from the oracle's own per-bin
+    primitives): the device must write exactly those bytes, walk the bins of the ordinary path, round-trip, and the
+    oracle must decode what the device wrote."""
     data = H.gen_stream(**kw)
     plain = H.batch_descs(A.index_h264(data), False)
     r_p, _ = ctx.compress(plain, data)
@@ -246,31 +298,30 @@ def test_wide_slices_equal_emulation_and_round_trip(ctx, kw):
     for i, d in enumerate(descs):
         d.n_streams = 0 if i % 3 == 2 else 2          # wide and ordinary slices in one batch
     res, blob = ctx.compress(descs, data)
-    r_e, b_e = H.emu_compress(descs, data)
-    assert [r.status for r in res] == [0] * len(descs)
-    assert H.slices_of(res, blob) == H.slices_of(r_e, b_e)
-    assert [(r.n_bins, r.n_mbs) for r in res] == [(r.n_bins, r.n_mbs) for r in r_p]
+    r_o, b_o = H.oracle_compress(descs, data)
+    assert [r.status for r in res] == [r.status for r in r_o] == [0] * len(descs)
+    assert H.slices_of(res, blob) == H.slices_of(r_o, b_o)
+    assert [(r.n_bins, r.n_mbs) for r in res] == [(r.n_bins, r.n_mbs) for r in r_p] == [(r.n_bins, r.n_mbs) for r in r_o]
     check_roundtrip(ctx, descs, data, res, blob)
-    # the emulation decodes what the device wrote
-    r_d, b_d = H.emu_decompress(H.coded_descs(descs, res), blob)
+    r_d, b_d = H.oracle_decompress(H.coded_descs(descs, res), blob)
     assert H.roundtrip_ok(descs, r_d, b_d, data)
 
 
-def test_wide_slices_in_the_container(ctx, monkeypatch):
+def test_wide_slices_in_the_container(built):
     data = H.gen_stream(width=640, height=368, frames=6, high=True, seed=41, kbps=6000)
-    monkeypatch.setenv("AVR_WIDE_STREAM_BYTES", "2048")
-    rec_w = ctx.file_compress(data, A.MODE_SLICE)
-    monkeypatch.setenv("AVR_WIDE_STREAM_BYTES", "0")
-    rec_0 = ctx.file_compress(data, A.MODE_SLICE)
-    monkeypatch.delenv("AVR_WIDE_STREAM_BYTES")
-    _, blocks_w = recproto.parse(rec_w)
-    _, blocks_0 = recproto.parse(rec_0)
-    assert any(b.get("streams") == 2 for b in blocks_w) and not any("streams" in b for b in blocks_0)
-    assert ctx.file_decompress(rec_w) == data and ctx.file_decompress(rec_0) == data
-    assert len(rec_w) < len(rec_0) * 1.02        # two models instead of one cost little
-    # file mode (the reference's format) never uses them
-    monkeypatch.setenv("AVR_WIDE_STREAM_BYTES", "2048")
-    assert not any("streams" in b for b in recproto.parse(ctx.file_compress(data, A.MODE_FILE))[1])
+    with A.Context(wide_stream_bytes=2048) as cw, A.Context(wide_stream_bytes=0) as c0:
+        rec_w = cw.file_compress(data, A.MODE_SLICE)
+        rec_0 = c0.file_compress(data, A.MODE_SLICE)
+        _, blocks_w = recproto.parse(rec_w)
+        _, blocks_0 = recproto.parse(rec_0)
+        assert any(b.get("streams") == 2 for b in blocks_w) and not any("streams" in b for b in blocks_0)
+        assert c0.file_decompress(rec_w) == data and cw.file_decompress(rec_0) == data
+        assert len(rec_w) < len(rec_0) * 1.02        # two models instead of one cost little
+        # file mode (the reference's format) never uses them
+        assert not any("streams" in b for b in recproto.parse(cw.file_compress(data, A.MODE_FILE))[1])
+    # a batch beyond avr_config.wide_batch_limit is a throughput job: no wide slices
+    with A.Context(wide_stream_bytes=2048, wide_batch_limit=3) as c:
+        assert not any("streams" in b for b in recproto.parse(c.file_compress(data, A.MODE_SLICE))[1])
 
 
 def test_wide_slice_errors(ctx):

@@ -225,3 +225,28 @@ def test_reference_arm_segments_tile_the_file(built):
     specs = B.corpus_spec(8)
     assert [s["seed"] for s in specs] == list(range(1000, 1008)) and {s["width"] for s in specs} == {1280, 1920}
     assert all(30 <= s["frames"] <= 120 and 5000 <= s["kbps"] <= 30000 for s in B.corpus_spec(256))
+
+
+@pytest.mark.parametrize("kw", [
+    dict(width=480, height=272, frames=6, slices=4, seed=2),
+    dict(width=640, height=368, frames=5, high=True, seed=3, ragged=True, slices=3),     # slices that start mid-row
+    dict(mbw=255, mbh=2, frames=2, seed=15, slices=2),                                  # fewer rows than streams
+    dict(width=480, height=272, frames=8, bpics=0.8, seed=17, refs=4, high=True, p8x8=0.8, pskip=0.5),
+], ids=lambda k: "seed%d" % k["seed"])
+def test_wide_format_restatement_equals_device_logic(built, kw):
+    """Wide slices have no reference counterpart: the oracle restates the format's DEFINITION serially with its own
+    per-bin primitives (WideCompressIO / WideDecompressIO), the device code (here: its host emulation) implements it
+    as a wavefront over rings.  Same bytes, and each decodes the other's output."""
+    data = H.gen_stream(**kw)
+    descs = H.batch_descs(A.index_h264(data), False)
+    for i, d in enumerate(descs):
+        d.n_streams = 0 if i % 3 == 2 else 2
+    r_e, b_e = H.emu_compress(descs, data)
+    r_o, b_o = H.oracle_compress(descs, data)
+    assert [r.status for r in r_o] == [0] * len(descs)
+    assert H.slices_of(r_e, b_e) == H.slices_of(r_o, b_o)
+    assert [(r.n_bins, r.n_mbs) for r in r_e] == [(r.n_bins, r.n_mbs) for r in r_o]
+    dd = H.coded_descs(descs, r_o)
+    for dec in (H.oracle_decompress, H.emu_decompress):
+        r_d, b_d = dec(dd, b_o)
+        assert H.roundtrip_ok(descs, r_d, b_d, data)

@@ -37,7 +37,7 @@ with A.Context() as ctx:
           (len(descs), pay, coded, bins, max(r.n_bins for r in res), ms_c, ms_d), flush=True)
     big = max(range(len(res)), key=lambda i: res[i].n_bins)
     for name, rr, ms in (("compress", res, ms_c), ("decompress", r_d, ms_d)):
-        w = rr[big].reserved
-        print("  longest slice, %s: parser waited for ring room %.1f ms, coder waited for entries %.1f ms (of ~%.1f ms at 1965 MHz)"
-              % (name, (w & 0xFFFF) * 65536 / 1.965e6, (w >> 16) * 65536 / 1.965e6, ms), flush=True)
+        w = [((rr[big].reserved >> (8 * i)) & 0xFF) * (1 << 22) / 1.965e6 for i in range(4)]   # units of 2^22 cycles
+        print("  longest slice, %s (~%.0f ms): waits in ms -- parser for ring room %.0f, warp behind it for entries %.0f, "
+              "estimator warp for record room %.0f, range-coder warp for records %.0f" % (name, ms, w[0], w[1], w[2], w[3]), flush=True)
     assert H.roundtrip_ok(descs, r_d, b_d, data)
