@@ -4,8 +4,8 @@ Python is only a thin ctypes binding over libavrecode_b200.so (include/avrecode_
 per-bin work runs in sm_100a CUDA kernels.  There is no CPU fallback: creating a Context without a
 CUDA device raises NoDeviceError."""
 from .api import (Context, NoDeviceError, AvrError, index_h264, slice_streams, probes, lib_path, load_library,
-                  MODE_FILE, MODE_SLICE)
+                  MODE_FILE, MODE_SLICE, MAX_STREAMS)
 from . import _abi
 
 __all__ = ["Context", "NoDeviceError", "AvrError", "index_h264", "slice_streams", "probes", "lib_path", "load_library",
-           "MODE_FILE", "MODE_SLICE", "_abi"]
+           "MODE_FILE", "MODE_SLICE", "MAX_STREAMS", "_abi"]

@@ -19,6 +19,7 @@ AVR_SLICE_SKIP = 0x80
 
 AVR_SLICE_OK, AVR_SLICE_UNSUPPORTED, AVR_SLICE_CORRUPT, AVR_SLICE_OVERFLOW = 0, 1, 2, 3
 AVR_MODE_FILE, AVR_MODE_SLICE = 0, 1
+AVR_MAX_STREAMS = 8          # include/avrecode_b200.h
 
 AVR_OK = 0
 AVR_ERR_NO_DEVICE, AVR_ERR_CUDA, AVR_ERR_ARG, AVR_ERR_NOMEM, AVR_ERR_FORMAT, AVR_ERR_STATE = -1, -2, -3, -4, -5, -6
@@ -57,7 +58,7 @@ class SliceResult(C.Structure):
 
 class Config(C.Structure):
     _fields_ = [("abi_version", C.c_int32), ("device", C.c_int32), ("blocks_per_sm", C.c_int32), ("wide_stream_bytes", C.c_int32),
-                ("resident", C.c_int32), ("wide_batch_limit", C.c_int32), ("reserved", C.c_int32 * 2)]
+                ("resident", C.c_int32), ("wide_batch_limit", C.c_int32), ("wide_max_streams", C.c_int32), ("reserved", C.c_int32 * 1)]
 
 
 class IndexEntry(C.Structure):

@@ -11,6 +11,7 @@ from . import _abi
 from ._abi import SliceDesc, SliceResult, Config, IndexEntry
 
 MODE_FILE, MODE_SLICE = _abi.AVR_MODE_FILE, _abi.AVR_MODE_SLICE
+MAX_STREAMS = _abi.AVR_MAX_STREAMS
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _lib = None
 
@@ -85,6 +86,16 @@ def _check(rc, what):
         raise AvrError(rc, what)
 
 
+def _string_at(ptr, n):
+    """ctypes.string_at for any size (it takes a C int: outputs of a corpus batch pass 2 GiB)."""
+    if not n:
+        return b""
+    addr = ptr.value if hasattr(ptr, "value") else ptr
+    if n < (1 << 31):
+        return C.string_at(addr, n)
+    return bytes((C.c_char * n).from_address(addr))
+
+
 def _buf(data):
     """-> (address, length, keepalive) for bytes / bytearray / numpy / torch (CPU) buffers."""
     if isinstance(data, (bytes, bytearray)):
@@ -141,12 +152,13 @@ def index_h264(data):
 class Context:
     """One CUDA device.  Raises NoDeviceError when there is none: no CPU fallback exists."""
 
-    def __init__(self, device=0, blocks_per_sm=0, wide_stream_bytes=-1, resident=-1, wide_batch_limit=-1):
+    def __init__(self, device=0, blocks_per_sm=0, wide_stream_bytes=-1, resident=-1, wide_batch_limit=-1, wide_max_streams=0):
         self._lib = load_library()
         cfg = Config()
         cfg.abi_version = self._lib.avr_abi_version()
         cfg.device, cfg.blocks_per_sm, cfg.wide_stream_bytes = device, blocks_per_sm, wide_stream_bytes
         cfg.resident, cfg.wide_batch_limit = resident, wide_batch_limit
+        cfg.wide_max_streams = wide_max_streams
         h = C.c_void_p()
         _check(self._lib.avr_create(C.byref(cfg), C.byref(h)), "avr_create")
         self._h = h
@@ -179,7 +191,7 @@ class Context:
         out = C.c_void_p()
         nout = C.c_uint64()
         _check(fn(self._h, arr, n, addr, nbytes, res, C.byref(out), C.byref(nout)), what)
-        blob = C.string_at(out, nout.value) if nout.value else b""
+        blob = _string_at(out, nout.value)
         return list(res), blob
 
     def compress(self, descs, data):
@@ -209,7 +221,7 @@ class Context:
         out = C.c_void_p()
         nout = C.c_uint64()
         _check(self._lib.avr_collect(self._h, res, C.byref(out), C.byref(nout)), "avr_collect")
-        blob = C.string_at(out, nout.value) if (copy and nout.value) else b""
+        blob = _string_at(out, nout.value) if copy else b""
         return list(res), blob
 
     def collect_hist(self):
@@ -238,7 +250,7 @@ class Context:
         out = C.c_void_p()
         nout = C.c_uint64()
         _check(self._lib.avr_file_compress(self._h, addr, n, mode, C.byref(out), C.byref(nout)), "avr_file_compress")
-        blob = C.string_at(out, nout.value)
+        blob = _string_at(out, nout.value)
         self._lib.avr_free(out)
         return blob
 
@@ -247,7 +259,7 @@ class Context:
         out = C.c_void_p()
         nout = C.c_uint64()
         _check(self._lib.avr_file_decompress(self._h, addr, n, C.byref(out), C.byref(nout)), "avr_file_decompress")
-        blob = C.string_at(out, nout.value)
+        blob = _string_at(out, nout.value)
         self._lib.avr_free(out)
         return blob
 
@@ -262,7 +274,7 @@ class Context:
         _check(fn(self._h, ptrs, sizes, n, *extra, outs, nouts), name)
         res = []
         for i in range(n):
-            res.append(C.string_at(outs[i], nouts[i]))
+            res.append(_string_at(outs[i], nouts[i]))
             self._lib.avr_free(outs[i])
         return res
 

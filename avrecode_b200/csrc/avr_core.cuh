@@ -537,7 +537,7 @@ enum : uint32_t {
   //   SP_QPD      first mb_qp_delta bin of a row: its CABAC context (60 + that bit) is only known to the
   //               re-encoder, which sees the rows in order; the bin value sits at SYM_BIT_SHIFT
   SYM_SPECIAL = 3u << 20, SP_ROW_END = 1u << 8, SP_QPD = 2u << 8,
-  WIDE_MAX = 2,          // most streams per wide slice: every stream's estimators are resident in shared memory
+  WIDE_MAX = AVR_MAX_STREAMS,   // most streams per wide slice (every stream is worked on by a thread block of its own)
   SYM_LEVEL = 1u << 30, LVL_BIT1 = 9, LVL_GCTX = 10, LVL_RUN = 19, LVL_TERM = 23, LVL_HAS_SIGN = 24, LVL_SIGN = 25,
   SYM_BLOCK = 1u << 29, BLK_NNZ = 8, BLK_MB8 = 15, BLK_HAS_LEFT = 16,
 };
@@ -548,13 +548,21 @@ AVR_DEV uint32_t lvl_entry(int ctx1, int b1, int gctx, int run, int term, int ha
 
 #if defined(__CUDACC__) && !defined(AVR_HOST_EMULATION)
 // release/acquire at block scope is all the ring needs (entries before the published index)
-AVR_DEV void ring_fence() { asm volatile("fence.acq_rel.cta;" ::: "memory"); }
+// ... at block scope; rings whose two ends are in DIFFERENT thread blocks (wide slices: control words and entries in
+// global memory) need device scope
+AVR_DEV void ring_fence(bool far = false) {
+  if (far) asm volatile("fence.acq_rel.gpu;" ::: "memory");
+  else asm volatile("fence.acq_rel.cta;" ::: "memory");
+}
 // Waits of the wide-slice kernel are long (a coder warp idles while the rows of the other streams are parsed, a
 // parser warp idles behind the row above), and a warp that polls flat out takes issue slots and shared-memory
 // cycles from the warps of its block that do the serial work: poll a few times, then sleep between polls.
 #define AVR_SYNCWARP_CORE() __syncwarp()
 #define AVR_BCAST_CORE(v) __shfl_sync(0xFFFFFFFFu, (v), 0)
 AVR_DEV void wide_backoff(uint32_t& polls) { if (++polls > 32) __nanosleep(polls > 256 ? 1000 : 100); }
+// No wait of this library lasts seconds unless something is wrong (a role of a wide slice that never got a block, a
+// protocol bug): rather than hang the device, give up the launch -- the host sees a CUDA error, not a dead GPU.
+AVR_DEV void wait_watchdog(long long t0) { if (clock64() - t0 > (1ll << 34)) __trap(); }
 struct RingCtl {
   uint32_t tail_pub, head_pub;
   uint32_t end_status, end_mbs, end_bins_lo, end_bins_hi;   // written by the parser before SYM_END
@@ -567,13 +575,13 @@ struct RecRing : RingCtl { uint32_t e[REC_ENTRIES]; };       // compress: estima
 AVR_DEV void ring_reset(RingCtl* r) { r->tail_pub = 0; r->head_pub = 0; r->prod_tail = 0; r->cons_head = 0; r->prod_wait = 0; r->cons_wait = 0; }
 // makes room for an entry of n words: publishes what is complete, waits for the consumer if the ring is full; returns
 // the tail value up to which the producer may go on without looking again.  One out-of-line copy (instruction cache).
-AVR_DEV_NOINLINE uint32_t ring_slow(RingCtl* r, uint32_t tail, uint32_t n, uint32_t cap) {
-  ring_fence();
+AVR_DEV_NOINLINE uint32_t ring_slow(RingCtl* r, uint32_t tail, uint32_t n, uint32_t cap, bool far) {
+  ring_fence(far);
   *reinterpret_cast<volatile uint32_t*>(&r->tail_pub) = tail;
   uint32_t head_seen = *reinterpret_cast<volatile uint32_t*>(&r->head_pub);
   if (tail + n - head_seen > cap) {
     const long long t0 = clock64();
-    do head_seen = *reinterpret_cast<volatile uint32_t*>(&r->head_pub); while (tail + n - head_seen > cap);
+    do { head_seen = *reinterpret_cast<volatile uint32_t*>(&r->head_pub); wait_watchdog(t0); } while (tail + n - head_seen > cap);
     r->prod_wait += uint32_t((clock64() - t0) >> 8);
   }
   const uint32_t a = head_seen + cap, b = tail + RING_PUBLISH;
@@ -584,7 +592,7 @@ AVR_DEV_NOINLINE uint32_t ring_slow(RingCtl* r, uint32_t tail, uint32_t n, uint3
 #include <vector>
 namespace avr {
 // host emulation: the parser runs a whole slice into an unbounded queue, then the coder drains it
-inline void ring_fence() {}
+inline void ring_fence(bool = false) {}
 #define AVR_SYNCWARP_CORE() ((void)0)
 #define AVR_BCAST_CORE(v) (v)
 struct RingShared {
@@ -620,32 +628,35 @@ struct RingReader {
   const uint32_t* ents;   // the ring's words when they are in shared memory
   uint32_t mask, head;
   bool patient;
-  AVR_DEV void init(RingShared* ring, bool long_waits = false) { r = ring; ents = ring->e; mask = RING_ENTRIES - 1; head = 0; patient = long_waits; }
-  AVR_DEV void init_rec(RecRing* ring, bool long_waits = false) { r = ring; ents = ring->e; mask = REC_ENTRIES - 1; head = 0; patient = long_waits; }
+  // patient: the other end is in another thread block (wide slices) -- long waits, device-scope fences
+  AVR_DEV void init(RingShared* ring) { r = ring; ents = ring->e; mask = RING_ENTRIES - 1; head = 0; patient = false; }
+  AVR_DEV void init_far(RingCtl* ring) { r = ring; ents = nullptr; mask = 0; head = 0; patient = true; }
+  AVR_DEV void init_rec(RecRing* ring) { r = ring; ents = ring->e; mask = REC_ENTRIES - 1; head = 0; patient = false; }
   AVR_DEV uint32_t wait_avail() {   // all lanes poll the same word: a broadcast, no divergence
     uint32_t tail = *reinterpret_cast<volatile uint32_t*>(&r->tail_pub);
     if (head == tail) {
       const long long t0 = clock64();
       uint32_t polls = 0;
-      while (head == (tail = *reinterpret_cast<volatile uint32_t*>(&r->tail_pub))) { if (patient) wide_backoff(polls); }
+      while (head == (tail = *reinterpret_cast<volatile uint32_t*>(&r->tail_pub))) { if (patient) wide_backoff(polls); wait_watchdog(t0); }
       const uint32_t w = uint32_t((clock64() - t0) >> 8);
       if ((threadIdx.x & 31) == 0) r->cons_wait += w;
     }
-    ring_fence();
+    ring_fence(patient);
     return tail - head;   // every entry that starts inside this count is complete
   }
   AVR_DEV void release(uint32_t n, int lane) {
     head += n;
     __syncwarp();
-    if (lane == 0) { ring_fence(); *reinterpret_cast<volatile uint32_t*>(&r->head_pub) = head; }
+    if (lane == 0) { ring_fence(patient); *reinterpret_cast<volatile uint32_t*>(&r->head_pub) = head; }
   }
 };
 #else
 struct RingReader {
   RingShared* r;
   size_t head;
-  void init(RingShared* ring, bool = false) { r = ring; head = 0; }
-  void init_rec(RingShared* ring, bool = false) { r = ring; head = 0; }
+  void init(RingShared* ring) { r = ring; head = 0; }
+  void init_far(RingShared* ring) { r = ring; head = 0; }
+  void init_rec(RingShared* ring) { r = ring; head = 0; }
   uint32_t wait_avail() { return uint32_t(r->e.size() - head); }
   void release(uint32_t n, int) { head += n; }
 };
@@ -683,7 +694,7 @@ struct RecWriter {     // producer side of the record ring, in registers (lane 0
   uint32_t tail, limit;
   AVR_DEV void init(RecRing* ring) { r = ring; tail = 0; limit = RING_PUBLISH; }
   AVR_DEV void put(uint32_t w) {
-    if (int32_t(limit - tail) < 1) limit = ring_slow(r, tail, 1, REC_ENTRIES);
+    if (int32_t(limit - tail) < 1) limit = ring_slow(r, tail, 1, REC_ENTRIES, false);
     r->e[tail & (REC_ENTRIES - 1)] = w;
     tail++;
   }
@@ -793,9 +804,10 @@ struct CoderCompress {     // the estimator warp (recode.cpp:1030-1047 + the mod
   // Drains a ring until SYM_END.  ALL lanes of the estimator warp call this.  far: nullptr = the ring's own shared-memory
   // entries; else (wide slices) the ring's entries are in global memory at `far`, staged through `stage`, so that this
   // warp may fall a good part of a macroblock row behind the parser and catch up while the parser feeds another stream.
-  AVR_DEV void run(RingShared* r, const uint32_t* far, uint32_t far_cap, bool patient, const SharedTables& t, uint16_t* cnt,
+  AVR_DEV void run(RingShared* r, RingCtl* far_ctl, const uint32_t* far, uint32_t far_cap, const SharedTables& t, uint16_t* cnt,
                    uint32_t* stage, int lane) {
-    RingReader q; q.init(r, patient);
+    RingReader q;
+    if (far_ctl) q.init_far(far_ctl); else q.init(r);
     for (;;) {
       WordSrc src;
       const uint32_t n = coder_fetch(q, far, far_cap, stage, lane, &src);
@@ -818,8 +830,8 @@ struct CoderCompress {     // the estimator warp (recode.cpp:1030-1047 + the mod
 struct RangeWarp {
   RangeEnc rc;
   AVR_DEV void begin(ByteSink* sink, uint8_t* dst, uint32_t cap) { rc.init(sink, dst, cap); }
-  AVR_DEV void run(RecRing* records, bool patient, const SharedTables& t, uint32_t* stage, int lane) {
-    RingReader q; q.init_rec(records, patient);
+  AVR_DEV void run(RecRing* records, const SharedTables& t, uint32_t* stage, int lane) {
+    RingReader q; q.init_rec(records);
     for (;;) {
       WordSrc src;
       const uint32_t n = coder_fetch(q, nullptr, 0, stage, lane, &src);
@@ -922,7 +934,7 @@ struct CoderDecompress {   // CABAC re-encoder (cabac_code.h:16-86; recode.cpp:1
   }
   // Ordinary slices: drains the shared-memory ring until SYM_END.  ALL lanes call this.
   AVR_DEV void run(RingShared* r, const SharedTables& t, U2* cstate, uint32_t* stage, int lane) {
-    RingReader q; q.init(r, false);
+    RingReader q; q.init(r);
     for (;;) {
       WordSrc src;
       const uint32_t n = coder_fetch(q, nullptr, 0, stage, lane, &src);
@@ -946,11 +958,11 @@ struct CoderDecompress {   // CABAC re-encoder (cabac_code.h:16-86; recode.cpp:1
   // macroblock rows j, j + K, ... and every row ends in SP_ROW_END.  ALL lanes of the warp call this: they
   // stage a batch of words with coalesced loads, lane 0 encodes the entries in it.  Leaves on the
   // first SYM_END and then drains the other rings so that their parser warps can finish.
-  AVR_DEV void run_wide(RingShared* rings, uint32_t n_rings, const uint32_t* far, uint32_t far_cap, const SharedTables& t, U2* cstate,
+  AVR_DEV void run_wide(RingCtl* rings, uint32_t n_rings, const uint32_t* far, uint32_t far_cap, const SharedTables& t, U2* cstate,
                         uint32_t* stage, int lane) {
     uint32_t cur = 0, qpd = 0;
     bool draining = false;
-    RingReader q; q.init(&rings[0], true);
+    RingReader q; q.init_far(&rings[0]);
     for (;;) {
       WordSrc src;
       const uint32_t n = coder_fetch(q, far ? far + size_t(cur) * far_cap : nullptr, far_cap, stage, lane, &src);
@@ -980,9 +992,6 @@ struct CoderDecompress {   // CABAC re-encoder (cabac_code.h:16-86; recode.cpp:1
       do { cur = cur + 1 == n_rings ? 0 : cur + 1; tries++; } while (draining && tries <= n_rings && rings[cur].cons_head == 0xFFFFFFFFu);
       if (draining && tries > n_rings) break;
       q.r = &rings[cur];
-#if defined(__CUDACC__) && !defined(AVR_HOST_EMULATION)
-      q.ents = rings[cur].e;
-#endif
       q.head = uint32_t(rings[cur].cons_head);
     }
   }
@@ -1007,9 +1016,10 @@ struct ResBins {
   AVR_DEV uint32_t cabac_bins() const { return cbf + sig + level + bypass + pred; }   // nnz bits are model-only bins
 };
 struct ParserHome {
-  RingShared* r;            // ring, producer side
-  uint32_t* ents;           //   the words: r->e, or (wide slices) a much longer ring in global memory
-  uint32_t* far_base;       //   wide compression: ring j lives at far_base + j * cap (null: the rings' own e[])
+  RingCtl* r;               // ring, producer side: its control words
+  uint32_t* ents;           //   its entries: the block's shared-memory ring, or (wide slices) a much longer one in global memory
+  uint32_t* far_base;       //   wide slices: ring j's entries live at far_base + j * cap, its control words at far_ctl[j]
+  RingCtl* far_ctl;
   uint32_t cap, tail, limit;
   const SharedTables* tab;
   U2* cstate;
@@ -1030,35 +1040,40 @@ AVR_DEV void home_add_bins(ParserHome* h, const ResBins& b) {
 }
 
 #if defined(__CUDACC__) && !defined(AVR_HOST_EMULATION)
-AVR_DEV void home_ring_init(ParserHome* h, RingShared* ring, uint32_t* far_entries, uint32_t far_cap) {
-  h->r = ring; h->tail = 0; h->limit = RING_PUBLISH;
-  h->ents = far_entries ? far_entries : ring->e;
-  h->cap = far_entries ? far_cap : uint32_t(RING_ENTRIES);
-  h->far_base = far_entries;
+// ordinary slices: the block's own ring.  Wide slices: ring `index` of the slice's rings in global memory.
+AVR_DEV void home_ring_init(ParserHome* h, RingShared* ring, RingCtl* far_ctl, uint32_t* far_entries, uint32_t far_cap, uint32_t index) {
+  h->tail = 0; h->limit = RING_PUBLISH;
+  h->far_base = far_entries; h->far_ctl = far_ctl;
+  if (far_ctl) { h->r = &far_ctl[index]; h->ents = far_entries + size_t(index) * far_cap; h->cap = far_cap; }
+  else { h->r = ring; h->ents = ring->e; h->cap = RING_ENTRIES; }
 }
 AVR_DEV void home_push(ParserHome* h, uint32_t e) {
   uint32_t tail = h->tail;
-  if (int32_t(h->limit - tail) < 1) h->limit = ring_slow(h->r, tail, 1, h->cap);
+  if (int32_t(h->limit - tail) < 1) h->limit = ring_slow(h->r, tail, 1, h->cap, h->far_ctl != nullptr);
   h->ents[tail & (h->cap - 1)] = e;
   h->tail = tail + 1;
 }
 AVR_DEV void home_publish(ParserHome* h) {
-  ring_fence();
+  ring_fence(h->far_ctl != nullptr);
   *reinterpret_cast<volatile uint32_t*>(&h->r->tail_pub) = h->tail;
 }
-AVR_DEV void home_switch_to(ParserHome* h, RingShared* next, uint32_t index) {   // wide compression: the next macroblock row goes to another ring
+AVR_DEV void home_switch_to(ParserHome* h, uint32_t index) {   // wide compression: the next macroblock row goes to another ring
   home_publish(h);
   h->r->prod_tail = h->tail;
+  RingCtl* next = &h->far_ctl[index];
   h->r = next;
-  h->ents = h->far_base ? h->far_base + size_t(index) * h->cap : next->e;
+  h->ents = h->far_base + size_t(index) * h->cap;
   h->tail = next->prod_tail;
-  h->limit = ring_slow(next, h->tail, ENTRY_MAX_WORDS, h->cap);
+  h->limit = ring_slow(next, h->tail, ENTRY_MAX_WORDS, h->cap, true);
 }
 #else
-inline void home_ring_init(ParserHome* h, RingShared* ring, uint32_t*, uint32_t) { h->r = ring; }
+inline void home_ring_init(ParserHome* h, RingShared* ring, RingCtl* far_ctl, uint32_t*, uint32_t, uint32_t index) {
+  h->far_ctl = far_ctl;
+  h->r = far_ctl ? &far_ctl[index] : ring;
+}
 inline void home_push(ParserHome* h, uint32_t e) { h->r->e.push_back(e); }
 inline void home_publish(ParserHome*) {}
-inline void home_switch_to(ParserHome* h, RingShared* next, uint32_t) { h->r = next; }
+inline void home_switch_to(ParserHome* h, uint32_t index) { h->r = &h->far_ctl[index]; }
 #endif
 
 // register copy of the ring's producer side, valid between enter() and leave()
@@ -1068,7 +1083,7 @@ struct RingWriter {
   uint32_t cap, tail, limit;
   AVR_DEV void enter(const ParserHome* h) { ents = h->ents; cap = h->cap; tail = h->tail; limit = h->limit; }
   AVR_DEV void leave(ParserHome* h) const { h->tail = tail; h->limit = limit; }
-  AVR_DEV void reserve(ParserHome* h, uint32_t n) { if (int32_t(limit - tail) < int32_t(n)) limit = ring_slow(h->r, tail, n, cap); }
+  AVR_DEV void reserve(ParserHome* h, uint32_t n) { if (int32_t(limit - tail) < int32_t(n)) limit = ring_slow(h->r, tail, n, cap, h->far_ctl != nullptr); }
   AVR_DEV void put(ParserHome*, uint32_t w) { ents[tail & (cap - 1)] = w; tail++; }
 #else
   void enter(const ParserHome*) {}
@@ -1088,11 +1103,11 @@ AVR_DEV void home_load(const ParserHome* h, CabacIn& c, ByteWindow& w) {
 }
 AVR_DEV void home_store(ParserHome* h, const CabacIn& c) { h->val = c.val; h->range = c.range; h->pos = c.pos; h->nbits = c.nbits; }
 struct HomeRing {   // the producer side of the ring, read in one go
-  RingShared* r; uint32_t* ents; uint32_t cap, tail, limit, n_bins;
-  AVR_DEV void load(const ParserHome* h) { r = h->r; ents = h->ents; cap = h->cap; tail = h->tail; limit = h->limit; n_bins = h->n_bins; }
+  RingCtl* r; uint32_t* ents; uint32_t cap, tail, limit, n_bins; bool far;
+  AVR_DEV void load(const ParserHome* h) { r = h->r; ents = h->ents; cap = h->cap; tail = h->tail; limit = h->limit; n_bins = h->n_bins; far = h->far_ctl != nullptr; }
   AVR_DEV void push_and_store(ParserHome* h, uint32_t e) {
 #if defined(__CUDACC__) && !defined(AVR_HOST_EMULATION)
-    if (int32_t(limit - tail) < 1) { limit = ring_slow(r, tail, 1, cap); h->limit = limit; }
+    if (int32_t(limit - tail) < 1) { limit = ring_slow(r, tail, 1, cap, far); h->limit = limit; }
     ents[tail & (cap - 1)] = e;
     h->tail = tail + 1;
 #else
@@ -1161,11 +1176,12 @@ struct Compress {
   CabacIn cabac;     // register copy
   RingWriter q;
   AVR_DEV void begin(ParserHome* home, const uint8_t* src, uint32_t n, uint8_t* window, uint32_t tail_byte, RingShared* ring,
-                     const SharedTables* tab, uint16_t* counters, U2* states, uint32_t* far_entries = nullptr, uint32_t far_cap = 0) {
+                     const SharedTables* tab, uint16_t* counters, U2* states, RingCtl* far_ctl = nullptr, uint32_t* far_entries = nullptr,
+                     uint32_t far_cap = 0, uint32_t far_index = 0) {
     h = home;
     in.attach(src, n, window, tail_byte);
     cstate = states; tabp = tab;
-    home_ring_init(h, ring, far_entries, far_cap);
+    home_ring_init(h, ring, far_ctl, far_entries, far_cap, far_index);
     h->tab = tab; h->cstate = states; h->cnt = counters; h->win = window; h->skew = in.skew; h->n_bins = 0;
     for (int i = 0; i < 8; i++) h->hist[i] = 0;
   }
@@ -1240,11 +1256,12 @@ struct Decompress {
   uint32_t byp_c;
   DivMagic byp_mg;
   AVR_DEV void begin(ParserHome* home, const uint8_t* src, uint32_t n, uint8_t* window, uint32_t, RingShared* ring,
-                     const SharedTables* tab, uint16_t* counters, U2* states, uint32_t* far_entries = nullptr, uint32_t far_cap = 0) {
+                     const SharedTables* tab, uint16_t* counters, U2* states, RingCtl* far_ctl = nullptr, uint32_t* far_entries = nullptr,
+                     uint32_t far_cap = 0, uint32_t far_index = 0) {
     h = home;
     in.attach(src, n, window, 0);
     cnt = counters; tabp = tab;
-    home_ring_init(h, ring, far_entries, far_cap);
+    home_ring_init(h, ring, far_ctl, far_entries, far_cap, far_index);
     h->tab = tab; h->cstate = states; h->cnt = counters; h->win = window; h->skew = in.skew; h->n_bins = 0;
     for (int i = 0; i < 8; i++) h->hist[i] = 0;
   }

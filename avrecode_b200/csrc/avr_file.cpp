@@ -115,6 +115,7 @@ bool parse_container(const uint8_t* p, size_t n, std::vector<Block>* blocks, std
 // a batch with more slices than avr_config.wide_batch_limit is a throughput job and gets none.
 extern "C" int avr_ctx_wide_stream_bytes(avr_ctx* c);
 extern "C" int avr_ctx_wide_batch_limit(avr_ctx* c);
+extern "C" int avr_ctx_wide_max_streams(avr_ctx* c);
 uint32_t wide_stream_bytes(avr_ctx* ctx, size_t n_batch_slices) {
   const int limit = ctx ? avr_ctx_wide_batch_limit(ctx) : 0;
   if (limit > 0 && n_batch_slices > size_t(limit)) return 0;
@@ -128,12 +129,12 @@ bool statically_unsupported(const avr_slice_desc& d) {
          d.mb_width < 1 || d.mb_height < 1 || uint64_t(d.mb_width) * d.mb_height > AVR_MAX_PICTURE_MBS ||
          d.first_mb >= uint32_t(d.mb_width) * d.mb_height;
 }
-uint8_t streams_for(const avr_slice_desc& d, uint32_t per_stream) {
+uint8_t streams_for(const avr_slice_desc& d, uint32_t per_stream, uint32_t max_streams) {
   if (per_stream == 0 || d.mb_width < 1 || d.mb_width > 256) return 0;
   uint32_t k = d.payload_size / per_stream;
   const uint32_t rows = d.first_mb / d.mb_width < d.mb_height ? d.mb_height - d.first_mb / d.mb_width : 1;
   if (k > rows) k = rows;
-  if (k > AVR_MAX_STREAMS) k = AVR_MAX_STREAMS;
+  if (k > max_streams) k = max_streams;
   return k >= 2 ? uint8_t(k) : uint8_t(0);
 }
 
@@ -175,9 +176,9 @@ extern "C" {
 
 void avr_free(void* p) { free(p); }
 
-int avr_slice_streams(const avr_slice_desc* desc) { return desc ? streams_for(*desc, wide_stream_bytes(nullptr, 0)) : 0; }
+int avr_slice_streams(const avr_slice_desc* desc) { return desc ? streams_for(*desc, wide_stream_bytes(nullptr, 0), AVR_DEFAULT_WIDE_STREAMS) : 0; }
 int avr_ctx_slice_streams(avr_ctx* ctx, const avr_slice_desc* desc, int n_batch_slices) {
-  return desc ? streams_for(*desc, wide_stream_bytes(ctx, size_t(n_batch_slices < 0 ? 0 : n_batch_slices))) : 0;
+  return desc ? streams_for(*desc, wide_stream_bytes(ctx, size_t(n_batch_slices < 0 ? 0 : n_batch_slices)), uint32_t(avr_ctx_wide_max_streams(ctx))) : 0;
 }
 
 // Shared driver of avr_file_compress / avr_files_compress: all CABAC slices of all files go to the
@@ -280,7 +281,7 @@ static int compress_many(avr_ctx* ctx, const uint8_t* const* files, const uint64
         }
         if (p.map.empty() || mode == AVR_MODE_SLICE) d.flags |= AVR_SLICE_NEW_MODEL;
         if (p.coded[i] == 2) { d.in_off = p.raw_off[i]; d.in_size = p.raw_size[i]; }
-        d.n_streams = p.coded[i] ? streams_for(d, per_stream) : 0;
+        d.n_streams = p.coded[i] ? streams_for(d, per_stream, uint32_t(avr_ctx_wide_max_streams(ctx))) : 0;
         descs.push_back(d);
         p.map.push_back(i);
       }

@@ -32,7 +32,7 @@ struct JobDesc {        // one block's work: slices [first, first + count) share
   uint32_t first_slice;
   uint32_t n_slices;
   uint32_t weight;      // host-side ordering key (input bytes)
-  uint32_t reserved;
+  uint32_t wide;        // 0: an ordinary job.  Else a role of the wide slice first_slice: bits 0..7 role + 1, bits 8.. its workspace slot
 };
 
 struct SliceIO {        // device-side view of one slice's buffers
@@ -49,9 +49,7 @@ struct BlockShared {
   alignas(16) uint8_t window[WIN_BYTES];
   U2 cstate[N_CTX_PAD];     // CABAC context states {state, rangeTabLPS row}
   WalkShared walk;          // left macroblock + per-macroblock scratch of the walker
-#if !defined(__CUDACC__) || defined(AVR_HOST_EMULATION)
-  uint32_t stage[RING_BATCH + 2 * ENTRY_MAX_WORDS];   // host emulation: the coder's view of a batch (the device reads the ring in place)
-#endif
+  uint32_t stage[RING_BATCH + 2 * ENTRY_MAX_WORDS];   // a batch of a wide slice's ring (global memory) staged for lane 0; host emulation: of any ring
   RecRing records;          // compress: estimator warp -> range-coder warp, one word per bin
 #if !defined(__CUDACC__) || defined(AVR_HOST_EMULATION)
   uint32_t stage2[RING_BATCH + 2 * ENTRY_MAX_WORDS];  // host emulation: the range-coder's view of a batch
@@ -142,8 +140,9 @@ struct Lane {               // what one parser warp works with
   WalkShared* walk;
   MbCtx* row;
   uint16_t* cnt;
-  uint32_t* far;            // wide decompression: this warp's symbol ring in global memory (else null)
-  uint32_t far_cap;
+  RingCtl* far_ctl;         // wide slices: the slice's rings in global memory (control words / entries), else null
+  uint32_t* far;
+  uint32_t far_cap, far_index;
   ParserHome* home;
 };
 
@@ -157,7 +156,8 @@ AVR_DEV void parser_begin(Walker<Dir>& wk, const Lane& ln, const uint8_t* src, u
   wk.ws = ln.walk;
   wk.use_planes = use_planes;
   wk.nnz_cur = nnz_cur; wk.nnz_prev = nnz_prev;
-  wk.dir.begin(ln.home, src, n, ln.window, (d.flags & AVR_SLICE_STOP_BYTE) ? 0x80u : 0u, ln.ring, ln.tab, ln.cnt, ln.cstate, ln.far, ln.far_cap);
+  wk.dir.begin(ln.home, src, n, ln.window, (d.flags & AVR_SLICE_STOP_BYTE) ? 0x80u : 0u, ln.ring, ln.tab, ln.cnt, ln.cstate, ln.far_ctl, ln.far,
+               ln.far_cap, ln.far_index);
   window_load_half(wk.dir.in, 0, lane);
   window_load_half(wk.dir.in, WIN_HALF, lane);
   AVR_SYNCWARP();
@@ -194,7 +194,7 @@ AVR_DEV void parser_run(Walker<Dir>& wk, int lane) {
   }
 }
 
-AVR_DEV void ring_end_record(RingShared* r, int status, uint32_t mbs, uint32_t bins_lo, uint32_t bins_hi) {
+AVR_DEV void ring_end_record(RingCtl* r, int status, uint32_t mbs, uint32_t bins_lo, uint32_t bins_hi) {
   r->end_status = uint32_t(status);
   r->end_mbs = mbs;
   r->end_bins_lo = bins_lo;
@@ -216,12 +216,11 @@ AVR_DEV void parser_end(Walker<Dir>& wk, int lane) {
     if (wk.wide_k && !Dir::kDecompress) {
       // Wide compression: every stream ends in a terminate bin, which flushes its range coder -- the
       // slice's own end_of_slice bin in the stream of the last row, one extra bin in each of the others.
-      RingShared* first = wk.rings;
-      ring_end_record(first, wk.status, wk.n_mbs, wk.n_bins_lo(), wk.n_bins_hi);
+      ring_end_record(&wk.dir.h->far_ctl[0], wk.status, wk.n_mbs, wk.n_bins_lo(), wk.n_bins_hi);
 #pragma unroll 1
       for (uint32_t j = 0; j < wk.wide_k; j++) {
         if (j == wk.cur_ring) continue;
-        home_switch_to(wk.dir.h, &wk.rings[j], j);
+        home_switch_to(wk.dir.h, j);
         if (wk.status == WALK_OK) home_push(wk.dir.h, CNT_TERM | 1u << SYM_BIT_SHIFT);
         home_push(wk.dir.h, SYM_END);
         home_publish(wk.dir.h);
@@ -231,17 +230,125 @@ AVR_DEV void parser_end(Walker<Dir>& wk, int lane) {
   AVR_SYNCWARP();
 }
 
+// ------------------------------------------------------------------------------------------------
+// Wide slices (container mode "avr-b200/slice" only; avr_slice_desc.n_streams = K >= 2).
+//
+// A slice that is much longer than the rest of its batch sets the time of the whole batch, because one
+// slice is one serial CABAC stream.  The CABAC side cannot be split, but OUR side of the format can: the
+// compressor writes macroblock row r into range-coder stream (r - first row) mod K, each stream with its
+// own estimators.  Decompression then runs K parsers as a wavefront -- the contexts of a macroblock
+// need its left and top neighbours only, so row r at column x waits for row r - 1 to be through column
+// x -- and one warp re-encodes the CABAC stream from the K rings in row order.  The single piece of
+// state that crosses a row boundary in decoding order, "previous macroblock had a non-zero mb_qp_delta",
+// is resolved by the re-encoder (SP_QPD / SP_ROW_END) and left out of the model (context 60).
+//
+// Blob layout (Block.cabac of a wide slice): u32 macroblocks | K x u32 stream bytes | streams.
+//
+// Every stream is worked on by a THREAD BLOCK of its own (its estimators fill half an SM's shared memory): a wide
+// slice is K + 1 ROLES that the persistent blocks of the job kernel take from the job queue like any other job --
+//   compress    role 0: the parser (CABAC decode + walk, feeds K rings)   role 1 + j: estimator + range-coder warps of stream j
+//   decompress  role 0: the CABAC re-encoder (drains K rings in row order) role 1 + j: the parser of stream j
+// The roles talk through global memory (WideCtl: ring control words, wavefront progress; the rings' entries; the
+// neighbour rows) with device-scope fences.  No deadlock: the roles of a slice are consecutive in the queue with the
+// one the others wait for last in line... first in line, jobs are handed out in order, and a block keeps its job until
+// it is done -- so when any role of a slice is running, all roles of every slice before it in the queue are, and the
+// first unfinished slice of the queue always has all of its roles running (the grid has at least K + 1 blocks).
+// ------------------------------------------------------------------------------------------------
+struct WideCtl {            // one per wide slice, global memory, zeroed by the host before the launch
+  RingCtl ring[WIDE_MAX];   // ring j carries the entries of stream j (its words: `far`)
+  uint32_t prog[WIDE_MAX];  // decompress: macroblocks of the picture (raster order) parser j has got past
+  uint32_t out_size[WIDE_MAX];
+  uint32_t hist[WIDE_MAX][8];   // per-class bin counts of each parser (HIST_*)
+  uint32_t abort_flag, overflow, roles_done, pad;
+};
+
+struct WideMem {            // where a wide slice keeps what its roles share (global memory)
+  WideCtl* ctl;
+  MbCtx* rows;              // decompress: [K][mb_width], row r in buffer r mod K
+  uint32_t* far;            // [K][far_cap] ring entries
+  uint32_t far_cap;
+};
+
+AVR_DEV uint32_t load_le32(const uint8_t* p) { return uint32_t(p[0]) | uint32_t(p[1]) << 8 | uint32_t(p[2]) << 16 | uint32_t(p[3]) << 24; }
+AVR_DEV void store_le32(uint8_t* p, uint32_t v) { p[0] = uint8_t(v); p[1] = uint8_t(v >> 8); p[2] = uint8_t(v >> 16); p[3] = uint8_t(v >> 24); }
+
+// what every role works out for itself from the descriptor (and, decompressing, the blob header)
+struct WideGeom {
+  uint32_t K, hdr, total_mbs, subcap;
+  int status;   // AVR_SLICE_OK or why the slice cannot be done (every role comes to the same verdict)
+};
+AVR_DEV WideGeom wide_geometry(const avr_slice_desc& d, const SliceIO& io, const uint8_t* blob, bool decompress, uint32_t max_mbw) {
+  WideGeom g;
+  g.K = d.n_streams & AVR_STREAMS_MASK; g.hdr = 4 + 4 * g.K; g.total_mbs = 0; g.subcap = 0; g.status = AVR_SLICE_OK;
+  const uint64_t picture_mbs = uint64_t(d.mb_width) * d.mb_height;
+  if (g.K < 2 || g.K > WIDE_MAX || picture_mbs < 1 || picture_mbs > AVR_MAX_PICTURE_MBS || d.mb_width > max_mbw) { g.status = AVR_SLICE_UNSUPPORTED; return g; }
+  if (decompress) {
+    bool ok = io.in_size >= g.hdr && d.first_mb < picture_mbs;
+    uint64_t sum = g.hdr;
+    if (ok) {
+      g.total_mbs = load_le32(blob);
+      for (uint32_t j = 0; j < g.K; j++) sum += load_le32(blob + 4 + 4 * j);
+      ok = sum == io.in_size && g.total_mbs >= 1 && g.total_mbs <= picture_mbs - d.first_mb;
+    }
+    if (!ok) g.status = AVR_SLICE_CORRUPT;
+  } else {
+    if (io.out_cap < g.hdr + 64 * g.K) g.status = AVR_SLICE_OVERFLOW;
+    else g.subcap = ((io.out_cap - g.hdr) / g.K) & ~15u;
+  }
+  return g;
+}
+
 template <class Dir>
-AVR_DEV void parser_role(const JobArgs& a, const JobMem& m, const avr_slice_desc& d, const SliceIO& io, int cur_frame, bool use_planes, int lane) {
+AVR_DEV void wide_walker(Walker<Dir>& wk, const WideMem& w, uint32_t K, uint32_t j) {
+  wk.wide_k = K;
+  wk.top_copy = Dir::kDecompress;   // the row above was written by another thread block
+  wk.rows_base = w.rows;
+  wk.prog_mine = &w.ctl->prog[j];
+  wk.prog_above = &w.ctl->prog[j == 0 ? K - 1 : j - 1];
+  wk.abort_flag = &w.ctl->abort_flag;
+}
+
+AVR_DEV void wide_result(const JobArgs& a, uint32_t s, const SliceIO& io, int status, uint32_t out_size, uint32_t mbs, uint64_t bins) {
+  avr_slice_result res;
+  res.out_off = io.out_off;
+  res.status = status;
+  res.out_size = status == AVR_SLICE_OK ? out_size : 0;
+  res.n_mbs = mbs;
+  res.reserved = 0;
+  res.n_bins = bins;
+  a.results[s] = res;
+}
+
+// How the calling block takes part in slice s.  An ordinary slice: all of it, through the block's own rings.  A wide
+// slice: ONE role of it (see above) -- the stages that are not this role's stay idle, the rings / rows / progress
+// counters are the slice's in global memory.  One code path (one inlined copy of the walker and of each coder) serves both.
+struct Unit {
+  bool parse, code;          // which stages run in this block
+  uint32_t K, j;             // wide: streams of the slice, the stream this role works on (0 = ordinary)
+  WideMem w;                 // wide: w.ctl != null
+  const uint8_t* src;        // parser input (payload / coded bytes of the stream)
+  uint32_t src_size;
+  uint8_t* dst;              // output bytes of the last stage
+  uint32_t dst_cap, total_mbs;
+  int esc_zeros;
+};
+
+template <class Dir>
+AVR_DEV void parser_role(const JobMem& m, const Unit& u, const avr_slice_desc& d, int cur_frame, bool use_planes, int lane) {
   Walker<Dir> wk;
   wk.wide_k = 0;
   wk.top_copy = false;
   Lane ln;
   ln.tab = &m.sh->tab; ln.ring = &m.sh->ring; ln.window = m.sh->window; ln.cstate = m.sh->cstate;
-  ln.walk = &m.sh->walk; ln.row = m.row; ln.cnt = m.cnt; ln.far = nullptr; ln.far_cap = 0; ln.home = &m.sh->phome;
-  parser_begin<Dir>(wk, ln, a.in_arena + io.in_off, io.in_size, d, cur_frame ? m.nnz1 : m.nnz0, cur_frame ? m.nnz0 : m.nnz1,
-                    use_planes, lane, 0, 0);
+  ln.walk = &m.sh->walk; ln.row = m.row; ln.cnt = m.cnt; ln.far_ctl = nullptr; ln.far = nullptr; ln.far_cap = 0; ln.far_index = 0; ln.home = &m.sh->phome;
+  if (u.w.ctl) {
+    wide_walker<Dir>(wk, u.w, u.K, u.j);
+    ln.far_ctl = u.w.ctl->ring; ln.far = u.w.far; ln.far_cap = u.w.far_cap; ln.far_index = u.j;
+    if (Dir::kDecompress) ln.row = u.w.rows + size_t(u.j) * d.mb_width;   // (compress walks in place: the block's own row)
+  }
+  parser_begin<Dir>(wk, ln, u.src, u.src_size, d, cur_frame ? m.nnz1 : m.nnz0, cur_frame ? m.nnz0 : m.nnz1, use_planes, lane, u.j, u.total_mbs);
   parser_run<Dir>(wk, lane);
+  if (u.w.ctl && lane == 0) for (int i = 0; i < 8; i++) u.w.ctl->hist[u.j][i] = m.sh->phome.hist[i];   // before the end of the ring is published
   parser_end<Dir>(wk, lane);
 }
 
@@ -263,6 +370,14 @@ AVR_DEV void write_hist(const JobArgs& a, uint32_t s, const ParserHome* homes, u
   h[HIST_MB] = uint32_t(n_bins) - (h[HIST_CBF] + h[HIST_SIG] + h[HIST_LEVEL] + h[HIST_BYPASS] + h[HIST_PRED] + h[HIST_TERM]);
   for (int i = 0; i < 8; i++) a.hist[size_t(s) * 8 + i] = h[i];
 }
+AVR_DEV void write_hist_rows(const JobArgs& a, uint32_t s, const volatile uint32_t (*rows)[8], uint32_t n_rows, uint32_t n_mbs, uint64_t n_bins) {
+  if (!a.hist) return;
+  uint32_t h[8];
+  for (int i = 0; i < 8; i++) { h[i] = 0; for (uint32_t j = 0; j < n_rows; j++) h[i] += rows[j][i]; }
+  h[HIST_TERM] = n_mbs;
+  h[HIST_MB] = uint32_t(n_bins) - (h[HIST_CBF] + h[HIST_SIG] + h[HIST_LEVEL] + h[HIST_BYPASS] + h[HIST_PRED] + h[HIST_TERM]);
+  for (int i = 0; i < 8; i++) a.hist[size_t(s) * 8 + i] = h[i];
+}
 AVR_DEV void write_result(const JobArgs& a, const JobMem& m, const SliceIO& io, uint32_t s, uint32_t out_bytes, bool overflowed, bool two_rings) {
   const volatile RingShared* r = &m.sh->ring;
   avr_slice_result res;
@@ -279,31 +394,111 @@ AVR_DEV void write_result(const JobArgs& a, const JobMem& m, const SliceIO& io, 
 }
 // decompress: the CABAC re-encoder, which owns the output bytes and the slice result; compress: the estimator warp
 template <class Dir>
-AVR_DEV void coder_role(const JobArgs& a, const JobMem& m, const SliceIO& io, uint32_t s, int lane) {
+AVR_DEV void coder_role(const JobArgs& a, const JobMem& m, const Unit& u, const SliceIO& io, uint32_t s, int lane) {
   typename Dir::Coder c;
   if constexpr (Dir::kDecompress) {
-    const uint8_t lay = a.descs[s].n_streams;   // put emulation-prevention bytes back (escaped slices, chunked mode)
-    c.begin(&m.sh->sink, a.out_arena + io.out_off, io.out_cap, (lay & AVR_SLICE_ESCAPED) ? int((lay >> AVR_ESC_ZEROS_SHIFT) & 3) : -1);
-    c.run(&m.sh->ring, m.sh->tab, m.sh->cstate, AVR_HOST_STAGE(m.sh->stage), lane);
-    if (lane == 0) write_result(a, m, io, s, c.out_bytes(), c.overflowed(), false);
+    c.begin(&m.sh->sink, u.dst, u.dst_cap, u.esc_zeros);
+    if (u.w.ctl) {
+      c.run_wide(u.w.ctl->ring, u.K, u.w.far, u.w.far_cap, m.sh->tab, m.sh->cstate, m.sh->stage, lane);
+      if (lane == 0) { u.w.ctl->out_size[0] = c.out_bytes(); if (c.overflowed()) u.w.ctl->overflow = 1; }
+    } else {
+      c.run(&m.sh->ring, m.sh->tab, m.sh->cstate, AVR_HOST_STAGE(m.sh->stage), lane);
+      if (lane == 0) write_result(a, m, io, s, c.out_bytes(), c.overflowed(), false);
+    }
   } else {
     c.begin(&m.sh->records);
-    c.run(&m.sh->ring, nullptr, 0, false, m.sh->tab, m.cnt, AVR_HOST_STAGE(m.sh->stage), lane);
+    c.run(&m.sh->ring, u.w.ctl ? &u.w.ctl->ring[u.j] : nullptr, u.w.ctl ? u.w.far + size_t(u.j) * u.w.far_cap : nullptr, u.w.far_cap,
+          m.sh->tab, m.cnt, m.sh->stage, lane);
   }
   AVR_SYNCWARP();
 }
-// compress: the range-coder warp, which owns the output bytes and the slice result
-AVR_DEV void range_role(const JobArgs& a, const JobMem& m, const SliceIO& io, uint32_t s, int lane) {
+// compress: the range-coder warp, which owns the output bytes and (ordinary slices) the slice result
+AVR_DEV void range_role(const JobArgs& a, const JobMem& m, const Unit& u, const SliceIO& io, uint32_t s, int lane) {
   RangeWarp c;
-  c.begin(&m.sh->sink, a.out_arena + io.out_off, io.out_cap);
-  c.run(&m.sh->records, false, m.sh->tab, AVR_HOST_STAGE(m.sh->stage2), lane);
-  if (lane == 0) write_result(a, m, io, s, c.out_bytes(), c.overflowed(), true);
+  c.begin(&m.sh->sink, u.dst, u.dst_cap);
+  c.run(&m.sh->records, m.sh->tab, AVR_HOST_STAGE(m.sh->stage2), lane);
+  if (lane == 0) {
+    if (u.w.ctl) { u.w.ctl->out_size[u.j] = c.out_bytes(); if (c.overflowed()) u.w.ctl->overflow = 1; }
+    else write_result(a, m, io, s, c.out_bytes(), c.overflowed(), true);
+  }
   AVR_SYNCWARP();
 }
 
-// Runs one job on the calling block.
+// What remains to be done for a wide slice once this block's role is through: compressing, the LAST role to finish moves
+// the K streams up against each other and writes the blob header and the result; decompressing, role 0 (the re-encoder,
+// which ends last by construction) writes the result.
 template <class Dir>
-AVR_DEV void run_job(const JobArgs& a, const JobDesc& job, const JobMem& m, int tid) {
+AVR_DEV void wide_finish(const JobArgs& a, const JobMem& m, const Unit& u, const WideGeom& g, const SliceIO& io, uint32_t s, uint32_t role, int tid) {
+  const int nthreads = AVR_THREADS_OF(Dir);
+  WideCtl* ctl = u.w.ctl;
+  const uint32_t K = u.K;
+  uint8_t* out = a.out_arena + io.out_off;
+  if constexpr (!Dir::kDecompress) {
+#if defined(__CUDACC__) && !defined(AVR_HOST_EMULATION)
+    if (tid == 0) { __threadfence(); m.sh->job = atomicAdd(&ctl->roles_done, 1u); }
+    AVR_SYNCBLOCK();
+    const bool last = m.sh->job == K;
+    AVR_SYNCBLOCK();
+    if (!last) return;
+    __threadfence();
+#else
+    (void)role;
+    if (++ctl->roles_done != K + 1) return;
+#endif
+    const volatile RingCtl* r0 = &ctl->ring[0];
+    int status = int(r0->end_status);
+    const uint32_t mbs = r0->end_mbs;
+    const uint64_t bins = uint64_t(r0->end_bins_lo) | uint64_t(r0->end_bins_hi) << 32;
+    if (status == AVR_SLICE_OK && *reinterpret_cast<volatile uint32_t*>(&ctl->overflow)) status = AVR_SLICE_OVERFLOW;
+    uint32_t out_size = 0;
+    if (status == AVR_SLICE_OK) {
+      uint32_t dst = g.hdr + *reinterpret_cast<volatile uint32_t*>(&ctl->out_size[0]);
+#pragma unroll 1
+      for (uint32_t j = 1; j < K; j++) {
+        const uint8_t* src = out + g.hdr + size_t(j) * g.subcap;
+        const uint32_t n = *reinterpret_cast<volatile uint32_t*>(&ctl->out_size[j]);
+#pragma unroll 1
+        for (uint32_t o = 0; o < n; o += uint32_t(nthreads)) {   // dst <= src: chunk by chunk, read before write
+          const uint32_t i = o + uint32_t(tid);
+          const uint8_t v = i < n ? reinterpret_cast<const volatile uint8_t*>(src)[i] : uint8_t(0);
+          AVR_SYNCBLOCK();
+          if (i < n) out[dst + i] = v;
+          AVR_SYNCBLOCK();
+        }
+        dst += n;
+      }
+      out_size = dst;
+      if (tid == 0) {
+        store_le32(out, mbs);
+        for (uint32_t j = 0; j < K; j++) store_le32(out + 4 + 4 * j, *reinterpret_cast<volatile uint32_t*>(&ctl->out_size[j]));
+      }
+    }
+    if (tid == 0) {
+      wide_result(a, s, io, status, out_size, mbs, bins);
+      write_hist_rows(a, s, ctl->hist, 1, mbs, bins);
+    }
+  } else {
+    if (role != 0 || tid != 0) return;
+    int status = AVR_SLICE_OK;
+    uint32_t mbs = 0;
+    uint64_t bins = 0;
+    for (uint32_t j = 0; j < K; j++) {
+      const volatile RingCtl* r = &ctl->ring[j];
+      if (status == AVR_SLICE_OK && r->end_status != AVR_SLICE_OK) status = int(r->end_status);
+      mbs += r->end_mbs;
+      bins += uint64_t(r->end_bins_lo) | uint64_t(r->end_bins_hi) << 32;
+    }
+    if (status == AVR_SLICE_OK && mbs != g.total_mbs) status = AVR_SLICE_CORRUPT;
+    if (status == AVR_SLICE_OK && ctl->overflow) status = AVR_SLICE_OVERFLOW;
+    wide_result(a, s, io, status, ctl->out_size[0], mbs, bins);
+    write_hist_rows(a, s, ctl->hist, K, mbs, bins);
+  }
+}
+
+// Runs one job on the calling block: the slices of a job share one model (one slice in chunked mode, a file in
+// reference-parity mode); wide != null: the job is role `role` of the wide slice job.first_slice.
+template <class Dir>
+AVR_DEV void run_job(const JobArgs& a, const JobDesc& job, const JobMem& m, const WideMem* wide, uint32_t role, int tid) {
   const int nthreads = AVR_THREADS_OF(Dir);
   const int lane = tid & (AVR_LANES - 1);
   FrameTags ft;
@@ -316,6 +511,37 @@ AVR_DEV void run_job(const JobArgs& a, const JobDesc& job, const JobMem& m, int 
   for (uint32_t s = job.first_slice; s < job.first_slice + job.n_slices; s++) {
     const avr_slice_desc d = a.descs[s];
     const SliceIO io = a.ios[s];
+    Unit u;
+    u.parse = u.code = true; u.K = 0; u.j = 0; u.w.ctl = nullptr; u.w.rows = nullptr; u.w.far = nullptr; u.w.far_cap = 0;
+    u.src = a.in_arena + io.in_off; u.src_size = io.in_size;
+    u.dst = a.out_arena + io.out_off; u.dst_cap = io.out_cap; u.total_mbs = 0;
+    u.esc_zeros = (Dir::kDecompress && (d.n_streams & AVR_SLICE_ESCAPED)) ? int((d.n_streams >> AVR_ESC_ZEROS_SHIFT) & 3) : -1;
+    WideGeom g;
+    g.status = AVR_SLICE_OK; g.K = 0; g.hdr = 0; g.total_mbs = 0; g.subcap = 0;
+    if (wide) {
+      g = wide_geometry(d, io, u.src, Dir::kDecompress, m.max_mbw);
+      if (g.status != AVR_SLICE_OK || role > g.K) {   // every role comes to the same verdict: role 0 reports, the others leave
+        if (g.status != AVR_SLICE_OK && role == 0 && tid == 0) {
+          wide_result(a, s, io, g.status, 0, 0, 0);
+          if (a.hist) for (int i = 0; i < 8; i++) a.hist[size_t(s) * 8 + i] = 0;
+        }
+        AVR_SYNCBLOCK();
+        return;
+      }
+      u.w = *wide; u.K = g.K; u.total_mbs = g.total_mbs;
+      // compress: role 0 parses, role 1 + j codes stream j.  decompress: role 0 re-encodes, role 1 + j parses stream j.
+      u.parse = Dir::kDecompress ? role >= 1 : role == 0;
+      u.code = !u.parse;
+      u.j = role >= 1 ? role - 1 : 0;
+      if (Dir::kDecompress) {
+        if (u.parse) {
+          uint32_t off = g.hdr;
+          for (uint32_t i = 0; i < u.j; i++) off += load_le32(u.src + 4 + 4 * i);
+          u.src_size = load_le32(u.src + 4 + 4 * u.j);
+          u.src += off;
+        }
+      } else if (u.code) { u.dst += g.hdr + size_t(u.j) * g.subcap; u.dst_cap = g.subcap; }
+    }
     const bool fresh = s == job.first_slice || (d.flags & AVR_SLICE_NEW_MODEL);
     const bool skip = (d.flags & AVR_SLICE_SKIP) != 0;   // frame_spec bookkeeping only
     const uint64_t picture_mbs = uint64_t(d.mb_width) * d.mb_height;   // Level 6.2 at most: frame_bytes cannot wrap
@@ -356,15 +582,15 @@ AVR_DEV void run_job(const JobArgs& a, const JobDesc& job, const JobMem& m, int 
     AVR_SYNCBLOCK();
     if (walk) {
 #if defined(__CUDACC__) && !defined(AVR_HOST_EMULATION)
-      if (tid < 32) parser_role<Dir>(a, m, d, io, ft.cur, use_planes, lane);
-      else if (tid < 64) coder_role<Dir>(a, m, io, s, lane);
-      else range_role(a, m, io, s, lane);
+      if (tid < 32) { if (u.parse) parser_role<Dir>(m, u, d, ft.cur, use_planes, lane); }
+      else if (tid < 64) { if (u.code) coder_role<Dir>(a, m, u, io, s, lane); }
+      else if (u.code) range_role(a, m, u, io, s, lane);
 #else
-      parser_role<Dir>(a, m, d, io, ft.cur, use_planes, lane);
-      coder_role<Dir>(a, m, io, s, lane);
-      if (!Dir::kDecompress) range_role(a, m, io, s, lane);
+      if (u.parse) parser_role<Dir>(m, u, d, ft.cur, use_planes, lane);
+      if (u.code) coder_role<Dir>(a, m, u, io, s, lane);
+      if (u.code && !Dir::kDecompress) range_role(a, m, u, io, s, lane);
 #endif
-    } else if (tid == 0) {
+    } else if (tid == 0 && (!wide || role == 0)) {
       avr_slice_result r;
       r.out_off = io.out_off; r.out_size = 0; r.n_mbs = 0; r.reserved = 0; r.n_bins = 0;
       r.status = usable ? AVR_SLICE_OK : (poisoned ? AVR_SLICE_CORRUPT : AVR_SLICE_UNSUPPORTED);
@@ -373,286 +599,70 @@ AVR_DEV void run_job(const JobArgs& a, const JobDesc& job, const JobMem& m, int 
       m.sh->final_status = uint32_t(r.status);
     }
     AVR_SYNCBLOCK();
+    if (wide) { if (walk) wide_finish<Dir>(a, m, u, g, io, s, role, tid); AVR_SYNCBLOCK(); return; }
     if (m.sh->final_status != AVR_SLICE_OK) poisoned = true;
   }
 }
 
-// ------------------------------------------------------------------------------------------------
-// Wide slices (container mode "avr-b200/slice" only; avr_slice_desc.n_streams = K >= 2).
-//
-// A slice that is much longer than the rest of its batch sets the time of the whole batch, because one
-// slice is one serial CABAC stream.  The CABAC side cannot be split, but OUR side of the format can: the
-// compressor writes macroblock row r into range-coder stream (r - first row) mod K, each stream with its
-// own estimators.  Decompression then runs K parser warps as a wavefront -- the contexts of a macroblock
-// need its left and top neighbours only, so row r at column x waits for row r - 1 to be through column
-// x -- and one warp re-encodes the CABAC stream from the K rings in row order.  The single piece of
-// state that crosses a row boundary in decoding order, "previous macroblock had a non-zero mb_qp_delta",
-// is resolved by the re-encoder (SP_QPD / SP_ROW_END) and left out of the model (context 60).
-//
-// Blob layout (Block.cabac of a wide slice): u32 macroblocks | K x u32 stream bytes | streams.
-// Block = 1 + WIDE_MAX warps.  compress: warp 0 parser, warps 1..K coders;  decompress: warp 0 CABAC
-// re-encoder, warps 1..K parsers.  Estimators: one set per stream, all in shared memory -- which is what
-// limits K to WIDE_MAX = 2 (2 x 96 KB); the neighbour rows and the long symbol rings are in the global workspace.
-// ------------------------------------------------------------------------------------------------
-#if defined(__CUDACC__) && !defined(AVR_HOST_EMULATION)
-#define AVR_WIDE_THREADS_OF(Dir) ((Dir::kDecompress) ? (WIDE_MAX + 1) * 32 : (2 * WIDE_MAX + 1) * 32)
-#else
-#define AVR_WIDE_THREADS_OF(Dir) 1
-#endif
-
-struct WideShared {
-  SharedTables tab;
-  RingShared ring[WIDE_MAX];
-  alignas(16) uint8_t window[WIDE_MAX][WIN_BYTES];
-  U2 cstate[N_CTX_PAD];
-  WalkShared walk[WIDE_MAX];
-  uint32_t prog[WIDE_MAX];       // decompress: wavefront progress of each parser warp
-  uint32_t abort_flag;
-  uint32_t out_size[WIDE_MAX];   // compress: bytes of each stream;  decompress: [0] = bytes of the slice
-  uint32_t overflow;
-  uint32_t job;
-  uint32_t stage[WIDE_MAX][144]; // the batch of ring words a coder warp is working on (decompress: [0] only)
-  RecRing records[WIDE_MAX];     // compress: estimator warp j -> range-coder warp j
-  ByteSink sink[WIDE_MAX];       // compress: one per range-coder warp; decompress: [0]
-  ParserHome phome[WIDE_MAX];    // one per parser warp (compress: [0])
-};
-
-struct WideMem {
-  WideShared* sh;
-  MbCtx* rows;      // [WIDE_MAX][max_mbw] (compress uses one): shared memory when they fit beside the estimators, else
-  bool rows_global; //   the global workspace -- slower: every publication fence then waits for the row stores
-  uint16_t* cnt;    // [WIDE_MAX][MODEL_COUNTERS_PAD], shared memory
-  uint32_t* far;    // [WIDE_MAX][far_cap] symbol rings of a decompression, global workspace: a parser warp may run a
-  uint32_t far_cap; //   whole macroblock row ahead of the re-encoder, far more than a shared-memory ring holds
-  uint32_t max_mbw;
-};
-
-AVR_DEV uint32_t load_le32(const uint8_t* p) { return uint32_t(p[0]) | uint32_t(p[1]) << 8 | uint32_t(p[2]) << 16 | uint32_t(p[3]) << 24; }
-AVR_DEV void store_le32(uint8_t* p, uint32_t v) { p[0] = uint8_t(v); p[1] = uint8_t(v >> 8); p[2] = uint8_t(v >> 16); p[3] = uint8_t(v >> 24); }
-
+#if !defined(__CUDACC__) || defined(AVR_HOST_EMULATION)
+// Host emulation of a wide slice: the roles one after the other (the decompression parsers round robin: a walker
+// runs until it has to wait for the row above), on one set of "block" state per role.
 template <class Dir>
-AVR_DEV void wide_fail(const JobArgs& a, uint32_t s, const SliceIO& io, int status, int tid) {
-  if (tid == 0) {
-    avr_slice_result r;
-    r.out_off = io.out_off; r.out_size = 0; r.n_mbs = 0; r.reserved = 0; r.n_bins = 0; r.status = status;
-    a.results[s] = r;
-  }
-  AVR_SYNCBLOCK();
-}
-
-template <class Dir>
-AVR_DEV void wide_lane(Lane& ln, const WideMem& m, uint32_t j, uint32_t mbw) {
-  WideShared* sh = m.sh;
-  ln.tab = &sh->tab; ln.ring = &sh->ring[j]; ln.window = sh->window[j]; ln.cstate = sh->cstate;
-  ln.walk = &sh->walk[j]; ln.row = m.rows + size_t(j) * mbw; ln.cnt = m.cnt + size_t(j) * MODEL_COUNTERS_PAD;
-  ln.far = m.far ? m.far + size_t(j) * m.far_cap : nullptr;   // compress: ring 0, the parser moves on from there
-  ln.far_cap = m.far ? m.far_cap : 0;
-  ln.home = &sh->phome[j];
-}
-
-template <class Dir>
-AVR_DEV void wide_walker(Walker<Dir>& wk, const WideMem& m, uint32_t K, uint32_t j) {
-  WideShared* sh = m.sh;
-  wk.wide_k = K;
-  wk.top_copy = m.rows_global;
-  wk.rings = sh->ring;
-  wk.rows_base = m.rows;
-  wk.prog_mine = &sh->prog[j];
-  wk.prog_above = &sh->prog[j == 0 ? K - 1 : j - 1];
-  wk.abort_flag = &sh->abort_flag;
-}
-
-template <class Dir>
-AVR_DEV void run_wide_job(const JobArgs& a, uint32_t s, const WideMem& m, int tid) {
-  const int nthreads = AVR_WIDE_THREADS_OF(Dir);
-  const int lane = tid & (AVR_LANES - 1);
-  WideShared* sh = m.sh;
+void emu_wide_slice(const JobArgs& a, uint32_t s, JobMem* mems, const WideMem& w) {
   const avr_slice_desc d = a.descs[s];
   const SliceIO io = a.ios[s];
-  const uint32_t K = d.n_streams & AVR_STREAMS_MASK;
-  const int esc_zeros = (Dir::kDecompress && (d.n_streams & AVR_SLICE_ESCAPED)) ? int((d.n_streams >> AVR_ESC_ZEROS_SHIFT) & 3) : -1;
-  (void)esc_zeros;
-  const uint32_t mbw = d.mb_width;
-  const uint32_t hdr = 4 + 4 * K;
-  if (K < 2 || K > WIDE_MAX || mbw < 1 || d.mb_height < 1 || mbw > m.max_mbw) { wide_fail<Dir>(a, s, io, AVR_SLICE_UNSUPPORTED, tid); return; }
   const uint8_t* blob = a.in_arena + io.in_off;
-  uint8_t* out = a.out_arena + io.out_off;
-  uint32_t total_mbs = 0;
-  uint32_t subcap = 0;
-  if (Dir::kDecompress) {
-    bool ok = io.in_size >= hdr;
-    uint64_t sum = hdr;
-    if (ok) {
-      total_mbs = load_le32(blob);
-      for (uint32_t j = 0; j < K; j++) sum += load_le32(blob + 4 + 4 * j);
-      const uint32_t mbs_left = uint32_t(d.mb_width) * d.mb_height - (d.first_mb < uint32_t(d.mb_width) * d.mb_height ? d.first_mb : 0);
-      ok = sum == io.in_size && total_mbs >= 1 && total_mbs <= mbs_left && d.first_mb < uint32_t(d.mb_width) * d.mb_height;
-    }
-    if (!ok) { wide_fail<Dir>(a, s, io, AVR_SLICE_CORRUPT, tid); return; }
-  } else {
-    if (io.out_cap < hdr + 64 * K) { wide_fail<Dir>(a, s, io, AVR_SLICE_OVERFLOW, tid); return; }
-    subcap = ((io.out_cap - hdr) / K) & ~15u;
+  const WideGeom g = wide_geometry(d, io, blob, Dir::kDecompress, mems[0].max_mbw);
+  if (g.status != AVR_SLICE_OK || !Dir::kDecompress) {
+    JobDesc job;
+    job.first_slice = s; job.n_slices = 1; job.weight = 0; job.wide = 1;
+    for (uint32_t role = 0; role <= (g.status == AVR_SLICE_OK ? g.K : 0u); role++) run_job<Dir>(a, job, mems[role], &w, role, 0);
+    return;
   }
-  init_contexts(sh->cstate, d, tid, nthreads);
-  fill_u32(reinterpret_cast<uint32_t*>(m.rows), (Dir::kDecompress ? K : 1u) * mbw * MBCTX_WORDS, 0, tid, nthreads);   // compress walks in place: one row
-  fill_u32(reinterpret_cast<uint32_t*>(m.cnt), K * (MODEL_COUNTERS_PAD / 2), EST_INIT * 0x10001u, tid, nthreads);
-  for (uint32_t j = uint32_t(tid); j < K; j += uint32_t(nthreads)) { ring_reset(&sh->ring[j]); ring_reset(&sh->records[j]); sh->prog[j] = d.first_mb; sh->out_size[j] = 0; }
-  if (tid == 0) { sh->abort_flag = 0; sh->overflow = 0; }
-  AVR_SYNCBLOCK();
-
-#if defined(__CUDACC__) && !defined(AVR_HOST_EMULATION)
-  const uint32_t warp = uint32_t(tid) >> 5;
-  if constexpr (!Dir::kDecompress) {
-    if (warp == 0) {
-      Walker<Dir> wk;
-      wide_walker<Dir>(wk, m, K, 0);
-      Lane ln;
-      wide_lane<Dir>(ln, m, 0, mbw);
-      parser_begin<Dir>(wk, ln, blob, io.in_size, d, nullptr, nullptr, false, lane, 0, 0);
-      parser_run<Dir>(wk, lane);
-      parser_end<Dir>(wk, lane);
-    } else if (warp <= K) {   // estimator warp of stream j
-      const uint32_t j = warp - 1;
-      typename Dir::Coder c;
-      c.begin(&sh->records[j]);
-      c.run(&sh->ring[j], m.far + size_t(j) * m.far_cap, m.far_cap, true, sh->tab, m.cnt + size_t(j) * MODEL_COUNTERS_PAD, sh->stage[j], lane);
-      AVR_SYNCWARP();   // the other lanes must not run ahead into the block barrier
-    } else if (warp <= 2 * K) {   // range-coder warp of stream j
-      const uint32_t j = warp - 1 - K;
-      RangeWarp c;
-      c.begin(&sh->sink[j], out + hdr + size_t(j) * subcap, subcap);
-      c.run(&sh->records[j], true, sh->tab, nullptr, lane);
-      if (lane == 0) {
-        sh->out_size[j] = c.out_bytes();
-        if (c.overflowed()) sh->overflow = 1;
-      }
-      AVR_SYNCWARP();
-    }
-  } else {
-    if (warp == 0) {
-      typename Dir::Coder c;
-      c.begin(&sh->sink[0], out, io.out_cap, esc_zeros);
-      c.run_wide(sh->ring, K, m.far, m.far_cap, sh->tab, sh->cstate, sh->stage[0], lane);
-      if (lane == 0) {
-        sh->out_size[0] = c.out_bytes();
-        if (c.overflowed()) sh->overflow = 1;
-      }
-      AVR_SYNCWARP();
-    } else if (warp <= K) {
-      const uint32_t j = warp - 1;
-      Walker<Dir> wk;
-      wide_walker<Dir>(wk, m, K, j);
-      Lane ln;
-      wide_lane<Dir>(ln, m, j, mbw);
-      uint32_t off = hdr;
-      for (uint32_t i = 0; i < j; i++) off += load_le32(blob + 4 + 4 * i);
-      parser_begin<Dir>(wk, ln, blob + off, load_le32(blob + 4 + 4 * j), d, nullptr, nullptr, false, lane, j, total_mbs);
-      parser_run<Dir>(wk, lane);
-      parser_end<Dir>(wk, lane);
-    }
-  }
-#else
-  if constexpr (!Dir::kDecompress) {
-    Walker<Dir> wk;
-    wide_walker<Dir>(wk, m, K, 0);
-    Lane ln;
-    wide_lane<Dir>(ln, m, 0, mbw);
-    parser_begin<Dir>(wk, ln, blob, io.in_size, d, nullptr, nullptr, false, lane, 0, 0);
-    parser_run<Dir>(wk, lane);
-    parser_end<Dir>(wk, lane);
-    for (uint32_t j = 0; j < K; j++) {
-      typename Dir::Coder c;
-      c.begin(&sh->records[j]);
-      c.run(&sh->ring[j], nullptr, 0, true, sh->tab, m.cnt + size_t(j) * MODEL_COUNTERS_PAD, sh->stage[j], lane);
-      RangeWarp rw;
-      rw.begin(&sh->sink[j], out + hdr + size_t(j) * subcap, subcap);
-      rw.run(&sh->records[j], true, sh->tab, sh->stage[j], lane);
-      sh->out_size[j] = rw.out_bytes();
-      if (rw.overflowed()) sh->overflow = 1;
-    }
-  } else {
+  if constexpr (Dir::kDecompress) {
+    const uint32_t K = g.K, mbw = d.mb_width;
     Walker<Dir>* wk = new Walker<Dir>[WIDE_MAX];
-    uint32_t off = hdr;
+    uint32_t off = g.hdr;
     for (uint32_t j = 0; j < K; j++) {
-      wide_walker<Dir>(wk[j], m, K, j);
+      const JobMem& m = mems[1 + j];
+      for (uint32_t i = 0; i < MODEL_COUNTERS_PAD; i++) m.cnt[i] = EST_INIT;
+      wide_walker<Dir>(wk[j], w, K, j);
       Lane ln;
-      wide_lane<Dir>(ln, m, j, mbw);
+      ln.tab = &m.sh->tab; ln.ring = &m.sh->ring; ln.window = m.sh->window; ln.cstate = m.sh->cstate; ln.walk = &m.sh->walk;
+      ln.row = w.rows + size_t(j) * mbw; ln.cnt = m.cnt; ln.home = &m.sh->phome;
+      ln.far_ctl = w.ctl->ring; ln.far = nullptr; ln.far_cap = 0; ln.far_index = j;
       const uint32_t sz = load_le32(blob + 4 + 4 * j);
-      parser_begin<Dir>(wk[j], ln, blob + off, sz, d, nullptr, nullptr, false, lane, j, total_mbs);
+      parser_begin<Dir>(wk[j], ln, blob + off, sz, d, nullptr, nullptr, false, 0, j, g.total_mbs);
       off += sz;
     }
-    for (bool busy = true; busy;) {   // round robin: a walker runs until it has to wait for the row above
+    for (bool busy = true; busy;) {
       busy = false;
       for (uint32_t j = 0; j < K; j++)
-        if (!wk[j].done) { parser_run<Dir>(wk[j], lane); busy = true; }
+        if (!wk[j].done) { parser_run<Dir>(wk[j], 0); busy = true; }
     }
-    for (uint32_t j = 0; j < K; j++) parser_end<Dir>(wk[j], lane);
+    for (uint32_t j = 0; j < K; j++) parser_end<Dir>(wk[j], 0);
     delete[] wk;
-    typename Dir::Coder c;
-    c.begin(&sh->sink[0], out, io.out_cap, esc_zeros);
-    c.run_wide(sh->ring, K, m.far, m.far_cap, sh->tab, sh->cstate, sh->stage[0], lane);
-    sh->out_size[0] = c.out_bytes();
-    if (c.overflowed()) sh->overflow = 1;
-  }
-#endif
-  AVR_SYNCBLOCK();
-
-  // result (and, compressing, the blob: header + the K streams moved up against each other)
-  int status;
-  uint32_t mbs = 0, out_size = 0;
-  uint64_t bins = 0;
-  if (!Dir::kDecompress) {
-    const volatile RingShared* r = &sh->ring[0];
-    status = int(r->end_status);
-    mbs = r->end_mbs;
-    bins = uint64_t(r->end_bins_lo) | uint64_t(r->end_bins_hi) << 32;
-    if (status == AVR_SLICE_OK && sh->overflow) status = AVR_SLICE_OVERFLOW;
-    if (status == AVR_SLICE_OK) {
-      uint32_t dst = hdr + sh->out_size[0];
-#pragma unroll 1
-      for (uint32_t j = 1; j < K; j++) {
-        const uint8_t* src = out + hdr + size_t(j) * subcap;
-        const uint32_t n = sh->out_size[j];
-#pragma unroll 1
-        for (uint32_t o = 0; o < n; o += uint32_t(nthreads)) {   // dst <= src: chunk by chunk, read before write
-          const uint32_t i = o + uint32_t(tid);
-          const uint8_t v = i < n ? src[i] : uint8_t(0);
-          AVR_SYNCBLOCK();
-          if (i < n) out[dst + i] = v;
-          AVR_SYNCBLOCK();
-        }
-        dst += n;
-      }
-      out_size = dst;
-      if (tid == 0) {
-        store_le32(out, mbs);
-        for (uint32_t j = 0; j < K; j++) store_le32(out + 4 + 4 * j, sh->out_size[j]);
-      }
-    }
-  } else {
-    status = AVR_SLICE_OK;
+    BlockShared* sh = mems[0].sh;
+    init_contexts(sh->cstate, d, 0, 1);
+    CoderDecompress c;
+    c.begin(&sh->sink, a.out_arena + io.out_off, io.out_cap, (d.n_streams & AVR_SLICE_ESCAPED) ? int((d.n_streams >> AVR_ESC_ZEROS_SHIFT) & 3) : -1);
+    c.run_wide(w.ctl->ring, K, nullptr, 0, sh->tab, sh->cstate, sh->stage, 0);
+    int status = AVR_SLICE_OK;
+    uint32_t mbs = 0;
+    uint64_t bins = 0;
     for (uint32_t j = 0; j < K; j++) {
-      const volatile RingShared* r = &sh->ring[j];
+      const RingCtl* r = &w.ctl->ring[j];
       if (status == AVR_SLICE_OK && r->end_status != AVR_SLICE_OK) status = int(r->end_status);
       mbs += r->end_mbs;
       bins += uint64_t(r->end_bins_lo) | uint64_t(r->end_bins_hi) << 32;
     }
-    if (status == AVR_SLICE_OK && mbs != total_mbs) status = AVR_SLICE_CORRUPT;
-    if (status == AVR_SLICE_OK && sh->overflow) status = AVR_SLICE_OVERFLOW;
-    out_size = sh->out_size[0];
+    if (status == AVR_SLICE_OK && mbs != g.total_mbs) status = AVR_SLICE_CORRUPT;
+    if (status == AVR_SLICE_OK && c.overflowed()) status = AVR_SLICE_OVERFLOW;
+    for (uint32_t j = 0; j < K; j++) for (int i = 0; i < 8; i++) w.ctl->hist[j][i] = mems[1 + j].sh->phome.hist[i];
+    wide_result(a, s, io, status, c.out_bytes(), mbs, bins);
+    write_hist_rows(a, s, w.ctl->hist, K, mbs, bins);
   }
-  if (tid == 0) {
-    avr_slice_result res;
-    res.out_off = io.out_off;
-    res.status = status;
-    res.out_size = status == AVR_SLICE_OK ? out_size : 0;
-    res.n_mbs = mbs;
-    res.reserved = 0;
-    res.n_bins = bins;
-    a.results[s] = res;
-    write_hist(a, s, sh->phome, Dir::kDecompress ? K : 1u, mbs, bins);
-  }
-  AVR_SYNCBLOCK();
 }
+#endif
 
 }  // namespace avr

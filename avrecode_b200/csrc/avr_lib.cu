@@ -26,9 +26,14 @@ struct KernelArgs {
   uint64_t work_stride;     // bytes of workspace per resident block
   uint32_t nnz_frame_bytes; // bytes of one nnz plane inside a slot
   uint32_t max_mbw;         // neighbour-row entries per block
+  uint8_t* wide_ws;         // per wide slice: WideCtl | neighbour rows [WIDE_MAX][wide_mbw] | ring entries [WIDE_MAX][far_cap]
+  uint64_t wide_stride;
+  uint32_t wide_mbw, far_cap;
 };
 
-size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+__host__ __device__ inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+__host__ __device__ inline size_t wide_ctl_bytes() { return align_up(sizeof(WideCtl), 256); }
+__host__ __device__ inline size_t wide_rows_bytes(uint32_t mbw) { return align_up(size_t(WIDE_MAX) * mbw * sizeof(MbCtx), 256); }
 size_t row_bytes(uint32_t max_mbw) { return align_up(size_t(max_mbw) * sizeof(MbCtx), 16); }
 size_t counters_bytes() { return align_up(size_t(MODEL_COUNTERS_PAD) * 2, 256); }
 size_t smem_bytes(uint32_t max_mbw, bool resident) {
@@ -60,60 +65,21 @@ __global__ void __launch_bounds__(AVR_THREADS_OF(Dir), RESIDENT ? 2 : 8) avr_job
     const uint32_t j = m.sh->job;
     __syncthreads();
     if (j >= k.n_jobs) break;
-    run_job<Dir>(k.a, k.jobs[j], m, tid);
-  }
-  // When this grid was launched as the programmatic dependent of the wide-slice kernel (see avr_launch), it must not
-  // complete before that one has: later work in the stream is ordered after THIS grid only.  No-op otherwise.
-  asm volatile("griddepcontrol.wait;" ::: "memory");
-}
-
-// Wide slices (avr_job.cuh, run_wide_job): one slice per block of 1 + WIDE_MAX warps.
-// Shared memory: WideShared | WIDE_MAX estimator sets.  Workspace slot: MbCtx rows[WIDE_MAX][max_mbw] |
-// WIDE_MAX symbol rings of far_cap entries (decompression).
-struct WideKernelArgs {
-  JobArgs a;
-  const uint32_t* slices;   // the wide slices of the batch, longest first
-  uint32_t n_jobs;
-  uint32_t* counter;
-  uint8_t* workspace;
-  uint64_t work_stride;
-  uint32_t max_mbw;
-  uint32_t far_cap;
-  uint32_t rows_in_shared;  // the neighbour rows follow the estimators in shared memory (else: start of the workspace slot)
-};
-enum : uint32_t { WIDE_FAR_CAP = 1u << 16 };
-size_t wide_rows_bytes(uint32_t max_mbw) { return align_up(size_t(WIDE_MAX) * max_mbw * sizeof(MbCtx), 256); }
-size_t wide_smem_bytes() { return align_up(sizeof(WideShared), 16) + align_up(size_t(WIDE_MAX) * MODEL_COUNTERS_PAD * 2, 16); }
-
-template <class Dir>
-__global__ void __launch_bounds__(AVR_WIDE_THREADS_OF(Dir), 1) avr_wide_kernel(WideKernelArgs k) {
-  extern __shared__ __align__(16) uint8_t smem[];
-  WideMem m;
-  m.sh = reinterpret_cast<WideShared*>(smem);
-  m.cnt = reinterpret_cast<uint16_t*>(smem + (sizeof(WideShared) + 15) / 16 * 16);
-  uint8_t* slot = k.workspace + uint64_t(blockIdx.x) * k.work_stride;
-  m.rows = k.rows_in_shared ? reinterpret_cast<MbCtx*>(smem + (sizeof(WideShared) + 15) / 16 * 16 + (size_t(WIDE_MAX) * MODEL_COUNTERS_PAD * 2 + 15) / 16 * 16)
-                            : reinterpret_cast<MbCtx*>(slot);
-  m.rows_global = !k.rows_in_shared;
-  m.far = reinterpret_cast<uint32_t*>(slot + (size_t(WIDE_MAX) * k.max_mbw * sizeof(MbCtx) + 255) / 256 * 256);
-  m.far_cap = k.far_cap;
-  m.max_mbw = k.max_mbw;
-  const int tid = threadIdx.x;
-  // every block of this grid is now resident: the ordinary kernel, queued behind it as a programmatic dependent,
-  // may start filling the remaining SMs (launched the other way round its blocks would take the shared memory
-  // of every SM and the wide blocks -- a whole SM each -- would wait for them)
-  asm volatile("griddepcontrol.launch_dependents;");
-  fill_shared_tables(&m.sh->tab, tid, AVR_WIDE_THREADS_OF(Dir));
-  __syncthreads();
-  for (;;) {
-    if (tid == 0) m.sh->job = atomicAdd(k.counter, 1u);
-    __syncthreads();
-    const uint32_t j = m.sh->job;
-    __syncthreads();
-    if (j >= k.n_jobs) break;
-    run_wide_job<Dir>(k.a, k.slices[j], m, tid);
+    const JobDesc job = k.jobs[j];
+    WideMem w;
+    w.ctl = nullptr;
+    if (job.wide) {   // one role of a wide slice (avr_job.cuh, "Wide slices")
+      uint8_t* ws = k.wide_ws + uint64_t(job.wide >> 8) * k.wide_stride;
+      w.ctl = reinterpret_cast<WideCtl*>(ws);
+      w.rows = reinterpret_cast<MbCtx*>(ws + wide_ctl_bytes());
+      w.far = reinterpret_cast<uint32_t*>(ws + wide_ctl_bytes() + wide_rows_bytes(k.wide_mbw));
+      w.far_cap = k.far_cap;
+    }
+    run_job<Dir>(k.a, job, m, job.wide ? &w : nullptr, job.wide ? (job.wide & 0xFF) - 1 : 0u, tid);
   }
 }
+
+enum : uint32_t { WIDE_FAR_CAP = 1u << 16 };   // words per ring of a wide slice (global memory)
 
 __global__ void avr_fill_kernel(uint4* p, size_t n, uint32_t v) {
   size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x;
@@ -160,6 +126,7 @@ struct avr_ctx {
   int force_resident = -1;   // avr_config.resident / AVR_RESIDENT env: 0 / 1, -1 = per batch
   int wide_stream_bytes = 32768;   // avr_config.wide_stream_bytes / AVR_WIDE_STREAM_BYTES env
   int wide_batch_limit = -1;       // avr_config.wide_batch_limit (-1: 4 x SMs, 0: none)
+  int wide_max_streams = 0;        // avr_config.wide_max_streams (0: default)
   // meta offsets
   size_t off_descs = 0, off_ios = 0, off_jobs = 0, off_res = 0, off_hist = 0, off_counter = 0;
   uint64_t work_stride = 0;
@@ -219,7 +186,7 @@ void avr_config_init(avr_config* cfg) {
   if (!cfg) return;
   memset(cfg, 0, sizeof *cfg);
   cfg->abi_version = AVR_ABI_VERSION;
-  cfg->wide_stream_bytes = -1; cfg->resident = -1; cfg->wide_batch_limit = -1;
+  cfg->wide_stream_bytes = -1; cfg->resident = -1; cfg->wide_batch_limit = -1; cfg->wide_max_streams = 0;
 }
 
 int avr_create(const avr_config* cfg, avr_ctx** out) {
@@ -238,6 +205,7 @@ int avr_create(const avr_config* cfg, avr_ctx** out) {
     c->force_resident = cfg->resident < 0 ? -1 : (cfg->resident ? 1 : 0);
     if (cfg->wide_stream_bytes >= 0) c->wide_stream_bytes = cfg->wide_stream_bytes;
     c->wide_batch_limit = cfg->wide_batch_limit;
+    c->wide_max_streams = cfg->wide_max_streams;
   }
   if (const char* e = getenv("AVR_WIDE_STREAM_BYTES")) c->wide_stream_bytes = int(strtoul(e, nullptr, 10));
   if (!ck(cudaSetDevice(dev), "cudaSetDevice")) { delete c; return AVR_ERR_NO_DEVICE; }
@@ -329,14 +297,29 @@ int avr_stage(avr_ctx* c, const avr_slice_desc* descs, int n, const uint8_t* in,
   }
   // longest jobs first (LPT order for the dynamic hand-out)
   std::stable_sort(c->jobs.begin(), c->jobs.end(), [](const JobDesc& a, const JobDesc& b) { return a.weight > b.weight; });
-  c->n_jobs = int(c->jobs.size());
+  // Wide slices go to the FRONT of the queue, longest first, each as K + 1 consecutive role jobs with role 0 -- the one
+  // the others feed or are fed by -- first (see avr_job.cuh for why that order cannot deadlock).
   std::stable_sort(c->wide.begin(), c->wide.end(), [&](uint32_t a, uint32_t b) { return descs[a].in_size > descs[b].in_size; });
-  c->grid_wide = 0;
+  uint32_t max_roles = 0;
   if (!c->wide.empty()) {
-    if (wide_smem_bytes() > size_t(c->max_smem_optin)) return AVR_ERR_ARG;
-    c->grid_wide = std::min<int>(int(c->wide.size()), c->sm_count);   // one block fills an SM's shared memory
-    c->wide_stride = align_up(wide_rows_bytes(c->max_mbw_wide) + size_t(WIDE_MAX) * WIDE_FAR_CAP * 4, 256);
+    std::vector<JobDesc> front;
+    for (size_t slot = 0; slot < c->wide.size(); slot++) {
+      const uint32_t i = c->wide[slot];
+      const uint32_t K = descs[i].n_streams & AVR_STREAMS_MASK;
+      max_roles = std::max(max_roles, K + 1);
+      for (uint32_t role = 0; role <= K; role++) {
+        JobDesc j; memset(&j, 0, sizeof j);
+        j.first_slice = i; j.n_slices = 1; j.weight = descs[i].in_size / (role == 0 ? 1 : K);
+        j.wide = (role + 1) | uint32_t(slot) << 8;
+        front.push_back(j);
+      }
+    }
+    c->jobs.insert(c->jobs.begin(), front.begin(), front.end());
   }
+  c->n_jobs = int(c->jobs.size());
+  c->grid_wide = int(c->wide.size());
+  c->wide_stride = align_up(wide_ctl_bytes() + wide_rows_bytes(c->max_mbw_wide) + size_t(WIDE_MAX) * WIDE_FAR_CAP * 4, 256);
+  c->max_mbw = std::max(c->max_mbw, c->max_mbw_wide);   // a role works in an ordinary block: its row and window
   c->max_frame_bytes = uint32_t(align_up(c->max_frame_bytes, 16));
 
   // Placement of the estimators: in shared memory (<= 2 blocks per SM, every per-bin access at LDS
@@ -351,20 +334,22 @@ int avr_stage(avr_ctx* c, const avr_slice_desc* descs, int n, const uint8_t* in,
   if (smem_glb + 1024 > size_t(c->max_smem_optin)) return AVR_ERR_ARG;   // picture too wide for the neighbour row
   // Which placement finishes the batch sooner?  A launch lasts max(total work / slots, longest job) x cycles per bin of
   // the variant; the global-memory variant has 4x the slots but every estimator access is an L1 / L2 access on the
-  // serial chain (measured ~2.1x the cycles per bin, profiles/r1d_corpus_case.txt vs r1k_bench.json), so it only
-  // wins when there are many jobs AND none of them is long.
+  // serial chain (measured 8x the cycles per bin on the 256-clip corpus, profiles/r2i_bench.json: 2240 against 280), so
+  // as things stand it never wins and is only taken when asked for (avr_config.resident = 0) -- kept as the variant
+  // for pictures whose neighbour row leaves no room for the estimators.
   uint64_t total_w = 0, longest_w = 0;
   for (const JobDesc& j : c->jobs) { total_w += j.weight; longest_w = std::max<uint64_t>(longest_w, j.weight); }
   bool resident = res_per_sm > 0;
   if (resident) {
     const double t_res = double(std::max<uint64_t>(total_w / uint64_t(res_per_sm * c->sm_count), longest_w));
-    const double t_glb = 2.1 * double(std::max<uint64_t>(total_w / uint64_t(glb_per_sm * c->sm_count), longest_w));
+    const double t_glb = 8.0 * double(std::max<uint64_t>(total_w / uint64_t(glb_per_sm * c->sm_count), longest_w));
     resident = t_res <= t_glb;
   }
   if (c->force_resident == 0) resident = false;
   if (c->force_resident == 1 && res_per_sm > 0) resident = true;
   c->resident = resident;
   c->grid = std::max(1, std::min(c->n_jobs, c->sm_count * (resident ? res_per_sm : glb_per_sm)));
+  if (uint32_t(c->grid) < max_roles) return AVR_ERR_ARG;   // (a device with fewer than 9 resident blocks: not a B200)
 
   // device memory
   // the nnz planes are only needed by jobs whose model spans several slices (file mode)
@@ -426,41 +411,20 @@ int avr_launch(avr_ctx* c, int direction) {
   const size_t smem = smem_bytes(c->max_mbw, c->resident);
   if (int(smem) > c->max_smem_optin) return AVR_ERR_ARG;
   CK(cudaMemsetAsync(k.counter, 0, 2 * sizeof(uint32_t), c->stream));
-  CK(cudaEventRecord(c->ev0, c->stream));
-  if (c->grid_wide > 0) {   // the longest slices first, on their own stream, so that they start at once
-    WideKernelArgs w;
-    w.a = k.a;
-    w.slices = reinterpret_cast<const uint32_t*>(c->d_meta + c->off_wide);
-    w.n_jobs = uint32_t(c->wide.size());
-    w.counter = k.counter + 1;
-    w.workspace = c->d_wide;
-    w.work_stride = c->wide_stride;
-    w.max_mbw = c->max_mbw_wide;
-    w.far_cap = WIDE_FAR_CAP;
-    // neighbour rows: one (compress) or WIDE_MAX (decompress), in shared memory when they fit
-    size_t wsmem = wide_smem_bytes();
-    const size_t rows_bytes = size_t(direction == 0 ? 1 : WIDE_MAX) * c->max_mbw_wide * sizeof(MbCtx);
-    w.rows_in_shared = wsmem + rows_bytes + 1024 <= size_t(c->max_smem_optin) ? 1u : 0u;
-    if (w.rows_in_shared) wsmem += rows_bytes;
-    if (direction == 0) {
-      CK(cudaFuncSetAttribute(avr_wide_kernel<Compress>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(wsmem)));
-      avr_wide_kernel<Compress><<<c->grid_wide, AVR_WIDE_THREADS_OF(Compress), wsmem, c->stream>>>(w);
-    } else {
-      CK(cudaFuncSetAttribute(avr_wide_kernel<Decompress>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(wsmem)));
-      avr_wide_kernel<Decompress><<<c->grid_wide, AVR_WIDE_THREADS_OF(Decompress), wsmem, c->stream>>>(w);
-    }
-    CK(cudaGetLastError());
-    c->launches++;
-  }
-  // The ordinary kernel follows in the same stream; behind a wide kernel it is a programmatic dependent launch
-  // (it starts as soon as every wide block has started and runs beside them).
-  cudaLaunchAttribute pdl;
-  pdl.id = cudaLaunchAttributeProgrammaticStreamSerialization;
-  pdl.val.programmaticStreamSerializationAllowed = 1;
+  k.wide_ws = c->d_wide;
+  k.wide_stride = c->wide_stride;
+  k.wide_mbw = c->max_mbw_wide;
+  k.far_cap = WIDE_FAR_CAP;
+  // the control block of every wide slice starts out zero (ring indices, wavefront progress, role count), and so do
+  // its neighbour rows: a macroblock of the slice's first row, or left of its first macroblock in the second, reads
+  // "nothing there" (all zero) from the row above, exactly as an ordinary slice does from its freshly cleared row
+  if (c->grid_wide)
+    CK(cudaMemset2DAsync(c->d_wide, size_t(c->wide_stride), 0, wide_ctl_bytes() + wide_rows_bytes(c->max_mbw_wide), size_t(c->grid_wide), c->stream));
   cudaLaunchConfig_t lc;
   memset(&lc, 0, sizeof lc);
   lc.gridDim = dim3(unsigned(c->grid)); lc.blockDim = dim3(direction == 0 ? AVR_THREADS_OF(Compress) : AVR_THREADS_OF(Decompress)); lc.dynamicSmemBytes = smem; lc.stream = c->stream;
-  lc.attrs = &pdl; lc.numAttrs = c->grid_wide > 0 ? 1 : 0;
+  lc.attrs = nullptr; lc.numAttrs = 0;
+  CK(cudaEventRecord(c->ev0, c->stream));
 #define AVR_LAUNCH(DIR, RES)                                                                                              \
   do {                                                                                                                    \
     CK(cudaFuncSetAttribute(avr_job_kernel<DIR, RES>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));          \
@@ -507,6 +471,7 @@ int avr_collect(avr_ctx* c, avr_slice_result* results, const uint8_t** out, uint
 
 // what the host file layer (avr_file.cpp) needs to know about the context
 int avr_ctx_wide_stream_bytes(avr_ctx* c) { return c ? c->wide_stream_bytes : 32768; }
+int avr_ctx_wide_max_streams(avr_ctx* c) { return !c || c->wide_max_streams < 2 ? AVR_DEFAULT_WIDE_STREAMS : c->wide_max_streams > AVR_MAX_STREAMS ? AVR_MAX_STREAMS : c->wide_max_streams; }
 int avr_ctx_wide_batch_limit(avr_ctx* c) { return !c ? 0 : c->wide_batch_limit < 0 ? 4 * c->sm_count : c->wide_batch_limit; }
 
 int avr_collect_hist(avr_ctx* c, uint32_t* hist, int n_slices) {

@@ -196,11 +196,11 @@ __device__ void probe_coder_c(ProbeShared* sh, const ProbeArgs& a, uint64_t* r, 
     if (tid < 32) {
       CoderCompress c;
       c.begin(&sh->records);
-      c.run(&sh->ring, nullptr, 0, false, sh->tab, sh->cnt, nullptr, lane);
+      c.run(&sh->ring, nullptr, nullptr, 0, sh->tab, sh->cnt, nullptr, lane);
     } else {
       RangeWarp w;
       w.begin(&sh->sink, sh->out, sizeof sh->out);
-      w.run(&sh->records, false, sh->tab, nullptr, lane);
+      w.run(&sh->records, sh->tab, nullptr, lane);
     }
     __syncthreads();
     bins += per;
@@ -227,7 +227,7 @@ __device__ void probe_range(ProbeShared* sh, const ProbeArgs& a, uint64_t* r, in
   const long long t0 = clock64();
 #pragma unroll 1
   for (uint32_t i = 0; i < a.iters; i++) {
-    w.run(&sh->records, false, sh->tab, nullptr, lane);
+    w.run(&sh->records, sh->tab, nullptr, lane);
     if (lane == 0) sh->sink.n = 0;
     bins += REC_ENTRIES - 1;
     __syncwarp();

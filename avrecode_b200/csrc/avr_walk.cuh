@@ -87,8 +87,7 @@ struct Walker {
   // K parser warps can decompress it as a wavefront -- row r at column x needs row r - 1 through column x only.
   uint32_t wide_k;       // 0: ordinary slice
   bool top_copy;         // the rows are in global memory, not in shared memory
-  RingShared* rings;     // compress: the K rings (one coder warp each); cur_ring = ring of the current row
-  uint32_t cur_ring;
+  uint32_t cur_ring;     // compress: ring (= stream) of the current row
   MbCtx* rows_base;      // decompress: K row buffers, row r in buffer r mod K
   int first_row, last_row;
   volatile uint32_t* prog_mine;          // decompress: macroblocks of the picture (raster order) this warp has got past
@@ -426,7 +425,7 @@ struct Walker {
     {   // neighbour facts into registers
       const MbCtx* l = &ws->left;
       if (top_copy) {   // rows in global memory (a wide slice of a very wide picture): one burst into shared memory per macroblock
-        const uint32_t* g = reinterpret_cast<const uint32_t*>(&row_top[mb_x]);
+        const volatile uint32_t* g = reinterpret_cast<const volatile uint32_t*>(&row_top[mb_x]);   // another block wrote it: not through L1
         uint32_t w[MBCTX_WORDS];
         for (int i = 0; i < MBCTX_WORDS; i++) w[i] = g[i];
         for (int i = 0; i < MBCTX_WORDS; i++) reinterpret_cast<uint32_t*>(&ws->top)[i] = w[i];
@@ -721,13 +720,15 @@ struct Walker {
     const uint32_t need = uint32_t((mb_y - 1) * mbw + mb_x + 1);
     if (above_seen >= need) return true;
 #if defined(__CUDACC__) && !defined(AVR_HOST_EMULATION)
+    const long long t0 = clock64();
     for (uint32_t polls = 0;;) {
       above_seen = *prog_above;
       if (*abort_flag) { fail(WALK_CORRUPT); done = true; return false; }
       if (above_seen >= need) break;
       wide_backoff(polls);
+      wait_watchdog(t0);
     }
-    ring_fence();
+    ring_fence(true);
     return true;
 #else
     above_seen = *prog_above;
@@ -786,14 +787,14 @@ struct Walker {
     mb_xy++;
     bool wrapped = false;
     if (++mb_x >= mbw) { mb_x = 0; mb_y++; wrapped = true; }
-    if (Dir::kDecompress && wide_k) { ring_fence(); *prog_mine = uint32_t(mb_xy); }   // the row below may use this macroblock
+    if (Dir::kDecompress && wide_k) { ring_fence(true); *prog_mine = uint32_t(mb_xy); }   // the row below may use this macroblock
     home_publish(dir.h);
     if (status != WALK_OK) { done = true; return; }
     if (eos) { done = true; return; }
     if (wide_k && wrapped) {
       if (!Dir::kDecompress) {   // next row -> next stream
         cur_ring = cur_ring + 1 == wide_k ? 0 : cur_ring + 1;
-        home_switch_to(dir.h, &rings[cur_ring], cur_ring);
+        home_switch_to(dir.h, cur_ring);
       } else {                   // on to this warp's next row, K - 1 rows further down
         dir.row_end(last_qp_delta != 0);
         mb_y += int(wide_k) - 1;

@@ -87,7 +87,8 @@ typedef struct avr_slice_desc {
 #define AVR_ESC_ZEROS_SHIFT 4
 #define AVR_SLICE_ESCAPED  0x80
 #define AVR_MAX_PICTURE_MBS 139264u /* Level 6.2 MaxFS (H.264 table A-1): larger pictures are reported unsupported */
-#define AVR_MAX_STREAMS 2   /* what this build runs (two estimator sets fill an SM's shared memory); the blob format allows more */
+#define AVR_DEFAULT_WIDE_STREAMS 2
+#define AVR_MAX_STREAMS 8   /* what this build runs: every stream of a wide slice is worked on by a thread block of its own */
 
 /* avr_slice_result.status */
 #define AVR_SLICE_OK           0
@@ -115,7 +116,10 @@ typedef struct avr_config {
                                 AVR_RESIDENT overrides (debugging aid). */
   int32_t wide_batch_limit;  /* wide slices are a latency device: the file calls only use them while a batch has at most this many
                                 CABAC slices.  -1 = default (4 x the device's SM count), 0 = no limit. */
-  int32_t reserved[2];
+  int32_t wide_max_streams;  /* most streams the file calls give a wide slice: 2..AVR_MAX_STREAMS, 0 = default (AVR_DEFAULT_WIDE_STREAMS:
+                                as measured, decompression of a wide slice is bound by the one warp that re-encodes the CABAC
+                                stream from two parsers on, and every further stream costs ratio -- DESIGN.md "Wide slices") */
+  int32_t reserved[1];
 } avr_config;
 
 /* fills *cfg with the defaults (abi_version set, device 0, everything else "choose for me") */
@@ -193,7 +197,7 @@ typedef struct avr_index_entry {
 
 int  avr_index_h264(const uint8_t* file, uint64_t file_bytes, avr_index_entry** entries, int* n_entries);
 /* The n_streams the file calls give this slice in AVR_MODE_SLICE when the batch is small enough for wide slices
- * (avr_config.wide_batch_limit): 2 when its payload is at least two stream quanta (avr_config.wide_stream_bytes of
+ * (avr_config.wide_batch_limit): one stream per quantum of payload, 2..avr_config.wide_max_streams, when it is at least two stream quanta (avr_config.wide_stream_bytes of
  * `ctx`; ctx == NULL: the default of 32 KiB each), else 0.  No reference counterpart. */
 int  avr_slice_streams(const avr_slice_desc* desc);
 int  avr_ctx_slice_streams(avr_ctx* ctx, const avr_slice_desc* desc, int n_batch_slices);

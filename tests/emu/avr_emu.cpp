@@ -43,30 +43,40 @@ static int run(const avr_slice_desc* descs, int n, const uint8_t* in, uint64_t i
   JobMem m;
   m.sh = sh; m.row = row.data(); m.cnt = counters.data();
   m.nnz0 = planes.data(); m.nnz1 = planes.data() + max_frame; m.nnz_frame_bytes = max_frame; m.max_mbw = uint32_t(max_mbw);
-  // wide slices (n_streams >= 2) get the block state of the wide kernel
-  WideShared* wsh = new WideShared();
-  fill_shared_tables(&wsh->tab, 0, 1);
+  // wide slices (n_streams >= 2): one set of block state per role, the shared control block / rows / rings on the heap
+  std::vector<BlockShared*> wsh;
+  std::vector<std::vector<uint16_t>> wcnt(WIDE_MAX + 1, std::vector<uint16_t>(MODEL_COUNTERS_PAD));
+  std::vector<std::vector<MbCtx>> wrow(WIDE_MAX + 1, std::vector<MbCtx>(max_mbw));
+  std::vector<JobMem> wmems(WIDE_MAX + 1);
+  for (uint32_t r = 0; r <= WIDE_MAX; r++) {
+    wsh.push_back(new BlockShared());
+    fill_shared_tables(&wsh[r]->tab, 0, 1);
+    wmems[r] = m;
+    wmems[r].sh = wsh[r]; wmems[r].row = wrow[r].data(); wmems[r].cnt = wcnt[r].data();
+  }
   std::vector<MbCtx> wrows(size_t(WIDE_MAX) * max_mbw);
-  std::vector<uint16_t> wcnt(size_t(WIDE_MAX) * MODEL_COUNTERS_PAD);
-  WideMem wm;
-  wm.sh = wsh; wm.rows = wrows.data(); wm.cnt = wcnt.data(); wm.rows_global = false; wm.far = nullptr; wm.far_cap = 0; wm.max_mbw = uint32_t(max_mbw);
   int i = 0;
   while (i < n) {
     if ((descs[i].n_streams & AVR_STREAMS_MASK) >= 2) {
       if (!(descs[i].flags & AVR_SLICE_NEW_MODEL) || (i + 1 < n && !(descs[i + 1].flags & AVR_SLICE_NEW_MODEL))) return AVR_ERR_ARG;
-      run_wide_job<Dir>(a, uint32_t(i), wm, 0);
+      WideCtl* ctl = new WideCtl();
+      memset(wrows.data(), 0, wrows.size() * sizeof(MbCtx));
+      WideMem wm;
+      wm.ctl = ctl; wm.rows = wrows.data(); wm.far = nullptr; wm.far_cap = 0;
+      emu_wide_slice<Dir>(a, uint32_t(i), wmems.data(), wm);
+      delete ctl;
       i++;
       continue;
     }
     int j = i + 1;
     while (j < n && !(descs[j].flags & AVR_SLICE_NEW_MODEL)) j++;
     JobDesc job;
-    job.first_slice = uint32_t(i); job.n_slices = uint32_t(j - i); job.weight = 0; job.reserved = 0;
-    run_job<Dir>(a, job, m, 0);
+    job.first_slice = uint32_t(i); job.n_slices = uint32_t(j - i); job.weight = 0; job.wide = 0;
+    run_job<Dir>(a, job, m, nullptr, 0, 0);
     i = j;
   }
   delete sh;
-  delete wsh;
+  for (BlockShared* p : wsh) delete p;
   // compact
   std::vector<uint8_t> all;
   for (int k = 0; k < n; k++) {

@@ -88,6 +88,9 @@ def oracle_decompress(descs, data, mirror_compressor=1):
     return _call(oracle_lib().avr_oracle_decompress, descs, data, C.c_int(mirror_compressor))
 
 
+WIDE_PATTERN = (2, 3, 0, 4, 8, 2, 5)   # avr_slice_desc.n_streams over the slices of a test batch (0 = ordinary)
+
+
 def emu_compress(descs, data):
     return _call(emu_lib().avr_emu_compress, descs, data)
 

@@ -134,13 +134,13 @@ def test_wide_slices_on_host_round_trip(built, kw):
     plain = H.batch_descs(A.index_h264(data), False)
     r_1, _ = H.emu_compress(plain, data)
     descs = H.batch_descs(A.index_h264(data), False)
-    for d in descs:
-        d.n_streams = 2
+    for i, d in enumerate(descs):
+        d.n_streams = (2, 3, 8)[i % 3]
     r_e, b_e = H.emu_compress(descs, data)
     assert [(r.status, r.n_bins, r.n_mbs) for r in r_e] == [(r.status, r.n_bins, r.n_mbs) for r in r_1]
     r_d, b_d = H.emu_decompress(H.coded_descs(descs, r_e), b_e)
     assert H.roundtrip_ok(descs, r_d, b_d, data)
-    assert sum(r.out_size for r in r_e) < 1.5 * sum(r.out_size for r in r_1) + 64 * len(descs)
+    assert sum(r.out_size for r in r_e) < 1.5 * sum(r.out_size for r in r_1) + 128 * len(descs)
 
 
 ESCAPED_STREAM = dict(width=640, height=368, frames=6, high=True, seed=108, kbps=9000)   # slice 4 has a 00 00 03 in its payload
@@ -240,7 +240,7 @@ def test_wide_format_restatement_equals_device_logic(built, kw):
     data = H.gen_stream(**kw)
     descs = H.batch_descs(A.index_h264(data), False)
     for i, d in enumerate(descs):
-        d.n_streams = 0 if i % 3 == 2 else 2
+        d.n_streams = H.WIDE_PATTERN[i % len(H.WIDE_PATTERN)]
     r_e, b_e = H.emu_compress(descs, data)
     r_o, b_o = H.oracle_compress(descs, data)
     assert [r.status for r in r_o] == [0] * len(descs)

@@ -14,7 +14,7 @@ data = H.gen_stream(width=1920, height=1088, frames=frames, high=True, kbps=3000
 descs = H.batch_descs(A.index_h264(data), False)
 if per_stream:
     for d in descs:
-        k = min(2, d.payload_size // per_stream)
+        k = min(int(os.environ.get("PROFILE_MAX_STREAMS", "2")), d.payload_size // per_stream)
         d.n_streams = k if k >= 2 else 0
 with A.Context() as ctx:
     ctx.stage(descs, data)
