@@ -83,6 +83,13 @@ enum : uint32_t {
   SIG_ENTRIES = SIG_OFF_CAT5 + SIG_CAT_8,       // 44160
   MODEL_COUNTERS = CNT_SIG + SIG_ENTRIES,       // 47892 estimators = 95784 bytes
   MODEL_COUNTERS_PAD = MODEL_COUNTERS + 36,     // the coders prefetch the estimator one step past a block (<= +17): allocated, never used
+  // Split placement (the kernel variant for throughput batches): the 8x8 significance slab -- 70 % of the table, used by
+  // one block category only -- lives in the global workspace (L1 / L2, prefetched per block), the rest in shared
+  // memory, so that four blocks fit an SM instead of two.  cnt8 points CNT8_SPLIT entries before that slab, so the
+  // same indices work with either placement (resident: cnt8 == cnt).
+  CNT8_SPLIT = CNT_SIG + SIG_OFF_CAT5,
+  CNT_LOW_PAD = CNT8_SPLIT + 36,
+  CNT8_ENTRIES = SIG_CAT_8 + 36,
   EST_INIT = 0x0201,                            // {pos = 1, neg = 1}
   NNZ_STRIDE = 52,                              // FrameBuffer meta: 51 block slots + pad per macroblock
 };
@@ -102,7 +109,7 @@ AVR_DEV uint32_t sig_slab(int cat, uint32_t key_nnz) {   // index of [observed =
 // ------------------------------------------------------------------------------------------------
 // Small read-only tables in shared memory (per thread block).
 // ------------------------------------------------------------------------------------------------
-struct U2 { uint32_t x, y; };
+struct alignas(8) U2 { uint32_t x, y; };
 struct alignas(16) U4 { uint32_t x, y, z, w; };   // two U2 side by side: one 16-byte load
 struct alignas(16) DivMagic { uint64_t magic; uint32_t shift, pad; };   // one 16-byte load per division
 struct SharedTables {
@@ -493,6 +500,16 @@ AVR_DEV uint32_t est_next(uint32_t c, uint32_t bit, uint32_t limit) {
   if (c2 >= ((limit + 1u) << 8)) c2 = est_halve(c2);
   return c2;
 }
+// the rows of the 8x8 slab a block is about to walk (split placement: global memory; a shared-memory address: no-op)
+AVR_DEV void est_prefetch(const uint16_t* p, uint32_t bytes) {
+#if defined(__CUDA_ARCH__)
+  const char* a = reinterpret_cast<const char*>(p);
+#pragma unroll 1
+  for (uint32_t o = 0; o < bytes; o += 128) asm volatile("prefetch.L1 [%0];" ::"l"(a + o));
+#else
+  (void)p; (void)bytes;
+#endif
+}
 // limits: 0x50 while the bin is a significance-map bin, else 0x60 (recode.cpp:1041-1042)
 enum : uint32_t { LIMIT_SIG = 0x50, LIMIT_ANY = 0x60 };
 
@@ -571,7 +588,7 @@ struct RingCtl {
 };
 enum : uint32_t { REC_ENTRIES = 256 };
 struct RingShared : RingCtl { uint32_t e[RING_ENTRIES]; };   // parser -> the warp behind it
-struct RecRing : RingCtl { uint32_t e[REC_ENTRIES]; };       // compress: estimator warp -> range-coder warp
+struct RecRing : RingCtl { alignas(8) uint32_t e[REC_ENTRIES]; };   // second warp -> third warp of a block (one or two words per bin)
 AVR_DEV void ring_reset(RingCtl* r) { r->tail_pub = 0; r->head_pub = 0; r->prod_tail = 0; r->cons_head = 0; r->prod_wait = 0; r->cons_wait = 0; }
 // makes room for an entry of n words: publishes what is complete, waits for the consumer if the ring is full; returns
 // the tail value up to which the producer may go on without looking again.  One out-of-line copy (instruction cache).
@@ -619,6 +636,7 @@ struct WordSrc {       // words of a batch: the shared-memory ring itself (mask 
   const uint32_t* e;
   uint32_t at, mask;
   AVR_DEV uint32_t take() { return e[at++ & mask]; }
+  AVR_DEV U2 take2() { const U2 v = *reinterpret_cast<const U2*>(&e[at & mask]); at += 2; return v; }   // at even
 };
 
 #if defined(__CUDACC__) && !defined(AVR_HOST_EMULATION)
@@ -698,17 +716,25 @@ struct RecWriter {     // producer side of the record ring, in registers (lane 0
     r->e[tail & (REC_ENTRIES - 1)] = w;
     tail++;
   }
+  AVR_DEV void put2(uint32_t w0, uint32_t w1) {   // a record of two words (tail stays even: one 8-byte store)
+    if (int32_t(limit - tail) < 2) limit = ring_slow(r, tail, 2, REC_ENTRIES, false);
+    U2 v; v.x = w0; v.y = w1;
+    *reinterpret_cast<U2*>(&r->e[tail & (REC_ENTRIES - 1)]) = v;
+    tail += 2;
+  }
   AVR_DEV void publish() { ring_fence(); *reinterpret_cast<volatile uint32_t*>(&r->tail_pub) = tail; }
 #else
   void init(RecRing* ring) { r = ring; }
   void put(uint32_t w) { r->e.push_back(w); }
+  void put2(uint32_t w0, uint32_t w1) { r->e.push_back(w0); r->e.push_back(w1); }
   void publish() {}
 #endif
 };
 
 struct CoderCompress {     // the estimator warp (recode.cpp:1030-1047 + the model keys of 676-815 as indices)
   RecWriter out;
-  AVR_DEV void begin(RecRing* records) { out.init(records); }
+  uint16_t* cnt8;          // estimators of the 8x8 significance slab (CNT8_SPLIT)
+  AVR_DEV void begin(RecRing* records, uint16_t* counters8) { out.init(records); cnt8 = counters8; }
   // one bin: the estimator's state goes to the range-coder warp, its update stays here
   AVR_DEV void code(uint16_t* cnt, uint32_t idx, uint32_t bit, uint32_t limit, uint32_t flags = 0) {
     const uint32_t c = cnt[idx];
@@ -735,6 +761,7 @@ struct CoderCompress {     // the estimator warp (recode.cpp:1030-1047 + the mod
   // 8x8 blocks: several positions share an estimator (sig_coeff_flag_offset_8x8)
   AVR_DEV void sig_bins8(const SharedTables& t, uint16_t* cnt, uint32_t slab, uint64_t mask, uint32_t nnz_true) {
     uint32_t zz = 0, observed = 0;
+    est_prefetch(cnt + slab, nnz_true * (SIG_ZZ * 2));
 #pragma unroll 1
     while (observed < nnz_true && zz < 63) {
       const uint32_t bit = uint32_t(mask >> zz) & 1u;
@@ -772,7 +799,7 @@ struct CoderCompress {     // the estimator warp (recode.cpp:1030-1047 + the mod
         const uint32_t slab = sig_slab(int(cat), nnz_true & 63);
         if (cat == 5) {
           const uint32_t mhi = s.take();
-          sig_bins8(t, cnt, slab, uint64_t(mlo) | uint64_t(mhi) << 32, nnz_true);
+          sig_bins8(t, cnt8, slab, uint64_t(mlo) | uint64_t(mhi) << 32, nnz_true);
         } else sig_bins4(cnt, slab, mlo, nnz_true, uint32_t(k_maxc[cat]) - 1);
         return false;
       }
@@ -862,9 +889,83 @@ struct RangeWarp {
   AVR_DEV bool overflowed() const { return rc.sink->overflow != 0; }
 };
 
-struct CoderDecompress {   // CABAC re-encoder (cabac_code.h:16-86; recode.cpp:1443, 1455, 1466)
+// Decompression has TWO recurrences behind the parser as well: the context states (serial per context) and the CABAC
+// arithmetic encoder (serial per slice: range, low, the bytes).  One warp doing both ran at 227 cycles per bin
+// (profiles/r2j_probes.txt) and, from two parsers on, set the time of a wide slice; so they are two warps joined by the
+// block's record ring, one RECORD of two words per bin:
+//   decision   w0 = the context's four rangeTabLPS bytes (entry word y), w1 = entry word x (valMPS, state, the
+//              renormalisation shifts of an LPS) with bit 1 = "this bin is the LPS"
+//   bypass / terminate   w0 = the bin, w1 = REC_BYPASS / REC_TERM;   REC_END closes the slice
+enum : uint32_t { REC_LPS = 1u << 1, REC_KIND = 3u << 2, REC_BYPASS = 1u << 2, REC_TERM = 2u << 2, REC_END = 3u << 2 };
+struct CtxOut {            // the context warp's view of the encoder: same calls as CabacOut, records instead of bytes
+  RecWriter out;
+  AVR_DEV void encode_core(const SharedTables& t, const U2 e, int bin, U2* next) {
+    const U4 pair = ctx_trans_row(t, e.x);
+    const uint32_t lps = uint32_t(bin) != (e.x & 1) ? 1u : 0u;
+    next->x = lps ? pair.z : pair.x;
+    next->y = lps ? pair.w : pair.y;
+    out.put2(e.y, (e.x & ~0xEu) | lps << 1);
+  }
+  AVR_DEV void decision(const SharedTables& t, int bin, U2* ctx) {
+    U2 n;
+    encode_core(t, *ctx, bin, &n);
+    *ctx = n;
+  }
+  AVR_DEV void bypass(int bin) { out.put2(uint32_t(bin), REC_BYPASS); }
+  AVR_DEV void terminate(int bin) { out.put2(uint32_t(bin), REC_TERM); }
+};
+
+// the arithmetic warp of a decompression (cabac_code.h:16-86 minus the context states): records -> slice_data bytes
+struct ArithWarp {
   CabacOut cabac;
   AVR_DEV void begin(ByteSink* sink, uint8_t* dst, uint32_t cap, int esc_zeros = -1) { cabac.init(sink, dst, cap, esc_zeros); }
+  AVR_DEV void decision(uint32_t w0, uint32_t w1) {   // CabacOut::encode_core with the context side already resolved
+    uint32_t low = cabac.low, range = cabac.range;
+    const uint32_t tq = range >> 6;
+    const uint32_t rlps = rlps_by_t(w0, tq);
+    const uint32_t sh_lps = (w1 >> (3 * tq + (CTX_SHLPS_SHIFT - 12))) & 7;
+    range -= rlps;
+    const uint32_t sh_mps = (range >> 8) ^ 1;
+    const bool lps = (w1 & REC_LPS) != 0;
+    if (lps) { low += range; range = rlps; }
+    const int shift = int(lps ? sh_lps : sh_mps);
+    cabac.range = range << shift; cabac.low = low << shift; cabac.queue += shift;
+    cabac.put_bytes();
+  }
+  AVR_DEV void run(RecRing* records, uint32_t* stage, int lane) {
+    RingReader q; q.init_rec(records);
+    for (;;) {
+      WordSrc src;
+      const uint32_t n = coder_fetch(q, nullptr, 0, stage, lane, &src);   // whole records: the writer's tail is always even
+      uint32_t done = 0;
+      if (lane == 0) {
+        // a record never changes once written: record k + 1 is fetched while record k goes through the encoder
+        U2 rec = src.take2();
+#pragma unroll 2
+        for (uint32_t k = 2;; k += 2) {
+          U2 nxt; nxt.x = 0; nxt.y = REC_END;
+          if (k < n) nxt = src.take2();
+          const uint32_t kind = rec.y & REC_KIND;
+          if (kind == 0) decision(rec.x, rec.y);
+          else if (kind == REC_BYPASS) cabac.bypass(int(rec.x));
+          else if (kind == REC_TERM) cabac.terminate(int(rec.x));
+          else { done = 1; break; }
+          if (k >= n) break;
+          rec = nxt;
+        }
+      }
+      done = AVR_BCAST_CORE(done);
+      q.release(n, lane);
+      if (done) break;
+    }
+  }
+  AVR_DEV uint32_t out_bytes() const { return cabac.sink->n; }
+  AVR_DEV bool overflowed() const { return cabac.sink->overflow != 0; }
+};
+
+struct CoderDecompress {   // the context warp: entries -> bins -> context states (recode.cpp:1443, 1455, 1466) -> records
+  CtxOut cabac;
+  AVR_DEV void begin(RecRing* records) { cabac.out.init(records); }
   // significant_coeff_flag / last_significant_coeff_flag bins of a block out of its mask (h264_cabac.c:1667-1703);
   // the last coefficient of a full scan is inferred, not coded.  4x4-class blocks: position i uses contexts
   // sig_base + i and last_base + i, all distinct, so the entries of the next position are fetched ahead.
@@ -944,10 +1045,11 @@ struct CoderDecompress {   // CABAC re-encoder (cabac_code.h:16-86; recode.cpp:1
 #pragma unroll 1
         while (src.at - at0 < n) {
           const uint32_t e = src.take();
-          if (e & SYM_END) { done = 1; break; }
+          if (e & SYM_END) { done = 1; cabac.out.put2(0, REC_END); break; }
           entry(src, t, cstate, e);
         }
         used = src.at - at0;
+        cabac.out.publish();
       }
       used = AVR_BCAST_CORE(used); done = AVR_BCAST_CORE(done);
       q.release(used, lane);
@@ -972,7 +1074,7 @@ struct CoderDecompress {   // CABAC re-encoder (cabac_code.h:16-86; recode.cpp:1
 #pragma unroll 1
         while (src.at - at0 < n) {
           const uint32_t e = src.take();
-          if (e & SYM_END) { why = 2; break; }
+          if (e & SYM_END) { why = 2; if (!draining) cabac.out.put2(0, REC_END); break; }
           if (draining) { if (e & SYM_BLOCK) src.at += (e & 7) == 5 ? 2 : 1; continue; }   // skip a block's mask words
           if (!(e & (SYM_LEVEL | SYM_BLOCK)) && (e & (3u << SYM_KIND_SHIFT)) == SYM_SPECIAL) {
             if (e & SP_ROW_END) { qpd = e & 1; why = 1; break; }
@@ -980,6 +1082,7 @@ struct CoderDecompress {   // CABAC re-encoder (cabac_code.h:16-86; recode.cpp:1
           } else entry(src, t, cstate, e);
         }
         used = src.at - at0;
+        cabac.out.publish();
       }
       used = AVR_BCAST_CORE(used); why = AVR_BCAST_CORE(why);
       q.release(used, lane);
@@ -995,8 +1098,6 @@ struct CoderDecompress {   // CABAC re-encoder (cabac_code.h:16-86; recode.cpp:1
       q.head = uint32_t(rings[cur].cons_head);
     }
   }
-  AVR_DEV uint32_t out_bytes() const { return cabac.sink->n; }
-  AVR_DEV bool overflowed() const { return cabac.sink->overflow != 0; }
 };
 
 // ------------------------------------------------------------------------------------------------
@@ -1011,9 +1112,9 @@ struct CoderDecompress {   // CABAC re-encoder (cabac_code.h:16-86; recode.cpp:1
 // regions of the walker keep them in registers and add them to the home state when they leave.
 enum : int { HIST_MB = 0, HIST_CBF = 1, HIST_SIG = 2, HIST_LEVEL = 3, HIST_BYPASS = 4, HIST_NNZ = 5, HIST_PRED = 6, HIST_TERM = 7 };
 struct ResBins {
-  uint32_t cbf, sig, level, bypass, nnz, pred;
-  AVR_DEV void clear() { cbf = sig = level = bypass = nnz = pred = 0; }
-  AVR_DEV uint32_t cabac_bins() const { return cbf + sig + level + bypass + pred; }   // nnz bits are model-only bins
+  uint32_t cbf, sig, level, bypass, nnz, pred, mb;   // mb: macroblock-level bins walked in register mode (HIST_MB is the remainder)
+  AVR_DEV void clear() { cbf = sig = level = bypass = nnz = pred = mb = 0; }
+  AVR_DEV uint32_t cabac_bins() const { return cbf + sig + level + bypass + pred + mb; }   // nnz bits are model-only bins
 };
 struct ParserHome {
   RingCtl* r;               // ring, producer side: its control words
@@ -1169,12 +1270,14 @@ AVR_DEV_NOINLINE uint32_t slow_d_bin(ParserHome* h, uint16_t* est, const SharedT
 struct Compress {
   static constexpr bool kDecompress = false;
   typedef CoderCompress Coder;
+  typedef RangeWarp Tail;
   ByteWindow in;
   ParserHome* h;
   U2* cstate;        // parser owns the CABAC context states
   const SharedTables* tabp;
   CabacIn cabac;     // register copy
   RingWriter q;
+  AVR_DEV void set_cnt8(uint16_t*) {}   // the parser of a compression touches no estimator
   AVR_DEV void begin(ParserHome* home, const uint8_t* src, uint32_t n, uint8_t* window, uint32_t tail_byte, RingShared* ring,
                      const SharedTables* tab, uint16_t* counters, U2* states, RingCtl* far_ctl = nullptr, uint32_t* far_entries = nullptr,
                      uint32_t far_cap = 0, uint32_t far_index = 0) {
@@ -1245,9 +1348,11 @@ struct Compress {
 struct Decompress {
   static constexpr bool kDecompress = true;
   typedef CoderDecompress Coder;
+  typedef ArithWarp Tail;
   ByteWindow in;
   ParserHome* h;
   uint16_t* cnt;     // parser owns the estimators
+  uint16_t* cnt8;    // ... those of the 8x8 significance slab (CNT8_SPLIT)
   const SharedTables* tabp;
   RangeDec rc;       // register copy
   RingWriter q;
@@ -1260,7 +1365,7 @@ struct Decompress {
                      uint32_t far_cap = 0, uint32_t far_index = 0) {
     h = home;
     in.attach(src, n, window, 0);
-    cnt = counters; tabp = tab;
+    cnt = counters; cnt8 = counters; tabp = tab;
     home_ring_init(h, ring, far_ctl, far_entries, far_cap, far_index);
     h->tab = tab; h->cstate = states; h->cnt = counters; h->win = window; h->skew = in.skew; h->n_bins = 0;
     for (int i = 0; i < 8; i++) h->hist[i] = 0;
@@ -1344,6 +1449,14 @@ struct Decompress {
   AVR_DEV int lvl_bypass(const SharedTables& t) {   // Exp-Golomb escape bins
     const int b = byp_bin(t);
     q.reserve(h, 1); q.put(h, uint32_t(b) << SYM_BIT_SHIFT | SYM_BYPASS);
+    return b;
+  }
+  AVR_DEV void set_cnt8(uint16_t* p) { cnt8 = p; }
+  AVR_DEV void sig8_prefetch(uint32_t slab, uint32_t rows) const { est_prefetch(cnt8 + slab, rows * (SIG_ZZ * 2)); }
+  AVR_DEV int sig8_bit(const SharedTables& t, uint32_t idx) {   // a significance bin of an 8x8 block
+    const uint32_t c = cnt8[idx];
+    const int b = rc.get(t.div[c >> 8], c & 0xFF);
+    cnt8[idx] = uint16_t(est_next(c, uint32_t(b), LIMIT_SIG));
     return b;
   }
   AVR_DEV int model_bit(const SharedTables& t, uint32_t idx) { return coded(t, idx, idx >= CNT_SIG ? uint32_t(LIMIT_SIG) : uint32_t(LIMIT_ANY)); }

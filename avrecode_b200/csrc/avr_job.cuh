@@ -11,7 +11,7 @@
 #include "avr_walk.cuh"
 
 #if defined(__CUDACC__) && !defined(AVR_HOST_EMULATION)
-#define AVR_THREADS_OF(Dir) ((Dir::kDecompress) ? 64 : 96)   // compress: parser + estimator warp + range-coder warp
+#define AVR_THREADS_OF(Dir) 96   // parser warp + estimator / context warp + range-coder / arithmetic warp
 #define AVR_HOST_STAGE(x) nullptr   // the device reads a shared-memory ring in place
 #define AVR_LANES 32
 #define AVR_SYNCWARP() __syncwarp()
@@ -73,7 +73,8 @@ struct JobArgs {
 struct JobMem {             // where this block keeps its state
   BlockShared* sh;
   MbCtx* row;               // [max_mbw], shared memory
-  uint16_t* cnt;            // MODEL_COUNTERS estimators: shared memory (resident) or global workspace
+  uint16_t* cnt;            // MODEL_COUNTERS estimators: shared memory (resident: all of them; split: the first CNT_LOW_PAD)
+  uint16_t* cnt8;           // the 8x8 significance slab is at cnt8 + CNT8_SPLIT: cnt8 == cnt (resident) or in the global workspace (split)
   uint8_t* nnz0;            // two FrameBuffer nnz planes, global workspace (scalars: the struct must stay in registers)
   uint8_t* nnz1;
   uint32_t nnz_frame_bytes; // capacity of one plane
@@ -140,6 +141,7 @@ struct Lane {               // what one parser warp works with
   WalkShared* walk;
   MbCtx* row;
   uint16_t* cnt;
+  uint16_t* cnt8;
   RingCtl* far_ctl;         // wide slices: the slice's rings in global memory (control words / entries), else null
   uint32_t* far;
   uint32_t far_cap, far_index;
@@ -158,6 +160,7 @@ AVR_DEV void parser_begin(Walker<Dir>& wk, const Lane& ln, const uint8_t* src, u
   wk.nnz_cur = nnz_cur; wk.nnz_prev = nnz_prev;
   wk.dir.begin(ln.home, src, n, ln.window, (d.flags & AVR_SLICE_STOP_BYTE) ? 0x80u : 0u, ln.ring, ln.tab, ln.cnt, ln.cstate, ln.far_ctl, ln.far,
                ln.far_cap, ln.far_index);
+  wk.dir.set_cnt8(ln.cnt8);
   window_load_half(wk.dir.in, 0, lane);
   window_load_half(wk.dir.in, WIN_HALF, lane);
   AVR_SYNCWARP();
@@ -340,7 +343,7 @@ AVR_DEV void parser_role(const JobMem& m, const Unit& u, const avr_slice_desc& d
   wk.top_copy = false;
   Lane ln;
   ln.tab = &m.sh->tab; ln.ring = &m.sh->ring; ln.window = m.sh->window; ln.cstate = m.sh->cstate;
-  ln.walk = &m.sh->walk; ln.row = m.row; ln.cnt = m.cnt; ln.far_ctl = nullptr; ln.far = nullptr; ln.far_cap = 0; ln.far_index = 0; ln.home = &m.sh->phome;
+  ln.walk = &m.sh->walk; ln.row = m.row; ln.cnt = m.cnt; ln.cnt8 = m.cnt8; ln.far_ctl = nullptr; ln.far = nullptr; ln.far_cap = 0; ln.far_index = 0; ln.home = &m.sh->phome;
   if (u.w.ctl) {
     wide_walker<Dir>(wk, u.w, u.K, u.j);
     ln.far_ctl = u.w.ctl->ring; ln.far = u.w.far; ln.far_cap = u.w.far_cap; ln.far_index = u.j;
@@ -392,31 +395,32 @@ AVR_DEV void write_result(const JobArgs& a, const JobMem& m, const SliceIO& io, 
   write_hist(a, s, &m.sh->phome, 1, res.n_mbs, res.n_bins);
   m.sh->final_status = uint32_t(res.status);
 }
-// decompress: the CABAC re-encoder, which owns the output bytes and the slice result; compress: the estimator warp
+// the warp behind the parser -- compress: the estimator warp; decompress: the context warp.  Both feed the record ring.
 template <class Dir>
-AVR_DEV void coder_role(const JobArgs& a, const JobMem& m, const Unit& u, const SliceIO& io, uint32_t s, int lane) {
+AVR_DEV void coder_role(const JobMem& m, const Unit& u, int lane) {
   typename Dir::Coder c;
+  if constexpr (Dir::kDecompress) c.begin(&m.sh->records); else c.begin(&m.sh->records, m.cnt8);
   if constexpr (Dir::kDecompress) {
-    c.begin(&m.sh->sink, u.dst, u.dst_cap, u.esc_zeros);
-    if (u.w.ctl) {
-      c.run_wide(u.w.ctl->ring, u.K, u.w.far, u.w.far_cap, m.sh->tab, m.sh->cstate, m.sh->stage, lane);
-      if (lane == 0) { u.w.ctl->out_size[0] = c.out_bytes(); if (c.overflowed()) u.w.ctl->overflow = 1; }
-    } else {
-      c.run(&m.sh->ring, m.sh->tab, m.sh->cstate, AVR_HOST_STAGE(m.sh->stage), lane);
-      if (lane == 0) write_result(a, m, io, s, c.out_bytes(), c.overflowed(), false);
-    }
+    if (u.w.ctl) c.run_wide(u.w.ctl->ring, u.K, u.w.far, u.w.far_cap, m.sh->tab, m.sh->cstate, m.sh->stage, lane);
+    else c.run(&m.sh->ring, m.sh->tab, m.sh->cstate, AVR_HOST_STAGE(m.sh->stage), lane);
   } else {
-    c.begin(&m.sh->records);
     c.run(&m.sh->ring, u.w.ctl ? &u.w.ctl->ring[u.j] : nullptr, u.w.ctl ? u.w.far + size_t(u.j) * u.w.far_cap : nullptr, u.w.far_cap,
           m.sh->tab, m.cnt, m.sh->stage, lane);
   }
   AVR_SYNCWARP();
 }
-// compress: the range-coder warp, which owns the output bytes and (ordinary slices) the slice result
-AVR_DEV void range_role(const JobArgs& a, const JobMem& m, const Unit& u, const SliceIO& io, uint32_t s, int lane) {
-  RangeWarp c;
-  c.begin(&m.sh->sink, u.dst, u.dst_cap);
-  c.run(&m.sh->records, m.sh->tab, AVR_HOST_STAGE(m.sh->stage2), lane);
+// the last warp of the pipeline, which owns the output bytes and (ordinary slices) the slice result -- compress: the
+// range coder; decompress: the CABAC arithmetic encoder
+template <class Dir>
+AVR_DEV void tail_role(const JobArgs& a, const JobMem& m, const Unit& u, const SliceIO& io, uint32_t s, int lane) {
+  typename Dir::Tail c;
+  if constexpr (Dir::kDecompress) {
+    c.begin(&m.sh->sink, u.dst, u.dst_cap, u.esc_zeros);
+    c.run(&m.sh->records, AVR_HOST_STAGE(m.sh->stage2), lane);
+  } else {
+    c.begin(&m.sh->sink, u.dst, u.dst_cap);
+    c.run(&m.sh->records, m.sh->tab, AVR_HOST_STAGE(m.sh->stage2), lane);
+  }
   if (lane == 0) {
     if (u.w.ctl) { u.w.ctl->out_size[u.j] = c.out_bytes(); if (c.overflowed()) u.w.ctl->overflow = 1; }
     else write_result(a, m, io, s, c.out_bytes(), c.overflowed(), true);
@@ -551,7 +555,11 @@ AVR_DEV void run_job(const JobArgs& a, const JobDesc& job, const JobMem& m, cons
     if (usable) {
       if (fresh) {
         // a brand-new h264_model: every estimator {1,1} (recode.cpp:1057), no frame buffers yet
-        fill_u32(reinterpret_cast<uint32_t*>(m.cnt), MODEL_COUNTERS_PAD / 2, EST_INIT * 0x10001u, tid, nthreads);
+        if (m.cnt8 == m.cnt) fill_u32(reinterpret_cast<uint32_t*>(m.cnt), MODEL_COUNTERS_PAD / 2, EST_INIT * 0x10001u, tid, nthreads);
+        else {
+          fill_u32(reinterpret_cast<uint32_t*>(m.cnt), CNT_LOW_PAD / 2, EST_INIT * 0x10001u, tid, nthreads);
+          fill_u32(reinterpret_cast<uint32_t*>(m.cnt8 + CNT8_SPLIT), CNT8_ENTRIES / 2, EST_INIT * 0x10001u, tid, nthreads);
+        }
         ft.clear();
       }
       const int mw = d.mb_width, mh = d.mb_height;
@@ -583,12 +591,12 @@ AVR_DEV void run_job(const JobArgs& a, const JobDesc& job, const JobMem& m, cons
     if (walk) {
 #if defined(__CUDACC__) && !defined(AVR_HOST_EMULATION)
       if (tid < 32) { if (u.parse) parser_role<Dir>(m, u, d, ft.cur, use_planes, lane); }
-      else if (tid < 64) { if (u.code) coder_role<Dir>(a, m, u, io, s, lane); }
-      else if (u.code) range_role(a, m, u, io, s, lane);
+      else if (tid < 64) { if (u.code) coder_role<Dir>(m, u, lane); }
+      else if (u.code) tail_role<Dir>(a, m, u, io, s, lane);
 #else
       if (u.parse) parser_role<Dir>(m, u, d, ft.cur, use_planes, lane);
-      if (u.code) coder_role<Dir>(a, m, u, io, s, lane);
-      if (u.code && !Dir::kDecompress) range_role(a, m, u, io, s, lane);
+      if (u.code) coder_role<Dir>(m, u, lane);
+      if (u.code) tail_role<Dir>(a, m, u, io, s, lane);
 #endif
     } else if (tid == 0 && (!wide || role == 0)) {
       avr_slice_result r;
@@ -629,7 +637,7 @@ void emu_wide_slice(const JobArgs& a, uint32_t s, JobMem* mems, const WideMem& w
       wide_walker<Dir>(wk[j], w, K, j);
       Lane ln;
       ln.tab = &m.sh->tab; ln.ring = &m.sh->ring; ln.window = m.sh->window; ln.cstate = m.sh->cstate; ln.walk = &m.sh->walk;
-      ln.row = w.rows + size_t(j) * mbw; ln.cnt = m.cnt; ln.home = &m.sh->phome;
+      ln.row = w.rows + size_t(j) * mbw; ln.cnt = m.cnt; ln.cnt8 = m.cnt8; ln.home = &m.sh->phome;
       ln.far_ctl = w.ctl->ring; ln.far = nullptr; ln.far_cap = 0; ln.far_index = j;
       const uint32_t sz = load_le32(blob + 4 + 4 * j);
       parser_begin<Dir>(wk[j], ln, blob + off, sz, d, nullptr, nullptr, false, 0, j, g.total_mbs);
@@ -644,9 +652,13 @@ void emu_wide_slice(const JobArgs& a, uint32_t s, JobMem* mems, const WideMem& w
     delete[] wk;
     BlockShared* sh = mems[0].sh;
     init_contexts(sh->cstate, d, 0, 1);
-    CoderDecompress c;
+    ring_reset(&sh->records);
+    CoderDecompress cw;
+    cw.begin(&sh->records);
+    cw.run_wide(w.ctl->ring, K, nullptr, 0, sh->tab, sh->cstate, sh->stage, 0);
+    ArithWarp c;
     c.begin(&sh->sink, a.out_arena + io.out_off, io.out_cap, (d.n_streams & AVR_SLICE_ESCAPED) ? int((d.n_streams >> AVR_ESC_ZEROS_SHIFT) & 3) : -1);
-    c.run_wide(w.ctl->ring, K, nullptr, 0, sh->tab, sh->cstate, sh->stage, 0);
+    c.run(&sh->records, sh->stage2, 0);
     int status = AVR_SLICE_OK;
     uint32_t mbs = 0;
     uint64_t bins = 0;

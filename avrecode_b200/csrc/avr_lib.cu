@@ -35,23 +35,24 @@ __host__ __device__ inline size_t align_up(size_t v, size_t a) { return (v + a -
 __host__ __device__ inline size_t wide_ctl_bytes() { return align_up(sizeof(WideCtl), 256); }
 __host__ __device__ inline size_t wide_rows_bytes(uint32_t mbw) { return align_up(size_t(WIDE_MAX) * mbw * sizeof(MbCtx), 256); }
 size_t row_bytes(uint32_t max_mbw) { return align_up(size_t(max_mbw) * sizeof(MbCtx), 16); }
-size_t counters_bytes() { return align_up(size_t(MODEL_COUNTERS_PAD) * 2, 256); }
+size_t counters_bytes() { return align_up(size_t(CNT8_ENTRIES) * 2, 256); }   // split placement: the 8x8 slab of a block
 size_t smem_bytes(uint32_t max_mbw, bool resident) {
-  return sizeof(BlockShared) + row_bytes(max_mbw) + (resident ? size_t(MODEL_COUNTERS_PAD) * 2 : 0);
+  return sizeof(BlockShared) + row_bytes(max_mbw) + (resident ? size_t(MODEL_COUNTERS_PAD) : size_t(CNT_LOW_PAD)) * 2;
 }
 
 // Block = parser warp + coder warp.  Shared memory: BlockShared | MbCtx row[max_mbw] | estimators (RESIDENT).
 // Persistent blocks take jobs from an atomic counter (longest first).
 template <class Dir, bool RESIDENT>
-__global__ void __launch_bounds__(AVR_THREADS_OF(Dir), RESIDENT ? 2 : 8) avr_job_kernel(KernelArgs k) {
+__global__ void __launch_bounds__(AVR_THREADS_OF(Dir), RESIDENT ? 2 : 4) avr_job_kernel(KernelArgs k) {
   extern __shared__ __align__(16) uint8_t smem[];
   JobMem m;
   m.sh = reinterpret_cast<BlockShared*>(smem);
   m.row = reinterpret_cast<MbCtx*>(smem + sizeof(BlockShared));
   uint8_t* slot = k.workspace + uint64_t(blockIdx.x) * k.work_stride;
   const size_t rb = (size_t(k.max_mbw) * sizeof(MbCtx) + 15) / 16 * 16;
-  if (RESIDENT) m.cnt = reinterpret_cast<uint16_t*>(smem + sizeof(BlockShared) + rb);
-  else { m.cnt = reinterpret_cast<uint16_t*>(slot); slot += (size_t(MODEL_COUNTERS_PAD) * 2 + 255) / 256 * 256; }
+  m.cnt = reinterpret_cast<uint16_t*>(smem + sizeof(BlockShared) + rb);
+  if (RESIDENT) m.cnt8 = m.cnt;
+  else { m.cnt8 = reinterpret_cast<uint16_t*>(slot) - CNT8_SPLIT; slot += (size_t(CNT8_ENTRIES) * 2 + 255) / 256 * 256; }
   m.nnz0 = slot;
   m.nnz1 = slot + k.nnz_frame_bytes;
   m.nnz_frame_bytes = k.nnz_frame_bytes;
@@ -322,29 +323,21 @@ int avr_stage(avr_ctx* c, const avr_slice_desc* descs, int n, const uint8_t* in,
   c->max_mbw = std::max(c->max_mbw, c->max_mbw_wide);   // a role works in an ordinary block: its row and window
   c->max_frame_bytes = uint32_t(align_up(c->max_frame_bytes, 16));
 
-  // Placement of the estimators: in shared memory (<= 2 blocks per SM, every per-bin access at LDS
-  // latency) while the batch is small enough to be latency-bound, in the global workspace with more
-  // blocks per SM once there are enough independent jobs to hide L1/L2 latency instead.
+  // Placement of the estimators: all of them in shared memory (2 blocks per SM), or split -- the 8x8 significance
+  // slab (70 % of the table) in the global workspace behind L1 / L2, the rest in shared memory, 4 blocks per SM.
   const size_t smem_res = smem_bytes(c->max_mbw, true), smem_glb = smem_bytes(c->max_mbw, false);
   const size_t smem_sm = size_t(c->max_smem_sm);
   int res_per_sm = smem_res + 1024 <= size_t(c->max_smem_optin) ? int(smem_sm / (smem_res + 1024)) : 0;
   res_per_sm = std::min(res_per_sm, 2);
-  int glb_per_sm = std::max(1, std::min(c->cfg_warps > 0 ? c->cfg_warps : 8, int(smem_sm / (smem_glb + 1024))));
-  glb_per_sm = std::min(glb_per_sm, 8);
+  int glb_per_sm = std::max(1, std::min(c->cfg_warps > 0 ? c->cfg_warps : 4, int(smem_sm / (smem_glb + 1024))));
+  glb_per_sm = std::min(glb_per_sm, 4);
   if (smem_glb + 1024 > size_t(c->max_smem_optin)) return AVR_ERR_ARG;   // picture too wide for the neighbour row
-  // Which placement finishes the batch sooner?  A launch lasts max(total work / slots, longest job) x cycles per bin of
-  // the variant; the global-memory variant has 4x the slots but every estimator access is an L1 / L2 access on the
-  // serial chain (measured 8x the cycles per bin on the 256-clip corpus, profiles/r2i_bench.json: 2240 against 280), so
-  // as things stand it never wins and is only taken when asked for (avr_config.resident = 0) -- kept as the variant
-  // for pictures whose neighbour row leaves no room for the estimators.
-  uint64_t total_w = 0, longest_w = 0;
-  for (const JobDesc& j : c->jobs) { total_w += j.weight; longest_w = std::max<uint64_t>(longest_w, j.weight); }
+  // Measured (profiles/r2m_throughput_placement.txt, 3458 slices of 64 corpus clips): twice the blocks per SM buy
+  // nothing -- 1564 / 2521 ms (compress / decompress) resident against 1613 / 3078 ms split.  An SM issues about one
+  // instruction per cycle from these warps however many it holds (instruction fetch and branch resolution are a third
+  // of every warp's stall samples, profiles/r2m_ncu_throughput.txt), so the resident placement is taken whenever it
+  // fits; the split one is for pictures whose neighbour row leaves no room, or on request (avr_config.resident = 0).
   bool resident = res_per_sm > 0;
-  if (resident) {
-    const double t_res = double(std::max<uint64_t>(total_w / uint64_t(res_per_sm * c->sm_count), longest_w));
-    const double t_glb = 8.0 * double(std::max<uint64_t>(total_w / uint64_t(glb_per_sm * c->sm_count), longest_w));
-    resident = t_res <= t_glb;
-  }
   if (c->force_resident == 0) resident = false;
   if (c->force_resident == 1 && res_per_sm > 0) resident = true;
   c->resident = resident;

@@ -254,9 +254,10 @@ struct Walker {
         }
         mask = m32;
       } else {
+        dir.sig8_prefetch(slab, nnz_true);
 #pragma unroll 1
         while (observed < nnz_true && zz < coefs) {
-          const int s = dir.model_bit(*tab, slab + observed * SIG_ZZ + uint32_t(tab->sig8[zz]));
+          const int s = dir.sig8_bit(*tab, slab + observed * SIG_ZZ + uint32_t(tab->sig8[zz]));
           mask |= uint64_t(s) << zz;
           observed += uint32_t(s);
           zz++;
@@ -340,27 +341,42 @@ struct Walker {
     else if (top_ok && (top_flags & uses)) b = list ? top_mb->mvd1_bottom[x][comp] : top_mb->mvd_bottom[x][comp];
     return a + b;
   }
-  AVR_DEV int mvd_component(int ctxbase, int amvd) {   // h264_cabac.c:1502-1537; returns stored |mvd|
-    if (!bin(ctxbase + (amvd > 2) + (amvd > 32))) return 0;
+  // reference indices and motion vector differences run in register mode (between dir.enter() and dir.leave()): in
+  // P and B slices they are the bulk of the macroblock-level bins, a quarter of all bins (profiles/r2k_bin_classes.txt)
+  AVR_DEV int mvd_component(int ctxbase, int amvd, ResBins& rb) {   // h264_cabac.c:1502-1537; returns stored |mvd|
+    rb.mb++;
+    if (!dir.fast_bin(*tab, ctxbase + (amvd > 2) + (amvd > 32))) return 0;
     int mvd = 1;
     ctxbase += 3;
 #pragma unroll 1
-    while (mvd < 9 && bin(ctxbase)) { if (mvd < 4) ctxbase++; mvd++; }
+    for (;;) {
+      if (mvd >= 9) break;
+      rb.mb++;
+      if (!dir.fast_bin(*tab, ctxbase)) break;
+      if (mvd < 4) ctxbase++;
+      mvd++;
+    }
     if (mvd >= 9) {
       int k = 3;
 #pragma unroll 1
-      while (bypass()) { mvd += 1 << k; k++; if (k > 24) { fail(WALK_CORRUPT); break; } }
+      for (;;) {   // Exp-Golomb prefix, then k suffix bits: one inlined bypass site
+        rb.mb++;
+        if (!dir.lvl_bypass(*tab)) break;
+        mvd += 1 << k; k++;
+        if (k > 24) { fail(WALK_CORRUPT); break; }
+      }
 #pragma unroll 1
-      while (k--) mvd += bypass() << k;
+      while (k--) { rb.mb++; mvd += dir.lvl_bypass(*tab) << k; }
     }
-    bypass();   // sign
+    rb.mb++;
+    dir.lvl_bypass(*tab);   // sign
     return mvd < 70 ? mvd : 70;
   }
-  AVR_DEV void mvd_part(int list, int n, int w, int h) {
+  AVR_DEV void mvd_part(int list, int n, int w, int h, ResBins& rb) {
     int s[2];
 #pragma unroll 1
     for (int comp = 0; comp < 2; comp++) {
-      const int v = mvd_component(40 + 7 * comp, mvd_sum(list, n, comp));
+      const int v = mvd_component(40 + 7 * comp, mvd_sum(list, n, comp), rb);
       if (comp == 0) s[0] = v; else s[1] = v;
     }
     const int x = blk_x(n), y = blk_y(n);
@@ -382,13 +398,15 @@ struct Walker {
     if (is_b && ((dir8 >> b8) & 1)) return 0;
     return int((refpos >> (4 * list + b8)) & 1);
   }
-  AVR_DEV int read_ref(int list, int n) {   // h264_cabac.c:1473-1500 with the rc > 1 guard of :2232-2240
+  AVR_DEV int read_ref(int list, int n, ResBins& rb) {   // h264_cabac.c:1473-1500 with the rc > 1 guard of :2232-2240
     const int rc = list ? num_ref_l1 : num_ref_l0;
     if (rc <= 1) return 0;
     int ctx = ref_pos_neighbor(list, n, false) + 2 * ref_pos_neighbor(list, n, true);
     int ref = 0;
 #pragma unroll 1
-    while (bin(54 + ctx)) {
+    for (;;) {
+      rb.mb++;
+      if (!dir.fast_bin(*tab, 54 + ctx)) break;
       ref++;
       ctx = (ctx >> 2) + 4;
       if (ref >= 32) { fail(WALK_CORRUPT); break; }
@@ -580,6 +598,8 @@ struct Walker {
         // partitions: 16x16 one, 16x8 / 8x16 two, 8x8 four quadrants (h264_cabac.c:2114-2330); for every
         // list all reference indices first, then for every list all motion vector differences
         const int nq = shape == 4 ? 4 : (shape == 1 ? 1 : 2);
+        dir.enter(*tab);
+        ResBins bins; bins.clear();
 #pragma unroll 1
         for (int list = 0; list < lists; list++) {
 #pragma unroll 1
@@ -588,7 +608,7 @@ struct Walker {
             if (!((pr >> list) & 1)) continue;
             const int n = shape == 2 ? 8 * q : (shape == 1 ? 0 : 4 * q);
             const uint32_t covers = shape == 1 ? 0xFu : shape == 2 ? (3u << (2 * q)) : shape == 3 ? (5u << q) : (1u << q);
-            if (read_ref(list, n) > 0) cur_refpos |= covers << (4 * list);
+            if (read_ref(list, n, bins) > 0) cur_refpos |= covers << (4 * list);
           }
         }
 #pragma unroll 1
@@ -606,38 +626,57 @@ struct Walker {
             else if (shape == 2) { base = 8 * q; w = 4; h = 2; }
             else { base = 4 * q; w = 2; h = 4; }
 #pragma unroll 1
-            for (int j = 0; j < cnt; j++) mvd_part(list, base + j * stride, w, h);
+            for (int j = 0; j < cnt; j++) mvd_part(list, base + j * stride, w, h, bins);
           }
         }
+        dir.leave(bins);
       }
     }
 
+    // Everything from here to the end of the macroblock runs in register mode: coded_block_pattern, the
+    // transform-size flag, mb_qp_delta (six inlined bin sites) and the residual blocks.
+    // First bin of mb_qp_delta: in a wide slice the first macroblock of a row cannot see how the previous row ended, so
+    // that bin crosses the ring as a special entry -- on the home state, before the region, and only once it is known
+    // that the macroblock has one (I16: no coded_block_pattern in between; else after it, which costs such a
+    // macroblock a second enter / leave pair).
+    const bool row_qpd = wide_k && mb_x == 0;
+    const int qctx = 60 + (last_qp_delta != 0);
+    int q1 = -1;
+    if (row_qpd && i16) q1 = dir.bin_row_qpd(qctx);
+    dir.enter(*tab);
+    ResBins bins; bins.clear();
     if (!i16) {   // coded_block_pattern (h264_cabac.c:1408-1443)
       const uint32_t a = left_cbp, b = top_cbp;
-      int c = 0;
-      c += bin(73 + !(a & 2) + 2 * !(b & 4));
-      c += bin(73 + !(c & 1) + 2 * !(b & 8)) << 1;
-      c += bin(73 + !(a & 8) + 2 * !(c & 1)) << 2;
-      c += bin(73 + !(c & 4) + 2 * !(c & 2)) << 3;
+      uint32_t c = 0;
+#pragma unroll 1
+      for (int i = 0; i < 4; i++) {   // luma: the 8x8 to the left / above, inside the macroblock or in the neighbour
+        const uint32_t lf = (i & 1) ? (c >> (i - 1)) & 1 : (a >> (1 + i)) & 1;
+        const uint32_t tp = (i & 2) ? (c >> (i - 2)) & 1 : (b >> (2 + i)) & 1;
+        bins.mb++;
+        c |= uint32_t(dir.fast_bin(*tab, 73 + int(!lf) + 2 * int(!tp))) << i;
+      }
       const int ca = int((a >> 4) & 3), cb = int((b >> 4) & 3);
-      if (bin(77 + (ca > 0) + 2 * (cb > 0))) c |= (1 + bin(77 + 4 + (ca == 2) + 2 * (cb == 2))) << 4;
-      cbp = c;
+      bins.mb++;
+      if (dir.fast_bin(*tab, 77 + (ca > 0) + 2 * (cb > 0))) { bins.mb++; c |= uint32_t(1 + dir.fast_bin(*tab, 77 + 4 + (ca == 2) + 2 * (cb == 2))) << 4; }
+      cbp = int(c);
     }
     cur_cbp = uint32_t(cbp);
-    if (t8_allowed && (cbp & 15) && !intra) t8 = bin(CTX_T8X8 + nts) != 0;   // h264_cabac.c:2348-2350
+    if (t8_allowed && (cbp & 15) && !intra) { bins.mb++; t8 = dir.fast_bin(*tab, CTX_T8X8 + nts) != 0; }   // h264_cabac.c:2348-2350
     if (t8) cur_flags |= MBF_T8x8;
 
     if (cbp || i16) {
       // mb_qp_delta (h264_cabac.c:2388-2416)
-      // first bin: in a wide slice the first macroblock of a row cannot see how the previous row ended
-      const int qctx = 60 + (last_qp_delta != 0);
-      int q1;
-      if (wide_k && mb_x == 0) q1 = dir.bin_row_qpd(qctx);
-      else q1 = bin(qctx);
+      if (row_qpd && !i16) { dir.leave(bins); bins.clear(); q1 = dir.bin_row_qpd(qctx); dir.enter(*tab); }
+      if (q1 < 0) { bins.mb++; q1 = dir.fast_bin(*tab, qctx); }
       if (q1) {
         int val = 1, ctx = 2;
 #pragma unroll 1
-        while (bin(60 + ctx)) { ctx = 3; val++; if (val > 102) { fail(WALK_CORRUPT); break; } }
+        for (;;) {
+          bins.mb++;
+          if (!dir.fast_bin(*tab, 60 + ctx)) break;
+          ctx = 3; val++;
+          if (val > 102) { fail(WALK_CORRUPT); break; }
+        }
         last_qp_delta = val;   // only "!= 0" is ever read
       } else last_qp_delta = 0;
       // residual blocks in coding order (h264_cabac.c:1874-1920, 2449-2463), one loop, one call site:
@@ -645,9 +684,7 @@ struct Walker {
       //   k = 1..16    luma 4x4 blocks 0..15  cat 1 (I16 AC) / 2 (4x4) / 5 (8x8, first block of a quadrant only)
       //   k = 17,18    chroma DC Cb, Cr       cat 3, blocks 49, 50
       //   k = 19..26   chroma AC              cat 4, blocks 16..19, 32..35
-      // the whole loop runs in register mode: coded_block_flag bins (one inlined site) and the blocks
-      dir.enter(*tab);
-      ResBins bins; bins.clear();
+      // coded_block_flag bins: one inlined site
 #pragma unroll 1
       for (int k = i16 ? 0 : 1; k < 27; k++) {
         int cat, blk, maxc;
@@ -674,8 +711,8 @@ struct Walker {
         else if (cat == 5) nzmask |= uint64_t(0xF) << blk;
         else nzmask |= uint64_t(1) << blk;
       }
-      dir.leave(bins);
     } else last_qp_delta = 0;
+    dir.leave(bins);
   }
 
   // what the neighbours will need from this macroblock -> row[mb_x] and ws->left

@@ -41,7 +41,7 @@ static int run(const avr_slice_desc* descs, int n, const uint8_t* in, uint64_t i
   g_hist.assign(size_t(n) * 8, 0);
   JobArgs a{descs, ios.data(), in, arena.data(), res, g_hist.data()};
   JobMem m;
-  m.sh = sh; m.row = row.data(); m.cnt = counters.data();
+  m.sh = sh; m.row = row.data(); m.cnt = counters.data(); m.cnt8 = m.cnt;
   m.nnz0 = planes.data(); m.nnz1 = planes.data() + max_frame; m.nnz_frame_bytes = max_frame; m.max_mbw = uint32_t(max_mbw);
   // wide slices (n_streams >= 2): one set of block state per role, the shared control block / rows / rings on the heap
   std::vector<BlockShared*> wsh;
@@ -52,7 +52,7 @@ static int run(const avr_slice_desc* descs, int n, const uint8_t* in, uint64_t i
     wsh.push_back(new BlockShared());
     fill_shared_tables(&wsh[r]->tab, 0, 1);
     wmems[r] = m;
-    wmems[r].sh = wsh[r]; wmems[r].row = wrow[r].data(); wmems[r].cnt = wcnt[r].data();
+    wmems[r].sh = wsh[r]; wmems[r].row = wrow[r].data(); wmems[r].cnt = wcnt[r].data(); wmems[r].cnt8 = wmems[r].cnt;
   }
   std::vector<MbCtx> wrows(size_t(WIDE_MAX) * max_mbw);
   int i = 0;
