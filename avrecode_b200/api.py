@@ -283,3 +283,54 @@ class Context:
 
     def files_decompress(self, recs):
         return self._many(self._lib.avr_files_decompress, "avr_files_decompress", recs)
+
+
+class MultiContext:
+    """Several CUDA devices of one node behind one handle (avr_multi_*): the slices (MODE_SLICE) or files (MODE_FILE) of
+    a call are dealt out over the devices, longest first; the containers are those one device writes."""
+
+    def __init__(self, devices, **config):
+        self._lib = load_library()
+        lib = self._lib
+        lib.avr_multi_create.argtypes = [C.POINTER(Config), C.POINTER(C.c_int), C.c_int, C.POINTER(C.c_void_p)]
+        lib.avr_multi_destroy.argtypes = [C.c_void_p]
+        lib.avr_multi_destroy.restype = None
+        lib.avr_multi_devices.argtypes = [C.c_void_p]
+        many = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_uint64), C.c_int]
+        lib.avr_multi_files_compress.argtypes = many + [C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]
+        lib.avr_multi_files_decompress.argtypes = many + [C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]
+        cfg = Config()
+        lib.avr_config_init(C.byref(cfg))
+        for k, v in config.items():
+            if not hasattr(cfg, k) or k in ("abi_version", "device", "reserved"):
+                raise TypeError("MultiContext: unknown option %r" % k)
+            setattr(cfg, k, v)
+        devs = (C.c_int * max(1, len(devices)))(*devices)
+        h = C.c_void_p()
+        _check(lib.avr_multi_create(C.byref(cfg), devs, len(devices), C.byref(h)), "avr_multi_create")
+        self._h = h
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._lib.avr_multi_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    @property
+    def n_devices(self):
+        return self._lib.avr_multi_devices(self._h)
+
+    _many = Context._many
+
+    def files_compress(self, files, mode=MODE_SLICE):
+        return self._many(self._lib.avr_multi_files_compress, "avr_multi_files_compress", files, C.c_int(mode))
+
+    def files_decompress(self, recs):
+        return self._many(self._lib.avr_multi_files_decompress, "avr_multi_files_decompress", recs)

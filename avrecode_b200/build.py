@@ -4,6 +4,7 @@
   avrecode_b200/recode                drop-in CLI linked against the .so
   oracle/_build/libavr_oracle.so      CPU restatement (test infrastructure)
   build/libavr_emu.so                 host emulation of the device code (test infrastructure)
+  build/libavr_emu_file.so            avr_file.cpp + h264_index.cpp on top of that emulation (test infrastructure)
   build/h264gen                       synthetic stream generator (test infrastructure)
   oracle/_ref/*                       the unmodified reference, only where /root/reference exists
 
@@ -50,14 +51,14 @@ def build(force=False, with_ref=True):
             if src.endswith(".cu"):
                 cmd = [NVCC, "-std=c++17", *ARCH, "-lineinfo", "-O3", "-Xcompiler", "-fPIC", "-c", "-o", obj, src]
             else:
-                cmd = ["g++", "-std=c++17", "-O2", "-fPIC", "-c", "-o", obj, src]
+                cmd = ["g++", "-std=c++17", "-O2", "-fPIC", "-pthread", "-c", "-o", obj, src]
             print("+", " ".join(cmd), flush=True)
             jobs.append((cmd, subprocess.Popen(cmd, cwd=ROOT)))
     for cmd, p in jobs:
         if p.wait() != 0:
             raise subprocess.CalledProcessError(p.returncode, cmd)
     if force or jobs or _newer(lib, objs):
-        _run([NVCC, *ARCH, "-shared", "-cudart", "static", "-o", lib, *objs])
+        _run([NVCC, *ARCH, "-shared", "-cudart", "static", "-Xcompiler", "-pthread", "-o", lib, *objs])
     cli = os.path.join(ROOT, "avrecode_b200", "recode")
     cli_src = [os.path.join(CSRC, "recode_main.cpp")]
     if force or _newer(cli, cli_src + [lib]):
@@ -71,6 +72,12 @@ def build(force=False, with_ref=True):
     emu_src = [os.path.join(ROOT, "tests", "emu", "avr_emu.cpp")]
     if force or _newer(emu, emu_src + hdrs):
         _run(["g++", "-std=c++17", "-O2", "-shared", "-fPIC", "-o", emu, emu_src[0]])
+    # the product's host file layer on top of the emulation (multi-device sharding, container codec: CPU tests)
+    emuf = os.path.join(ROOT, "build", "libavr_emu_file.so")
+    emuf_src = [os.path.join(ROOT, "tests", "emu", "avr_emu_file.cpp"), emu_src[0], os.path.join(CSRC, "avr_file.cpp"),
+                os.path.join(CSRC, "h264_index.cpp")]
+    if force or _newer(emuf, emuf_src + hdrs):
+        _run(["g++", "-std=c++17", "-O2", "-shared", "-fPIC", "-pthread", "-o", emuf, emuf_src[0], emuf_src[2], emuf_src[3]])
     gen = os.path.join(ROOT, "build", "h264gen")
     gen_src = [os.path.join(ROOT, "tools", "h264gen.cpp"), ora_src[1]]
     if force or _newer(gen, gen_src + hdrs):

@@ -9,7 +9,10 @@
 #include <stdint.h>
 #include <stdlib.h>
 #include <string.h>
+#include <algorithm>
 #include <string>
+#include <thread>
+#include <new>
 #include <vector>
 #include "../../include/avrecode_b200.h"
 
@@ -162,6 +165,80 @@ void emit_block(std::string& out, const std::string& body) {
   out.append(body);
 }
 
+// The devices a file call runs on: one context (avr_file_* / avr_files_*) or the contexts of an avr_multi.
+struct DevSet { avr_ctx* const* ctx; int n; };
+
+// One batch of slices over the devices of `ds`.  A UNIT is a run of slices that share a model -- from one
+// AVR_SLICE_NEW_MODEL to the next: a slice in chunked mode, a file in the reference's mode -- and units are independent,
+// so they are dealt out over the devices longest first (by input bytes) with no exchange between devices: every device
+// gets its own compact arena (only the bytes of its slices travel) and runs its share on a host thread of its own.
+// out_at[i]: where slice i's output bytes are (in the buffer of the context that produced them, valid until that
+// context's next call).
+int run_batch(const DevSet& ds, int direction, const std::vector<avr_slice_desc>& descs, const uint8_t* arena, uint64_t arena_bytes,
+              std::vector<avr_slice_result>* res, std::vector<const uint8_t*>* out_at) {
+  const size_t n = descs.size();
+  res->assign(n, avr_slice_result());
+  out_at->assign(n, nullptr);
+  auto call = direction == 0 ? avr_compress : avr_decompress;
+  if (ds.n == 1) {
+    const uint8_t* out = nullptr;
+    uint64_t out_bytes = 0;
+    const int rc = call(ds.ctx[0], descs.data(), int(n), arena ? arena : reinterpret_cast<const uint8_t*>(""), arena_bytes, res->data(), &out, &out_bytes);
+    if (rc) return rc;
+    for (size_t i = 0; i < n; i++) (*out_at)[i] = out + (*res)[i].out_off;
+    return AVR_OK;
+  }
+  struct Unit { size_t first, count; uint64_t weight; };
+  std::vector<Unit> units;
+  for (size_t i = 0; i < n; i++) {
+    if (units.empty() || (descs[i].flags & AVR_SLICE_NEW_MODEL)) units.push_back(Unit{i, 0, 0});
+    units.back().count++;
+    units.back().weight += descs[i].in_size + 64;
+  }
+  std::vector<size_t> order(units.size());
+  for (size_t u = 0; u < units.size(); u++) order[u] = u;
+  std::stable_sort(order.begin(), order.end(), [&](size_t a, size_t b) { return units[a].weight > units[b].weight; });
+  struct Share { std::vector<size_t> idx; std::vector<avr_slice_desc> descs; std::vector<uint8_t> arena; std::vector<avr_slice_result> res;
+                 const uint8_t* out = nullptr; uint64_t out_bytes = 0, load = 0; int rc = AVR_OK; };
+  std::vector<Share> shares(size_t(ds.n));
+  for (size_t u : order) {   // longest first onto the least loaded device
+    size_t best = 0;
+    for (size_t k = 1; k < shares.size(); k++) if (shares[k].load < shares[best].load) best = k;
+    shares[best].load += units[u].weight;
+    for (size_t i = units[u].first; i < units[u].first + units[u].count; i++) shares[best].idx.push_back(i);
+  }
+  for (Share& sh : shares) {
+    std::sort(sh.idx.begin(), sh.idx.end());   // units stay contiguous and in file order
+    for (size_t i : sh.idx) {
+      avr_slice_desc d = descs[i];
+      const size_t at = (sh.arena.size() + 15) & ~size_t(15);
+      sh.arena.resize(at);
+      if (d.in_size) {
+        if (uint64_t(d.in_off) + d.in_size > arena_bytes) return AVR_ERR_ARG;
+        sh.arena.insert(sh.arena.end(), arena + d.in_off, arena + d.in_off + d.in_size);
+      }
+      d.in_off = at;
+      sh.descs.push_back(d);
+    }
+    sh.arena.resize(sh.arena.size() + 16);
+    sh.res.assign(sh.descs.size(), avr_slice_result());
+  }
+  std::vector<std::thread> threads;
+  for (int k = 0; k < ds.n; k++) {
+    threads.emplace_back([&, k]() {
+      Share& sh = shares[size_t(k)];
+      if (sh.descs.empty()) return;
+      sh.rc = call(ds.ctx[k], sh.descs.data(), int(sh.descs.size()), sh.arena.data(), sh.arena.size(), sh.res.data(), &sh.out, &sh.out_bytes);
+    });
+  }
+  for (std::thread& t : threads) t.join();
+  for (const Share& sh : shares) {
+    if (sh.rc) return sh.rc;
+    for (size_t k = 0; k < sh.idx.size(); k++) { (*res)[sh.idx[k]] = sh.res[k]; (*out_at)[sh.idx[k]] = sh.out + sh.res[k].out_off; }
+  }
+  return AVR_OK;
+}
+
 int to_malloc(const std::string& s, uint8_t** p, uint64_t* n) {
   *p = static_cast<uint8_t*>(malloc(s.size() ? s.size() : 1));
   if (!*p) return AVR_ERR_NOMEM;
@@ -183,8 +260,9 @@ int avr_ctx_slice_streams(avr_ctx* ctx, const avr_slice_desc* desc, int n_batch_
 
 // Shared driver of avr_file_compress / avr_files_compress: all CABAC slices of all files go to the
 // device as ONE batch (files are independent, so in either mode every file starts a fresh model).
-static int compress_many(avr_ctx* ctx, const uint8_t* const* files, const uint64_t* sizes, int n_files, int mode,
+static int compress_many(const DevSet& ds, const uint8_t* const* files, const uint64_t* sizes, int n_files, int mode,
                          uint8_t** recs, uint64_t* rec_sizes) {
+  avr_ctx* ctx = ds.ctx[0];   // the policy (wide slices) is that of the first context
   struct Plan {
     avr_index_entry* ents = nullptr;
     int n_ents = 0;
@@ -262,8 +340,7 @@ static int compress_many(avr_ctx* ctx, const uint8_t* const* files, const uint64
   const uint32_t per_stream = mode == AVR_MODE_SLICE ? wide_stream_bytes(ctx, n_batch) : 0;
   std::vector<avr_slice_desc> descs;
   std::vector<avr_slice_result> res;
-  const uint8_t* out = nullptr;
-  uint64_t out_bytes = 0;
+  std::vector<const uint8_t*> out_at;
   // In file mode the slices of a file share one model, so a slice the device rejects poisons everything
   // after it; drop it (it becomes skip_coded + literal, recode.cpp:1289-1296) and run again.
   for (int attempt = 0; attempt < 64; attempt++) {
@@ -286,9 +363,7 @@ static int compress_many(avr_ctx* ctx, const uint8_t* const* files, const uint64
         p.map.push_back(i);
       }
     }
-    res.assign(descs.size(), avr_slice_result());
-    int rc = avr_compress(ctx, descs.data(), int(descs.size()), arena ? arena : reinterpret_cast<const uint8_t*>(""),
-                          arena_bytes, res.data(), &out, &out_bytes);
+    int rc = run_batch(ds, 0, descs, arena, arena_bytes, &res, &out_at);
     if (rc) { cleanup(); return rc; }
     // slice mode: a failed slice becomes a literal, done.  File mode: the first slice of a file that fails poisons the
     // model of everything behind it (those come back CORRUPT whatever they are): drop it, and with it every slice the
@@ -330,7 +405,7 @@ static int compress_many(avr_ctx* ctx, const uint8_t* const* files, const uint64
         put_len(lit, 2, file + prev, size_t(d.in_off - prev));
         emit_block(o, lit);
         put_var(body, 1, d.payload_size);
-        put_len(body, 4, out + r->out_off, r->out_size);
+        put_len(body, 4, out_at[p.first + k], r->out_size);
         put_var(body, 5, d.payload_size & 1);
         if (d.payload_size > 1) put_len(body, 6, file + d.in_off + d.payload_size - 1, 1);
         if ((descs[p.first + k].n_streams & AVR_STREAMS_MASK) >= 2) put_var(body, 7, descs[p.first + k].n_streams & AVR_STREAMS_MASK);
@@ -355,7 +430,8 @@ static int compress_many(avr_ctx* ctx, const uint8_t* const* files, const uint64
 
 int avr_file_compress(avr_ctx* ctx, const uint8_t* file, uint64_t file_bytes, int mode, uint8_t** rec, uint64_t* rec_bytes) {
   if (!ctx || !file || !rec || !rec_bytes || (mode != AVR_MODE_FILE && mode != AVR_MODE_SLICE)) return AVR_ERR_ARG;
-  return compress_many(ctx, &file, &file_bytes, 1, mode, rec, rec_bytes);
+  const DevSet ds{&ctx, 1};
+  return compress_many(ds, &file, &file_bytes, 1, mode, rec, rec_bytes);
 }
 
 int avr_files_compress(avr_ctx* ctx, const uint8_t* const* files, const uint64_t* file_bytes, int n_files, int mode,
@@ -364,13 +440,14 @@ int avr_files_compress(avr_ctx* ctx, const uint8_t* const* files, const uint64_t
       (mode != AVR_MODE_FILE && mode != AVR_MODE_SLICE)) return AVR_ERR_ARG;
   for (int f = 0; f < n_files; f++) { if (!files[f]) return AVR_ERR_ARG; recs[f] = nullptr; rec_bytes[f] = 0; }
   if (n_files == 0) return AVR_OK;
-  int rc = compress_many(ctx, files, file_bytes, n_files, mode, recs, rec_bytes);
+  const DevSet ds{&ctx, 1};
+  int rc = compress_many(ds, files, file_bytes, n_files, mode, recs, rec_bytes);
   if (rc) for (int f = 0; f < n_files; f++) { free(recs[f]); recs[f] = nullptr; rec_bytes[f] = 0; }
   return rc;
 }
 
 // Shared driver of avr_file_decompress / avr_files_decompress: every Block.cabac of every container in one batch.
-static int decompress_many(avr_ctx* ctx, const uint8_t* const* recs, const uint64_t* rec_sizes, int n_files,
+static int decompress_many(const DevSet& ds, const uint8_t* const* recs, const uint64_t* rec_sizes, int n_files,
                            uint8_t** files, uint64_t* file_sizes) {
   struct CodedRef { size_t block; uint64_t off; bool is_cabac; };
   struct Plan {
@@ -441,12 +518,10 @@ static int decompress_many(avr_ctx* ctx, const uint8_t* const* recs, const uint6
     p.count = p.which.size();
     free(ents);
   }
-  std::vector<avr_slice_result> res(descs.size());
-  const uint8_t* out = nullptr;
-  uint64_t out_bytes = 0;
+  std::vector<avr_slice_result> res;
+  std::vector<const uint8_t*> out_at;
   if (in.empty()) in.push_back(0);
-  int rc = avr_decompress(ctx, descs.data(), int(descs.size()), reinterpret_cast<const uint8_t*>(in.data()), in.size(),
-                          res.data(), &out, &out_bytes);
+  int rc = run_batch(ds, 1, descs, reinterpret_cast<const uint8_t*>(in.data()), in.size(), &res, &out_at);
   if (rc) return rc;
   // 3. splice the rebuilt payloads in, with the x264 padding fix-up of recode.cpp:1345-1354
   for (int f = 0; f < n_files; f++) {
@@ -457,7 +532,7 @@ static int decompress_many(avr_ctx* ctx, const uint8_t* const* recs, const uint6
       if (descs[p.first + k].flags & AVR_SLICE_SKIP) continue;
       const CodedRef& cr = p.coded[p.which[k]];
       const Block& b = p.blocks[cr.block];
-      std::string bytes(reinterpret_cast<const char*>(out + r.out_off), r.out_size);
+      std::string bytes(reinterpret_cast<const char*>(out_at[p.first + k]), r.out_size);
       if (b.has_parity && b.has_last && b.last_n > 0) {
         if (int(b.parity) != int(bytes.size() & 1)) bytes.push_back(char(b.last[0]));
         else if (!bytes.empty()) bytes[bytes.size() - 1] = char(b.last[0]);
@@ -477,7 +552,8 @@ static int decompress_many(avr_ctx* ctx, const uint8_t* const* recs, const uint6
 int avr_file_decompress(avr_ctx* ctx, const uint8_t* rec, uint64_t rec_bytes, uint8_t** file, uint64_t* file_bytes) {
   if (!ctx || !rec || !file || !file_bytes) return AVR_ERR_ARG;
   *file = nullptr; *file_bytes = 0;
-  return decompress_many(ctx, &rec, &rec_bytes, 1, file, file_bytes);
+  const DevSet ds{&ctx, 1};
+  return decompress_many(ds, &rec, &rec_bytes, 1, file, file_bytes);
 }
 
 int avr_files_decompress(avr_ctx* ctx, const uint8_t* const* recs, const uint64_t* rec_bytes, int n_files,
@@ -485,7 +561,60 @@ int avr_files_decompress(avr_ctx* ctx, const uint8_t* const* recs, const uint64_
   if (!ctx || n_files < 0 || (n_files > 0 && (!recs || !rec_bytes || !files || !file_bytes))) return AVR_ERR_ARG;
   for (int f = 0; f < n_files; f++) { if (!recs[f]) return AVR_ERR_ARG; files[f] = nullptr; file_bytes[f] = 0; }
   if (n_files == 0) return AVR_OK;
-  int rc = decompress_many(ctx, recs, rec_bytes, n_files, files, file_bytes);
+  const DevSet ds{&ctx, 1};
+  int rc = decompress_many(ds, recs, rec_bytes, n_files, files, file_bytes);
+  if (rc) for (int f = 0; f < n_files; f++) { free(files[f]); files[f] = nullptr; file_bytes[f] = 0; }
+  return rc;
+}
+
+// ---- several devices behind one handle ---------------------------------------------------------------
+struct avr_multi { std::vector<avr_ctx*> ctx; };
+
+int avr_multi_create(const avr_config* cfg, const int* devices, int n_devices, avr_multi** out) {
+  if (!out) return AVR_ERR_ARG;
+  *out = nullptr;
+  if (n_devices < 1 || n_devices > 64 || !devices) return AVR_ERR_ARG;
+  for (int i = 0; i < n_devices; i++) for (int j = 0; j < i; j++) if (devices[i] == devices[j]) return AVR_ERR_ARG;
+  avr_multi* m = new (std::nothrow) avr_multi();
+  if (!m) return AVR_ERR_NOMEM;
+  for (int i = 0; i < n_devices; i++) {
+    avr_config c;
+    if (cfg) c = *cfg; else avr_config_init(&c);
+    c.device = devices[i];
+    avr_ctx* x = nullptr;
+    const int rc = avr_create(&c, &x);
+    if (rc) { avr_multi_destroy(m); return rc; }
+    m->ctx.push_back(x);
+  }
+  *out = m;
+  return AVR_OK;
+}
+void avr_multi_destroy(avr_multi* m) {
+  if (!m) return;
+  for (avr_ctx* c : m->ctx) avr_destroy(c);
+  delete m;
+}
+int avr_multi_devices(const avr_multi* m) { return m ? int(m->ctx.size()) : 0; }
+avr_ctx* avr_multi_ctx(avr_multi* m, int i) { return m && i >= 0 && size_t(i) < m->ctx.size() ? m->ctx[size_t(i)] : nullptr; }
+
+int avr_multi_files_compress(avr_multi* m, const uint8_t* const* files, const uint64_t* file_bytes, int n_files, int mode,
+                             uint8_t** recs, uint64_t* rec_bytes) {
+  if (!m || m->ctx.empty() || n_files < 0 || (n_files > 0 && (!files || !file_bytes || !recs || !rec_bytes)) ||
+      (mode != AVR_MODE_FILE && mode != AVR_MODE_SLICE)) return AVR_ERR_ARG;
+  for (int f = 0; f < n_files; f++) { if (!files[f]) return AVR_ERR_ARG; recs[f] = nullptr; rec_bytes[f] = 0; }
+  if (n_files == 0) return AVR_OK;
+  const DevSet ds{m->ctx.data(), int(m->ctx.size())};
+  int rc = compress_many(ds, files, file_bytes, n_files, mode, recs, rec_bytes);
+  if (rc) for (int f = 0; f < n_files; f++) { free(recs[f]); recs[f] = nullptr; rec_bytes[f] = 0; }
+  return rc;
+}
+int avr_multi_files_decompress(avr_multi* m, const uint8_t* const* recs, const uint64_t* rec_bytes, int n_files,
+                               uint8_t** files, uint64_t* file_bytes) {
+  if (!m || m->ctx.empty() || n_files < 0 || (n_files > 0 && (!recs || !rec_bytes || !files || !file_bytes))) return AVR_ERR_ARG;
+  for (int f = 0; f < n_files; f++) { if (!recs[f]) return AVR_ERR_ARG; files[f] = nullptr; file_bytes[f] = 0; }
+  if (n_files == 0) return AVR_OK;
+  const DevSet ds{m->ctx.data(), int(m->ctx.size())};
+  int rc = decompress_many(ds, recs, rec_bytes, n_files, files, file_bytes);
   if (rc) for (int f = 0; f < n_files; f++) { free(files[f]); files[f] = nullptr; file_bytes[f] = 0; }
   return rc;
 }

@@ -3,6 +3,7 @@
 // Options come from the environment so the argv surface stays identical:
 //   AVR_MODE=slice (default; B200 chunked format) | file (reference-parity bytes)
 //   AVR_DEVICE=<cuda ordinal>
+//   AVR_DEVICES=<ordinal>,<ordinal>,...   several devices: the slices (AVR_MODE=slice) of the file are dealt out over them
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
@@ -28,14 +29,25 @@ void check(int rc, const char* what) {
 }
 
 struct Ctx {
-  avr_ctx* c = nullptr;
+  avr_multi* m = nullptr;
   Ctx() {
     avr_config cfg;
     avr_config_init(&cfg);
-    cfg.device = getenv("AVR_DEVICE") ? atoi(getenv("AVR_DEVICE")) : 0;
-    check(avr_create(&cfg, &c), "avr_create");
+    std::vector<int> devices;
+    if (const char* list = getenv("AVR_DEVICES")) {
+      for (const char* p = list; *p;) {
+        char* end = nullptr;
+        const long v = strtol(p, &end, 10);
+        if (end == p) throw std::invalid_argument(std::string("AVR_DEVICES: not a list of device ordinals: ") + list);
+        devices.push_back(int(v));
+        p = *end == ',' ? end + 1 : end;
+        if (*end && *end != ',') throw std::invalid_argument(std::string("AVR_DEVICES: not a list of device ordinals: ") + list);
+      }
+    }
+    if (devices.empty()) devices.push_back(getenv("AVR_DEVICE") ? atoi(getenv("AVR_DEVICE")) : 0);
+    check(avr_multi_create(&cfg, devices.data(), int(devices.size()), &m), "avr_multi_create");
   }
-  ~Ctx() { avr_destroy(c); }
+  ~Ctx() { avr_multi_destroy(m); }
 };
 
 int mode_from_env() {
@@ -46,14 +58,17 @@ int mode_from_env() {
 
 std::string compress(Ctx& ctx, const std::vector<uint8_t>& in) {
   uint8_t* rec = nullptr; uint64_t n = 0;
-  check(avr_file_compress(ctx.c, in.data(), in.size(), mode_from_env(), &rec, &n), "compress");
+  const uint8_t* file = in.data();
+  const uint64_t size = in.size();
+  check(avr_multi_files_compress(ctx.m, &file, &size, 1, mode_from_env(), &rec, &n), "compress");
   std::string s(reinterpret_cast<char*>(rec), size_t(n));
   avr_free(rec);
   return s;
 }
 std::string decompress(Ctx& ctx, const uint8_t* p, size_t n_in) {
   uint8_t* out = nullptr; uint64_t n = 0;
-  check(avr_file_decompress(ctx.c, p, n_in, &out, &n), "decompress");
+  const uint64_t size = n_in;
+  check(avr_multi_files_decompress(ctx.m, &p, &size, 1, &out, &n), "decompress");
   std::string s(reinterpret_cast<char*>(out), size_t(n));
   avr_free(out);
   return s;

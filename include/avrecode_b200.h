@@ -223,6 +223,22 @@ int  avr_files_compress(avr_ctx* ctx, const uint8_t* const* files, const uint64_
                         uint8_t** recs, uint64_t* rec_bytes);
 int  avr_files_decompress(avr_ctx* ctx, const uint8_t* const* recs, const uint64_t* rec_bytes, int n_files,
                           uint8_t** files, uint64_t* file_bytes);
+
+/* ---- several devices of one node behind one handle ----------------------------------------------------------------
+ * The reference runs one file on one core (recode.cpp main); its unit of parallelism is the process.  Here the units are
+ * the slices (AVR_MODE_SLICE) or the files (AVR_MODE_FILE: the slices of a file share one model) of a call: they are dealt
+ * out over the devices longest first, every device gets only the bytes of its share and runs it on a host thread of its
+ * own, and nothing is exchanged between devices (the path shards, it has no collective).  The containers
+ * are byte-identical to what one device writes.  `cfg` as for avr_create (its `device` is ignored; NULL = defaults). */
+typedef struct avr_multi avr_multi;
+int  avr_multi_create(const avr_config* cfg, const int* devices, int n_devices, avr_multi** out);
+void avr_multi_destroy(avr_multi* m);
+int  avr_multi_devices(const avr_multi* m);
+avr_ctx* avr_multi_ctx(avr_multi* m, int i);   /* the context of device i (owned by m) */
+int  avr_multi_files_compress(avr_multi* m, const uint8_t* const* files, const uint64_t* file_bytes, int n_files, int mode,
+                              uint8_t** recs, uint64_t* rec_bytes);
+int  avr_multi_files_decompress(avr_multi* m, const uint8_t* const* recs, const uint64_t* rec_bytes, int n_files,
+                                uint8_t** files, uint64_t* file_bytes);
 void avr_free(void* p);
 
 /* ---- measurement: single-lane microbenchmarks of the per-bin primitives ------------------------

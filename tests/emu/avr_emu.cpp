@@ -11,7 +11,7 @@
 
 using namespace avr;
 
-static std::vector<uint32_t> g_hist;   // per-class bin counts of the last call
+static thread_local std::vector<uint32_t> g_hist;   // per-class bin counts of the last call (of this thread)
 
 template <class Dir>
 static int run(const avr_slice_desc* descs, int n, const uint8_t* in, uint64_t in_bytes, avr_slice_result* res,

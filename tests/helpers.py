@@ -165,3 +165,52 @@ def escaped_slice_case(data, entries):
             d.flags |= _abi.AVR_SLICE_NEW_MODEL
             return e, d, raw, e.desc.n_streams & 0xF0
     return None
+
+
+# ---- the product's host file layer on top of the emulation (build/libavr_emu_file.so, tests/emu/avr_emu_file.cpp) ----
+_emu_file = None
+
+
+def emu_file_lib():
+    global _emu_file
+    if _emu_file is None:
+        lib = C.CDLL(os.path.join(ROOT, "build", "libavr_emu_file.so"))
+        u8p = C.POINTER(C.c_uint8)
+        lib.avr_create.argtypes = [C.c_void_p, C.POINTER(C.c_void_p)]
+        lib.avr_destroy.argtypes = [C.c_void_p]
+        lib.avr_destroy.restype = None
+        lib.avr_multi_create.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.c_int, C.POINTER(C.c_void_p)]
+        lib.avr_multi_destroy.argtypes = [C.c_void_p]
+        lib.avr_multi_destroy.restype = None
+        lib.avr_multi_ctx.argtypes = [C.c_void_p, C.c_int]
+        lib.avr_multi_ctx.restype = C.c_void_p
+        lib.avr_emu_ctx_calls.argtypes = [C.c_void_p]
+        many = [C.c_void_p, C.POINTER(u8p), C.POINTER(C.c_uint64), C.c_int]
+        lib.avr_files_compress.argtypes = many + [C.c_int, C.POINTER(u8p), C.POINTER(C.c_uint64)]
+        lib.avr_multi_files_compress.argtypes = many + [C.c_int, C.POINTER(u8p), C.POINTER(C.c_uint64)]
+        lib.avr_files_decompress.argtypes = many + [C.POINTER(u8p), C.POINTER(C.c_uint64)]
+        lib.avr_multi_files_decompress.argtypes = many + [C.POINTER(u8p), C.POINTER(C.c_uint64)]
+        lib.avr_free.argtypes = [C.c_void_p]
+        lib.avr_free.restype = None
+        _emu_file = lib
+    return _emu_file
+
+
+def emu_files_call(fn, handle, blobs, mode=None):
+    """avr_[multi_]files_compress / _decompress of the emulation-backed file layer: list of bytes -> (rc, list of bytes)."""
+    lib = emu_file_lib()
+    u8p = C.POINTER(C.c_uint8)
+    n = len(blobs)
+    keep = [(C.c_uint8 * max(1, len(b))).from_buffer_copy(b if b else b"\0") for b in blobs]
+    ptrs = (u8p * max(1, n))(*[C.cast(k, u8p) for k in keep])
+    sizes = (C.c_uint64 * max(1, n))(*[len(b) for b in blobs])
+    outs = (u8p * max(1, n))()
+    out_sizes = (C.c_uint64 * max(1, n))()
+    args = [handle, ptrs, sizes, n] + ([mode] if mode is not None else []) + [outs, out_sizes]
+    rc = fn(*args)
+    got = []
+    if rc == 0:
+        for i in range(n):
+            got.append(C.string_at(outs[i], out_sizes[i]))
+            lib.avr_free(outs[i])
+    return rc, got

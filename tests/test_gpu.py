@@ -381,3 +381,23 @@ def test_escaped_slices_are_recoded_in_chunked_mode(ctx):
     assert sum(1 for b in recproto.parse(rec_f)[1] if b.get("skip_coded")) == 1
     assert ctx.file_decompress(rec_s) == data and ctx.file_decompress(rec_f) == data
     assert ctx.files_decompress(ctx.files_compress([data, data[:1000], data], A.MODE_SLICE)) == [data, data[:1000], data]
+
+
+# ---- several devices behind one handle (avr_multi_*): every device this box has; one device is the degenerate case ----
+def test_multi_context_equals_one_device(ctx):
+    import torch
+    from test_oracle_pin import load_case
+    n_dev = torch.cuda.device_count()
+    files = [load_case(n)[0] for n in ("main_ip_4slices", "high_b_8x8_slices", "main_ip_mp4", "rich_headers_b")]
+    files += [H.gen_stream(width=1280, height=720, frames=8, seed=70 + i, kbps=6000) for i in range(4)]
+    with A.MultiContext(list(range(n_dev))) as m:
+        assert m.n_devices == n_dev
+        for mode in (A.MODE_FILE, A.MODE_SLICE):
+            one = ctx.files_compress(files, mode)
+            many = m.files_compress(files, mode)
+            assert many == one
+            assert m.files_decompress(one) == files and ctx.files_decompress(many) == files
+    with pytest.raises(A.AvrError):
+        A.MultiContext([0, 0])
+    with pytest.raises(A.AvrError):
+        A.MultiContext([n_dev])

@@ -47,6 +47,8 @@ def test_struct_layouts_match_header(built):
 def test_no_device_fails_loudly(built):
     with pytest.raises(A.NoDeviceError):
         A.Context()
+    with pytest.raises(A.NoDeviceError):
+        A.MultiContext([0, 1])
     cli = os.path.join(ROOT, "avrecode_b200", "recode")
     src = os.path.join(ROOT, "tests", "golden", CASES[0] + ".h264")
     p = subprocess.run([cli, "roundtrip", src], capture_output=True)
@@ -250,3 +252,72 @@ def test_wide_format_restatement_equals_device_logic(built, kw):
     for dec in (H.oracle_decompress, H.emu_decompress):
         r_d, b_d = dec(dd, b_o)
         assert H.roundtrip_ok(descs, r_d, b_d, data)
+
+
+# ---- the product's file layer (avr_file.cpp + h264_index.cpp) on the host emulation: container codec, multi-device ----
+FILE_LAYER_CASES = ["main_ip_4slices", "high_b_8x8_slices", "main_ip_mp4", "one_mb_stop_byte", "high_8x8_ragged"]
+
+
+@pytest.fixture(scope="module")
+def emu_ctx(built):
+    lib = H.emu_file_lib()
+    h = C.c_void_p()
+    assert lib.avr_create(None, C.byref(h)) == 0
+    yield h
+    lib.avr_destroy(h)
+
+
+@pytest.fixture(scope="module")
+def emu_multi(built):
+    lib = H.emu_file_lib()
+    devs = (C.c_int * 3)(0, 1, 2)
+    m = C.c_void_p()
+    assert lib.avr_multi_create(None, devs, 3, C.byref(m)) == 0
+    yield m
+    lib.avr_multi_destroy(m)
+
+
+def test_file_layer_writes_the_references_containers(emu_ctx):
+    """AVR_MODE_FILE through the product's own host code (index -> batch -> Recoded container): byte-identical to the
+    .rec files the reference binary wrote for the golden cases (tests/golden), raw streams and mp4."""
+    lib = H.emu_file_lib()
+    files, want = zip(*[load_case(n) for n in FILE_LAYER_CASES])
+    rc, recs = H.emu_files_call(lib.avr_files_compress, emu_ctx, list(files), A.MODE_FILE)
+    assert rc == 0
+    assert [hashlib_sha(r) for r in recs] == [hashlib_sha(w) for w in want]
+    rc, back = H.emu_files_call(lib.avr_files_decompress, emu_ctx, list(want))
+    assert rc == 0 and back == list(files)
+
+
+def hashlib_sha(b):
+    import hashlib
+    return hashlib.sha256(b).hexdigest()
+
+
+@pytest.mark.parametrize("mode", [A.MODE_FILE, A.MODE_SLICE], ids=["file", "slice"])
+def test_multi_device_sharding_is_invisible_in_the_output(emu_ctx, emu_multi, mode):
+    """avr_multi_*: the units of a call (files in the reference's mode, slices in chunked mode) are dealt out over three
+    "devices" (emulation contexts), each with a compact arena of its own and a host thread of its own.  Same containers
+    as one device, byte for byte; every device took part; either side decompresses the other's output."""
+    lib = H.emu_file_lib()
+    files = [load_case(n)[0] for n in FILE_LAYER_CASES] + [H.gen_stream(**ESCAPED_STREAM), b"", b"\x00\x00\x01\x09\x10"]
+    rc, one = H.emu_files_call(lib.avr_files_compress, emu_ctx, files, mode)
+    assert rc == 0
+    before = [lib.avr_emu_ctx_calls(lib.avr_multi_ctx(emu_multi, i)) for i in range(3)]
+    rc, many = H.emu_files_call(lib.avr_multi_files_compress, emu_multi, files, mode)
+    assert rc == 0 and many == one
+    after = [lib.avr_emu_ctx_calls(lib.avr_multi_ctx(emu_multi, i)) for i in range(3)]
+    assert all(a > b for a, b in zip(after, before))
+    rc, back = H.emu_files_call(lib.avr_multi_files_decompress, emu_multi, one)
+    assert rc == 0 and back == files
+    rc, back = H.emu_files_call(lib.avr_files_decompress, emu_ctx, many)
+    assert rc == 0 and back == files
+
+
+def test_multi_device_argument_errors(built):
+    lib = H.emu_file_lib()
+    m = C.c_void_p()
+    assert lib.avr_multi_create(None, (C.c_int * 2)(0, 0), 2, C.byref(m)) != 0      # the same device twice
+    assert lib.avr_multi_create(None, (C.c_int * 1)(0), 0, C.byref(m)) != 0
+    assert lib.avr_multi_create(None, None, 2, C.byref(m)) != 0
+    assert lib.avr_multi_ctx(None, 0) is None
