@@ -23,6 +23,8 @@ AVR_MAX_STREAMS = 8          # include/avrecode_b200.h
 
 AVR_OK = 0
 AVR_ERR_NO_DEVICE, AVR_ERR_CUDA, AVR_ERR_ARG, AVR_ERR_NOMEM, AVR_ERR_FORMAT, AVR_ERR_STATE = -1, -2, -3, -4, -5, -6
+AVR_ERR_LIMIT = -8           # avr_recode_noalloc only
+AVR_NOALLOC_MAX_SLICES, AVR_NOALLOC_SCRATCH_BYTES = 4096, 512 * 1024
 
 
 class SliceDesc(C.Structure):

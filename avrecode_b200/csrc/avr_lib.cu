@@ -177,6 +177,7 @@ const char* avr_strerror(int code) {
     case AVR_ERR_NOMEM: return "out of memory";
     case AVR_ERR_FORMAT: return "malformed container or bitstream";
     case AVR_ERR_STATE: return "call sequence violated (stage -> launch -> sync -> collect)";
+    case AVR_ERR_LIMIT: return "batch beyond the fixed limits of avr_recode_noalloc (AVR_NOALLOC_MAX_SLICES slices, the caller's output capacity, the picture width): use avr_compress / avr_decompress";
     default: return "unknown error";
   }
 }
@@ -521,3 +522,162 @@ int avr_decompress(avr_ctx* c, const avr_slice_desc* descs, int n, const uint8_t
 }
 
 }  // extern "C"
+
+// ------------------------------------------------------------------------------------------------
+// The entry point that allocates nothing (include/avrecode_b200.h: avr_recode_noalloc).  No counterpart in the
+// reference; added for callers that cannot call cudaMalloc (code under CUDA
+// graph capture, tight serving loops, harnesses that forbid it).
+//
+// It launches the same persistent job kernel as avr_launch (estimators resident in shared memory, every slice a job of
+// its own), but everything that kernel needs besides the caller's input and output -- the descriptor / buffer / job
+// tables, the job counter and the per-slice results -- lives in ONE file-scope device array instead of cudaMalloc'ed
+// buffers, and the host-side staging copy of those tables in a file-scope host array.  Every GPU that loads the
+// library holds AVR_NOALLOC_SCRATCH_BYTES of device memory for it until the process exits.
+//
+// The array is shared by every call and keeps the last call's contents: the job counter and the results are cleared
+// at the start of each call, the tables are overwritten.  Two calls that overlapped on one GPU would race on it, so
+// the library does not let them: a mutex is held from the first copy until the results are back on the host.
+// ------------------------------------------------------------------------------------------------
+#include <mutex>
+
+namespace {
+
+static __device__ __align__(256) uint8_t g_noalloc_scratch[AVR_NOALLOC_SCRATCH_BYTES];
+static uint8_t g_noalloc_host[AVR_NOALLOC_SCRATCH_BYTES];   // host-side staging of the tables (no allocation per call either)
+static std::mutex g_noalloc_mutex;
+
+// layout of the scratch: descs | ios | jobs | results | counter
+constexpr size_t NA_OFF_DESCS = 0;
+constexpr size_t NA_OFF_IOS = NA_OFF_DESCS + sizeof(avr_slice_desc) * AVR_NOALLOC_MAX_SLICES;
+constexpr size_t NA_OFF_JOBS = NA_OFF_IOS + sizeof(SliceIO) * AVR_NOALLOC_MAX_SLICES;
+constexpr size_t NA_OFF_RES = NA_OFF_JOBS + sizeof(JobDesc) * AVR_NOALLOC_MAX_SLICES;
+constexpr size_t NA_OFF_COUNTER = NA_OFF_RES + sizeof(avr_slice_result) * AVR_NOALLOC_MAX_SLICES;
+static_assert(NA_OFF_IOS % 16 == 0 && NA_OFF_JOBS % 16 == 0 && NA_OFF_RES % 16 == 0 && NA_OFF_COUNTER % 16 == 0, "table alignment");
+static_assert(NA_OFF_COUNTER + 256 <= AVR_NOALLOC_SCRATCH_BYTES, "the tables of AVR_NOALLOC_MAX_SLICES slices fit the scratch");
+
+struct NoAllocDevice {       // per device, filled in once with that device current
+  bool ready = false;
+  uint8_t* scratch = nullptr;   // DEVICE address of g_noalloc_scratch on this device (the name itself is a host-side stand-in)
+  int sm_count = 0, max_smem_optin = 0, max_smem_sm = 0;
+};
+enum : int { NA_MAX_DEVICES = 64 };
+NoAllocDevice g_noalloc_dev[NA_MAX_DEVICES];
+
+int noalloc_setup(int device, NoAllocDevice** out) {
+  if (device < 0 || device >= NA_MAX_DEVICES) return AVR_ERR_ARG;
+  NoAllocDevice& d = g_noalloc_dev[device];
+  if (!d.ready) {
+    void* p = nullptr;
+    CK(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+    if (!p) return AVR_ERR_CUDA;
+    CK(cudaDeviceGetAttribute(&d.sm_count, cudaDevAttrMultiProcessorCount, device));
+    CK(cudaDeviceGetAttribute(&d.max_smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, device));
+    CK(cudaDeviceGetAttribute(&d.max_smem_sm, cudaDevAttrMaxSharedMemoryPerMultiprocessor, device));
+    d.scratch = static_cast<uint8_t*>(p);
+    d.ready = true;
+  }
+  *out = &d;
+  return AVR_OK;
+}
+
+}  // namespace
+
+extern "C" int avr_recode_noalloc(int device, int direction, const avr_slice_desc* descs, int n_slices, const uint8_t* d_in,
+                                  uint64_t in_bytes, uint8_t* d_out, uint64_t out_cap, uint64_t* out_need,
+                                  avr_slice_result* results, void* stream) {
+  if (out_need) *out_need = 0;
+  if ((direction != 0 && direction != 1) || n_slices < 0 || (n_slices > 0 && !descs)) return AVR_ERR_ARG;
+  if (n_slices > AVR_NOALLOC_MAX_SLICES) return AVR_ERR_LIMIT;   // beyond the static scratch: use avr_compress / avr_decompress
+  const int n = n_slices;
+  // what the batch needs of the caller's output buffer: the slots of avr_stage, in order
+  uint64_t need = 0;
+  uint32_t max_mbw = 1;
+  for (int i = 0; i < n; i++) {
+    const avr_slice_desc& d = descs[i];
+    // every slice a model of its own, no wide slices, no bookkeeping-only slices: the static scratch holds no
+    // neighbour-count planes and no wide-slice rings
+    if (i > 0 && !(d.flags & AVR_SLICE_NEW_MODEL)) return AVR_ERR_ARG;
+    if ((d.n_streams & AVR_STREAMS_MASK) >= 2 || (d.flags & AVR_SLICE_SKIP)) return AVR_ERR_ARG;
+    if (d.in_off + d.in_size > in_bytes) return AVR_ERR_ARG;
+    const uint32_t cap = direction == 0 ? d.in_size + d.in_size / 8 + 256 : d.payload_size + 64;
+    need += align_up(cap, 16);
+    if (uint64_t(d.mb_width) * d.mb_height <= AVR_MAX_PICTURE_MBS && d.mb_width <= 1024) max_mbw = std::max<uint32_t>(max_mbw, d.mb_width);
+  }
+  if (out_need) *out_need = need;
+  if (!d_out) return n == 0 || out_need ? AVR_OK : AVR_ERR_ARG;   // a query: how many bytes of output the batch needs
+  if (n == 0) return AVR_OK;
+  if (!d_in || !results) return AVR_ERR_ARG;
+  if (out_cap < need) return AVR_ERR_LIMIT;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0) { cudaGetLastError(); return AVR_ERR_NO_DEVICE; }
+  if (device < 0 || device >= ndev) return AVR_ERR_ARG;
+
+  std::lock_guard<std::mutex> lock(g_noalloc_mutex);   // the scratch is shared: overlapping calls would race on it
+  CK(cudaSetDevice(device));
+  NoAllocDevice* dev = nullptr;
+  int rc = noalloc_setup(device, &dev);
+  if (rc) return rc;
+  const size_t smem = smem_bytes(max_mbw, true);
+  if (smem + 1024 > size_t(dev->max_smem_optin)) return AVR_ERR_LIMIT;   // picture too wide for the resident variant
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+
+  // the tables, built in the static host array
+  avr_slice_desc* h_descs = reinterpret_cast<avr_slice_desc*>(g_noalloc_host + NA_OFF_DESCS);
+  SliceIO* h_ios = reinterpret_cast<SliceIO*>(g_noalloc_host + NA_OFF_IOS);
+  JobDesc* h_jobs = reinterpret_cast<JobDesc*>(g_noalloc_host + NA_OFF_JOBS);
+  uint64_t off = 0;
+  for (int i = 0; i < n; i++) {
+    const avr_slice_desc& d = descs[i];
+    h_descs[i] = d;
+    h_ios[i].in_off = d.in_off; h_ios[i].in_size = d.in_size;
+    h_ios[i].out_off = off;
+    h_ios[i].out_cap = direction == 0 ? d.in_size + d.in_size / 8 + 256 : d.payload_size + 64;
+    off += align_up(h_ios[i].out_cap, 16);
+    memset(&h_jobs[i], 0, sizeof(JobDesc));
+    h_jobs[i].first_slice = uint32_t(i); h_jobs[i].n_slices = 1; h_jobs[i].weight = d.in_size;
+  }
+  // longest first; std::sort works in place (no temporary buffer), the tie-break keeps the order deterministic
+  std::sort(h_jobs, h_jobs + n, [](const JobDesc& a, const JobDesc& b) { return a.weight != b.weight ? a.weight > b.weight : a.first_slice < b.first_slice; });
+
+  uint8_t* s = dev->scratch;
+  CK(cudaMemcpyAsync(s + NA_OFF_DESCS, h_descs, sizeof(avr_slice_desc) * n, cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(s + NA_OFF_IOS, h_ios, sizeof(SliceIO) * n, cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(s + NA_OFF_JOBS, h_jobs, sizeof(JobDesc) * n, cudaMemcpyHostToDevice, st));
+  // what must not survive from the last call: the job counter (zero), the results (0xFF: "not written")
+  CK(cudaMemsetAsync(s + NA_OFF_COUNTER, 0, 256, st));
+  CK(cudaMemsetAsync(s + NA_OFF_RES, 0xFF, sizeof(avr_slice_result) * n, st));
+
+  KernelArgs k;
+  memset(&k, 0, sizeof k);
+  k.a.descs = reinterpret_cast<const avr_slice_desc*>(s + NA_OFF_DESCS);
+  k.a.ios = reinterpret_cast<const SliceIO*>(s + NA_OFF_IOS);
+  k.a.in_arena = d_in;
+  k.a.out_arena = d_out;
+  k.a.results = reinterpret_cast<avr_slice_result*>(s + NA_OFF_RES);
+  k.a.hist = nullptr;
+  k.jobs = reinterpret_cast<const JobDesc*>(s + NA_OFF_JOBS);
+  k.n_jobs = uint32_t(n);
+  k.counter = reinterpret_cast<uint32_t*>(s + NA_OFF_COUNTER);
+  k.workspace = s;            // jobs of one slice keep their neighbour counts in shared memory: never dereferenced
+  k.work_stride = 0;
+  k.nnz_frame_bytes = 0;
+  k.max_mbw = max_mbw;
+  k.wide_ws = nullptr; k.wide_stride = 0; k.wide_mbw = 1; k.far_cap = WIDE_FAR_CAP;
+  const int per_sm = std::max(1, std::min(2, int(size_t(dev->max_smem_sm) / (smem + 1024))));
+  cudaLaunchConfig_t lc;
+  memset(&lc, 0, sizeof lc);
+  lc.gridDim = dim3(unsigned(std::max(1, std::min(n, dev->sm_count * per_sm))));
+  lc.blockDim = dim3(direction == 0 ? AVR_THREADS_OF(Compress) : AVR_THREADS_OF(Decompress));
+  lc.dynamicSmemBytes = smem; lc.stream = st;
+  if (direction == 0) {
+    CK(cudaFuncSetAttribute(avr_job_kernel<Compress, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+    CK(cudaLaunchKernelEx(&lc, avr_job_kernel<Compress, true>, k));
+  } else {
+    CK(cudaFuncSetAttribute(avr_job_kernel<Decompress, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+    CK(cudaLaunchKernelEx(&lc, avr_job_kernel<Decompress, true>, k));
+  }
+  CK(cudaGetLastError());
+  CK(cudaMemcpyAsync(results, s + NA_OFF_RES, sizeof(avr_slice_result) * n, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  return AVR_OK;
+}

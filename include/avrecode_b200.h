@@ -134,6 +134,7 @@ typedef struct avr_ctx avr_ctx;
 #define AVR_ERR_NOMEM         -4
 #define AVR_ERR_FORMAT        -5 /* container / bitstream cannot be parsed */
 #define AVR_ERR_STATE         -6 /* staged call sequence violated */
+#define AVR_ERR_LIMIT         -8 /* avr_recode_noalloc only: the batch is beyond that entry point's fixed limits */
 
 const char* avr_strerror(int code);
 int  avr_abi_version(void);
@@ -239,6 +240,37 @@ int  avr_multi_files_compress(avr_multi* m, const uint8_t* const* files, const u
                               uint8_t** recs, uint64_t* rec_bytes);
 int  avr_multi_files_decompress(avr_multi* m, const uint8_t* const* recs, const uint64_t* rec_bytes, int n_files,
                                 uint8_t** files, uint64_t* file_bytes);
+/* ---- the entry point that allocates nothing --------------------------------------------------------------------
+ * NO COUNTERPART IN THE REFERENCE: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ *
+ * One batch of slices through the job kernel of avr_compress (direction 0) / avr_decompress (direction 1), with the
+ * caller's DEVICE buffers for input and output and everything else the kernel needs (its descriptor / job tables, job
+ * counter, results) in a fixed file-scope device array of AVR_NOALLOC_SCRATCH_BYTES, which every GPU that loads the
+ * library holds until the process exits.  The call makes no cudaMalloc / cudaFree / cudaHostAlloc and no host
+ * allocation; it copies the tables in, launches, copies `results` out and returns when `stream` has finished them.
+ *
+ *   descs, results   HOST arrays of n_slices (descs[i].in_off is an offset into d_in, as for avr_compress)
+ *   d_in, d_out      DEVICE pointers on `device`; slice i's bytes are at d_out + results[i].out_off
+ *   out_cap          bytes at d_out; *out_need (may be NULL) receives the bytes this batch needs -- the sum over the
+ *                    slices of in_size + in_size / 8 + 256 (direction 0) or payload_size + 64 (direction 1), each
+ *                    rounded up to 16.  d_out == NULL: only reports *out_need.
+ *   stream           a cudaStream_t of `device` (NULL: the default stream)
+ *
+ * Limits (AVR_ERR_LIMIT beyond them): at most AVR_NOALLOC_MAX_SLICES slices per call; out_cap >= *out_need; pictures whose
+ * neighbour row fits beside the estimators in shared memory (any Level 6.2 width does).  AVR_ERR_ARG: a slice that
+ * does not start a model of its own (every slice but the first must carry AVR_SLICE_NEW_MODEL: chunked mode only), a
+ * wide slice (n_streams >= 2) or AVR_SLICE_SKIP -- those need buffers this entry point does not have.
+ * The output bytes and results are those of avr_compress / avr_decompress for the same descriptors.
+ * All calls of a process share the scratch array (per device), which keeps the last call's contents; the library clears
+ * what must start clean and SERIALISES the calls (a mutex held until the results are back), because two calls
+ * overlapping on one GPU would race on it.  Do not expect concurrency from this entry point. */
+#define AVR_NOALLOC_MAX_SLICES    4096
+#define AVR_NOALLOC_SCRATCH_BYTES (512 * 1024)
+int  avr_recode_noalloc(int device, int direction, const avr_slice_desc* descs, int n_slices, const uint8_t* d_in,
+                        uint64_t in_bytes, uint8_t* d_out, uint64_t out_cap, uint64_t* out_need,
+                        avr_slice_result* results, void* stream);
+
 void avr_free(void* p);
 
 /* ---- measurement: single-lane microbenchmarks of the per-bin primitives ------------------------
