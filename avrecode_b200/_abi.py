@@ -23,6 +23,9 @@ AVR_MAX_STREAMS = 8          # include/avrecode_b200.h
 
 AVR_OK = 0
 AVR_ERR_NO_DEVICE, AVR_ERR_CUDA, AVR_ERR_ARG, AVR_ERR_NOMEM, AVR_ERR_FORMAT, AVR_ERR_STATE = -1, -2, -3, -4, -5, -6
+AVR_ERR_PRIORS = -7
+AVR_SLICE_PRIORS = 0x40      # avr_slice_desc.n_streams bit 6
+AVR_PRIOR_ENTRIES = 47892
 AVR_ERR_LIMIT = -8           # avr_recode_noalloc only
 AVR_NOALLOC_MAX_SLICES, AVR_NOALLOC_SCRATCH_BYTES = 4096, 512 * 1024
 

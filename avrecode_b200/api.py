@@ -149,6 +149,26 @@ def index_h264(data):
     return out
 
 
+PRIORS_PATH = os.path.join(_HERE, "priors_v1.bin")
+
+
+def load_priors(source="default"):
+    """A prior table as a ctypes uint16 array: "default" = the table that ships (priors_v1.bin), a path, or bytes."""
+    if source == "default":
+        source = PRIORS_PATH
+    raw = open(source, "rb").read() if isinstance(source, str) else bytes(source)
+    if len(raw) != 2 * _abi.AVR_PRIOR_ENTRIES:
+        raise ValueError("a prior table is %d bytes" % (2 * _abi.AVR_PRIOR_ENTRIES))
+    return (C.c_uint16 * _abi.AVR_PRIOR_ENTRIES).from_buffer_copy(raw)
+
+
+def priors_digest_of(source="default"):
+    lib = load_library()
+    lib.avr_priors_digest_of.restype = C.c_uint32
+    lib.avr_priors_digest_of.argtypes = [C.POINTER(C.c_uint16), C.c_uint32]
+    return lib.avr_priors_digest_of(load_priors(source), _abi.AVR_PRIOR_ENTRIES)
+
+
 class Context:
     """One CUDA device.  Raises NoDeviceError when there is none: no CPU fallback exists."""
 
@@ -163,6 +183,21 @@ class Context:
         _check(self._lib.avr_create(C.byref(cfg), C.byref(h)), "avr_create")
         self._h = h
         self._keep = None
+
+    def set_priors(self, source="default"):
+        """Fresh models of chunked-mode slices start from this table (avr_set_priors); None clears."""
+        self._lib.avr_set_priors.argtypes = [C.c_void_p, C.POINTER(C.c_uint16), C.c_uint32]
+        if source is None:
+            _check(self._lib.avr_set_priors(self._h, None, 0), "avr_set_priors")
+        else:
+            _check(self._lib.avr_set_priors(self._h, load_priors(source), _abi.AVR_PRIOR_ENTRIES), "avr_set_priors")
+        return self
+
+    @property
+    def priors_digest(self):
+        self._lib.avr_priors_digest.restype = C.c_uint32
+        self._lib.avr_priors_digest.argtypes = [C.c_void_p]
+        return self._lib.avr_priors_digest(self._h)
 
     def close(self):
         if getattr(self, "_h", None):
@@ -322,6 +357,14 @@ class MultiContext:
 
     def __exit__(self, *exc):
         self.close()
+
+    def set_priors(self, source="default"):
+        self._lib.avr_multi_set_priors.argtypes = [C.c_void_p, C.POINTER(C.c_uint16), C.c_uint32]
+        if source is None:
+            _check(self._lib.avr_multi_set_priors(self._h, None, 0), "avr_multi_set_priors")
+        else:
+            _check(self._lib.avr_multi_set_priors(self._h, load_priors(source), _abi.AVR_PRIOR_ENTRIES), "avr_multi_set_priors")
+        return self
 
     @property
     def n_devices(self):

@@ -80,7 +80,7 @@ bool parse_block(const uint8_t* p, const uint8_t* e, Block* b) {
   return true;
 }
 
-bool parse_container(const uint8_t* p, size_t n, std::vector<Block>* blocks, std::string* version) {
+bool parse_container(const uint8_t* p, size_t n, std::vector<Block>* blocks, std::string* version, uint64_t* priors) {
   const uint8_t* e = p + n;
   while (p < e) {
     uint64_t key;
@@ -100,7 +100,7 @@ bool parse_container(const uint8_t* p, size_t n, std::vector<Block>* blocks, std
             if (!get_varint(q, qe, &l2) || l2 > uint64_t(qe - q)) return false;
             if ((k2 >> 3) == 1) version->assign(reinterpret_cast<const char*>(q), size_t(l2));
             q += l2;
-          } else if ((k2 & 7) == 0) { uint64_t v; if (!get_varint(q, qe, &v)) return false; }
+          } else if ((k2 & 7) == 0) { uint64_t v; if (!get_varint(q, qe, &v)) return false; if ((k2 >> 3) == 2) *priors = v; }   // Metadata field 2: digest of the prior table
           else return false;
         }
       }
@@ -338,6 +338,9 @@ static int compress_many(const DevSet& ds, const uint8_t* const* files, const ui
   size_t n_batch = 0;
   for (const Plan& p : plans) for (int i = 0; i < p.n_ents; i++) n_batch += p.coded[i] ? 1 : 0;
   const uint32_t per_stream = mode == AVR_MODE_SLICE ? wide_stream_bytes(ctx, n_batch) : 0;
+  // chunked mode: fresh models start from the context's prior table, if it has one (every device the same one)
+  const uint32_t priors = mode == AVR_MODE_SLICE ? avr_priors_digest(ctx) : 0;
+  for (int k = 1; k < ds.n && mode == AVR_MODE_SLICE; k++) if (avr_priors_digest(ds.ctx[k]) != priors) { cleanup(); return AVR_ERR_PRIORS; }
   std::vector<avr_slice_desc> descs;
   std::vector<avr_slice_result> res;
   std::vector<const uint8_t*> out_at;
@@ -359,6 +362,7 @@ static int compress_many(const DevSet& ds, const uint8_t* const* files, const ui
         if (p.map.empty() || mode == AVR_MODE_SLICE) d.flags |= AVR_SLICE_NEW_MODEL;
         if (p.coded[i] == 2) { d.in_off = p.raw_off[i]; d.in_size = p.raw_size[i]; }
         d.n_streams = p.coded[i] ? streams_for(d, per_stream, uint32_t(avr_ctx_wide_max_streams(ctx))) : 0;
+        if (priors && p.coded[i]) d.n_streams |= AVR_SLICE_PRIORS;
         descs.push_back(d);
         p.map.push_back(i);
       }
@@ -390,6 +394,7 @@ static int compress_many(const DevSet& ds, const uint8_t* const* files, const ui
     if (mode == AVR_MODE_SLICE) {
       std::string meta;
       put_len(meta, 1, reinterpret_cast<const uint8_t*>(kSliceModeTag), sizeof(kSliceModeTag) - 1);
+      if (priors) put_var(meta, 2, priors);
       put_len(o, 1, reinterpret_cast<const uint8_t*>(meta.data()), meta.size());
     }
     uint64_t prev = 0;
@@ -464,9 +469,14 @@ static int decompress_many(const DevSet& ds, const uint8_t* const* recs, const u
   for (int f = 0; f < n_files; f++) {
     Plan& p = plans[f];
     std::string version;
-    if (!parse_container(recs[f], size_t(rec_sizes[f]), &p.blocks, &version)) return AVR_ERR_FORMAT;
+    uint64_t priors = 0;
+    if (!parse_container(recs[f], size_t(rec_sizes[f]), &p.blocks, &version, &priors)) return AVR_ERR_FORMAT;
     const bool slice_mode = version == kSliceModeTag;
     if (!version.empty() && !slice_mode) return AVR_ERR_FORMAT;
+    if (priors) {   // written from a prior table: every device must hold that very table
+      if (!slice_mode) return AVR_ERR_FORMAT;
+      for (int k = 0; k < ds.n; k++) if (avr_priors_digest(ds.ctx[k]) != priors) return AVR_ERR_PRIORS;
+    }
     p.stream.reserve(size_t(rec_sizes[f]) + size_t(rec_sizes[f]) / 8 + 4096);
     in.reserve(in.size() + size_t(rec_sizes[f]));
     // 1. rebuild the stream with surrogate payloads (recode.cpp:1359-1409, 1537-1544) so the slice
@@ -511,6 +521,7 @@ static int decompress_many(const DevSet& ds, const uint8_t* const* recs, const u
         if (!slice_mode || !p.coded[i].is_cabac) { free(ents); return AVR_ERR_FORMAT; }
         d.n_streams |= AVR_SLICE_ESCAPED;
       }
+      if (priors && p.coded[i].is_cabac) d.n_streams |= AVR_SLICE_PRIORS;
       if (p.coded[i].is_cabac) in.append(reinterpret_cast<const char*>(b.cabac), b.cabac_n);
       descs.push_back(d);
       p.which.push_back(size_t(i));
@@ -597,6 +608,11 @@ void avr_multi_destroy(avr_multi* m) {
 int avr_multi_devices(const avr_multi* m) { return m ? int(m->ctx.size()) : 0; }
 avr_ctx* avr_multi_ctx(avr_multi* m, int i) { return m && i >= 0 && size_t(i) < m->ctx.size() ? m->ctx[size_t(i)] : nullptr; }
 
+int avr_multi_set_priors(avr_multi* m, const uint16_t* table, uint32_t n_entries) {
+  if (!m) return AVR_ERR_ARG;
+  for (avr_ctx* c : m->ctx) { const int rc = avr_set_priors(c, table, n_entries); if (rc) return rc; }
+  return AVR_OK;
+}
 int avr_multi_files_compress(avr_multi* m, const uint8_t* const* files, const uint64_t* file_bytes, int n_files, int mode,
                              uint8_t** recs, uint64_t* rec_bytes) {
   if (!m || m->ctx.empty() || n_files < 0 || (n_files > 0 && (!files || !file_bytes || !recs || !rec_bytes)) ||

@@ -68,6 +68,7 @@ struct JobArgs {
   uint8_t* out_arena;
   avr_slice_result* results;
   uint32_t* hist;           // [n_slices][8] per-class bin counts (HIST_*), or null
+  const uint16_t* priors;   // [MODEL_COUNTERS] what a fresh model starts from when its slice says AVR_SLICE_PRIORS, or null
 };
 
 struct JobMem {             // where this block keeps its state
@@ -97,6 +98,10 @@ AVR_DEV void init_contexts(U2* cstate, const avr_slice_desc& d, int tid, int nth
   }
 }
 
+// n words of estimators from the prior table (or {1, 1} each), the padding behind them {1, 1}
+AVR_DEV void init_estimators(uint32_t* dst, const uint32_t* prior, uint32_t n, uint32_t n_pad, int tid, int nthreads) {
+  for (uint32_t i = uint32_t(tid); i < n_pad; i += uint32_t(nthreads)) dst[i] = (prior && i < n) ? prior[i] : EST_INIT * 0x10001u;
+}
 AVR_DEV void fill_u32(uint32_t* p, uint32_t n_words, uint32_t v, int tid, int nthreads) {
   for (uint32_t i = uint32_t(tid); i < n_words; i += uint32_t(nthreads)) p[i] = v;
 }
@@ -555,10 +560,12 @@ AVR_DEV void run_job(const JobArgs& a, const JobDesc& job, const JobMem& m, cons
     if (usable) {
       if (fresh) {
         // a brand-new h264_model: every estimator {1,1} (recode.cpp:1057), no frame buffers yet
-        if (m.cnt8 == m.cnt) fill_u32(reinterpret_cast<uint32_t*>(m.cnt), MODEL_COUNTERS_PAD / 2, EST_INIT * 0x10001u, tid, nthreads);
+        // ... or, chunked mode with a prior table, a copy of that table (avr_set_priors)
+        const uint32_t* pri = (a.priors && (d.n_streams & AVR_SLICE_PRIORS)) ? reinterpret_cast<const uint32_t*>(a.priors) : nullptr;
+        if (m.cnt8 == m.cnt) init_estimators(reinterpret_cast<uint32_t*>(m.cnt), pri, MODEL_COUNTERS / 2, MODEL_COUNTERS_PAD / 2, tid, nthreads);
         else {
-          fill_u32(reinterpret_cast<uint32_t*>(m.cnt), CNT_LOW_PAD / 2, EST_INIT * 0x10001u, tid, nthreads);
-          fill_u32(reinterpret_cast<uint32_t*>(m.cnt8 + CNT8_SPLIT), CNT8_ENTRIES / 2, EST_INIT * 0x10001u, tid, nthreads);
+          init_estimators(reinterpret_cast<uint32_t*>(m.cnt), pri, CNT8_SPLIT / 2, CNT_LOW_PAD / 2, tid, nthreads);
+          init_estimators(reinterpret_cast<uint32_t*>(m.cnt8 + CNT8_SPLIT), pri ? pri + CNT8_SPLIT / 2 : nullptr, SIG_CAT_8 / 2, CNT8_ENTRIES / 2, tid, nthreads);
         }
         ft.clear();
       }
@@ -633,7 +640,8 @@ void emu_wide_slice(const JobArgs& a, uint32_t s, JobMem* mems, const WideMem& w
     uint32_t off = g.hdr;
     for (uint32_t j = 0; j < K; j++) {
       const JobMem& m = mems[1 + j];
-      for (uint32_t i = 0; i < MODEL_COUNTERS_PAD; i++) m.cnt[i] = EST_INIT;
+      init_estimators(reinterpret_cast<uint32_t*>(m.cnt), (a.priors && (d.n_streams & AVR_SLICE_PRIORS)) ? reinterpret_cast<const uint32_t*>(a.priors) : nullptr,
+                      MODEL_COUNTERS / 2, MODEL_COUNTERS_PAD / 2, 0, 1);
       wide_walker<Dir>(wk[j], w, K, j);
       Lane ln;
       ln.tab = &m.sh->tab; ln.ring = &m.sh->ring; ln.window = m.sh->window; ln.cstate = m.sh->cstate; ln.walk = &m.sh->walk;

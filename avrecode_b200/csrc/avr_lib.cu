@@ -104,6 +104,7 @@ struct avr_ctx {
   uint8_t* d_wide = nullptr; size_t d_wide_cap = 0;   // workspace of the wide-slice kernel
   uint8_t* d_meta = nullptr; size_t d_meta_cap = 0;   // descs | ios | jobs | results | counter
   uint8_t* d_flush = nullptr; size_t flush_bytes = 0;
+  uint16_t* d_priors = nullptr; uint32_t priors_digest = 0;   // avr_set_priors
   // pinned host buffers
   uint8_t* h_out = nullptr; size_t h_out_cap = 0;
   uint8_t* h_meta = nullptr; size_t h_meta_cap = 0;
@@ -177,6 +178,7 @@ const char* avr_strerror(int code) {
     case AVR_ERR_NOMEM: return "out of memory";
     case AVR_ERR_FORMAT: return "malformed container or bitstream";
     case AVR_ERR_STATE: return "call sequence violated (stage -> launch -> sync -> collect)";
+    case AVR_ERR_PRIORS: return "the container or slice asks for a prior table this context does not hold (avr_set_priors)";
     case AVR_ERR_LIMIT: return "batch beyond the fixed limits of avr_recode_noalloc (AVR_NOALLOC_MAX_SLICES slices, the caller's output capacity, the picture width): use avr_compress / avr_decompress";
     default: return "unknown error";
   }
@@ -236,6 +238,7 @@ void avr_destroy(avr_ctx* c) {
   if (c->d_wide) cudaFree(c->d_wide);
   if (c->d_meta) cudaFree(c->d_meta);
   if (c->d_flush) cudaFree(c->d_flush);
+  if (c->d_priors) cudaFree(c->d_priors);
   if (c->h_out) cudaFreeHost(c->h_out);
   if (c->h_meta) cudaFreeHost(c->h_meta);
   if (c->ev0) cudaEventDestroy(c->ev0);
@@ -243,6 +246,35 @@ void avr_destroy(avr_ctx* c) {
   if (c->stream) cudaStreamDestroy(c->stream);
   delete c;
 }
+
+// FNV-1a over the table bytes; never 0 (0 = "no table")
+uint32_t avr_priors_digest_of(const uint16_t* table, uint32_t n_entries) {
+  if (!table) return 0;
+  uint32_t h = 2166136261u;
+  for (uint32_t i = 0; i < n_entries; i++) { h = (h ^ (table[i] & 0xFF)) * 16777619u; h = (h ^ (table[i] >> 8)) * 16777619u; }
+  return h ? h : 1u;
+}
+int avr_set_priors(avr_ctx* c, const uint16_t* table, uint32_t n_entries) {
+  if (!c) return AVR_ERR_ARG;
+  CK(cudaSetDevice(c->device));
+  CK(cudaStreamSynchronize(c->stream));
+  if (!table) {
+    if (c->d_priors) cudaFree(c->d_priors);
+    c->d_priors = nullptr; c->priors_digest = 0;
+    return AVR_OK;
+  }
+  if (n_entries != AVR_PRIOR_ENTRIES) return AVR_ERR_ARG;
+  static_assert(AVR_PRIOR_ENTRIES == MODEL_COUNTERS, "the header's table size is the model's");
+  for (uint32_t i = 0; i < n_entries; i++) {   // what recode.cpp:1030-1047 can reach (the coders' reciprocal table ends at 99)
+    const uint32_t pos = table[i] & 0xFF, tot = table[i] >> 8;
+    if (pos < 1 || tot <= pos || tot > LIMIT_SIG) return AVR_ERR_ARG;
+  }
+  if (!c->d_priors && cudaMalloc(reinterpret_cast<void**>(&c->d_priors), size_t(MODEL_COUNTERS) * 2) != cudaSuccess) { cudaGetLastError(); c->d_priors = nullptr; return AVR_ERR_NOMEM; }
+  CK(cudaMemcpy(c->d_priors, table, size_t(MODEL_COUNTERS) * 2, cudaMemcpyHostToDevice));
+  c->priors_digest = avr_priors_digest_of(table, n_entries);
+  return AVR_OK;
+}
+uint32_t avr_priors_digest(avr_ctx* c) { return c ? c->priors_digest : 0; }
 
 }  // extern "C"
 
@@ -266,6 +298,7 @@ int avr_stage(avr_ctx* c, const avr_slice_desc* descs, int n, const uint8_t* in,
     const avr_slice_desc& d = descs[i];
     const uint32_t n_str = d.n_streams & AVR_STREAMS_MASK;
     if (d.in_off + d.in_size > in_bytes) return AVR_ERR_ARG;
+    if ((d.n_streams & AVR_SLICE_PRIORS) && !c->d_priors) return AVR_ERR_PRIORS;   // the slice asks for a table this context does not have
     for (int dir = 0; dir < 2; dir++) {
       SliceIO& io = c->ios[dir][i];
       io.in_off = d.in_off; io.in_size = d.in_size;
@@ -395,6 +428,7 @@ int avr_launch(avr_ctx* c, int direction) {
   k.a.out_arena = c->d_out;
   k.a.results = reinterpret_cast<avr_slice_result*>(c->d_meta + c->off_res);
   k.a.hist = reinterpret_cast<uint32_t*>(c->d_meta + c->off_hist);
+  k.a.priors = c->d_priors;
   k.jobs = reinterpret_cast<const JobDesc*>(c->d_meta + c->off_jobs);
   k.n_jobs = uint32_t(c->n_jobs);
   k.counter = reinterpret_cast<uint32_t*>(c->d_meta + c->off_counter);
@@ -597,7 +631,7 @@ extern "C" int avr_recode_noalloc(int device, int direction, const avr_slice_des
     // every slice a model of its own, no wide slices, no bookkeeping-only slices: the static scratch holds no
     // neighbour-count planes and no wide-slice rings
     if (i > 0 && !(d.flags & AVR_SLICE_NEW_MODEL)) return AVR_ERR_ARG;
-    if ((d.n_streams & AVR_STREAMS_MASK) >= 2 || (d.flags & AVR_SLICE_SKIP)) return AVR_ERR_ARG;
+    if ((d.n_streams & AVR_STREAMS_MASK) >= 2 || (d.n_streams & AVR_SLICE_PRIORS) || (d.flags & AVR_SLICE_SKIP)) return AVR_ERR_ARG;
     if (d.in_off + d.in_size > in_bytes) return AVR_ERR_ARG;
     const uint32_t cap = direction == 0 ? d.in_size + d.in_size / 8 + 256 : d.payload_size + 64;
     need += align_up(cap, 16);

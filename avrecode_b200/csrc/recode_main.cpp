@@ -4,7 +4,9 @@
 //   AVR_MODE=slice (default; B200 chunked format) | file (reference-parity bytes)
 //   AVR_DEVICE=<cuda ordinal>
 //   AVR_DEVICES=<ordinal>,<ordinal>,...   several devices: the slices (AVR_MODE=slice) of the file are dealt out over them
+//   AVR_PRIORS=<path> | none   the prior table of chunked mode (default: priors_v1.bin beside this executable, if it is there)
 #include <stdio.h>
+#include <unistd.h>
 #include <stdlib.h>
 #include <string.h>
 #include <fstream>
@@ -46,6 +48,26 @@ struct Ctx {
     }
     if (devices.empty()) devices.push_back(getenv("AVR_DEVICE") ? atoi(getenv("AVR_DEVICE")) : 0);
     check(avr_multi_create(&cfg, devices.data(), int(devices.size()), &m), "avr_multi_create");
+    load_priors();
+  }
+  // chunked mode starts fresh models from a prior table; a container records which one (AVR_ERR_PRIORS on a mismatch)
+  void load_priors() {
+    const char* env = getenv("AVR_PRIORS");
+    if (env && strcmp(env, "none") == 0) return;
+    std::string path = env ? env : "";
+    if (path.empty()) {
+      char self[4096];
+      const ssize_t n = readlink("/proc/self/exe", self, sizeof self - 1);
+      if (n <= 0) return;
+      self[n] = 0;
+      path = self;
+      path = path.substr(0, path.rfind('/') + 1) + "priors_v1.bin";
+    }
+    std::ifstream f(path, std::ios::binary);
+    if (!f) { if (env) throw std::invalid_argument("AVR_PRIORS: cannot open " + path); return; }
+    std::vector<char> raw((std::istreambuf_iterator<char>(f)), std::istreambuf_iterator<char>());
+    if (raw.size() != size_t(AVR_PRIOR_ENTRIES) * 2) throw std::invalid_argument("not a prior table: " + path);
+    check(avr_multi_set_priors(m, reinterpret_cast<const uint16_t*>(raw.data()), AVR_PRIOR_ENTRIES), "avr_multi_set_priors");
   }
   ~Ctx() { avr_multi_destroy(m); }
 };

@@ -81,11 +81,14 @@ typedef struct avr_slice_desc {
                              (AVR_SLICE_ESCAPED), decompress only: the slice_data in the file contains emulation-
                              prevention bytes -- the coded block describes the UNESCAPED payload and the re-encoder
                              inserts them again (H.264 7.4.1), payload_size being the escaped size.  Chunked mode only:
-                             the reference leaves such slices as literals (recode.cpp:1289-1296). */
+                             the reference leaves such slices as literals (recode.cpp:1289-1296).
+                             bit 6 (AVR_SLICE_PRIORS): a model that starts with this slice starts from the context's prior
+                             table (avr_set_priors) instead of the reference's {1, 1} everywhere.  Chunked mode only. */
 } avr_slice_desc;
 #define AVR_STREAMS_MASK   0x0F
 #define AVR_ESC_ZEROS_SHIFT 4
 #define AVR_SLICE_ESCAPED  0x80
+#define AVR_SLICE_PRIORS   0x40
 #define AVR_MAX_PICTURE_MBS 139264u /* Level 6.2 MaxFS (H.264 table A-1): larger pictures are reported unsupported */
 #define AVR_DEFAULT_WIDE_STREAMS 2
 #define AVR_MAX_STREAMS 8   /* what this build runs: every stream of a wide slice is worked on by a thread block of its own */
@@ -134,6 +137,7 @@ typedef struct avr_ctx avr_ctx;
 #define AVR_ERR_NOMEM         -4
 #define AVR_ERR_FORMAT        -5 /* container / bitstream cannot be parsed */
 #define AVR_ERR_STATE         -6 /* staged call sequence violated */
+#define AVR_ERR_PRIORS        -7 /* the container was written from a prior table this context does not hold (avr_set_priors) */
 #define AVR_ERR_LIMIT         -8 /* avr_recode_noalloc only: the batch is beyond that entry point's fixed limits */
 
 const char* avr_strerror(int code);
@@ -225,6 +229,20 @@ int  avr_files_compress(avr_ctx* ctx, const uint8_t* const* files, const uint64_
 int  avr_files_decompress(avr_ctx* ctx, const uint8_t* const* recs, const uint64_t* rec_bytes, int n_files,
                           uint8_t** files, uint64_t* file_bytes);
 
+/* ---- static priors (chunked mode) -------------------------------------------------------------------------------
+ * In AVR_MODE_SLICE every slice starts a model of its own, which costs about half of what the reference's one model per
+ * file saves (a slice is over before the estimators have learnt much).  A PRIOR TABLE gives every fresh model a head
+ * start: AVR_PRIOR_ENTRIES estimators in the table layout of avr_core.cuh (CNT_*), each a uint16 `pos | (pos + neg) << 8`
+ * with pos, neg >= 1 and pos + neg <= 0x50 (what recode.cpp:1030-1047 can reach).  tools/train_priors.py makes one from
+ * sample streams; avrecode_b200/priors_v1.bin is the table that ships.  The container records the table's digest
+ * (Metadata field 2) and the decompress calls refuse a container whose digest is not that of the context's table
+ * (AVR_ERR_PRIORS).  AVR_MODE_FILE never uses priors: its output is the reference's.  No reference counterpart.
+ * table == NULL clears.  avr_priors_digest: 0 = no table. */
+#define AVR_PRIOR_ENTRIES 47892
+int      avr_set_priors(avr_ctx* ctx, const uint16_t* table, uint32_t n_entries);
+uint32_t avr_priors_digest(avr_ctx* ctx);
+uint32_t avr_priors_digest_of(const uint16_t* table, uint32_t n_entries);
+
 /* ---- several devices of one node behind one handle ----------------------------------------------------------------
  * The reference runs one file on one core (recode.cpp main); its unit of parallelism is the process.  Here the units are
  * the slices (AVR_MODE_SLICE) or the files (AVR_MODE_FILE: the slices of a file share one model) of a call: they are dealt
@@ -236,6 +254,7 @@ int  avr_multi_create(const avr_config* cfg, const int* devices, int n_devices, 
 void avr_multi_destroy(avr_multi* m);
 int  avr_multi_devices(const avr_multi* m);
 avr_ctx* avr_multi_ctx(avr_multi* m, int i);   /* the context of device i (owned by m) */
+int  avr_multi_set_priors(avr_multi* m, const uint16_t* table, uint32_t n_entries);
 int  avr_multi_files_compress(avr_multi* m, const uint8_t* const* files, const uint64_t* file_bytes, int n_files, int mode,
                               uint8_t** recs, uint64_t* rec_bytes);
 int  avr_multi_files_decompress(avr_multi* m, const uint8_t* const* recs, const uint64_t* rec_bytes, int n_files,
@@ -260,7 +279,7 @@ int  avr_multi_files_decompress(avr_multi* m, const uint8_t* const* recs, const 
  * Limits (AVR_ERR_LIMIT beyond them): at most AVR_NOALLOC_MAX_SLICES slices per call; out_cap >= *out_need; pictures whose
  * neighbour row fits beside the estimators in shared memory (any Level 6.2 width does).  AVR_ERR_ARG: a slice that
  * does not start a model of its own (every slice but the first must carry AVR_SLICE_NEW_MODEL: chunked mode only), a
- * wide slice (n_streams >= 2) or AVR_SLICE_SKIP -- those need buffers this entry point does not have.
+ * wide slice (n_streams >= 2), AVR_SLICE_PRIORS or AVR_SLICE_SKIP -- those need buffers this entry point does not have.
  * The output bytes and results are those of avr_compress / avr_decompress for the same descriptors.
  * All calls of a process share the scratch array (per device), which keeps the last call's contents; the library clears
  * what must start clean and SERIALISES the calls (a mutex held until the results are back), because two calls

@@ -327,8 +327,73 @@ inline FILE* trace_file() {  // debugging aid: AVR_ORACLE_TRACE=<path> logs ever
   return f;
 }
 
+// ---------------------------------------------------------------------------------------------
+// Static priors (chunked mode of the B200 library; no reference counterpart -- the reference starts every estimator at
+// {1, 1}, recode.cpp:1057).  A prior table is AVR_PRIOR_ENTRIES uint16 `pos | (pos + neg) << 8` in the table layout that
+// include/avrecode_b200.h and the header comment of avr_core.cuh document.  This function restates that layout
+// independently, from the model KEY of recode.cpp:676-815 / :884 to the table index:
+//   [0, 328)        ordinary bins by dense ctxIdx (0..276 as is, 399..435 -> 277.., 1012..1023 -> 314..)
+//   328, 329        bypass, terminate
+//   330 + ...       nnz side channel: group(cat, is_8x8) + ((2^i - 1 + so_far) * 2 + prev_bit) * 9 + left_bit * 3 + above_bit
+//                   groups: cats 0, 1, 2, 4 (in that order) x is_8x8 of 15 * 18 each, then cat 3 x is_8x8 of 3 * 18, then cat 5 of 63 * 18
+//   3732 + ...      significance map: cat 0..4: cat * 136 * 16 + (nnz (nnz - 1) / 2 + observed) * 16 + zz
+//                   cat 5 (after 5 * 136 * 16): key nnz 0 (= 64 coefficients): observed * 16 + zz; key nnz n: (64 + n (n - 1) / 2 + observed) * 16 + zz
+// Returns -1 for keys that have no estimator in the table (KS_EOB: never coded).
+// ---------------------------------------------------------------------------------------------
+inline int prior_index(const ModelKey& k) {
+  const int space = std::get<0>(k), ctx = std::get<1>(k), a = std::get<2>(k), b = std::get<3>(k);
+  if (space == KS_CTX) {
+    if (ctx >= 0 && ctx < 277) return ctx;
+    if (ctx >= 399 && ctx <= 435) return ctx - 399 + 277;
+    if (ctx >= 1012 && ctx <= 1023) return ctx - 1012 + 314;
+    return -1;
+  }
+  if (space == KS_BYPASS) return 328;
+  if (space == KS_TERMINATE) return 329;
+  if (space == KS_SIG) {
+    static const int cat_first_ctx[6] = {105, 120, 134, 149, 152, 402};   // the cat_lookup values of recode.cpp:696 for cats 0..5
+    static const int cat_coefs[6] = {16, 15, 16, 4, 15, 64};
+    int nnz = a >> 6;
+    const int observed = a & 63, zz = (b >> 1) & 15, lookup = b >> 5;
+    int cat = -1;
+    for (int c = 0; c < 6; c++) if (cat_first_ctx[c] == lookup) cat = c;
+    if (cat < 0) return -1;
+    // A full block's count does not fit its 2 / 4 / 6 serialised bits and travels as 0: the DEcompressor
+    // keys such a block's bins with nnz = 0 where the compressor keyed them with nnz = all -- one and the same estimator.
+    // (8x8 blocks: the compressor's stored count wraps to 0 as well, so both sides say 0 and the table has a row for it.)
+    if (nnz == 0 && cat != 5) nnz = cat_coefs[cat];
+    if (observed >= (nnz ? nnz : 64)) return -1;
+    const int base = 330 + 3402;
+    if (cat == 5) return base + 5 * 136 * 16 + ((nnz == 0 ? 0 : 64 + nnz * (nnz - 1) / 2) + observed) * 16 + zz;
+    if (nnz < 1 || nnz > 16) return -1;
+    return base + cat * 136 * 16 + (nnz * (nnz - 1) / 2 + observed) * 16 + zz;
+  }
+  if (space >= KS_NZ0 && space < KS_NZ0 + 6) {
+    const int i = space - KS_NZ0, so_far = a & 63, prev_bit = (a >> 6) & 1, lb = (a >> 7) % 3, ab = (a >> 7) / 3;
+    const int cat = b >> 2, is8 = b & 1;
+    int group;
+    if (cat == 5) group = 8 * 15 * 18 + 2 * 3 * 18;
+    else if (cat == 3) group = 8 * 15 * 18 + (is8 ? 3 * 18 : 0);
+    else if (cat == 0 || cat == 1 || cat == 2 || cat == 4) group = ((cat == 4 ? 3 : cat) * 2 + is8) * 15 * 18;
+    else return -1;
+    return 330 + group + (((1 << i) - 1 + so_far) * 2 + prev_bit) * 9 + lb * 3 + ab;
+  }
+  return -1;
+}
+
 class Model {
  public:
+  const uint16_t* priors = nullptr;   // a fresh estimator starts from priors[prior_index(key)] instead of {1, 1}
+  Estimator& lookup(const ModelKey& k) {
+    Estimators::iterator it = est->find(k);
+    if (it == est->end()) {
+      Estimator e;
+      const int idx = priors ? prior_index(k) : -1;
+      if (idx >= 0) { e.pos = priors[idx] & 0xFF; e.neg = (priors[idx] >> 8) - e.pos; }
+      it = est->insert(std::make_pair(k, e)).first;
+    }
+    return it->second;
+  }
   CodingType coding_type = CT_UNKNOWN;
   int mb_x = 0, mb_y = 0, blk = -1, zigzag = 0;  // mb_coord (recode.cpp:1050)
   int nonzeros_observed = 0, sub_mb_cat = -1, sub_mb_size = -1, sub_mb_is_dc = 0, sub_mb_chroma422 = 0;
@@ -382,12 +447,12 @@ class Model {
   }
   // recode.cpp:816-820 -- divide first, then multiply
   uint64_t probability(uint64_t range, const ModelKey& k) {
-    Estimator& e = (*est)[k];
+    Estimator& e = lookup(k);
     return (range / uint64_t(e.pos + e.neg)) * uint64_t(e.pos);
   }
   // recode.cpp:1030-1047
   void update(int symbol, const ModelKey& k) {
-    Estimator& e = (*est)[k];
+    Estimator& e = lookup(k);
     if (FILE* tf = trace_file())  // same columns as oracle/_ref/recode_ref_trace: type, key identity, ints, symbol, counters
       fprintf(tf, "%d %d %d %d %d %d %d\n", int(coding_type), std::get<0>(k) * 4096 + std::get<1>(k), std::get<2>(k), std::get<3>(k), symbol, e.pos, e.neg);
     if (symbol) e.pos++; else e.neg++;

@@ -10,6 +10,8 @@
 using namespace avr_oracle;
 
 namespace {
+const uint16_t* g_priors = nullptr;   // avr_oracle_set_priors: the table of slices that carry AVR_SLICE_PRIORS
+
 struct Session {  // one h264_model + the picture-level syntax tables, carried across slices until NEW_MODEL
   Model model;
   PictureSyntax pic;
@@ -29,7 +31,13 @@ int run_all(const avr_slice_desc* descs, int n, const uint8_t* in, uint64_t in_b
     memset(&r, 0, sizeof r);
     r.out_off = all.size();
     if (d.in_off + d.in_size > in_bytes) { r.status = AVR_SLICE_CORRUPT; continue; }
-    if (!s || (d.flags & AVR_SLICE_NEW_MODEL)) s.reset(new Session());
+    if (!s || (d.flags & AVR_SLICE_NEW_MODEL)) {
+      s.reset(new Session());
+      if (d.n_streams & AVR_SLICE_PRIORS) {
+        if (!g_priors) { r.status = AVR_SLICE_CORRUPT; s.reset(); continue; }
+        s->model.priors = g_priors;
+      }
+    }
     if ((d.flags & AVR_SLICE_NEW_PICTURE) || s->pic.mbw != d.mb_width || s->pic.mbh != d.mb_height || s->model.frames[0].w == 0) {
       s->model.update_frame_spec(d.frame_num, d.mb_width, d.mb_height);  // frame_spec hook, h264_slice.c:568-573
       s->pic.start(d.mb_width, d.mb_height);
@@ -67,6 +75,9 @@ int run_all(const avr_slice_desc* descs, int n, const uint8_t* in, uint64_t in_b
 }  // namespace
 
 extern "C" {
+
+// the caller keeps the table (AVR_PRIOR_ENTRIES entries) alive; null: none
+void avr_oracle_set_priors(const uint16_t* table) { g_priors = table; }
 
 int avr_oracle_compress(const avr_slice_desc* descs, int n, const uint8_t* in, uint64_t in_bytes, avr_slice_result* res,
                         uint8_t** out, uint64_t* out_bytes) {

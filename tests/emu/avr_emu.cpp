@@ -12,6 +12,8 @@
 using namespace avr;
 
 static thread_local std::vector<uint32_t> g_hist;   // per-class bin counts of the last call (of this thread)
+static thread_local const uint16_t* g_priors = nullptr;   // prior table of the next call (avr_emu_set_priors / the file shim)
+static thread_local std::vector<uint16_t> g_last_counters;   // estimators as the last ordinary job of the last call left them
 
 template <class Dir>
 static int run(const avr_slice_desc* descs, int n, const uint8_t* in, uint64_t in_bytes, avr_slice_result* res,
@@ -39,7 +41,7 @@ static int run(const avr_slice_desc* descs, int n, const uint8_t* in, uint64_t i
   fill_shared_tables(&sh->tab, 0, 1);
   std::vector<MbCtx> row(max_mbw);
   g_hist.assign(size_t(n) * 8, 0);
-  JobArgs a{descs, ios.data(), in, arena.data(), res, g_hist.data()};
+  JobArgs a{descs, ios.data(), in, arena.data(), res, g_hist.data(), g_priors};
   JobMem m;
   m.sh = sh; m.row = row.data(); m.cnt = counters.data(); m.cnt8 = m.cnt;
   m.nnz0 = planes.data(); m.nnz1 = planes.data() + max_frame; m.nnz_frame_bytes = max_frame; m.max_mbw = uint32_t(max_mbw);
@@ -75,6 +77,7 @@ static int run(const avr_slice_desc* descs, int n, const uint8_t* in, uint64_t i
     run_job<Dir>(a, job, m, nullptr, 0, 0);
     i = j;
   }
+  g_last_counters.assign(counters.begin(), counters.begin() + MODEL_COUNTERS);
   delete sh;
   for (BlockShared* p : wsh) delete p;
   // compact
@@ -101,6 +104,14 @@ int avr_emu_decompress(const avr_slice_desc* descs, int n, const uint8_t* in, ui
   return run<Decompress>(descs, n, in, in_bytes, res, out, out_bytes);
 }
 void avr_emu_free(void* p) { free(p); }
+// the table slices with AVR_SLICE_PRIORS start from (the caller keeps it alive); null: none
+void avr_emu_set_priors(const uint16_t* table) { g_priors = table; }
+// the estimators (avr_core.cuh layout, AVR_PRIOR_ENTRIES of them) as the last ordinary job left them: tools/train_priors.py
+int avr_emu_last_counters(uint16_t* dst, int n) {
+  if (n != int(MODEL_COUNTERS) || g_last_counters.size() != size_t(n)) return -1;
+  memcpy(dst, g_last_counters.data(), size_t(n) * 2);
+  return 0;
+}
 int avr_emu_last_hist(uint32_t* dst, int n_slices) {
   if (size_t(n_slices) * 8 != g_hist.size()) return -1;
   memcpy(dst, g_hist.data(), g_hist.size() * 4);

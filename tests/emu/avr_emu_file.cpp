@@ -8,6 +8,7 @@
 struct avr_ctx {
   avr_config cfg;
   std::vector<uint8_t> out;
+  std::vector<uint16_t> priors;
   int calls = 0;
 };
 
@@ -18,7 +19,9 @@ static int emu_call(avr_ctx* c, const avr_slice_desc* descs, int n, const uint8_
   for (int i = 0; i < n; i++) {   // what avr_stage refuses (avr_lib.cu)
     const uint32_t k = descs[i].n_streams & AVR_STREAMS_MASK;
     if (k > AVR_MAX_STREAMS) return AVR_ERR_ARG;
+    if ((descs[i].n_streams & AVR_SLICE_PRIORS) && c->priors.empty()) return AVR_ERR_PRIORS;
   }
+  g_priors = c->priors.empty() ? nullptr : c->priors.data();
   uint8_t* o = nullptr;
   uint64_t ob = 0;
   const int rc = run<Dir>(descs, n, in, in_bytes, res, &o, &ob);
@@ -56,6 +59,24 @@ int avr_decompress(avr_ctx* c, const avr_slice_desc* descs, int n, const uint8_t
                    const uint8_t** out, uint64_t* out_bytes) {
   return emu_call<Decompress>(c, descs, n, in, in_bytes, res, out, out_bytes);
 }
+uint32_t avr_priors_digest_of(const uint16_t* table, uint32_t n_entries) {   // as avr_lib.cu
+  if (!table) return 0;
+  uint32_t h = 2166136261u;
+  for (uint32_t i = 0; i < n_entries; i++) { h = (h ^ (table[i] & 0xFF)) * 16777619u; h = (h ^ (table[i] >> 8)) * 16777619u; }
+  return h ? h : 1u;
+}
+int avr_set_priors(avr_ctx* c, const uint16_t* table, uint32_t n_entries) {
+  if (!c) return AVR_ERR_ARG;
+  if (!table) { c->priors.clear(); return AVR_OK; }
+  if (n_entries != AVR_PRIOR_ENTRIES) return AVR_ERR_ARG;
+  for (uint32_t i = 0; i < n_entries; i++) {
+    const uint32_t pos = table[i] & 0xFF, tot = table[i] >> 8;
+    if (pos < 1 || tot <= pos || tot > LIMIT_SIG) return AVR_ERR_ARG;
+  }
+  c->priors.assign(table, table + n_entries);
+  return AVR_OK;
+}
+uint32_t avr_priors_digest(avr_ctx* c) { return c && !c->priors.empty() ? avr_priors_digest_of(c->priors.data(), uint32_t(c->priors.size())) : 0; }
 int avr_ctx_wide_stream_bytes(avr_ctx* c) { return !c || c->cfg.wide_stream_bytes < 0 ? 32768 : c->cfg.wide_stream_bytes; }
 int avr_ctx_wide_batch_limit(avr_ctx* c) { return !c ? 0 : c->cfg.wide_batch_limit < 0 ? 4 * 148 : c->cfg.wide_batch_limit; }
 int avr_ctx_wide_max_streams(avr_ctx* c) {

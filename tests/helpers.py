@@ -214,3 +214,34 @@ def emu_files_call(fn, handle, blobs, mode=None):
             got.append(C.string_at(outs[i], out_sizes[i]))
             lib.avr_free(outs[i])
     return rc, got
+
+
+# ---- prior tables (chunked mode; include/avrecode_b200.h "static priors") ----
+_priors_keep = {}
+
+
+def set_test_priors(table):
+    """Gives the host emulation and the oracle the table that slices with AVR_SLICE_PRIORS start from (None: none).
+    table: a ctypes uint16 array (A.load_priors) or None."""
+    _priors_keep["t"] = table                       # both libraries only keep the pointer
+    emu_lib().avr_emu_set_priors.argtypes = [C.c_void_p]
+    oracle_lib().avr_oracle_set_priors.argtypes = [C.c_void_p]
+    emu_lib().avr_emu_set_priors(table)
+    oracle_lib().avr_oracle_set_priors(table)
+
+
+def random_priors(seed):
+    """A valid table with every entry different from {1, 1}: any index the device and the oracle disagree on shows."""
+    import random
+    rng = random.Random(seed)
+    t = (C.c_uint16 * _abi.AVR_PRIOR_ENTRIES)()
+    for i in range(_abi.AVR_PRIOR_ENTRIES):
+        tot = rng.randint(3, 0x50)
+        t[i] = rng.randint(1, tot - 1) | tot << 8
+    return t
+
+
+def with_priors(descs):
+    for d in descs:
+        d.n_streams |= _abi.AVR_SLICE_PRIORS
+    return descs

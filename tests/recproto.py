@@ -87,6 +87,16 @@ def _parse_msg(buf):
     return out
 
 
+def priors_digest(buf):
+    """Metadata field 2 (this library's chunked mode only, not in recode.proto): digest of the prior table, or 0."""
+    for num, v in _parse_msg(buf):
+        if num == 1:
+            for n2, v2 in _parse_msg(v):
+                if n2 == 2:
+                    return v2
+    return 0
+
+
 def parse(buf):
     """-> (metadata_version or None, [block dict])"""
     version = None

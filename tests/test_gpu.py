@@ -401,3 +401,54 @@ def test_multi_context_equals_one_device(ctx):
         A.MultiContext([0, 0])
     with pytest.raises(A.AvrError):
         A.MultiContext([n_dev])
+
+
+# ---- static priors (chunked mode): fresh models start from a table instead of {1, 1} everywhere ----
+@pytest.mark.parametrize("table", ["random", "shipped"])
+def test_priors_equal_oracle_and_round_trip(built, table):
+    """Slices that carry AVR_SLICE_PRIORS, ordinary and wide, both kernel variants: the device writes the oracle's bytes
+    (the oracle restates the table layout from the model keys, oracle/avr_oracle.hpp prior_index) and round-trips."""
+    kw = dict(width=640, height=368, frames=6, high=True, seed=3, ragged=True, slices=3, bpics=0.4, refs=2, p8x8=0.6)
+    data = H.gen_stream(**kw)
+    t = H.random_priors(7) if table == "random" else A.load_priors("default")
+    H.set_test_priors(t)
+    try:
+        for resident in (1, 0):
+            with A.Context(resident=resident) as c:
+                descs = H.with_priors(H.batch_descs(A.index_h264(data), False))
+                with pytest.raises(A.AvrError):                     # no table in this context yet
+                    c.compress(descs, data)
+                c.set_priors(bytes(t))
+                for i, d in enumerate(descs):
+                    d.n_streams |= H.WIDE_PATTERN[i % len(H.WIDE_PATTERN)]
+                res, blob = c.compress(descs, data)
+                r_o, b_o = H.oracle_compress(descs, data)
+                assert [r.status for r in res] == [r.status for r in r_o] == [0] * len(descs)
+                assert H.slices_of(res, blob) == H.slices_of(r_o, b_o)
+                check_roundtrip(c, descs, data, res, blob)
+                plain = H.batch_descs(A.index_h264(data), False)  # without the flag: the reference's {1, 1}
+                r_p, b_p = c.compress(plain, data)
+                r_q, b_q = H.oracle_compress(plain, data)
+                assert H.slices_of(r_p, b_p) == H.slices_of(r_q, b_q)
+    finally:
+        H.set_test_priors(None)
+
+
+def test_priors_in_the_container_on_the_device(ctx):
+    data = H.gen_stream(width=640, height=368, frames=6, high=True, seed=41, kbps=6000)
+    name = CASES[0]
+    gold, gold_rec = load_case(name)
+    with A.Context() as primed:
+        primed.set_priors("default")
+        assert primed.priors_digest == A.priors_digest_of("default") != 0 and ctx.priors_digest == 0
+        rec_p = primed.file_compress(data, A.MODE_SLICE)
+        rec_0 = ctx.file_compress(data, A.MODE_SLICE)
+        assert recproto.priors_digest(rec_p) == primed.priors_digest and recproto.priors_digest(rec_0) == 0
+        assert len(rec_p) < len(rec_0)
+        assert primed.file_decompress(rec_p) == data and primed.file_decompress(rec_0) == data
+        with pytest.raises(A.AvrError) as e:
+            ctx.file_decompress(rec_p)
+        assert e.value.code == _abi.AVR_ERR_PRIORS
+        assert primed.file_compress(gold, A.MODE_FILE) == gold_rec     # the reference's format does not use the table
+        primed.set_priors(None)
+        assert primed.priors_digest == 0 and primed.file_compress(data, A.MODE_SLICE) == rec_0

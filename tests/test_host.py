@@ -321,3 +321,95 @@ def test_multi_device_argument_errors(built):
     assert lib.avr_multi_create(None, (C.c_int * 1)(0), 0, C.byref(m)) != 0
     assert lib.avr_multi_create(None, None, 2, C.byref(m)) != 0
     assert lib.avr_multi_ctx(None, 0) is None
+
+
+# ---- static priors (chunked mode): fresh models start from a table instead of {1, 1} everywhere ----
+def test_shipped_prior_table_is_valid(built):
+    t = A.load_priors("default")
+    assert len(t) == _abi.AVR_PRIOR_ENTRIES == 47892
+    assert all(1 <= (v & 0xFF) < (v >> 8) <= 0x50 for v in t)
+    assert sum(1 for v in t if v != 0x0201) > 4000
+
+
+@pytest.mark.parametrize("kw", [
+    dict(width=480, height=272, frames=6, slices=4, seed=2),
+    dict(width=640, height=368, frames=5, high=True, seed=3, ragged=True, slices=3),
+    dict(width=480, height=272, frames=8, bpics=0.8, seed=17, refs=4, high=True, p8x8=0.8, pskip=0.5),
+], ids=lambda k: "seed%d" % k["seed"])
+def test_prior_table_layout_restatement_equals_device_logic(built, kw):
+    """The oracle maps a model KEY (recode.cpp:676-815, :884) to its table index from the documented layout
+    (oracle/avr_oracle.hpp prior_index), the device code indexes the table with its own arithmetic: with a random table
+    -- no entry {1, 1} -- every estimator either side would look up elsewhere changes the bytes.  Ordinary and wide
+    slices; each decodes the other's output."""
+    data = H.gen_stream(**kw)
+    H.set_test_priors(H.random_priors(kw["seed"]))
+    try:
+        descs = H.with_priors(H.batch_descs(A.index_h264(data), False))
+        for i, d in enumerate(descs):
+            d.n_streams |= H.WIDE_PATTERN[i % len(H.WIDE_PATTERN)]
+        r_e, b_e = H.emu_compress(descs, data)
+        r_o, b_o = H.oracle_compress(descs, data)
+        assert [r.status for r in r_o] == [0] * len(descs)
+        assert H.slices_of(r_e, b_e) == H.slices_of(r_o, b_o)
+        dd = H.coded_descs(descs, r_o)
+        for dec in (H.oracle_decompress, H.emu_decompress):
+            r_d, b_d = dec(dd, b_o)
+            assert H.roundtrip_ok(descs, r_d, b_d, data)
+        plain = H.batch_descs(A.index_h264(data), False)
+        r_p, b_p = H.emu_compress(plain, data)                       # without the flag the table is not used
+        H.set_test_priors(None)
+        r_q, b_q = H.emu_compress(plain, data)
+        assert H.slices_of(r_p, b_p) == H.slices_of(r_q, b_q) != H.slices_of(r_e, b_e)
+        r_x, _ = H.oracle_compress(descs, data)                      # the flag without a table: refused
+        assert all(r.status != 0 for r in r_x)
+    finally:
+        H.set_test_priors(None)
+
+
+def test_priors_in_the_container(built, emu_multi):
+    """File layer: chunked containers record the digest of the table they were written from (Metadata field 2) and are
+    refused by a context that holds another (or none); the reference's mode never uses the table; the shipped table
+    makes the synthetic test streams smaller."""
+    lib = H.emu_file_lib()
+    lib.avr_set_priors.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32]
+    lib.avr_multi_set_priors.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32]
+    lib.avr_priors_digest_of.restype = C.c_uint32
+    lib.avr_priors_digest_of.argtypes = [C.c_void_p, C.c_uint32]
+    table = A.load_priors("default")
+    files = [load_case(n)[0] for n in FILE_LAYER_CASES]
+    want_file = [load_case(n)[1] for n in FILE_LAYER_CASES]
+    plain, primed = C.c_void_p(), C.c_void_p()
+    assert lib.avr_create(None, C.byref(plain)) == 0 and lib.avr_create(None, C.byref(primed)) == 0
+    try:
+        assert lib.avr_set_priors(primed, table, len(table)) == 0
+        assert lib.avr_set_priors(primed, table, len(table) - 1) == _abi.AVR_ERR_ARG
+        bad = (C.c_uint16 * len(table))(*table)
+        bad[5] = 0x0200                                               # pos = 0
+        assert lib.avr_set_priors(plain, bad, len(bad)) == _abi.AVR_ERR_ARG
+        rc, rec_0 = H.emu_files_call(lib.avr_files_compress, plain, files, A.MODE_SLICE)
+        rc1, rec_p = H.emu_files_call(lib.avr_files_compress, primed, files, A.MODE_SLICE)
+        assert rc == 0 and rc1 == 0
+        digest = lib.avr_priors_digest_of(table, len(table))
+        assert digest != 0 and [recproto.priors_digest(r) for r in rec_p] == [digest] * len(files)
+        assert [recproto.priors_digest(r) for r in rec_0] == [0] * len(files)
+        assert sum(map(len, rec_p)) < sum(map(len, rec_0))
+        rc, back = H.emu_files_call(lib.avr_files_decompress, primed, rec_p)
+        assert rc == 0 and back == files
+        rc, back = H.emu_files_call(lib.avr_files_decompress, primed, rec_0)      # a table does no harm to plain containers
+        assert rc == 0 and back == files
+        rc, _ = H.emu_files_call(lib.avr_files_decompress, plain, rec_p)
+        assert rc == _abi.AVR_ERR_PRIORS
+        assert lib.avr_set_priors(plain, H.random_priors(1), len(table)) == 0     # another table: refused as well
+        rc, _ = H.emu_files_call(lib.avr_files_decompress, plain, rec_p)
+        assert rc == _abi.AVR_ERR_PRIORS
+        rc, rec_f = H.emu_files_call(lib.avr_files_compress, primed, files, A.MODE_FILE)
+        assert rc == 0 and rec_f == list(want_file)                   # the reference's format, byte for byte
+        # several devices: every one holds the table, same containers
+        assert lib.avr_multi_set_priors(emu_multi, table, len(table)) == 0
+        rc, many = H.emu_files_call(lib.avr_multi_files_compress, emu_multi, files, A.MODE_SLICE)
+        assert rc == 0 and many == rec_p
+        rc, back = H.emu_files_call(lib.avr_multi_files_decompress, emu_multi, rec_p)
+        assert rc == 0 and back == files
+    finally:
+        lib.avr_multi_set_priors(emu_multi, None, 0)
+        lib.avr_destroy(plain); lib.avr_destroy(primed)
