@@ -588,7 +588,7 @@ struct RingCtl {
 };
 enum : uint32_t { REC_ENTRIES = 256 };
 struct RingShared : RingCtl { uint32_t e[RING_ENTRIES]; };   // parser -> the warp behind it
-struct RecRing : RingCtl { alignas(8) uint32_t e[REC_ENTRIES]; };   // second warp -> third warp of a block (one or two words per bin)
+struct RecRing : RingCtl { uint32_t e[REC_ENTRIES]; };       // compress: estimator warp -> range-coder warp
 AVR_DEV void ring_reset(RingCtl* r) { r->tail_pub = 0; r->head_pub = 0; r->prod_tail = 0; r->cons_head = 0; r->prod_wait = 0; r->cons_wait = 0; }
 // makes room for an entry of n words: publishes what is complete, waits for the consumer if the ring is full; returns
 // the tail value up to which the producer may go on without looking again.  One out-of-line copy (instruction cache).
@@ -636,7 +636,6 @@ struct WordSrc {       // words of a batch: the shared-memory ring itself (mask 
   const uint32_t* e;
   uint32_t at, mask;
   AVR_DEV uint32_t take() { return e[at++ & mask]; }
-  AVR_DEV U2 take2() { const U2 v = *reinterpret_cast<const U2*>(&e[at & mask]); at += 2; return v; }   // at even
 };
 
 #if defined(__CUDACC__) && !defined(AVR_HOST_EMULATION)
@@ -716,17 +715,10 @@ struct RecWriter {     // producer side of the record ring, in registers (lane 0
     r->e[tail & (REC_ENTRIES - 1)] = w;
     tail++;
   }
-  AVR_DEV void put2(uint32_t w0, uint32_t w1) {   // a record of two words (tail stays even: one 8-byte store)
-    if (int32_t(limit - tail) < 2) limit = ring_slow(r, tail, 2, REC_ENTRIES, false);
-    U2 v; v.x = w0; v.y = w1;
-    *reinterpret_cast<U2*>(&r->e[tail & (REC_ENTRIES - 1)]) = v;
-    tail += 2;
-  }
   AVR_DEV void publish() { ring_fence(); *reinterpret_cast<volatile uint32_t*>(&r->tail_pub) = tail; }
 #else
   void init(RecRing* ring) { r = ring; }
   void put(uint32_t w) { r->e.push_back(w); }
-  void put2(uint32_t w0, uint32_t w1) { r->e.push_back(w0); r->e.push_back(w1); }
   void publish() {}
 #endif
 };
@@ -889,83 +881,14 @@ struct RangeWarp {
   AVR_DEV bool overflowed() const { return rc.sink->overflow != 0; }
 };
 
-// Decompression has TWO recurrences behind the parser as well: the context states (serial per context) and the CABAC
-// arithmetic encoder (serial per slice: range, low, the bytes).  One warp doing both ran at 227 cycles per bin
-// (profiles/r2j_probes.txt) and, from two parsers on, set the time of a wide slice; so they are two warps joined by the
-// block's record ring, one RECORD of two words per bin:
-//   decision   w0 = the context's four rangeTabLPS bytes (entry word y), w1 = entry word x (valMPS, state, the
-//              renormalisation shifts of an LPS) with bit 1 = "this bin is the LPS"
-//   bypass / terminate   w0 = the bin, w1 = REC_BYPASS / REC_TERM;   REC_END closes the slice
-enum : uint32_t { REC_LPS = 1u << 1, REC_KIND = 3u << 2, REC_BYPASS = 1u << 2, REC_TERM = 2u << 2, REC_END = 3u << 2 };
-struct CtxOut {            // the context warp's view of the encoder: same calls as CabacOut, records instead of bytes
-  RecWriter out;
-  AVR_DEV void encode_core(const SharedTables& t, const U2 e, int bin, U2* next) {
-    const U4 pair = ctx_trans_row(t, e.x);
-    const uint32_t lps = uint32_t(bin) != (e.x & 1) ? 1u : 0u;
-    next->x = lps ? pair.z : pair.x;
-    next->y = lps ? pair.w : pair.y;
-    out.put2(e.y, (e.x & ~0xEu) | lps << 1);
-  }
-  AVR_DEV void decision(const SharedTables& t, int bin, U2* ctx) {
-    U2 n;
-    encode_core(t, *ctx, bin, &n);
-    *ctx = n;
-  }
-  AVR_DEV void bypass(int bin) { out.put2(uint32_t(bin), REC_BYPASS); }
-  AVR_DEV void terminate(int bin) { out.put2(uint32_t(bin), REC_TERM); }
-};
-
-// the arithmetic warp of a decompression (cabac_code.h:16-86 minus the context states): records -> slice_data bytes
-struct ArithWarp {
+// Decompression behind the parser stays ONE warp (context states + CABAC arithmetic).  Tried and dropped
+// (profiles/r2o_ab_decompress_split.txt): splitting it like the compressor's coder into a context warp and an arithmetic
+// warp joined by the record ring.  The parser is the slow stage of this direction, so a lone slice gained nothing
+// (409.6 -> 408.4 ms on the profile case), and with every SM full the third warp's instructions cost 21 % of the
+// throughput (1728 slices: 999 -> 1209 ms).
+struct CoderDecompress {   // CABAC re-encoder (cabac_code.h:16-86; recode.cpp:1443, 1455, 1466)
   CabacOut cabac;
   AVR_DEV void begin(ByteSink* sink, uint8_t* dst, uint32_t cap, int esc_zeros = -1) { cabac.init(sink, dst, cap, esc_zeros); }
-  AVR_DEV void decision(uint32_t w0, uint32_t w1) {   // CabacOut::encode_core with the context side already resolved
-    uint32_t low = cabac.low, range = cabac.range;
-    const uint32_t tq = range >> 6;
-    const uint32_t rlps = rlps_by_t(w0, tq);
-    const uint32_t sh_lps = (w1 >> (3 * tq + (CTX_SHLPS_SHIFT - 12))) & 7;
-    range -= rlps;
-    const uint32_t sh_mps = (range >> 8) ^ 1;
-    const bool lps = (w1 & REC_LPS) != 0;
-    if (lps) { low += range; range = rlps; }
-    const int shift = int(lps ? sh_lps : sh_mps);
-    cabac.range = range << shift; cabac.low = low << shift; cabac.queue += shift;
-    cabac.put_bytes();
-  }
-  AVR_DEV void run(RecRing* records, uint32_t* stage, int lane) {
-    RingReader q; q.init_rec(records);
-    for (;;) {
-      WordSrc src;
-      const uint32_t n = coder_fetch(q, nullptr, 0, stage, lane, &src);   // whole records: the writer's tail is always even
-      uint32_t done = 0;
-      if (lane == 0) {
-        // a record never changes once written: record k + 1 is fetched while record k goes through the encoder
-        U2 rec = src.take2();
-#pragma unroll 2
-        for (uint32_t k = 2;; k += 2) {
-          U2 nxt; nxt.x = 0; nxt.y = REC_END;
-          if (k < n) nxt = src.take2();
-          const uint32_t kind = rec.y & REC_KIND;
-          if (kind == 0) decision(rec.x, rec.y);
-          else if (kind == REC_BYPASS) cabac.bypass(int(rec.x));
-          else if (kind == REC_TERM) cabac.terminate(int(rec.x));
-          else { done = 1; break; }
-          if (k >= n) break;
-          rec = nxt;
-        }
-      }
-      done = AVR_BCAST_CORE(done);
-      q.release(n, lane);
-      if (done) break;
-    }
-  }
-  AVR_DEV uint32_t out_bytes() const { return cabac.sink->n; }
-  AVR_DEV bool overflowed() const { return cabac.sink->overflow != 0; }
-};
-
-struct CoderDecompress {   // the context warp: entries -> bins -> context states (recode.cpp:1443, 1455, 1466) -> records
-  CtxOut cabac;
-  AVR_DEV void begin(RecRing* records) { cabac.out.init(records); }
   // significant_coeff_flag / last_significant_coeff_flag bins of a block out of its mask (h264_cabac.c:1667-1703);
   // the last coefficient of a full scan is inferred, not coded.  4x4-class blocks: position i uses contexts
   // sig_base + i and last_base + i, all distinct, so the entries of the next position are fetched ahead.
@@ -1045,11 +968,10 @@ struct CoderDecompress {   // the context warp: entries -> bins -> context state
 #pragma unroll 1
         while (src.at - at0 < n) {
           const uint32_t e = src.take();
-          if (e & SYM_END) { done = 1; cabac.out.put2(0, REC_END); break; }
+          if (e & SYM_END) { done = 1; break; }
           entry(src, t, cstate, e);
         }
         used = src.at - at0;
-        cabac.out.publish();
       }
       used = AVR_BCAST_CORE(used); done = AVR_BCAST_CORE(done);
       q.release(used, lane);
@@ -1074,7 +996,7 @@ struct CoderDecompress {   // the context warp: entries -> bins -> context state
 #pragma unroll 1
         while (src.at - at0 < n) {
           const uint32_t e = src.take();
-          if (e & SYM_END) { why = 2; if (!draining) cabac.out.put2(0, REC_END); break; }
+          if (e & SYM_END) { why = 2; break; }
           if (draining) { if (e & SYM_BLOCK) src.at += (e & 7) == 5 ? 2 : 1; continue; }   // skip a block's mask words
           if (!(e & (SYM_LEVEL | SYM_BLOCK)) && (e & (3u << SYM_KIND_SHIFT)) == SYM_SPECIAL) {
             if (e & SP_ROW_END) { qpd = e & 1; why = 1; break; }
@@ -1082,7 +1004,6 @@ struct CoderDecompress {   // the context warp: entries -> bins -> context state
           } else entry(src, t, cstate, e);
         }
         used = src.at - at0;
-        cabac.out.publish();
       }
       used = AVR_BCAST_CORE(used); why = AVR_BCAST_CORE(why);
       q.release(used, lane);
@@ -1098,6 +1019,8 @@ struct CoderDecompress {   // the context warp: entries -> bins -> context state
       q.head = uint32_t(rings[cur].cons_head);
     }
   }
+  AVR_DEV uint32_t out_bytes() const { return cabac.sink->n; }
+  AVR_DEV bool overflowed() const { return cabac.sink->overflow != 0; }
 };
 
 // ------------------------------------------------------------------------------------------------
@@ -1348,7 +1271,6 @@ struct Compress {
 struct Decompress {
   static constexpr bool kDecompress = true;
   typedef CoderDecompress Coder;
-  typedef ArithWarp Tail;
   ByteWindow in;
   ParserHome* h;
   uint16_t* cnt;     // parser owns the estimators

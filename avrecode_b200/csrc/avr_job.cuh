@@ -11,7 +11,7 @@
 #include "avr_walk.cuh"
 
 #if defined(__CUDACC__) && !defined(AVR_HOST_EMULATION)
-#define AVR_THREADS_OF(Dir) 96   // parser warp + estimator / context warp + range-coder / arithmetic warp
+#define AVR_THREADS_OF(Dir) ((Dir::kDecompress) ? 64 : 96)   // parser warp + coder warp (+ compress: range-coder warp)
 #define AVR_HOST_STAGE(x) nullptr   // the device reads a shared-memory ring in place
 #define AVR_LANES 32
 #define AVR_SYNCWARP() __syncwarp()
@@ -400,32 +400,32 @@ AVR_DEV void write_result(const JobArgs& a, const JobMem& m, const SliceIO& io, 
   write_hist(a, s, &m.sh->phome, 1, res.n_mbs, res.n_bins);
   m.sh->final_status = uint32_t(res.status);
 }
-// the warp behind the parser -- compress: the estimator warp; decompress: the context warp.  Both feed the record ring.
+// the warp behind the parser -- decompress: the CABAC re-encoder, which owns the output bytes and (ordinary slices) the
+// slice result; compress: the estimator warp, which feeds the record ring
 template <class Dir>
-AVR_DEV void coder_role(const JobMem& m, const Unit& u, int lane) {
+AVR_DEV void coder_role(const JobArgs& a, const JobMem& m, const Unit& u, const SliceIO& io, uint32_t s, int lane) {
   typename Dir::Coder c;
-  if constexpr (Dir::kDecompress) c.begin(&m.sh->records); else c.begin(&m.sh->records, m.cnt8);
   if constexpr (Dir::kDecompress) {
-    if (u.w.ctl) c.run_wide(u.w.ctl->ring, u.K, u.w.far, u.w.far_cap, m.sh->tab, m.sh->cstate, m.sh->stage, lane);
-    else c.run(&m.sh->ring, m.sh->tab, m.sh->cstate, AVR_HOST_STAGE(m.sh->stage), lane);
+    c.begin(&m.sh->sink, u.dst, u.dst_cap, u.esc_zeros);
+    if (u.w.ctl) {
+      c.run_wide(u.w.ctl->ring, u.K, u.w.far, u.w.far_cap, m.sh->tab, m.sh->cstate, m.sh->stage, lane);
+      if (lane == 0) { u.w.ctl->out_size[0] = c.out_bytes(); if (c.overflowed()) u.w.ctl->overflow = 1; }
+    } else {
+      c.run(&m.sh->ring, m.sh->tab, m.sh->cstate, AVR_HOST_STAGE(m.sh->stage), lane);
+      if (lane == 0) write_result(a, m, io, s, c.out_bytes(), c.overflowed(), false);
+    }
   } else {
+    c.begin(&m.sh->records, m.cnt8);
     c.run(&m.sh->ring, u.w.ctl ? &u.w.ctl->ring[u.j] : nullptr, u.w.ctl ? u.w.far + size_t(u.j) * u.w.far_cap : nullptr, u.w.far_cap,
           m.sh->tab, m.cnt, m.sh->stage, lane);
   }
   AVR_SYNCWARP();
 }
-// the last warp of the pipeline, which owns the output bytes and (ordinary slices) the slice result -- compress: the
-// range coder; decompress: the CABAC arithmetic encoder
-template <class Dir>
-AVR_DEV void tail_role(const JobArgs& a, const JobMem& m, const Unit& u, const SliceIO& io, uint32_t s, int lane) {
-  typename Dir::Tail c;
-  if constexpr (Dir::kDecompress) {
-    c.begin(&m.sh->sink, u.dst, u.dst_cap, u.esc_zeros);
-    c.run(&m.sh->records, AVR_HOST_STAGE(m.sh->stage2), lane);
-  } else {
-    c.begin(&m.sh->sink, u.dst, u.dst_cap);
-    c.run(&m.sh->records, m.sh->tab, AVR_HOST_STAGE(m.sh->stage2), lane);
-  }
+// compress: the range-coder warp, which owns the output bytes and (ordinary slices) the slice result
+AVR_DEV void range_role(const JobArgs& a, const JobMem& m, const Unit& u, const SliceIO& io, uint32_t s, int lane) {
+  RangeWarp c;
+  c.begin(&m.sh->sink, u.dst, u.dst_cap);
+  c.run(&m.sh->records, m.sh->tab, AVR_HOST_STAGE(m.sh->stage2), lane);
   if (lane == 0) {
     if (u.w.ctl) { u.w.ctl->out_size[u.j] = c.out_bytes(); if (c.overflowed()) u.w.ctl->overflow = 1; }
     else write_result(a, m, io, s, c.out_bytes(), c.overflowed(), true);
@@ -598,12 +598,12 @@ AVR_DEV void run_job(const JobArgs& a, const JobDesc& job, const JobMem& m, cons
     if (walk) {
 #if defined(__CUDACC__) && !defined(AVR_HOST_EMULATION)
       if (tid < 32) { if (u.parse) parser_role<Dir>(m, u, d, ft.cur, use_planes, lane); }
-      else if (tid < 64) { if (u.code) coder_role<Dir>(m, u, lane); }
-      else if (u.code) tail_role<Dir>(a, m, u, io, s, lane);
+      else if (tid < 64) { if (u.code) coder_role<Dir>(a, m, u, io, s, lane); }
+      else if (u.code) range_role(a, m, u, io, s, lane);
 #else
       if (u.parse) parser_role<Dir>(m, u, d, ft.cur, use_planes, lane);
-      if (u.code) coder_role<Dir>(m, u, lane);
-      if (u.code) tail_role<Dir>(a, m, u, io, s, lane);
+      if (u.code) coder_role<Dir>(a, m, u, io, s, lane);
+      if (u.code && !Dir::kDecompress) range_role(a, m, u, io, s, lane);
 #endif
     } else if (tid == 0 && (!wide || role == 0)) {
       avr_slice_result r;
@@ -660,13 +660,9 @@ void emu_wide_slice(const JobArgs& a, uint32_t s, JobMem* mems, const WideMem& w
     delete[] wk;
     BlockShared* sh = mems[0].sh;
     init_contexts(sh->cstate, d, 0, 1);
-    ring_reset(&sh->records);
-    CoderDecompress cw;
-    cw.begin(&sh->records);
-    cw.run_wide(w.ctl->ring, K, nullptr, 0, sh->tab, sh->cstate, sh->stage, 0);
-    ArithWarp c;
+    CoderDecompress c;
     c.begin(&sh->sink, a.out_arena + io.out_off, io.out_cap, (d.n_streams & AVR_SLICE_ESCAPED) ? int((d.n_streams >> AVR_ESC_ZEROS_SHIFT) & 3) : -1);
-    c.run(&sh->records, sh->stage2, 0);
+    c.run_wide(w.ctl->ring, K, nullptr, 0, sh->tab, sh->cstate, sh->stage, 0);
     int status = AVR_SLICE_OK;
     uint32_t mbs = 0;
     uint64_t bins = 0;

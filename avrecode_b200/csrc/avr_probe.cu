@@ -236,71 +236,25 @@ __device__ void probe_range(ProbeShared* sh, const ProbeArgs& a, uint64_t* r, in
   r[0] = uint64_t(t1 - t0); r[1] = bins; r[2] = w.rc.low;
 }
 
-// 6: the two warps behind the decompress parser as a pipeline: context warp (warp 0) -> record ring -> arithmetic warp
-//    (warp 1), over a full ring of block / level entries.  mode 1 (probe 10): warp 1 only takes the records away, so the
-//    figure is the context warp's own.
-__device__ void probe_coder_d(ProbeShared* sh, const ProbeArgs& a, uint64_t* r, int tid, int mode) {
-  const int lane = tid & 31;
+// 6: the decompress coder warp (lane 0 runs the CABAC re-encoder: context states + arithmetic) over a full ring
+__device__ void probe_coder_d(ProbeShared* sh, const ProbeArgs& a, uint64_t* r, int lane) {
   uint32_t per = 0;
-  if (tid == 0) per = fill_ring(sh, true);
-  __syncthreads();
+  if (lane == 0) per = fill_ring(sh, true);
+  per = __shfl_sync(0xFFFFFFFFu, per, 0);
   uint64_t bins = 0;
-  const long long t0 = clock64();
-#pragma unroll 1
-  for (uint32_t i = 0; i < a.iters; i++) {
-    if (tid == 0) { ring_reset(&sh->records); sh->sink.n = 0; }
-    __syncthreads();
-    if (tid < 32) {
-      CoderDecompress c;
-      c.begin(&sh->records);
-      c.run(&sh->ring, sh->tab, sh->cstate, nullptr, lane);
-    } else if (mode == 0) {
-      ArithWarp w;
-      w.begin(&sh->sink, sh->out, sizeof sh->out);
-      w.run(&sh->records, nullptr, lane);
-    } else {
-      RingReader q; q.init_rec(&sh->records);
-      for (;;) {
-        const uint32_t n = q.wait_avail();
-        const uint32_t last = sh->records.e[(q.head + n - 1) & (REC_ENTRIES - 1)];
-        q.release(n, lane);
-        if ((last & REC_KIND) == REC_END) break;
-      }
-    }
-    __syncthreads();
-    bins += per;
-  }
-  const long long t1 = clock64();
-  r[0] = uint64_t(t1 - t0); r[1] = bins; r[2] = sh->sink.n;
-}
-
-// 9: the arithmetic warp alone over a full record ring (ArithWarp::run): decisions of mixed states, one bypass in eight
-__device__ void probe_arith(ProbeShared* sh, const ProbeArgs& a, uint64_t* r, int lane) {
-  if (lane == 0) {
-    uint32_t s = 99u;
-    for (uint32_t i = 0; i + 2 < REC_ENTRIES; i += 2) {
-      const uint32_t p = lcg(s) % 63, mps = lcg(s) & 1;
-      U2 e; e.x = ctx_word_x(p << 1 | mps); e.y = rlps4_of(p);
-      if (lcg(s) % 8 == 0) { sh->records.e[i] = lcg(s) & 1; sh->records.e[i + 1] = REC_BYPASS; }
-      else { sh->records.e[i] = e.y; sh->records.e[i + 1] = (e.x & ~0xEu) | (lcg(s) % 4 == 0 ? uint32_t(REC_LPS) : 0u); }
-    }
-    sh->records.e[REC_ENTRIES - 2] = 0; sh->records.e[REC_ENTRIES - 1] = REC_END;
-    sh->records.tail_pub = REC_ENTRIES; sh->records.head_pub = 0;
-  }
+  CoderDecompress c;
+  c.begin(&sh->sink, sh->out, sizeof sh->out);
   __syncwarp();
-  uint64_t bins = 0;
-  ArithWarp w;
-  w.begin(&sh->sink, sh->out, sizeof sh->out);
   const long long t0 = clock64();
 #pragma unroll 1
   for (uint32_t i = 0; i < a.iters; i++) {
-    w.run(&sh->records, nullptr, lane);
+    c.run(&sh->ring, sh->tab, sh->cstate, nullptr, lane);
     if (lane == 0) sh->sink.n = 0;
-    bins += REC_ENTRIES / 2 - 1;
+    bins += per;
     __syncwarp();
   }
   const long long t1 = clock64();
-  r[0] = uint64_t(t1 - t0); r[1] = bins; r[2] = w.cabac.low;
+  r[0] = uint64_t(t1 - t0); r[1] = bins; r[2] = c.cabac.low;
 }
 
 // 7: one macroblock-level bin through the out-of-line primitive (compress: CABAC decision on the shared-memory copy
@@ -325,12 +279,10 @@ __global__ void __launch_bounds__(64, 1) avr_probe_kernel(ProbeArgs a) {
   __shared__ ProbeShared sh;
   probe_setup(&sh, threadIdx.x, int(blockDim.x));
   __syncthreads();
-  if (WHICH == 5 || WHICH == 6 || WHICH == 8 || WHICH == 9 || WHICH == 10) {   // warp-wide roles
+  if (WHICH == 5 || WHICH == 6 || WHICH == 8) {   // warp-wide roles
     uint64_t r[3] = {0, 0, 0};
     if (WHICH == 5) probe_coder_c(&sh, a, r, int(threadIdx.x));
-    if (WHICH == 6) probe_coder_d(&sh, a, r, int(threadIdx.x), 0);
-    if (WHICH == 10) probe_coder_d(&sh, a, r, int(threadIdx.x), 1);
-    if (WHICH == 9) probe_arith(&sh, a, r, int(threadIdx.x));
+    if (WHICH == 6) probe_coder_d(&sh, a, r, int(threadIdx.x));
     if (WHICH == 8) probe_range(&sh, a, r, int(threadIdx.x));
     if (threadIdx.x == 0) { a.result[0] = r[0]; a.result[1] = r[1]; a.result[2] = r[2]; }
   } else if (threadIdx.x == 0) {
@@ -357,11 +309,9 @@ const char* avr_probe_name(int which) {
     "decompress bin: estimator + exact division + RangeDec::get + update (Decompress::coded)",
     "decompress significance loop, 4x4 block (both successors prefetched)",
     "compress, the two warps behind the parser as a pipeline: estimator warp -> records -> range-coder warp, over block / level entries",
-    "decompress, the two warps behind the parser as a pipeline: context warp -> records -> arithmetic warp, over block / level entries",
+    "decompress coder warp: CABAC re-encoder over a ring of block / level entries (CoderDecompress::run)",
     "macroblock-level bin, compress: out-of-line CABAC decision on the shared-memory engine copy + ring entry",
     "compress range-coder warp alone: reciprocal + RangeEnc::put over a ring of records (RangeWarp::run)",
-    "decompress arithmetic warp alone: CABAC range / low / bytes over a ring of records (ArithWarp::run)",
-    "decompress context warp alone: entries -> bins -> context states -> records, the records taken away unread (CoderDecompress::run)",
   };
   return which >= 0 && which < int(sizeof names / sizeof names[0]) ? names[which] : nullptr;
 }
@@ -383,11 +333,9 @@ int avr_probe(int device, int which, uint32_t iters, uint64_t* cycles, uint64_t*
       case 3: avr_probe_kernel<3><<<1, 32>>>(a); break;
       case 4: avr_probe_kernel<4><<<1, 32>>>(a); break;
       case 5: avr_probe_kernel<5><<<1, 64>>>(a); break;
-      case 6: avr_probe_kernel<6><<<1, 64>>>(a); break;
+      case 6: avr_probe_kernel<6><<<1, 32>>>(a); break;
       case 7: avr_probe_kernel<7><<<1, 32>>>(a); break;
-      case 8: avr_probe_kernel<8><<<1, 32>>>(a); break;
-      case 9: avr_probe_kernel<9><<<1, 32>>>(a); break;
-      default: avr_probe_kernel<10><<<1, 64>>>(a); break;
+      default: avr_probe_kernel<8><<<1, 32>>>(a); break;
     }
     if (cudaDeviceSynchronize() != cudaSuccess) { cudaGetLastError(); cudaFree(d); return AVR_ERR_CUDA; }
   }

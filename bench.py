@@ -352,12 +352,15 @@ class Gpu:
         finally:
             self.cc.set_priors("default")
 
-    def descs_of(self, data, wide=True):
+    def descs_of(self, data, wide=True, n_batch=0):
+        """n_batch: CABAC slices of the whole batch these descriptors go into (0: just this file's)."""
         A, H = self.A, self.H
         descs = H.batch_descs(A.index_h264(data), mode_file=False)
         if wide:
-            for d in descs:   # what the file API does in chunked mode: long slices become wide slices
-                d.n_streams = A.slice_streams(d)
+            # what the file API does in chunked mode: long slices become wide slices -- while the batch is small enough to
+            # be a latency job (avr_config.wide_batch_limit); a throughput batch gets none
+            for d in descs:
+                d.n_streams = self.cc.slice_streams(d, n_batch or len(descs))
         return descs
 
     def prepare(self, name, data, copies=1):
@@ -365,7 +368,7 @@ class Gpu:
         ordinary slices' coded bytes equal the oracle's (digest in tests/golden/bench_gate.json).  Nothing under oracle/
         runs here."""
         H, cc, cd = self.H, self.cc, self.cd
-        descs = self.descs_of(data)
+        descs = self.descs_of(data, n_batch=copies * len(self.A.index_h264(data)) if copies > 1 else 0)
         arena = data
         if copies > 1:   # the same file `copies` times in one batch
             pad = (-len(data)) % 16
@@ -485,8 +488,9 @@ class Gpu:
         del back
         # kernel only, inputs resident in HBM
         pieces, descs, offs = [], [], 0
+        n_total = sum(len(self.A.index_h264(c)) for c in clips)
         for c in clips:
-            for d in self.descs_of(c):
+            for d in self.descs_of(c, n_batch=n_total):
                 d.in_off += offs
                 descs.append(d)
             pad = (-len(c)) % 16

@@ -1,11 +1,13 @@
 #!/bin/bash
-# A/B of two builds of the library (build/ab/base.so, build/ab/new.so) on the P/B-slice case and the profile case
-O=gpurun_out; T=${1:-ab}
-for v in base new; do
+# A/B of builds of the library (build/ab/<name>.so) on the throughput case, the P/B-slice case and the profile case
+# usage: tools/gpu_ab.sh <tag> <name> [<name> ...]
+O=gpurun_out; T=$1; shift
+cp avrecode_b200/libavrecode_b200.so build/ab/_keep.so
+for v in "$@"; do
   cp build/ab/$v.so avrecode_b200/libavrecode_b200.so
   echo "== $v"
-  timeout 300 python tools/pb_case.py 2>&1 | tail -4 | tee $O/${T}_pb_$v.txt
-  timeout 300 python tools/profile_case.py 30 0 2>&1 | tail -3 | tee $O/${T}_profile_$v.txt
+  THROUGHPUT_RESIDENT=1 timeout 600 python tools/throughput_case.py ${AB_CLIPS:-32} 2>&1 | tail -1 | tee $O/${T}_tp_$v.txt
+  timeout 300 python tools/pb_case.py 2>&1 | tail -1 | tee $O/${T}_pb_$v.txt
+  timeout 300 python tools/profile_case.py 30 0 2>&1 | head -1 | tee $O/${T}_profile_$v.txt
 done
-cp build/ab/new.so avrecode_b200/libavrecode_b200.so
-timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -3 | tee $O/${T}_pytest.txt
+cp build/ab/_keep.so avrecode_b200/libavrecode_b200.so
