@@ -123,8 +123,8 @@ struct avr_ctx {
   uint64_t out_total[2] = {0, 0};
   size_t in_bytes = 0;
   uint32_t max_mbw = 1, max_frame_bytes = 0;
-  int grid = 0;
-  bool resident = true;
+  int grid[2] = {0, 0};                   // per direction (0 compress, 1 decompress)
+  bool resident[2] = {true, true};
   int force_resident = -1;   // avr_config.resident / AVR_RESIDENT env: 0 / 1, -1 = per batch
   int wide_stream_bytes = 32768;   // avr_config.wide_stream_bytes / AVR_WIDE_STREAM_BYTES env
   int wide_batch_limit = -1;       // avr_config.wide_batch_limit (-1: 4 x SMs, 0: none)
@@ -366,29 +366,42 @@ int avr_stage(avr_ctx* c, const avr_slice_desc* descs, int n, const uint8_t* in,
   int glb_per_sm = std::max(1, std::min(c->cfg_warps > 0 ? c->cfg_warps : 4, int(smem_sm / (smem_glb + 1024))));
   glb_per_sm = std::min(glb_per_sm, 4);
   if (smem_glb + 1024 > size_t(c->max_smem_optin)) return AVR_ERR_ARG;   // picture too wide for the neighbour row
-  // Measured (profiles/r2m_throughput_placement.txt, 3458 slices of 64 corpus clips): twice the blocks per SM buy
-  // nothing -- 1564 / 2521 ms (compress / decompress) resident against 1613 / 3078 ms split.  An SM issues about one
-  // instruction per cycle from these warps however many it holds (instruction fetch and branch resolution are a third
-  // of every warp's stall samples, profiles/r2m_ncu_throughput.txt), so the resident placement is taken whenever it
-  // fits; the split one is for pictures whose neighbour row leaves no room, or on request (avr_config.resident = 0).
-  bool resident = res_per_sm > 0;
-  if (c->force_resident == 0) resident = false;
-  if (c->force_resident == 1 && res_per_sm > 0) resident = true;
-  c->resident = resident;
-  c->grid = std::max(1, std::min(c->n_jobs, c->sm_count * (resident ? res_per_sm : glb_per_sm)));
-  if (uint32_t(c->grid) < max_roles) return AVR_ERR_ARG;   // (a device with fewer than 9 resident blocks: not a B200)
+  // Measured with every SM full (profiles/r2p_throughput_placement.txt, 1728 slices of 32 corpus clips; compress /
+  // decompress): resident 771 / 985 ms, split 825 / 871 ms.  Twice the blocks make a block 2.14x / 1.77x slower: a loss
+  // for compression (three warps per block), a 13 % gain for decompression (two) -- when the batch has the slices to
+  // fill them.  So per direction: the launch lasts max(total work / block slots, longest job) x the variant's cost per
+  // unit of work, and the cheaper one is taken; compression stays resident whenever that fits.  The split placement is
+  // also the one for pictures whose neighbour row leaves the estimators no room, and avr_config.resident forces either.
+  uint64_t total_w = 0, longest_w = 0;
+  for (const JobDesc& j : c->jobs) { total_w += j.weight; longest_w = std::max<uint64_t>(longest_w, j.weight); }
+  const bool fits = res_per_sm > 0;
+  for (int dir = 0; dir < 2; dir++) {
+    bool resident = fits;
+    if (fits && dir == 1 && c->wide.empty()) {
+      const double t_res = double(std::max<uint64_t>(total_w / uint64_t(res_per_sm * c->sm_count), longest_w));
+      const double t_spl = 1.77 * double(std::max<uint64_t>(total_w / uint64_t(glb_per_sm * c->sm_count), longest_w));
+      resident = t_res <= t_spl;
+    }
+    if (c->force_resident == 0) resident = false;
+    if (c->force_resident == 1 && fits) resident = true;
+    c->resident[dir] = resident;
+    c->grid[dir] = std::max(1, std::min(c->n_jobs, c->sm_count * (resident ? res_per_sm : glb_per_sm)));
+    if (uint32_t(c->grid[dir]) < max_roles) return AVR_ERR_ARG;   // (a device with fewer than 9 resident blocks: not a B200)
+  }
+  const bool all_resident = c->resident[0] && c->resident[1];
+  const int max_grid = std::max(c->grid[0], c->grid[1]);
 
   // device memory
   // the nnz planes are only needed by jobs whose model spans several slices (file mode)
   bool any_multi = false;
   for (const JobDesc& j : c->jobs) any_multi = any_multi || j.n_slices > 1;
   if (!any_multi) c->max_frame_bytes = 0;
-  const uint64_t work_stride = align_up((resident ? 0 : counters_bytes()) + 2 * size_t(c->max_frame_bytes) + 16, 256);
+  const uint64_t work_stride = align_up((all_resident ? 0 : counters_bytes()) + 2 * size_t(c->max_frame_bytes) + 16, 256);
   c->work_stride = work_stride;
   int rc;
   if ((rc = grow_dev(&c->d_in, &c->d_in_cap, size_t(in_bytes) + 64))) return rc;
   if ((rc = grow_dev(&c->d_out, &c->d_out_cap, size_t(std::max(c->out_total[0], c->out_total[1])) + 64))) return rc;
-  if ((rc = grow_dev(&c->d_work, &c->d_work_cap, size_t(work_stride) * c->grid + 256))) return rc;
+  if ((rc = grow_dev(&c->d_work, &c->d_work_cap, size_t(work_stride) * max_grid + 256))) return rc;
   if (c->grid_wide && (rc = grow_dev(&c->d_wide, &c->d_wide_cap, size_t(c->wide_stride) * c->grid_wide + 256))) return rc;
   c->off_descs = 0;
   c->off_ios = align_up(c->off_descs + sizeof(avr_slice_desc) * n, 256);
@@ -436,7 +449,7 @@ int avr_launch(avr_ctx* c, int direction) {
   k.work_stride = c->work_stride;
   k.nnz_frame_bytes = c->max_frame_bytes;
   k.max_mbw = c->max_mbw;
-  const size_t smem = smem_bytes(c->max_mbw, c->resident);
+  const size_t smem = smem_bytes(c->max_mbw, c->resident[direction]);
   if (int(smem) > c->max_smem_optin) return AVR_ERR_ARG;
   CK(cudaMemsetAsync(k.counter, 0, 2 * sizeof(uint32_t), c->stream));
   k.wide_ws = c->d_wide;
@@ -450,7 +463,7 @@ int avr_launch(avr_ctx* c, int direction) {
     CK(cudaMemset2DAsync(c->d_wide, size_t(c->wide_stride), 0, wide_ctl_bytes() + wide_rows_bytes(c->max_mbw_wide), size_t(c->grid_wide), c->stream));
   cudaLaunchConfig_t lc;
   memset(&lc, 0, sizeof lc);
-  lc.gridDim = dim3(unsigned(c->grid)); lc.blockDim = dim3(direction == 0 ? AVR_THREADS_OF(Compress) : AVR_THREADS_OF(Decompress)); lc.dynamicSmemBytes = smem; lc.stream = c->stream;
+  lc.gridDim = dim3(unsigned(c->grid[direction])); lc.blockDim = dim3(direction == 0 ? AVR_THREADS_OF(Compress) : AVR_THREADS_OF(Decompress)); lc.dynamicSmemBytes = smem; lc.stream = c->stream;
   lc.attrs = nullptr; lc.numAttrs = 0;
   CK(cudaEventRecord(c->ev0, c->stream));
 #define AVR_LAUNCH(DIR, RES)                                                                                              \
@@ -459,8 +472,8 @@ int avr_launch(avr_ctx* c, int direction) {
     CK(cudaLaunchKernelEx(&lc, avr_job_kernel<DIR, RES>, k));                                                             \
   } while (0)
   if (c->n_jobs > 0) {
-    if (direction == 0) { if (c->resident) AVR_LAUNCH(Compress, true); else AVR_LAUNCH(Compress, false); }
-    else { if (c->resident) AVR_LAUNCH(Decompress, true); else AVR_LAUNCH(Decompress, false); }
+    if (direction == 0) { if (c->resident[0]) AVR_LAUNCH(Compress, true); else AVR_LAUNCH(Compress, false); }
+    else { if (c->resident[1]) AVR_LAUNCH(Decompress, true); else AVR_LAUNCH(Decompress, false); }
     c->launches++;
   }
 #undef AVR_LAUNCH

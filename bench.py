@@ -449,6 +449,41 @@ class Gpu:
         assert back == data
         return s, len(rec)
 
+    def file_mode(self, data):
+        """Throughput of the reference's own container format, end to end through the file calls with host buffers: a
+        file is ONE job (its slices share one model), so one file runs on one thread block and a set of files on as
+        many.  (a) one file: cfg1; (b) the headline file as its closed-GOP segments -- the very files the reference arm
+        times on the host cores -- in one avr_files_compress(AVR_MODE_FILE) call."""
+        A, cc = self.A, self.cc
+        out = {"unit": UNIT, "api": "avr_file[s]_compress(AVR_MODE_FILE) + avr_file[s]_decompress, host buffers, wall clock",
+               "note": "byte-identical to the reference compressor's containers (tests/golden, bench_gate ref_rec_bytes); "
+                       "parallelism = number of files"}
+        one, _ = gen_workload("cfg1", 0)
+        rec = cc.file_compress(one, A.MODE_FILE)                      # warm-up + check
+        if cc.file_decompress(rec) != one:
+            raise SystemExit("bench.py: file-mode round trip is not the identity")
+        pin = self.gate.get("cfg1") or {}
+        t0 = time.perf_counter()
+        rec = cc.file_compress(one, A.MODE_FILE)
+        back = cc.file_decompress(rec)
+        s1 = time.perf_counter() - t0
+        assert back == one
+        out["one_file"] = {"workload": DESCR["cfg1"], "value": len(one) / s1 / 1e6, "bytes_saved_frac": 1.0 - len(rec) / len(one),
+                           "container_bytes_equal_reference": (len(rec) == pin["ref_rec_bytes"]) if pin.get("ref_rec_bytes") else None}
+        segs = gop_segments(data, A.index_h264(data))
+        recs = cc.files_compress(segs, A.MODE_FILE)
+        if cc.files_decompress(recs) != segs:
+            raise SystemExit("bench.py: file-mode segment round trip is not the identity")
+        t0 = time.perf_counter()
+        recs = cc.files_compress(segs, A.MODE_FILE)
+        back = cc.files_decompress(recs)
+        s2 = time.perf_counter() - t0
+        assert back == segs
+        total = sum(len(x) for x in segs)
+        out["segments"] = {"workload": "the headline file as %d closed-GOP segment files (what the reference arm times)" % len(segs),
+                           "files": len(segs), "value": total / s2 / 1e6, "bytes_saved_frac": 1.0 - sum(len(r) for r in recs) / total}
+        return out
+
     def per_config(self, name, steps=2, warmup=1, f_hz=0.0, inst_per_bin=None):
         data, _ = gen_workload(name, 0)
         p = self.prepare(name, data)
@@ -466,6 +501,7 @@ class Gpu:
                 "bit_exact": True, "parity_gate": p["gate"], "bytes_saved_frac": saved, "bytes_saved_frac_reference": ref_saved,
                 "bytes_saved_frac_no_priors": (1.0 - rec_plain / len(data)) if rec_plain else None,
                 "delta_saved_vs_ref": (saved - ref_saved) if ref_saved is not None else None,
+                "saved_frac_of_reference": (saved / ref_saved) if ref_saved else None,
                 "slices": len(p["descs"]), "wide_slices": p["n_wide"], "longest_slice_bins": int(p["longest"]),
                 "cycles_per_bin_longest": (dom_ms * 1e-3 * f_hz / p["longest"]) if f_hz else None,
                 "issue_frac": (bins_s / issue_peak) if issue_peak else None, "steps": steps}
@@ -631,6 +667,15 @@ def run_ours(args):
             except BaseException as e:   # a secondary figure must never sink the headline
                 per_config[name] = {"error": str(e)}
 
+    # ---- the reference's own format (AVR_MODE_FILE: one model per file = one serial job per file), N = 1 only ----
+    file_mode = None
+    if world == 1 and os.environ.get("AVR_BENCH_FILE_MODE", "1") != "0":
+        try:
+            file_mode = g.file_mode(data)
+            extra_launches += 8
+        except BaseException as e:
+            file_mode = {"error": str(e)}
+
     if rank != 0:
         return 0
     peak, peak_src = load_peaks()
@@ -702,6 +747,8 @@ def run_ours(args):
                             "tools/train_priors.py on h264gen streams of OTHER seeds: synthetic like this workload, so on real video expect "
                             "less); _no_priors: the same without the table; _reference: one model per file, the reference's format" if g.priors else None,
         "delta_saved_vs_ref": (saved - ref_saved) if ref_saved is not None else None,
+        "saved_frac_of_reference": (saved / ref_saved) if ref_saved else None,
+        "saved_frac_of_reference_no_priors": (saved_plain / ref_saved) if (ref_saved and saved_plain is not None) else None,
         "bit_exact": True, "parity_gate": p["gate"], "wall_ms_per_step": wall_ms,
         "gpu_launches": int(launches), "gpu_launches_other_sections": int(extra_launches),
         "e2e": {"value": total_bytes / e2e_s / 1e6, "unit": UNIT, "h2d_bytes_per_step": len(data) + p["coded"] + 80 * len(p["descs"]),
@@ -719,6 +766,8 @@ def run_ours(args):
         line["corpus"] = corpus
     if per_config is not None:
         line["per_config"] = per_config
+    if file_mode is not None:
+        line["file_mode"] = file_mode
     if world == 1:
         try:
             m = cpu_reference_measure(args.workload, steps=2)
