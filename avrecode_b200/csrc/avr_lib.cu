@@ -369,18 +369,20 @@ int avr_stage(avr_ctx* c, const avr_slice_desc* descs, int n, const uint8_t* in,
   // Measured with every SM full (profiles/r2p_throughput_placement.txt, 1728 slices of 32 corpus clips; compress /
   // decompress): resident 771 / 985 ms, split 825 / 871 ms.  Twice the blocks make a block 2.14x / 1.77x slower: a loss
   // for compression (three warps per block), a 13 % gain for decompression (two) -- when the batch has the slices to
-  // fill them.  So per direction: the launch lasts max(total work / block slots, longest job) x the variant's cost per
-  // unit of work, and the cheaper one is taken; compression stays resident whenever that fits.  The split placement is
-  // also the one for pictures whose neighbour row leaves the estimators no room, and avr_config.resident forces either.
+  // fill them for the whole launch.  So per direction: compression stays resident whenever that fits, decompression goes
+  // split when the batch is throughput-bound.  (The factors are averages over a launch with full SMs: the longest jobs
+  // start first and finish among fewer and fewer neighbours, so "1.77 x the longest job" overestimates the split launch.)
+  // The split placement is also the one for pictures whose neighbour row leaves the estimators no room, and
+  // avr_config.resident forces either.
   uint64_t total_w = 0, longest_w = 0;
   for (const JobDesc& j : c->jobs) { total_w += j.weight; longest_w = std::max<uint64_t>(longest_w, j.weight); }
   const bool fits = res_per_sm > 0;
   for (int dir = 0; dir < 2; dir++) {
     bool resident = fits;
     if (fits && dir == 1 && c->wide.empty()) {
-      const double t_res = double(std::max<uint64_t>(total_w / uint64_t(res_per_sm * c->sm_count), longest_w));
-      const double t_spl = 1.77 * double(std::max<uint64_t>(total_w / uint64_t(glb_per_sm * c->sm_count), longest_w));
-      resident = t_res <= t_spl;
+      // throughput-bound with 2 blocks per SM (the slots stay full for longer than the longest job lasts)?  Then 4 slower
+      // blocks per SM finish sooner; a latency-bound batch -- a file with a few long slices -- stays resident
+      resident = total_w / uint64_t(res_per_sm * c->sm_count) < longest_w;
     }
     if (c->force_resident == 0) resident = false;
     if (c->force_resident == 1 && fits) resident = true;

@@ -700,14 +700,18 @@ def run_ours(args):
         # the serial stage of the dominant direction: the CABAC decoder + walk (compress) or the CABAC re-encoder (decompress)
         floor = None
         if isinstance(floors, dict) and "error" not in floors:
-            key = [k for k in floors if ("compress significance loop" in k if dom == "compress" else "decompress significance loop" in k)]
+            # the serial stage that bounds the longest slice: the parser's inner loop; for a wide slice being decompressed
+            # (K parsers share the slice) the one warp that re-encodes the CABAC stream
+            want = "compress significance loop" if dom == "compress" else ("decompress coder warp" if p["n_wide"] else "decompress significance loop")
+            key = [k for k in floors if want in k]
             floor = floors[key[0]] if key else None
         bounds = {
             "latency": {"longest_slice_bins": int(p["longest"]), "mean_slice_bins": bins / max(1, len(p["descs"])),
                         "cycles_per_bin_on_longest_slice": cpb, "floor_cycles_per_bin": floor,
                         "frac_of_floor": (floor / cpb) if (floor and cpb) else None,
                         "floor_note": "avr_probe on this device: one lane looping the serial primitive of the dominant direction "
-                                      "(the parser warp's inner loop -- compress: CABAC decode of a significance map; decompress: range decode of one)",
+                                      "(compress: the parser's CABAC decode of a significance map; decompress: the parser's range decode of one, or -- when the "
+                                      "longest slices are wide, K parsers each -- the CABAC re-encoder warp over a ring of entries)",
                         "note": "a launch lasts as long as its longest slice; cycles/bin = kernel time x SM clock / its bins"},
             "issue": {"achieved_bins_per_s": bins_s_dom, "peak_bins_per_s": issue_peak,
                       "frac": (bins_s_dom / issue_peak) if issue_peak else None,
@@ -722,7 +726,8 @@ def run_ours(args):
             "workload": DESCR[args.workload], "value": len(data) / (ms_c + ms_d) / 1e3, "e2e": len(data) / e2e_s / 1e6, "unit": UNIT,
             "compress_MBps": len(data) / ms_c / 1e3, "decompress_MBps": len(data) / ms_d / 1e3, "bit_exact": True, "parity_gate": p["gate"],
             "bytes_saved_frac": saved, "bytes_saved_frac_reference": ref_saved, "bytes_saved_frac_no_priors": saved_plain,
-            "delta_saved_vs_ref": (saved - ref_saved) if ref_saved is not None else None, "slices": len(p["descs"]),
+            "delta_saved_vs_ref": (saved - ref_saved) if ref_saved is not None else None,
+            "saved_frac_of_reference": (saved / ref_saved) if ref_saved else None, "slices": len(p["descs"]),
             "wide_slices": p["n_wide"], "longest_slice_bins": int(p["longest"]),
             "cycles_per_bin_longest": bounds.get("latency", {}).get("cycles_per_bin_on_longest_slice"),
             "issue_frac": bounds.get("issue", {}).get("frac"), "steps": steps}
