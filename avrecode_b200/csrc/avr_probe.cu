@@ -324,7 +324,9 @@ int avr_probe(int device, int which, uint32_t iters, uint64_t* cycles, uint64_t*
   if (device < 0 || device >= ndev || cudaSetDevice(device) != cudaSuccess) return AVR_ERR_ARG;
   uint64_t* d = nullptr;
   if (cudaMalloc(reinterpret_cast<void**>(&d), 3 * sizeof(uint64_t)) != cudaSuccess) return AVR_ERR_NOMEM;
-  ProbeArgs a; a.iters = iters; a.result = d;
+  ProbeArgs a; a.result = d;
+  // the warp-wide probes work through a whole ring (~1500 bins) per iteration, the single-lane ones through one bin
+  a.iters = (which == 5 || which == 6 || which == 8) ? iters / 64 + 1 : iters;
   for (int rep = 0; rep < 2; rep++) {   // the first run also loads the kernel
     switch (which) {
       case 0: avr_probe_kernel<0><<<1, 32>>>(a); break;
