@@ -385,6 +385,10 @@ class Gpu:
         res, blob = cc.collect()
         if not all(r.status == 0 for r in res):
             raise SystemExit("bench.py: compress failed on %d slices of %s" % (sum(1 for r in res if r.status), name))
+        try:   # per-class bin counts of the launch (the reference's per-CodingType bills, recode.cpp:635-655, as counts)
+            hist = [sum(h[k] for h in cc.collect_hist()) for k in range(8)]
+        except Exception:
+            hist = None
         dd = H.coded_descs(descs, res)
         cd.stage(dd, blob)
         cd.launch(1); cd.sync()
@@ -404,7 +408,7 @@ class Gpu:
             cc.stage(descs, arena)
         if not ok:
             raise SystemExit("bench.py: parity check failed on %s -- refusing to time a wrong kernel" % name)
-        return dict(descs=descs, res=res, gate=gate, payload=sum(d.payload_size for d in descs), coded=sum(r.out_size for r in res),
+        return dict(descs=descs, res=res, gate=gate, hist=hist, payload=sum(d.payload_size for d in descs), coded=sum(r.out_size for r in res),
                     bins=sum(r.n_bins for r in res), longest=max(r.n_bins for r in res), n_wide=sum(1 for d in descs if (d.n_streams & 15) >= 2),
                     k_wide=max([d.n_streams & 15 for d in descs] + [0]), nbytes=len(arena))
 
@@ -754,6 +758,8 @@ def run_ours(args):
         "delta_saved_vs_ref": (saved - ref_saved) if ref_saved is not None else None,
         "saved_frac_of_reference": (saved / ref_saved) if ref_saved else None,
         "saved_frac_of_reference_no_priors": (saved_plain / ref_saved) if (ref_saved and saved_plain is not None) else None,
+        "bin_classes": (dict(zip(("mb", "cbf", "sig", "level", "bypass", "nnz_side_channel", "pred_mode", "terminate"),
+                                 [h / max(1, p["bins"]) for h in p["hist"]])) if p.get("hist") else None),
         "bit_exact": True, "parity_gate": p["gate"], "wall_ms_per_step": wall_ms,
         "gpu_launches": int(launches), "gpu_launches_other_sections": int(extra_launches),
         "e2e": {"value": total_bytes / e2e_s / 1e6, "unit": UNIT, "h2d_bytes_per_step": len(data) + p["coded"] + 80 * len(p["descs"]),
