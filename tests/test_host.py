@@ -413,3 +413,60 @@ def test_priors_in_the_container(built, emu_multi):
     finally:
         lib.avr_multi_set_priors(emu_multi, None, 0)
         lib.avr_destroy(plain); lib.avr_destroy(primed)
+
+
+# ---- damaged inputs: refused or lossless, never a crash (file layer on the host emulation) ----
+def _mutate(rng, b):
+    d = bytearray(b)
+    for _ in range(rng.randint(1, 4)):
+        if len(d) < 2:
+            break
+        op = rng.randint(0, 3)
+        if op == 0:
+            d[rng.randrange(len(d))] ^= 1 << rng.randrange(8)
+        elif op == 1 and len(d) > 8:
+            i = rng.randrange(len(d))
+            del d[i:i + rng.randint(1, 8)]
+        elif op == 2:
+            i = rng.randrange(len(d) + 1)
+            d[i:i] = bytes(rng.randrange(256) for _ in range(rng.randint(1, 4)))
+        else:
+            d = d[:rng.randrange(len(d) + 1)]
+    return bytes(d)
+
+
+def test_damaged_streams_are_refused_or_recoded_losslessly(emu_ctx):
+    """Any byte string is a legal input of `recode compress` (what cannot be parsed stays literal): a mutated stream
+    either is refused with an error code or round-trips to exactly the mutated bytes, in both container modes."""
+    import random
+    lib = H.emu_file_lib()
+    rng = random.Random(11)
+    srcs = [load_case(n)[0] for n in ("main_ip_4slices", "main_ip_mp4", "rich_headers_b", "tiny_1mb_rows")]
+    for it in range(24):
+        d = _mutate(rng, rng.choice(srcs))
+        mode = (A.MODE_FILE, A.MODE_SLICE)[it & 1]
+        rc, rec = H.emu_files_call(lib.avr_files_compress, emu_ctx, [d], mode)
+        if rc != 0:
+            continue
+        rc, back = H.emu_files_call(lib.avr_files_decompress, emu_ctx, rec)
+        assert rc == 0 and back == [d], "mutation %d is not lossless" % it
+
+
+def test_damaged_containers_are_refused_not_crashed_on(emu_ctx):
+    """A damaged container decodes to an error or to some byte string -- the coded payloads carry their own check (the
+    rebuilt slice must have the recorded size) -- but never takes the process down or hangs."""
+    import random
+    lib = H.emu_file_lib()
+    rng = random.Random(5)
+    data = load_case("main_ip_4slices")[0]
+    recs = []
+    for mode in (A.MODE_FILE, A.MODE_SLICE):
+        rc, r = H.emu_files_call(lib.avr_files_compress, emu_ctx, [data], mode)
+        assert rc == 0
+        recs.append(r[0])
+    errors = 0
+    for it in range(120):
+        rc, out = H.emu_files_call(lib.avr_files_decompress, emu_ctx, [_mutate(rng, recs[it & 1])])
+        errors += rc != 0
+        assert rc != 0 or len(out) == 1
+    assert errors > 60
