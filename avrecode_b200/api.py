@@ -98,8 +98,10 @@ def _string_at(ptr, n):
 
 def _buf(data):
     """-> (address, length, keepalive) for bytes / bytearray / numpy / torch (CPU) buffers."""
-    if isinstance(data, (bytes, bytearray)):
-        arr = (C.c_uint8 * len(data)).from_buffer_copy(data) if isinstance(data, bytes) else (C.c_uint8 * len(data)).from_buffer(data)
+    if isinstance(data, bytes):      # the bytes object's own storage: no copy (the library only reads its inputs)
+        return C.cast(C.c_char_p(data), C.c_void_p).value or 0, len(data), data
+    if isinstance(data, bytearray):
+        arr = (C.c_uint8 * len(data)).from_buffer(data)
         return C.addressof(arr), len(data), arr
     if hasattr(data, "data_ptr"):  # torch tensor (pinned host memory for the e2e path)
         return data.data_ptr(), data.numel() * data.element_size(), data

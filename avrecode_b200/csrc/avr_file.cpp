@@ -10,6 +10,9 @@
 #include <stdlib.h>
 #include <string.h>
 #include <algorithm>
+#include <atomic>
+#include <chrono>
+#include <stdio.h>
 #include <string>
 #include <thread>
 #include <new>
@@ -17,6 +20,18 @@
 #include "../../include/avrecode_b200.h"
 
 namespace {
+
+// AVR_FILE_TIMING=1: where a file call spends its time, to stderr (debugging aid)
+struct Stopwatch {
+  bool on = getenv("AVR_FILE_TIMING") != nullptr;
+  std::chrono::steady_clock::time_point t = std::chrono::steady_clock::now();
+  void lap(const char* what) {
+    if (!on) return;
+    const auto now = std::chrono::steady_clock::now();
+    fprintf(stderr, "avr_file: %-28s %8.1f ms\n", what, std::chrono::duration<double, std::milli>(now - t).count());
+    t = now;
+  }
+};
 
 const char kSliceModeTag[] = "avr-b200/slice";
 
@@ -165,6 +180,28 @@ void emit_block(std::string& out, const std::string& body) {
   out.append(body);
 }
 
+// a byte vector whose resize() does not zero-fill (gigabytes of arena are overwritten right away)
+template <class T>
+struct no_init_alloc : std::allocator<T> {
+  template <class U> struct rebind { typedef no_init_alloc<U> other; };
+  template <class U> void construct(U* p) { ::new (static_cast<void*>(p)) U; }
+  template <class U, class A0, class... A> void construct(U* p, A0&& a0, A&&... a) { ::new (static_cast<void*>(p)) U(std::forward<A0>(a0), std::forward<A>(a)...); }
+};
+typedef std::vector<uint8_t, no_init_alloc<uint8_t>> RawBytes;
+
+// Files of a call are independent on the host side too: index, container parse and assembly run one task per file.
+template <class F>
+void parallel_for(int n, F f) {
+  const unsigned hw = std::thread::hardware_concurrency();
+  const int workers = std::min(n, int(std::min(hw ? hw : 1u, 16u)));
+  if (workers <= 1) { for (int i = 0; i < n; i++) f(i); return; }
+  std::atomic<int> next(0);
+  std::vector<std::thread> threads;
+  for (int t = 0; t < workers; t++)
+    threads.emplace_back([&]() { for (int i = next++; i < n; i = next++) f(i); });
+  for (std::thread& t : threads) t.join();
+}
+
 // The devices a file call runs on: one context (avr_file_* / avr_files_*) or the contexts of an avr_multi.
 struct DevSet { avr_ctx* const* ctx; int n; };
 
@@ -276,28 +313,35 @@ static int compress_many(const DevSet& ds, const uint8_t* const* files, const ui
   std::vector<Plan> plans;
   plans.resize(size_t(n_files));
   auto cleanup = [&]() { for (Plan& p : plans) free(p.ents); };
+  Stopwatch sw;
   // one contiguous arena (a single file is used in place)
-  std::vector<uint8_t> arena_store;
+  RawBytes arena_store;
   const uint8_t* arena = n_files == 1 ? files[0] : nullptr;
   uint64_t arena_bytes = n_files == 1 ? sizes[0] : 0;
   if (n_files != 1) {
     uint64_t total = 0;
     for (int f = 0; f < n_files; f++) { plans[f].base = total; total += (sizes[f] + 15) & ~uint64_t(15); }
     arena_store.resize(size_t(total) + 16);
-    for (int f = 0; f < n_files; f++) memcpy(arena_store.data() + plans[f].base, files[f], size_t(sizes[f]));
+    memset(arena_store.data() + total, 0, 16);
     arena = arena_store.data(); arena_bytes = total;
   }
-  for (int f = 0; f < n_files; f++) {
+  std::vector<int> rcs(size_t(n_files), AVR_OK);
+  parallel_for(n_files, [&](int f) {   // one task per file: its copy into the arena and its slice index
     Plan& p = plans[f];
-    int rc = avr_index_h264(files[f], sizes[f], &p.ents, &p.n_ents);
-    if (rc) { cleanup(); return rc; }
+    if (n_files != 1) {
+      memcpy(arena_store.data() + p.base, files[f], size_t(sizes[f]));
+      memset(arena_store.data() + p.base + sizes[f], 0, size_t(((sizes[f] + 15) & ~uint64_t(15)) - sizes[f]));   // the pad up to the next file
+    }
+    rcs[f] = avr_index_h264(files[f], sizes[f], &p.ents, &p.n_ents);
+    if (rcs[f]) return;
     p.coded.assign(size_t(p.n_ents), 0);
     p.raw_off.assign(size_t(p.n_ents), 0);
     p.raw_size.assign(size_t(p.n_ents), 0);
     // slices the device would only hand back as unsupported stay literals from the start (in file mode every failed
     // attempt costs a whole pass: the slices of a file share one model)
     for (int i = 0; i < p.n_ents; i++) p.coded[i] = (p.ents[i].recodable && !statically_unsupported(p.ents[i].desc)) ? 1 : 0;
-  }
+  });
+  for (int f = 0; f < n_files; f++) if (rcs[f]) { cleanup(); return rcs[f]; }
   // Chunked mode recodes slices whose payload contains emulation-prevention bytes too (the reference leaves
   // them as literals): the device gets an unescaped copy, appended to the arena, and puts the bytes back when
   // it decompresses.  Only if escaping the copy gives the file's bytes again.
@@ -325,16 +369,19 @@ static int compress_many(const DevSet& ds, const uint8_t* const* files, const ui
         arena_store.reserve(size_t(total) + raws.size() + 16);
         arena_store.insert(arena_store.end(), files[0], files[0] + sizes[0]);
         arena_store.resize(size_t(total));
+        memset(arena_store.data() + sizes[0], 0, size_t(total - sizes[0]));
       } else {
         total = arena_bytes;
         arena_store.resize(size_t(total));
       }
       arena_store.insert(arena_store.end(), raws.begin(), raws.end());
       arena_store.resize(arena_store.size() + 16);
+      memset(arena_store.data() + arena_store.size() - 16, 0, 16);
       for (Plan& p : plans) for (int i = 0; i < p.n_ents; i++) if (p.coded[i] == 2) p.raw_off[i] += total;
       arena = arena_store.data(); arena_bytes = total + raws.size();
     }
   }
+  sw.lap("compress: arena + index");
   size_t n_batch = 0;
   for (const Plan& p : plans) for (int i = 0; i < p.n_ents; i++) n_batch += p.coded[i] ? 1 : 0;
   const uint32_t per_stream = mode == AVR_MODE_SLICE ? wide_stream_bytes(ctx, n_batch) : 0;
@@ -385,8 +432,8 @@ static int compress_many(const DevSet& ds, const uint8_t* const* files, const ui
     }
     if (!retry) break;
   }
-  int rc_all = AVR_OK;
-  for (int f = 0; f < n_files; f++) {
+  sw.lap("compress: device batch");
+  parallel_for(n_files, [&](int f) {   // one task per file: its container
     const Plan& p = plans[f];
     const uint8_t* file = files[f];
     std::string o;
@@ -426,10 +473,12 @@ static int compress_many(const DevSet& ds, const uint8_t* const* files, const ui
     std::string lit;
     put_len(lit, 2, file + prev, size_t(sizes[f] - prev));
     emit_block(o, lit);
-    int rc = to_malloc(o, &recs[f], &rec_sizes[f]);
-    if (rc) rc_all = rc;
-  }
+    rcs[f] = to_malloc(o, &recs[f], &rec_sizes[f]);
+  });
+  sw.lap("compress: containers");
   cleanup();
+  int rc_all = AVR_OK;
+  for (int f = 0; f < n_files; f++) if (rcs[f]) rc_all = rcs[f];
   return rc_all;
 }
 
@@ -461,102 +510,121 @@ static int decompress_many(const DevSet& ds, const uint8_t* const* recs, const u
     std::vector<CodedRef> coded;
     std::vector<size_t> which;        // batch position (relative to first) -> coded index
     size_t first = 0, count = 0;
+    std::vector<avr_slice_desc> descs; // this file's share of the batch, in_off relative to its own coded bytes
+    uint64_t in_bytes = 0, in_base = 0;
+    int rc = AVR_OK;
   };
   std::vector<Plan> plans;
   plans.resize(size_t(n_files));
   std::vector<avr_slice_desc> descs;
+  Stopwatch sw;
   std::string in;   // all Block.cabac bytes back to back
-  for (int f = 0; f < n_files; f++) {
+  // Phase A, one task per container (files are independent): parse, rebuild the stream with surrogate payloads, index it,
+  // pair the entries with the coded blocks.  Descriptors carry offsets into the file's own run of coded bytes.
+  parallel_for(n_files, [&](int f) {
     Plan& p = plans[f];
-    std::string version;
-    uint64_t priors = 0;
-    if (!parse_container(recs[f], size_t(rec_sizes[f]), &p.blocks, &version, &priors)) return AVR_ERR_FORMAT;
-    const bool slice_mode = version == kSliceModeTag;
-    if (!version.empty() && !slice_mode) return AVR_ERR_FORMAT;
-    if (priors) {   // written from a prior table: every device must hold that very table
-      if (!slice_mode) return AVR_ERR_FORMAT;
-      for (int k = 0; k < ds.n; k++) if (avr_priors_digest(ds.ctx[k]) != priors) return AVR_ERR_PRIORS;
-    }
-    p.stream.reserve(size_t(rec_sizes[f]) + size_t(rec_sizes[f]) / 8 + 4096);
-    in.reserve(in.size() + size_t(rec_sizes[f]));
-    // 1. rebuild the stream with surrogate payloads (recode.cpp:1359-1409, 1537-1544) so the slice
-    //    headers can be indexed exactly as on the compress side
-    for (size_t i = 0; i < p.blocks.size(); i++) {
-      const Block& b = p.blocks[i];
-      if (int(b.has_literal) + int(b.has_cabac) + int(b.has_skip) != 1) return AVR_ERR_FORMAT;   // recode.cpp:1364-1366
-      if (b.has_literal) p.stream.append(reinterpret_cast<const char*>(b.literal), b.literal_n);
-      else if (b.has_cabac) {
-        // :1377-1379, 1538-1540; and no honest block is 4096x its coded size (an estimator never goes below 1/97:
-        // a bin costs > 0.01 bit), so a few bytes of container cannot demand gigabytes of output
-        if (!b.has_size || b.size < 8 || b.size > (int64_t(1) << 31) || uint64_t(b.size) > (uint64_t(b.cabac_n) + 16) * 4096) return AVR_ERR_FORMAT;
-        p.coded.push_back(CodedRef{i, p.stream.size(), true});
-        p.stream.append(size_t(b.size), 'X');
-      } else {
-        if (!b.has_size) return AVR_ERR_FORMAT;
-        p.coded.push_back(CodedRef{i, 0, false});
+    p.rc = [&]() -> int {
+      std::string version;
+      uint64_t priors = 0;
+      if (!parse_container(recs[f], size_t(rec_sizes[f]), &p.blocks, &version, &priors)) return AVR_ERR_FORMAT;
+      const bool slice_mode = version == kSliceModeTag;
+      if (!version.empty() && !slice_mode) return AVR_ERR_FORMAT;
+      if (priors) {   // written from a prior table: every device must hold that very table
+        if (!slice_mode) return AVR_ERR_FORMAT;
+        for (int k = 0; k < ds.n; k++) if (avr_priors_digest(ds.ctx[k]) != priors) return AVR_ERR_PRIORS;
       }
-    }
-    avr_index_entry* ents = nullptr;
-    int n_ents = 0;
-    int rc = avr_index_h264(reinterpret_cast<const uint8_t*>(p.stream.data()), p.stream.size(), &ents, &n_ents);
-    if (rc) return rc;
-    // 2. pair index entries with coded blocks in order (recognize_coded_block, recode.cpp:1546-1573)
-    if (size_t(n_ents) != p.coded.size()) { free(ents); return AVR_ERR_FORMAT; }
-    p.first = descs.size();
-    for (int i = 0; i < n_ents; i++) {
-      const Block& b = p.blocks[p.coded[i].block];
-      if (uint64_t(b.size) != ents[i].desc.payload_size) { free(ents); return AVR_ERR_FORMAT; }   // "Invalid surrogate block size"
-      if (!p.coded[i].is_cabac && slice_mode) continue;
-      if (p.coded[i].is_cabac && ents[i].desc.in_off != p.coded[i].off) { free(ents); return AVR_ERR_FORMAT; }
-      avr_slice_desc d = ents[i].desc;
-      d.in_off = in.size();
-      d.in_size = p.coded[i].is_cabac ? uint32_t(b.cabac_n) : 0;
-      if (!p.coded[i].is_cabac) d.flags |= AVR_SLICE_SKIP;
-      if (p.which.empty() || slice_mode) d.flags |= AVR_SLICE_NEW_MODEL;
-      if (b.streams) {
-        if (!slice_mode || !p.coded[i].is_cabac || b.streams < 2 || b.streams > AVR_MAX_STREAMS) { free(ents); return AVR_ERR_FORMAT; }
-        d.n_streams = uint8_t((d.n_streams & ~AVR_STREAMS_MASK) | b.streams);
+      p.stream.reserve(size_t(rec_sizes[f]) + size_t(rec_sizes[f]) / 8 + 4096);
+      // 1. rebuild the stream with surrogate payloads (recode.cpp:1359-1409, 1537-1544) so the slice
+      //    headers can be indexed exactly as on the compress side
+      for (size_t i = 0; i < p.blocks.size(); i++) {
+        const Block& b = p.blocks[i];
+        if (int(b.has_literal) + int(b.has_cabac) + int(b.has_skip) != 1) return AVR_ERR_FORMAT;   // recode.cpp:1364-1366
+        if (b.has_literal) p.stream.append(reinterpret_cast<const char*>(b.literal), b.literal_n);
+        else if (b.has_cabac) {
+          // :1377-1379, 1538-1540; and no honest block is 4096x its coded size (an estimator never goes below 1/97:
+          // a bin costs > 0.01 bit), so a few bytes of container cannot demand gigabytes of output
+          if (!b.has_size || b.size < 8 || b.size > (int64_t(1) << 31) || uint64_t(b.size) > (uint64_t(b.cabac_n) + 16) * 4096) return AVR_ERR_FORMAT;
+          p.coded.push_back(CodedRef{i, p.stream.size(), true});
+          p.stream.append(size_t(b.size), 'X');
+        } else {
+          if (!b.has_size) return AVR_ERR_FORMAT;
+          p.coded.push_back(CodedRef{i, 0, false});
+        }
       }
-      if (b.escaped) {
-        if (!slice_mode || !p.coded[i].is_cabac) { free(ents); return AVR_ERR_FORMAT; }
-        d.n_streams |= AVR_SLICE_ESCAPED;
+      avr_index_entry* ents = nullptr;
+      int n_ents = 0;
+      int rc = avr_index_h264(reinterpret_cast<const uint8_t*>(p.stream.data()), p.stream.size(), &ents, &n_ents);
+      if (rc) return rc;
+      struct Free { avr_index_entry* e; ~Free() { free(e); } } guard{ents};
+      // 2. pair index entries with coded blocks in order (recognize_coded_block, recode.cpp:1546-1573)
+      if (size_t(n_ents) != p.coded.size()) return AVR_ERR_FORMAT;
+      for (int i = 0; i < n_ents; i++) {
+        const Block& b = p.blocks[p.coded[i].block];
+        if (uint64_t(b.size) != ents[i].desc.payload_size) return AVR_ERR_FORMAT;   // "Invalid surrogate block size"
+        if (!p.coded[i].is_cabac && slice_mode) continue;
+        if (p.coded[i].is_cabac && ents[i].desc.in_off != p.coded[i].off) return AVR_ERR_FORMAT;
+        avr_slice_desc d = ents[i].desc;
+        d.in_off = p.in_bytes;
+        d.in_size = p.coded[i].is_cabac ? uint32_t(b.cabac_n) : 0;
+        if (!p.coded[i].is_cabac) d.flags |= AVR_SLICE_SKIP;
+        if (p.which.empty() || slice_mode) d.flags |= AVR_SLICE_NEW_MODEL;
+        if (b.streams) {
+          if (!slice_mode || !p.coded[i].is_cabac || b.streams < 2 || b.streams > AVR_MAX_STREAMS) return AVR_ERR_FORMAT;
+          d.n_streams = uint8_t((d.n_streams & ~AVR_STREAMS_MASK) | b.streams);
+        }
+        if (b.escaped) {
+          if (!slice_mode || !p.coded[i].is_cabac) return AVR_ERR_FORMAT;
+          d.n_streams |= AVR_SLICE_ESCAPED;
+        }
+        if (priors && p.coded[i].is_cabac) d.n_streams |= AVR_SLICE_PRIORS;
+        p.in_bytes += d.in_size;
+        p.descs.push_back(d);
+        p.which.push_back(size_t(i));
       }
-      if (priors && p.coded[i].is_cabac) d.n_streams |= AVR_SLICE_PRIORS;
-      if (p.coded[i].is_cabac) in.append(reinterpret_cast<const char*>(b.cabac), b.cabac_n);
-      descs.push_back(d);
-      p.which.push_back(size_t(i));
-    }
-    p.count = p.which.size();
-    free(ents);
-  }
+      p.count = p.which.size();
+      return AVR_OK;
+    }();
+  });
+  for (const Plan& p : plans) if (p.rc) return p.rc;
+  // Phase B: the batch -- every file's coded bytes back to back (copied in parallel), descriptors rebased
+  uint64_t in_total = 0;
+  for (Plan& p : plans) { p.in_base = in_total; in_total += p.in_bytes; p.first = descs.size(); for (avr_slice_desc d : p.descs) { d.in_off += p.in_base; descs.push_back(d); } }
+  in.resize(size_t(in_total));
+  parallel_for(n_files, [&](int f) {
+    const Plan& p = plans[f];
+    for (size_t k = 0; k < p.descs.size(); k++)
+      if (p.descs[k].in_size) memcpy(&in[size_t(p.in_base + p.descs[k].in_off)], p.blocks[p.coded[p.which[k]].block].cabac, p.descs[k].in_size);
+  });
+  sw.lap("decompress: parse + index");
   std::vector<avr_slice_result> res;
   std::vector<const uint8_t*> out_at;
   if (in.empty()) in.push_back(0);
   int rc = run_batch(ds, 1, descs, reinterpret_cast<const uint8_t*>(in.data()), in.size(), &res, &out_at);
   if (rc) return rc;
-  // 3. splice the rebuilt payloads in, with the x264 padding fix-up of recode.cpp:1345-1354
-  for (int f = 0; f < n_files; f++) {
+  sw.lap("decompress: device batch");
+  // 3. splice the rebuilt payloads in, with the x264 padding fix-up of recode.cpp:1345-1354, and hand the files over
+  std::vector<int> rcs(size_t(n_files), AVR_OK);
+  parallel_for(n_files, [&](int f) {
     Plan& p = plans[f];
     for (size_t k = 0; k < p.count; k++) {
       const avr_slice_result& r = res[p.first + k];
-      if (r.status != AVR_SLICE_OK) return AVR_ERR_FORMAT;   // "Not all blocks were decoded."
+      if (r.status != AVR_SLICE_OK) { rcs[f] = AVR_ERR_FORMAT; return; }   // "Not all blocks were decoded."
       if (descs[p.first + k].flags & AVR_SLICE_SKIP) continue;
       const CodedRef& cr = p.coded[p.which[k]];
       const Block& b = p.blocks[cr.block];
-      std::string bytes(reinterpret_cast<const char*>(out_at[p.first + k]), r.out_size);
-      if (b.has_parity && b.has_last && b.last_n > 0) {
-        if (int(b.parity) != int(bytes.size() & 1)) bytes.push_back(char(b.last[0]));
-        else if (!bytes.empty()) bytes[bytes.size() - 1] = char(b.last[0]);
-      }
-      if (bytes.size() != size_t(b.size)) return AVR_ERR_FORMAT;
-      memcpy(&p.stream[cr.off], bytes.data(), bytes.size());
+      size_t n = r.out_size;
+      const bool fix = b.has_parity && b.has_last && b.last_n > 0;
+      if (fix && int(b.parity) != int(n & 1)) n++;              // the byte x264 padded with comes back (recode.cpp:1347-1354)
+      if (n != size_t(b.size)) { rcs[f] = AVR_ERR_FORMAT; return; }
+      memcpy(&p.stream[cr.off], out_at[p.first + k], std::min<size_t>(n, r.out_size));
+      if (fix && n > 0) p.stream[cr.off + n - 1] = char(b.last[0]);
     }
-  }
+    rcs[f] = to_malloc(p.stream, &files[f], &file_sizes[f]);
+  });
+  sw.lap("decompress: splice + copy out");
   int rc_all = AVR_OK;
-  for (int f = 0; f < n_files; f++) {
-    int r2 = to_malloc(plans[f].stream, &files[f], &file_sizes[f]);
-    if (r2) rc_all = r2;
-  }
+  for (int f = 0; f < n_files; f++) if (rcs[f]) rc_all = rcs[f];
+  if (rc_all) return rc_all;
   return rc_all;
 }
 
