@@ -1231,6 +1231,11 @@ struct Compress {
   // ---- registers ----
   AVR_DEV void enter(const SharedTables&) { ByteWindow w; home_load(h, cabac, w); q.enter(h); }
   AVR_DEV void leave(const ResBins& bins) { home_store(h, cabac); q.leave(h); home_add_bins(h, bins); }
+  AVR_DEV int fast_terminate(const SharedTables&) {   // end_of_slice / I_PCM bin in register mode
+    const int b = cabac.terminate(in);
+    q.reserve(h, 1); q.put(h, CNT_TERM | uint32_t(b) << SYM_BIT_SHIFT);
+    return b;
+  }
   AVR_DEV int fast_bin(const SharedTables& t, int ctx) {   // an ordinary bin in register mode
     const int b = cabac.decision(in, t, &cstate[ctx]);
     q.reserve(h, 1); q.put(h, uint32_t(CNT_CTX + ctx) | uint32_t(b) << SYM_BIT_SHIFT);
@@ -1322,6 +1327,11 @@ struct Decompress {
     const uint32_t c = cnt[idx];
     const int b = rc.get(t.div[c >> 8], c & 0xFF);
     cnt[idx] = uint16_t(est_next(c, uint32_t(b), limit));
+    return b;
+  }
+  AVR_DEV int fast_terminate(const SharedTables& t) {   // end_of_slice / I_PCM bin in register mode
+    const int b = coded(t, CNT_TERM, LIMIT_ANY);
+    q.reserve(h, 1); q.put(h, uint32_t(b) << SYM_BIT_SHIFT | SYM_TERMINATE);
     return b;
   }
   AVR_DEV int fast_bin(const SharedTables& t, int ctx) {   // an ordinary bin in register mode
