@@ -71,6 +71,25 @@ __device__ void probe_decide(ProbeShared* sh, const ProbeArgs& a, uint64_t* r) {
   r[0] = uint64_t(t1 - t0); r[1] = a.iters; r[2] = acc + c.pos;
 }
 
+// 9: the 64-bit range-coder recurrence alone (RangeEnc::put, arithmetic_code.h:106-126): reciprocals, positions and bins
+//    in registers, nothing loaded inside the loop -- what one bin costs the range-coder warp at the very least
+__device__ void probe_range_put(ProbeShared* sh, const ProbeArgs& a, uint64_t* r) {
+  RangeEnc rc; rc.init(&sh->sink, sh->out, sizeof sh->out);
+  const DivMagic m0 = sh->tab.div[7], m1 = sh->tab.div[23], m2 = sh->tab.div[64], m3 = sh->tab.div[90];
+  const uint32_t bits = a.iters * 2654435761u;
+  const long long t0 = clock64();
+#pragma unroll 1
+  for (uint32_t i = 0; i < a.iters; i += 4) {
+    rc.put(m0, int((bits >> (i & 15)) & 1), 3);
+    rc.put(m1, int((bits >> ((i + 5) & 15)) & 1), 11);
+    rc.put(m2, int((bits >> ((i + 9) & 15)) & 1), 40);
+    rc.put(m3, int((bits >> ((i + 13) & 15)) & 1), 77);
+    if (sh->sink.n > 2000) sh->sink.n = 0;
+  }
+  const long long t1 = clock64();
+  r[0] = uint64_t(t1 - t0); r[1] = a.iters; r[2] = rc.low ^ rc.range;
+}
+
 // 2: the compress-side significance loop of a 4x4 block (distinct contexts, branch on the bin, last flag)
 __device__ void probe_sigloop_c(ProbeShared* sh, const ProbeArgs& a, uint64_t* r) {
   Compress d;
@@ -293,6 +312,7 @@ __global__ void __launch_bounds__(64, 1) avr_probe_kernel(ProbeArgs a) {
     if (WHICH == 3) probe_coded(&sh, a, r);
     if (WHICH == 4) probe_sigloop_d(&sh, a, r);
     if (WHICH == 7) probe_push(&sh, a, r);
+    if (WHICH == 9) probe_range_put(&sh, a, r);
     a.result[0] = r[0]; a.result[1] = r[1]; a.result[2] = r[2];
   }
 }
@@ -312,6 +332,7 @@ const char* avr_probe_name(int which) {
     "decompress coder warp: CABAC re-encoder over a ring of block / level entries (CoderDecompress::run)",
     "macroblock-level bin, compress: out-of-line CABAC decision on the shared-memory engine copy + ring entry",
     "compress range-coder warp alone: reciprocal + RangeEnc::put over a ring of records (RangeWarp::run)",
+    "64-bit range-coder recurrence alone, operands in registers (RangeEnc::put)",
   };
   return which >= 0 && which < int(sizeof names / sizeof names[0]) ? names[which] : nullptr;
 }
@@ -337,7 +358,8 @@ int avr_probe(int device, int which, uint32_t iters, uint64_t* cycles, uint64_t*
       case 5: avr_probe_kernel<5><<<1, 64>>>(a); break;
       case 6: avr_probe_kernel<6><<<1, 32>>>(a); break;
       case 7: avr_probe_kernel<7><<<1, 32>>>(a); break;
-      default: avr_probe_kernel<8><<<1, 32>>>(a); break;
+      case 8: avr_probe_kernel<8><<<1, 32>>>(a); break;
+      default: avr_probe_kernel<9><<<1, 32>>>(a); break;
     }
     if (cudaDeviceSynchronize() != cudaSuccess) { cudaGetLastError(); cudaFree(d); return AVR_ERR_CUDA; }
   }
